@@ -1,0 +1,288 @@
+/*
+ * hpcx.h — C ABI of libhpcx.so: the B200 (sm_100a) implementation of the libHPC
+ * data-parallel sparse hot path (CSR SpMV y = A*x and ghost-cell stencil sweeps).
+ *
+ * Drop-in boundary.  The reference (Liupeter01/libHPC) has no FFI for this path: its
+ * public surface is header-only C++ containers that callers index from their own
+ * OpenMP loops.  Every entry point below therefore cites the reference interface or
+ * loop it replaces (paths relative to the reference root):
+ *
+ *   grid containers   lib/hpc/include/HPCHighDimensionFlatArray.hpp:54-224
+ *   aligned storage   lib/hpc/include/AlignedAlloc.hpp:29-158
+ *   managed vectors   lib/gpu/util/include/cudaAllocator.hpp:39-83
+ *   error convention  lib/gpu/util/include/cudaHelper.cuh:10-27,96-101
+ *   x/y box sweeps    tests/test_hpc_benchmark/test_hpc_benchmark.cpp:354-368,425-441,
+ *                     444-457,575-601
+ *   static partition  tests/test_hpc_benchmark/test_hpc_benchmark.cpp:1356,1369-1377
+ *   stream overlap    lib/gpu/transfer_overlap_testsuite/src/cuda_tut_transfer_overlap.cu:92-103
+ *
+ * Conventions: plain pointers and sizes only; no exception crosses this boundary; every
+ * call returns hpcx_status (0 = ok) and leaves a message retrievable with
+ * hpcx_last_error_string().  `stream` arguments are cudaStream_t passed as void*
+ * (NULL = the context's own compute stream, and the call synchronises before returning).
+ * Handles are thread-compatible: one caller at a time per handle.
+ * There is no CPU fallback: every compute entry point fails with HPCX_CUDA_ERROR when no
+ * sm_100 device is usable.
+ */
+#ifndef HPCX_H_
+#define HPCX_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define HPCX_API __attribute__((visibility("default")))
+#else
+#define HPCX_API
+#endif
+
+typedef int32_t hpcx_status;
+enum {
+  HPCX_OK = 0,
+  HPCX_INVALID_ARG = 1,
+  HPCX_OOM = 2,          /* std::bad_alloc in the reference (AlignedAlloc.hpp:78-80) */
+  HPCX_CUDA_ERROR = 3,   /* std::system_error, CUDA category (cudaHelper.cuh:24-27) */
+  HPCX_NCCL_ERROR = 4,
+  HPCX_UNSUPPORTED = 5,
+  HPCX_OUT_OF_RANGE = 6  /* std::out_of_range of at() (HPCHighDimensionFlatArray.hpp:201-203) */
+};
+
+enum { HPCX_F32 = 0, HPCX_F64 = 1 };
+enum { HPCX_MEM_HOST = 0, HPCX_MEM_DEVICE = 1, HPCX_MEM_MANAGED = 2 };
+
+typedef struct hpcx_ctx_s *hpcx_ctx;
+typedef struct hpcx_csr_s *hpcx_csr;
+typedef struct hpcx_grid_s *hpcx_grid;
+
+/* ------------------------------------------------------------------ context */
+
+HPCX_API const char *hpcx_version(void);
+/* One context per process and device (one process per GPU). */
+HPCX_API hpcx_status hpcx_init(int32_t device, hpcx_ctx *out);
+HPCX_API hpcx_status hpcx_finalize(hpcx_ctx ctx);
+HPCX_API const char *hpcx_last_error_string(hpcx_ctx ctx);
+HPCX_API hpcx_status hpcx_synchronize(hpcx_ctx ctx);
+/* Number of kernels of this library launched through ctx since hpcx_init. */
+HPCX_API int64_t hpcx_launch_count(hpcx_ctx ctx);
+/* Pinned host buffers (the reference hands kernels CudaAllocator-backed vectors,
+ * cudaAllocator.hpp:39-83; pinned memory is what the copy pipeline needs). */
+HPCX_API hpcx_status hpcx_host_alloc(hpcx_ctx ctx, size_t bytes, void **out);
+HPCX_API hpcx_status hpcx_host_free(hpcx_ctx ctx, void *p);
+HPCX_API hpcx_status hpcx_device_alloc(hpcx_ctx ctx, size_t bytes, void **out);
+HPCX_API hpcx_status hpcx_device_free(hpcx_ctx ctx, void *p);
+HPCX_API hpcx_status hpcx_memcpy(hpcx_ctx ctx, void *dst, const void *src, size_t bytes);
+
+/* ------------------------------------------------- ghost-padded grid (a1, a2)
+ * hpcx_grid_desc describes hpc::HPCHighDimensionFlatArray<ndim,T,lo,hi>
+ * (HPCHighDimensionFlatArray.hpp:54-57): dim[] are the logical sizes, slowest first
+ * (row-major, last dimension fastest); lo/hi ghost cells on each side of every
+ * dimension.  The HOST layout is exactly the reference's flat buffer:
+ * stride[i] = prod_{j>i}(dim[j]+lo+hi), offset = sum stride[i]*(idx[i]+lo).
+ * The DEVICE layout keeps the same logical indexing but pads the fastest dimension so
+ * that interior x = 0 starts on a 128-byte boundary and the pitch is a multiple of
+ * 128 bytes (TMA needs 16-byte strides; vector stores need aligned rows). */
+typedef struct {
+  int32_t ndim;    /* 1..3 */
+  int32_t dtype;   /* HPCX_F32 | HPCX_F64 */
+  int32_t lo, hi;  /* Low_Bound, High_Bound */
+  int64_t dim[3];  /* slowest .. fastest */
+} hpcx_grid_desc;
+
+/* compute_stride_and_total (HPCHighDimensionFlatArray.hpp:161-171). Host only. */
+HPCX_API hpcx_status hpcx_grid_stride_total(const hpcx_grid_desc *d, int64_t *stride,
+                                            int64_t *total);
+/* unsafe_linearize (…:180-187) when checked == 0, safe_linearize (…:197-208) otherwise:
+ * returns HPCX_OUT_OF_RANGE where at() throws std::out_of_range. Host only. */
+HPCX_API hpcx_status hpcx_grid_linearize(const hpcx_grid_desc *d, const int64_t *idx,
+                                         int32_t checked, int64_t *offset);
+
+/* Value-initialised device grid (resize(dim, T{}), …:135-144: ghosts are zero). */
+HPCX_API hpcx_status hpcx_grid_create(hpcx_ctx ctx, const hpcx_grid_desc *d, hpcx_grid *out);
+HPCX_API hpcx_status hpcx_grid_destroy(hpcx_grid g);
+/* Copy the whole padded array (ghosts included) host(reference layout) <-> device. */
+HPCX_API hpcx_status hpcx_grid_upload(hpcx_grid g, const void *host_flat, void *stream);
+HPCX_API hpcx_status hpcx_grid_download(hpcx_grid g, void *host_flat, void *stream);
+/* Device layout introspection: x offset of interior x=0 inside a row, row pitch and
+ * total element count, and the raw device pointer (data() of the device mirror). */
+HPCX_API hpcx_status hpcx_grid_device_layout(hpcx_grid g, int64_t *xoff, int64_t *pitch,
+                                             int64_t *total, void **dev_ptr);
+
+/* --------------------------------------------------- stencil sweeps (a3, a4, a10) */
+enum {
+  /* b(y,x) = sum_{k=-r..r} a(y,x+k), k ascending from 0.0f: BM_x_blur,
+   * BM_x_blur_tiling_simd_prefetch (test_hpc_benchmark.cpp:354-368, 425-441). */
+  HPCX_STENCIL_BOX_X = 1,
+  /* b(y,x) = sum_{k=-r..r} a(y+k,x): BM_y_blur, BM_YXx_blur_tiling_prefetch_streamed_IPL
+   * (test_hpc_benchmark.cpp:444-457, 575-601). */
+  HPCX_STENCIL_BOX_Y = 2,
+  /* out = (in[z-1]+in[y-1]+in[x-1]+in[x+1]+in[y+1]+in[z+1]) * (1/6), adds in that
+   * (ascending address) order; 3-D, ghost >= 1; ping-pong for steps > 1. */
+  HPCX_STENCIL_JACOBI7 = 3
+};
+enum { HPCX_VARIANT_AUTO = 0, HPCX_VARIANT_TMA = 1, HPCX_VARIANT_DIRECT = 2 };
+typedef struct {
+  int32_t kind;
+  int32_t radius;   /* BOX_*: r (the reference uses nblur = 8); JACOBI7: ignored */
+  int32_t variant;  /* HPCX_VARIANT_* */
+  int32_t zsplit;   /* JACOBI7: number of z segments per (x,y) tile; 0 = auto */
+} hpcx_stencil_desc;
+
+/* Reads the (ghost-padded) grid `in`, writes the interior of `out`.
+ * BOX_*: in has lo,hi >= radius along the swept axis, out may have any ghost width,
+ *        steps must be 1.
+ * JACOBI7: in/out same shape, lo,hi >= 1, both hold the same (Dirichlet) ghost values;
+ *        after `steps` sweeps the newest iterate is in `out` and the previous one in
+ *        `in` (the two handles swap device buffers when steps is even). */
+HPCX_API hpcx_status hpcx_stencil_sweep(hpcx_grid in, hpcx_grid out,
+                                        const hpcx_stencil_desc *st, int32_t steps,
+                                        void *stream);
+
+/* Ghost-cell pack / unpack (a11).  axis: 0 = slowest.  side: 0 = low, 1 = high.
+ * pack copies the `width` INTERIOR planes adjacent to that side into a dense buffer
+ * (planes in ascending index order; each plane dense over the full padded extent of the
+ * faster axes and the interior extent of the slower ones is also padded, i.e. a plane is
+ * exactly what the neighbour needs as its ghost plane); unpack writes a buffer of the
+ * same shape into the `width` GHOST planes on that side.  buf may be host or device. */
+HPCX_API hpcx_status hpcx_grid_face_elems(hpcx_grid g, int32_t axis, int32_t width,
+                                          int64_t *elems);
+HPCX_API hpcx_status hpcx_grid_pack_face(hpcx_grid g, int32_t axis, int32_t side,
+                                         int32_t width, void *buf, int32_t buf_mem,
+                                         void *stream);
+HPCX_API hpcx_status hpcx_grid_unpack_face(hpcx_grid g, int32_t axis, int32_t side,
+                                           int32_t width, const void *buf, int32_t buf_mem,
+                                           void *stream);
+
+/* ------------------------------------------------------------- CSR matrix (a7-a9) */
+typedef struct {
+  int64_t nrows, ncols, nnz;
+  const void *row_ptr;   /* nrows+1 entries */
+  int32_t idx_bytes;     /* 4 (int32) or 8 (int64) row_ptr entries */
+  int32_t dtype;         /* HPCX_F32 | HPCX_F64 */
+  const int32_t *col_idx;/* nnz entries, ascending within a row */
+  const void *values;    /* nnz entries */
+  int32_t mem;           /* where row_ptr/col_idx/values live: HPCX_MEM_* */
+  int32_t reserved;
+} hpcx_csr_desc;
+
+enum {
+  HPCX_SPMV_AUTO = 0,
+  HPCX_SPMV_STREAM = 1,  /* row-blocked, TMA-bulk staged tiles, adaptive row reduction */
+  HPCX_SPMV_VECTOR = 2,  /* classic sub-warp vector-per-row */
+  HPCX_SPMV_SELL = 3     /* SELL-C-sigma repack */
+};
+typedef struct {
+  int32_t kernel;      /* HPCX_SPMV_* */
+  int32_t tile_nnz;    /* STREAM: nonzeros staged per CTA (0 = default) */
+  int32_t sell_c;      /* SELL slice height (0 = 32) */
+  int32_t sell_sigma;  /* SELL sort window in rows (0 = 1024; 1 = no sorting) */
+  int32_t lanes_per_row; /* VECTOR: 0 = from mean row length */
+  int32_t reserved[3];
+} hpcx_csr_opts;
+
+/* Uploads (or adopts, when already on the device the arrays are copied device-to-device)
+ * the matrix, builds row blocks / bins / optional SELL repack on the way. */
+HPCX_API hpcx_status hpcx_csr_create(hpcx_ctx ctx, const hpcx_csr_desc *d,
+                                     const hpcx_csr_opts *opts, hpcx_csr *out);
+HPCX_API hpcx_status hpcx_csr_destroy(hpcx_csr A);
+/* y = A*x.  x: ncols entries, y: nrows entries of A's dtype; each may be host, device or
+ * managed memory (HPCX_MEM_*).  Host operands are staged through the copy pipeline. */
+HPCX_API hpcx_status hpcx_spmv(hpcx_csr A, const void *x, int32_t x_mem, void *y,
+                               int32_t y_mem, void *stream);
+/* Round trip of the device-resident CSR arrays (bit-exact structure check). Any pointer
+ * may be NULL. row_ptr is written with the idx_bytes the matrix was created with. */
+HPCX_API hpcx_status hpcx_csr_download(hpcx_csr A, void *row_ptr, int32_t *col_idx,
+                                       void *values);
+/* Row-block table of the STREAM kernel: per block {row0, nrows, part, lanes, p0, p1}
+ * as 6 int64 (part >= 0 marks one chunk of a row longer than a tile). */
+HPCX_API hpcx_status hpcx_csr_rowblocks(hpcx_csr A, int64_t *nblocks, int64_t *out,
+                                        int64_t capacity);
+/* Row-length histogram by ceil(log2(len)) bin: bins[0] = empty rows, bins[k] = rows
+ * with 2^(k-1) < len <= 2^k (k = 1: len 1..2 -> see DESIGN.md), 34 entries. */
+HPCX_API hpcx_status hpcx_csr_row_bins(hpcx_csr A, int64_t *bins34);
+/* SELL-C-sigma arrays (only for matrices created with HPCX_SPMV_SELL): sizes first
+ * (any output pointer may be NULL), then data. */
+HPCX_API hpcx_status hpcx_csr_sell_info(hpcx_csr A, int64_t *nslices, int64_t *padded_nnz,
+                                        int32_t *c, int32_t *sigma);
+HPCX_API hpcx_status hpcx_csr_sell_download(hpcx_csr A, int32_t *perm, int64_t *slice_ptr,
+                                            int32_t *slice_len, int32_t *col, void *val);
+
+/* ------------------------------------------------- partitioner + halo maps (a12) */
+/* Contiguous row blocks: bounds[p] .. bounds[p+1] for p in [0, nparts).
+ * mode 0: balanced by rows with the reference's static chunking idiom
+ *         chunk = ceil(n/nparts), [p*chunk, min((p+1)*chunk, n))
+ *         (test_hpc_benchmark.cpp:1356,1371-1372);
+ * mode 1: balanced by nonzeros (first row whose prefix nnz reaches p*nnz/nparts).
+ * row_ptr is a host array. */
+HPCX_API hpcx_status hpcx_partition_rows(int64_t nrows, const void *row_ptr,
+                                         int32_t idx_bytes, int32_t nparts, int32_t mode,
+                                         int64_t *bounds);
+/* z-slab split of n planes: same static chunking as mode 0. */
+HPCX_API hpcx_status hpcx_partition_slabs(int64_t n, int32_t nparts, int64_t *bounds);
+
+/* Local view of rank `rank`'s row block of a host CSR matrix (square, ncols == nrows,
+ * x partitioned like the rows).  Columns are renumbered [owned | halo], halo sorted by
+ * (owner, global column).  Two-call protocol: call with all output pointers NULL to get
+ * the sizes, allocate, call again.
+ *   local_row_ptr[nloc+1] (int64), local_col[nnz_loc] (int32), value positions unchanged
+ *   halo_gcol[nhalo] (int64 global column of each halo slot)
+ *   recv_counts[nparts], send_counts[nparts] (int64), send_idx[nsend] (int32 local owned
+ *   index to gather, grouped by destination rank ascending, ascending within a group)
+ *   row_kind[nloc] (uint8: 0 interior = all columns owned, 1 boundary) */
+typedef struct {
+  int64_t nloc, nnz_loc, nhalo, nsend;
+} hpcx_halo_sizes;
+HPCX_API hpcx_status hpcx_csr_localize(int64_t nrows, const void *row_ptr, int32_t idx_bytes,
+                                       const int32_t *col_idx, const int64_t *bounds,
+                                       int32_t nparts, int32_t rank, hpcx_halo_sizes *sizes,
+                                       int64_t *local_row_ptr, int32_t *local_col,
+                                       int64_t *halo_gcol, int64_t *recv_counts,
+                                       int64_t *send_counts, int32_t *send_idx,
+                                       uint8_t *row_kind);
+
+/* ------------------------------------------------ multi-GPU transport (a13)
+ * One process per GPU.  The caller bootstraps (e.g. through torch.distributed or MPI):
+ * rank 0 calls hpcx_comm_unique_id, broadcasts the 128 bytes, every rank calls
+ * hpcx_comm_init.  Peer (NVLink) windows for the fused halo path are exchanged with
+ * hpcx_comm_ipc_export / hpcx_comm_ipc_open. */
+HPCX_API hpcx_status hpcx_comm_unique_id(hpcx_ctx ctx, void *id128);
+HPCX_API hpcx_status hpcx_comm_init(hpcx_ctx ctx, int32_t nranks, int32_t rank,
+                                    const void *id128);
+HPCX_API hpcx_status hpcx_comm_finalize(hpcx_ctx ctx);
+HPCX_API hpcx_status hpcx_comm_barrier(hpcx_ctx ctx);
+HPCX_API hpcx_status hpcx_comm_ipc_export(hpcx_ctx ctx, const void *dev_ptr, void *handle64);
+HPCX_API hpcx_status hpcx_comm_ipc_open(hpcx_ctx ctx, const void *handle64, void **peer_ptr);
+HPCX_API hpcx_status hpcx_comm_ipc_close(hpcx_ctx ctx, void *peer_ptr);
+
+/* Distributed stencil: every rank owns a z-slab (axis 0) grid pair created with
+ * hpcx_grid_create; neighbours are rank-1 / rank+1 (no periodic wrap: the outermost
+ * ghost planes stay Dirichlet).  transport: 0 = NCCL send/recv on the comm stream
+ * overlapped with the interior sweep (1 is reserved for fused peer stores, where the
+ * boundary planes are written straight into the neighbour's ghost planes over NVLink). */
+typedef struct hpcx_halo_plan_s *hpcx_halo_plan;
+HPCX_API hpcx_status hpcx_stencil_dist_plan(hpcx_ctx ctx, hpcx_grid in, hpcx_grid out,
+                                            const hpcx_stencil_desc *st, int32_t transport,
+                                            hpcx_halo_plan *out_plan);
+HPCX_API hpcx_status hpcx_stencil_dist_sweep(hpcx_halo_plan plan, int32_t steps, void *stream);
+HPCX_API hpcx_status hpcx_stencil_dist_destroy(hpcx_halo_plan plan);
+
+/* Distributed SpMV: A was created from the LOCAL matrix produced by hpcx_csr_localize
+ * (ncols = nloc + nhalo).  hpcx_csr_set_halo attaches the exchange lists; hpcx_spmv_dist
+ * then runs {gather boundary x | interior rows} -> exchange -> boundary rows.
+ * x_local has nloc entries (device), y_local nloc entries (device). */
+HPCX_API hpcx_status hpcx_csr_set_halo(hpcx_csr A, int64_t nloc, int64_t nhalo,
+                                       const int64_t *recv_counts, const int64_t *send_counts,
+                                       const int32_t *send_idx, const uint8_t *row_kind);
+/* Device buffer [owned | halo] the distributed product reads x from; callers that write
+ * their owned x entries straight into it and pass it as x_local avoid a device copy. */
+HPCX_API hpcx_status hpcx_csr_x_buffer(hpcx_csr A, void **x_full);
+HPCX_API hpcx_status hpcx_spmv_dist(hpcx_csr A, const void *x_local, void *y_local,
+                                    void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HPCX_H_ */

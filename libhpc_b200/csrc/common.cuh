@@ -1,0 +1,141 @@
+// common.cuh — shared internals of libhpcx (context, error plumbing, PTX helpers).
+// Error convention follows the reference's checkCuda/throwCudaError
+// (lib/gpu/util/include/cudaHelper.cuh:10-27,96-101) but nothing is thrown across the
+// C ABI: failures become an hpcx_status plus a message stored in the context.
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "../../include/hpcx.h"
+
+struct hpcx_ctx_s {
+  int device = 0;
+  int sm_count = 148;
+  int cc_major = 0, cc_minor = 0;
+  cudaStream_t compute = nullptr;  // default stream of the context
+  cudaStream_t comm = nullptr;     // halo exchange / copy pipeline
+  cudaStream_t copy_in = nullptr, copy_out = nullptr;
+  cudaEvent_t ev[8] = {};
+  int64_t launches = 0;
+  bool debug_sync = false;  // HPCX_DEBUG_SYNC=1: sync + check after every launch
+                            // (reference idiom, cuda_radix_sort_v4.cu:104-107)
+  std::string last_error;
+  // multi-GPU
+  int nranks = 1, rank = 0;
+  void *nccl_lib = nullptr;
+  void *nccl_comm = nullptr;
+  // driver entry points
+  void *encode_tiled = nullptr;  // cuTensorMapEncodeTiled
+};
+
+namespace hpcx {
+
+inline hpcx_status fail(hpcx_ctx ctx, hpcx_status st, const std::string &msg) {
+  if (ctx) ctx->last_error = msg;
+  return st;
+}
+
+#define HPCX_CUDA(ctx, expr)                                                          \
+  do {                                                                                \
+    cudaError_t e__ = (expr);                                                         \
+    if (e__ != cudaSuccess) {                                                         \
+      char b__[512];                                                                  \
+      snprintf(b__, sizeof b__, "%s:%d: %s: %s", __FILE__, __LINE__, #expr,           \
+               cudaGetErrorString(e__));                                              \
+      return hpcx::fail((ctx),                                                        \
+                        e__ == cudaErrorMemoryAllocation ? HPCX_OOM : HPCX_CUDA_ERROR, \
+                        b__);                                                         \
+    }                                                                                 \
+  } while (0)
+
+#define HPCX_REQUIRE(ctx, cond, msg)                                            \
+  do {                                                                          \
+    if (!(cond)) return hpcx::fail((ctx), HPCX_INVALID_ARG, std::string(msg)); \
+  } while (0)
+
+// Called after every kernel launch of the library.
+inline hpcx_status after_launch(hpcx_ctx ctx, const char *what, int n = 1) {
+  ctx->launches += n;
+  cudaError_t e = cudaGetLastError();
+  if (e == cudaSuccess && ctx->debug_sync) e = cudaDeviceSynchronize();
+  if (e != cudaSuccess)
+    return fail(ctx, HPCX_CUDA_ERROR, std::string(what) + ": " + cudaGetErrorString(e));
+  return HPCX_OK;
+}
+
+inline size_t dtype_size(int dtype) { return dtype == HPCX_F64 ? 8 : 4; }
+inline int64_t round_up(int64_t v, int64_t m) { return (v + m - 1) / m * m; }
+
+// ----------------------------------------------------------------- device PTX helpers
+#ifdef __CUDACC__
+__device__ __forceinline__ uint32_t smem_u32(const void *p) {
+  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_fence_init() {
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)),
+               "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra DONE_%=;\n"
+      "bra WAIT_%=;\n"
+      "DONE_%=:\n"
+      "}\n" ::"r"(smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}
+// 1-D bulk copy global -> shared (TMA engine, SASS UBLKCP). 16-byte aligned, size % 16 == 0.
+__device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t bytes,
+                                         uint64_t *bar) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::
+          "r"(smem_u32(dst)),
+      "l"(src), "r"(bytes), "r"(smem_u32(bar))
+      : "memory");
+}
+// Tiled tensor loads (TMA, SASS UTMALDG).
+__device__ __forceinline__ void tma_load_2d(void *dst, const CUtensorMap *map, int c0, int c1,
+                                            uint64_t *bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes "
+      "[%0], [%1, {%2, %3}], [%4];" ::"r"(smem_u32(dst)),
+      "l"(reinterpret_cast<uint64_t>(map)), "r"(c0), "r"(c1), "r"(smem_u32(bar))
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_3d(void *dst, const CUtensorMap *map, int c0, int c1,
+                                            int c2, uint64_t *bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes "
+      "[%0], [%1, {%2, %3, %4}], [%5];" ::"r"(smem_u32(dst)),
+      "l"(reinterpret_cast<uint64_t>(map)), "r"(c0), "r"(c1), "r"(c2), "r"(smem_u32(bar))
+      : "memory");
+}
+__device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap *map) {
+  asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(map)) : "memory");
+}
+#endif
+
+// Host: build a tiled tensor map through the driver entry point held by the context.
+hpcx_status make_tensor_map(hpcx_ctx ctx, CUtensorMap *map, int dtype, int rank, void *base,
+                            const uint64_t *dims, const uint64_t *strides_bytes,
+                            const uint32_t *box);
+
+}  // namespace hpcx

@@ -1,0 +1,435 @@
+// dist.cu — multi-GPU transport: one process per GPU, NCCL
+// send/recv between neighbouring ranks over NVLink, overlapped with interior compute on a
+// second stream; the event-chained two-stream shape generalises the only overlap idiom the
+// reference has (lib/gpu/transfer_overlap_testsuite/src/cuda_tut_transfer_overlap.cu:92-103).
+//
+// NCCL is bound at run time (dlopen of libnccl.so.2 — the copy torch already mapped when the
+// caller is a torch.distributed program) so that libhpcx.so loads on machines without it.
+#include <dlfcn.h>
+#include <nccl.h>
+
+#include <algorithm>
+
+#include "grid.cuh"
+#include "spmv.cuh"
+
+using namespace hpcx;
+
+namespace hpcx {
+hpcx_status jacobi7_launch(hpcx_grid_s *g, void *src, void *dst, int variant, int zsplit,
+                           int64_t zbeg, int64_t zend, cudaStream_t s);
+hpcx_status spmv_launch_blocks(hpcx_csr A, const RowBlock *d_blocks, int64_t nblocks, const void *x,
+                               void *y, cudaStream_t s);
+hpcx_status spmv_launch_fixup_tables(hpcx_csr A, const int32_t *long_row, const int32_t *long_off,
+                                     int64_t nlong, void *y, cudaStream_t s);
+void spmv_build_rowblocks(const int64_t *rp, int64_t nrows, int tile, const uint8_t *kind, int want,
+                          std::vector<RowBlock> &out, std::vector<int32_t> *long_row,
+                          std::vector<int32_t> *long_off);
+}  // namespace hpcx
+
+namespace {
+
+struct NcclApi {
+  ncclResult_t (*GetUniqueId)(ncclUniqueId *);
+  ncclResult_t (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int);
+  ncclResult_t (*CommDestroy)(ncclComm_t);
+  ncclResult_t (*Send)(const void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t);
+  ncclResult_t (*Recv)(void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t);
+  ncclResult_t (*GroupStart)();
+  ncclResult_t (*GroupEnd)();
+  ncclResult_t (*AllReduce)(const void *, void *, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t,
+                            cudaStream_t);
+  const char *(*GetErrorString)(ncclResult_t);
+};
+NcclApi g_nccl{};
+
+hpcx_status load_nccl(hpcx_ctx ctx) {
+  if (ctx->nccl_lib) return HPCX_OK;
+  void *h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+  if (!h) h = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+  if (!h) return fail(ctx, HPCX_NCCL_ERROR, std::string("cannot load libnccl: ") + dlerror());
+#define HPCX_SYM(field, name)                                                        \
+  g_nccl.field = reinterpret_cast<decltype(g_nccl.field)>(dlsym(h, name));           \
+  if (!g_nccl.field) return fail(ctx, HPCX_NCCL_ERROR, "libnccl lacks " name)
+  HPCX_SYM(GetUniqueId, "ncclGetUniqueId");
+  HPCX_SYM(CommInitRank, "ncclCommInitRank");
+  HPCX_SYM(CommDestroy, "ncclCommDestroy");
+  HPCX_SYM(Send, "ncclSend");
+  HPCX_SYM(Recv, "ncclRecv");
+  HPCX_SYM(GroupStart, "ncclGroupStart");
+  HPCX_SYM(GroupEnd, "ncclGroupEnd");
+  HPCX_SYM(AllReduce, "ncclAllReduce");
+  HPCX_SYM(GetErrorString, "ncclGetErrorString");
+#undef HPCX_SYM
+  ctx->nccl_lib = h;
+  return HPCX_OK;
+}
+
+#define HPCX_NCCL(ctx, expr)                                                             \
+  do {                                                                                   \
+    ncclResult_t r__ = (expr);                                                           \
+    if (r__ != ncclSuccess)                                                              \
+      return hpcx::fail((ctx), HPCX_NCCL_ERROR,                                          \
+                        std::string(#expr) + ": " + g_nccl.GetErrorString(r__));         \
+  } while (0)
+
+inline ncclComm_t comm_of(hpcx_ctx ctx) { return static_cast<ncclComm_t>(ctx->nccl_comm); }
+inline ncclDataType_t nccl_type(int dtype) { return dtype == HPCX_F64 ? ncclFloat64 : ncclFloat32; }
+
+}  // namespace
+
+// ------------------------------------------------------------------ distributed stencil
+struct hpcx_halo_plan_s {
+  hpcx_ctx ctx = nullptr;
+  hpcx_grid in = nullptr, out = nullptr;
+  hpcx_stencil_desc st{};
+  int transport = 0;
+  cudaEvent_t ev_bnd = nullptr, ev_recv = nullptr, ev_start = nullptr;
+};
+
+namespace {
+
+// Exchange one ghost plane per side of buffer `buf` (device layout of grid g) with the z
+// neighbours.  Planes are contiguous in the device layout, so nothing is packed.
+hpcx_status exchange_planes(hpcx_grid g, void *buf, cudaStream_t s) {
+  hpcx_ctx ctx = g->ctx;
+  if (ctx->nranks <= 1) return HPCX_OK;
+  const int64_t plane = g->ext[1] * g->pitch;
+  char *base = static_cast<char *>(buf);
+  auto at = [&](int64_t z) { return base + (z + g->glo[0]) * plane * g->es; };
+  const ncclDataType_t ty = nccl_type(g->desc.dtype);
+  const int lo = ctx->rank - 1, hi = ctx->rank + 1;
+  HPCX_NCCL(ctx, g_nccl.GroupStart());
+  if (lo >= 0) {
+    HPCX_NCCL(ctx, g_nccl.Send(at(0), (size_t)plane, ty, lo, comm_of(ctx), s));
+    HPCX_NCCL(ctx, g_nccl.Recv(at(-1), (size_t)plane, ty, lo, comm_of(ctx), s));
+  }
+  if (hi < ctx->nranks) {
+    HPCX_NCCL(ctx, g_nccl.Send(at(g->n[0] - 1), (size_t)plane, ty, hi, comm_of(ctx), s));
+    HPCX_NCCL(ctx, g_nccl.Recv(at(g->n[0]), (size_t)plane, ty, hi, comm_of(ctx), s));
+  }
+  HPCX_NCCL(ctx, g_nccl.GroupEnd());
+  return HPCX_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+hpcx_status hpcx_comm_unique_id(hpcx_ctx ctx, void *id128) {
+  if (!ctx || !id128) return HPCX_INVALID_ARG;
+  hpcx_status st = load_nccl(ctx);
+  if (st != HPCX_OK) return st;
+  static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId is 128 bytes");
+  ncclUniqueId id;
+  HPCX_NCCL(ctx, g_nccl.GetUniqueId(&id));
+  memcpy(id128, &id, sizeof id);
+  return HPCX_OK;
+}
+
+hpcx_status hpcx_comm_init(hpcx_ctx ctx, int32_t nranks, int32_t rank, const void *id128) {
+  if (!ctx || !id128) return HPCX_INVALID_ARG;
+  HPCX_REQUIRE(ctx, nranks >= 1 && rank >= 0 && rank < nranks, "bad rank / nranks");
+  HPCX_REQUIRE(ctx, ctx->nccl_comm == nullptr, "communicator already initialised");
+  hpcx_status st = load_nccl(ctx);
+  if (st != HPCX_OK) return st;
+  ncclUniqueId id;
+  memcpy(&id, id128, sizeof id);
+  ncclComm_t comm;
+  HPCX_CUDA(ctx, cudaSetDevice(ctx->device));
+  HPCX_NCCL(ctx, g_nccl.CommInitRank(&comm, nranks, id, rank));
+  ctx->nccl_comm = comm;
+  ctx->nranks = nranks;
+  ctx->rank = rank;
+  return HPCX_OK;
+}
+
+hpcx_status hpcx_comm_finalize(hpcx_ctx ctx) {
+  if (!ctx) return HPCX_INVALID_ARG;
+  if (ctx->nccl_comm) {
+    cudaDeviceSynchronize();
+    g_nccl.CommDestroy(comm_of(ctx));
+    ctx->nccl_comm = nullptr;
+  }
+  ctx->nranks = 1;
+  ctx->rank = 0;
+  return HPCX_OK;
+}
+
+hpcx_status hpcx_comm_barrier(hpcx_ctx ctx) {
+  if (!ctx) return HPCX_INVALID_ARG;
+  if (ctx->nranks <= 1 || !ctx->nccl_comm) {
+    HPCX_CUDA(ctx, cudaDeviceSynchronize());
+    return HPCX_OK;
+  }
+  static thread_local float *token = nullptr;
+  if (!token) HPCX_CUDA(ctx, cudaMalloc((void **)&token, 16));
+  HPCX_CUDA(ctx, cudaDeviceSynchronize());
+  HPCX_NCCL(ctx, g_nccl.AllReduce(token, token, 1, ncclFloat32, ncclSum, comm_of(ctx), ctx->comm));
+  HPCX_CUDA(ctx, cudaStreamSynchronize(ctx->comm));
+  return HPCX_OK;
+}
+
+hpcx_status hpcx_comm_ipc_export(hpcx_ctx ctx, const void *dev_ptr, void *handle64) {
+  if (!ctx || !dev_ptr || !handle64) return HPCX_INVALID_ARG;
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t is 64 bytes");
+  cudaIpcMemHandle_t h;
+  HPCX_CUDA(ctx, cudaIpcGetMemHandle(&h, const_cast<void *>(dev_ptr)));
+  memcpy(handle64, &h, sizeof h);
+  return HPCX_OK;
+}
+
+hpcx_status hpcx_comm_ipc_open(hpcx_ctx ctx, const void *handle64, void **peer_ptr) {
+  if (!ctx || !handle64 || !peer_ptr) return HPCX_INVALID_ARG;
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle64, sizeof h);
+  HPCX_CUDA(ctx, cudaIpcOpenMemHandle(peer_ptr, h, cudaIpcMemLazyEnablePeerAccess));
+  return HPCX_OK;
+}
+
+hpcx_status hpcx_comm_ipc_close(hpcx_ctx ctx, void *peer_ptr) {
+  if (!ctx) return HPCX_INVALID_ARG;
+  HPCX_CUDA(ctx, cudaIpcCloseMemHandle(peer_ptr));
+  return HPCX_OK;
+}
+
+hpcx_status hpcx_stencil_dist_plan(hpcx_ctx ctx, hpcx_grid in, hpcx_grid out,
+                                   const hpcx_stencil_desc *st, int32_t transport,
+                                   hpcx_halo_plan *out_plan) {
+  if (!ctx || !in || !out || !st || !out_plan) return HPCX_INVALID_ARG;
+  *out_plan = nullptr;
+  HPCX_REQUIRE(ctx, st->kind == HPCX_STENCIL_JACOBI7, "distributed sweeps support JACOBI7");
+  HPCX_REQUIRE(ctx, in->desc.ndim == 3 && out->desc.ndim == 3, "JACOBI7 takes 3-D grids");
+  HPCX_REQUIRE(ctx, in->desc.dtype == out->desc.dtype, "grids differ in dtype");
+  for (int i = 0; i < 3; ++i)
+    HPCX_REQUIRE(ctx, in->desc.dim[i] == out->desc.dim[i], "grids differ in logical extent");
+  HPCX_REQUIRE(ctx, in->desc.lo >= 1 && in->desc.hi >= 1 && in->desc.lo == out->desc.lo &&
+                        in->desc.hi == out->desc.hi,
+               "JACOBI7 needs identical ghost widths >= 1 on both grids");
+  HPCX_REQUIRE(ctx, in->n[0] >= 1, "a slab needs at least one plane");
+  if (transport != 0)
+    return fail(ctx, HPCX_UNSUPPORTED, "only transport 0 (NCCL send/recv) is available");
+  if (ctx->nranks > 1 && !ctx->nccl_comm)
+    return fail(ctx, HPCX_NCCL_ERROR, "hpcx_comm_init has not been called");
+  hpcx_halo_plan p = new (std::nothrow) hpcx_halo_plan_s();
+  if (!p) return fail(ctx, HPCX_OOM, "host allocation failed");
+  p->ctx = ctx;
+  p->in = in;
+  p->out = out;
+  p->st = *st;
+  p->transport = transport;
+  cudaError_t e = cudaEventCreateWithFlags(&p->ev_bnd, cudaEventDisableTiming);
+  if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->ev_recv, cudaEventDisableTiming);
+  if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->ev_start, cudaEventDisableTiming);
+  if (e != cudaSuccess) {
+    delete p;
+    return fail(ctx, HPCX_CUDA_ERROR, std::string("cudaEventCreate: ") + cudaGetErrorString(e));
+  }
+  *out_plan = p;
+  return HPCX_OK;
+}
+
+// Per step t (src -> dst):
+//   compute stream: [wait ghosts of src] boundary planes z = 0, n-1  -> record ev_bnd
+//   comm stream   : [wait ev_bnd] send dst boundary planes / receive dst ghost planes
+//   compute stream: interior planes 1 .. n-2 (overlaps the exchange)
+// The ghost planes a step needs were produced by the previous step's exchange.
+hpcx_status hpcx_stencil_dist_sweep(hpcx_halo_plan p, int32_t steps, void *stream) {
+  if (!p) return HPCX_INVALID_ARG;
+  hpcx_ctx ctx = p->ctx;
+  HPCX_REQUIRE(ctx, steps >= 1, "steps must be >= 1");
+  hpcx_grid g = p->in;
+  cudaStream_t cs = stream ? (cudaStream_t)stream : ctx->compute;
+  cudaStream_t ms = ctx->comm;
+  const int64_t nz = g->n[0];
+  hpcx_status rc = HPCX_OK;
+
+  // Make the ghosts of the first source iterate consistent with the neighbours.
+  HPCX_CUDA(ctx, cudaEventRecord(p->ev_start, cs));
+  HPCX_CUDA(ctx, cudaStreamWaitEvent(ms, p->ev_start, 0));
+  rc = exchange_planes(g, p->in->dev, ms);
+  if (rc != HPCX_OK) return rc;
+  HPCX_CUDA(ctx, cudaEventRecord(p->ev_recv, ms));
+
+  void *src = p->in->dev, *dst = p->out->dev;
+  for (int t = 0; t < steps; ++t) {
+    HPCX_CUDA(ctx, cudaStreamWaitEvent(cs, p->ev_recv, 0));
+    rc = jacobi7_launch(g, src, dst, p->st.variant, 1, 0, 1, cs);
+    if (rc == HPCX_OK && nz > 1) rc = jacobi7_launch(g, src, dst, p->st.variant, 1, nz - 1, nz, cs);
+    if (rc != HPCX_OK) return rc;
+    if (t + 1 < steps) {
+      HPCX_CUDA(ctx, cudaEventRecord(p->ev_bnd, cs));
+      HPCX_CUDA(ctx, cudaStreamWaitEvent(ms, p->ev_bnd, 0));
+      rc = exchange_planes(g, dst, ms);
+      if (rc != HPCX_OK) return rc;
+      HPCX_CUDA(ctx, cudaEventRecord(p->ev_recv, ms));
+    }
+    if (nz > 2) {
+      rc = jacobi7_launch(g, src, dst, p->st.variant, p->st.zsplit, 1, nz - 1, cs);
+      if (rc != HPCX_OK) return rc;
+    }
+    std::swap(src, dst);
+  }
+  if ((steps & 1) == 0) std::swap(p->in->dev, p->out->dev);
+  if (!stream) HPCX_CUDA(ctx, cudaStreamSynchronize(cs));
+  return HPCX_OK;
+}
+
+hpcx_status hpcx_stencil_dist_destroy(hpcx_halo_plan p) {
+  if (!p) return HPCX_INVALID_ARG;
+  cudaEventDestroy(p->ev_bnd);
+  cudaEventDestroy(p->ev_recv);
+  cudaEventDestroy(p->ev_start);
+  delete p;
+  return HPCX_OK;
+}
+
+}  // extern "C"
+
+// ------------------------------------------------------------------ distributed SpMV
+namespace {
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+gather_boundary_x_kernel(const T *__restrict__ x, const int32_t *__restrict__ send_idx,
+                         T *__restrict__ sendbuf, int64_t n) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n;
+       i += (int64_t)gridDim.x * blockDim.x)
+    sendbuf[i] = __ldg(x + send_idx[i]);
+}
+
+}  // namespace
+
+extern "C" {
+
+hpcx_status hpcx_csr_set_halo(hpcx_csr A, int64_t nloc, int64_t nhalo, const int64_t *recv_counts,
+                              const int64_t *send_counts, const int32_t *send_idx,
+                              const uint8_t *row_kind) {
+  if (!A) return HPCX_INVALID_ARG;
+  hpcx_ctx ctx = A->ctx;
+  HPCX_REQUIRE(ctx, nloc == A->nrows && nloc + nhalo == A->ncols,
+               "local matrix must have nloc rows and nloc + nhalo columns");
+  HPCX_REQUIRE(ctx, recv_counts && send_counts && row_kind, "null halo table");
+  const int P = ctx->nranks;
+  A->nloc = nloc;
+  A->nhalo = nhalo;
+  A->recv_counts.assign(recv_counts, recv_counts + P);
+  A->send_counts.assign(send_counts, send_counts + P);
+  int64_t nsend = 0, nrecv = 0;
+  for (int q = 0; q < P; ++q) {
+    HPCX_REQUIRE(ctx, send_counts[q] >= 0 && recv_counts[q] >= 0, "negative halo count");
+    nsend += send_counts[q];
+    nrecv += recv_counts[q];
+  }
+  HPCX_REQUIRE(ctx, nrecv == nhalo, "recv_counts do not add up to nhalo");
+  HPCX_REQUIRE(ctx, nsend == 0 || send_idx, "null send_idx");
+  A->nsend = nsend;
+  cudaFree(A->d_send_idx);
+  cudaFree(A->d_sendbuf);
+  cudaFree(A->d_xfull);
+  cudaFree(A->d_blocks_int);
+  cudaFree(A->d_blocks_bnd);
+  cudaFree(A->d_long_row_dist);
+  cudaFree(A->d_long_off_dist);
+  A->d_send_idx = nullptr;
+  A->d_sendbuf = A->d_xfull = nullptr;
+  A->d_blocks_int = A->d_blocks_bnd = nullptr;
+  A->d_long_row_dist = A->d_long_off_dist = nullptr;
+  HPCX_CUDA(ctx, cudaMalloc((void **)&A->d_send_idx, std::max<size_t>((size_t)nsend, 1) * 4));
+  HPCX_CUDA(ctx, cudaMalloc(&A->d_sendbuf, std::max<size_t>((size_t)nsend, 1) * A->es));
+  HPCX_CUDA(ctx, cudaMalloc(&A->d_xfull, std::max<size_t>((size_t)A->ncols, 1) * A->es));
+  if (nsend)
+    HPCX_CUDA(ctx, cudaMemcpy(A->d_send_idx, send_idx, (size_t)nsend * 4, cudaMemcpyHostToDevice));
+
+  // Interior / boundary row-block tables over the device-resident row_ptr.
+  std::vector<int32_t> rp32(A->nrows + 1);
+  HPCX_CUDA(ctx, cudaMemcpy(rp32.data(), A->d_row_ptr, rp32.size() * 4, cudaMemcpyDeviceToHost));
+  std::vector<int64_t> rp(rp32.begin(), rp32.end());
+  std::vector<int32_t> long_row, long_off;
+  A->h_blocks_int.clear();
+  A->h_blocks_bnd.clear();
+  spmv_build_rowblocks(rp.data(), A->nrows, A->tile, row_kind, 0, A->h_blocks_int, &long_row,
+                       &long_off);
+  spmv_build_rowblocks(rp.data(), A->nrows, A->tile, row_kind, 1, A->h_blocks_bnd, &long_row,
+                       &long_off);
+  A->nlong_dist = (int64_t)long_row.size();
+  auto up = [&](const void *h, size_t bytes, void **d) -> cudaError_t {
+    cudaError_t e = cudaMalloc(d, std::max<size_t>(bytes, 16));
+    if (e == cudaSuccess && bytes) e = cudaMemcpy(*d, h, bytes, cudaMemcpyHostToDevice);
+    return e;
+  };
+  HPCX_CUDA(ctx, up(A->h_blocks_int.data(), A->h_blocks_int.size() * sizeof(RowBlock),
+                    (void **)&A->d_blocks_int));
+  HPCX_CUDA(ctx, up(A->h_blocks_bnd.data(), A->h_blocks_bnd.size() * sizeof(RowBlock),
+                    (void **)&A->d_blocks_bnd));
+  HPCX_CUDA(ctx, up(long_row.data(), long_row.size() * 4, (void **)&A->d_long_row_dist));
+  HPCX_CUDA(ctx, up(long_off.data(), long_off.size() * 4, (void **)&A->d_long_off_dist));
+  return HPCX_OK;
+}
+
+hpcx_status hpcx_csr_x_buffer(hpcx_csr A, void **x_full) {
+  if (!A || !x_full) return HPCX_INVALID_ARG;
+  HPCX_REQUIRE(A->ctx, A->d_xfull != nullptr, "hpcx_csr_set_halo has not been called");
+  *x_full = A->d_xfull;
+  return HPCX_OK;
+}
+
+// compute stream: gather boundary x -> ev ; interior rows ; [wait recv] boundary rows
+// comm stream   : [wait ev] grouped send/recv of the x halo segments -> ev_recv
+hpcx_status hpcx_spmv_dist(hpcx_csr A, const void *x_local, void *y_local, void *stream) {
+  if (!A || !x_local || !y_local) return HPCX_INVALID_ARG;
+  hpcx_ctx ctx = A->ctx;
+  HPCX_REQUIRE(ctx, A->d_xfull != nullptr, "hpcx_csr_set_halo has not been called");
+  if (ctx->nranks > 1 && !ctx->nccl_comm)
+    return fail(ctx, HPCX_NCCL_ERROR, "hpcx_comm_init has not been called");
+  cudaStream_t cs = stream ? (cudaStream_t)stream : ctx->compute;
+  cudaStream_t ms = ctx->comm;
+  const int P = ctx->nranks;
+  char *xfull = static_cast<char *>(A->d_xfull);
+  if (x_local != A->d_xfull)
+    HPCX_CUDA(ctx, cudaMemcpyAsync(xfull, x_local, (size_t)A->nloc * A->es,
+                                   cudaMemcpyDeviceToDevice, cs));
+  hpcx_status rc;
+  if (A->nsend) {
+    const int blocks = (int)std::min<int64_t>((A->nsend + 255) / 256, (int64_t)ctx->sm_count * 8);
+    if (A->dtype == HPCX_F64)
+      gather_boundary_x_kernel<double><<<blocks, 256, 0, cs>>>(
+          (const double *)xfull, A->d_send_idx, (double *)A->d_sendbuf, A->nsend);
+    else
+      gather_boundary_x_kernel<float><<<blocks, 256, 0, cs>>>(
+          (const float *)xfull, A->d_send_idx, (float *)A->d_sendbuf, A->nsend);
+    rc = after_launch(ctx, "gather_boundary_x_kernel");
+    if (rc != HPCX_OK) return rc;
+  }
+  const bool exchange = P > 1 && (A->nsend || A->nhalo);
+  if (exchange) {
+    HPCX_CUDA(ctx, cudaEventRecord(ctx->ev[0], cs));
+    HPCX_CUDA(ctx, cudaStreamWaitEvent(ms, ctx->ev[0], 0));
+    const ncclDataType_t ty = nccl_type(A->dtype);
+    HPCX_NCCL(ctx, g_nccl.GroupStart());
+    int64_t soff = 0, roff = 0;
+    for (int q = 0; q < P; ++q) {
+      if (A->send_counts[q])
+        HPCX_NCCL(ctx, g_nccl.Send((char *)A->d_sendbuf + soff * A->es, (size_t)A->send_counts[q],
+                                   ty, q, comm_of(ctx), ms));
+      if (A->recv_counts[q])
+        HPCX_NCCL(ctx, g_nccl.Recv(xfull + (A->nloc + roff) * A->es, (size_t)A->recv_counts[q], ty,
+                                   q, comm_of(ctx), ms));
+      soff += A->send_counts[q];
+      roff += A->recv_counts[q];
+    }
+    HPCX_NCCL(ctx, g_nccl.GroupEnd());
+    HPCX_CUDA(ctx, cudaEventRecord(ctx->ev[1], ms));
+  }
+  rc = spmv_launch_blocks(A, A->d_blocks_int, (int64_t)A->h_blocks_int.size(), xfull, y_local, cs);
+  if (rc != HPCX_OK) return rc;
+  if (exchange) HPCX_CUDA(ctx, cudaStreamWaitEvent(cs, ctx->ev[1], 0));
+  rc = spmv_launch_blocks(A, A->d_blocks_bnd, (int64_t)A->h_blocks_bnd.size(), xfull, y_local, cs);
+  if (rc != HPCX_OK) return rc;
+  rc = spmv_launch_fixup_tables(A, A->d_long_row_dist, A->d_long_off_dist, A->nlong_dist, y_local, cs);
+  if (rc != HPCX_OK) return rc;
+  if (!stream) HPCX_CUDA(ctx, cudaStreamSynchronize(cs));
+  return HPCX_OK;
+}
+
+}  // extern "C"

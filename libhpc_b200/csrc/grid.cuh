@@ -1,0 +1,29 @@
+// grid.cuh — device mirror of hpc::HPCHighDimensionFlatArray
+// (reference: lib/hpc/include/HPCHighDimensionFlatArray.hpp:54-224).
+#pragma once
+#include "common.cuh"
+
+struct hpcx_grid_s {
+  hpcx_ctx ctx = nullptr;
+  hpcx_grid_desc desc{};
+  int es = 4;          // element size in bytes
+  // Normalised to 3-D, slowest first; missing leading dimensions have n = 1 and no ghosts.
+  int64_t n[3] = {1, 1, 1};    // logical extents
+  int64_t glo[3] = {0, 0, 0};  // ghost cells per side
+  int64_t ghi[3] = {0, 0, 0};
+  int64_t ext[3] = {1, 1, 1};  // padded extents n + glo + ghi (host layout)
+  int64_t xoff = 0;            // device: element offset of interior x = 0 inside a row
+  int64_t pitch = 0;           // device: row pitch in elements
+  int64_t rows = 0;            // ext[0] * ext[1]
+  int64_t total = 0;           // rows * pitch
+  void *dev = nullptr;
+};
+
+namespace hpcx {
+// Device element index of logical (z, y, x) — ghost indices are negative / >= n.
+__host__ __device__ inline int64_t grid_dev_index(int64_t z, int64_t y, int64_t x, int64_t glo0,
+                                                  int64_t glo1, int64_t ext1, int64_t pitch,
+                                                  int64_t xoff) {
+  return ((z + glo0) * ext1 + (y + glo1)) * pitch + xoff + x;
+}
+}  // namespace hpcx

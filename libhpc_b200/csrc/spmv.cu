@@ -1,0 +1,705 @@
+// spmv.cu — CSR sparse matrix-vector product y = A*x for sm_100a.
+//
+// No reference implementation exists; the arithmetic contract is
+// the CPU restatement in oracle/hpcx_oracle.c (hpcx_oracle_spmv_*): per row, products
+// values[p]*x[col_idx[p]] rounded separately and added in ascending p.
+//
+// STREAM kernel (default).  The matrix is cut at create time into row blocks whose
+// nonzeros fit one shared-memory tile.  One CTA per block:
+//   1. one thread issues two 1-D bulk copies (TMA engine, cp.async.bulk -> SASS UBLKCP) that
+//      bring the block's contiguous values[] and col_idx[] ranges into shared memory and
+//      complete on an mbarrier — perfectly coalesced, no registers held while in flight;
+//      several CTAs are resident per SM, so copies of one overlap the arithmetic of others;
+//   2. all threads gather x[col] through the read-only path (ld.global.nc) and turn the
+//      staged values into products in place;
+//   3. rows are reduced out of shared memory with a per-block choice of 1, 2..32 lanes or
+//      the whole CTA per row (row-length binning at block granularity); with 1 lane per row
+//      the summation order is exactly the oracle's, so short-row matrices are bit-exact.
+// Rows longer than a tile are split into tile-sized chunks whose partial sums are added in
+// chunk order by a small fix-up kernel (deterministic, no atomics).
+#include "spmv.cuh"
+
+#include <algorithm>
+
+using namespace hpcx;
+
+namespace {
+
+constexpr int kThreads = 256;
+
+template <typename T>
+__device__ __forceinline__ T ldg_nc(const T *p) {
+  return __ldg(p);
+}
+
+__device__ __forceinline__ float mul_rn(float a, float b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ double mul_rn(double a, double b) { return __dmul_rn(a, b); }
+__device__ __forceinline__ float add_rn(float a, float b) { return __fadd_rn(a, b); }
+__device__ __forceinline__ double add_rn(double a, double b) { return __dadd_rn(a, b); }
+
+template <typename T>
+__device__ __forceinline__ T shfl_xor(T v, int m) {
+  return __shfl_xor_sync(0xffffffffu, v, m);
+}
+
+// Dynamic shared memory layout: [values TILE+8][cols TILE+8][mbarrier][warp sums].
+template <typename T, int TILE>
+struct StreamSmem {
+  static constexpr int kVal = (TILE + 8) * (int)sizeof(T);
+  static constexpr int kCol = (TILE + 8) * 4;
+  static constexpr int kBar = kVal + kCol;
+  static constexpr int kWsum = kBar + 16;
+  static constexpr int kBytes = kWsum + (kThreads / 32) * (int)sizeof(T);
+};
+
+template <typename T, int TILE>
+__global__ void __launch_bounds__(kThreads)
+spmv_stream_kernel(const int32_t *__restrict__ row_ptr, const int32_t *__restrict__ col,
+                   const T *__restrict__ val, const T *__restrict__ x, T *__restrict__ y,
+                   const RowBlock *__restrict__ blocks, T *__restrict__ partials) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  using L = StreamSmem<T, TILE>;
+  T *sval = reinterpret_cast<T *>(smem);
+  int32_t *scol = reinterpret_cast<int32_t *>(smem + L::kVal);
+  uint64_t *bar = reinterpret_cast<uint64_t *>(smem + L::kBar);
+  T *wsum = reinterpret_cast<T *>(smem + L::kWsum);
+
+  const int tid = threadIdx.x;
+  // Block descriptor: 32 bytes, same for every thread (two broadcast 16-byte loads).
+  const int4 d0 = __ldg(reinterpret_cast<const int4 *>(blocks + blockIdx.x));
+  const longlong2 d1 = __ldg(reinterpret_cast<const longlong2 *>(blocks + blockIdx.x) + 1);
+  const int row0 = d0.x, nrows = d0.y, part = d0.z, lanes = d0.w;
+  const int64_t p0 = d1.x, p1 = d1.y;
+  const int64_t p0a = p0 & ~int64_t(3);          // 16-byte aligned start in col_idx[]
+  const int lead = (int)(p0 - p0a);              // staged entries before the block's first
+  const int cnt = (int)(p1 - p0a);               // staged entries up to the block's last
+  const int cnt_a = (cnt + 3) & ~3;
+
+  if (tid == 0) {
+    mbar_init(bar, 1);
+    mbar_fence_init();
+  }
+  __syncthreads();
+  if (tid == 0 && cnt_a > 0) {
+    mbar_expect_tx(bar, (uint32_t)cnt_a * (uint32_t)(sizeof(T) + 4));
+    bulk_g2s(sval, val + p0a, (uint32_t)cnt_a * (uint32_t)sizeof(T), bar);
+    bulk_g2s(scol, col + p0a, (uint32_t)cnt_a * 4u, bar);
+  }
+  if (cnt_a > 0) mbar_wait(bar, 0);
+
+  // Products in place. Four gathers in flight per thread per round.
+  for (int base = lead + tid; base < cnt; base += 4 * kThreads) {
+    T xv[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int i = base + k * kThreads;
+      xv[k] = i < cnt ? ldg_nc(x + scol[i]) : T(0);
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int i = base + k * kThreads;
+      if (i < cnt) sval[i] = mul_rn(sval[i], xv[k]);
+    }
+  }
+  __syncthreads();
+
+  if (lanes == 1) {
+    // One thread per row, ascending p: the oracle's order.
+    for (int r = tid; r < nrows; r += kThreads) {
+      const int a = (int)((int64_t)row_ptr[row0 + r] - p0a);
+      const int e = (int)((int64_t)row_ptr[row0 + r + 1] - p0a);
+      T s = T(0);
+      for (int i = a; i < e; ++i) s = add_rn(s, sval[i]);
+      y[row0 + r] = s;
+    }
+  } else if (lanes > 1) {
+    // `lanes` threads per row: strided partial sums, xor-shuffle tree.
+    const int g = tid / lanes, l = tid % lanes;
+    const int groups = kThreads / lanes;
+    for (int rb = 0; rb < nrows; rb += groups) {
+      const int r = rb + g;
+      T s = T(0);
+      if (r < nrows) {
+        const int a = (int)((int64_t)row_ptr[row0 + r] - p0a);
+        const int e = (int)((int64_t)row_ptr[row0 + r + 1] - p0a);
+        for (int i = a + l; i < e; i += lanes) s = add_rn(s, sval[i]);
+      }
+      for (int m = lanes >> 1; m > 0; m >>= 1) s = add_rn(s, shfl_xor(s, m));
+      if (r < nrows && l == 0) y[row0 + r] = s;
+    }
+  } else {
+    // Whole CTA on one row (or one chunk of a long row).
+    T s = T(0);
+    for (int i = lead + tid; i < cnt; i += kThreads) s = add_rn(s, sval[i]);
+    for (int m = 16; m > 0; m >>= 1) s = add_rn(s, shfl_xor(s, m));
+    if ((tid & 31) == 0) wsum[tid >> 5] = s;
+    __syncthreads();
+    if (tid == 0) {
+      T t = wsum[0];
+#pragma unroll
+      for (int w = 1; w < kThreads / 32; ++w) t = add_rn(t, wsum[w]);
+      if (part >= 0)
+        partials[part] = t;
+      else
+        y[row0] = t;
+    }
+  }
+}
+
+// Adds the chunk partial sums of every long row in chunk order.
+template <typename T>
+__global__ void spmv_longrow_fixup_kernel(const int32_t *__restrict__ long_row,
+                                          const int32_t *__restrict__ long_off,
+                                          const T *__restrict__ partials, T *__restrict__ y,
+                                          int nlong) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= nlong) return;
+  T s = T(0);
+  for (int k = long_off[j]; k < long_off[j + 1]; ++k) s = add_rn(s, partials[k]);
+  y[long_row[j]] = s;
+}
+
+// Classic vector-per-row kernel: G lanes per row straight from global memory.
+// Kept as the A/B baseline for the STREAM kernel (ncu: sectors/request, achieved GB/s).
+template <typename T, int G>
+__global__ void __launch_bounds__(kThreads)
+spmv_vector_kernel(const int32_t *__restrict__ row_ptr, const int32_t *__restrict__ col,
+                   const T *__restrict__ val, const T *__restrict__ x, T *__restrict__ y,
+                   int64_t nrows) {
+  const int64_t t = blockIdx.x * (int64_t)kThreads + threadIdx.x;
+  const int64_t row = t / G;
+  const int l = (int)(t % G);
+  T s = T(0);
+  if (row < nrows) {
+    const int a = row_ptr[row], e = row_ptr[row + 1];
+    for (int i = a + l; i < e; i += G) s = add_rn(s, mul_rn(__ldg(val + i), ldg_nc(x + __ldg(col + i))));
+  }
+#pragma unroll
+  for (int m = G >> 1; m > 0; m >>= 1) s = add_rn(s, shfl_xor(s, m));
+  if (row < nrows && l == 0) y[row] = s;
+}
+
+// SELL-C-sigma: one thread per row of a slice, slices stored column-major (C consecutive
+// rows interleaved) so a warp reads C consecutive values per step.
+template <typename T>
+__global__ void __launch_bounds__(kThreads)
+spmv_sell_kernel(const int64_t *__restrict__ slice_ptr, const int32_t *__restrict__ slice_len,
+                 const int32_t *__restrict__ perm, const int32_t *__restrict__ col,
+                 const T *__restrict__ val, const T *__restrict__ x, T *__restrict__ y,
+                 int64_t nrows, int C) {
+  const int64_t t = blockIdx.x * (int64_t)kThreads + threadIdx.x;
+  const int64_t slice = t / C;
+  const int lane = (int)(t % C);
+  const int64_t srow = slice * C + lane;  // position in the sorted order
+  if (srow >= nrows) return;
+  const int64_t base = slice_ptr[slice];
+  const int len = slice_len[slice];
+  T s = T(0);
+  for (int k = 0; k < len; ++k) {
+    const int64_t i = base + (int64_t)k * C + lane;
+    s = add_rn(s, mul_rn(__ldg(val + i), ldg_nc(x + __ldg(col + i))));
+  }
+  y[perm[srow]] = s;
+}
+
+int lanes_for(int64_t nnz_blk, int64_t nrows) {
+  if (nrows <= 0) return 1;
+  const int64_t avg = (nnz_blk + nrows - 1) / nrows;
+  if (nrows == 1 && nnz_blk > 256) return 0;
+  if (avg <= 8) return 1;
+  if (avg <= 16) return 2;
+  if (avg <= 32) return 4;
+  if (avg <= 64) return 8;
+  if (avg <= 128) return 16;
+  return 32;
+}
+
+// Greedy row blocking. `kind` (may be null) forces a cut wherever the row kind changes
+// and `want` selects which kind to emit (distributed interior / boundary tables).
+void build_rowblocks(const int64_t *rp, int64_t nrows, int tile, const uint8_t *kind, int want,
+                     std::vector<RowBlock> &out, std::vector<int32_t> *long_row,
+                     std::vector<int32_t> *long_off) {
+  int64_t r = 0;
+  int32_t nparts = long_off && !long_off->empty() ? long_off->back() : 0;
+  if (long_off && long_off->empty()) long_off->push_back(0);
+  while (r < nrows) {
+    if (kind && kind[r] != want) {
+      ++r;
+      continue;
+    }
+    const int64_t len = rp[r + 1] - rp[r];
+    if (len > tile) {
+      for (int64_t p = rp[r]; p < rp[r + 1]; p += tile) {
+        RowBlock b{(int32_t)r, 1, nparts++, 0, p, std::min<int64_t>(p + tile, rp[r + 1])};
+        out.push_back(b);
+      }
+      if (long_row) long_row->push_back((int32_t)r);
+      if (long_off) long_off->push_back(nparts);
+      ++r;
+      continue;
+    }
+    const int64_t r0 = r, p0 = rp[r];
+    while (r < nrows && r - r0 < tile && rp[r + 1] - p0 <= tile && (!kind || kind[r] == want)) ++r;
+    RowBlock b{(int32_t)r0, (int32_t)(r - r0), -1, lanes_for(rp[r] - p0, r - r0), p0, rp[r]};
+    out.push_back(b);
+  }
+}
+
+template <typename T, int TILE>
+hpcx_status launch_stream_t(hpcx_csr A, const RowBlock *d_blocks, int64_t nblocks, const T *x, T *y,
+                            cudaStream_t s) {
+  if (nblocks == 0) return HPCX_OK;
+  using L = StreamSmem<T, TILE>;
+  static bool configured = false;
+  if (!configured) {
+    HPCX_CUDA(A->ctx, cudaFuncSetAttribute(spmv_stream_kernel<T, TILE>,
+                                           cudaFuncAttributeMaxDynamicSharedMemorySize, L::kBytes));
+    configured = true;
+  }
+  spmv_stream_kernel<T, TILE><<<(unsigned)nblocks, kThreads, L::kBytes, s>>>(
+      A->d_row_ptr, A->d_col, (const T *)A->d_val, x, y, d_blocks, (T *)A->d_partials);
+  return after_launch(A->ctx, "spmv_stream_kernel");
+}
+
+template <typename T>
+hpcx_status launch_stream(hpcx_csr A, const RowBlock *d_blocks, int64_t nblocks, const T *x, T *y,
+                          cudaStream_t s) {
+  switch (A->tile) {
+    case 1024: return launch_stream_t<T, 1024>(A, d_blocks, nblocks, x, y, s);
+    case 2048: return launch_stream_t<T, 2048>(A, d_blocks, nblocks, x, y, s);
+    case 4096: return launch_stream_t<T, 4096>(A, d_blocks, nblocks, x, y, s);
+    default: return fail(A->ctx, HPCX_INVALID_ARG, "tile_nnz must be 1024, 2048 or 4096");
+  }
+}
+
+template <typename T>
+hpcx_status launch_fixup(hpcx_csr A, const int32_t *long_row, const int32_t *long_off,
+                         int64_t nlong, T *y, cudaStream_t s) {
+  if (nlong == 0) return HPCX_OK;
+  spmv_longrow_fixup_kernel<T><<<(unsigned)((nlong + 127) / 128), 128, 0, s>>>(
+      long_row, long_off, (const T *)A->d_partials, y, (int)nlong);
+  return after_launch(A->ctx, "spmv_longrow_fixup_kernel");
+}
+
+template <typename T>
+hpcx_status launch_vector(hpcx_csr A, const T *x, T *y, cudaStream_t s) {
+  int G = A->lanes_per_row;
+  if (G <= 0) {
+    const int64_t avg = A->nrows ? (A->nnz + A->nrows - 1) / A->nrows : 1;
+    G = avg <= 2 ? 1 : avg <= 4 ? 2 : avg <= 8 ? 4 : avg <= 16 ? 8 : avg <= 32 ? 16 : 32;
+  }
+  const int64_t threads = A->nrows * G;
+  const unsigned blocks = (unsigned)((threads + kThreads - 1) / kThreads);
+  if (blocks == 0) return HPCX_OK;
+#define HPCX_VEC(GG)                                                                       \
+  case GG:                                                                                 \
+    spmv_vector_kernel<T, GG><<<blocks, kThreads, 0, s>>>(A->d_row_ptr, A->d_col,          \
+                                                          (const T *)A->d_val, x, y, A->nrows); \
+    break;
+  switch (G) {
+    HPCX_VEC(1) HPCX_VEC(2) HPCX_VEC(4) HPCX_VEC(8) HPCX_VEC(16) HPCX_VEC(32)
+    default: return fail(A->ctx, HPCX_INVALID_ARG, "lanes_per_row must be a power of two <= 32");
+  }
+#undef HPCX_VEC
+  return after_launch(A->ctx, "spmv_vector_kernel");
+}
+
+template <typename T>
+hpcx_status launch_sell(hpcx_csr A, const T *x, T *y, cudaStream_t s) {
+  const int64_t threads = A->sell_nslices * A->sell_c;
+  const unsigned blocks = (unsigned)((threads + kThreads - 1) / kThreads);
+  if (blocks == 0) return HPCX_OK;
+  spmv_sell_kernel<T><<<blocks, kThreads, 0, s>>>(A->d_slice_ptr, A->d_slice_len, A->d_perm,
+                                                  A->d_sell_col, (const T *)A->d_sell_val, x, y,
+                                                  A->nrows, A->sell_c);
+  return after_launch(A->ctx, "spmv_sell_kernel");
+}
+
+template <typename T>
+hpcx_status spmv_device(hpcx_csr A, const T *x, T *y, cudaStream_t s) {
+  hpcx_status st;
+  switch (A->kernel) {
+    case HPCX_SPMV_STREAM:
+      st = launch_stream<T>(A, A->d_blocks, (int64_t)A->h_blocks.size(), x, y, s);
+      if (st == HPCX_OK) st = launch_fixup<T>(A, A->d_long_row, A->d_long_off, A->nlong, y, s);
+      return st;
+    case HPCX_SPMV_VECTOR: return launch_vector<T>(A, x, y, s);
+    case HPCX_SPMV_SELL: return launch_sell<T>(A, x, y, s);
+    default: return fail(A->ctx, HPCX_INVALID_ARG, "unknown SpMV kernel");
+  }
+}
+
+// SELL-C-sigma builder (host). Within every window of sigma consecutive rows, rows are
+// stably sorted by descending length (ties keep ascending row id); slices of C sorted rows
+// are stored column-major, padded to the slice's longest row with col = the row's own index
+// clamped to ncols-1 and value 0.
+template <typename T>
+void build_sell(hpcx_csr A, const int64_t *rp, const int32_t *col, const T *val,
+                std::vector<int32_t> &scol, std::vector<T> &sval) {
+  const int64_t n = A->nrows;
+  const int C = A->sell_c, S = A->sell_sigma;
+  A->h_perm.resize(n);
+  for (int64_t i = 0; i < n; ++i) A->h_perm[i] = (int32_t)i;
+  if (S > 1)
+    for (int64_t w = 0; w < n; w += S) {
+      const int64_t e = std::min<int64_t>(w + S, n);
+      std::stable_sort(A->h_perm.begin() + w, A->h_perm.begin() + e, [&](int32_t a, int32_t b) {
+        return rp[a + 1] - rp[a] > rp[b + 1] - rp[b];
+      });
+    }
+  const int64_t ns = (n + C - 1) / C;
+  A->sell_nslices = ns;
+  A->h_slice_ptr.assign(ns + 1, 0);
+  A->h_slice_len.assign(ns, 0);
+  for (int64_t s = 0; s < ns; ++s) {
+    int64_t m = 0;
+    for (int64_t j = s * C; j < std::min<int64_t>((s + 1) * C, n); ++j) {
+      const int32_t r = A->h_perm[j];
+      m = std::max<int64_t>(m, rp[r + 1] - rp[r]);
+    }
+    A->h_slice_len[s] = (int32_t)m;
+    A->h_slice_ptr[s + 1] = A->h_slice_ptr[s] + m * C;
+  }
+  A->sell_padded = A->h_slice_ptr[ns];
+  scol.assign(A->sell_padded, 0);
+  sval.assign(A->sell_padded, T(0));
+  for (int64_t s = 0; s < ns; ++s)
+    for (int lane = 0; lane < C; ++lane) {
+      const int64_t j = s * C + lane;
+      const int64_t base = A->h_slice_ptr[s];
+      const int len = A->h_slice_len[s];
+      if (j < n) {
+        const int32_t r = A->h_perm[j];
+        const int64_t a = rp[r], rl = rp[r + 1] - rp[r];
+        const int32_t padc = (int32_t)std::min<int64_t>(r, A->ncols - 1);
+        for (int k = 0; k < len; ++k) {
+          const int64_t i = base + (int64_t)k * C + lane;
+          if (k < rl) {
+            scol[i] = col[a + k];
+            sval[i] = val[a + k];
+          } else {
+            scol[i] = padc;
+          }
+        }
+      }
+    }
+}
+
+void free_csr(hpcx_csr A) {
+  cudaFree(A->d_row_ptr);
+  cudaFree(A->d_col);
+  cudaFree(A->d_val);
+  cudaFree(A->d_blocks);
+  cudaFree(A->d_long_row);
+  cudaFree(A->d_long_off);
+  cudaFree(A->d_partials);
+  cudaFree(A->d_perm);
+  cudaFree(A->d_slice_len);
+  cudaFree(A->d_sell_col);
+  cudaFree(A->d_slice_ptr);
+  cudaFree(A->d_sell_val);
+  cudaFree(A->d_x);
+  cudaFree(A->d_y);
+  cudaFree(A->d_send_idx);
+  cudaFree(A->d_sendbuf);
+  cudaFree(A->d_xfull);
+  cudaFree(A->d_blocks_int);
+  cudaFree(A->d_blocks_bnd);
+  cudaFree(A->d_long_row_dist);
+  cudaFree(A->d_long_off_dist);
+  delete A;
+}
+
+template <typename V>
+hpcx_status upload_vec(hpcx_ctx ctx, const std::vector<V> &h, V **d) {
+  *d = nullptr;
+  HPCX_CUDA(ctx, cudaMalloc((void **)d, std::max<size_t>(h.size(), 1) * sizeof(V)));
+  if (!h.empty())
+    HPCX_CUDA(ctx, cudaMemcpy(*d, h.data(), h.size() * sizeof(V), cudaMemcpyHostToDevice));
+  return HPCX_OK;
+}
+
+}  // namespace
+
+namespace hpcx {
+// Shared with dist.cu.
+hpcx_status spmv_launch_blocks(hpcx_csr A, const RowBlock *d_blocks, int64_t nblocks, const void *x,
+                               void *y, cudaStream_t s) {
+  if (A->dtype == HPCX_F64)
+    return launch_stream<double>(A, d_blocks, nblocks, (const double *)x, (double *)y, s);
+  return launch_stream<float>(A, d_blocks, nblocks, (const float *)x, (float *)y, s);
+}
+hpcx_status spmv_launch_fixup_tables(hpcx_csr A, const int32_t *long_row, const int32_t *long_off,
+                                     int64_t nlong, void *y, cudaStream_t s) {
+  if (A->dtype == HPCX_F64) return launch_fixup<double>(A, long_row, long_off, nlong, (double *)y, s);
+  return launch_fixup<float>(A, long_row, long_off, nlong, (float *)y, s);
+}
+void spmv_build_rowblocks(const int64_t *rp, int64_t nrows, int tile, const uint8_t *kind, int want,
+                          std::vector<RowBlock> &out, std::vector<int32_t> *long_row,
+                          std::vector<int32_t> *long_off) {
+  build_rowblocks(rp, nrows, tile, kind, want, out, long_row, long_off);
+}
+}  // namespace hpcx
+
+extern "C" {
+
+hpcx_status hpcx_csr_create(hpcx_ctx ctx, const hpcx_csr_desc *d, const hpcx_csr_opts *opts,
+                            hpcx_csr *out) {
+  if (!ctx || !out) return HPCX_INVALID_ARG;
+  *out = nullptr;
+  HPCX_REQUIRE(ctx, d != nullptr, "null CSR descriptor");
+  HPCX_REQUIRE(ctx, d->nrows >= 0 && d->ncols >= 0 && d->nnz >= 0, "negative CSR size");
+  HPCX_REQUIRE(ctx, d->idx_bytes == 4 || d->idx_bytes == 8, "idx_bytes must be 4 or 8");
+  HPCX_REQUIRE(ctx, d->dtype == HPCX_F32 || d->dtype == HPCX_F64, "bad dtype");
+  HPCX_REQUIRE(ctx, d->row_ptr && (d->nnz == 0 || (d->col_idx && d->values)), "null CSR array");
+  if (d->nnz > INT32_MAX || d->nrows >= INT32_MAX)
+    return fail(ctx, HPCX_UNSUPPORTED, "nnz and nrows must be below 2^31 in this build");
+
+  hpcx_csr A = new (std::nothrow) hpcx_csr_s();
+  if (!A) return fail(ctx, HPCX_OOM, "host allocation failed");
+  A->ctx = ctx;
+  A->nrows = d->nrows;
+  A->ncols = d->ncols;
+  A->nnz = d->nnz;
+  A->dtype = d->dtype;
+  A->es = (int)dtype_size(d->dtype);
+  A->idx_bytes = d->idx_bytes;
+  A->kernel = opts && opts->kernel ? opts->kernel : HPCX_SPMV_STREAM;
+  A->tile = opts && opts->tile_nnz ? opts->tile_nnz : 2048;
+  A->lanes_per_row = opts ? opts->lanes_per_row : 0;
+  A->sell_c = opts && opts->sell_c ? opts->sell_c : 32;
+  A->sell_sigma = opts && opts->sell_sigma ? opts->sell_sigma : 1024;
+  if (A->tile != 1024 && A->tile != 2048 && A->tile != 4096) {
+    delete A;
+    return fail(ctx, HPCX_INVALID_ARG, "tile_nnz must be 1024, 2048 or 4096");
+  }
+  if (A->kernel < HPCX_SPMV_STREAM || A->kernel > HPCX_SPMV_SELL || A->sell_c < 1 ||
+      A->sell_c > kThreads || kThreads % A->sell_c != 0) {
+    delete A;
+    return fail(ctx, HPCX_INVALID_ARG, "bad SpMV kernel / SELL slice height");
+  }
+
+#define HPCX_TRY(expr)                 \
+  do {                                 \
+    hpcx_status st__ = (expr);         \
+    if (st__ != HPCX_OK) {             \
+      free_csr(A);                     \
+      return st__;                     \
+    }                                  \
+  } while (0)
+#define HPCX_TRY_CUDA(expr)                                                                   \
+  do {                                                                                        \
+    cudaError_t e__ = (expr);                                                                 \
+    if (e__ != cudaSuccess) {                                                                 \
+      free_csr(A);                                                                            \
+      return fail(ctx, e__ == cudaErrorMemoryAllocation ? HPCX_OOM : HPCX_CUDA_ERROR,         \
+                  std::string(#expr) + ": " + cudaGetErrorString(e__));                       \
+    }                                                                                         \
+  } while (0)
+
+  // Host copy of row_ptr as int64 (drives every table build).
+  std::vector<int64_t> rp(d->nrows + 1);
+  {
+    const size_t bytes = (size_t)(d->nrows + 1) * d->idx_bytes;
+    std::vector<unsigned char> tmp;
+    const void *src = d->row_ptr;
+    if (d->mem != HPCX_MEM_HOST) {
+      tmp.resize(bytes);
+      HPCX_TRY_CUDA(cudaMemcpy(tmp.data(), d->row_ptr, bytes, cudaMemcpyDeviceToHost));
+      src = tmp.data();
+    }
+    if (d->idx_bytes == 4)
+      for (int64_t i = 0; i <= d->nrows; ++i) rp[i] = ((const int32_t *)src)[i];
+    else
+      for (int64_t i = 0; i <= d->nrows; ++i) rp[i] = ((const int64_t *)src)[i];
+  }
+  if (rp[0] != 0 || rp[d->nrows] != d->nnz) {
+    free_csr(A);
+    return fail(ctx, HPCX_INVALID_ARG, "row_ptr[0] != 0 or row_ptr[nrows] != nnz");
+  }
+  for (int64_t i = 0; i < d->nrows; ++i)
+    if (rp[i + 1] < rp[i]) {
+      free_csr(A);
+      return fail(ctx, HPCX_INVALID_ARG, "row_ptr is not non-decreasing");
+    }
+  // Row-length histogram: bin 0 = empty, bin k = 2^(k-1) <= len < 2^k.
+  for (int64_t i = 0; i < d->nrows; ++i) {
+    int64_t len = rp[i + 1] - rp[i];
+    int b = 0;
+    while (len) {
+      ++b;
+      len >>= 1;
+    }
+    A->bins[b]++;
+  }
+
+  // Device CSR. Padded so that 16-byte aligned bulk copies never run past the allocation.
+  A->nnz_alloc = round_up(d->nnz, 4) + 8;
+  HPCX_TRY_CUDA(cudaMalloc((void **)&A->d_row_ptr, (size_t)(d->nrows + 1) * 4));
+  HPCX_TRY_CUDA(cudaMalloc((void **)&A->d_col, (size_t)A->nnz_alloc * 4));
+  HPCX_TRY_CUDA(cudaMalloc(&A->d_val, (size_t)A->nnz_alloc * A->es));
+  HPCX_TRY_CUDA(cudaMemset(A->d_col + d->nnz, 0, (size_t)(A->nnz_alloc - d->nnz) * 4));
+  HPCX_TRY_CUDA(cudaMemset((char *)A->d_val + (size_t)d->nnz * A->es, 0,
+                           (size_t)(A->nnz_alloc - d->nnz) * A->es));
+  {
+    std::vector<int32_t> rp32(d->nrows + 1);
+    for (int64_t i = 0; i <= d->nrows; ++i) rp32[i] = (int32_t)rp[i];
+    HPCX_TRY_CUDA(cudaMemcpy(A->d_row_ptr, rp32.data(), rp32.size() * 4, cudaMemcpyHostToDevice));
+  }
+  if (d->nnz) {
+    HPCX_TRY_CUDA(cudaMemcpy(A->d_col, d->col_idx, (size_t)d->nnz * 4, cudaMemcpyDefault));
+    HPCX_TRY_CUDA(cudaMemcpy(A->d_val, d->values, (size_t)d->nnz * A->es, cudaMemcpyDefault));
+  }
+
+  // STREAM tables are always built (the distributed path and the bins use them).
+  {
+    std::vector<int32_t> long_row, long_off;
+    build_rowblocks(rp.data(), d->nrows, A->tile, nullptr, 0, A->h_blocks, &long_row, &long_off);
+    A->nlong = (int64_t)long_row.size();
+    HPCX_TRY(upload_vec(ctx, A->h_blocks, &A->d_blocks));
+    HPCX_TRY(upload_vec(ctx, long_row, &A->d_long_row));
+    HPCX_TRY(upload_vec(ctx, long_off, &A->d_long_off));
+    const size_t nparts = long_off.empty() ? 0 : (size_t)long_off.back();
+    HPCX_TRY_CUDA(cudaMalloc(&A->d_partials, std::max<size_t>(nparts, 1) * A->es));
+  }
+
+  if (A->kernel == HPCX_SPMV_SELL) {
+    // The SELL repack needs host copies of col/val.
+    std::vector<int32_t> hcol(d->nnz);
+    std::vector<unsigned char> hval((size_t)d->nnz * A->es);
+    if (d->nnz) {
+      HPCX_TRY_CUDA(cudaMemcpy(hcol.data(), d->col_idx, (size_t)d->nnz * 4, cudaMemcpyDefault));
+      HPCX_TRY_CUDA(cudaMemcpy(hval.data(), d->values, hval.size(), cudaMemcpyDefault));
+    }
+    std::vector<int32_t> scol;
+    if (A->dtype == HPCX_F64) {
+      std::vector<double> sval;
+      build_sell<double>(A, rp.data(), hcol.data(), (const double *)hval.data(), scol, sval);
+      HPCX_TRY(upload_vec(ctx, sval, (double **)&A->d_sell_val));
+    } else {
+      std::vector<float> sval;
+      build_sell<float>(A, rp.data(), hcol.data(), (const float *)hval.data(), scol, sval);
+      HPCX_TRY(upload_vec(ctx, sval, (float **)&A->d_sell_val));
+    }
+    HPCX_TRY(upload_vec(ctx, scol, &A->d_sell_col));
+    HPCX_TRY(upload_vec(ctx, A->h_perm, &A->d_perm));
+    HPCX_TRY(upload_vec(ctx, A->h_slice_len, &A->d_slice_len));
+    HPCX_TRY(upload_vec(ctx, A->h_slice_ptr, &A->d_slice_ptr));
+  }
+  *out = A;
+  return HPCX_OK;
+}
+
+hpcx_status hpcx_csr_destroy(hpcx_csr A) {
+  if (!A) return HPCX_INVALID_ARG;
+  free_csr(A);
+  return HPCX_OK;
+}
+
+hpcx_status hpcx_spmv(hpcx_csr A, const void *x, int32_t x_mem, void *y, int32_t y_mem,
+                      void *stream) {
+  if (!A || !x || !y) return HPCX_INVALID_ARG;
+  hpcx_ctx ctx = A->ctx;
+  cudaStream_t s = stream ? (cudaStream_t)stream : ctx->compute;
+  const void *dx = x;
+  void *dy = y;
+  if (x_mem == HPCX_MEM_HOST) {
+    if (!A->d_x) HPCX_CUDA(ctx, cudaMalloc(&A->d_x, std::max<size_t>((size_t)A->ncols * A->es, 1)));
+    HPCX_CUDA(ctx, cudaMemcpyAsync(A->d_x, x, (size_t)A->ncols * A->es, cudaMemcpyHostToDevice, s));
+    dx = A->d_x;
+  }
+  if (y_mem == HPCX_MEM_HOST) {
+    if (!A->d_y) HPCX_CUDA(ctx, cudaMalloc(&A->d_y, std::max<size_t>((size_t)A->nrows * A->es, 1)));
+    dy = A->d_y;
+  }
+  hpcx_status st = A->dtype == HPCX_F64
+                       ? spmv_device<double>(A, (const double *)dx, (double *)dy, s)
+                       : spmv_device<float>(A, (const float *)dx, (float *)dy, s);
+  if (st != HPCX_OK) return st;
+  if (y_mem == HPCX_MEM_HOST)
+    HPCX_CUDA(ctx, cudaMemcpyAsync(y, dy, (size_t)A->nrows * A->es, cudaMemcpyDeviceToHost, s));
+  if (!stream || y_mem == HPCX_MEM_HOST) HPCX_CUDA(ctx, cudaStreamSynchronize(s));
+  return HPCX_OK;
+}
+
+hpcx_status hpcx_csr_download(hpcx_csr A, void *row_ptr, int32_t *col_idx, void *values) {
+  if (!A) return HPCX_INVALID_ARG;
+  hpcx_ctx ctx = A->ctx;
+  if (row_ptr) {
+    if (A->idx_bytes == 4) {
+      HPCX_CUDA(ctx, cudaMemcpy(row_ptr, A->d_row_ptr, (size_t)(A->nrows + 1) * 4,
+                                cudaMemcpyDeviceToHost));
+    } else {
+      std::vector<int32_t> t(A->nrows + 1);
+      HPCX_CUDA(ctx, cudaMemcpy(t.data(), A->d_row_ptr, t.size() * 4, cudaMemcpyDeviceToHost));
+      for (int64_t i = 0; i <= A->nrows; ++i) ((int64_t *)row_ptr)[i] = t[i];
+    }
+  }
+  if (col_idx && A->nnz)
+    HPCX_CUDA(ctx, cudaMemcpy(col_idx, A->d_col, (size_t)A->nnz * 4, cudaMemcpyDeviceToHost));
+  if (values && A->nnz)
+    HPCX_CUDA(ctx, cudaMemcpy(values, A->d_val, (size_t)A->nnz * A->es, cudaMemcpyDeviceToHost));
+  return HPCX_OK;
+}
+
+hpcx_status hpcx_csr_rowblocks(hpcx_csr A, int64_t *nblocks, int64_t *out, int64_t capacity) {
+  if (!A || !nblocks) return HPCX_INVALID_ARG;
+  *nblocks = (int64_t)A->h_blocks.size();
+  if (out) {
+    HPCX_REQUIRE(A->ctx, capacity >= *nblocks, "row-block buffer too small");
+    for (size_t i = 0; i < A->h_blocks.size(); ++i) {
+      const RowBlock &b = A->h_blocks[i];
+      int64_t *o = out + 6 * i;
+      o[0] = b.row0;
+      o[1] = b.nrows;
+      o[2] = b.part;
+      o[3] = b.lanes;
+      o[4] = b.p0;
+      o[5] = b.p1;
+    }
+  }
+  return HPCX_OK;
+}
+
+hpcx_status hpcx_csr_row_bins(hpcx_csr A, int64_t *bins34) {
+  if (!A || !bins34) return HPCX_INVALID_ARG;
+  memcpy(bins34, A->bins, sizeof A->bins);
+  return HPCX_OK;
+}
+
+hpcx_status hpcx_csr_sell_info(hpcx_csr A, int64_t *nslices, int64_t *padded_nnz, int32_t *c,
+                               int32_t *sigma) {
+  if (!A) return HPCX_INVALID_ARG;
+  if (A->kernel != HPCX_SPMV_SELL)
+    return fail(A->ctx, HPCX_UNSUPPORTED, "matrix was not created with HPCX_SPMV_SELL");
+  if (nslices) *nslices = A->sell_nslices;
+  if (padded_nnz) *padded_nnz = A->sell_padded;
+  if (c) *c = A->sell_c;
+  if (sigma) *sigma = A->sell_sigma;
+  return HPCX_OK;
+}
+
+hpcx_status hpcx_csr_sell_download(hpcx_csr A, int32_t *perm, int64_t *slice_ptr,
+                                   int32_t *slice_len, int32_t *col, void *val) {
+  if (!A) return HPCX_INVALID_ARG;
+  hpcx_ctx ctx = A->ctx;
+  if (A->kernel != HPCX_SPMV_SELL)
+    return fail(ctx, HPCX_UNSUPPORTED, "matrix was not created with HPCX_SPMV_SELL");
+  // Structure comes back from the DEVICE copies (what the kernel reads).
+  if (perm && A->nrows)
+    HPCX_CUDA(ctx, cudaMemcpy(perm, A->d_perm, (size_t)A->nrows * 4, cudaMemcpyDeviceToHost));
+  if (slice_ptr)
+    HPCX_CUDA(ctx, cudaMemcpy(slice_ptr, A->d_slice_ptr, (size_t)(A->sell_nslices + 1) * 8,
+                              cudaMemcpyDeviceToHost));
+  if (slice_len && A->sell_nslices)
+    HPCX_CUDA(ctx, cudaMemcpy(slice_len, A->d_slice_len, (size_t)A->sell_nslices * 4,
+                              cudaMemcpyDeviceToHost));
+  if (col && A->sell_padded)
+    HPCX_CUDA(ctx, cudaMemcpy(col, A->d_sell_col, (size_t)A->sell_padded * 4, cudaMemcpyDeviceToHost));
+  if (val && A->sell_padded)
+    HPCX_CUDA(ctx, cudaMemcpy(val, A->d_sell_val, (size_t)A->sell_padded * A->es,
+                              cudaMemcpyDeviceToHost));
+  return HPCX_OK;
+}
+
+}  // extern "C"

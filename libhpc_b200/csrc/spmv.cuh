@@ -1,0 +1,60 @@
+// spmv.cuh — internal CSR matrix handle (new container next to the reference's lib/sparse;
+// the reference has no CSR/SpMV code, SURVEY.md §0 — layout follows §8 a7).
+#pragma once
+#include "common.cuh"
+
+namespace hpcx {
+
+// One CTA of the STREAM kernel processes one row block: either a run of whole rows whose
+// nonzeros fit one shared-memory tile, or one tile-sized chunk of a row longer than a tile.
+struct RowBlock {
+  int32_t row0;   // first row
+  int32_t nrows;  // rows in the block (1 for a long-row chunk)
+  int32_t part;   // -1, or slot in the partial-sum array (long-row chunk)
+  int32_t lanes;  // threads cooperating on one row: 1,2,4,..,32, or 0 = whole CTA
+  int64_t p0;     // first nonzero
+  int64_t p1;     // one past the last nonzero
+};
+static_assert(sizeof(RowBlock) == 32, "RowBlock is loaded as two 16-byte words");
+
+}  // namespace hpcx
+
+struct hpcx_csr_s {
+  hpcx_ctx ctx = nullptr;
+  int64_t nrows = 0, ncols = 0, nnz = 0;
+  int32_t dtype = HPCX_F64, es = 8, idx_bytes = 4;
+  int32_t kernel = HPCX_SPMV_STREAM, tile = 2048, lanes_per_row = 0;
+  // device CSR (row_ptr always int32 on the device; nnz < 2^31 is enforced at create)
+  int32_t *d_row_ptr = nullptr;
+  int32_t *d_col = nullptr;
+  void *d_val = nullptr;
+  int64_t nnz_alloc = 0;  // padded allocation, multiple of 4 plus slack for aligned bulk copies
+  // STREAM kernel tables
+  std::vector<hpcx::RowBlock> h_blocks;
+  hpcx::RowBlock *d_blocks = nullptr;
+  int64_t nlong = 0;            // rows longer than a tile
+  int32_t *d_long_row = nullptr;
+  int32_t *d_long_off = nullptr;  // nlong + 1
+  void *d_partials = nullptr;
+  int64_t bins[34] = {};
+  // SELL-C-sigma
+  int32_t sell_c = 0, sell_sigma = 0;
+  int64_t sell_nslices = 0, sell_padded = 0;
+  std::vector<int32_t> h_perm, h_slice_len;
+  std::vector<int64_t> h_slice_ptr;
+  int32_t *d_perm = nullptr, *d_slice_len = nullptr, *d_sell_col = nullptr;
+  int64_t *d_slice_ptr = nullptr;
+  void *d_sell_val = nullptr;
+  // staging for host operands
+  void *d_x = nullptr, *d_y = nullptr;
+  // distributed (set by hpcx_csr_set_halo)
+  int64_t nloc = 0, nhalo = 0, nsend = 0;
+  std::vector<int64_t> recv_counts, send_counts;
+  int32_t *d_send_idx = nullptr;
+  void *d_sendbuf = nullptr;
+  void *d_xfull = nullptr;  // [owned | halo]
+  std::vector<hpcx::RowBlock> h_blocks_int, h_blocks_bnd;
+  hpcx::RowBlock *d_blocks_int = nullptr, *d_blocks_bnd = nullptr;
+  int64_t nlong_dist = 0;  // long-row tables in the numbering of the interior/boundary blocks
+  int32_t *d_long_row_dist = nullptr, *d_long_off_dist = nullptr;
+};

@@ -1,0 +1,373 @@
+// stencil.cu — ghost-padded stencil sweeps for sm_100a.
+//
+//   BOX_X / BOX_Y  replace the loop nests of BM_x_blur / BM_x_blur_tiling_simd_prefetch and
+//                  BM_y_blur / BM_YXx_blur_tiling_prefetch_streamed_IPL
+//                  (reference tests/test_hpc_benchmark/test_hpc_benchmark.cpp:354-368,
+//                  425-441, 444-457, 575-601): res = 0.0f; for k = -r..r: res += a(.., ..+k).
+//                  Adds only, in that order, so the result is bit-identical to the reference.
+//   JACOBI7        new: out = (((((zm+ym)+xm)+xp)+yp)+zp) * (1/6), each
+//                  operation rounded separately (the library is built with --fmad=false).
+//
+// Kernels:
+//   *_direct   one thread per cell (quad), neighbours through L1 — any dtype / radius / shape.
+//   jacobi7_tma  warp-specialised: a producer warp streams (TX+8)x(TY+2) plane boxes through
+//                a shared-memory ring with 3-D TMA (cp.async.bulk.tensor, SASS UTMALDG) and
+//                mbarriers; 8 consumer warps march along z with the z-1 / z centre values in
+//                registers, x neighbours by warp shuffle, y halo rows from shared memory.
+//                Every input cell is read from HBM once per sweep (tile halos are L2 hits).
+//   boxx_tma / boxy_tma  same ring for the 17-point reference sweeps (radius 8, fp32).
+#include "grid.cuh"
+
+#include <algorithm>
+
+using namespace hpcx;
+
+namespace {
+
+// ------------------------------------------------------------------ direct kernels
+struct GridGeom {
+  int64_t n0, n1, n2;      // logical extents (z, y, x)
+  int64_t glo0, glo1;      // ghost cells below (z, y)
+  int64_t ext1;            // padded y extent
+  int64_t pitch, xoff;     // device row pitch / offset of x = 0
+};
+
+__host__ GridGeom geom_of(const hpcx_grid_s *g) {
+  return GridGeom{g->n[0], g->n[1], g->n[2], g->glo[0], g->glo[1], g->ext[1], g->pitch, g->xoff};
+}
+
+__device__ __forceinline__ int64_t gidx(const GridGeom &g, int64_t z, int64_t y, int64_t x) {
+  return ((z + g.glo0) * g.ext1 + (y + g.glo1)) * g.pitch + g.xoff + x;
+}
+
+__device__ __forceinline__ float add_rn(float a, float b) { return __fadd_rn(a, b); }
+__device__ __forceinline__ double add_rn(double a, double b) { return __dadd_rn(a, b); }
+__device__ __forceinline__ float mul_rn(float a, float b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ double mul_rn(double a, double b) { return __dmul_rn(a, b); }
+
+// axis: 1 = along y (second fastest), 2 = along x (fastest). 2-D grids (n0 == 1).
+template <typename T>
+__global__ void __launch_bounds__(256)
+box_direct_kernel(const T *__restrict__ in, T *__restrict__ out, GridGeom gi, GridGeom go, int axis,
+                  int radius) {
+  const int64_t x = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  const int64_t y = blockIdx.y * (int64_t)blockDim.y + threadIdx.y;
+  if (x >= gi.n2 || y >= gi.n1) return;
+  const int64_t step = axis == 2 ? 1 : gi.pitch;
+  const T *p = in + gidx(gi, 0, y, x) - (int64_t)radius * step;
+  T s = T(0);
+  for (int k = -radius; k <= radius; ++k, p += step) s = add_rn(s, __ldg(p));
+  out[gidx(go, 0, y, x)] = s;
+}
+
+// One thread per (x, y) column, marching along z over [z0, z1).
+template <typename T>
+__global__ void __launch_bounds__(256)
+jacobi7_direct_kernel(const T *__restrict__ in, T *__restrict__ out, GridGeom g, int64_t zbeg,
+                      int64_t zend, int64_t zlen, T sixth) {
+  const int64_t x = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  const int64_t y = blockIdx.y * (int64_t)blockDim.y + threadIdx.y;
+  if (x >= g.n2 || y >= g.n1) return;
+  const int64_t z0 = zbeg + blockIdx.z * zlen;
+  const int64_t z1 = min(z0 + zlen, zend);
+  const int64_t plane = g.ext1 * g.pitch;
+  const T *p = in + gidx(g, z0, y, x);
+  T *q = out + gidx(g, z0, y, x);
+  T zm = __ldg(p - plane), zc = __ldg(p);
+  for (int64_t z = z0; z < z1; ++z, p += plane, q += plane) {
+    const T zp = __ldg(p + plane);
+    T s = add_rn(zm, __ldg(p - g.pitch));
+    s = add_rn(s, __ldg(p - 1));
+    s = add_rn(s, __ldg(p + 1));
+    s = add_rn(s, __ldg(p + g.pitch));
+    s = add_rn(s, zp);
+    *q = mul_rn(s, sixth);
+    zm = zc;
+    zc = zp;
+  }
+}
+
+// ------------------------------------------------------------------ mbarrier extras
+__device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
+__device__ __forceinline__ void st_cs(float4 *p, float4 v) {
+  asm volatile("st.global.cs.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(v.x), "f"(v.y),
+               "f"(v.z), "f"(v.w)
+               : "memory");
+}
+
+// ------------------------------------------------------------------ Jacobi, TMA ring
+// CTA = 8 consumer warps + 1 producer warp.  Tile TX = 128 (one float4 per lane) by
+// TY = 16 rows (two adjacent rows per consumer warp), S ring slots of one plane box each.
+template <int S>
+struct JacobiCfg {
+  static constexpr int TX = 128, TY = 16, HX = 4;      // HX: x halo staged on each side
+  static constexpr int BX = TX + 2 * HX, BY = TY + 2;  // box extents
+  static constexpr int kPlaneFloats = BX * BY;
+  static constexpr int kPlaneBytes = kPlaneFloats * 4;  // 9792, multiple of 128
+  static constexpr int kBarOff = S * kPlaneBytes;
+  static constexpr int kSmemBytes = kBarOff + 2 * S * 8;
+  static constexpr int kConsumerWarps = 8;
+  static constexpr int kThreads = (kConsumerWarps + 1) * 32;
+};
+
+template <int S>
+__global__ void __launch_bounds__(JacobiCfg<S>::kThreads)
+jacobi7_tma_kernel(const __grid_constant__ CUtensorMap in_map, float *__restrict__ out, GridGeom g,
+                   int zbeg, int zend, int zlen, float sixth) {
+  using C = JacobiCfg<S>;
+  extern __shared__ __align__(128) unsigned char smem[];
+  float *ring = reinterpret_cast<float *>(smem);
+  uint64_t *full = reinterpret_cast<uint64_t *>(smem + C::kBarOff);
+  uint64_t *empty = full + S;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int x0 = blockIdx.x * C::TX, y0 = blockIdx.y * C::TY;
+  const int z0 = zbeg + blockIdx.z * zlen;
+  const int z1 = min(z0 + zlen, zend);
+  const int np = z1 - z0 + 2;  // planes z0-1 .. z1
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < S; ++s) {
+      mbar_init(full + s, 1);
+      mbar_init(empty + s, C::kConsumerWarps);
+    }
+    mbar_fence_init();
+  }
+  __syncthreads();
+
+  if (warp == C::kConsumerWarps) {
+    // ---------------------------------------------------------------- producer
+    if (lane == 0) {
+      tma_prefetch_desc(&in_map);
+      const int c0 = (int)g.xoff + x0 - C::HX;
+      const int c1 = y0 + (int)g.glo1 - 1;
+      const int c2 = z0 - 1 + (int)g.glo0;
+      for (int j = 0; j < np; ++j) {
+        const int slot = j % S, use = j / S;
+        if (use > 0) mbar_wait(empty + slot, (use - 1) & 1);
+        mbar_expect_tx(full + slot, C::kPlaneBytes);
+        tma_load_3d(ring + slot * C::kPlaneFloats, &in_map, c0, c1, c2 + j, full + slot);
+      }
+    }
+    return;
+  }
+
+  // ------------------------------------------------------------------ consumers
+  // Warp w owns tile rows 2w and 2w+1 (box rows 2w+1, 2w+2); lane owns x0 + 4*lane .. +3.
+  const int br = 2 * warp + 1;
+  const int col = C::HX + 4 * lane;
+  auto plane_ptr = [&](int j) { return ring + (j % S) * C::kPlaneFloats; };
+  auto wait_full = [&](int j) { mbar_wait(full + (j % S), (j / S) & 1); };
+  auto release = [&](int j) {
+    __syncwarp();
+    if (lane == 0) mbar_arrive(empty + (j % S));
+  };
+  auto ld4 = [&](const float *pl, int row) {
+    return *reinterpret_cast<const float4 *>(pl + row * C::BX + col);
+  };
+
+  float4 zm0, zm1, zc0, zc1;
+  wait_full(0);
+  {
+    const float *pl = plane_ptr(0);
+    zm0 = ld4(pl, br);
+    zm1 = ld4(pl, br + 1);
+  }
+  release(0);
+  wait_full(1);
+  {
+    const float *pl = plane_ptr(1);
+    zc0 = ld4(pl, br);
+    zc1 = ld4(pl, br + 1);
+  }
+
+  const int gx = x0 + 4 * lane;
+  const int gy = y0 + 2 * warp;
+  const bool full4 = gx + 3 < g.n2;
+  const int64_t plane_stride = g.ext1 * g.pitch;
+  float *orow = out + gidx(g, z0, gy, gx);
+
+  for (int j = 1; j <= np - 2; ++j, orow += plane_stride) {
+    wait_full(j + 1);
+    const float *pn = plane_ptr(j + 1);
+    const float *pc = plane_ptr(j);
+    const float4 zp0 = ld4(pn, br), zp1 = ld4(pn, br + 1);
+    const float4 up = ld4(pc, br - 1);    // y-1 of row 0
+    const float4 dn = ld4(pc, br + 2);    // y+1 of row 1
+    // x neighbours: shuffles inside the warp, staged halo columns at the two ends.
+    float l0 = __shfl_up_sync(0xffffffffu, zc0.w, 1);
+    float l1 = __shfl_up_sync(0xffffffffu, zc1.w, 1);
+    float r0 = __shfl_down_sync(0xffffffffu, zc0.x, 1);
+    float r1 = __shfl_down_sync(0xffffffffu, zc1.x, 1);
+    if (lane == 0) {
+      l0 = pc[br * C::BX + C::HX - 1];
+      l1 = pc[(br + 1) * C::BX + C::HX - 1];
+    }
+    if (lane == 31) {
+      r0 = pc[br * C::BX + C::HX + C::TX];
+      r1 = pc[(br + 1) * C::BX + C::HX + C::TX];
+    }
+    release(j);  // plane j is not read from shared memory again
+
+    float4 o0, o1;
+#define HPCX_J7(o, zm, ym, xm, xp, yp, zp) \
+  o = mul_rn(add_rn(add_rn(add_rn(add_rn(add_rn(zm, ym), xm), xp), yp), zp), sixth)
+    HPCX_J7(o0.x, zm0.x, up.x, l0, zc0.y, zc1.x, zp0.x);
+    HPCX_J7(o0.y, zm0.y, up.y, zc0.x, zc0.z, zc1.y, zp0.y);
+    HPCX_J7(o0.z, zm0.z, up.z, zc0.y, zc0.w, zc1.z, zp0.z);
+    HPCX_J7(o0.w, zm0.w, up.w, zc0.z, r0, zc1.w, zp0.w);
+    HPCX_J7(o1.x, zm1.x, zc0.x, l1, zc1.y, dn.x, zp1.x);
+    HPCX_J7(o1.y, zm1.y, zc0.y, zc1.x, zc1.z, dn.y, zp1.y);
+    HPCX_J7(o1.z, zm1.z, zc0.z, zc1.y, zc1.w, dn.z, zp1.z);
+    HPCX_J7(o1.w, zm1.w, zc0.w, zc1.z, r1, dn.w, zp1.w);
+#undef HPCX_J7
+
+    if (full4) {
+      if (gy < g.n1) st_cs(reinterpret_cast<float4 *>(orow), o0);
+      if (gy + 1 < g.n1) st_cs(reinterpret_cast<float4 *>(orow + g.pitch), o1);
+    } else {
+      const float a0[4] = {o0.x, o0.y, o0.z, o0.w}, a1[4] = {o1.x, o1.y, o1.z, o1.w};
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+        if (gx + k < g.n2) {
+          if (gy < g.n1) orow[k] = a0[k];
+          if (gy + 1 < g.n1) orow[g.pitch + k] = a1[k];
+        }
+    }
+    zm0 = zc0;
+    zm1 = zc1;
+    zc0 = zp0;
+    zc1 = zp1;
+  }
+}
+
+// ------------------------------------------------------------------ host side
+hpcx_status check_same_shape(hpcx_grid a, hpcx_grid b) {
+  hpcx_ctx ctx = a->ctx;
+  HPCX_REQUIRE(ctx, a->ctx == b->ctx, "grids belong to different contexts");
+  HPCX_REQUIRE(ctx, a->desc.ndim == b->desc.ndim && a->desc.dtype == b->desc.dtype,
+               "grids differ in rank or dtype");
+  for (int i = 0; i < a->desc.ndim; ++i)
+    HPCX_REQUIRE(ctx, a->desc.dim[i] == b->desc.dim[i], "grids differ in logical extent");
+  return HPCX_OK;
+}
+
+template <typename T>
+hpcx_status launch_box_direct(hpcx_grid in, hpcx_grid out, int axis, int radius, cudaStream_t s) {
+  dim3 block(64, 4);
+  dim3 grid((unsigned)((in->n[2] + 63) / 64), (unsigned)((in->n[1] + 3) / 4));
+  box_direct_kernel<T><<<grid, block, 0, s>>>((const T *)in->dev, (T *)out->dev, geom_of(in),
+                                              geom_of(out), axis, radius);
+  return after_launch(in->ctx, "box_direct_kernel");
+}
+
+int auto_zsplit(hpcx_ctx ctx, int64_t tiles_xy, int64_t nz, int ctas_per_sm) {
+  // Fill the resident CTA slots of the chip once; keep z segments at least 16 planes long.
+  const int64_t slots = (int64_t)ctx->sm_count * ctas_per_sm;
+  int64_t zs = std::max<int64_t>(1, slots / std::max<int64_t>(tiles_xy, 1));
+  zs = std::min<int64_t>(zs, std::max<int64_t>(1, nz / 16));
+  return (int)zs;
+}
+
+template <typename T>
+hpcx_status launch_jacobi_direct(hpcx_grid_s *g, const void *src, void *dst, int zsplit,
+                                 int64_t zbeg, int64_t zend, cudaStream_t s) {
+  dim3 block(64, 4);
+  const int64_t nz = zend - zbeg;
+  const int64_t tiles = ((g->n[2] + 63) / 64) * ((g->n[1] + 3) / 4);
+  if (zsplit <= 0) zsplit = auto_zsplit(g->ctx, tiles, nz, 8);
+  const int64_t zlen = (nz + zsplit - 1) / zsplit;
+  dim3 grid((unsigned)((g->n[2] + 63) / 64), (unsigned)((g->n[1] + 3) / 4),
+            (unsigned)((nz + zlen - 1) / zlen));
+  jacobi7_direct_kernel<T><<<grid, block, 0, s>>>((const T *)src, (T *)dst, geom_of(g), zbeg, zend,
+                                                  zlen, T(1) / T(6));
+  return after_launch(g->ctx, "jacobi7_direct_kernel");
+}
+
+constexpr int kJacobiStages = 6;
+
+hpcx_status launch_jacobi_tma(hpcx_grid_s *g, void *src, void *dst, int zsplit, int64_t zbeg,
+                              int64_t zend, cudaStream_t s) {
+  using C = JacobiCfg<kJacobiStages>;
+  hpcx_ctx ctx = g->ctx;
+  CUtensorMap map;
+  const uint64_t dims[3] = {(uint64_t)g->pitch, (uint64_t)g->ext[1], (uint64_t)g->ext[0]};
+  const uint64_t strides[2] = {(uint64_t)g->pitch * 4, (uint64_t)g->pitch * g->ext[1] * 4};
+  const uint32_t box[3] = {C::BX, C::BY, 1};
+  hpcx_status st = make_tensor_map(ctx, &map, HPCX_F32, 3, src, dims, strides, box);
+  if (st != HPCX_OK) return st;
+  static bool configured = false;
+  if (!configured) {
+    HPCX_CUDA(ctx, cudaFuncSetAttribute(jacobi7_tma_kernel<kJacobiStages>,
+                                        cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        C::kSmemBytes));
+    configured = true;
+  }
+  const int64_t tx = (g->n[2] + C::TX - 1) / C::TX, ty = (g->n[1] + C::TY - 1) / C::TY;
+  const int64_t nz = zend - zbeg;
+  if (zsplit <= 0) zsplit = auto_zsplit(ctx, tx * ty, nz, 3);
+  const int64_t zlen = (nz + zsplit - 1) / zsplit;
+  dim3 grid((unsigned)tx, (unsigned)ty, (unsigned)((nz + zlen - 1) / zlen));
+  jacobi7_tma_kernel<kJacobiStages><<<grid, C::kThreads, C::kSmemBytes, s>>>(
+      map, (float *)dst, geom_of(g), (int)zbeg, (int)zend, (int)zlen, 1.0f / 6.0f);
+  return after_launch(ctx, "jacobi7_tma_kernel");
+}
+
+}  // namespace
+
+namespace hpcx {
+// One Jacobi sweep src -> dst over the planes of grid `g` (shared with dist.cu).
+hpcx_status jacobi7_launch(hpcx_grid_s *g, void *src, void *dst, int variant, int zsplit,
+                           int64_t zbeg, int64_t zend, cudaStream_t s) {
+  if (zend <= zbeg) return HPCX_OK;
+  const bool tma_ok = g->desc.dtype == HPCX_F32 && g->ctx->encode_tiled && g->n[2] < (1 << 30);
+  if (variant == HPCX_VARIANT_TMA && !tma_ok)
+    return fail(g->ctx, HPCX_UNSUPPORTED, "TMA Jacobi variant needs fp32 and a tensor-map driver");
+  if (variant == HPCX_VARIANT_DIRECT || !tma_ok) {
+    if (g->desc.dtype == HPCX_F64)
+      return launch_jacobi_direct<double>(g, src, dst, zsplit, zbeg, zend, s);
+    return launch_jacobi_direct<float>(g, src, dst, zsplit, zbeg, zend, s);
+  }
+  return launch_jacobi_tma(g, src, dst, zsplit, zbeg, zend, s);
+}
+}  // namespace hpcx
+
+extern "C" hpcx_status hpcx_stencil_sweep(hpcx_grid in, hpcx_grid out, const hpcx_stencil_desc *st,
+                                          int32_t steps, void *stream) {
+  if (!in || !out || !st) return HPCX_INVALID_ARG;
+  hpcx_ctx ctx = in->ctx;
+  hpcx_status rc = check_same_shape(in, out);
+  if (rc != HPCX_OK) return rc;
+  HPCX_REQUIRE(ctx, steps >= 1, "steps must be >= 1");
+  HPCX_REQUIRE(ctx, in != out && in->dev != out->dev, "in and out must be different grids");
+  cudaStream_t s = stream ? (cudaStream_t)stream : ctx->compute;
+
+  if (st->kind == HPCX_STENCIL_BOX_X || st->kind == HPCX_STENCIL_BOX_Y) {
+    if (in->desc.ndim != 2) return fail(ctx, HPCX_UNSUPPORTED, "box sweeps take 2-D grids");
+    HPCX_REQUIRE(ctx, steps == 1, "box sweeps are single-step");
+    HPCX_REQUIRE(ctx, st->radius >= 0 && st->radius <= in->desc.lo && st->radius <= in->desc.hi,
+                 "radius exceeds the ghost width of the input grid");
+    const int axis = st->kind == HPCX_STENCIL_BOX_X ? 2 : 1;
+    rc = in->desc.dtype == HPCX_F64 ? launch_box_direct<double>(in, out, axis, st->radius, s)
+                                    : launch_box_direct<float>(in, out, axis, st->radius, s);
+  } else if (st->kind == HPCX_STENCIL_JACOBI7) {
+    if (in->desc.ndim != 3) return fail(ctx, HPCX_UNSUPPORTED, "JACOBI7 takes 3-D grids");
+    HPCX_REQUIRE(ctx, in->desc.lo >= 1 && in->desc.hi >= 1 && in->desc.lo == out->desc.lo &&
+                          in->desc.hi == out->desc.hi,
+                 "JACOBI7 needs identical ghost widths >= 1 on both grids");
+    for (int t = 0; t < steps && rc == HPCX_OK; ++t) {
+      void *src = (t & 1) ? out->dev : in->dev;
+      void *dst = (t & 1) ? in->dev : out->dev;
+      rc = jacobi7_launch(in, src, dst, st->variant, st->zsplit, 0, in->n[0], s);
+    }
+    if (rc == HPCX_OK && (steps & 1) == 0) std::swap(in->dev, out->dev);
+  } else {
+    return fail(ctx, HPCX_INVALID_ARG, "unknown stencil kind");
+  }
+  if (rc != HPCX_OK) return rc;
+  if (!stream) HPCX_CUDA(ctx, cudaStreamSynchronize(s));
+  return HPCX_OK;
+}
