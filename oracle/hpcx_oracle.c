@@ -1,0 +1,479 @@
+/*
+ * hpcx_oracle.c — CPU ORACLE for libhpcx.  TEST INFRASTRUCTURE ONLY.
+ *
+ * Nothing in the product path (libhpc_b200/, include/) may call, link or import this file;
+ * only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs
+ * use it, as the checker or the timed CPU baseline.
+ *
+ * Pinning status:
+ *   - REFERENCE-PINNED: grid index math (orc_grid_*) and the 17-point box sweeps
+ *     (orc_box_sweep_*).  tests/test_oracle_vs_ref.py compares them bit-for-bit with the
+ *     reference's own header and loop bodies compiled into oracle/_ref/libhpcref.so
+ *     (oracle/Makefile), on this container; golden digests are committed in tests/golden/.
+ *   - PARITY UNPINNED by reference tests: CSR builders, SpMV, SELL, Jacobi-7, pack/unpack,
+ *     partitioner and halo maps.  The reference contains no such code and no golden
+ *     vectors; these are restatements of the contract in include/hpcx.h,
+ *     pinned by analytic known-answer tests in tests/test_oracle_kat.py.
+ *
+ * Arithmetic contract: every floating-point operation is rounded separately (build with
+ * -ffp-contract=off), sums run in ascending memory order.  Loop shape follows the
+ * reference's OpenMP idiom (tests/test_hpc_benchmark/test_hpc_benchmark.cpp:356-363).
+ */
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+
+#define ORC_API __attribute__((visibility("default")))
+
+/* ------------------------------------------------------------------ deterministic RNG
+ * Counter-based: u(seed, i) = top 53 bits of
+ * splitmix64_mix(splitmix64_mix(seed) ^ i) times 2^-53, in [0, 1). */
+static inline uint64_t orc_mix(uint64_t z) {
+  z += 0x9E3779B97F4A7C15ull;
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+  return z ^ (z >> 31);
+}
+ORC_API uint64_t orc_bits(uint64_t seed, uint64_t i) { return orc_mix(orc_mix(seed) ^ i); }
+ORC_API double orc_u(uint64_t seed, uint64_t i) {
+  return (double)(orc_bits(seed, i) >> 11) * (1.0 / 9007199254740992.0);
+}
+/* out[i] = 2u(seed, first + i) - 1 */
+ORC_API void orc_fill_f64(double *out, int64_t n, uint64_t seed, uint64_t first) {
+#pragma omp parallel for
+  for (int64_t i = 0; i < n; ++i) out[i] = 2.0 * orc_u(seed, first + (uint64_t)i) - 1.0;
+}
+ORC_API void orc_fill_f32(float *out, int64_t n, uint64_t seed, uint64_t first) {
+#pragma omp parallel for
+  for (int64_t i = 0; i < n; ++i) out[i] = (float)(2.0 * orc_u(seed, first + (uint64_t)i) - 1.0);
+}
+
+/* ------------------------------------------------------------------ grid index math
+ * compute_stride_and_total: lib/hpc/include/HPCHighDimensionFlatArray.hpp:161-171. */
+ORC_API int64_t orc_grid_stride_total(int ndim, const int64_t *dim, int64_t lo, int64_t hi,
+                                      int64_t *stride) {
+  int64_t total = 1;
+  for (int i = ndim; i-- > 0;) {
+    if (stride) stride[i] = total;
+    total *= dim[i] + lo + hi;
+  }
+  return total;
+}
+/* unsafe_linearize (…:180-187) for checked == 0, safe_linearize (…:197-208) otherwise.
+ * Returns 0, or 1 where the reference throws std::out_of_range. */
+ORC_API int orc_grid_linearize(int ndim, const int64_t *dim, int64_t lo, int64_t hi,
+                               const int64_t *idx, int checked, int64_t *offset) {
+  int64_t stride[8];
+  orc_grid_stride_total(ndim, dim, lo, hi, stride);
+  int64_t r = 0;
+  for (int i = ndim; i-- > 0;) {
+    if (checked && (idx[i] < -lo || idx[i] >= dim[i] + hi)) return 1;
+    r += stride[i] * (idx[i] + lo); /* padded_index, …:151-153 */
+  }
+  *offset = r;
+  return 0;
+}
+
+/* ------------------------------------------------------------------ box sweeps (a3, a4)
+ * b(y,x) = sum_{k=-r..r} a(y, x+k)   (axis 1: BM_x_blur, test_hpc_benchmark.cpp:354-368)
+ * b(y,x) = sum_{k=-r..r} a(y+k, x)   (axis 0: BM_y_blur, :444-457)
+ * res starts at 0 and taps are added in ascending k.  `a` is the flat buffer of a
+ * <2,T,alo,ahi> array of logical size ny x nx, `b` that of a <2,T,blo,bhi> array. */
+#define ORC_BOX(NAME, T)                                                                   \
+  ORC_API void NAME(const T *a, T *b, int64_t ny, int64_t nx, int64_t alo, int64_t ahi,    \
+                    int64_t blo, int64_t bhi, int axis, int radius) {                      \
+    const int64_t ap = nx + alo + ahi, bp = nx + blo + bhi;                                \
+    const int64_t step = axis == 1 ? 1 : ap;                                               \
+    _Pragma("omp parallel for") for (int64_t y = 0; y < ny; ++y) {                         \
+      for (int64_t x = 0; x < nx; ++x) {                                                   \
+        const T *p = a + (y + alo) * ap + (x + alo) - radius * step;                       \
+        T res = 0;                                                                         \
+        for (int k = -radius; k <= radius; ++k, p += step) res += *p;                      \
+        b[(y + blo) * bp + (x + blo)] = res;                                               \
+      }                                                                                    \
+    }                                                                                      \
+  }
+ORC_BOX(orc_box_sweep_f32, float)
+ORC_BOX(orc_box_sweep_f64, double)
+
+/* ------------------------------------------------------------------ Jacobi-7 (a10)
+ * out = (((((in[z-1]+in[y-1])+in[x-1])+in[x+1])+in[y+1])+in[z+1]) * (1/6) over the interior
+ * of a <3,T,lo,hi> array (lo, hi >= 1); ghosts of `out` are left untouched.  One sweep. */
+#define ORC_JACOBI(NAME, T)                                                                \
+  ORC_API void NAME(const T *in, T *out, int64_t nz, int64_t ny, int64_t nx, int64_t lo,   \
+                    int64_t hi) {                                                          \
+    const int64_t px = nx + lo + hi, py = ny + lo + hi;                                    \
+    const int64_t sy = px, sz = px * py;                                                   \
+    const T sixth = (T)1 / (T)6;                                                           \
+    _Pragma("omp parallel for collapse(2)") for (int64_t z = 0; z < nz; ++z) {             \
+      for (int64_t y = 0; y < ny; ++y) {                                                   \
+        const T *p = in + (z + lo) * sz + (y + lo) * sy + lo;                              \
+        T *q = out + (z + lo) * sz + (y + lo) * sy + lo;                                   \
+        for (int64_t x = 0; x < nx; ++x) {                                                 \
+          T s = p[x - sz] + p[x - sy];                                                     \
+          s = s + p[x - 1];                                                                \
+          s = s + p[x + 1];                                                                \
+          s = s + p[x + sy];                                                               \
+          s = s + p[x + sz];                                                               \
+          q[x] = s * sixth;                                                                \
+        }                                                                                  \
+      }                                                                                    \
+    }                                                                                      \
+  }
+ORC_JACOBI(orc_jacobi7_f32, float)
+ORC_JACOBI(orc_jacobi7_f64, double)
+
+/* ------------------------------------------------------------------ pack / unpack (a11)
+ * Host restatement of hpcx_grid_pack_face / hpcx_grid_unpack_face on the reference layout
+ * (3 dims, slowest first; ndim < 3 callers pass leading dims of 1 with lo = hi = 0 there
+ * via glo/ghi arrays).  es = element size in bytes. */
+ORC_API void orc_face_copy(void *grid, void *buf, const int64_t *n, const int64_t *glo,
+                           const int64_t *ghi, int axis, int side, int width, int ghost,
+                           int pack, int es) {
+  int64_t ext[3], b[3], s[3] = {0, 0, 0};
+  for (int i = 0; i < 3; ++i) ext[i] = b[i] = n[i] + glo[i] + ghi[i];
+  b[axis] = width;
+  if (ghost)
+    s[axis] = side ? glo[axis] + n[axis] : glo[axis] - width;
+  else
+    s[axis] = side ? glo[axis] + n[axis] - width : glo[axis];
+  char *g = (char *)grid, *q = (char *)buf;
+  for (int64_t z = 0; z < b[0]; ++z)
+    for (int64_t y = 0; y < b[1]; ++y) {
+      char *grow = g + ((((z + s[0]) * ext[1]) + (y + s[1])) * ext[2] + s[2]) * es;
+      char *brow = q + ((z * b[1] + y) * b[2]) * es;
+      if (pack)
+        memcpy(brow, grow, (size_t)b[2] * es);
+      else
+        memcpy(grow, brow, (size_t)b[2] * es);
+    }
+}
+
+/* ------------------------------------------------------------------ CSR builders (a7)
+ * 2-D 5-point Laplacian on an ny x nx grid: row i = y*nx + x,
+ * columns ascending {i-nx, i-1, i, i+1, i+nx}, out-of-grid neighbours omitted, values
+ * {-1,-1,4,-1,-1}.  nnz = 5*nx*ny - 2*nx - 2*ny.  row_ptr int64; val may be NULL. */
+ORC_API int64_t orc_laplace2d_nnz(int64_t ny, int64_t nx) { return 5 * nx * ny - 2 * nx - 2 * ny; }
+static inline int64_t lap2d_row_start(int64_t y, int64_t x, int64_t ny, int64_t nx) {
+  /* nonzeros in rows before (y, x): closed form so that rows can be filled in parallel */
+  int64_t before_rows = 0;
+  if (y > 0) {
+    /* row y' has 5*nx - 2 entries minus nx if y'==0 minus nx if y'==ny-1 */
+    before_rows = y * (5 * nx - 2) - nx - (y > ny - 1 ? nx : 0);
+  }
+  const int64_t per = 3 + (y > 0) + (y < ny - 1); /* interior-x cell of this grid row */
+  int64_t in_row = x * per;
+  if (x > 0) in_row -= 1; /* cell x = 0 has no left neighbour */
+  return before_rows + in_row;
+}
+ORC_API void orc_laplace2d_csr(int64_t ny, int64_t nx, int64_t *row_ptr, int32_t *col, double *val) {
+  const int64_t n = nx * ny;
+#pragma omp parallel for
+  for (int64_t y = 0; y < ny; ++y)
+    for (int64_t x = 0; x < nx; ++x) {
+      const int64_t i = y * nx + x;
+      int64_t p = lap2d_row_start(y, x, ny, nx);
+      row_ptr[i] = p;
+      if (y > 0) { col[p] = (int32_t)(i - nx); if (val) val[p] = -1.0; ++p; }
+      if (x > 0) { col[p] = (int32_t)(i - 1); if (val) val[p] = -1.0; ++p; }
+      col[p] = (int32_t)i; if (val) val[p] = 4.0; ++p;
+      if (x < nx - 1) { col[p] = (int32_t)(i + 1); if (val) val[p] = -1.0; ++p; }
+      if (y < ny - 1) { col[p] = (int32_t)(i + nx); if (val) val[p] = -1.0; ++p; }
+    }
+  row_ptr[n] = orc_laplace2d_nnz(ny, nx);
+}
+
+/* 3-D 27-point operator on an n^3 grid (C4): row i = (z*n+y)*n+x, the 27 neighbours in
+ * ascending column order with Dirichlet truncation, centre 26, others -1.
+ * nnz = (3n-2)^3.  Two passes: counts, then fill. */
+ORC_API int64_t orc_op27_nnz(int64_t n) { return (3 * n - 2) * (3 * n - 2) * (3 * n - 2); }
+ORC_API void orc_op27_csr(int64_t n, int64_t *row_ptr, int32_t *col, double *val) {
+  const int64_t N = n * n * n;
+  row_ptr[0] = 0;
+  for (int64_t i = 0; i < N; ++i) {
+    const int64_t x = i % n, y = (i / n) % n, z = i / (n * n);
+    const int64_t cx = 1 + (x > 0) + (x < n - 1), cy = 1 + (y > 0) + (y < n - 1),
+                  cz = 1 + (z > 0) + (z < n - 1);
+    row_ptr[i + 1] = row_ptr[i] + cx * cy * cz;
+  }
+#pragma omp parallel for
+  for (int64_t i = 0; i < N; ++i) {
+    const int64_t x = i % n, y = (i / n) % n, z = i / (n * n);
+    int64_t p = row_ptr[i];
+    for (int64_t dz = -1; dz <= 1; ++dz)
+      for (int64_t dy = -1; dy <= 1; ++dy)
+        for (int64_t dx = -1; dx <= 1; ++dx) {
+          const int64_t zz = z + dz, yy = y + dy, xx = x + dx;
+          if (zz < 0 || zz >= n || yy < 0 || yy >= n || xx < 0 || xx >= n) continue;
+          col[p] = (int32_t)((zz * n + yy) * n + xx);
+          if (val) val[p] = (dz == 0 && dy == 0 && dx == 0) ? 26.0 : -1.0;
+          ++p;
+        }
+  }
+}
+
+/* R-MAT (C5): 2^scale vertices, nedges generated edges, (a,b,c,d) = (.57,.19,.19,.05), no
+ * vertex permutation.  Edge k takes `scale` quadrant choices, level l from
+ * u(seed, k*scale + l): u < a -> (0,0); < a+b -> (0,1); < a+b+c -> (1,0); else (1,1), most
+ * significant bit first.  Value of edge k = (float)(2u(seed+1, k) - 1).  Edges are sorted by
+ * (row, col, k) and duplicates merged by adding their values in ascending k.
+ * Returns the merged nnz; row_ptr has 2^scale + 1 entries; col/val need room for nedges. */
+typedef struct { uint64_t key; uint32_t k; } orc_edge;
+static int orc_edge_cmp(const void *pa, const void *pb) {
+  const orc_edge *a = (const orc_edge *)pa, *b = (const orc_edge *)pb;
+  if (a->key != b->key) return a->key < b->key ? -1 : 1;
+  return a->k < b->k ? -1 : (a->k > b->k);
+}
+ORC_API int64_t orc_rmat_csr(int scale, int64_t nedges, uint64_t seed, int64_t *row_ptr,
+                             int32_t *col, float *val) {
+  const int64_t n = (int64_t)1 << scale;
+  orc_edge *e = (orc_edge *)malloc((size_t)nedges * sizeof(orc_edge));
+  if (!e) return -1;
+#pragma omp parallel for
+  for (int64_t k = 0; k < nedges; ++k) {
+    uint64_t r = 0, c = 0;
+    for (int l = 0; l < scale; ++l) {
+      const double u = orc_u(seed, (uint64_t)k * (uint64_t)scale + (uint64_t)l);
+      const int q = u < 0.57 ? 0 : u < 0.76 ? 1 : u < 0.95 ? 2 : 3;
+      r = (r << 1) | (uint64_t)(q >> 1);
+      c = (c << 1) | (uint64_t)(q & 1);
+    }
+    e[k].key = (r << 32) | c;
+    e[k].k = (uint32_t)k;
+  }
+  qsort(e, (size_t)nedges, sizeof(orc_edge), orc_edge_cmp);
+  memset(row_ptr, 0, (size_t)(n + 1) * sizeof(int64_t));
+  int64_t m = 0;
+  for (int64_t j = 0; j < nedges; ++j) {
+    const float v = (float)(2.0 * orc_u(seed + 1, e[j].k) - 1.0);
+    if (j > 0 && e[j].key == e[j - 1].key) {
+      val[m - 1] = val[m - 1] + v;
+    } else {
+      col[m] = (int32_t)(e[j].key & 0xffffffffu);
+      val[m] = v;
+      row_ptr[(e[j].key >> 32) + 1]++;
+      ++m;
+    }
+  }
+  for (int64_t i = 0; i < n; ++i) row_ptr[i + 1] += row_ptr[i];
+  free(e);
+  return m;
+}
+
+/* ------------------------------------------------------------------ SpMV (a8)
+ * y_i = sum_{p = row_ptr[i]}^{row_ptr[i+1]-1} values[p] * x[col_idx[p]], p ascending,
+ * product and sum rounded separately. */
+#define ORC_SPMV(NAME, T)                                                                  \
+  ORC_API void NAME(int64_t nrows, const int64_t *row_ptr, const int32_t *col, const T *val, \
+                    const T *x, T *y) {                                                    \
+    _Pragma("omp parallel for schedule(static)") for (int64_t i = 0; i < nrows; ++i) {      \
+      T s = 0;                                                                             \
+      for (int64_t p = row_ptr[i]; p < row_ptr[i + 1]; ++p) {                              \
+        const T prod = val[p] * x[col[p]];                                                 \
+        s = s + prod;                                                                      \
+      }                                                                                    \
+      y[i] = s;                                                                            \
+    }                                                                                      \
+  }
+ORC_SPMV(orc_spmv_f64, double)
+ORC_SPMV(orc_spmv_f32, float)
+/* int32 row_ptr flavour (what the CPU baseline times: same bytes as the GPU kernel reads) */
+#define ORC_SPMV32(NAME, T)                                                                \
+  ORC_API void NAME(int64_t nrows, const int32_t *row_ptr, const int32_t *col, const T *val, \
+                    const T *x, T *y) {                                                    \
+    _Pragma("omp parallel for schedule(static)") for (int64_t i = 0; i < nrows; ++i) {      \
+      T s = 0;                                                                             \
+      for (int32_t p = row_ptr[i]; p < row_ptr[i + 1]; ++p) {                              \
+        const T prod = val[p] * x[col[p]];                                                 \
+        s = s + prod;                                                                      \
+      }                                                                                    \
+      y[i] = s;                                                                            \
+    }                                                                                      \
+  }
+ORC_SPMV32(orc_spmv_i32_f64, double)
+ORC_SPMV32(orc_spmv_i32_f32, float)
+/* Row-wise magnitude sum_p |a_p x_p| in double (the tolerance scale of SURVEY.md §8c). */
+#define ORC_SPMV_ABS(NAME, T)                                                              \
+  ORC_API void NAME(int64_t nrows, const int64_t *row_ptr, const int32_t *col, const T *val, \
+                    const T *x, double *mag) {                                             \
+    _Pragma("omp parallel for") for (int64_t i = 0; i < nrows; ++i) {                       \
+      double s = 0;                                                                        \
+      for (int64_t p = row_ptr[i]; p < row_ptr[i + 1]; ++p) {                              \
+        double t = (double)val[p] * (double)x[col[p]];                                     \
+        s += t < 0 ? -t : t;                                                               \
+      }                                                                                    \
+      mag[i] = s;                                                                          \
+    }                                                                                      \
+  }
+ORC_SPMV_ABS(orc_spmv_abs_f64, double)
+ORC_SPMV_ABS(orc_spmv_abs_f32, float)
+
+/* ------------------------------------------------------------------ binning / SELL (a9)
+ * bins[0] = empty rows; bins[k] = rows with 2^(k-1) <= len < 2^k (k = bit length of len). */
+ORC_API void orc_row_bins(int64_t nrows, const int64_t *row_ptr, int64_t *bins34) {
+  memset(bins34, 0, 34 * sizeof(int64_t));
+  for (int64_t i = 0; i < nrows; ++i) {
+    int64_t len = row_ptr[i + 1] - row_ptr[i];
+    int b = 0;
+    for (; len; len >>= 1) ++b;
+    bins34[b]++;
+  }
+}
+/* SELL-C-sigma: inside every window of `sigma` consecutive rows, rows are ordered by
+ * descending length, ties by ascending row id (insertion sort = stable by construction);
+ * slice s holds sorted rows [s*C, (s+1)*C), stored column-major and padded to its longest
+ * row with value 0 and column min(row, ncols-1).  Lanes past nrows hold col 0 / val 0.
+ * Call with col == NULL to get sizes (returns padded nnz; slice_ptr/slice_len/perm filled). */
+ORC_API int64_t orc_sell_build(int64_t nrows, int64_t ncols, const int64_t *row_ptr,
+                               const int32_t *col, const void *val, int es, int C, int sigma,
+                               int32_t *perm, int64_t *slice_ptr, int32_t *slice_len,
+                               int32_t *scol, void *sval) {
+  for (int64_t i = 0; i < nrows; ++i) perm[i] = (int32_t)i;
+  if (sigma > 1)
+    for (int64_t w = 0; w < nrows; w += sigma) {
+      const int64_t e = w + sigma < nrows ? w + sigma : nrows;
+      for (int64_t i = w + 1; i < e; ++i) {
+        const int32_t r = perm[i];
+        const int64_t len = row_ptr[r + 1] - row_ptr[r];
+        int64_t j = i;
+        while (j > w && row_ptr[perm[j - 1] + 1] - row_ptr[perm[j - 1]] < len) {
+          perm[j] = perm[j - 1];
+          --j;
+        }
+        perm[j] = r;
+      }
+    }
+  const int64_t ns = (nrows + C - 1) / C;
+  slice_ptr[0] = 0;
+  for (int64_t s = 0; s < ns; ++s) {
+    int64_t m = 0;
+    for (int64_t j = s * C; j < (s + 1) * C && j < nrows; ++j) {
+      const int64_t len = row_ptr[perm[j] + 1] - row_ptr[perm[j]];
+      if (len > m) m = len;
+    }
+    slice_len[s] = (int32_t)m;
+    slice_ptr[s + 1] = slice_ptr[s] + m * C;
+  }
+  if (!scol) return slice_ptr[ns];
+  memset(scol, 0, (size_t)slice_ptr[ns] * 4);
+  memset(sval, 0, (size_t)slice_ptr[ns] * es);
+  for (int64_t s = 0; s < ns; ++s)
+    for (int lane = 0; lane < C; ++lane) {
+      const int64_t j = s * C + lane;
+      if (j >= nrows) continue;
+      const int32_t r = perm[j];
+      const int64_t a = row_ptr[r], rl = row_ptr[r + 1] - a;
+      for (int64_t k = 0; k < slice_len[s]; ++k) {
+        const int64_t i = slice_ptr[s] + k * C + lane;
+        if (k < rl) {
+          scol[i] = col[a + k];
+          memcpy((char *)sval + i * es, (const char *)val + (a + k) * es, (size_t)es);
+        } else {
+          scol[i] = (int32_t)(r < ncols - 1 ? r : ncols - 1);
+        }
+      }
+    }
+  return slice_ptr[ns];
+}
+
+/* ------------------------------------------------------------------ partitioner (a12)
+ * mode 0: the reference's static chunking, chunk = ceil(n/P), [p*chunk, min((p+1)*chunk, n))
+ * (tests/test_hpc_benchmark/test_hpc_benchmark.cpp:1356,1371-1372).
+ * mode 1: bounds[p] = first row r with row_ptr[r] >= floor(nnz*p/P) (linear scan here). */
+ORC_API void orc_partition_rows(int64_t nrows, const int64_t *row_ptr, int nparts, int mode,
+                                int64_t *bounds) {
+  if (mode == 0) {
+    const int64_t chunk = (nrows + nparts - 1) / nparts;
+    for (int p = 0; p <= nparts; ++p) bounds[p] = p * chunk < nrows ? p * chunk : nrows;
+    return;
+  }
+  const int64_t nnz = row_ptr[nrows];
+  bounds[0] = 0;
+  for (int p = 1; p < nparts; ++p) {
+    const int64_t target = (int64_t)(((__int128)nnz * p) / nparts);
+    int64_t r = 0;
+    while (r < nrows && row_ptr[r] < target) ++r;
+    bounds[p] = r > bounds[p - 1] ? r : bounds[p - 1];
+  }
+  bounds[nparts] = nrows;
+}
+
+/* Local view of rank `rank` (contract: include/hpcx.h, hpcx_csr_localize), restated with
+ * explicit sorted lists instead of the product's mark arrays.  Outputs may be NULL except
+ * sizes[4] = {nloc, nnz_loc, nhalo, nsend}. */
+static int orc_i64_cmp(const void *a, const void *b) {
+  const int64_t x = *(const int64_t *)a, y = *(const int64_t *)b;
+  return x < y ? -1 : x > y;
+}
+static int64_t orc_sorted_unique(int64_t *v, int64_t n) {
+  if (n == 0) return 0;
+  qsort(v, (size_t)n, sizeof(int64_t), orc_i64_cmp);
+  int64_t m = 1;
+  for (int64_t i = 1; i < n; ++i)
+    if (v[i] != v[m - 1]) v[m++] = v[i];
+  return m;
+}
+static int64_t orc_find(const int64_t *v, int64_t n, int64_t key) {
+  int64_t lo = 0, hi = n;
+  while (lo < hi) {
+    const int64_t mid = (lo + hi) / 2;
+    if (v[mid] < key) lo = mid + 1; else hi = mid;
+  }
+  return lo;
+}
+ORC_API int orc_csr_localize(int64_t nrows, const int64_t *row_ptr, const int32_t *col,
+                             const int64_t *bounds, int nparts, int rank, int64_t *sizes,
+                             int64_t *local_row_ptr, int32_t *local_col, int64_t *halo_gcol,
+                             int64_t *recv_counts, int64_t *send_counts, int32_t *send_idx,
+                             uint8_t *row_kind) {
+  const int64_t r0 = bounds[rank], r1 = bounds[rank + 1], nloc = r1 - r0;
+  const int64_t p0 = row_ptr[r0], p1 = row_ptr[r1];
+  int64_t *halo = (int64_t *)malloc((size_t)(p1 - p0 + 1) * sizeof(int64_t));
+  int64_t nh = 0;
+  for (int64_t p = p0; p < p1; ++p)
+    if (col[p] < r0 || col[p] >= r1) halo[nh++] = col[p];
+  nh = orc_sorted_unique(halo, nh);
+  sizes[0] = nloc;
+  sizes[1] = p1 - p0;
+  sizes[2] = nh;
+  if (local_row_ptr)
+    for (int64_t i = 0; i <= nloc; ++i) local_row_ptr[i] = row_ptr[r0 + i] - p0;
+  if (local_col)
+    for (int64_t p = p0; p < p1; ++p)
+      local_col[p - p0] = (col[p] >= r0 && col[p] < r1)
+                              ? (int32_t)(col[p] - r0)
+                              : (int32_t)(nloc + orc_find(halo, nh, col[p]));
+  if (row_kind)
+    for (int64_t i = 0; i < nloc; ++i) {
+      row_kind[i] = 0;
+      for (int64_t p = row_ptr[r0 + i]; p < row_ptr[r0 + i + 1]; ++p)
+        if (col[p] < r0 || col[p] >= r1) row_kind[i] = 1;
+    }
+  if (halo_gcol) memcpy(halo_gcol, halo, (size_t)nh * sizeof(int64_t));
+  if (recv_counts)
+    for (int q = 0; q < nparts; ++q) {
+      recv_counts[q] = 0;
+      for (int64_t h = 0; h < nh; ++h)
+        if (halo[h] >= bounds[q] && halo[h] < bounds[q + 1]) recv_counts[q]++;
+    }
+  free(halo);
+  /* send lists: what rank q's halo asks of us, i.e. q's sorted unique columns inside [r0,r1) */
+  int64_t nsend = 0;
+  for (int q = 0; q < nparts; ++q) {
+    if (send_counts) send_counts[q] = 0;
+    if (q == rank) continue;
+    const int64_t a = row_ptr[bounds[q]], b = row_ptr[bounds[q + 1]];
+    int64_t *want = (int64_t *)malloc((size_t)(b - a + 1) * sizeof(int64_t));
+    int64_t nw = 0;
+    for (int64_t p = a; p < b; ++p)
+      if (col[p] >= r0 && col[p] < r1) want[nw++] = col[p] - r0;
+    nw = orc_sorted_unique(want, nw);
+    if (send_idx)
+      for (int64_t i = 0; i < nw; ++i) send_idx[nsend + i] = (int32_t)want[i];
+    if (send_counts) send_counts[q] = nw;
+    nsend += nw;
+    free(want);
+  }
+  sizes[3] = nsend;
+  return 0;
+}
