@@ -1,0 +1,157 @@
+"""Deterministic synthetic inputs of BASELINE.json's configs (host side, numpy).
+
+These are input generators, not compute: the matrices and fields they build are what
+bench.py and the tests hand to the CUDA library.  The oracle has its own C generators
+(oracle/hpcx_oracle.c); tests/test_synth.py checks the two agree bit-for-bit.
+
+RNG: counter-based, u(seed, i) = (mix(mix(seed) ^ i) >> 11) * 2^-53 with
+mix = the splitmix64 finaliser, so any element can be generated independently.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+_G = np.uint64(0x9E3779B97F4A7C15)
+_M1 = np.uint64(0xBF58476D1CE4E5B9)
+_M2 = np.uint64(0x94D049BB133111EB)
+
+
+def _mix(z: np.ndarray) -> np.ndarray:
+    with np.errstate(over="ignore"):
+        z = z + _G
+        z = (z ^ (z >> np.uint64(30))) * _M1
+        z = (z ^ (z >> np.uint64(27))) * _M2
+        return z ^ (z >> np.uint64(31))
+
+
+def bits(seed: int, first: int, n: int) -> np.ndarray:
+    s = _mix(np.array([seed], dtype=np.uint64))[0]
+    idx = np.arange(first, first + n, dtype=np.uint64)
+    return _mix(s ^ idx)
+
+
+def uniform(seed: int, n: int, first: int = 0) -> np.ndarray:
+    """u(seed, first .. first+n) in [0, 1) as float64."""
+    return (bits(seed, first, n) >> np.uint64(11)).astype(np.float64) * (1.0 / 9007199254740992.0)
+
+
+def field(seed: int, n: int, dtype=np.float64, first: int = 0, chunk: int = 1 << 24) -> np.ndarray:
+    """2u - 1 in `dtype` (x vectors, grid fills), generated in chunks to bound memory."""
+    out = np.empty(n, dtype=dtype)
+    for a in range(0, n, chunk):
+        b = min(n, a + chunk)
+        out[a:b] = (2.0 * uniform(seed, b - a, first + a) - 1.0).astype(dtype)
+    return out
+
+
+def laplace2d(ny: int, nx: int, dtype=np.float64, index_dtype=np.int32):
+    """2-D 5-point Laplacian (C1/C2): row i = y*nx + x, columns ascending
+    {i-nx, i-1, i, i+1, i+nx} with out-of-grid neighbours omitted, values {-1,-1,4,-1,-1}."""
+    n = ny * nx
+    y = np.repeat(np.arange(ny, dtype=np.int64), nx)
+    x = np.tile(np.arange(nx, dtype=np.int64), ny)
+    has = np.stack([y > 0, x > 0, np.ones(n, dtype=bool), x < nx - 1, y < ny - 1], axis=1)
+    del y, x
+    i = np.arange(n, dtype=np.int64)[:, None]
+    off = np.array([-nx, -1, 0, 1, nx], dtype=np.int64)[None, :]
+    cols = (i + off)[has].astype(np.int32)
+    vals = np.broadcast_to(np.array([-1, -1, 4, -1, -1], dtype=dtype)[None, :], has.shape)[has]
+    rp = np.zeros(n + 1, dtype=np.int64)
+    np.cumsum(has.sum(axis=1), out=rp[1:])
+    return rp.astype(index_dtype), cols, np.ascontiguousarray(vals)
+
+
+def laplace2d_big(ny: int, nx: int, dtype=np.float64, index_dtype=np.int32, rows_per_chunk=1024):
+    """Same matrix as laplace2d, built in row-slab chunks (bounded temporaries; 8192^2)."""
+    nnz = 5 * nx * ny - 2 * nx - 2 * ny
+    rp = np.empty(ny * nx + 1, dtype=index_dtype)
+    col = np.empty(nnz, dtype=np.int32)
+    val = np.empty(nnz, dtype=dtype)
+    p = 0
+    for y0 in range(0, ny, rows_per_chunk):
+        y1 = min(ny, y0 + rows_per_chunk)
+        m = (y1 - y0) * nx
+        y = np.repeat(np.arange(y0, y1, dtype=np.int64), nx)
+        x = np.tile(np.arange(nx, dtype=np.int64), y1 - y0)
+        has = np.stack([y > 0, x > 0, np.ones(m, dtype=bool), x < nx - 1, y < ny - 1], axis=1)
+        i = (y * nx + x)[:, None]
+        off = np.array([-nx, -1, 0, 1, nx], dtype=np.int64)[None, :]
+        c = (i + off)[has]
+        k = len(c)
+        col[p:p + k] = c
+        val[p:p + k] = np.broadcast_to(np.array([-1, -1, 4, -1, -1], dtype=dtype)[None, :],
+                                       has.shape)[has]
+        cnt = has.sum(axis=1)
+        rp[y0 * nx:y1 * nx] = p + np.cumsum(cnt) - cnt
+        p += k
+    rp[ny * nx] = p
+    assert p == nnz
+    return rp, col, val
+
+
+def op27(n: int, dtype=np.float64, index_dtype=np.int32, z_lo: int = 0, z_hi: int | None = None):
+    """3-D 27-point operator on n^3 (C4): 27 neighbours ascending, Dirichlet truncation,
+    centre 26, others -1.  [z_lo, z_hi) selects a slab of rows (global column numbering)."""
+    z_hi = n if z_hi is None else z_hi
+    zz, yy, xx = np.meshgrid(np.arange(z_lo, z_hi, dtype=np.int64), np.arange(n, dtype=np.int64),
+                             np.arange(n, dtype=np.int64), indexing="ij")
+    zz, yy, xx = zz.ravel(), yy.ravel(), xx.ravel()
+    m = len(zz)
+    has = np.empty((m, 27), dtype=bool)
+    off = np.empty(27, dtype=np.int64)
+    k = 0
+    for dz in (-1, 0, 1):
+        for dy in (-1, 0, 1):
+            for dx in (-1, 0, 1):
+                has[:, k] = ((zz + dz >= 0) & (zz + dz < n) & (yy + dy >= 0) & (yy + dy < n) &
+                             (xx + dx >= 0) & (xx + dx < n))
+                off[k] = (dz * n + dy) * n + dx
+                k += 1
+    i = ((zz * n + yy) * n + xx)[:, None]
+    cols = (i + off[None, :])[has].astype(np.int32)
+    v = np.full(27, -1, dtype=dtype)
+    v[13] = 26
+    vals = np.ascontiguousarray(np.broadcast_to(v[None, :], has.shape)[has])
+    rp = np.zeros(m + 1, dtype=np.int64)
+    np.cumsum(has.sum(axis=1), out=rp[1:])
+    return rp.astype(index_dtype), cols, vals
+
+
+def rmat(scale: int, edge_factor: int = 16, seed: int = 24, index_dtype=np.int32):
+    """R-MAT (C5): (a,b,c,d) = (.57,.19,.19,.05), no vertex permutation, level l of edge k
+    from u(seed, k*scale + l); values (float32)(2u(seed+1, k) - 1); sorted by (row, col, k),
+    duplicates merged by adding in ascending k."""
+    n = 1 << scale
+    ne = n * edge_factor
+    r = np.zeros(ne, dtype=np.uint64)
+    c = np.zeros(ne, dtype=np.uint64)
+    k = np.arange(ne, dtype=np.uint64)
+    s = _mix(np.array([seed], dtype=np.uint64))[0]
+    for l in range(scale):
+        with np.errstate(over="ignore"):
+            u = (_mix(s ^ (k * np.uint64(scale) + np.uint64(l))) >> np.uint64(11)).astype(
+                np.float64) * (1.0 / 9007199254740992.0)
+        q = (u >= 0.57).astype(np.uint64) + (u >= 0.76) + (u >= 0.95)
+        r = (r << np.uint64(1)) | (q >> np.uint64(1))
+        c = (c << np.uint64(1)) | (q & np.uint64(1))
+    key = (r << np.uint64(32)) | c
+    order = np.argsort(key, kind="stable")  # stable => ties stay in ascending k
+    key = key[order]
+    v = (2.0 * uniform(seed + 1, ne) - 1.0).astype(np.float32)[order]
+    first = np.ones(ne, dtype=bool)
+    first[1:] = key[1:] != key[:-1]
+    starts = np.flatnonzero(first)
+    col = (key[starts] & np.uint64(0xFFFFFFFF)).astype(np.int32)
+    rows = (key[starts] >> np.uint64(32)).astype(np.int64)
+    # sequential float32 accumulation inside each duplicate run, ascending k
+    val = v[starts].copy()
+    run = np.diff(np.append(starts, ne))
+    j = 1
+    todo = np.flatnonzero(run > j)
+    while len(todo):
+        val[todo] = val[todo] + v[starts[todo] + j]
+        j += 1
+        todo = todo[run[todo] > j]
+    rp = np.zeros(n + 1, dtype=np.int64)
+    np.cumsum(np.bincount(rows, minlength=n), out=rp[1:])
+    return rp.astype(index_dtype), col, val

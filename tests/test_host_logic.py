@@ -1,0 +1,147 @@
+"""Host-side logic of the product through the C ABI (no GPU): grid index math, partitioner,
+halo maps, synthetic generators — bit-exact against the oracle and the reference golden."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+import libhpc_b200 as hp
+import oracle
+from libhpc_b200 import synth
+from util import random_csr
+
+G = os.path.join(os.path.dirname(__file__), "golden")
+INDEX = json.load(open(os.path.join(G, "index_ref.json")))
+
+
+def test_grid_index_math_matches_reference_golden():
+    for c in INDEX:
+        a = hp.HPCHighDimensionFlatArray.__new__(hp.HPCHighDimensionFlatArray)
+        if c["total"] > 1 << 26:  # do not allocate the 8192^2 / 512^3 buffers here
+            hp.HPCHighDimensionFlatArray.__init__(a, *c["dim"], lo=c["lo"], hi=c["hi"],
+                                                  buffer=np.lib.stride_tricks.as_strided(
+                                                      np.zeros(1, np.float32), (c["total"],), (0,)))
+        else:
+            hp.HPCHighDimensionFlatArray.__init__(a, *c["dim"], lo=c["lo"], hi=c["hi"])
+        assert list(a.stride) == c["stride"] and a.total == c["total"]
+        assert a._lin(tuple(c["idx"]), 0) == c["unsafe"]
+        if c["safe"] is None:
+            with pytest.raises(IndexError):  # std::out_of_range in the reference
+                a.at(c["idx"])
+        else:
+            assert a._lin(tuple(c["idx"]), 1) == c["safe"]
+
+
+def test_array_container_semantics():
+    a = hp.HPCHighDimensionFlatArray(4, 6, dtype=np.float32, lo=2)
+    assert a.data().shape == (8 * 10,) and not a.data().any()  # value-initialised, ghosts zero
+    a.set((-2, -2), 5.0)
+    a.set((3, 5), 7.0)
+    assert a.data()[0] == 5.0 and a(-2, -2) == 5.0 and a.at((3, 5)) == 7.0
+    assert a.interior()[3, 5] == 7.0 and a.padded_view()[0, 0] == 5.0
+    with pytest.raises(IndexError):
+        a.at((4 + 2, 0))
+    with pytest.raises(ValueError):
+        hp.HPCHighDimensionFlatArray(0, 4)
+    with pytest.raises(TypeError):
+        hp.HPCHighDimensionFlatArray(4, dtype=np.int32)
+    b = hp.HPCHighDimensionFlatArray(3, 4, 5, dtype=np.float64, lo=1, hi=3)
+    assert b.stride == (8 * 9, 9, 1) and b.total == 7 * 8 * 9
+
+
+@pytest.mark.parametrize("n,p", [(10, 4), (3, 8), (0, 2), (512, 8), (513, 8), (1, 1)])
+def test_partition_slabs_static_chunking(n, p):
+    chunk = (n + p - 1) // p
+    want = [min(i * chunk, n) for i in range(p + 1)]
+    assert list(hp.partition_slabs(n, p)) == want
+    assert list(hp.partition_rows(n, None, p, 0)) == want
+    assert list(oracle.partition_rows(None, n, p, 0)) == want
+
+
+@pytest.mark.parametrize("idx", [np.int32, np.int64])
+def test_partition_rows_by_nnz_matches_oracle(idx):
+    rp, col, val = oracle.rmat(11, 8, 3)
+    for p in (1, 2, 3, 4, 8):
+        got = hp.partition_rows(len(rp) - 1, rp.astype(idx), p, 1)
+        assert np.array_equal(got, oracle.partition_rows(rp, len(rp) - 1, p, 1))
+        assert got[0] == 0 and got[-1] == len(rp) - 1 and (np.diff(got) >= 0).all()
+
+
+def _check_localize(rp, col, val, bounds):
+    A = hp.CsrMatrix(rp, col, val)
+    for r in range(len(bounds) - 1):
+        got = hp.csr_localize(A, bounds, r)
+        want = oracle.localize(rp, col, bounds, r)
+        for k in ("nloc", "nnz_loc", "nhalo", "nsend"):
+            assert got[k] == want[k], k
+        for k in ("local_row_ptr", "local_col", "halo_gcol", "recv_counts", "send_counts",
+                  "send_idx", "row_kind"):
+            assert np.array_equal(got[k], want[k]), (k, r)  # bit-exact integer structure
+
+
+def test_localize_matches_oracle_banded():
+    rp, col, val = oracle.op27(6)
+    _check_localize(rp, col, val, hp.partition_rows(6 ** 3, rp, 4, 0))
+    rp, col, val = oracle.laplace2d(9, 7)
+    _check_localize(rp.astype(np.int32), col, val, hp.partition_rows(63, rp, 3, 1))
+
+
+def test_localize_matches_oracle_irregular_and_empty_parts():
+    rp, col, val = oracle.rmat(9, 8, 5)
+    _check_localize(rp, col, val, hp.partition_rows(512, rp, 8, 1))
+    _check_localize(rp, col, val, np.array([0, 0, 100, 100, 512], dtype=np.int64))
+    lens = [0, 3, 0, 0, 12, 1, 0, 40, 2, 0]
+    rp, col, val = random_csr(10, 10, lens, 2, np.float32)
+    _check_localize(rp, col, val, np.array([0, 4, 5, 10], dtype=np.int64))
+
+
+def test_localize_send_recv_are_mutually_consistent():
+    rp, col, val = oracle.rmat(9, 8, 6)
+    A = hp.CsrMatrix(rp, col, val)
+    P = 4
+    bounds = hp.partition_rows(512, rp, P, 1)
+    L = [hp.csr_localize(A, bounds, r) for r in range(P)]
+    for r in range(P):
+        for q in range(P):
+            assert L[r]["send_counts"][q] == L[q]["recv_counts"][r]
+        # what r sends to q are exactly q's halo columns owned by r, in q's halo order
+        off = 0
+        for q in range(P):
+            n = L[r]["send_counts"][q]
+            sent = L[r]["send_idx"][off:off + n] + bounds[r]
+            roff = L[q]["recv_counts"][:r].sum()
+            assert np.array_equal(sent, L[q]["halo_gcol"][roff:roff + n])
+            off += n
+
+
+def test_synth_generators_match_oracle_bit_for_bit():
+    for ny, nx in ((1, 1), (6, 5), (1, 7), (64, 33)):
+        a = oracle.laplace2d(ny, nx)
+        for b in (synth.laplace2d(ny, nx, index_dtype=np.int64),
+                  synth.laplace2d_big(ny, nx, index_dtype=np.int64, rows_per_chunk=5)):
+            assert all(np.array_equal(u, v) and u.dtype == v.dtype for u, v in zip(a, b))
+    a, b = oracle.op27(5), synth.op27(5, index_dtype=np.int64)
+    assert all(np.array_equal(u, v) for u, v in zip(a, b))
+    a, b = oracle.rmat(11, 16, 24), synth.rmat(11, 16, 24, index_dtype=np.int64)
+    assert all(np.array_equal(u, v) and u.dtype == v.dtype for u, v in zip(a, b))
+    assert np.array_equal(oracle.fill(1000, 42, np.float64, 5), synth.field(42, 1000, np.float64, 5))
+    assert np.array_equal(oracle.fill(1000, 7, np.float32), synth.field(7, 1000, np.float32, chunk=64))
+
+
+def test_op27_slab_rows_equal_global_rows():
+    rp, col, val = synth.op27(6, index_dtype=np.int64)
+    rs, cs, vs = synth.op27(6, index_dtype=np.int64, z_lo=2, z_hi=4)
+    a, b = rp[2 * 36], rp[4 * 36]
+    assert np.array_equal(cs, col[a:b]) and np.array_equal(vs, val[a:b])
+    assert np.array_equal(rs, rp[2 * 36:4 * 36 + 1] - a)
+
+
+def test_compute_entry_points_fail_loudly_without_gpu():
+    """No CPU fallback: without a device the context cannot be created."""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    with pytest.raises(hp.HpcxError) as e:
+        hp.Context(0)
+    assert e.value.status == hp._abi.CUDA_ERROR and "no CPU fallback" in str(e.value)
