@@ -1,0 +1,424 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the hot path (BASELINE.json metric).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+Workload (config.workload): configs[1] of BASELINE.json — CSR SpMV y = A*x, fp64, on the
+2-D 5-point Laplacian of an 8192 x 8192 grid (67.1 M rows, 335.5 M nnz) per GPU.  At N > 1
+the grid grows to (8192*N) x 8192 and is row-partitioned into N slabs (weak scaling); each
+product exchanges one grid row of x (8192 doubles) with each neighbour through
+hpcx_spmv_dist (NCCL send/recv on the library's comm stream, overlapped with interior rows).
+
+A step is one product.  `value` = effective GB/s = algorithmic bytes (12 B/nnz + 20 B/row,
+SURVEY.md §8d) of all ranks / max-over-ranks device time, operands resident in HBM.
+`e2e` is the same metric through the reference-facing host call (hpcx_spmv with HOST x and
+y: H2D of x and D2H of y inside the timed region, matrix resident as in any iterative use).
+The matrix (4.3 GB) is far larger than L2 (126 MB), so no explicit flush is needed.
+
+--impl reference times the CPU restatement of the path (oracle/, OpenMP, all host threads)
+on the same matrix: the reference itself has no SpMV, so kind = "port".
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+GRID = 8192  # configs[1]
+METRIC = "spmv_effective_GBps"
+UNIT = "GB/s"
+
+
+def log(*a):
+    print(*a, file=sys.stderr, flush=True)
+
+
+def measured_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.rows, self.proc = [], None
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.time(), [c.strip() for c in line.split(",")]))
+
+    def stop(self, t0: float, t1: float):
+        if not self.proc:
+            return None
+        time.sleep(0.25)
+        self.proc.terminate()
+        rows = [r for t, r in self.rows if t0 - 0.05 <= t <= t1 + 0.15] or [r for _, r in self.rows]
+        sm = [float(r[0]) for r in rows if r[0].replace(".", "").isdigit()]
+        if not sm:
+            return None
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(r[3 + i] == "Active" for r in rows)]
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(rows[0][1]), "reasons": reasons,
+                "samples": len(sm)}
+
+
+def build_local_problem(world: int, rank: int):
+    """This rank's slab of the (GRID*world) x GRID Laplacian in local numbering."""
+    from libhpc_b200 import synth
+    t = time.time()
+    L = synth.laplace2d_slab_local(GRID * world, GRID, rank * GRID, (rank + 1) * GRID)
+    L["recv_counts"], L["send_counts"] = synth.slab_counts(L, world, rank, GRID)
+    L["local_row_ptr"] = L["local_row_ptr"].astype(np.int32)
+    log(f"[rank {rank}] built slab: {L['nloc']} rows, {L['nnz_loc']} nnz in {time.time() - t:.1f}s")
+    return L
+
+
+def algorithmic_bytes(nrows: int, nnz: int, es: int = 8) -> int:
+    return nnz * (es + 4) + nrows * (4 + 2 * es) + 4
+
+
+def cpu_spmv_baseline(L: dict, x: np.ndarray, budget_s: float = 12.0, min_reps: int = 3, max_reps: int = 20):
+    """The CPU restatement (oracle/hpcx_oracle.c: orc_spmv_i32_f64, OpenMP static rows, product
+    and sum rounded separately) timed on this box's host cores on the SAME matrix.
+    This is the one place bench.py executes oracle/: as the measured CPU baseline."""
+    import oracle
+    rp, col, val = L["local_row_ptr"], L["local_col"], np.ascontiguousarray(L["values"])
+    xfull = np.zeros(L["nloc"] + L["nhalo"])
+    xfull[:L["nloc"]] = x
+    y = np.empty(L["nloc"])
+    oracle.spmv(rp, col, val, xfull, out=y)  # warm-up (first touch of y, page faults)
+    times = []
+    t_start = time.time()
+    while len(times) < min_reps or (time.time() - t_start < budget_s and len(times) < max_reps):
+        t = time.perf_counter()
+        oracle.spmv(rp, col, val, xfull, out=y)
+        times.append(time.perf_counter() - t)
+    return times
+
+
+def host_threads() -> int:
+    n = len(os.sched_getaffinity(0))
+    env = os.environ.get("OMP_NUM_THREADS")
+    return min(n, int(env)) if env and env.isdigit() else n
+
+
+def run_reference(args, rank: int, world: int):
+    """--impl reference: the CPU path on the host cores, rank 0 only."""
+    if rank != 0:
+        return
+    L = build_local_problem(1, 0)
+    from libhpc_b200 import synth
+    x = synth.field(42, L["nloc"])
+    import oracle
+    rp, col, val = L["local_row_ptr"], L["local_col"], np.ascontiguousarray(L["values"])
+    y = np.empty(L["nloc"])
+    for _ in range(max(args.warmup, 1)):
+        oracle.spmv(rp, col, val, x, out=y)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        oracle.spmv(rp, col, val, x, out=y)
+    dt = time.perf_counter() - t0
+    nbytes = algorithmic_bytes(L["nloc"], L["nnz_loc"])
+    gbs = nbytes * args.steps / dt / 1e9
+    cores = host_threads()
+    sample = f"full configs[1] matrix ({L['nloc']} rows, {L['nnz_loc']} nnz), {args.steps} products"
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": gbs, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic", "config": workload_config(1),
+        "cpu_baseline": {"value": gbs, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample,
+                         "note": "the reference has no SpMV (SURVEY.md §0); this is the OpenMP CPU "
+                                 "restatement in oracle/hpcx_oracle.c"},
+        "e2e": {"value": gbs, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0, "checksum": float(np.abs(y).sum()),
+    }), flush=True)
+
+
+def workload_config(world: int) -> dict:
+    return {"workload": "BASELINE configs[1]: CSR SpMV fp64, 2-D 5-point Laplacian 8192x8192 per GPU "
+                        "(67,108,864 rows, 335,511,552 nnz at N=1)",
+            "grid": [GRID * world, GRID], "rows_per_gpu": GRID * GRID,
+            "partition": "1 slab" if world == 1 else f"{world} row slabs, x-halo 8192 doubles per neighbour",
+            "l2": "inputs (4.3 GB matrix per GPU) larger than L2; no explicit flush",
+            "algorithmic_bytes": "12 B/nnz + 20 B/row (SURVEY.md §8d)"}
+
+
+def time_steps(torch, stream, step, steps: int, barrier):
+    """K steps between two events on `stream`, bracketed by barrier + synchronize."""
+    barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    w0 = time.time()
+    e0.record(stream)
+    for _ in range(steps):
+        step()
+    e1.record(stream)
+    torch.cuda.synchronize()
+    w1 = time.time()
+    barrier()
+    return e0.elapsed_time(e1) * 1e-3, w0, w1
+
+
+def run_ours(args, rank: int, world: int, local: int):
+    import torch
+    import torch.distributed as dist
+
+    import libhpc_b200 as hp
+    from libhpc_b200 import dist as hd
+    from libhpc_b200 import synth
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (libhpcx has no CPU fallback)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    ctx = hp.Context(local)
+    if world > 1:
+        hd.init_comm(ctx, rank, world)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+
+    def max_over_ranks(v: float) -> float:
+        if world == 1:
+            return v
+        t = torch.tensor([v], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    L = build_local_problem(world, rank)
+    nloc, nnz = L["nloc"], L["nnz_loc"]
+    A = hp.CsrMatrix(L["local_row_ptr"], L["local_col"], L["values"], ncols=nloc + L["nhalo"])
+    t = time.time()
+    D = hp.DeviceCsr(ctx, A)
+    if world > 1:
+        D.set_halo(L)
+    log(f"[rank {rank}] hpcx_csr_create {time.time() - t:.1f}s")
+
+    stream = torch.cuda.Stream()
+    x_pin = torch.empty(nloc, dtype=torch.float64).pin_memory()
+    y_pin = torch.empty(nloc, dtype=torch.float64).pin_memory()
+    x_pin.numpy()[:] = synth.field(42, nloc, first=rank * nloc)
+    yd = torch.empty(nloc, dtype=torch.float64, device="cuda")
+    if world == 1:
+        xd = x_pin.cuda()
+        x_arg = xd
+        step = lambda: D.spmv(x_arg, yd, stream)  # noqa: E731
+    else:
+        xd = torch.empty(nloc, dtype=torch.float64, device="cuda")
+        xd.copy_(x_pin)
+        xfull = D.x_buffer()  # [owned | halo]: write owned x in place, no per-step device copy
+        ctx.memcpy((xfull, hp.MEM_DEVICE), xd, nloc * 8)
+        x_arg = (xfull, hp.MEM_DEVICE)
+        step = lambda: D.spmv_dist(x_arg, yd, stream)  # noqa: E731
+    torch.cuda.synchronize()
+
+    # ---- device-resident timing
+    with torch.cuda.stream(stream):
+        for _ in range(args.warmup):
+            step()
+        sampler = ClockSampler(local) if rank == 0 else None
+        n0 = ctx.launch_count()
+        dt, w0, w1 = time_steps(torch, stream, step, args.steps, barrier)
+        launches = ctx.launch_count() - n0
+        clocks = sampler.stop(w0, w1) if sampler else None
+    dt = max_over_ranks(dt)
+    nbytes_rank = algorithmic_bytes(nloc, nnz)
+    value = nbytes_rank * world * args.steps / dt / 1e9
+
+    # ---- property check of the timed operator (no oracle here): A*1 = missing-neighbour count
+    ones = torch.ones(nloc + L["nhalo"], dtype=torch.float64, device="cuda")
+    if world == 1:
+        D.spmv(ones, yd, stream)
+    else:
+        ctx.memcpy((xfull, hp.MEM_DEVICE), ones, nloc * 8)
+        D.spmv_dist(x_arg, yd, stream)
+    stream.synchronize()
+    yv = yd.view(GRID, GRID)
+    expect = torch.zeros(GRID, GRID, dtype=torch.float64, device="cuda")
+    expect[:, 0] += 1
+    expect[:, -1] += 1
+    if rank == 0:
+        expect[0] += 1
+    if rank == world - 1:
+        expect[-1] += 1
+    if not torch.equal(yv, expect):
+        raise SystemExit(f"[rank {rank}] bench.py: A*1 does not match the closed form")
+    if world > 1:
+        ctx.memcpy((xfull, hp.MEM_DEVICE), xd, nloc * 8)
+
+    # ---- end to end: host x in, host y out, every step
+    def e2e_step():
+        if world == 1:
+            D.spmv(x_pin.numpy(), y_pin.numpy(), stream)  # hpcx_spmv(HOST, HOST): H2D + kernel + D2H + sync
+        else:
+            xd.copy_(x_pin, non_blocking=True)
+            D.spmv_dist(xd, yd, stream)
+            y_pin.copy_(yd, non_blocking=True)
+            stream.synchronize()
+
+    with torch.cuda.stream(stream):
+        for _ in range(min(args.warmup, 3)):
+            e2e_step()
+        k_e2e = max(3, min(args.steps, 10))
+        dt_e2e, _, _ = time_steps(torch, stream, e2e_step, k_e2e, barrier)
+    dt_e2e = max_over_ranks(dt_e2e)
+    e2e_value = nbytes_rank * world * k_e2e / dt_e2e / 1e9
+    checksum = float(np.abs(y_pin.numpy()).sum())
+
+    extra = stencil_extra(ctx, torch, stream, world, rank, barrier, max_over_ranks, hp, hd, synth)
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        times = cpu_spmv_baseline(L, x_pin.numpy())
+        best = min(times)
+        cpu = {"value": nbytes_rank / best / 1e9, "unit": UNIT, "cores": host_threads(), "kind": "port",
+               "sample": f"full configs[1] matrix, best of {len(times)} products (mean "
+                         f"{nbytes_rank / np.mean(times) / 1e9:.1f} GB/s) after 1 warm-up",
+               "note": "OpenMP CPU restatement oracle/hpcx_oracle.c:orc_spmv_i32_f64; the reference has no SpMV"}
+
+    if rank == 0:
+        peak, how = measured_peak()
+        per_launch_s = dt / args.steps
+        achieved = nbytes_rank / per_launch_s / 1e9
+        traffic = None
+        tp = os.path.join(ROOT, "profiles", "traffic.json")
+        if os.path.exists(tp):
+            traffic = json.load(open(tp)).get("spmv_stream_kernel_c2_dram_bytes_per_launch")
+        print(json.dumps({
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": workload_config(world),
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak, "traffic": traffic, "peak_source": how,
+                         "kernel": "spmv_stream_kernel<double,2048>",
+                         "frac_of_nominal_8000": achieved / 8000.0,
+                         "algorithmic_bytes_per_launch": nbytes_rank,
+                         "note": "per-rank step time / per-rank bytes" + (
+                             "" if world == 1 else " (step = gather + interior + boundary kernels)")},
+            "cpu_baseline": cpu,
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": nloc * 8 * world,
+                    "d2h_bytes_per_step": nloc * 8 * world, "steps": k_e2e,
+                    "ms_per_step": dt_e2e / k_e2e * 1e3,
+                    "call": "hpcx_spmv(A, x HOST, y HOST)" if world == 1 else
+                            "pinned H2D + hpcx_spmv_dist + D2H per rank"},
+            "gpu_launches": launches, "clocks": clocks, "checksum": checksum, "extra": extra,
+        }), flush=True)
+    D.destroy()
+    ctx.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def stencil_extra(ctx, torch, stream, world, rank, barrier, max_over_ranks, hp, hd, synth):
+    """Second half of BASELINE.json's metric: stencil Gcell-updates/s.
+    configs[2]: 3-D 7-point Jacobi, 512^3 fp32 per GPU (z-slabs of a 512*N x 512 x 512 domain at
+    N > 1, ghost planes exchanged every sweep), 8 B/cell algorithmic; and at N = 1 the
+    reference-native 17-point box sweeps on 8192^2 fp32 (R0)."""
+    out = {}
+    n, T = 512, 50
+    peak, _ = measured_peak()
+    f = synth.field(7, (n + 2) ** 3, np.float32, first=rank * (n + 2) ** 3)
+    ga, gb = hp.DeviceGrid(ctx, (n, n, n), np.float32, 1), hp.DeviceGrid(ctx, (n, n, n), np.float32, 1)
+    ga.upload(f)
+    gb.upload(f)
+    del f
+    plan = hd.HaloPlan(ctx, ga, gb, hp.STENCIL_JACOBI7) if world > 1 else None
+    for variant, name in ((hp.VARIANT_TMA, "tma"), (hp.VARIANT_DIRECT, "direct")):
+        if world > 1 and name == "direct":
+            continue
+        if world > 1:
+            step = lambda: plan.sweep(T, stream)  # noqa: E731
+        else:
+            step = lambda: hp.stencil_sweep(ga, gb, hp.STENCIL_JACOBI7, steps=T, variant=variant,  # noqa: E731
+                                            stream=stream)
+        with torch.cuda.stream(stream):
+            step()
+            n0 = ctx.launch_count()
+            dt, _, _ = time_steps(torch, stream, step, 2, barrier)
+            launches = ctx.launch_count() - n0
+        dt = max_over_ranks(dt)
+        cells = n ** 3 * world * T * 2
+        out[f"jacobi7_512cubed_fp32_{name}"] = {
+            "metric": "stencil_Gcell_updates_per_s", "value": cells / dt / 1e9, "sweeps": 2 * T,
+            "ms_per_sweep": dt / (2 * T) * 1e3, "gpu_launches": launches,
+            "roofline": {"bound": "hbm", "achieved": cells * 8 / world / dt / 1e9, "peak": peak,
+                         "unit": "GB/s", "frac": cells * 8 / world / dt / 1e9 / peak,
+                         "algorithmic_bytes_per_cell": 8}}
+    if plan:
+        plan.destroy()
+    ga.destroy()
+    gb.destroy()
+    if world == 1:
+        m = 8192
+        a = hp.DeviceGrid(ctx, (m, m), np.float32, 8)
+        b = hp.DeviceGrid(ctx, (m, m), np.float32, 0)
+        a.upload(synth.field(3, (m + 16) ** 2, np.float32))
+        for kind, name in ((hp.STENCIL_BOX_X, "box_x"), (hp.STENCIL_BOX_Y, "box_y")):
+            step = lambda: hp.stencil_sweep(a, b, kind, radius=8, stream=stream)  # noqa: E731
+            with torch.cuda.stream(stream):
+                for _ in range(3):
+                    step()
+                dt, _, _ = time_steps(torch, stream, step, 20, barrier)
+            out[f"r0_{name}_8192sq_fp32"] = {
+                "metric": "stencil_Gcell_updates_per_s", "value": m * m * 20 / dt / 1e9,
+                "ms_per_sweep": dt / 20 * 1e3,
+                "roofline": {"bound": "hbm", "achieved": m * m * 8 * 20 / dt / 1e9, "peak": peak,
+                             "unit": "GB/s", "frac": m * m * 8 * 20 / dt / 1e9 / peak}}
+        a.destroy()
+        b.destroy()
+    return out
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    if world != args.gpus and world == 1 and args.gpus > 1:
+        # launched without torchrun: re-exec under it, one rank per GPU
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1",
+               f"--nproc-per-node={args.gpus}", "--master-addr", "127.0.0.1", "--master-port", "29533",
+               os.path.abspath(__file__)] + sys.argv[1:]
+        raise SystemExit(subprocess.call(cmd))
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+    else:
+        run_ours(args, rank, world, local)
+
+
+if __name__ == "__main__":
+    main()

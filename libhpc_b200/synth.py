@@ -2,7 +2,7 @@
 
 These are input generators, not compute: the matrices and fields they build are what
 bench.py and the tests hand to the CUDA library.  The oracle has its own C generators
-(oracle/hpcx_oracle.c); tests/test_synth.py checks the two agree bit-for-bit.
+(oracle/hpcx_oracle.c); tests/test_host_logic.py checks the two agree bit-for-bit.
 
 RNG: counter-based, u(seed, i) = (mix(mix(seed) ^ i) >> 11) * 2^-53 with
 mix = the splitmix64 finaliser, so any element can be generated independently.
@@ -155,3 +155,50 @@ def rmat(scale: int, edge_factor: int = 16, seed: int = 24, index_dtype=np.int32
     rp = np.zeros(n + 1, dtype=np.int64)
     np.cumsum(np.bincount(rows, minlength=n), out=rp[1:])
     return rp.astype(index_dtype), col, val
+
+
+def laplace2d_slab_local(ny_total: int, nx: int, y0: int, y1: int, dtype=np.float64):
+    """Rank-local view of grid rows [y0, y1) of the ny_total x nx 5-point Laplacian, built
+    without ever forming the global matrix.  Returns exactly the tables hpcx_csr_localize
+    produces for a contiguous row partition whose block is [y0*nx, y1*nx)
+    (tests/test_host_logic.py checks the two agree): columns renumbered [owned | halo], halo
+    = grid row y0-1 (from the rank below) then grid row y1 (from the rank above)."""
+    ny = y1 - y0
+    nloc = ny * nx
+    has_lo, has_hi = y0 > 0, y1 < ny_total
+    # Build the slab as the interior rows of a (ny + has_lo + has_hi)-row grid, then cut.
+    pad_lo, pad_hi = int(has_lo), int(has_hi)
+    rp_e, col_e, val_e = laplace2d_big(ny + pad_lo + pad_hi, nx, dtype, np.int64)
+    a, b = rp_e[pad_lo * nx], rp_e[(pad_lo + ny) * nx]
+    local_row_ptr = rp_e[pad_lo * nx:(pad_lo + ny) * nx + 1] - a
+    c = col_e[a:b].astype(np.int64) - pad_lo * nx  # owned -> [0, nloc); below -> [-nx, 0); above -> [nloc, nloc+nx)
+    del rp_e, col_e
+    local_col = np.where(c < 0, c + nx + nloc, np.where(c >= nloc, c + pad_lo * nx, c)).astype(np.int32)
+    values = val_e[a:b]
+    nhalo = (pad_lo + pad_hi) * nx
+    P_lo = np.arange(nx, dtype=np.int32)
+    send_idx = np.concatenate(([P_lo] if has_lo else []) + ([nloc - nx + P_lo] if has_hi else []) +
+                              [np.empty(0, np.int32)]).astype(np.int32)
+    row_kind = np.zeros(nloc, dtype=np.uint8)
+    if has_lo:
+        row_kind[:nx] = 1
+    if has_hi:
+        row_kind[nloc - nx:] = 1
+    halo_gcol = np.concatenate(([(y0 - 1) * nx + np.arange(nx, dtype=np.int64)] if has_lo else []) +
+                               ([y1 * nx + np.arange(nx, dtype=np.int64)] if has_hi else []) +
+                               [np.empty(0, np.int64)])
+    return dict(nloc=nloc, nnz_loc=int(b - a), nhalo=nhalo, nsend=len(send_idx),
+                local_row_ptr=local_row_ptr, local_col=local_col, values=values,
+                halo_gcol=halo_gcol, send_idx=send_idx, row_kind=row_kind, has_lo=has_lo,
+                has_hi=has_hi)
+
+
+def slab_counts(local: dict, nparts: int, rank: int, nx: int):
+    """recv_counts / send_counts of a slab partition (neighbours rank-1 and rank+1)."""
+    recv = np.zeros(nparts, dtype=np.int64)
+    send = np.zeros(nparts, dtype=np.int64)
+    if local["has_lo"]:
+        recv[rank - 1] = send[rank - 1] = nx
+    if local["has_hi"]:
+        recv[rank + 1] = send[rank + 1] = nx
+    return recv, send

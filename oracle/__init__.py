@@ -156,8 +156,8 @@ def rmat(scale: int, edge_factor: int = 16, seed: int = 24):
     return rp, col[:m].copy(), val[:m].copy()
 
 
-def spmv(rp, col, val, x):
-    y = np.empty(len(rp) - 1, dtype=val.dtype)
+def spmv(rp, col, val, x, out=None):
+    y = np.empty(len(rp) - 1, dtype=val.dtype) if out is None else out
     rp = np.ascontiguousarray(rp)
     if rp.dtype == np.int32:
         fn = lib().orc_spmv_i32_f64 if val.dtype == np.float64 else lib().orc_spmv_i32_f32

