@@ -105,9 +105,11 @@ template <int S>
 struct JacobiCfg {
   static constexpr int TX = 128, TY = 16, HX = 4;      // HX: x halo staged on each side
   static constexpr int BX = TX + 2 * HX, BY = TY + 2;  // box extents
-  static constexpr int kPlaneFloats = BX * BY;
-  static constexpr int kPlaneBytes = kPlaneFloats * 4;  // 9792, multiple of 128
-  static constexpr int kBarOff = S * kPlaneBytes;
+  static constexpr int kPlaneBytes = BX * BY * 4;  // 9792 bytes arrive per box
+  // TMA writes need a 128-byte aligned shared-memory destination: pad the slot stride.
+  static constexpr int kSlotBytes = (kPlaneBytes + 127) / 128 * 128;  // 9856
+  static constexpr int kSlotFloats = kSlotBytes / 4;                 // slot stride in floats
+  static constexpr int kBarOff = S * kSlotBytes;
   static constexpr int kSmemBytes = kBarOff + 2 * S * 8;
   static constexpr int kConsumerWarps = 8;
   static constexpr int kThreads = (kConsumerWarps + 1) * 32;
@@ -149,7 +151,7 @@ jacobi7_tma_kernel(const __grid_constant__ CUtensorMap in_map, float *__restrict
         const int slot = j % S, use = j / S;
         if (use > 0) mbar_wait(empty + slot, (use - 1) & 1);
         mbar_expect_tx(full + slot, C::kPlaneBytes);
-        tma_load_3d(ring + slot * C::kPlaneFloats, &in_map, c0, c1, c2 + j, full + slot);
+        tma_load_3d(ring + slot * C::kSlotFloats, &in_map, c0, c1, c2 + j, full + slot);
       }
     }
     return;
@@ -159,7 +161,7 @@ jacobi7_tma_kernel(const __grid_constant__ CUtensorMap in_map, float *__restrict
   // Warp w owns tile rows 2w and 2w+1 (box rows 2w+1, 2w+2); lane owns x0 + 4*lane .. +3.
   const int br = 2 * warp + 1;
   const int col = C::HX + 4 * lane;
-  auto plane_ptr = [&](int j) { return ring + (j % S) * C::kPlaneFloats; };
+  auto plane_ptr = [&](int j) { return ring + (j % S) * C::kSlotFloats; };
   auto wait_full = [&](int j) { mbar_wait(full + (j % S), (j / S) & 1); };
   auto release = [&](int j) {
     __syncwarp();
