@@ -253,6 +253,7 @@ def run_ours(args, rank: int, world: int, local: int):
 
     # ---- property check of the timed operator (no oracle here): A*1 = missing-neighbour count
     ones = torch.ones(nloc + L["nhalo"], dtype=torch.float64, device="cuda")
+    torch.cuda.synchronize()  # `ones` was filled on torch's default stream, the product runs on `stream`
     if world == 1:
         D.spmv(ones, yd, stream)
     else:

@@ -131,7 +131,11 @@ hpcx_status hpcx_device_free(hpcx_ctx ctx, void *p) {
 }
 hpcx_status hpcx_memcpy(hpcx_ctx ctx, void *dst, const void *src, size_t bytes) {
   if (!ctx) return HPCX_INVALID_ARG;
+  // Synchronous on both sides: device-to-device cudaMemcpy returns before the copy has run and
+  // is not ordered with non-blocking streams, so drain the device before and after.
+  HPCX_CUDA(ctx, cudaDeviceSynchronize());
   HPCX_CUDA(ctx, cudaMemcpy(dst, src, bytes, cudaMemcpyDefault));
+  HPCX_CUDA(ctx, cudaDeviceSynchronize());
   return HPCX_OK;
 }
 
