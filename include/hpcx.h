@@ -83,8 +83,8 @@ HPCX_API hpcx_status hpcx_memcpy(hpcx_ctx ctx, void *dst, const void *src, size_
  * dimension.  The HOST layout is exactly the reference's flat buffer:
  * stride[i] = prod_{j>i}(dim[j]+lo+hi), offset = sum stride[i]*(idx[i]+lo).
  * The DEVICE layout keeps the same logical indexing but pads the fastest dimension so
- * that interior x = 0 starts on a 128-byte boundary and the pitch is a multiple of
- * 128 bytes (TMA needs 16-byte strides; vector stores need aligned rows). */
+ * that interior x = 0 starts on a 32-byte boundary and the pitch is a multiple of
+ * 32 bytes (TMA needs 16-byte strides; vector stores need sector-aligned rows). */
 typedef struct {
   int32_t ndim;    /* 1..3 */
   int32_t dtype;   /* HPCX_F32 | HPCX_F64 */

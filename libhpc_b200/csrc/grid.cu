@@ -66,10 +66,13 @@ hpcx_status hpcx_grid_create(hpcx_ctx ctx, const hpcx_grid_desc *d, hpcx_grid *o
     delete g;
     return fail(ctx, HPCX_INVALID_ARG, "zero-sized flat array");
   }
-  const int64_t per128 = 128 / g->es;
-  g->xoff = round_up(g->glo[2], per128);
-  const int64_t tail = g->ghi[2] > 4 ? g->ghi[2] : 4;
-  g->pitch = round_up(g->xoff + g->n[2] + tail, per128);
+  // Dense rows: interior x = 0 starts on a 32-byte sector boundary and the pitch is a multiple
+  // of 32 bytes (TMA needs 16-byte strides; float4 / double2 stores stay sector aligned).
+  // Padding rows out to 128-byte lines cost 13 % extra DRAM reads on 512^3 (ncu, profiles/r01):
+  // every touched line is fetched whole, including the pad.
+  const int64_t per32 = 32 / g->es;
+  g->xoff = round_up(g->glo[2], per32);
+  g->pitch = round_up(g->xoff + g->n[2] + g->ghi[2], per32);
   g->rows = g->ext[0] * g->ext[1];
   g->total = g->rows * g->pitch;
   cudaError_t e = cudaMalloc(&g->dev, (size_t)g->total * g->es);

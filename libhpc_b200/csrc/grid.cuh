@@ -17,6 +17,13 @@ struct hpcx_grid_s {
   int64_t rows = 0;            // ext[0] * ext[1]
   int64_t total = 0;           // rows * pitch
   void *dev = nullptr;
+  // tensor maps of the TMA sweeps, keyed by (buffer, box height); see stencil.cu
+  struct MapEntry {
+    void *base = nullptr;
+    int boxh = 0;
+    CUtensorMap map;
+  };
+  std::vector<MapEntry> maps;
 };
 
 namespace hpcx {

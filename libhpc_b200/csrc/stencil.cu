@@ -19,6 +19,7 @@
 #include "grid.cuh"
 
 #include <algorithm>
+#include <type_traits>
 
 using namespace hpcx;
 
@@ -58,6 +59,75 @@ box_direct_kernel(const T *__restrict__ in, T *__restrict__ out, GridGeom gi, Gr
   T s = T(0);
   for (int k = -radius; k <= radius; ++k, p += step) s = add_rn(s, __ldg(p));
   out[gidx(go, 0, y, x)] = s;
+}
+
+// Register-tiled box sweeps (the 17-point reference sweeps at full HBM rate).  Every output is
+// still res = 0; res += a(.. + k) for k = -R..R in that order (bit-exact with the reference
+// loops); what changes is how the taps reach the registers.
+//
+// BOX_X: one thread per 16-byte vector of outputs.  It loads the 2R/V + 1 aligned vectors that
+// cover x-R .. x+V-1+R (neighbouring threads share them through L1) and forms V ordered sums.
+template <typename T, int R>
+__global__ void __launch_bounds__(256)
+box_x_vec_kernel(const T *__restrict__ in, T *__restrict__ out, GridGeom gi, GridGeom go) {
+  constexpr int V = 16 / (int)sizeof(T);
+  static_assert(R % V == 0, "radius must be a multiple of the vector width");
+  constexpr int NV = 2 * R / V + 1;
+  using Vec = typename std::conditional<sizeof(T) == 4, float4, double2>::type;
+  const int64_t x = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) * V;
+  const int64_t y = blockIdx.y;
+  if (x >= gi.n2) return;
+  const Vec *p = reinterpret_cast<const Vec *>(in + gidx(gi, 0, y, x) - R);
+  T w[NV * V];
+#pragma unroll
+  for (int k = 0; k < NV; ++k) {
+    const Vec v = __ldg(p + k);
+    if constexpr (V == 4) {
+      w[4 * k] = v.x; w[4 * k + 1] = v.y; w[4 * k + 2] = v.z; w[4 * k + 3] = v.w;
+    } else {
+      w[2 * k] = v.x; w[2 * k + 1] = v.y;
+    }
+  }
+  T o[V];
+#pragma unroll
+  for (int j = 0; j < V; ++j) {
+    T s = T(0);
+#pragma unroll
+    for (int k = 0; k <= 2 * R; ++k) s = add_rn(s, w[j + k]);
+    o[j] = s;
+  }
+  Vec r;
+  if constexpr (V == 4) {
+    r.x = o[0]; r.y = o[1]; r.z = o[2]; r.w = o[3];
+  } else {
+    r.x = o[0]; r.y = o[1];
+  }
+  *reinterpret_cast<Vec *>(out + gidx(go, 0, y, x)) = r;
+}
+
+// BOX_Y: one thread per column and ROWS consecutive outputs.  The ROWS + 2R taps are
+// independent coalesced loads (all in flight at once), each reused by up to 2R + 1 outputs from
+// registers; the 2R halo rows shared with the neighbouring row blocks are L2 hits.
+template <typename T, int R, int ROWS>
+__global__ void __launch_bounds__(128)
+box_y_reg_kernel(const T *__restrict__ in, T *__restrict__ out, GridGeom gi, GridGeom go) {
+  const int64_t x = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  const int64_t y0 = blockIdx.y * (int64_t)ROWS;
+  if (x >= gi.n2) return;
+  const T *p = in + gidx(gi, 0, y0 - R, x);
+  const int64_t rows = min((int64_t)ROWS, gi.n1 - y0);  // outputs of this block
+  T w[ROWS + 2 * R];
+#pragma unroll
+  for (int k = 0; k < ROWS + 2 * R; ++k)
+    w[k] = k < rows + 2 * R ? __ldg(p + k * gi.pitch) : T(0);
+  T *q = out + gidx(go, 0, y0, x);
+#pragma unroll
+  for (int j = 0; j < ROWS; ++j) {
+    T s = T(0);
+#pragma unroll
+    for (int k = 0; k <= 2 * R; ++k) s = add_rn(s, w[j + k]);
+    if (j < rows) q[j * go.pitch] = s;
+  }
 }
 
 // One thread per (x, y) column, marching along z over [z0, z1).
@@ -115,10 +185,21 @@ struct JacobiCfg {
   static constexpr int kThreads = (kConsumerWarps + 1) * 32;
 };
 
+// Work split (host planner jacobi_plan): the (x, y, z) space is cut into ntx * nty * zs CTAs of
+// equal size — x tiles of TX, y tiles by even division of the rows (tile heights h and h-1 only,
+// one tensor map per height), z segments by even division of the planes — with the CTA count a
+// multiple of the SM count, so every SM streams the same number of cells.  All CTAs of a z
+// segment march through the planes in step, which is what lets L2 serve the tile halos.
+struct JacobiSplit {
+  int ntx, nty, zs;   // tiles along x, y; z segments
+  int hmax;           // height of the taller y tiles (<= TY)
+};
+
 template <int S>
 __global__ void __launch_bounds__(JacobiCfg<S>::kThreads)
-jacobi7_tma_kernel(const __grid_constant__ CUtensorMap in_map, float *__restrict__ out, GridGeom g,
-                   int zbeg, int zend, int zlen, float sixth) {
+jacobi7_tma_kernel(const __grid_constant__ CUtensorMap map_hi, const __grid_constant__ CUtensorMap map_lo,
+                   float *__restrict__ out, GridGeom g, JacobiSplit sp, int zbeg, int zend,
+                   float sixth) {
   using C = JacobiCfg<S>;
   extern __shared__ __align__(128) unsigned char smem[];
   float *ring = reinterpret_cast<float *>(smem);
@@ -126,10 +207,17 @@ jacobi7_tma_kernel(const __grid_constant__ CUtensorMap in_map, float *__restrict
   uint64_t *empty = full + S;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int x0 = blockIdx.x * C::TX, y0 = blockIdx.y * C::TY;
-  const int z0 = zbeg + blockIdx.z * zlen;
-  const int z1 = min(z0 + zlen, zend);
+  const int bx = blockIdx.x % sp.ntx;
+  const int by = (blockIdx.x / sp.ntx) % sp.nty;
+  const int bz = blockIdx.x / (sp.ntx * sp.nty);
+  const int x0 = bx * C::TX;
+  const int y0 = (int)((int64_t)by * g.n1 / sp.nty);
+  const int h = (int)((int64_t)(by + 1) * g.n1 / sp.nty) - y0;  // rows of this tile
+  const int nzr = zend - zbeg;
+  const int z0 = zbeg + (int)((int64_t)bz * nzr / sp.zs);
+  const int z1 = zbeg + (int)((int64_t)(bz + 1) * nzr / sp.zs);
   const int np = z1 - z0 + 2;  // planes z0-1 .. z1
+  if (h <= 0 || z1 <= z0) return;
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < S; ++s) {
@@ -143,15 +231,17 @@ jacobi7_tma_kernel(const __grid_constant__ CUtensorMap in_map, float *__restrict
   if (warp == C::kConsumerWarps) {
     // ---------------------------------------------------------------- producer
     if (lane == 0) {
-      tma_prefetch_desc(&in_map);
+      const CUtensorMap *map = h == sp.hmax ? &map_hi : &map_lo;
+      tma_prefetch_desc(map);
+      const uint32_t bytes = (uint32_t)(C::BX * (h + 2) * 4);
       const int c0 = (int)g.xoff + x0 - C::HX;
       const int c1 = y0 + (int)g.glo1 - 1;
       const int c2 = z0 - 1 + (int)g.glo0;
       for (int j = 0; j < np; ++j) {
         const int slot = j % S, use = j / S;
         if (use > 0) mbar_wait(empty + slot, (use - 1) & 1);
-        mbar_expect_tx(full + slot, C::kPlaneBytes);
-        tma_load_3d(ring + slot * C::kSlotFloats, &in_map, c0, c1, c2 + j, full + slot);
+        mbar_expect_tx(full + slot, bytes);
+        tma_load_3d(ring + slot * C::kSlotFloats, map, c0, c1, c2 + j, full + slot);
       }
     }
     return;
@@ -188,6 +278,7 @@ jacobi7_tma_kernel(const __grid_constant__ CUtensorMap in_map, float *__restrict
 
   const int gx = x0 + 4 * lane;
   const int gy = y0 + 2 * warp;
+  const bool row0 = 2 * warp < h, row1 = 2 * warp + 1 < h;
   const bool full4 = gx + 3 < g.n2;
   const int64_t plane_stride = g.ext1 * g.pitch;
   float *orow = out + gidx(g, z0, gy, gx);
@@ -228,15 +319,15 @@ jacobi7_tma_kernel(const __grid_constant__ CUtensorMap in_map, float *__restrict
 #undef HPCX_J7
 
     if (full4) {
-      if (gy < g.n1) st_cs(reinterpret_cast<float4 *>(orow), o0);
-      if (gy + 1 < g.n1) st_cs(reinterpret_cast<float4 *>(orow + g.pitch), o1);
+      if (row0) st_cs(reinterpret_cast<float4 *>(orow), o0);
+      if (row1) st_cs(reinterpret_cast<float4 *>(orow + g.pitch), o1);
     } else {
       const float a0[4] = {o0.x, o0.y, o0.z, o0.w}, a1[4] = {o1.x, o1.y, o1.z, o1.w};
 #pragma unroll
       for (int k = 0; k < 4; ++k)
         if (gx + k < g.n2) {
-          if (gy < g.n1) orow[k] = a0[k];
-          if (gy + 1 < g.n1) orow[g.pitch + k] = a1[k];
+          if (row0) orow[k] = a0[k];
+          if (row1) orow[g.pitch + k] = a1[k];
         }
     }
     zm0 = zc0;
@@ -266,6 +357,41 @@ hpcx_status launch_box_direct(hpcx_grid in, hpcx_grid out, int axis, int radius,
   return after_launch(in->ctx, "box_direct_kernel");
 }
 
+// Register-tiled variants exist for the radii a 16-byte vector divides (the reference's
+// nblur = 8 among them); everything else takes the direct kernel.
+template <typename T, int R>
+hpcx_status launch_box_fast_r(hpcx_grid in, hpcx_grid out, int axis, cudaStream_t s) {
+  constexpr int V = 16 / (int)sizeof(T);
+  if (axis == 2) {
+    dim3 grid((unsigned)((in->n[2] / V + 255) / 256), (unsigned)in->n[1]);
+    box_x_vec_kernel<T, R><<<grid, 256, 0, s>>>((const T *)in->dev, (T *)out->dev, geom_of(in),
+                                                 geom_of(out));
+    return after_launch(in->ctx, "box_x_vec_kernel");
+  }
+  constexpr int ROWS = 32;
+  dim3 grid((unsigned)((in->n[2] + 127) / 128), (unsigned)((in->n[1] + ROWS - 1) / ROWS));
+  box_y_reg_kernel<T, R, ROWS><<<grid, 128, 0, s>>>((const T *)in->dev, (T *)out->dev, geom_of(in),
+                                                     geom_of(out));
+  return after_launch(in->ctx, "box_y_reg_kernel");
+}
+
+template <typename T>
+hpcx_status launch_box(hpcx_grid in, hpcx_grid out, int axis, int radius, int variant,
+                       cudaStream_t s) {
+  constexpr int V = 16 / (int)sizeof(T);
+  const bool fast_ok = variant != HPCX_VARIANT_DIRECT && in->n[1] <= 65535 * 32 &&
+                       (axis != 2 || (in->n[2] % V == 0 && in->n[1] <= 65535));
+  if (fast_ok) {
+    switch (radius) {
+      case 8: return launch_box_fast_r<T, 8>(in, out, axis, s);
+      case 4: return launch_box_fast_r<T, 4>(in, out, axis, s);
+      default: break;
+    }
+  }
+  if (in->n[1] > 65535 * 4) return fail(in->ctx, HPCX_UNSUPPORTED, "grid too tall for the box sweep");
+  return launch_box_direct<T>(in, out, axis, radius, s);
+}
+
 int auto_zsplit(hpcx_ctx ctx, int64_t tiles_xy, int64_t nz, int ctas_per_sm) {
   // Fill the resident CTA slots of the chip once; keep z segments at least 16 planes long.
   const int64_t slots = (int64_t)ctx->sm_count * ctas_per_sm;
@@ -291,16 +417,67 @@ hpcx_status launch_jacobi_direct(hpcx_grid_s *g, const void *src, void *dst, int
 
 constexpr int kJacobiStages = 6;
 
+// Equal-work split: minimise (CTAs per SM, rounded up, at least 3) x (cells one CTA loads).  `zsplit` > 0
+// pins the number of z segments (tests exercise short segments that way).
+JacobiSplit jacobi_plan(hpcx_ctx ctx, int64_t nx, int64_t ny, int64_t nz, int zsplit) {
+  using C = JacobiCfg<kJacobiStages>;
+  const int64_t ntx = (nx + C::TX - 1) / C::TX;
+  const int64_t nty_min = (ny + C::TY - 1) / C::TY;
+  JacobiSplit best{(int)ntx, (int)nty_min, 1, (int)((ny + nty_min - 1) / nty_min)};
+  double best_cost = 1e300;
+  const int64_t nty_max = std::min<int64_t>(ny, std::max<int64_t>(nty_min * 2, nty_min + 8));
+  const int64_t zs_lo = zsplit > 0 ? std::min<int64_t>(zsplit, nz) : 1;
+  const int64_t zs_hi = zsplit > 0 ? zs_lo : std::max<int64_t>(1, nz / 8);
+  for (int64_t nty = nty_min; nty <= nty_max; ++nty) {
+    const int64_t h = (ny + nty - 1) / nty;
+    for (int64_t zs = zs_lo; zs <= zs_hi; ++zs) {
+      const int64_t zl = (nz + zs - 1) / zs;
+      const int64_t ncta = ntx * nty * zs;
+      const int64_t per_sm = (ncta + ctx->sm_count - 1) / ctx->sm_count;
+      // + 3 planes: ring fill before the first output plane of a segment
+      // An SM reaches its streaming rate only with all 3 resident CTA slots busy (59 KB of
+      // ring each), so fewer than 3 CTAs per SM cost as much as 3.
+      const double cost = (double)std::max<int64_t>(per_sm, 3) * (double)(h + 2) * (double)(zl + 2 + 3);
+      if (cost < best_cost * (1.0 - 1e-9)) {
+        best_cost = cost;
+        best = JacobiSplit{(int)ntx, (int)nty, (int)zs, (int)h};
+      }
+    }
+  }
+  return best;
+}
+
+// Tensor maps are cached on the grid handle, keyed by (buffer, box height).
+const CUtensorMap *jacobi_map(hpcx_grid_s *g, void *src, int boxh, hpcx_status *st) {
+  using C = JacobiCfg<kJacobiStages>;
+  for (auto &e : g->maps)
+    if (e.base == src && e.boxh == boxh) return &e.map;
+  if (g->maps.size() >= 8) g->maps.clear();
+  g->maps.reserve(8);  // entries never move while the cache holds fewer than 8
+  hpcx_grid_s::MapEntry e;
+  e.base = src;
+  e.boxh = boxh;
+  const uint64_t dims[3] = {(uint64_t)g->pitch, (uint64_t)g->ext[1], (uint64_t)g->ext[0]};
+  const uint64_t strides[2] = {(uint64_t)g->pitch * 4, (uint64_t)g->pitch * g->ext[1] * 4};
+  const uint32_t box[3] = {C::BX, (uint32_t)boxh, 1};
+  *st = make_tensor_map(g->ctx, &e.map, HPCX_F32, 3, src, dims, strides, box);
+  if (*st != HPCX_OK) return nullptr;
+  g->maps.push_back(e);
+  return &g->maps.back().map;
+}
+
 hpcx_status launch_jacobi_tma(hpcx_grid_s *g, void *src, void *dst, int zsplit, int64_t zbeg,
                               int64_t zend, cudaStream_t s) {
   using C = JacobiCfg<kJacobiStages>;
   hpcx_ctx ctx = g->ctx;
-  CUtensorMap map;
-  const uint64_t dims[3] = {(uint64_t)g->pitch, (uint64_t)g->ext[1], (uint64_t)g->ext[0]};
-  const uint64_t strides[2] = {(uint64_t)g->pitch * 4, (uint64_t)g->pitch * g->ext[1] * 4};
-  const uint32_t box[3] = {C::BX, C::BY, 1};
-  hpcx_status st = make_tensor_map(ctx, &map, HPCX_F32, 3, src, dims, strides, box);
-  if (st != HPCX_OK) return st;
+  const JacobiSplit sp = jacobi_plan(ctx, g->n[2], g->n[1], zend - zbeg, zsplit);
+  hpcx_status st = HPCX_OK;
+  const CUtensorMap *hi = jacobi_map(g, src, sp.hmax + 2, &st);
+  if (!hi) return st;
+  const CUtensorMap *lo = sp.hmax > 1 ? jacobi_map(g, src, sp.hmax + 1, &st) : hi;
+  if (!lo) return st;
+  // `hi` may have moved if the cache reallocated: fetch it again (cheap, by key).
+  hi = jacobi_map(g, src, sp.hmax + 2, &st);
   static bool configured = false;
   if (!configured) {
     HPCX_CUDA(ctx, cudaFuncSetAttribute(jacobi7_tma_kernel<kJacobiStages>,
@@ -308,13 +485,9 @@ hpcx_status launch_jacobi_tma(hpcx_grid_s *g, void *src, void *dst, int zsplit, 
                                         C::kSmemBytes));
     configured = true;
   }
-  const int64_t tx = (g->n[2] + C::TX - 1) / C::TX, ty = (g->n[1] + C::TY - 1) / C::TY;
-  const int64_t nz = zend - zbeg;
-  if (zsplit <= 0) zsplit = auto_zsplit(ctx, tx * ty, nz, 3);
-  const int64_t zlen = (nz + zsplit - 1) / zsplit;
-  dim3 grid((unsigned)tx, (unsigned)ty, (unsigned)((nz + zlen - 1) / zlen));
-  jacobi7_tma_kernel<kJacobiStages><<<grid, C::kThreads, C::kSmemBytes, s>>>(
-      map, (float *)dst, geom_of(g), (int)zbeg, (int)zend, (int)zlen, 1.0f / 6.0f);
+  const unsigned ncta = (unsigned)(sp.ntx * sp.nty * sp.zs);
+  jacobi7_tma_kernel<kJacobiStages><<<ncta, C::kThreads, C::kSmemBytes, s>>>(
+      *hi, *lo, (float *)dst, geom_of(g), sp, (int)zbeg, (int)zend, 1.0f / 6.0f);
   return after_launch(ctx, "jacobi7_tma_kernel");
 }
 
@@ -353,8 +526,8 @@ extern "C" hpcx_status hpcx_stencil_sweep(hpcx_grid in, hpcx_grid out, const hpc
     HPCX_REQUIRE(ctx, st->radius >= 0 && st->radius <= in->desc.lo && st->radius <= in->desc.hi,
                  "radius exceeds the ghost width of the input grid");
     const int axis = st->kind == HPCX_STENCIL_BOX_X ? 2 : 1;
-    rc = in->desc.dtype == HPCX_F64 ? launch_box_direct<double>(in, out, axis, st->radius, s)
-                                    : launch_box_direct<float>(in, out, axis, st->radius, s);
+    rc = in->desc.dtype == HPCX_F64 ? launch_box<double>(in, out, axis, st->radius, st->variant, s)
+                                    : launch_box<float>(in, out, axis, st->radius, st->variant, s);
   } else if (st->kind == HPCX_STENCIL_JACOBI7) {
     if (in->desc.ndim != 3) return fail(ctx, HPCX_UNSUPPORTED, "JACOBI7 takes 3-D grids");
     HPCX_REQUIRE(ctx, in->desc.lo >= 1 && in->desc.hi >= 1 && in->desc.lo == out->desc.lo &&

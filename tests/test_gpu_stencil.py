@@ -19,10 +19,10 @@ KIND = {"x_scalar": hp.STENCIL_BOX_X, "x_sse": hp.STENCIL_BOX_X, "y_scalar": hp.
         "y_sse_ipl": hp.STENCIL_BOX_Y}
 
 
-def _box(ctx, a_flat, ny, nx, kind, radius=8, alo=8, blo=0, dtype=np.float32):
+def _box(ctx, a_flat, ny, nx, kind, radius=8, alo=8, blo=0, dtype=np.float32, variant=hp.VARIANT_AUTO):
     a = hp.HPCHighDimensionFlatArray(ny, nx, dtype=dtype, lo=alo, buffer=a_flat)
     b = hp.HPCHighDimensionFlatArray(ny, nx, dtype=dtype, lo=blo)
-    hp.stencil_sweep_host(ctx, a, b, kind, radius)
+    hp.stencil_sweep_host(ctx, a, b, kind, radius, 1, variant)
     return b.data()
 
 
@@ -43,13 +43,18 @@ def test_box_sweeps_match_reference_digest(ctx, which):
 
 @pytest.mark.parametrize("dtype", [np.float32, np.float64])
 @pytest.mark.parametrize("shape,radius,alo,blo", [((1, 1), 0, 0, 0), ((5, 7), 2, 2, 0), ((33, 129), 8, 8, 3),
-                                                  ((64, 250), 3, 5, 1), ((257, 31), 8, 9, 0)])
+                                                  ((64, 250), 3, 5, 1), ((257, 31), 8, 9, 0),
+                                                  ((40, 256), 8, 8, 0), ((100, 64), 4, 4, 2),
+                                                  ((31, 36), 8, 9, 1), ((67, 1028), 8, 8, 0),
+                                                  ((32, 12), 4, 6, 0)])
 def test_box_sweeps_ragged_shapes(ctx, dtype, shape, radius, alo, blo):
     ny, nx = shape
     a = oracle.fill((ny + 2 * alo) * (nx + 2 * alo), 13, dtype)
     for kind, axis in ((hp.STENCIL_BOX_X, 1), (hp.STENCIL_BOX_Y, 0)):
         want = oracle.box_sweep(a, ny, nx, alo, alo, blo, blo, axis, radius)
+        # AUTO takes the register-tiled kernels where they apply, DIRECT the one-thread-per-cell one
         assert bits_equal(_box(ctx, a, ny, nx, kind, radius, alo, blo, dtype), want)
+        assert bits_equal(_box(ctx, a, ny, nx, kind, radius, alo, blo, dtype, hp.VARIANT_DIRECT), want)
 
 
 def test_r0_full_size_8192_matches_oracle(ctx):
@@ -75,7 +80,8 @@ def _jacobi(ctx, f, dims, lo, hi, steps, variant, zsplit=0):
 
 @pytest.mark.parametrize("variant", [hp.VARIANT_TMA, hp.VARIANT_DIRECT, hp.VARIANT_AUTO])
 @pytest.mark.parametrize("dims,lo,hi", [((1, 1, 1), 1, 1), ((3, 5, 7), 1, 1), ((16, 16, 128), 1, 1),
-                                        ((17, 33, 129), 1, 1), ((40, 50, 300), 2, 3), ((64, 64, 64), 1, 1)])
+                                        ((17, 33, 129), 1, 1), ((40, 50, 300), 2, 3), ((64, 64, 64), 1, 1),
+                                        ((24, 100, 256), 1, 1), ((5, 37, 64), 1, 2)])
 @pytest.mark.parametrize("steps", [1, 2, 8])
 def test_jacobi7_fp32_bit_exact(ctx, variant, dims, lo, hi, steps):
     nz, ny, nx = dims
