@@ -350,11 +350,14 @@ def stencil_extra(ctx, torch, stream, world, rank, barrier, max_over_ranks, hp, 
     ga.upload(f)
     gb.upload(f)
     del f
-    plan = hd.HaloPlan(ctx, ga, gb, hp.STENCIL_JACOBI7) if world > 1 else None
-    for variant, name in ((hp.VARIANT_TMA, "tma"), (hp.VARIANT_DIRECT, "direct")):
-        if world > 1 and name == "direct":
+    # N > 1: transport 1 = fused peer stores (one kernel per sweep), transport 0 = NCCL send/recv
+    plans = {"tma": hd.HaloPlan(ctx, ga, gb, hp.STENCIL_JACOBI7, hp.VARIANT_TMA, transport=1),
+             "tma_nccl": hd.HaloPlan(ctx, ga, gb, hp.STENCIL_JACOBI7, hp.VARIANT_TMA, transport=0)} if world > 1 else {}
+    for variant, name in ((hp.VARIANT_TMA, "tma"), (hp.VARIANT_TMA, "tma_nccl"), (hp.VARIANT_DIRECT, "direct")):
+        if (world > 1) != (name in plans):
             continue
         if world > 1:
+            plan = plans[name]
             step = lambda: plan.sweep(T, stream)  # noqa: E731
         else:
             step = lambda: hp.stencil_sweep(ga, gb, hp.STENCIL_JACOBI7, steps=T, variant=variant,  # noqa: E731
@@ -369,10 +372,11 @@ def stencil_extra(ctx, torch, stream, world, rank, barrier, max_over_ranks, hp, 
         out[f"jacobi7_512cubed_fp32_{name}"] = {
             "metric": "stencil_Gcell_updates_per_s", "value": cells / dt / 1e9, "sweeps": 2 * T,
             "ms_per_sweep": dt / (2 * T) * 1e3, "gpu_launches": launches,
+            "transport": {"tma": "peer stores + flags (fused)", "tma_nccl": "NCCL send/recv"}.get(name) if world > 1 else None,
             "roofline": {"bound": "hbm", "achieved": cells * 8 / world / dt / 1e9, "peak": peak,
                          "unit": "GB/s", "frac": cells * 8 / world / dt / 1e9 / peak,
                          "algorithmic_bytes_per_cell": 8}}
-    if plan:
+    for plan in plans.values():
         plan.destroy()
     ga.destroy()
     gb.destroy()

@@ -128,7 +128,8 @@ typedef struct {
   int32_t kind;
   int32_t radius;   /* BOX_*: r (the reference uses nblur = 8); JACOBI7: ignored */
   int32_t variant;  /* HPCX_VARIANT_* */
-  int32_t zsplit;   /* JACOBI7: number of z segments per (x,y) tile; 0 = auto */
+  int32_t zsplit;   /* JACOBI7: number of z segments per (x,y) tile; BOX_Y: output rows per
+                       thread (16 or 32); 0 = auto */
 } hpcx_stencil_desc;
 
 /* Reads the (ghost-padded) grid `in`, writes the interior of `out`.
@@ -259,9 +260,13 @@ HPCX_API hpcx_status hpcx_comm_ipc_close(hpcx_ctx ctx, void *peer_ptr);
 
 /* Distributed stencil: every rank owns a z-slab (axis 0) grid pair created with
  * hpcx_grid_create; neighbours are rank-1 / rank+1 (no periodic wrap: the outermost
- * ghost planes stay Dirichlet).  transport: 0 = NCCL send/recv on the comm stream
- * overlapped with the interior sweep (1 is reserved for fused peer stores, where the
- * boundary planes are written straight into the neighbour's ghost planes over NVLink). */
+ * ghost planes stay Dirichlet).  transport:
+ *   0  NCCL send/recv of the boundary planes on the comm stream, overlapped with the interior
+ *      sweep on the compute stream (three launches per sweep);
+ *   1  fused: one kernel per sweep whose boundary CTAs store their plane straight into the
+ *      neighbour's ghost plane over NVLink (CUDA IPC peer windows) and publish a sweep-number
+ *      flag that the neighbour's next sweep acquires before reading the ghost (fp32 TMA sweep
+ *      only; plan creation is collective over the communicator). */
 typedef struct hpcx_halo_plan_s *hpcx_halo_plan;
 HPCX_API hpcx_status hpcx_stencil_dist_plan(hpcx_ctx ctx, hpcx_grid in, hpcx_grid out,
                                             const hpcx_stencil_desc *st, int32_t transport,

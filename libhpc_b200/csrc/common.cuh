@@ -24,6 +24,7 @@ struct hpcx_ctx_s {
   cudaStream_t copy_in = nullptr, copy_out = nullptr;
   cudaEvent_t ev[8] = {};
   int64_t launches = 0;
+  bool force_jacobi_down = false;  // HPCX_JACOBI_DOWN=1 (test hook, see stencil.cu)
   bool debug_sync = false;  // HPCX_DEBUG_SYNC=1: sync + check after every launch
                             // (reference idiom, cuda_radix_sort_v4.cu:104-107)
   std::string last_error;
@@ -128,6 +129,30 @@ __device__ __forceinline__ void tma_load_3d(void *dst, const CUtensorMap *map, i
       "l"(reinterpret_cast<uint64_t>(map)), "r"(c0), "r"(c1), "r"(c2), "r"(smem_u32(bar))
       : "memory");
 }
+// ---- cross-GPU flags (system scope), used by the peer-store halo paths
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t *p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_sys(uint32_t *p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+// Spin until *flag >= want (wrap-safe).  Bounded: after about two seconds the error word is set
+// and the sweep goes on, so a lost neighbour surfaces as HPCX_NCCL_ERROR instead of a hang.
+__device__ __forceinline__ void wait_flag(const uint32_t *flag, uint32_t want, uint32_t *err) {
+  for (uint32_t it = 0; (int32_t)(ld_acquire_sys(flag) - want) < 0; ++it) {
+    if (it > (1u << 23)) {
+      atomicExch(err, 1u);
+      break;
+    }
+    __nanosleep(128);
+  }
+  // the ghost plane was written by the neighbour's generic stores; TMA reads it through the
+  // async proxy
+  asm volatile("fence.proxy.async;" ::: "memory");
+}
+
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap *map) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(map)) : "memory");
 }

@@ -73,6 +73,8 @@ hpcx_status hpcx_init(int32_t device, hpcx_ctx *out) {
   for (auto &ev : ctx->ev) HPCX_CUDA(ctx, cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
   const char *dbg = getenv("HPCX_DEBUG_SYNC");
   ctx->debug_sync = dbg && dbg[0] == '1';
+  const char *jd = getenv("HPCX_JACOBI_DOWN");
+  ctx->force_jacobi_down = jd && jd[0] == '1';
   cudaDriverEntryPointQueryResult qres;
   void *fn = nullptr;
   e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);

@@ -17,7 +17,7 @@ using namespace hpcx;
 
 namespace hpcx {
 hpcx_status jacobi7_launch(hpcx_grid_s *g, void *src, void *dst, int variant, int zsplit,
-                           int64_t zbeg, int64_t zend, cudaStream_t s);
+                           int64_t zbeg, int64_t zend, cudaStream_t s, const JacobiPeer *peer);
 hpcx_status spmv_launch_blocks(hpcx_csr A, const RowBlock *d_blocks, int64_t nblocks, const void *x,
                                void *y, cudaStream_t s);
 hpcx_status spmv_launch_fixup_tables(hpcx_csr A, const int32_t *long_row, const int32_t *long_off,
@@ -39,6 +39,7 @@ struct NcclApi {
   ncclResult_t (*GroupEnd)();
   ncclResult_t (*AllReduce)(const void *, void *, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t,
                             cudaStream_t);
+  ncclResult_t (*AllGather)(const void *, void *, size_t, ncclDataType_t, ncclComm_t, cudaStream_t);
   const char *(*GetErrorString)(ncclResult_t);
 };
 NcclApi g_nccl{};
@@ -59,6 +60,7 @@ hpcx_status load_nccl(hpcx_ctx ctx) {
   HPCX_SYM(GroupStart, "ncclGroupStart");
   HPCX_SYM(GroupEnd, "ncclGroupEnd");
   HPCX_SYM(AllReduce, "ncclAllReduce");
+  HPCX_SYM(AllGather, "ncclAllGather");
   HPCX_SYM(GetErrorString, "ncclGetErrorString");
 #undef HPCX_SYM
   ctx->nccl_lib = h;
@@ -85,6 +87,14 @@ struct hpcx_halo_plan_s {
   hpcx_stencil_desc st{};
   int transport = 0;
   cudaEvent_t ev_bnd = nullptr, ev_recv = nullptr, ev_start = nullptr;
+  // transport 1 (peer stores): neighbour side 0 = rank-1, 1 = rank+1
+  uint32_t *flags = nullptr;          // local block: [0],[1] flags, [4],[5] counters, [6] error word
+  void *buf[2] = {nullptr, nullptr};  // this rank's two grid buffers at plan time (A = in, B = out)
+  void *peer_open[2][3] = {};         // bases returned by cudaIpcOpenMemHandle (A, B, flags)
+  float *peer_buf[2][2] = {};         // the neighbour's A and B
+  uint32_t *peer_flags[2] = {nullptr, nullptr};
+  int64_t peer_n0[2] = {0, 0};
+  uint32_t epoch = 0;                 // sweeps completed through this plan
 };
 
 namespace {
@@ -110,6 +120,109 @@ hpcx_status exchange_planes(hpcx_grid g, void *buf, cudaStream_t s) {
   }
   HPCX_NCCL(ctx, g_nccl.GroupEnd());
   return HPCX_OK;
+}
+
+// ---- transport 1: peer windows over CUDA IPC ------------------------------------------
+// What every rank publishes about itself (gathered with ncclAllGather at plan time).
+struct PeerInfo {
+  cudaIpcMemHandle_t handle[3];  // allocations holding grid buffer A, grid buffer B, flag block
+  int64_t offset[3];             // byte offset of each inside its allocation
+  int64_t n0, n1, n2, pitch, ext1;
+};
+
+// cudaIpcGetMemHandle names the whole allocation a pointer lives in; carry the offset too.
+hpcx_status ipc_export(hpcx_ctx ctx, void *ptr, cudaIpcMemHandle_t *h, int64_t *offset) {
+  typedef CUresult (*range_fn)(CUdeviceptr *, size_t *, CUdeviceptr);
+  static range_fn get_range = nullptr;
+  if (!get_range) {
+    cudaDriverEntryPointQueryResult q;
+    void *fn = nullptr;
+    if (cudaGetDriverEntryPoint("cuMemGetAddressRange", &fn, cudaEnableDefault, &q) != cudaSuccess || !fn)
+      return fail(ctx, HPCX_CUDA_ERROR, "cuMemGetAddressRange entry point unavailable");
+    get_range = reinterpret_cast<range_fn>(fn);
+  }
+  CUdeviceptr base = 0;
+  size_t size = 0;
+  if (get_range(&base, &size, (CUdeviceptr)ptr) != CUDA_SUCCESS)
+    return fail(ctx, HPCX_CUDA_ERROR, "cuMemGetAddressRange failed");
+  *offset = (int64_t)((CUdeviceptr)ptr - base);
+  HPCX_CUDA(ctx, cudaIpcGetMemHandle(h, (void *)base));
+  return HPCX_OK;
+}
+
+hpcx_status allgather_bytes(hpcx_ctx ctx, const void *mine, void *all, size_t bytes) {
+  char *d = nullptr;
+  HPCX_CUDA(ctx, cudaMalloc((void **)&d, bytes * (size_t)(ctx->nranks + 1)));
+  HPCX_CUDA(ctx, cudaMemcpy(d, mine, bytes, cudaMemcpyHostToDevice));
+  ncclResult_t r = g_nccl.AllGather(d, d + bytes, bytes, ncclChar, comm_of(ctx), ctx->comm);
+  cudaError_t e = cudaStreamSynchronize(ctx->comm);
+  if (r == ncclSuccess && e == cudaSuccess)
+    e = cudaMemcpy(all, d + bytes, bytes * (size_t)ctx->nranks, cudaMemcpyDeviceToHost);
+  cudaFree(d);
+  if (r != ncclSuccess) return fail(ctx, HPCX_NCCL_ERROR, std::string("ncclAllGather: ") + g_nccl.GetErrorString(r));
+  if (e != cudaSuccess) return fail(ctx, HPCX_CUDA_ERROR, std::string("allgather: ") + cudaGetErrorString(e));
+  return HPCX_OK;
+}
+
+void close_peers(hpcx_halo_plan p) {
+  for (int side = 0; side < 2; ++side)
+    for (int k = 0; k < 3; ++k)
+      if (p->peer_open[side][k]) {
+        cudaIpcCloseMemHandle(p->peer_open[side][k]);
+        p->peer_open[side][k] = nullptr;
+      }
+  cudaFree(p->flags);
+  p->flags = nullptr;
+}
+
+// Opens the neighbours' grid buffers and flag blocks.  Collective over the communicator.
+hpcx_status open_peers(hpcx_halo_plan p) {
+  hpcx_ctx ctx = p->ctx;
+  hpcx_grid g = p->in;
+  p->buf[0] = p->in->dev;
+  p->buf[1] = p->out->dev;
+  // A flag block of its own allocation (2 MiB keeps cudaMalloc from sub-allocating it).
+  HPCX_CUDA(ctx, cudaMalloc((void **)&p->flags, 2u << 20));
+  HPCX_CUDA(ctx, cudaMemset(p->flags, 0, 256));
+  PeerInfo mine{};
+  void *ptrs[3] = {p->buf[0], p->buf[1], p->flags};
+  for (int k = 0; k < 3; ++k) {
+    hpcx_status st = ipc_export(ctx, ptrs[k], &mine.handle[k], &mine.offset[k]);
+    if (st != HPCX_OK) return st;
+  }
+  mine.n0 = g->n[0];
+  mine.n1 = g->n[1];
+  mine.n2 = g->n[2];
+  mine.pitch = g->pitch;
+  mine.ext1 = g->ext[1];
+  std::vector<PeerInfo> all(ctx->nranks);
+  hpcx_status st = allgather_bytes(ctx, &mine, all.data(), sizeof(PeerInfo));
+  if (st != HPCX_OK) return st;
+  for (int side = 0; side < 2; ++side) {
+    const int q = ctx->rank + (side ? 1 : -1);
+    if (q < 0 || q >= ctx->nranks) continue;
+    const PeerInfo &o = all[q];
+    if (o.n1 != mine.n1 || o.n2 != mine.n2 || o.pitch != mine.pitch || o.ext1 != mine.ext1)
+      return fail(ctx, HPCX_INVALID_ARG, "neighbouring slabs differ in their (y, x) extents");
+    void *base[3];
+    for (int k = 0; k < 3; ++k) {
+      HPCX_CUDA(ctx, cudaIpcOpenMemHandle(&base[k], o.handle[k], cudaIpcMemLazyEnablePeerAccess));
+      p->peer_open[side][k] = base[k];
+    }
+    p->peer_buf[side][0] = reinterpret_cast<float *>((char *)base[0] + o.offset[0]);
+    p->peer_buf[side][1] = reinterpret_cast<float *>((char *)base[1] + o.offset[1]);
+    p->peer_flags[side] = reinterpret_cast<uint32_t *>((char *)base[2] + o.offset[2]);
+    p->peer_n0[side] = o.n0;
+  }
+  return HPCX_OK;
+}
+
+// Last launch of a peer-store sweep sequence: the stream does not complete before both
+// neighbours have delivered the ghost planes of the newest iterate.
+__global__ void halo_wait_kernel(const uint32_t *flags, uint32_t *err, uint32_t want, int has_lo,
+                                 int has_hi) {
+  if (has_lo) wait_flag(flags + 0, want, err);
+  if (has_hi) wait_flag(flags + 1, want, err);
 }
 
 }  // namespace
@@ -207,8 +320,11 @@ hpcx_status hpcx_stencil_dist_plan(hpcx_ctx ctx, hpcx_grid in, hpcx_grid out,
                         in->desc.hi == out->desc.hi,
                "JACOBI7 needs identical ghost widths >= 1 on both grids");
   HPCX_REQUIRE(ctx, in->n[0] >= 1, "a slab needs at least one plane");
-  if (transport != 0)
-    return fail(ctx, HPCX_UNSUPPORTED, "only transport 0 (NCCL send/recv) is available");
+  if (transport != 0 && transport != 1)
+    return fail(ctx, HPCX_INVALID_ARG, "transport must be 0 (NCCL send/recv) or 1 (peer stores)");
+  if (transport == 1 && (in->desc.dtype != HPCX_F32 || st->variant == HPCX_VARIANT_DIRECT ||
+                         !ctx->encode_tiled))
+    return fail(ctx, HPCX_UNSUPPORTED, "the peer-store transport needs the fp32 TMA sweep");
   if (ctx->nranks > 1 && !ctx->nccl_comm)
     return fail(ctx, HPCX_NCCL_ERROR, "hpcx_comm_init has not been called");
   hpcx_halo_plan p = new (std::nothrow) hpcx_halo_plan_s();
@@ -225,7 +341,63 @@ hpcx_status hpcx_stencil_dist_plan(hpcx_ctx ctx, hpcx_grid in, hpcx_grid out,
     delete p;
     return fail(ctx, HPCX_CUDA_ERROR, std::string("cudaEventCreate: ") + cudaGetErrorString(e));
   }
+  if (transport == 1 && ctx->nranks > 1) {
+    hpcx_status rc = open_peers(p);
+    if (rc != HPCX_OK) {
+      close_peers(p);
+      hpcx_stencil_dist_destroy(p);
+      return rc;
+    }
+  }
   *out_plan = p;
+  return HPCX_OK;
+}
+
+// Transport 1: ONE kernel per sweep.  Its boundary CTAs run first (the top z segment marches
+// downwards), write their plane into this rank's dst AND into the neighbour's ghost plane with
+// peer stores over NVLink, and release a sweep-number flag in the neighbour; the next sweep's
+// producer warps acquire that flag before their first TMA load of a ghost plane.  No NCCL call,
+// no second stream and no pack kernel on the data path; the exchange overlaps the interior
+// planes of the same kernel.
+static hpcx_status dist_sweep_peer(hpcx_halo_plan p, int32_t steps, cudaStream_t cs, bool sync) {
+  hpcx_ctx ctx = p->ctx;
+  hpcx_grid g = p->in;
+  const bool has_lo = ctx->rank > 0, has_hi = ctx->rank + 1 < ctx->nranks;
+  const int64_t plane = g->ext[1] * g->pitch;
+  int cur = p->in->dev == p->buf[0] ? 0 : 1;  // which of (A, B) is the source
+  if (p->in->dev != p->buf[cur] || p->out->dev != p->buf[cur ^ 1])
+    return fail(ctx, HPCX_INVALID_ARG, "grid buffers changed since the plan was made");
+  hpcx_status rc = HPCX_OK;
+  for (int t = 0; t < steps; ++t) {
+    const int dst = cur ^ 1;
+    JacobiPeer pr;
+    if (has_lo) {
+      pr.ghost_lo = p->peer_buf[0][dst] + (p->peer_n0[0] + g->glo[0]) * plane;
+      pr.sig_lo = p->peer_flags[0] + 1;  // this rank is the low neighbour's HIGH side
+    }
+    if (has_hi) {
+      pr.ghost_hi = p->peer_buf[1][dst] + (g->glo[0] - 1) * plane;
+      pr.sig_hi = p->peer_flags[1] + 0;
+    }
+    pr.flags = p->flags;
+    pr.counters = p->flags + 4;
+    pr.wait_val = t == 0 ? 0 : p->epoch + (uint32_t)t;  // sweep 0 reads NCCL-exchanged ghosts
+    pr.sig_val = p->epoch + (uint32_t)t + 1;
+    rc = jacobi7_launch(g, p->buf[cur], p->buf[dst], HPCX_VARIANT_TMA, p->st.zsplit, 0, g->n[0], cs, &pr);
+    if (rc != HPCX_OK) return rc;
+    cur = dst;
+  }
+  p->epoch += (uint32_t)steps;
+  halo_wait_kernel<<<1, 1, 0, cs>>>(p->flags, p->flags + 6, p->epoch, has_lo, has_hi);
+  rc = after_launch(ctx, "halo_wait_kernel");
+  if (rc != HPCX_OK) return rc;
+  if ((steps & 1) == 0) std::swap(p->in->dev, p->out->dev);  // newest iterate is `out`
+  if (sync) {
+    HPCX_CUDA(ctx, cudaStreamSynchronize(cs));
+    uint32_t err = 0;
+    HPCX_CUDA(ctx, cudaMemcpy(&err, p->flags + 6, 4, cudaMemcpyDeviceToHost));
+    if (err) return fail(ctx, HPCX_NCCL_ERROR, "timed out waiting for a neighbour's halo flag");
+  }
   return HPCX_OK;
 }
 
@@ -251,11 +423,16 @@ hpcx_status hpcx_stencil_dist_sweep(hpcx_halo_plan p, int32_t steps, void *strea
   if (rc != HPCX_OK) return rc;
   HPCX_CUDA(ctx, cudaEventRecord(p->ev_recv, ms));
 
+  if (p->transport == 1 && ctx->nranks > 1) {
+    HPCX_CUDA(ctx, cudaStreamWaitEvent(cs, p->ev_recv, 0));
+    return dist_sweep_peer(p, steps, cs, stream == nullptr);
+  }
+
   void *src = p->in->dev, *dst = p->out->dev;
   for (int t = 0; t < steps; ++t) {
     HPCX_CUDA(ctx, cudaStreamWaitEvent(cs, p->ev_recv, 0));
-    rc = jacobi7_launch(g, src, dst, p->st.variant, 1, 0, 1, cs);
-    if (rc == HPCX_OK && nz > 1) rc = jacobi7_launch(g, src, dst, p->st.variant, 1, nz - 1, nz, cs);
+    rc = jacobi7_launch(g, src, dst, p->st.variant, 1, 0, 1, cs, nullptr);
+    if (rc == HPCX_OK && nz > 1) rc = jacobi7_launch(g, src, dst, p->st.variant, 1, nz - 1, nz, cs, nullptr);
     if (rc != HPCX_OK) return rc;
     if (t + 1 < steps) {
       HPCX_CUDA(ctx, cudaEventRecord(p->ev_bnd, cs));
@@ -265,7 +442,7 @@ hpcx_status hpcx_stencil_dist_sweep(hpcx_halo_plan p, int32_t steps, void *strea
       HPCX_CUDA(ctx, cudaEventRecord(p->ev_recv, ms));
     }
     if (nz > 2) {
-      rc = jacobi7_launch(g, src, dst, p->st.variant, p->st.zsplit, 1, nz - 1, cs);
+      rc = jacobi7_launch(g, src, dst, p->st.variant, p->st.zsplit, 1, nz - 1, cs, nullptr);
       if (rc != HPCX_OK) return rc;
     }
     std::swap(src, dst);
@@ -277,6 +454,8 @@ hpcx_status hpcx_stencil_dist_sweep(hpcx_halo_plan p, int32_t steps, void *strea
 
 hpcx_status hpcx_stencil_dist_destroy(hpcx_halo_plan p) {
   if (!p) return HPCX_INVALID_ARG;
+  cudaDeviceSynchronize();
+  close_peers(p);
   cudaEventDestroy(p->ev_bnd);
   cudaEventDestroy(p->ev_recv);
   cudaEventDestroy(p->ev_start);

@@ -130,6 +130,57 @@ box_y_reg_kernel(const T *__restrict__ in, T *__restrict__ out, GridGeom gi, Gri
   }
 }
 
+// fp32 BOX_Y, two columns per thread: the pair of ordered sums advances with one packed
+// add.rn.f32x2 per tap (IEEE round-to-nearest per lane, so still bit-exact), which halves the
+// issue slots of the 17 adds per cell, and a warp covers 256 contiguous bytes of every row.
+__device__ __forceinline__ float2 add2_rn(float2 a, float2 b) {
+  float2 d;
+  asm("{\n"
+      ".reg .b64 ra, rb, rd;\n"
+      "mov.b64 ra, {%2, %3};\n"
+      "mov.b64 rb, {%4, %5};\n"
+      "add.rn.f32x2 rd, ra, rb;\n"
+      "mov.b64 {%0, %1}, rd;\n"
+      "}"
+      : "=f"(d.x), "=f"(d.y)
+      : "f"(a.x), "f"(a.y), "f"(b.x), "f"(b.y));
+  return d;
+}
+
+// ROWS consecutive outputs of two adjacent columns per thread.  Full row blocks take the
+// unpredicated path (FULL), the last partial block the guarded one.
+template <int R, int ROWS, bool FULL>
+__device__ __forceinline__ void box_y_reg2_body(const float *__restrict__ p, float *__restrict__ q,
+                                                int64_t ip, int64_t op, int rows) {
+  float2 w[ROWS + 2 * R];
+#pragma unroll
+  for (int k = 0; k < ROWS + 2 * R; ++k)
+    w[k] = FULL || k < rows + 2 * R ? __ldg(reinterpret_cast<const float2 *>(p + k * ip))
+                                    : make_float2(0.f, 0.f);
+#pragma unroll
+  for (int j = 0; j < ROWS; ++j) {
+    float2 s = make_float2(0.f, 0.f);
+#pragma unroll
+    for (int k = 0; k <= 2 * R; ++k) s = add2_rn(s, w[j + k]);
+    if (FULL || j < rows) *reinterpret_cast<float2 *>(q + j * op) = s;
+  }
+}
+
+template <int R, int ROWS>
+__global__ void __launch_bounds__(128)
+box_y_reg2_kernel(const float *__restrict__ in, float *__restrict__ out, GridGeom gi, GridGeom go) {
+  const int64_t x = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) * 2;
+  const int64_t y0 = blockIdx.y * (int64_t)ROWS;
+  if (x >= gi.n2) return;
+  const float *p = in + gidx(gi, 0, y0 - R, x);
+  float *q = out + gidx(go, 0, y0, x);
+  const int rows = (int)min((int64_t)ROWS, gi.n1 - y0);
+  if (rows == ROWS)
+    box_y_reg2_body<R, ROWS, true>(p, q, gi.pitch, go.pitch, rows);
+  else
+    box_y_reg2_body<R, ROWS, false>(p, q, gi.pitch, go.pitch, rows);
+}
+
 // One thread per (x, y) column, marching along z over [z0, z1).
 template <typename T>
 __global__ void __launch_bounds__(256)
@@ -193,13 +244,144 @@ struct JacobiCfg {
 struct JacobiSplit {
   int ntx, nty, zs;   // tiles along x, y; z segments
   int hmax;           // height of the taller y tiles (<= TY)
+  int down_last;      // the last z segment marches downwards (top plane first)
 };
 
+// Consumer side of the ring.  DOWN: planes arrive in descending z (plane j is z_first - j), so
+// the plane read before the centre is z+1 and the one after it z-1; the add order of the sum is
+// the same either way.
+template <int S, bool DOWN>
+__device__ __forceinline__ void jacobi7_consume(float *ring, uint64_t *full, uint64_t *empty,
+                                                float *__restrict__ out, const GridGeom &g,
+                                                const JacobiPeer &pr, int x0, int y0, int h,
+                                                int zfirst, int np, int tiles_xy, float sixth) {
+  using C = JacobiCfg<S>;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // Warp w owns tile rows 2w and 2w+1 (box rows 2w+1, 2w+2); lane owns x0 + 4*lane .. +3.
+  const int br = 2 * warp + 1;
+  const int col = C::HX + 4 * lane;
+  auto plane_ptr = [&](int j) { return ring + (j % S) * C::kSlotFloats; };
+  auto wait_full = [&](int j) { mbar_wait(full + (j % S), (j / S) & 1); };
+  auto release = [&](int j) {
+    __syncwarp();
+    if (lane == 0) mbar_arrive(empty + (j % S));
+  };
+  auto ld4 = [&](const float *pl, int row) {
+    return *reinterpret_cast<const float4 *>(pl + row * C::BX + col);
+  };
+
+  float4 pv0, pv1, zc0, zc1;  // plane j-1 and plane j of this thread's two rows
+  wait_full(0);
+  {
+    const float *pl = plane_ptr(0);
+    pv0 = ld4(pl, br);
+    pv1 = ld4(pl, br + 1);
+  }
+  release(0);
+  wait_full(1);
+  {
+    const float *pl = plane_ptr(1);
+    zc0 = ld4(pl, br);
+    zc1 = ld4(pl, br + 1);
+  }
+
+  const int gx = x0 + 4 * lane;
+  const int gy = y0 + 2 * warp;
+  const bool row0 = 2 * warp < h, row1 = 2 * warp + 1 < h;
+  const bool full4 = gx + 3 < g.n2;
+  const int64_t plane_stride = g.ext1 * g.pitch;
+  const int64_t inplane = (gy + g.glo1) * g.pitch + g.xoff + gx;  // offset inside a plane
+  const int dz = DOWN ? -1 : 1;
+  int z = zfirst + dz;  // first output plane
+  float *orow = out + gidx(g, z, gy, gx);
+
+  for (int j = 1; j <= np - 2; ++j, orow += dz * plane_stride, z += dz) {
+    wait_full(j + 1);
+    const float *pn = plane_ptr(j + 1);
+    const float *pc = plane_ptr(j);
+    const float4 nx0 = ld4(pn, br), nx1 = ld4(pn, br + 1);
+    const float4 up = ld4(pc, br - 1);    // y-1 of row 0
+    const float4 dn = ld4(pc, br + 2);    // y+1 of row 1
+    // x neighbours: shuffles inside the warp, staged halo columns at the two ends.
+    float l0 = __shfl_up_sync(0xffffffffu, zc0.w, 1);
+    float l1 = __shfl_up_sync(0xffffffffu, zc1.w, 1);
+    float r0 = __shfl_down_sync(0xffffffffu, zc0.x, 1);
+    float r1 = __shfl_down_sync(0xffffffffu, zc1.x, 1);
+    if (lane == 0) {
+      l0 = pc[br * C::BX + C::HX - 1];
+      l1 = pc[(br + 1) * C::BX + C::HX - 1];
+    }
+    if (lane == 31) {
+      r0 = pc[br * C::BX + C::HX + C::TX];
+      r1 = pc[(br + 1) * C::BX + C::HX + C::TX];
+    }
+    release(j);  // plane j is not read from shared memory again
+
+    const float4 &zm0 = DOWN ? nx0 : pv0, &zm1 = DOWN ? nx1 : pv1;
+    const float4 &zp0 = DOWN ? pv0 : nx0, &zp1 = DOWN ? pv1 : nx1;
+    float4 o0, o1;
+#define HPCX_J7(o, zm, ym, xm, xp, yp, zp) \
+  o = mul_rn(add_rn(add_rn(add_rn(add_rn(add_rn(zm, ym), xm), xp), yp), zp), sixth)
+    HPCX_J7(o0.x, zm0.x, up.x, l0, zc0.y, zc1.x, zp0.x);
+    HPCX_J7(o0.y, zm0.y, up.y, zc0.x, zc0.z, zc1.y, zp0.y);
+    HPCX_J7(o0.z, zm0.z, up.z, zc0.y, zc0.w, zc1.z, zp0.z);
+    HPCX_J7(o0.w, zm0.w, up.w, zc0.z, r0, zc1.w, zp0.w);
+    HPCX_J7(o1.x, zm1.x, zc0.x, l1, zc1.y, dn.x, zp1.x);
+    HPCX_J7(o1.y, zm1.y, zc0.y, zc1.x, zc1.z, dn.y, zp1.y);
+    HPCX_J7(o1.z, zm1.z, zc0.z, zc1.y, zc1.w, dn.z, zp1.z);
+    HPCX_J7(o1.w, zm1.w, zc0.w, zc1.z, r1, dn.w, zp1.w);
+#undef HPCX_J7
+
+    // Boundary plane of the slab: the same registers also go straight into the neighbour's
+    // ghost plane over NVLink (peer store), then one CTA per side publishes the sweep number.
+    float *peer0 = pr.ghost_lo && z == 0 ? pr.ghost_lo + inplane : nullptr;
+    float *peer1 = pr.ghost_hi && z == (int)g.n0 - 1 ? pr.ghost_hi + inplane : nullptr;
+    if (full4) {
+      if (row0) st_cs(reinterpret_cast<float4 *>(orow), o0);
+      if (row1) st_cs(reinterpret_cast<float4 *>(orow + g.pitch), o1);
+      if (peer0) {
+        if (row0) *reinterpret_cast<float4 *>(peer0) = o0;
+        if (row1) *reinterpret_cast<float4 *>(peer0 + g.pitch) = o1;
+      }
+      if (peer1) {
+        if (row0) *reinterpret_cast<float4 *>(peer1) = o0;
+        if (row1) *reinterpret_cast<float4 *>(peer1 + g.pitch) = o1;
+      }
+    } else {
+      const float a0[4] = {o0.x, o0.y, o0.z, o0.w}, a1[4] = {o1.x, o1.y, o1.z, o1.w};
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+        if (gx + k < g.n2) {
+          if (row0) orow[k] = a0[k];
+          if (row1) orow[g.pitch + k] = a1[k];
+          if (peer0 && row0) peer0[k] = a0[k];
+          if (peer0 && row1) peer0[g.pitch + k] = a1[k];
+          if (peer1 && row0) peer1[k] = a0[k];
+          if (peer1 && row1) peer1[g.pitch + k] = a1[k];
+        }
+    }
+    if (peer0 || peer1) {  // uniform over the CTA's consumer warps
+      __threadfence_system();
+      asm volatile("bar.sync 1, %0;" ::"n"(C::kConsumerWarps * 32) : "memory");
+      if (threadIdx.x == 0) {
+        if (peer0 && (atomicAdd(pr.counters + 0, 1u) + 1) % (uint32_t)tiles_xy == 0)
+          st_release_sys(pr.sig_lo, pr.sig_val);
+        if (peer1 && (atomicAdd(pr.counters + 1, 1u) + 1) % (uint32_t)tiles_xy == 0)
+          st_release_sys(pr.sig_hi, pr.sig_val);
+      }
+    }
+    pv0 = zc0;
+    pv1 = zc1;
+    zc0 = nx0;
+    zc1 = nx1;
+  }
+}
+
 template <int S>
-__global__ void __launch_bounds__(JacobiCfg<S>::kThreads)
+__global__ void __launch_bounds__(JacobiCfg<S>::kThreads, 3)
 jacobi7_tma_kernel(const __grid_constant__ CUtensorMap map_hi, const __grid_constant__ CUtensorMap map_lo,
-                   float *__restrict__ out, GridGeom g, JacobiSplit sp, int zbeg, int zend,
-                   float sixth) {
+                   float *__restrict__ out, GridGeom g, JacobiSplit sp, JacobiPeer pr, int zbeg,
+                   int zend, float sixth) {
   using C = JacobiCfg<S>;
   extern __shared__ __align__(128) unsigned char smem[];
   float *ring = reinterpret_cast<float *>(smem);
@@ -218,6 +400,8 @@ jacobi7_tma_kernel(const __grid_constant__ CUtensorMap map_hi, const __grid_cons
   const int z1 = zbeg + (int)((int64_t)(bz + 1) * nzr / sp.zs);
   const int np = z1 - z0 + 2;  // planes z0-1 .. z1
   if (h <= 0 || z1 <= z0) return;
+  const bool down = sp.down_last && sp.zs > 1 && bz == sp.zs - 1;
+  const int zfirst = down ? z1 : z0 - 1;  // first plane streamed
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < S; ++s) {
@@ -236,105 +420,27 @@ jacobi7_tma_kernel(const __grid_constant__ CUtensorMap map_hi, const __grid_cons
       const uint32_t bytes = (uint32_t)(C::BX * (h + 2) * 4);
       const int c0 = (int)g.xoff + x0 - C::HX;
       const int c1 = y0 + (int)g.glo1 - 1;
-      const int c2 = z0 - 1 + (int)g.glo0;
+      const int dz = down ? -1 : 1;
       for (int j = 0; j < np; ++j) {
+        const int z = zfirst + dz * j;
+        // ghost planes filled by a neighbour: wait for its sweep number first
+        if (pr.wait_val) {
+          if (z == -1 && pr.sig_lo) wait_flag(pr.flags + 0, pr.wait_val, pr.counters + 2);
+          if (z == (int)g.n0 && pr.sig_hi) wait_flag(pr.flags + 1, pr.wait_val, pr.counters + 2);
+        }
         const int slot = j % S, use = j / S;
         if (use > 0) mbar_wait(empty + slot, (use - 1) & 1);
         mbar_expect_tx(full + slot, bytes);
-        tma_load_3d(ring + slot * C::kSlotFloats, map, c0, c1, c2 + j, full + slot);
+        tma_load_3d(ring + slot * C::kSlotFloats, map, c0, c1, z + (int)g.glo0, full + slot);
       }
     }
     return;
   }
 
-  // ------------------------------------------------------------------ consumers
-  // Warp w owns tile rows 2w and 2w+1 (box rows 2w+1, 2w+2); lane owns x0 + 4*lane .. +3.
-  const int br = 2 * warp + 1;
-  const int col = C::HX + 4 * lane;
-  auto plane_ptr = [&](int j) { return ring + (j % S) * C::kSlotFloats; };
-  auto wait_full = [&](int j) { mbar_wait(full + (j % S), (j / S) & 1); };
-  auto release = [&](int j) {
-    __syncwarp();
-    if (lane == 0) mbar_arrive(empty + (j % S));
-  };
-  auto ld4 = [&](const float *pl, int row) {
-    return *reinterpret_cast<const float4 *>(pl + row * C::BX + col);
-  };
-
-  float4 zm0, zm1, zc0, zc1;
-  wait_full(0);
-  {
-    const float *pl = plane_ptr(0);
-    zm0 = ld4(pl, br);
-    zm1 = ld4(pl, br + 1);
-  }
-  release(0);
-  wait_full(1);
-  {
-    const float *pl = plane_ptr(1);
-    zc0 = ld4(pl, br);
-    zc1 = ld4(pl, br + 1);
-  }
-
-  const int gx = x0 + 4 * lane;
-  const int gy = y0 + 2 * warp;
-  const bool row0 = 2 * warp < h, row1 = 2 * warp + 1 < h;
-  const bool full4 = gx + 3 < g.n2;
-  const int64_t plane_stride = g.ext1 * g.pitch;
-  float *orow = out + gidx(g, z0, gy, gx);
-
-  for (int j = 1; j <= np - 2; ++j, orow += plane_stride) {
-    wait_full(j + 1);
-    const float *pn = plane_ptr(j + 1);
-    const float *pc = plane_ptr(j);
-    const float4 zp0 = ld4(pn, br), zp1 = ld4(pn, br + 1);
-    const float4 up = ld4(pc, br - 1);    // y-1 of row 0
-    const float4 dn = ld4(pc, br + 2);    // y+1 of row 1
-    // x neighbours: shuffles inside the warp, staged halo columns at the two ends.
-    float l0 = __shfl_up_sync(0xffffffffu, zc0.w, 1);
-    float l1 = __shfl_up_sync(0xffffffffu, zc1.w, 1);
-    float r0 = __shfl_down_sync(0xffffffffu, zc0.x, 1);
-    float r1 = __shfl_down_sync(0xffffffffu, zc1.x, 1);
-    if (lane == 0) {
-      l0 = pc[br * C::BX + C::HX - 1];
-      l1 = pc[(br + 1) * C::BX + C::HX - 1];
-    }
-    if (lane == 31) {
-      r0 = pc[br * C::BX + C::HX + C::TX];
-      r1 = pc[(br + 1) * C::BX + C::HX + C::TX];
-    }
-    release(j);  // plane j is not read from shared memory again
-
-    float4 o0, o1;
-#define HPCX_J7(o, zm, ym, xm, xp, yp, zp) \
-  o = mul_rn(add_rn(add_rn(add_rn(add_rn(add_rn(zm, ym), xm), xp), yp), zp), sixth)
-    HPCX_J7(o0.x, zm0.x, up.x, l0, zc0.y, zc1.x, zp0.x);
-    HPCX_J7(o0.y, zm0.y, up.y, zc0.x, zc0.z, zc1.y, zp0.y);
-    HPCX_J7(o0.z, zm0.z, up.z, zc0.y, zc0.w, zc1.z, zp0.z);
-    HPCX_J7(o0.w, zm0.w, up.w, zc0.z, r0, zc1.w, zp0.w);
-    HPCX_J7(o1.x, zm1.x, zc0.x, l1, zc1.y, dn.x, zp1.x);
-    HPCX_J7(o1.y, zm1.y, zc0.y, zc1.x, zc1.z, dn.y, zp1.y);
-    HPCX_J7(o1.z, zm1.z, zc0.z, zc1.y, zc1.w, dn.z, zp1.z);
-    HPCX_J7(o1.w, zm1.w, zc0.w, zc1.z, r1, dn.w, zp1.w);
-#undef HPCX_J7
-
-    if (full4) {
-      if (row0) st_cs(reinterpret_cast<float4 *>(orow), o0);
-      if (row1) st_cs(reinterpret_cast<float4 *>(orow + g.pitch), o1);
-    } else {
-      const float a0[4] = {o0.x, o0.y, o0.z, o0.w}, a1[4] = {o1.x, o1.y, o1.z, o1.w};
-#pragma unroll
-      for (int k = 0; k < 4; ++k)
-        if (gx + k < g.n2) {
-          if (row0) orow[k] = a0[k];
-          if (row1) orow[g.pitch + k] = a1[k];
-        }
-    }
-    zm0 = zc0;
-    zm1 = zc1;
-    zc0 = zp0;
-    zc1 = zp1;
-  }
+  if (down)
+    jacobi7_consume<S, true>(ring, full, empty, out, g, pr, x0, y0, h, zfirst, np, sp.ntx * sp.nty, sixth);
+  else
+    jacobi7_consume<S, false>(ring, full, empty, out, g, pr, x0, y0, h, zfirst, np, sp.ntx * sp.nty, sixth);
 }
 
 // ------------------------------------------------------------------ host side
@@ -359,7 +465,7 @@ hpcx_status launch_box_direct(hpcx_grid in, hpcx_grid out, int axis, int radius,
 
 // Register-tiled variants exist for the radii a 16-byte vector divides (the reference's
 // nblur = 8 among them); everything else takes the direct kernel.
-template <typename T, int R>
+template <typename T, int R, int ROWS>
 hpcx_status launch_box_fast_r(hpcx_grid in, hpcx_grid out, int axis, cudaStream_t s) {
   constexpr int V = 16 / (int)sizeof(T);
   if (axis == 2) {
@@ -368,7 +474,14 @@ hpcx_status launch_box_fast_r(hpcx_grid in, hpcx_grid out, int axis, cudaStream_
                                                  geom_of(out));
     return after_launch(in->ctx, "box_x_vec_kernel");
   }
-  constexpr int ROWS = 32;
+  if constexpr (sizeof(T) == 4) {
+    if (in->n[2] % 2 == 0) {  // pitches and x offsets are multiples of 8 floats: 8-byte aligned pairs
+      dim3 grid2((unsigned)((in->n[2] / 2 + 127) / 128), (unsigned)((in->n[1] + ROWS - 1) / ROWS));
+      box_y_reg2_kernel<R, ROWS><<<grid2, 128, 0, s>>>((const float *)in->dev, (float *)out->dev,
+                                                       geom_of(in), geom_of(out));
+      return after_launch(in->ctx, "box_y_reg2_kernel");
+    }
+  }
   dim3 grid((unsigned)((in->n[2] + 127) / 128), (unsigned)((in->n[1] + ROWS - 1) / ROWS));
   box_y_reg_kernel<T, R, ROWS><<<grid, 128, 0, s>>>((const T *)in->dev, (T *)out->dev, geom_of(in),
                                                      geom_of(out));
@@ -376,15 +489,19 @@ hpcx_status launch_box_fast_r(hpcx_grid in, hpcx_grid out, int axis, cudaStream_
 }
 
 template <typename T>
-hpcx_status launch_box(hpcx_grid in, hpcx_grid out, int axis, int radius, int variant,
+hpcx_status launch_box(hpcx_grid in, hpcx_grid out, int axis, int radius, int variant, int rows,
                        cudaStream_t s) {
   constexpr int V = 16 / (int)sizeof(T);
   const bool fast_ok = variant != HPCX_VARIANT_DIRECT && in->n[1] <= 65535 * 32 &&
                        (axis != 2 || (in->n[2] % V == 0 && in->n[1] <= 65535));
   if (fast_ok) {
     switch (radius) {
-      case 8: return launch_box_fast_r<T, 8>(in, out, axis, s);
-      case 4: return launch_box_fast_r<T, 4>(in, out, axis, s);
+      case 8:
+        return rows == 16 ? launch_box_fast_r<T, 8, 16>(in, out, axis, s)
+                          : launch_box_fast_r<T, 8, 32>(in, out, axis, s);
+      case 4:
+        return rows == 16 ? launch_box_fast_r<T, 4, 16>(in, out, axis, s)
+                          : launch_box_fast_r<T, 4, 32>(in, out, axis, s);
       default: break;
     }
   }
@@ -419,15 +536,16 @@ constexpr int kJacobiStages = 6;
 
 // Equal-work split: minimise (CTAs per SM, rounded up, at least 3) x (cells one CTA loads).  `zsplit` > 0
 // pins the number of z segments (tests exercise short segments that way).
-JacobiSplit jacobi_plan(hpcx_ctx ctx, int64_t nx, int64_t ny, int64_t nz, int zsplit) {
+JacobiSplit jacobi_plan(hpcx_ctx ctx, int64_t nx, int64_t ny, int64_t nz, int zsplit, bool down_last) {
   using C = JacobiCfg<kJacobiStages>;
   const int64_t ntx = (nx + C::TX - 1) / C::TX;
   const int64_t nty_min = (ny + C::TY - 1) / C::TY;
-  JacobiSplit best{(int)ntx, (int)nty_min, 1, (int)((ny + nty_min - 1) / nty_min)};
+  JacobiSplit best{(int)ntx, (int)nty_min, 1, (int)((ny + nty_min - 1) / nty_min), 0};
   double best_cost = 1e300;
   const int64_t nty_max = std::min<int64_t>(ny, std::max<int64_t>(nty_min * 2, nty_min + 8));
-  const int64_t zs_lo = zsplit > 0 ? std::min<int64_t>(zsplit, nz) : 1;
-  const int64_t zs_hi = zsplit > 0 ? zs_lo : std::max<int64_t>(1, nz / 8);
+  // a downward-marching top segment needs a segment of its own
+  const int64_t zs_lo = zsplit > 0 ? std::min<int64_t>(zsplit, nz) : (down_last && nz >= 2 ? 2 : 1);
+  const int64_t zs_hi = zsplit > 0 ? zs_lo : std::max<int64_t>(zs_lo, nz / 8);
   for (int64_t nty = nty_min; nty <= nty_max; ++nty) {
     const int64_t h = (ny + nty - 1) / nty;
     for (int64_t zs = zs_lo; zs <= zs_hi; ++zs) {
@@ -440,10 +558,11 @@ JacobiSplit jacobi_plan(hpcx_ctx ctx, int64_t nx, int64_t ny, int64_t nz, int zs
       const double cost = (double)std::max<int64_t>(per_sm, 3) * (double)(h + 2) * (double)(zl + 2 + 3);
       if (cost < best_cost * (1.0 - 1e-9)) {
         best_cost = cost;
-        best = JacobiSplit{(int)ntx, (int)nty, (int)zs, (int)h};
+        best = JacobiSplit{(int)ntx, (int)nty, (int)zs, (int)h, 0};
       }
     }
   }
+  best.down_last = down_last && best.zs > 1 ? 1 : 0;
   return best;
 }
 
@@ -467,10 +586,14 @@ const CUtensorMap *jacobi_map(hpcx_grid_s *g, void *src, int boxh, hpcx_status *
 }
 
 hpcx_status launch_jacobi_tma(hpcx_grid_s *g, void *src, void *dst, int zsplit, int64_t zbeg,
-                              int64_t zend, cudaStream_t s) {
+                              int64_t zend, const JacobiPeer *peer, cudaStream_t s) {
   using C = JacobiCfg<kJacobiStages>;
   hpcx_ctx ctx = g->ctx;
-  const JacobiSplit sp = jacobi_plan(ctx, g->n[2], g->n[1], zend - zbeg, zsplit);
+  const JacobiPeer pr = peer ? *peer : JacobiPeer{};
+  // The top segment marches downwards when its first plane feeds a neighbour (and under
+  // HPCX_JACOBI_DOWN=1, which lets single-GPU tests cover that path).
+  const bool down = pr.ghost_hi != nullptr || ctx->force_jacobi_down;
+  const JacobiSplit sp = jacobi_plan(ctx, g->n[2], g->n[1], zend - zbeg, zsplit, down);
   hpcx_status st = HPCX_OK;
   const CUtensorMap *hi = jacobi_map(g, src, sp.hmax + 2, &st);
   if (!hi) return st;
@@ -487,7 +610,7 @@ hpcx_status launch_jacobi_tma(hpcx_grid_s *g, void *src, void *dst, int zsplit, 
   }
   const unsigned ncta = (unsigned)(sp.ntx * sp.nty * sp.zs);
   jacobi7_tma_kernel<kJacobiStages><<<ncta, C::kThreads, C::kSmemBytes, s>>>(
-      *hi, *lo, (float *)dst, geom_of(g), sp, (int)zbeg, (int)zend, 1.0f / 6.0f);
+      *hi, *lo, (float *)dst, geom_of(g), sp, pr, (int)zbeg, (int)zend, 1.0f / 6.0f);
   return after_launch(ctx, "jacobi7_tma_kernel");
 }
 
@@ -496,17 +619,19 @@ hpcx_status launch_jacobi_tma(hpcx_grid_s *g, void *src, void *dst, int zsplit, 
 namespace hpcx {
 // One Jacobi sweep src -> dst over the planes of grid `g` (shared with dist.cu).
 hpcx_status jacobi7_launch(hpcx_grid_s *g, void *src, void *dst, int variant, int zsplit,
-                           int64_t zbeg, int64_t zend, cudaStream_t s) {
+                           int64_t zbeg, int64_t zend, cudaStream_t s, const JacobiPeer *peer) {
   if (zend <= zbeg) return HPCX_OK;
   const bool tma_ok = g->desc.dtype == HPCX_F32 && g->ctx->encode_tiled && g->n[2] < (1 << 30);
   if (variant == HPCX_VARIANT_TMA && !tma_ok)
     return fail(g->ctx, HPCX_UNSUPPORTED, "TMA Jacobi variant needs fp32 and a tensor-map driver");
+  if (peer && (variant == HPCX_VARIANT_DIRECT || !tma_ok))
+    return fail(g->ctx, HPCX_UNSUPPORTED, "the peer-store transport needs the fp32 TMA sweep");
   if (variant == HPCX_VARIANT_DIRECT || !tma_ok) {
     if (g->desc.dtype == HPCX_F64)
       return launch_jacobi_direct<double>(g, src, dst, zsplit, zbeg, zend, s);
     return launch_jacobi_direct<float>(g, src, dst, zsplit, zbeg, zend, s);
   }
-  return launch_jacobi_tma(g, src, dst, zsplit, zbeg, zend, s);
+  return launch_jacobi_tma(g, src, dst, zsplit, zbeg, zend, peer, s);
 }
 }  // namespace hpcx
 
@@ -526,8 +651,8 @@ extern "C" hpcx_status hpcx_stencil_sweep(hpcx_grid in, hpcx_grid out, const hpc
     HPCX_REQUIRE(ctx, st->radius >= 0 && st->radius <= in->desc.lo && st->radius <= in->desc.hi,
                  "radius exceeds the ghost width of the input grid");
     const int axis = st->kind == HPCX_STENCIL_BOX_X ? 2 : 1;
-    rc = in->desc.dtype == HPCX_F64 ? launch_box<double>(in, out, axis, st->radius, st->variant, s)
-                                    : launch_box<float>(in, out, axis, st->radius, st->variant, s);
+    rc = in->desc.dtype == HPCX_F64 ? launch_box<double>(in, out, axis, st->radius, st->variant, st->zsplit, s)
+                                    : launch_box<float>(in, out, axis, st->radius, st->variant, st->zsplit, s);
   } else if (st->kind == HPCX_STENCIL_JACOBI7) {
     if (in->desc.ndim != 3) return fail(ctx, HPCX_UNSUPPORTED, "JACOBI7 takes 3-D grids");
     HPCX_REQUIRE(ctx, in->desc.lo >= 1 && in->desc.hi >= 1 && in->desc.lo == out->desc.lo &&
@@ -536,7 +661,7 @@ extern "C" hpcx_status hpcx_stencil_sweep(hpcx_grid in, hpcx_grid out, const hpc
     for (int t = 0; t < steps && rc == HPCX_OK; ++t) {
       void *src = (t & 1) ? out->dev : in->dev;
       void *dst = (t & 1) ? in->dev : out->dev;
-      rc = jacobi7_launch(in, src, dst, st->variant, st->zsplit, 0, in->n[0], s);
+      rc = jacobi7_launch(in, src, dst, st->variant, st->zsplit, 0, in->n[0], s, nullptr);
     }
     if (rc == HPCX_OK && (steps & 1) == 0) std::swap(in->dev, out->dev);
   } else {

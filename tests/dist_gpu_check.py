@@ -32,8 +32,13 @@ def main():
         hd.init_comm(ctx, rank, world)
 
     # ---- stencil: global (nz, ny, nx) split into z-slabs
-    for (nz, ny, nx), steps, variant in (((24, 20, 140), 5, hp.VARIANT_TMA), ((13, 9, 33), 4, hp.VARIANT_DIRECT),
-                                         ((64, 64, 256), 6, hp.VARIANT_AUTO)):
+    # transport 0: NCCL send/recv on the comm stream; 1: fused peer stores + flags (TMA sweep)
+    for (nz, ny, nx), steps, variant, transport in (
+            ((24, 20, 140), 5, hp.VARIANT_TMA, 0), ((13, 9, 33), 4, hp.VARIANT_DIRECT, 0),
+            ((64, 64, 256), 6, hp.VARIANT_AUTO, 0), ((24, 20, 140), 5, hp.VARIANT_TMA, 1),
+            ((64, 64, 256), 6, hp.VARIANT_AUTO, 1), ((17, 33, 129), 3, hp.VARIANT_TMA, 1),
+            ((8, 40, 64), 1, hp.VARIANT_TMA, 1), ((2 * world, 16, 32), 4, hp.VARIANT_TMA, 1),
+            ((world, 16, 32), 3, hp.VARIANT_TMA, 1)):
         full = oracle.fill((nz + 2) * (ny + 2) * (nx + 2), 7, np.float32)
         want = oracle.jacobi7(full, nz, ny, nx, 1, 1, steps).reshape(nz + 2, ny + 2, nx + 2)
         b = hp.partition_slabs(nz, world)
@@ -43,11 +48,25 @@ def main():
         gb = hp.DeviceGrid(ctx, (z1 - z0, ny, nx), np.float32, 1)
         ga.upload(slab)
         gb.upload(slab)
-        plan = hd.HaloPlan(ctx, ga, gb, hp.STENCIL_JACOBI7, variant)
+        plan = hd.HaloPlan(ctx, ga, gb, hp.STENCIL_JACOBI7, variant, transport=transport)
         plan.sweep(steps)
         out = gb.download().reshape(z1 - z0 + 2, ny + 2, nx + 2)
         assert bits_equal(np.ascontiguousarray(out[1:-1, 1:-1, 1:-1]),
-                          np.ascontiguousarray(want[z0 + 1:z1 + 1, 1:-1, 1:-1])), (rank, nz, "jacobi")
+                          np.ascontiguousarray(want[z0 + 1:z1 + 1, 1:-1, 1:-1])), (rank, nz, "jacobi", transport)
+        # a second call sweeps `in` (iterate steps-1) again: in -> out semantics, epoch carries on
+        plan.sweep(2)
+        want2 = oracle.jacobi7(full, nz, ny, nx, 1, 1, steps + 1).reshape(nz + 2, ny + 2, nx + 2)
+        out = gb.download().reshape(z1 - z0 + 2, ny + 2, nx + 2)
+        assert bits_equal(np.ascontiguousarray(out[1:-1, 1:-1, 1:-1]),
+                          np.ascontiguousarray(want2[z0 + 1:z1 + 1, 1:-1, 1:-1])), (rank, nz, "jacobi+2", transport)
+        if world > 1:
+            # ghost planes of the newest iterate are the neighbours' boundary planes
+            if rank > 0 and transport == 1:
+                assert bits_equal(np.ascontiguousarray(out[0, 1:-1, 1:-1]),
+                                  np.ascontiguousarray(want2[z0, 1:-1, 1:-1])), (rank, "ghost lo")
+            if rank < world - 1 and transport == 1:
+                assert bits_equal(np.ascontiguousarray(out[-1, 1:-1, 1:-1]),
+                                  np.ascontiguousarray(want2[z1 + 1, 1:-1, 1:-1])), (rank, "ghost hi")
         plan.destroy()
         ga.destroy()
         gb.destroy()
