@@ -162,7 +162,8 @@ def workload_config(world: int) -> dict:
     return {"workload": "BASELINE configs[1]: CSR SpMV fp64, 2-D 5-point Laplacian 8192x8192 per GPU "
                         "(67,108,864 rows, 335,511,552 nnz at N=1)",
             "grid": [GRID * world, GRID], "rows_per_gpu": GRID * GRID,
-            "partition": "1 slab" if world == 1 else f"{world} row slabs, x-halo 8192 doubles per neighbour",
+            "partition": "1 slab" if world == 1 else f"{world} row slabs, x-halo 8192 doubles per neighbour, "
+                         "pushed by peer stores over NVLink (hpcx_csr_halo_transport 1)",
             "l2": "inputs (4.3 GB matrix per GPU) larger than L2; no explicit flush",
             "algorithmic_bytes": "12 B/nnz + 20 B/row (SURVEY.md §8d)"}
 
@@ -218,6 +219,7 @@ def run_ours(args, rank: int, world: int, local: int):
     D = hp.DeviceCsr(ctx, A)
     if world > 1:
         D.set_halo(L)
+        D.halo_transport(1)  # fused gather + peer stores + flags (NCCL variant timed below as extra)
     log(f"[rank {rank}] hpcx_csr_create {time.time() - t:.1f}s")
 
     stream = torch.cuda.Stream()
@@ -293,6 +295,16 @@ def run_ours(args, rank: int, world: int, local: int):
     checksum = float(np.abs(y_pin.numpy()).sum())
 
     extra = stencil_extra(ctx, torch, stream, world, rank, barrier, max_over_ranks, hp, hd, synth)
+    if world > 1:
+        # the same product with the NCCL send/recv exchange, for comparison
+        D.halo_transport(0)
+        with torch.cuda.stream(stream):
+            for _ in range(3):
+                step()
+            dt_n, _, _ = time_steps(torch, stream, step, args.steps, barrier)
+        dt_n = max_over_ranks(dt_n)
+        extra["spmv_nccl_transport"] = {"metric": METRIC, "value": nbytes_rank * world * args.steps / dt_n / 1e9,
+                                        "ms_per_step": dt_n / args.steps * 1e3}
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
@@ -322,7 +334,7 @@ def run_ours(args, rank: int, world: int, local: int):
                          "frac_of_nominal_8000": achieved / 8000.0,
                          "algorithmic_bytes_per_launch": nbytes_rank,
                          "note": "per-rank step time / per-rank bytes" + (
-                             "" if world == 1 else " (step = gather + interior + boundary kernels)")},
+                             "" if world == 1 else " (step = push + interior + flag wait + boundary + ack kernels)")},
             "cpu_baseline": cpu,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": nloc * 8 * world,
                     "d2h_bytes_per_step": nloc * 8 * world, "steps": k_e2e,

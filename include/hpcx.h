@@ -281,6 +281,14 @@ HPCX_API hpcx_status hpcx_stencil_dist_destroy(hpcx_halo_plan plan);
 HPCX_API hpcx_status hpcx_csr_set_halo(hpcx_csr A, int64_t nloc, int64_t nhalo,
                                        const int64_t *recv_counts, const int64_t *send_counts,
                                        const int32_t *send_idx, const uint8_t *row_kind);
+/* Selects how hpcx_spmv_dist moves the boundary x entries (collective over the communicator,
+ * call after hpcx_csr_set_halo):
+ *   0  gather kernel -> grouped NCCL send/recv on the comm stream -> boundary rows (default);
+ *   1  fused: the gather kernel stores every boundary entry straight into its slot of the
+ *      destination rank's [owned | halo] buffer over NVLink (CUDA IPC peer windows) and
+ *      releases a product-number flag there; the boundary rows start once the flags of all
+ *      source ranks have been acquired.  One stream, no NCCL call on the data path. */
+HPCX_API hpcx_status hpcx_csr_halo_transport(hpcx_csr A, int32_t transport);
 /* Device buffer [owned | halo] the distributed product reads x from; callers that write
  * their owned x entries straight into it and pass it as x_local avoid a device copy. */
 HPCX_API hpcx_status hpcx_csr_x_buffer(hpcx_csr A, void **x_full);

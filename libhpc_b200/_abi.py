@@ -101,6 +101,7 @@ PROTOTYPES = {
     "hpcx_stencil_dist_sweep": (_i32, [_vp, _i32, _vp]),
     "hpcx_stencil_dist_destroy": (_i32, [_vp]),
     "hpcx_csr_set_halo": (_i32, [_vp, _i64, _i64, _vp, _vp, _vp, _vp]),
+    "hpcx_csr_halo_transport": (_i32, [_vp, _i32]),
     "hpcx_csr_x_buffer": (_i32, [_vp, _P(_vp)]),
     "hpcx_spmv_dist": (_i32, [_vp, _vp, _vp, _vp]),
 }

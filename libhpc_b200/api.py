@@ -391,6 +391,10 @@ class DeviceCsr:
             loc["send_counts"].ctypes.data, loc["send_idx"].ctypes.data if loc["nsend"] else None,
             loc["row_kind"].ctypes.data))
 
+    def halo_transport(self, transport: int):
+        """0 = NCCL send/recv, 1 = fused peer stores + flags (collective; after set_halo)."""
+        self.ctx.check(self.ctx.lib.hpcx_csr_halo_transport(self.h, transport))
+
     def x_buffer(self) -> int:
         p = C.c_void_p()
         self.ctx.check(self.ctx.lib.hpcx_csr_x_buffer(self.h, C.byref(p)))

@@ -466,6 +466,9 @@ hpcx_status hpcx_stencil_dist_destroy(hpcx_halo_plan p) {
 }  // extern "C"
 
 // ------------------------------------------------------------------ distributed SpMV
+namespace hpcx {
+void csr_close_peers(hpcx_csr A);
+}
 namespace {
 
 template <typename T>
@@ -477,7 +480,78 @@ gather_boundary_x_kernel(const T *__restrict__ x, const int32_t *__restrict__ se
     sendbuf[i] = __ldg(x + send_idx[i]);
 }
 
+// ---- transport 1: gather + peer store + flag in one kernel ------------------------------
+constexpr int kSyncData = 0, kSyncAck = 64, kSyncCount = 128, kSyncErr = 129, kMaxPeers = 64;
+
+// grid = (blocks per segment, segments).  Segment s holds the entries destined for rank
+// seg_rank[s]; they are stored straight into that rank's halo slots.  The last CTA to finish
+// publishes the product number in every destination.
+template <typename T>
+__global__ void __launch_bounds__(256)
+push_boundary_x_kernel(const T *__restrict__ x, const int32_t *__restrict__ send_idx,
+                       const int32_t *__restrict__ seg_start, const int32_t *__restrict__ seg_rank,
+                       void *const *__restrict__ seg_dst, uint32_t *const *__restrict__ seg_flag,
+                       uint32_t *sync, uint32_t epoch) {
+  const int s = blockIdx.y;
+  // The destination must have finished reading the previous product's halo (its ack).
+  if (threadIdx.x == 0) wait_flag(sync + kSyncAck + seg_rank[s], epoch - 1, sync + kSyncErr);
+  __syncthreads();
+  const int a = seg_start[s], e = seg_start[s + 1];
+  T *dst = static_cast<T *>(seg_dst[s]);
+  for (int i = a + blockIdx.x * blockDim.x + threadIdx.x; i < e; i += gridDim.x * blockDim.x)
+    dst[i - a] = __ldg(x + send_idx[i]);
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const uint32_t total = gridDim.x * gridDim.y;
+    if ((atomicAdd(sync + kSyncCount, 1u) + 1) % total == 0)
+      for (int k = 0; k < (int)gridDim.y; ++k) st_release_sys(seg_flag[k], epoch);
+  }
+}
+
+// Holds the stream until every source rank's boundary entries of product `epoch` have landed.
+__global__ void halo_x_ready_kernel(uint32_t *sync, const int32_t *__restrict__ src_rank, int nsrc,
+                                    uint32_t epoch) {
+  if ((int)threadIdx.x < nsrc)
+    wait_flag(sync + kSyncData + src_rank[threadIdx.x], epoch, sync + kSyncErr);
+}
+
+// Tells every source rank that this rank's boundary rows of product `epoch` have read the halo.
+__global__ void halo_x_ack_kernel(uint32_t *const *__restrict__ src_ack, int nsrc, uint32_t epoch) {
+  if ((int)threadIdx.x < nsrc) st_release_sys(src_ack[threadIdx.x], epoch);
+}
+
+struct CsrPeerInfo {
+  cudaIpcMemHandle_t handle[2];  // allocations holding [owned | halo] x and the sync block
+  int64_t offset[2];
+  int64_t nloc;
+  int64_t recv_off[kMaxPeers];   // element offset inside the halo of the segment from rank q
+  int64_t recv_cnt[kMaxPeers];
+};
+
+void close_csr_peers(hpcx_csr A) {
+  for (void *b : A->peer_open) cudaIpcCloseMemHandle(b);
+  A->peer_open.clear();
+  cudaFree(A->d_sync);
+  cudaFree(A->d_seg_start);
+  cudaFree(A->d_seg_rank);
+  cudaFree(A->d_seg_dst);
+  cudaFree(A->d_seg_flag);
+  cudaFree(A->d_src_rank);
+  cudaFree(A->d_src_ack);
+  A->d_sync = nullptr;
+  A->d_seg_start = A->d_seg_rank = A->d_src_rank = nullptr;
+  A->d_seg_dst = nullptr;
+  A->d_seg_flag = A->d_src_ack = nullptr;
+  A->nseg = A->nsrc = 0;
+  A->transport = 0;
+}
+
 }  // namespace
+
+namespace hpcx {
+void csr_close_peers(hpcx_csr A) { close_csr_peers(A); }
+}  // namespace hpcx
 
 extern "C" {
 
@@ -490,6 +564,7 @@ hpcx_status hpcx_csr_set_halo(hpcx_csr A, int64_t nloc, int64_t nhalo, const int
                "local matrix must have nloc rows and nloc + nhalo columns");
   HPCX_REQUIRE(ctx, recv_counts && send_counts && row_kind, "null halo table");
   const int P = ctx->nranks;
+  close_csr_peers(A);  // peer windows point into the buffers replaced below
   A->nloc = nloc;
   A->nhalo = nhalo;
   A->recv_counts.assign(recv_counts, recv_counts + P);
@@ -546,6 +621,126 @@ hpcx_status hpcx_csr_set_halo(hpcx_csr A, int64_t nloc, int64_t nhalo, const int
   return HPCX_OK;
 }
 
+hpcx_status hpcx_csr_halo_transport(hpcx_csr A, int32_t transport) {
+  if (!A) return HPCX_INVALID_ARG;
+  hpcx_ctx ctx = A->ctx;
+  HPCX_REQUIRE(ctx, transport == 0 || transport == 1, "transport must be 0 or 1");
+  HPCX_REQUIRE(ctx, A->d_xfull != nullptr, "hpcx_csr_set_halo has not been called");
+  HPCX_CUDA(ctx, cudaDeviceSynchronize());
+  close_csr_peers(A);
+  if (transport == 0 || ctx->nranks <= 1) return HPCX_OK;
+  if (!ctx->nccl_comm) return fail(ctx, HPCX_NCCL_ERROR, "hpcx_comm_init has not been called");
+  const int P = ctx->nranks, me = ctx->rank;
+  HPCX_REQUIRE(ctx, P <= kMaxPeers, "the peer-store transport supports up to 64 ranks");
+
+  HPCX_CUDA(ctx, cudaMalloc((void **)&A->d_sync, 2u << 20));  // an allocation of its own
+  HPCX_CUDA(ctx, cudaMemset(A->d_sync, 0, 1024));
+  CsrPeerInfo mine{};
+  hpcx_status st = ipc_export(ctx, A->d_xfull, &mine.handle[0], &mine.offset[0]);
+  if (st == HPCX_OK) st = ipc_export(ctx, A->d_sync, &mine.handle[1], &mine.offset[1]);
+  if (st != HPCX_OK) return st;
+  mine.nloc = A->nloc;
+  int64_t roff = 0;
+  for (int q = 0; q < P; ++q) {
+    mine.recv_off[q] = roff;
+    mine.recv_cnt[q] = A->recv_counts[q];
+    roff += A->recv_counts[q];
+  }
+  std::vector<CsrPeerInfo> all(P);
+  st = allgather_bytes(ctx, &mine, all.data(), sizeof(CsrPeerInfo));
+  if (st != HPCX_OK) return st;
+
+  std::vector<int32_t> seg_start{0}, seg_rank, src_rank;
+  std::vector<void *> seg_dst;
+  std::vector<uint32_t *> seg_flag, src_ack;
+  int64_t soff = 0;
+  for (int q = 0; q < P; ++q) {
+    const bool sends = A->send_counts[q] > 0, recvs = A->recv_counts[q] > 0;
+    if (q == me || (!sends && !recvs)) {
+      soff += A->send_counts[q];
+      continue;
+    }
+    if (all[q].recv_cnt[me] != A->send_counts[q])
+      return fail(ctx, HPCX_INVALID_ARG, "send/recv counts of two ranks do not match");
+    void *bx = nullptr, *bs = nullptr;
+    HPCX_CUDA(ctx, cudaIpcOpenMemHandle(&bx, all[q].handle[0], cudaIpcMemLazyEnablePeerAccess));
+    A->peer_open.push_back(bx);
+    HPCX_CUDA(ctx, cudaIpcOpenMemHandle(&bs, all[q].handle[1], cudaIpcMemLazyEnablePeerAccess));
+    A->peer_open.push_back(bs);
+    char *px = (char *)bx + all[q].offset[0];
+    uint32_t *ps = reinterpret_cast<uint32_t *>((char *)bs + all[q].offset[1]);
+    if (sends) {
+      seg_rank.push_back(q);
+      seg_dst.push_back(px + (all[q].nloc + all[q].recv_off[me]) * A->es);
+      seg_flag.push_back(ps + kSyncData + me);
+      soff += A->send_counts[q];
+      seg_start.push_back((int32_t)soff);
+    }
+    if (recvs) {
+      src_rank.push_back(q);
+      src_ack.push_back(ps + kSyncAck + me);
+    }
+  }
+  A->nseg = (int32_t)seg_rank.size();
+  A->nsrc = (int32_t)src_rank.size();
+  auto up = [&](const void *h, size_t bytes, void **d) -> cudaError_t {
+    cudaError_t e = cudaMalloc(d, std::max<size_t>(bytes, 16));
+    if (e == cudaSuccess && bytes) e = cudaMemcpy(*d, h, bytes, cudaMemcpyHostToDevice);
+    return e;
+  };
+  HPCX_CUDA(ctx, up(seg_start.data(), seg_start.size() * 4, (void **)&A->d_seg_start));
+  HPCX_CUDA(ctx, up(seg_rank.data(), seg_rank.size() * 4, (void **)&A->d_seg_rank));
+  HPCX_CUDA(ctx, up(seg_dst.data(), seg_dst.size() * sizeof(void *), (void **)&A->d_seg_dst));
+  HPCX_CUDA(ctx, up(seg_flag.data(), seg_flag.size() * sizeof(void *), (void **)&A->d_seg_flag));
+  HPCX_CUDA(ctx, up(src_rank.data(), src_rank.size() * 4, (void **)&A->d_src_rank));
+  HPCX_CUDA(ctx, up(src_ack.data(), src_ack.size() * sizeof(void *), (void **)&A->d_src_ack));
+  A->epoch = 0;
+  A->transport = 1;
+  // Nobody may push before every rank's sync block is zeroed and its windows are open.
+  return hpcx_comm_barrier(ctx);
+}
+
+// Transport 1, all on the caller's stream:
+//   push kernel (gather + peer stores + flags) ; interior rows ; wait for the source ranks'
+//   flags ; boundary rows ; ack to the source ranks.
+static hpcx_status spmv_dist_peer(hpcx_csr A, char *xfull, void *y_local, cudaStream_t cs) {
+  hpcx_ctx ctx = A->ctx;
+  const uint32_t epoch = ++A->epoch;
+  hpcx_status rc;
+  if (A->nseg) {
+    int64_t longest = 0;
+    for (int q = 0; q < ctx->nranks; ++q) longest = std::max(longest, A->send_counts[q]);
+    dim3 grid((unsigned)std::min<int64_t>(std::max<int64_t>((longest + 255) / 256, 1), ctx->sm_count * 2),
+              (unsigned)A->nseg);
+    if (A->dtype == HPCX_F64)
+      push_boundary_x_kernel<double><<<grid, 256, 0, cs>>>((const double *)xfull, A->d_send_idx,
+                                                           A->d_seg_start, A->d_seg_rank, A->d_seg_dst,
+                                                           A->d_seg_flag, A->d_sync, epoch);
+    else
+      push_boundary_x_kernel<float><<<grid, 256, 0, cs>>>((const float *)xfull, A->d_send_idx,
+                                                          A->d_seg_start, A->d_seg_rank, A->d_seg_dst,
+                                                          A->d_seg_flag, A->d_sync, epoch);
+    rc = after_launch(ctx, "push_boundary_x_kernel");
+    if (rc != HPCX_OK) return rc;
+  }
+  rc = spmv_launch_blocks(A, A->d_blocks_int, (int64_t)A->h_blocks_int.size(), xfull, y_local, cs);
+  if (rc != HPCX_OK) return rc;
+  if (A->nsrc) {
+    halo_x_ready_kernel<<<1, 64, 0, cs>>>(A->d_sync, A->d_src_rank, A->nsrc, epoch);
+    rc = after_launch(ctx, "halo_x_ready_kernel");
+    if (rc != HPCX_OK) return rc;
+  }
+  rc = spmv_launch_blocks(A, A->d_blocks_bnd, (int64_t)A->h_blocks_bnd.size(), xfull, y_local, cs);
+  if (rc != HPCX_OK) return rc;
+  rc = spmv_launch_fixup_tables(A, A->d_long_row_dist, A->d_long_off_dist, A->nlong_dist, y_local, cs);
+  if (rc != HPCX_OK) return rc;
+  if (A->nsrc) {
+    halo_x_ack_kernel<<<1, 64, 0, cs>>>(A->d_src_ack, A->nsrc, epoch);
+    rc = after_launch(ctx, "halo_x_ack_kernel");
+  }
+  return rc;
+}
+
 hpcx_status hpcx_csr_x_buffer(hpcx_csr A, void **x_full) {
   if (!A || !x_full) return HPCX_INVALID_ARG;
   HPCX_REQUIRE(A->ctx, A->d_xfull != nullptr, "hpcx_csr_set_halo has not been called");
@@ -569,6 +764,17 @@ hpcx_status hpcx_spmv_dist(hpcx_csr A, const void *x_local, void *y_local, void 
     HPCX_CUDA(ctx, cudaMemcpyAsync(xfull, x_local, (size_t)A->nloc * A->es,
                                    cudaMemcpyDeviceToDevice, cs));
   hpcx_status rc;
+  if (A->transport == 1 && P > 1) {
+    rc = spmv_dist_peer(A, xfull, y_local, cs);
+    if (rc != HPCX_OK) return rc;
+    if (!stream) {
+      HPCX_CUDA(ctx, cudaStreamSynchronize(cs));
+      uint32_t err = 0;
+      HPCX_CUDA(ctx, cudaMemcpy(&err, A->d_sync + kSyncErr, 4, cudaMemcpyDeviceToHost));
+      if (err) return fail(ctx, HPCX_NCCL_ERROR, "timed out waiting for a neighbour's x-halo flag");
+    }
+    return HPCX_OK;
+  }
   if (A->nsend) {
     const int blocks = (int)std::min<int64_t>((A->nsend + 255) / 256, (int64_t)ctx->sm_count * 8);
     if (A->dtype == HPCX_F64)

@@ -23,6 +23,10 @@
 
 using namespace hpcx;
 
+namespace hpcx {
+void csr_close_peers(hpcx_csr A);  // dist.cu
+}
+
 namespace {
 
 constexpr int kThreads = 256;
@@ -386,6 +390,7 @@ void build_sell(hpcx_csr A, const int64_t *rp, const int32_t *col, const T *val,
 }
 
 void free_csr(hpcx_csr A) {
+  hpcx::csr_close_peers(A);
   cudaFree(A->d_row_ptr);
   cudaFree(A->d_col);
   cudaFree(A->d_val);

@@ -55,6 +55,19 @@ struct hpcx_csr_s {
   void *d_xfull = nullptr;  // [owned | halo]
   std::vector<hpcx::RowBlock> h_blocks_int, h_blocks_bnd;
   hpcx::RowBlock *d_blocks_int = nullptr, *d_blocks_bnd = nullptr;
+  // transport 1 (peer stores, hpcx_csr_halo_transport): see dist.cu
+  int32_t transport = 0;
+  uint32_t epoch = 0;          // distributed products issued through this handle
+  uint32_t *d_sync = nullptr;  // [0..63] data flags by source rank, [64..127] acks by destination
+                               // rank, [128] CTA counter, [129] error word
+  std::vector<void *> peer_open;  // cudaIpcOpenMemHandle bases to close
+  int32_t nseg = 0, nsrc = 0;     // destination / source neighbours
+  int32_t *d_seg_start = nullptr; // nseg + 1 offsets into send_idx
+  int32_t *d_seg_rank = nullptr;  // destination rank of each segment
+  void **d_seg_dst = nullptr;     // where each segment lands in the destination's [owned | halo] x
+  uint32_t **d_seg_flag = nullptr;// the destination's data flag for this rank
+  int32_t *d_src_rank = nullptr;  // ranks this one receives from
+  uint32_t **d_src_ack = nullptr; // their ack word for this rank
   int64_t nlong_dist = 0;  // long-row tables in the numbering of the interior/boundary blocks
   int32_t *d_long_row_dist = nullptr, *d_long_off_dist = nullptr;
 };

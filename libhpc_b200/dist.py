@@ -61,11 +61,14 @@ class HaloPlan:
             self.h = None
 
 
-def distributed_csr(ctx: Context, local: dict, dtype, **opts) -> DeviceCsr:
-    """Device matrix of this rank's block from the tables of csr_localize (+ halo lists)."""
+def distributed_csr(ctx: Context, local: dict, dtype, transport: int = 0, **opts) -> DeviceCsr:
+    """Device matrix of this rank's block from the tables of csr_localize (+ halo lists).
+    transport 1 selects the fused peer-store exchange (hpcx_csr_halo_transport)."""
     A = CsrMatrix(local["local_row_ptr"], local["local_col"],
                   np.ascontiguousarray(local["values"], dtype=dtype),
                   ncols=local["nloc"] + local["nhalo"])
     D = DeviceCsr(ctx, A, **opts)
     D.set_halo(local)
+    if transport:
+        D.halo_transport(transport)
     return D

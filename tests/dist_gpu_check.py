@@ -81,17 +81,24 @@ def main():
         A = hp.CsrMatrix(rp, col, val)
         bounds = hp.partition_rows(n, rp, world, mode)
         L = hp.csr_localize(A, bounds, rank)
-        D = hd.distributed_csr(ctx, L, val.dtype)
         r0, r1 = int(bounds[rank]), int(bounds[rank + 1])
-        xd = torch.from_numpy(x[r0:r1].copy()).cuda()
-        yd = torch.full((r1 - r0,), float("nan"), dtype=xd.dtype, device="cuda")
-        torch.cuda.synchronize()
-        for _ in range(3):
-            D.spmv_dist(xd, yd)
-        y = yd.cpu().numpy()
         tol = 1e-12 if val.dtype == np.float64 else 1e-5
-        assert_spmv_close(y, y_ref[r0:r1], mag[r0:r1], tol)
-        D.destroy()
+        for transport in (0, 1):  # NCCL send/recv, fused peer stores
+            D = hd.distributed_csr(ctx, L, val.dtype, transport=transport)
+            xd = torch.from_numpy(x[r0:r1].copy()).cuda()
+            yd = torch.full((r1 - r0,), float("nan"), dtype=xd.dtype, device="cuda")
+            torch.cuda.synchronize()
+            for _ in range(3):
+                D.spmv_dist(xd, yd)
+            assert_spmv_close(yd.cpu().numpy(), y_ref[r0:r1], mag[r0:r1], tol)
+            # a different x through the same handle: the halo slots must carry the NEW values
+            x2 = synth.field(43, n, val.dtype)
+            xd.copy_(torch.from_numpy(x2[r0:r1].copy()))
+            torch.cuda.synchronize()
+            D.spmv_dist(xd, yd)
+            assert_spmv_close(yd.cpu().numpy(), oracle.spmv(rp, col, val, x2)[r0:r1],
+                              oracle.spmv_abs(rp, col, val, x2)[r0:r1], tol)
+            D.destroy()
 
     if world > 1:
         hd.barrier(ctx)
