@@ -1,0 +1,224 @@
+// host_check.cpp — exercises the C++ face of libhpcx (include/hpcx/*.hpp).
+//
+//   host_check index            prints strides / totals / offsets / at() verdicts of
+//                               hpc::HPCHighDimensionFlatArray for tests/test_cpp_host.py to compare
+//                               with the reference header (oracle/_ref) and the golden file
+//   host_check csr              prints FNV-1a digests of the CsrMatrix builders' arrays
+//   host_check gpu              runs the sweeps and the product on cuda:0 through the C++ entry
+//                               points and compares with reference-style loop nests written here
+//
+// Built by tests/test_cpp_host.py with g++ -std=c++17 -fopenmp -Iinclude -Llibhpc_b200 -lhpcx.
+#include <cinttypes>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include <hpcx/CsrMatrix.hpp>
+#include <hpcx/HPCHighDimensionFlatArray.hpp>
+#include <hpcx/Stencil.hpp>
+
+static uint64_t fnv1a(const void *p, size_t n, uint64_t h = 1469598103934665603ull) {
+  const unsigned char *b = static_cast<const unsigned char *>(p);
+  for (size_t i = 0; i < n; ++i) h = (h ^ b[i]) * 1099511628211ull;
+  return h;
+}
+
+// Exposes the protected helpers the reference header also keeps protected.
+template <std::size_t D, typename T, std::size_t Lo, std::size_t Hi>
+struct Probe : hpc::HPCHighDimensionFlatArray<D, T, Lo, Hi> {
+  using Base = hpc::HPCHighDimensionFlatArray<D, T, Lo, Hi>;
+  using Base::Base;
+  static void layout(const std::array<std::size_t, D> &dims) {
+    const auto st = Base::compute_stride_and_total(dims);
+    std::printf("layout D=%zu lo=%zu hi=%zu dims", D, Lo, Hi);
+    for (auto d : dims) std::printf(" %zu", d);
+    std::printf(" stride");
+    for (auto s : st.first) std::printf(" %zu", s);
+    std::printf(" total %zu\n", st.second);
+  }
+};
+
+template <std::size_t Lo, std::size_t Hi>
+static void probe2(std::size_t ny, std::size_t nx) {
+  Probe<2, float, Lo, Hi>::layout({ny, nx});
+  Probe<2, float, Lo, Hi> a(ny, nx);
+  const float *base = a.data();
+  for (std::intptr_t y = -(std::intptr_t)Lo - 1; y <= (std::intptr_t)(ny + Hi); ++y)
+    for (std::intptr_t x = -(std::intptr_t)Lo - 1; x <= (std::intptr_t)(nx + Hi); ++x) {
+      long long off = -1;
+      try {
+        off = &a.at({y, x}) - base;
+      } catch (const std::out_of_range &) {
+        off = -1;  // the reference throws std::out_of_range here
+      }
+      std::printf("at2 lo=%zu hi=%zu dims %zu %zu idx %td %td off %lld\n", Lo, Hi, ny, nx, y, x, off);
+    }
+}
+
+template <std::size_t Lo, std::size_t Hi>
+static void probe3(std::size_t nz, std::size_t ny, std::size_t nx) {
+  Probe<3, double, Lo, Hi>::layout({nz, ny, nx});
+  Probe<3, double, Lo, Hi> a(nz, ny, nx);
+  const double *base = a.data();
+  for (std::intptr_t z = -(std::intptr_t)Lo; z < (std::intptr_t)(nz + Hi); ++z)
+    for (std::intptr_t y = -(std::intptr_t)Lo; y < (std::intptr_t)(ny + Hi); ++y)
+      for (std::intptr_t x = -(std::intptr_t)Lo; x < (std::intptr_t)(nx + Hi); ++x)
+        std::printf("op3 lo=%zu hi=%zu dims %zu %zu %zu idx %td %td %td off %lld\n", Lo, Hi, nz, ny, nx, z,
+                    y, x, (long long)(&a(z, y, x) - base));
+}
+
+static int run_index() {
+  probe2<0, 0>(3, 4);
+  probe2<8, 8>(4, 5);
+  probe2<1, 3>(2, 7);
+  probe3<1, 1>(2, 3, 4);
+  probe3<2, 1>(3, 2, 2);
+  Probe<1, float, 2, 2>::layout({9});
+  Probe<2, float, 8, 8>::layout({8192, 8192});
+  Probe<3, float, 1, 1>::layout({512, 512, 512});
+  hpc::HPCHighDimensionFlatArray<2, float, 8> z(4, 4);
+  bool zero = true;
+  for (std::size_t i = 0; i < z.size(); ++i) zero = zero && z.data()[i] == 0.0f;
+  std::printf("value_initialised %d\n", zero ? 1 : 0);
+  return 0;
+}
+
+template <typename M>
+static void digest(const char *name, const M &m) {
+  std::printf("csr %s nrows %zu nnz %zu row_ptr %016" PRIx64 " col %016" PRIx64 " val %016" PRIx64 " bytes %zu\n",
+              name, m.nrows(), m.nnz(), fnv1a(m.row_ptr(), (m.nrows() + 1) * sizeof(*m.row_ptr())),
+              fnv1a(m.col_idx(), m.nnz() * 4), fnv1a(m.values(), m.nnz() * sizeof(*m.values())),
+              m.algorithmic_bytes());
+}
+
+static int run_csr() {
+  digest("laplace2d_64x48_f64_i32", sparse::CsrMatrix<double, int32_t>::laplace2d(64, 48));
+  digest("laplace2d_1024_f64_i32", sparse::CsrMatrix<double, int32_t>::laplace2d(1024, 1024));
+  digest("op27_12_f64_i64", sparse::CsrMatrix<double, int64_t>::op27(12));
+  using Trip = std::tuple<std::int64_t, std::int32_t, float>;
+  std::vector<Trip> t = {{2, 1, 1.f}, {0, 3, 2.f}, {2, 1, 0.5f}, {1, 0, -1.f}, {0, 0, 4.f}, {2, 1, 0.25f}};
+  auto m = sparse::CsrMatrix<float, int32_t>::from_triplets(3, 4, t);
+  std::printf("triplets nnz %zu rp %d %d %d %d col %d %d %d %d val %g %g %g %g\n", m.nnz(), m.row_ptr()[0],
+              m.row_ptr()[1], m.row_ptr()[2], m.row_ptr()[3], m.col_idx()[0], m.col_idx()[1], m.col_idx()[2],
+              m.col_idx()[3], m.values()[0], m.values()[1], m.values()[2], m.values()[3]);
+  try {
+    std::vector<Trip> bad = {{5, 0, 1.f}};
+    (void)sparse::CsrMatrix<float, int32_t>::from_triplets(3, 4, bad);
+    std::printf("triplets_oob no_throw\n");
+  } catch (const std::out_of_range &) {
+    std::printf("triplets_oob out_of_range\n");
+  }
+  return 0;
+}
+
+static float frand(uint64_t &s) {
+  s = s * 6364136223846793005ull + 1442695040888963407ull;
+  return (float)((s >> 40) & 0xFFFF) / 65536.0f - 0.5f;
+}
+
+static int run_gpu() {
+  int bad = 0;
+  hpcx::Context ctx(0);
+  uint64_t seed = 7;
+  {  // the reference's sweeps: BM_x_blur / BM_y_blur loop nests (test_hpc_benchmark.cpp:354-368, 444-457)
+    constexpr int nblur = 8;
+    const int ny = 96, nx = 256;
+    hpc::HPCHighDimensionFlatArray<2, float, nblur> a(ny, nx);
+    hpc::HPCHighDimensionFlatArray<2, float> b(ny, nx), want(ny, nx);
+    for (std::size_t i = 0; i < a.size(); ++i) a.data()[i] = frand(seed);
+    for (int axis = 0; axis < 2; ++axis) {
+#pragma omp parallel for collapse(2)
+      for (int y = 0; y < ny; ++y)
+        for (int x = 0; x < nx; ++x) {
+          float res = 0.0f;
+          for (int t = -nblur; t <= nblur; ++t) res += axis == 1 ? a(y, x + t) : a(y + t, x);
+          want(y, x) = res;
+        }
+      hpc::stencil_sweep(ctx, a, b, hpc::Box1D{axis, nblur});
+      const int same = std::memcmp(b.data(), want.data(), b.size() * sizeof(float)) == 0;
+      std::printf("box axis %d bit_exact %d\n", axis, same);
+      bad += !same;
+    }
+    try {
+      hpc::stencil_sweep(ctx, a, b, hpc::Box1D{1, nblur + 1});  // radius beyond the ghost cells
+      std::printf("box_radius no_throw\n");
+      ++bad;
+    } catch (const std::system_error &e) {
+      std::printf("box_radius system_error %s\n", e.what());
+    }
+  }
+  {  // 7-point Jacobi, two steps
+    const int nz = 20, ny = 18, nx = 130;
+    hpc::HPCHighDimensionFlatArray<3, float, 1> u(nz, ny, nx), v(nz, ny, nx), w0(nz, ny, nx), w1(nz, ny, nx);
+    for (std::size_t i = 0; i < u.size(); ++i) u.data()[i] = v.data()[i] = w0.data()[i] = w1.data()[i] = frand(seed);
+    auto sweep = [&](auto &src, auto &dst) {
+      for (int z = 0; z < nz; ++z)
+        for (int y = 0; y < ny; ++y)
+          for (int x = 0; x < nx; ++x) {
+            float s = src(z - 1, y, x) + src(z, y - 1, x);
+            s = s + src(z, y, x - 1);
+            s = s + src(z, y, x + 1);
+            s = s + src(z, y + 1, x);
+            s = s + src(z + 1, y, x);
+            dst(z, y, x) = s * (1.0f / 6.0f);
+          }
+    };
+    sweep(w0, w1);
+    sweep(w1, w0);  // newest iterate in w0
+    hpc::stencil_sweep(ctx, u, v, hpc::Jacobi7{2});
+    const int same = std::memcmp(v.data(), w0.data(), v.size() * sizeof(float)) == 0 &&
+                     std::memcmp(u.data(), w1.data(), u.size() * sizeof(float)) == 0;
+    std::printf("jacobi7 bit_exact %d\n", same);
+    bad += !same;
+  }
+  {  // SpMV, 5-point Laplacian (rows of <= 5 entries: the device order is the CPU order)
+    auto A = sparse::CsrMatrix<double>::laplace2d(200, 300);
+    std::vector<double> x(A.ncols()), y, want(A.nrows());
+    for (auto &v : x) v = frand(seed);
+    for (std::size_t i = 0; i < A.nrows(); ++i) {
+      double s = 0.0;
+      for (auto p = A.row_ptr()[i]; p < A.row_ptr()[i + 1]; ++p) {
+        const double prod = A.values()[p] * x[A.col_idx()[p]];
+        s = s + prod;
+      }
+      want[i] = s;
+    }
+    sparse::spmv(ctx, A, x, y);
+    double err = 0, mag = 0;
+    for (std::size_t i = 0; i < y.size(); ++i) {
+      err = std::fmax(err, std::fabs(y[i] - want[i]));
+      mag = std::fmax(mag, std::fabs(want[i]));
+    }
+    std::printf("spmv rel_err %.3e\n", err / mag);
+    bad += !(err <= 1e-12 * mag);
+    sparse::DeviceCsr<double> dA(ctx, A);
+    std::vector<double> y2;
+    sparse::spmv(dA, x, y2);
+    bad += std::memcmp(y.data(), y2.data(), y.size() * 8) != 0;
+    try {
+      std::vector<double> shortx(3);
+      sparse::spmv(dA, shortx, y2);
+      ++bad;
+    } catch (const std::out_of_range &) {
+      std::printf("spmv_short_x out_of_range\n");
+    }
+  }
+  std::printf("launches %lld\n", (long long)ctx.launchCount());
+  std::printf(bad ? "CPP GPU FAIL\n" : "CPP GPU OK\n");
+  return bad;
+}
+
+int main(int argc, char **argv) {
+  const std::string mode = argc > 1 ? argv[1] : "index";
+  try {
+    if (mode == "index") return run_index();
+    if (mode == "csr") return run_csr();
+    if (mode == "gpu") return run_gpu();
+  } catch (const std::exception &e) {
+    std::printf("exception %s\n", e.what());
+    return 2;
+  }
+  return 1;
+}
