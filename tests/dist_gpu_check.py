@@ -42,6 +42,13 @@ def main():
         full = oracle.fill((nz + 2) * (ny + 2) * (nx + 2), 7, np.float32)
         want = oracle.jacobi7(full, nz, ny, nx, 1, 1, steps).reshape(nz + 2, ny + 2, nx + 2)
         b = hp.partition_slabs(nz, world)
+        if int(np.diff(b).min()) < 1:
+            # the static chunking idiom leaves trailing ranks without planes when nz < chunk*world;
+            # the transport requires >= 1 plane per slab (HPCX_INVALID_ARG otherwise), so scale nz up
+            nz = nz * world
+            full = oracle.fill((nz + 2) * (ny + 2) * (nx + 2), 7, np.float32)
+            want = oracle.jacobi7(full, nz, ny, nx, 1, 1, steps).reshape(nz + 2, ny + 2, nx + 2)
+            b = hp.partition_slabs(nz, world)
         z0, z1 = int(b[rank]), int(b[rank + 1])
         slab = np.ascontiguousarray(full.reshape(nz + 2, ny + 2, nx + 2)[z0:z1 + 2]).ravel()
         ga = hp.DeviceGrid(ctx, (z1 - z0, ny, nx), np.float32, 1)
