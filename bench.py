@@ -295,6 +295,8 @@ def run_ours(args, rank: int, world: int, local: int):
     checksum = float(np.abs(y_pin.numpy()).sum())
 
     extra = stencil_extra(ctx, torch, stream, world, rank, barrier, max_over_ranks, hp, hd, synth)
+    if args.configs == "all":
+        extra.update(sparse_extra(args, ctx, torch, stream, world, rank, barrier, max_over_ranks, hp, hd, synth))
     if world > 1:
         # the same product with the NCCL send/recv exchange, for comparison
         D.halo_transport(0)
@@ -413,6 +415,118 @@ def stencil_extra(ctx, torch, stream, world, rank, barrier, max_over_ranks, hp, 
     return out
 
 
+def sparse_extra(args, ctx, torch, stream, world, rank, barrier, max_over_ranks, hp, hd, synth):
+    """The other SpMV configs of BASELINE.json as `extra` entries.
+    C4 (configs[3]): 27-point operator on 256^3, fp64, row-partitioned into z-slab blocks with
+    an x-halo of one plane (65,536 doubles) per neighbour — STRONG scaling (global size fixed).
+    C5 (configs[4]): R-MAT scale 24, average degree 16, fp32, built on the device; N = 1 only."""
+    out = {}
+    peak, _ = measured_peak()
+    n = 256
+    zb = hp.partition_slabs(n, world)
+    t = time.time()
+    L = synth.op27_slab_local(n, int(zb[rank]), int(zb[rank + 1]))
+    L["recv_counts"], L["send_counts"] = synth.slab_counts(L, world, rank, n * n)
+    L["local_row_ptr"] = L["local_row_ptr"].astype(np.int32)
+    nloc = L["nloc"]
+    A = hp.CsrMatrix(L["local_row_ptr"], L["local_col"], L["values"], ncols=nloc + L["nhalo"])
+    D = hp.DeviceCsr(ctx, A)
+    log(f"[rank {rank}] C4 slab: {nloc} rows, {L['nnz_loc']} nnz built + uploaded in {time.time() - t:.1f}s")
+    yd = torch.empty(nloc, dtype=torch.float64, device="cuda")
+    xd = torch.ones(nloc + L["nhalo"], dtype=torch.float64, device="cuda")
+    torch.cuda.synchronize()
+    if world > 1:
+        D.set_halo(L)
+        D.halo_transport(1)
+        xfull = D.x_buffer()
+        ctx.memcpy((xfull, hp.MEM_DEVICE), xd, nloc * 8)
+        x_arg = (xfull, hp.MEM_DEVICE)
+        step = lambda: D.spmv_dist(x_arg, yd, stream)  # noqa: E731
+    else:
+        step = lambda: D.spmv(xd, yd, stream)  # noqa: E731
+    # property check (no oracle): row sums of the operator are 27 - (entries in the row)
+    step()
+    stream.synchronize()
+    want = 27.0 - torch.from_numpy(np.diff(L["local_row_ptr"]).astype(np.float64)).cuda()
+    if not torch.equal(yd, want):
+        raise SystemExit(f"[rank {rank}] bench.py: C4 A*1 does not match the closed form")
+    x = torch.empty(nloc, dtype=torch.float64, device="cuda")
+    hp.synth_field(ctx, 42, nloc, x, np.float64, first=int(zb[rank]) * n * n)
+    if world > 1:
+        ctx.memcpy((xfull, hp.MEM_DEVICE), x, nloc * 8)
+    else:
+        xd[:nloc].copy_(x)
+    torch.cuda.synchronize()
+    with torch.cuda.stream(stream):
+        for _ in range(3):
+            step()
+        n0 = ctx.launch_count()
+        dt, _, _ = time_steps(torch, stream, step, args.steps, barrier)
+        launches = ctx.launch_count() - n0
+    dt = max_over_ranks(dt)
+    nnz_total = (3 * n - 2) ** 3
+    gbytes = algorithmic_bytes(n ** 3, nnz_total)
+    rbytes = algorithmic_bytes(nloc, L["nnz_loc"])
+    out["c4_op27_256cubed_fp64"] = {
+        "metric": METRIC, "value": gbytes * args.steps / dt / 1e9, "unit": UNIT, "scaling": "strong",
+        "ms_per_step": dt / args.steps * 1e3, "rows": n ** 3, "nnz": nnz_total, "gpu_launches": launches,
+        "partition": f"{world} z-slab row blocks, x-halo {n * n} doubles per neighbour" +
+                     (" (peer stores + flags)" if world > 1 else ""),
+        "roofline": {"bound": "hbm", "achieved": rbytes * args.steps / dt / 1e9, "peak": peak, "unit": "GB/s",
+                     "frac": rbytes * args.steps / dt / 1e9 / peak, "algorithmic_bytes_per_launch": rbytes,
+                     "note": "rank 0's bytes / max-over-ranks step time"}}
+    D.destroy()
+    del xd, yd, x, A, L
+    if world > 1:
+        return out
+
+    scale = 24
+    t = time.time()
+    arrs = hp.synth_rmat_csr(ctx, scale, 16, 24, 4)
+    R = hp.DeviceCsr.from_device_arrays(ctx, arrs)
+    log(f"C5 R-MAT scale {scale}: {arrs.nnz} nnz after merging, generated + assembled + row-blocked "
+        f"on the device in {time.time() - t:.1f}s")
+    nr = 1 << scale
+    rp, _, val = arrs.download()
+    arrs.destroy()
+    x = torch.ones(nr, dtype=torch.float32, device="cuda")
+    y = torch.empty(nr, dtype=torch.float32, device="cuda")
+    torch.cuda.synchronize()
+    R.spmv(x, y, stream)
+    stream.synchronize()
+    # property check (no oracle): A*1 = row sums, against float64 prefix sums of the values
+    cs = np.concatenate(([0.0], np.cumsum(val, dtype=np.float64)))
+    ca = np.concatenate(([0.0], np.cumsum(np.abs(val), dtype=np.float64)))
+    rs, ra = cs[rp[1:]] - cs[rp[:-1]], ca[rp[1:]] - ca[rp[:-1]]
+    err = np.abs(y.cpu().numpy().astype(np.float64) - rs)
+    if not np.all(err <= 1e-5 * ra + 1e-7 * np.abs(ca[-1]) / len(val)):
+        raise SystemExit("bench.py: C5 A*1 does not match the row sums within 1e-5")
+    lens = np.diff(rp)
+    del cs, ca, rs, ra, val
+    hp.synth_field(ctx, 42, nr, x, np.float32)
+    torch.cuda.synchronize()
+    step = lambda: R.spmv(x, y, stream)  # noqa: E731
+    with torch.cuda.stream(stream):
+        for _ in range(3):
+            step()
+        n0 = ctx.launch_count()
+        dt, _, _ = time_steps(torch, stream, step, args.steps, barrier)
+        launches = ctx.launch_count() - n0
+    rbytes = algorithmic_bytes(nr, R.nnz, 4)
+    bins = R.row_bins()
+    out["c5_rmat_scale24_fp32"] = {
+        "metric": METRIC, "value": rbytes * args.steps / dt / 1e9, "unit": UNIT,
+        "ms_per_step": dt / args.steps * 1e3, "rows": nr, "nnz": int(R.nnz), "gpu_launches": launches,
+        "row_length": {"max": int(lens.max()), "mean": float(lens.mean()), "empty_rows": int((lens == 0).sum()),
+                       "ceil_log2_bins": [int(b) for b in bins[:int(np.flatnonzero(bins)[-1]) + 1]]},
+        "roofline": {"bound": "hbm", "achieved": rbytes * args.steps / dt / 1e9, "peak": peak, "unit": "GB/s",
+                     "frac": rbytes * args.steps / dt / 1e9 / peak, "algorithmic_bytes_per_launch": rbytes,
+                     "note": "8 B/nnz + 12 B/row: x counted as compulsory only (4 B/row); the gather's "
+                             "real DRAM traffic is in profiles/"}}
+    R.destroy()
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -420,6 +534,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--configs", default="all", choices=["all", "headline"],
+                    help="all: also time configs[3] (27-point 256^3) and configs[4] (R-MAT) as extras")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", 0))
     world = int(os.environ.get("WORLD_SIZE", 1))

@@ -211,6 +211,32 @@ HPCX_API hpcx_status hpcx_csr_sell_info(hpcx_csr A, int64_t *nslices, int64_t *p
 HPCX_API hpcx_status hpcx_csr_sell_download(hpcx_csr A, int32_t *perm, int64_t *slice_ptr,
                                             int32_t *slice_len, int32_t *col, void *val);
 
+/* Device-side assembly of a CSR matrix from an edge (COO) list: entries sorted by
+ * (row, col, position in the list), equal (row, col) merged by adding their values in list
+ * order (one rounding per add), exactly the CPU builder's rule.  rows/cols/vals live in
+ * `mem` (HPCX_MEM_HOST or device/managed).  The three result arrays are DEVICE memory owned
+ * by the caller (hpcx_device_free); hand them to hpcx_csr_create with mem = HPCX_MEM_DEVICE.
+ * nedges < 2^31; row_ptr is written with idx_bytes (4 or 8) per entry. */
+typedef struct {
+  int64_t nnz;
+  void *row_ptr;
+  int32_t *col_idx;
+  void *values;
+} hpcx_csr_arrays;
+HPCX_API hpcx_status hpcx_csr_from_coo(hpcx_ctx ctx, int64_t nrows, int64_t nedges,
+                                       const int32_t *rows, const int32_t *cols,
+                                       const void *vals, int32_t dtype, int32_t mem,
+                                       int32_t idx_bytes, hpcx_csr_arrays *out);
+/* Counter-based generators of the synthetic configs, on the device (bit-identical to the
+ * host generators).  R-MAT edge k: `scale` quadrant choices with
+ * (a,b,c,d) = (.57,.19,.19,.05) from u(seed, k*scale + level), value (float)(2u(seed+1,k)-1).
+ * Field: out[i] = 2u(seed, first+i) - 1 in dtype. */
+HPCX_API hpcx_status hpcx_synth_rmat_coo(hpcx_ctx ctx, int32_t scale, int64_t nedges,
+                                         uint64_t seed, int32_t *rows_dev, int32_t *cols_dev,
+                                         float *vals_dev);
+HPCX_API hpcx_status hpcx_synth_field(hpcx_ctx ctx, uint64_t seed, int64_t first, int64_t n,
+                                      int32_t dtype, void *out_dev);
+
 /* ------------------------------------------------- partitioner + halo maps (a12) */
 /* Contiguous row blocks: bounds[p] .. bounds[p+1] for p in [0, nparts).
  * mode 0: balanced by rows with the reference's static chunking idiom

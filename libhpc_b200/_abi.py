@@ -46,6 +46,11 @@ class CsrOpts(C.Structure):
                 ("reserved", C.c_int32 * 3)]
 
 
+class CsrArrays(C.Structure):
+    _fields_ = [("nnz", C.c_int64), ("row_ptr", C.c_void_p), ("col_idx", C.c_void_p),
+                ("values", C.c_void_p)]
+
+
 class HaloSizes(C.Structure):
     _fields_ = [("nloc", C.c_int64), ("nnz_loc", C.c_int64), ("nhalo", C.c_int64),
                 ("nsend", C.c_int64)]
@@ -86,6 +91,9 @@ PROTOTYPES = {
     "hpcx_csr_row_bins": (_i32, [_vp, _vp]),
     "hpcx_csr_sell_info": (_i32, [_vp, _P(_i64), _P(_i64), _P(_i32), _P(_i32)]),
     "hpcx_csr_sell_download": (_i32, [_vp, _vp, _vp, _vp, _vp, _vp]),
+    "hpcx_csr_from_coo": (_i32, [_vp, _i64, _i64, _vp, _vp, _vp, _i32, _i32, _i32, _P(CsrArrays)]),
+    "hpcx_synth_rmat_coo": (_i32, [_vp, _i32, _i64, C.c_uint64, _vp, _vp, _vp]),
+    "hpcx_synth_field": (_i32, [_vp, C.c_uint64, _i64, _i64, _i32, _vp]),
     "hpcx_partition_rows": (_i32, [_i64, _vp, _i32, _i32, _i32, _vp]),
     "hpcx_partition_slabs": (_i32, [_i64, _i32, _vp]),
     "hpcx_csr_localize": (_i32, [_i64, _vp, _i32, _vp, _vp, _i32, _i32, _P(HaloSizes), _vp, _vp,

@@ -340,6 +340,30 @@ class DeviceCsr:
         self.h = h
         self.nrows, self.ncols, self.nnz, self.dtype = A.nrows, A.ncols, A.nnz, A.dtype
         self.kernel = kernel
+        self._rp_dtype = A.row_ptr.dtype
+
+    @classmethod
+    def from_device_arrays(cls, ctx: Context, arrays: "DeviceCsrArrays", ncols: int | None = None,
+                           kernel: int = SPMV_STREAM, tile_nnz: int = 0, sell_c: int = 0,
+                           sell_sigma: int = 0, lanes_per_row: int = 0) -> "DeviceCsr":
+        """Matrix whose CSR arrays already live on the device (csr_from_coo)."""
+        self = cls.__new__(cls)
+        self.ctx, self.host = ctx, None
+        ncols = arrays.nrows if ncols is None else int(ncols)
+        d = _abi.CsrDesc(arrays.nrows, ncols, arrays.nnz, arrays.row_ptr, arrays.idx_bytes,
+                         _dtype_code(arrays.dtype), arrays.col_idx, arrays.values, MEM_DEVICE, 0)
+        o = _abi.CsrOpts(kernel, tile_nnz, sell_c, sell_sigma, lanes_per_row)
+        h = C.c_void_p()
+        ctx.check(ctx.lib.hpcx_csr_create(ctx.h, C.byref(d), C.byref(o), C.byref(h)))
+        self.h = h
+        self.nrows, self.ncols, self.nnz, self.dtype = arrays.nrows, ncols, arrays.nnz, arrays.dtype
+        self.kernel = kernel
+        self._rp_dtype = np.dtype(np.int32 if arrays.idx_bytes == 4 else np.int64)
+        return self
+
+    def algorithmic_bytes(self) -> int:
+        es = np.dtype(self.dtype).itemsize
+        return self.nnz * (es + 4) + self.nrows * (4 + 2 * es) + 4
 
     def spmv(self, x, y, stream=None):
         """y = A*x; x and y may be numpy arrays (host) or CUDA tensors / (ptr, mem) pairs."""
@@ -349,7 +373,7 @@ class DeviceCsr:
         return y
 
     def download(self):
-        rp = np.empty(self.nrows + 1, dtype=self.host.row_ptr.dtype)
+        rp = np.empty(self.nrows + 1, dtype=self._rp_dtype)
         col = np.empty(self.nnz, dtype=np.int32)
         val = np.empty(self.nnz, dtype=self.dtype)
         self.ctx.check(self.ctx.lib.hpcx_csr_download(self.h, rp.ctypes.data, col.ctypes.data,
@@ -408,6 +432,75 @@ class DeviceCsr:
         if self.h:
             self.ctx.lib.hpcx_csr_destroy(self.h)
             self.h = None
+
+
+class DeviceCsrArrays:
+    """CSR arrays in device memory produced by hpcx_csr_from_coo (owned here until destroy())."""
+
+    def __init__(self, ctx: Context, nrows: int, idx_bytes: int, dtype, raw: "_abi.CsrArrays"):
+        self.ctx, self.nrows, self.idx_bytes, self.dtype = ctx, int(nrows), idx_bytes, np.dtype(dtype)
+        self.nnz, self.row_ptr, self.col_idx, self.values = raw.nnz, raw.row_ptr, raw.col_idx, raw.values
+
+    def download(self):
+        rp = np.empty(self.nrows + 1, dtype=np.int32 if self.idx_bytes == 4 else np.int64)
+        col = np.empty(self.nnz, dtype=np.int32)
+        val = np.empty(self.nnz, dtype=self.dtype)
+        self.ctx.memcpy(rp, (self.row_ptr, MEM_DEVICE), rp.nbytes)
+        if self.nnz:
+            self.ctx.memcpy(col, (self.col_idx, MEM_DEVICE), col.nbytes)
+            self.ctx.memcpy(val, (self.values, MEM_DEVICE), val.nbytes)
+        return rp, col, val
+
+    def destroy(self):
+        for name in ("row_ptr", "col_idx", "values"):
+            p = getattr(self, name)
+            if p:
+                self.ctx.device_free(p)
+                setattr(self, name, None)
+
+
+def csr_from_coo(ctx: Context, nrows: int, rows, cols, vals, idx_bytes: int = 4,
+                 nedges: int | None = None, dtype=None) -> DeviceCsrArrays:
+    """Device assembly of a CSR matrix from an edge list (hpcx_csr_from_coo): sort by
+    (row, col, list position), merge duplicates by adding in list order.  rows/cols/vals are
+    numpy arrays (host), CUDA tensors or (ptr, mem) pairs (then give nedges and dtype)."""
+    pr, mr = _ptr(rows)
+    pc, mc = _ptr(cols)
+    pv, mv = _ptr(vals)
+    if not (mr == mc == mv):
+        raise ValueError("rows, cols and vals must live in the same memory space")
+    if isinstance(rows, np.ndarray) and (rows.dtype != np.int32 or cols.dtype != np.int32):
+        raise TypeError("rows and cols must be int32")
+    if nedges is None:
+        nedges = len(rows)
+    if dtype is None:
+        dtype = vals.dtype if isinstance(vals, np.ndarray) else {"torch.float32": np.float32,
+                                                                  "torch.float64": np.float64}[str(vals.dtype)]
+    raw = _abi.CsrArrays()
+    ctx.check(ctx.lib.hpcx_csr_from_coo(ctx.h, nrows, nedges, pr, pc, pv, _dtype_code(dtype), mr,
+                                        idx_bytes, C.byref(raw)))
+    return DeviceCsrArrays(ctx, nrows, idx_bytes, dtype, raw)
+
+
+def synth_rmat_csr(ctx: Context, scale: int, edge_factor: int = 16, seed: int = 24,
+                   idx_bytes: int = 4) -> DeviceCsrArrays:
+    """C5 on the device: R-MAT edges (hpcx_synth_rmat_coo) assembled by hpcx_csr_from_coo.
+    Bit-identical to synth.rmat / the oracle's orc_rmat_csr."""
+    ne = (1 << scale) * edge_factor
+    r, c, v = ctx.device_alloc(4 * ne), ctx.device_alloc(4 * ne), ctx.device_alloc(4 * ne)
+    try:
+        ctx.check(ctx.lib.hpcx_synth_rmat_coo(ctx.h, scale, ne, seed, r, c, v))
+        return csr_from_coo(ctx, 1 << scale, (r, MEM_DEVICE), (c, MEM_DEVICE), (v, MEM_DEVICE),
+                            idx_bytes, nedges=ne, dtype=np.float32)
+    finally:
+        for p in (r, c, v):
+            ctx.device_free(p)
+
+
+def synth_field(ctx: Context, seed: int, n: int, out, dtype, first: int = 0):
+    """out[i] = 2u(seed, first+i) - 1 generated on the device (out: CUDA tensor or (ptr, mem))."""
+    ctx.check(ctx.lib.hpcx_synth_field(ctx.h, seed, first, n, _dtype_code(dtype), _ptr(out)[0]))
+    return out
 
 
 def spmv(ctx: Context, A: CsrMatrix, x: np.ndarray, y: np.ndarray | None = None, **opts):

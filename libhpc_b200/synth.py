@@ -202,3 +202,38 @@ def slab_counts(local: dict, nparts: int, rank: int, nx: int):
     if local["has_hi"]:
         recv[rank + 1] = send[rank + 1] = nx
     return recv, send
+
+
+def op27_slab_local(n: int, z0: int, z1: int, dtype=np.float64, planes_per_chunk: int = 16):
+    """Rank-local view of planes [z0, z1) of the n^3 27-point operator (C4) without forming the
+    global matrix: the tables hpcx_csr_localize yields for the row block [z0*n^2, z1*n^2).
+    Halo = plane z0-1 (owned by the rank below) then plane z1 (rank above)."""
+    pl = n * n
+    nloc = (z1 - z0) * pl
+    has_lo, has_hi = z0 > 0, z1 < n
+    rps, cols, vals = [np.zeros(1, np.int64)], [], []
+    base = 0
+    for a in range(z0, z1, planes_per_chunk):
+        b = min(z1, a + planes_per_chunk)
+        rp, c, v = op27(n, dtype, np.int64, a, b)
+        c = c.astype(np.int64) - z0 * pl  # owned -> [0, nloc); below -> [-pl, 0); above -> [nloc, nloc+pl)
+        c = np.where(c < 0, c + pl + nloc, np.where(c >= nloc, c + int(has_lo) * pl, c))
+        cols.append(c.astype(np.int32))
+        vals.append(v)
+        rps.append(rp[1:] + base)
+        base += int(rp[-1])
+    P = np.arange(pl, dtype=np.int32)
+    send_idx = np.concatenate(([P] if has_lo else []) + ([nloc - pl + P] if has_hi else []) +
+                              [np.empty(0, np.int32)]).astype(np.int32)
+    row_kind = np.zeros(nloc, dtype=np.uint8)
+    if has_lo:
+        row_kind[:pl] = 1
+    if has_hi:
+        row_kind[nloc - pl:] = 1
+    halo_gcol = np.concatenate(([(z0 - 1) * pl + np.arange(pl, dtype=np.int64)] if has_lo else []) +
+                               ([z1 * pl + np.arange(pl, dtype=np.int64)] if has_hi else []) +
+                               [np.empty(0, np.int64)])
+    return dict(nloc=nloc, nnz_loc=base, nhalo=(int(has_lo) + int(has_hi)) * pl, nsend=len(send_idx),
+                local_row_ptr=np.concatenate(rps), local_col=np.concatenate(cols),
+                values=np.concatenate(vals), halo_gcol=halo_gcol, send_idx=send_idx,
+                row_kind=row_kind, has_lo=has_lo, has_hi=has_hi)

@@ -163,3 +163,22 @@ def test_slab_local_builder_equals_localize_of_global(P):
             assert np.array_equal(got[k], want[k]), (k, r)
         recv, send = synth.slab_counts(got, P, r, nx)
         assert np.array_equal(recv, want["recv_counts"]) and np.array_equal(send, want["send_counts"])
+
+
+@pytest.mark.parametrize("P", [1, 2, 3])
+def test_op27_slab_local_builder_equals_localize_of_global(P):
+    n = 6
+    rp, col, val = synth.op27(n, index_dtype=np.int64)
+    A = hp.CsrMatrix(rp, col, val)
+    zb = hp.partition_slabs(n, P)
+    bounds = zb * n * n
+    for r in range(P):
+        want = hp.csr_localize(A, bounds, r)
+        got = synth.op27_slab_local(n, int(zb[r]), int(zb[r + 1]), planes_per_chunk=1 + r)
+        for k in ("nloc", "nnz_loc", "nhalo", "nsend"):
+            assert got[k] == want[k], k
+        for k in ("local_row_ptr", "local_col", "halo_gcol", "send_idx", "row_kind"):
+            assert np.array_equal(got[k], want[k]), (k, r)
+        assert np.array_equal(got["values"], val[rp[bounds[r]]:rp[bounds[r + 1]]])
+        recv, send = synth.slab_counts(got, P, r, n * n)
+        assert np.array_equal(recv, want["recv_counts"]) and np.array_equal(send, want["send_counts"])
