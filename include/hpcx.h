@@ -181,7 +181,9 @@ typedef struct {
   int32_t sell_c;      /* SELL slice height (0 = 32) */
   int32_t sell_sigma;  /* SELL sort window in rows (0 = 1024; 1 = no sorting) */
   int32_t lanes_per_row; /* VECTOR: 0 = from mean row length */
-  int32_t reserved[3];
+  int32_t short_row_max; /* STREAM: row blocks whose longest row is at most this take the
+                            one-thread-per-row path (0 = 48) */
+  int32_t reserved[2];
 } hpcx_csr_opts;
 
 /* Uploads (or adopts, when already on the device the arrays are copied device-to-device)

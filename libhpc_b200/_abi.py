@@ -43,7 +43,7 @@ class CsrDesc(C.Structure):
 class CsrOpts(C.Structure):
     _fields_ = [("kernel", C.c_int32), ("tile_nnz", C.c_int32), ("sell_c", C.c_int32),
                 ("sell_sigma", C.c_int32), ("lanes_per_row", C.c_int32),
-                ("reserved", C.c_int32 * 3)]
+                ("short_row_max", C.c_int32), ("reserved", C.c_int32 * 2)]
 
 
 class CsrArrays(C.Structure):

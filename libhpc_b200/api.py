@@ -328,13 +328,13 @@ class DeviceCsr:
     """Device-resident matrix behind hpcx_csr_create."""
 
     def __init__(self, ctx: Context, A: CsrMatrix, kernel: int = SPMV_STREAM, tile_nnz: int = 0,
-                 sell_c: int = 0, sell_sigma: int = 0, lanes_per_row: int = 0):
+                 sell_c: int = 0, sell_sigma: int = 0, lanes_per_row: int = 0, short_row_max: int = 0):
         self.ctx, self.host = ctx, A
         d = _abi.CsrDesc(A.nrows, A.ncols, A.nnz, A.row_ptr.ctypes.data,
                          A.row_ptr.dtype.itemsize, _dtype_code(A.dtype),
                          A.col_idx.ctypes.data if A.nnz else None,
                          A.values.ctypes.data if A.nnz else None, MEM_HOST, 0)
-        o = _abi.CsrOpts(kernel, tile_nnz, sell_c, sell_sigma, lanes_per_row)
+        o = _abi.CsrOpts(kernel, tile_nnz, sell_c, sell_sigma, lanes_per_row, short_row_max)
         h = C.c_void_p()
         ctx.check(ctx.lib.hpcx_csr_create(ctx.h, C.byref(d), C.byref(o), C.byref(h)))
         self.h = h
@@ -345,14 +345,14 @@ class DeviceCsr:
     @classmethod
     def from_device_arrays(cls, ctx: Context, arrays: "DeviceCsrArrays", ncols: int | None = None,
                            kernel: int = SPMV_STREAM, tile_nnz: int = 0, sell_c: int = 0,
-                           sell_sigma: int = 0, lanes_per_row: int = 0) -> "DeviceCsr":
+                           sell_sigma: int = 0, lanes_per_row: int = 0, short_row_max: int = 0) -> "DeviceCsr":
         """Matrix whose CSR arrays already live on the device (csr_from_coo)."""
         self = cls.__new__(cls)
         self.ctx, self.host = ctx, None
         ncols = arrays.nrows if ncols is None else int(ncols)
         d = _abi.CsrDesc(arrays.nrows, ncols, arrays.nnz, arrays.row_ptr, arrays.idx_bytes,
                          _dtype_code(arrays.dtype), arrays.col_idx, arrays.values, MEM_DEVICE, 0)
-        o = _abi.CsrOpts(kernel, tile_nnz, sell_c, sell_sigma, lanes_per_row)
+        o = _abi.CsrOpts(kernel, tile_nnz, sell_c, sell_sigma, lanes_per_row, short_row_max)
         h = C.c_void_p()
         ctx.check(ctx.lib.hpcx_csr_create(ctx.h, C.byref(d), C.byref(o), C.byref(h)))
         self.h = h

@@ -91,6 +91,34 @@ spmv_stream_kernel(const int32_t *__restrict__ row_ptr, const int32_t *__restric
   }
   if (cnt_a > 0) mbar_wait(bar, 0);
 
+  if (lanes == 1) {
+    // Short rows: one thread per row straight out of the staged tile, ascending p — the oracle's
+    // order, so the result is bit-identical.  A warp's 32 lanes hold 32 consecutive rows, so for
+    // banded matrices the k-th gathers of a warp fall into one or two 128-byte lines of x
+    // (columns i+off_k for consecutive i), and the staged col/val reads are stride-(row length)
+    // accesses to shared memory (conflict-free for odd lengths such as 5 and 27).  No product is
+    // written back and no second barrier is needed.
+    for (int r = tid; r < nrows; r += kThreads) {
+      const int a = (int)((int64_t)row_ptr[row0 + r] - p0a);
+      const int e = (int)((int64_t)row_ptr[row0 + r + 1] - p0a);
+      T s = T(0);
+      for (int i = a; i < e; i += 4) {
+        T xv[4], vv[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const bool on = i + k < e;
+          xv[k] = on ? ldg_nc(x + scol[i + k]) : T(0);
+          vv[k] = on ? sval[i + k] : T(0);
+        }
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          if (i + k < e) s = add_rn(s, mul_rn(vv[k], xv[k]));
+      }
+      y[row0 + r] = s;
+    }
+    return;
+  }
+
   // Products in place. Four gathers in flight per thread per round.
   for (int base = lead + tid; base < cnt; base += 4 * kThreads) {
     T xv[4];
@@ -107,16 +135,7 @@ spmv_stream_kernel(const int32_t *__restrict__ row_ptr, const int32_t *__restric
   }
   __syncthreads();
 
-  if (lanes == 1) {
-    // One thread per row, ascending p: the oracle's order.
-    for (int r = tid; r < nrows; r += kThreads) {
-      const int a = (int)((int64_t)row_ptr[row0 + r] - p0a);
-      const int e = (int)((int64_t)row_ptr[row0 + r + 1] - p0a);
-      T s = T(0);
-      for (int i = a; i < e; ++i) s = add_rn(s, sval[i]);
-      y[row0 + r] = s;
-    }
-  } else if (lanes > 1) {
+  if (lanes > 1) {
     // `lanes` threads per row: strided partial sums, xor-shuffle tree.
     const int g = tid / lanes, l = tid % lanes;
     const int groups = kThreads / lanes;
@@ -206,16 +225,18 @@ spmv_sell_kernel(const int64_t *__restrict__ slice_ptr, const int32_t *__restric
   y[perm[srow]] = s;
 }
 
-int lanes_for(int64_t nnz_blk, int64_t nrows) {
+// Threads per row of a block.  Rows no longer than g_short_row_max all take the fused
+// one-thread-per-row path (lanes = 1, oracle order); otherwise lanes grow with the mean row
+// length and are raised until the block's longest row costs a lane at most 64 entries.
+int g_short_row_max = 48;
+int lanes_for(int64_t nnz_blk, int64_t nrows, int64_t max_len) {
   if (nrows <= 0) return 1;
   const int64_t avg = (nnz_blk + nrows - 1) / nrows;
   if (nrows == 1 && nnz_blk > 256) return 0;
-  if (avg <= 8) return 1;
-  if (avg <= 16) return 2;
-  if (avg <= 32) return 4;
-  if (avg <= 64) return 8;
-  if (avg <= 128) return 16;
-  return 32;
+  if (max_len <= g_short_row_max) return 1;
+  int lanes = avg <= 16 ? 2 : avg <= 32 ? 4 : avg <= 64 ? 8 : avg <= 128 ? 16 : 32;
+  while (lanes < 32 && max_len > 64 * (int64_t)lanes) lanes <<= 1;
+  return lanes;
 }
 
 // Greedy row blocking. `kind` (may be null) forces a cut wherever the row kind changes
@@ -243,8 +264,12 @@ void build_rowblocks(const int64_t *rp, int64_t nrows, int tile, const uint8_t *
       continue;
     }
     const int64_t r0 = r, p0 = rp[r];
-    while (r < nrows && r - r0 < tile && rp[r + 1] - p0 <= tile && (!kind || kind[r] == want)) ++r;
-    RowBlock b{(int32_t)r0, (int32_t)(r - r0), -1, lanes_for(rp[r] - p0, r - r0), p0, rp[r]};
+    int64_t max_len = 0;
+    while (r < nrows && r - r0 < tile && rp[r + 1] - p0 <= tile && (!kind || kind[r] == want)) {
+      max_len = std::max(max_len, rp[r + 1] - rp[r]);
+      ++r;
+    }
+    RowBlock b{(int32_t)r0, (int32_t)(r - r0), -1, lanes_for(rp[r] - p0, r - r0, max_len), p0, rp[r]};
     out.push_back(b);
   }
 }
@@ -472,6 +497,7 @@ hpcx_status hpcx_csr_create(hpcx_ctx ctx, const hpcx_csr_desc *d, const hpcx_csr
   A->kernel = opts && opts->kernel ? opts->kernel : HPCX_SPMV_STREAM;
   A->tile = opts && opts->tile_nnz ? opts->tile_nnz : 2048;
   A->lanes_per_row = opts ? opts->lanes_per_row : 0;
+  g_short_row_max = opts && opts->short_row_max > 0 ? opts->short_row_max : 48;
   A->sell_c = opts && opts->sell_c ? opts->sell_c : 32;
   A->sell_sigma = opts && opts->sell_sigma ? opts->sell_sigma : 1024;
   if (A->tile != 1024 && A->tile != 2048 && A->tile != 4096) {
