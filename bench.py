@@ -295,6 +295,8 @@ def run_ours(args, rank: int, world: int, local: int):
     checksum = float(np.abs(y_pin.numpy()).sum())
 
     extra = stencil_extra(ctx, torch, stream, world, rank, barrier, max_over_ranks, hp, hd, synth)
+    extra["cg_iteration_c2_fp64"] = cg_extra(args, ctx, torch, stream, world, barrier, max_over_ranks, hp, D,
+                                             nloc, nnz, xd)
     if args.configs == "all":
         extra.update(sparse_extra(args, ctx, torch, stream, world, rank, barrier, max_over_ranks, hp, hd, synth))
     if world > 1:
@@ -413,6 +415,35 @@ def stencil_extra(ctx, torch, stream, world, rank, barrier, max_over_ranks, hp, 
         a.destroy()
         b.destroy()
     return out
+
+
+def cg_extra(args, ctx, torch, stream, world, barrier, max_over_ranks, hp, D, nloc, nnz, b):
+    """CG iterations around the configs[1] operator (fused SpMV + <p,q>, then
+    {x, r, <r,r>} and {p} passes; scalars on the device, all-reduced over the ranks).
+    Algorithmic bytes per iteration and rank: SpMV (12 B/nnz + 20 B/row) + 72 B/row."""
+    peak, _ = measured_peak()
+    S = hp.CgSolver(D)
+    x = torch.zeros(nloc, dtype=torch.float64, device="cuda")
+    iters = max(args.steps, 10)
+    torch.cuda.synchronize()
+    with torch.cuda.stream(stream):
+        S.solve(b, x, 3, 0.0, stream=stream, want_result=False)  # warm-up
+        n0 = ctx.launch_count()
+        x.zero_()
+        dt, _, _ = time_steps(torch, stream,
+                              lambda: S.solve(b, x, iters, 0.0, stream=stream, want_result=False), 1, barrier)
+        launches = ctx.launch_count() - n0
+    res = S.solve(b, x, 0)  # reads back the recurrence scalars of the timed solve's final state
+    dt = max_over_ranks(dt)
+    per_iter = dt / (iters + 1)  # the initial residual costs one more product + vector pass
+    nbytes = algorithmic_bytes(nloc, nnz) + 72 * nloc
+    S.destroy()
+    return {"metric": "cg_effective_GBps", "value": nbytes * world / per_iter / 1e9, "unit": "GB/s",
+            "iterations": iters, "ms_per_iteration": per_iter * 1e3, "gpu_launches": launches,
+            "rr_over_bb_after_restart": res["rr"] / res["bb"] if res["bb"] else None,
+            "roofline": {"bound": "hbm", "achieved": nbytes / per_iter / 1e9, "peak": peak, "unit": "GB/s",
+                         "frac": nbytes / per_iter / 1e9 / peak, "algorithmic_bytes_per_iteration": nbytes,
+                         "note": "three passes per iteration: fused SpMV+dot, x/r update + <r,r>, p update"}}
 
 
 def sparse_extra(args, ctx, torch, stream, world, rank, barrier, max_over_ranks, hp, hd, synth):

@@ -323,6 +323,30 @@ HPCX_API hpcx_status hpcx_csr_x_buffer(hpcx_csr A, void **x_full);
 HPCX_API hpcx_status hpcx_spmv_dist(hpcx_csr A, const void *x_local, void *y_local,
                                     void *stream);
 
+/* ------------------------------------------------ CG iteration around SpMV
+ * Conjugate gradients for a symmetric positive definite A created with the STREAM kernel —
+ * either a single-rank matrix (nrows == ncols) or a distributed one (hpcx_csr_set_halo done:
+ * b and x are then the rank's nloc owned entries and the dot products are all-reduced over
+ * the communicator; every rank must make the same calls).  One iteration is three passes over
+ * HBM: q = A*p with <p, q> fused into the SpMV kernel, {x += alpha p, r -= alpha q, <r, r>},
+ * {p = r + beta p}; the scalars stay on the device.  Starts from the x passed in.  Stops after
+ * max_iters iterations or once ||r||^2 <= rel_tol^2 * ||b||^2 (later launches of the call then
+ * leave x untouched); check_every > 0 makes the host poll the convergence flag every that
+ * many iterations so that a converged solve returns early.  `result` (may be NULL) receives
+ * the iteration count, the flag and the recurrence values of ||r||^2 and ||b||^2. */
+typedef struct hpcx_cg_s *hpcx_cg;
+typedef struct {
+  int32_t iterations;
+  int32_t converged;
+  double rr;  /* ||r||^2 from the recurrence */
+  double bb;  /* ||b||^2 */
+} hpcx_cg_result;
+HPCX_API hpcx_status hpcx_cg_create(hpcx_csr A, hpcx_cg *out);
+HPCX_API hpcx_status hpcx_cg_destroy(hpcx_cg S);
+HPCX_API hpcx_status hpcx_cg_solve(hpcx_cg S, const void *b, int32_t b_mem, void *x, int32_t x_mem,
+                                   int32_t max_iters, double rel_tol, int32_t check_every,
+                                   hpcx_cg_result *result, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -51,6 +51,11 @@ class CsrArrays(C.Structure):
                 ("values", C.c_void_p)]
 
 
+class CgResult(C.Structure):
+    _fields_ = [("iterations", C.c_int32), ("converged", C.c_int32), ("rr", C.c_double),
+                ("bb", C.c_double)]
+
+
 class HaloSizes(C.Structure):
     _fields_ = [("nloc", C.c_int64), ("nnz_loc", C.c_int64), ("nhalo", C.c_int64),
                 ("nsend", C.c_int64)]
@@ -112,6 +117,9 @@ PROTOTYPES = {
     "hpcx_csr_halo_transport": (_i32, [_vp, _i32]),
     "hpcx_csr_x_buffer": (_i32, [_vp, _P(_vp)]),
     "hpcx_spmv_dist": (_i32, [_vp, _vp, _vp, _vp]),
+    "hpcx_cg_create": (_i32, [_vp, _P(_vp)]),
+    "hpcx_cg_destroy": (_i32, [_vp]),
+    "hpcx_cg_solve": (_i32, [_vp, _vp, _i32, _vp, _i32, _i32, C.c_double, _i32, _P(CgResult), _vp]),
 }
 
 _LIB = None

@@ -503,6 +503,33 @@ def synth_field(ctx: Context, seed: int, n: int, out, dtype, first: int = 0):
     return out
 
 
+class CgSolver:
+    """Conjugate gradients around a DeviceCsr (hpcx_cg_*): fused SpMV + dot, device scalars."""
+
+    def __init__(self, A: DeviceCsr):
+        self.A, self.ctx = A, A.ctx
+        h = C.c_void_p()
+        self.ctx.check(self.ctx.lib.hpcx_cg_create(A.h, C.byref(h)))
+        self.h = h
+
+    def solve(self, b, x, max_iters: int, rel_tol: float = 0.0, check_every: int = 0, stream=None,
+              want_result: bool = True):
+        """x is the start vector and receives the iterate; returns a dict (or None)."""
+        pb, mb = _ptr(b)
+        px, mx = _ptr(x)
+        res = _abi.CgResult()
+        self.ctx.check(self.ctx.lib.hpcx_cg_solve(self.h, pb, mb, px, mx, max_iters, rel_tol, check_every,
+                                                  C.byref(res) if want_result else None, _stream(stream)))
+        if not want_result:
+            return None
+        return dict(iterations=res.iterations, converged=bool(res.converged), rr=res.rr, bb=res.bb)
+
+    def destroy(self):
+        if self.h:
+            self.ctx.lib.hpcx_cg_destroy(self.h)
+            self.h = None
+
+
 def spmv(ctx: Context, A: CsrMatrix, x: np.ndarray, y: np.ndarray | None = None, **opts):
     """The reference-facing free function sparse::spmv(A, x, y) with host containers.
     The device mirror of A is cached on the host matrix (keyed by context and options)."""

@@ -19,9 +19,10 @@ namespace hpcx {
 hpcx_status jacobi7_launch(hpcx_grid_s *g, void *src, void *dst, int variant, int zsplit,
                            int64_t zbeg, int64_t zend, cudaStream_t s, const JacobiPeer *peer);
 hpcx_status spmv_launch_blocks(hpcx_csr A, const RowBlock *d_blocks, int64_t nblocks, const void *x,
-                               void *y, cudaStream_t s);
+                               void *y, cudaStream_t s, void *dot_part);
 hpcx_status spmv_launch_fixup_tables(hpcx_csr A, const int32_t *long_row, const int32_t *long_off,
-                                     int64_t nlong, void *y, cudaStream_t s);
+                                     int64_t nlong, void *y, cudaStream_t s, const void *x,
+                                     void *dot_part);
 void spmv_build_rowblocks(const int64_t *rp, int64_t nrows, int tile, const uint8_t *kind, int want,
                           std::vector<RowBlock> &out, std::vector<int32_t> *long_row,
                           std::vector<int32_t> *long_off);
@@ -700,6 +701,22 @@ hpcx_status hpcx_csr_halo_transport(hpcx_csr A, int32_t transport) {
   return hpcx_comm_barrier(ctx);
 }
 
+namespace hpcx {
+// In-place sum over the ranks of `count` scalars on stream s (the CG solver's dot products).
+hpcx_status allreduce_sum(hpcx_ctx ctx, void *buf, size_t count, int dtype, cudaStream_t s) {
+  if (ctx->nranks <= 1) return HPCX_OK;
+  if (!ctx->nccl_comm) return fail(ctx, HPCX_NCCL_ERROR, "hpcx_comm_init has not been called");
+  HPCX_NCCL(ctx, g_nccl.AllReduce(buf, buf, count, nccl_type(dtype), ncclSum, comm_of(ctx), s));
+  return HPCX_OK;
+}
+}  // namespace hpcx
+
+// Where the fused <x, y> partials of the distributed product go when a CG solver has attached a
+// partial array (A->dot_part): [interior blocks | boundary blocks | long rows].
+static inline void *dot_slot(hpcx_csr A, int64_t first) {
+  return A->dot_part ? static_cast<char *>(A->dot_part) + first * A->es : nullptr;
+}
+
 // Transport 1, all on the caller's stream:
 //   push kernel (gather + peer stores + flags) ; interior rows ; wait for the source ranks'
 //   flags ; boundary rows ; ack to the source ranks.
@@ -723,16 +740,19 @@ static hpcx_status spmv_dist_peer(hpcx_csr A, char *xfull, void *y_local, cudaSt
     rc = after_launch(ctx, "push_boundary_x_kernel");
     if (rc != HPCX_OK) return rc;
   }
-  rc = spmv_launch_blocks(A, A->d_blocks_int, (int64_t)A->h_blocks_int.size(), xfull, y_local, cs);
+  rc = spmv_launch_blocks(A, A->d_blocks_int, (int64_t)A->h_blocks_int.size(), xfull, y_local, cs,
+                          dot_slot(A, 0));
   if (rc != HPCX_OK) return rc;
   if (A->nsrc) {
     halo_x_ready_kernel<<<1, 64, 0, cs>>>(A->d_sync, A->d_src_rank, A->nsrc, epoch);
     rc = after_launch(ctx, "halo_x_ready_kernel");
     if (rc != HPCX_OK) return rc;
   }
-  rc = spmv_launch_blocks(A, A->d_blocks_bnd, (int64_t)A->h_blocks_bnd.size(), xfull, y_local, cs);
+  rc = spmv_launch_blocks(A, A->d_blocks_bnd, (int64_t)A->h_blocks_bnd.size(), xfull, y_local, cs,
+                          dot_slot(A, (int64_t)A->h_blocks_int.size()));
   if (rc != HPCX_OK) return rc;
-  rc = spmv_launch_fixup_tables(A, A->d_long_row_dist, A->d_long_off_dist, A->nlong_dist, y_local, cs);
+  rc = spmv_launch_fixup_tables(A, A->d_long_row_dist, A->d_long_off_dist, A->nlong_dist, y_local, cs, xfull,
+                                dot_slot(A, (int64_t)(A->h_blocks_int.size() + A->h_blocks_bnd.size())));
   if (rc != HPCX_OK) return rc;
   if (A->nsrc) {
     halo_x_ack_kernel<<<1, 64, 0, cs>>>(A->d_src_ack, A->nsrc, epoch);
@@ -806,12 +826,15 @@ hpcx_status hpcx_spmv_dist(hpcx_csr A, const void *x_local, void *y_local, void 
     HPCX_NCCL(ctx, g_nccl.GroupEnd());
     HPCX_CUDA(ctx, cudaEventRecord(ctx->ev[1], ms));
   }
-  rc = spmv_launch_blocks(A, A->d_blocks_int, (int64_t)A->h_blocks_int.size(), xfull, y_local, cs);
+  rc = spmv_launch_blocks(A, A->d_blocks_int, (int64_t)A->h_blocks_int.size(), xfull, y_local, cs,
+                          dot_slot(A, 0));
   if (rc != HPCX_OK) return rc;
   if (exchange) HPCX_CUDA(ctx, cudaStreamWaitEvent(cs, ctx->ev[1], 0));
-  rc = spmv_launch_blocks(A, A->d_blocks_bnd, (int64_t)A->h_blocks_bnd.size(), xfull, y_local, cs);
+  rc = spmv_launch_blocks(A, A->d_blocks_bnd, (int64_t)A->h_blocks_bnd.size(), xfull, y_local, cs,
+                          dot_slot(A, (int64_t)A->h_blocks_int.size()));
   if (rc != HPCX_OK) return rc;
-  rc = spmv_launch_fixup_tables(A, A->d_long_row_dist, A->d_long_off_dist, A->nlong_dist, y_local, cs);
+  rc = spmv_launch_fixup_tables(A, A->d_long_row_dist, A->d_long_off_dist, A->nlong_dist, y_local, cs, xfull,
+                                dot_slot(A, (int64_t)(A->h_blocks_int.size() + A->h_blocks_bnd.size())));
   if (rc != HPCX_OK) return rc;
   if (!stream) HPCX_CUDA(ctx, cudaStreamSynchronize(cs));
   return HPCX_OK;

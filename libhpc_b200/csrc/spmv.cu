@@ -56,11 +56,14 @@ struct StreamSmem {
   static constexpr int kBytes = kWsum + (kThreads / 32) * (int)sizeof(T);
 };
 
-template <typename T, int TILE>
+// DOT: additionally emits dot_part[blockIdx.x] = sum over the block's rows of y_i * x_i (square
+// matrices: the fused q = A*p, <p, q> of the CG step, cg.cu), reduced in a fixed order.
+template <typename T, int TILE, bool DOT>
 __global__ void __launch_bounds__(kThreads)
 spmv_stream_kernel(const int32_t *__restrict__ row_ptr, const int32_t *__restrict__ col,
                    const T *__restrict__ val, const T *__restrict__ x, T *__restrict__ y,
-                   const RowBlock *__restrict__ blocks, T *__restrict__ partials) {
+                   const RowBlock *__restrict__ blocks, T *__restrict__ partials,
+                   T *__restrict__ dot_part) {
   extern __shared__ __align__(128) unsigned char smem[];
   using L = StreamSmem<T, TILE>;
   T *sval = reinterpret_cast<T *>(smem);
@@ -91,6 +94,8 @@ spmv_stream_kernel(const int32_t *__restrict__ row_ptr, const int32_t *__restric
   }
   if (cnt_a > 0) mbar_wait(bar, 0);
 
+  T dot = T(0);
+  (void)dot;
   if (lanes == 1) {
     // Short rows: one thread per row straight out of the staged tile, ascending p — the oracle's
     // order, so the result is bit-identical.  A warp's 32 lanes hold 32 consecutive rows, so for
@@ -115,9 +120,10 @@ spmv_stream_kernel(const int32_t *__restrict__ row_ptr, const int32_t *__restric
           if (i + k < e) s = add_rn(s, mul_rn(vv[k], xv[k]));
       }
       y[row0 + r] = s;
+      if constexpr (DOT) dot = add_rn(dot, mul_rn(s, ldg_nc(x + row0 + r)));
     }
-    return;
-  }
+    if constexpr (!DOT) return;
+  } else {
 
   // Products in place. Four gathers in flight per thread per round.
   for (int base = lead + tid; base < cnt; base += 4 * kThreads) {
@@ -148,7 +154,10 @@ spmv_stream_kernel(const int32_t *__restrict__ row_ptr, const int32_t *__restric
         for (int i = a + l; i < e; i += lanes) s = add_rn(s, sval[i]);
       }
       for (int m = lanes >> 1; m > 0; m >>= 1) s = add_rn(s, shfl_xor(s, m));
-      if (r < nrows && l == 0) y[row0 + r] = s;
+      if (r < nrows && l == 0) {
+        y[row0 + r] = s;
+        if constexpr (DOT) dot = add_rn(dot, mul_rn(s, ldg_nc(x + row0 + r)));
+      }
     }
   } else {
     // Whole CTA on one row (or one chunk of a long row).
@@ -161,25 +170,43 @@ spmv_stream_kernel(const int32_t *__restrict__ row_ptr, const int32_t *__restric
       T t = wsum[0];
 #pragma unroll
       for (int w = 1; w < kThreads / 32; ++w) t = add_rn(t, wsum[w]);
-      if (part >= 0)
-        partials[part] = t;
-      else
+      if (part >= 0) {
+        partials[part] = t;  // the row's <y, x> term is added by the fix-up kernel
+      } else {
         y[row0] = t;
+        if constexpr (DOT) dot = mul_rn(t, ldg_nc(x + row0));
+      }
+    }
+    if constexpr (DOT) __syncthreads();  // wsum is reused below
+  }
+  }
+  if constexpr (DOT) {
+    for (int m = 16; m > 0; m >>= 1) dot = add_rn(dot, shfl_xor(dot, m));
+    if ((tid & 31) == 0) wsum[tid >> 5] = dot;
+    __syncthreads();
+    if (tid == 0) {
+      T t = wsum[0];
+#pragma unroll
+      for (int w = 1; w < kThreads / 32; ++w) t = add_rn(t, wsum[w]);
+      dot_part[blockIdx.x] = t;
     }
   }
 }
 
 // Adds the chunk partial sums of every long row in chunk order.
+// dot_part (may be null): dot_part[j] = y_row * x_row of long row j.
 template <typename T>
 __global__ void spmv_longrow_fixup_kernel(const int32_t *__restrict__ long_row,
                                           const int32_t *__restrict__ long_off,
                                           const T *__restrict__ partials, T *__restrict__ y,
-                                          int nlong) {
+                                          int nlong, const T *__restrict__ x,
+                                          T *__restrict__ dot_part) {
   const int j = blockIdx.x * blockDim.x + threadIdx.x;
   if (j >= nlong) return;
   T s = T(0);
   for (int k = long_off[j]; k < long_off[j + 1]; ++k) s = add_rn(s, partials[k]);
   y[long_row[j]] = s;
+  if (dot_part) dot_part[j] = mul_rn(s, x[long_row[j]]);
 }
 
 // Classic vector-per-row kernel: G lanes per row straight from global memory.
@@ -274,39 +301,48 @@ void build_rowblocks(const int64_t *rp, int64_t nrows, int tile, const uint8_t *
   }
 }
 
-template <typename T, int TILE>
+template <typename T, int TILE, bool DOT>
 hpcx_status launch_stream_t(hpcx_csr A, const RowBlock *d_blocks, int64_t nblocks, const T *x, T *y,
-                            cudaStream_t s) {
+                            T *dot_part, cudaStream_t s) {
   if (nblocks == 0) return HPCX_OK;
   using L = StreamSmem<T, TILE>;
   static bool configured = false;
   if (!configured) {
-    HPCX_CUDA(A->ctx, cudaFuncSetAttribute(spmv_stream_kernel<T, TILE>,
+    HPCX_CUDA(A->ctx, cudaFuncSetAttribute(spmv_stream_kernel<T, TILE, DOT>,
                                            cudaFuncAttributeMaxDynamicSharedMemorySize, L::kBytes));
     configured = true;
   }
-  spmv_stream_kernel<T, TILE><<<(unsigned)nblocks, kThreads, L::kBytes, s>>>(
-      A->d_row_ptr, A->d_col, (const T *)A->d_val, x, y, d_blocks, (T *)A->d_partials);
+  spmv_stream_kernel<T, TILE, DOT><<<(unsigned)nblocks, kThreads, L::kBytes, s>>>(
+      A->d_row_ptr, A->d_col, (const T *)A->d_val, x, y, d_blocks, (T *)A->d_partials, dot_part);
   return after_launch(A->ctx, "spmv_stream_kernel");
 }
 
 template <typename T>
 hpcx_status launch_stream(hpcx_csr A, const RowBlock *d_blocks, int64_t nblocks, const T *x, T *y,
-                          cudaStream_t s) {
+                          cudaStream_t s, T *dot_part = nullptr) {
+  if (dot_part) {
+    switch (A->tile) {
+      case 1024: return launch_stream_t<T, 1024, true>(A, d_blocks, nblocks, x, y, dot_part, s);
+      case 2048: return launch_stream_t<T, 2048, true>(A, d_blocks, nblocks, x, y, dot_part, s);
+      case 4096: return launch_stream_t<T, 4096, true>(A, d_blocks, nblocks, x, y, dot_part, s);
+      default: return fail(A->ctx, HPCX_INVALID_ARG, "tile_nnz must be 1024, 2048 or 4096");
+    }
+  }
   switch (A->tile) {
-    case 1024: return launch_stream_t<T, 1024>(A, d_blocks, nblocks, x, y, s);
-    case 2048: return launch_stream_t<T, 2048>(A, d_blocks, nblocks, x, y, s);
-    case 4096: return launch_stream_t<T, 4096>(A, d_blocks, nblocks, x, y, s);
+    case 1024: return launch_stream_t<T, 1024, false>(A, d_blocks, nblocks, x, y, nullptr, s);
+    case 2048: return launch_stream_t<T, 2048, false>(A, d_blocks, nblocks, x, y, nullptr, s);
+    case 4096: return launch_stream_t<T, 4096, false>(A, d_blocks, nblocks, x, y, nullptr, s);
     default: return fail(A->ctx, HPCX_INVALID_ARG, "tile_nnz must be 1024, 2048 or 4096");
   }
 }
 
 template <typename T>
 hpcx_status launch_fixup(hpcx_csr A, const int32_t *long_row, const int32_t *long_off,
-                         int64_t nlong, T *y, cudaStream_t s) {
+                         int64_t nlong, T *y, cudaStream_t s, const T *x = nullptr,
+                         T *dot_part = nullptr) {
   if (nlong == 0) return HPCX_OK;
   spmv_longrow_fixup_kernel<T><<<(unsigned)((nlong + 127) / 128), 128, 0, s>>>(
-      long_row, long_off, (const T *)A->d_partials, y, (int)nlong);
+      long_row, long_off, (const T *)A->d_partials, y, (int)nlong, x, dot_part);
   return after_launch(A->ctx, "spmv_longrow_fixup_kernel");
 }
 
@@ -349,8 +385,11 @@ hpcx_status spmv_device(hpcx_csr A, const T *x, T *y, cudaStream_t s) {
   hpcx_status st;
   switch (A->kernel) {
     case HPCX_SPMV_STREAM:
-      st = launch_stream<T>(A, A->d_blocks, (int64_t)A->h_blocks.size(), x, y, s);
-      if (st == HPCX_OK) st = launch_fixup<T>(A, A->d_long_row, A->d_long_off, A->nlong, y, s);
+      // A->dot_part (set by the CG solver): [row blocks | long rows] partials of <x, y>
+      st = launch_stream<T>(A, A->d_blocks, (int64_t)A->h_blocks.size(), x, y, s, (T *)A->dot_part);
+      if (st == HPCX_OK)
+        st = launch_fixup<T>(A, A->d_long_row, A->d_long_off, A->nlong, y, s, x,
+                             A->dot_part ? (T *)A->dot_part + A->h_blocks.size() : nullptr);
       return st;
     case HPCX_SPMV_VECTOR: return launch_vector<T>(A, x, y, s);
     case HPCX_SPMV_SELL: return launch_sell<T>(A, x, y, s);
@@ -454,15 +493,20 @@ hpcx_status upload_vec(hpcx_ctx ctx, const std::vector<V> &h, V **d) {
 namespace hpcx {
 // Shared with dist.cu.
 hpcx_status spmv_launch_blocks(hpcx_csr A, const RowBlock *d_blocks, int64_t nblocks, const void *x,
-                               void *y, cudaStream_t s) {
+                               void *y, cudaStream_t s, void *dot_part) {
   if (A->dtype == HPCX_F64)
-    return launch_stream<double>(A, d_blocks, nblocks, (const double *)x, (double *)y, s);
-  return launch_stream<float>(A, d_blocks, nblocks, (const float *)x, (float *)y, s);
+    return launch_stream<double>(A, d_blocks, nblocks, (const double *)x, (double *)y, s,
+                                 (double *)dot_part);
+  return launch_stream<float>(A, d_blocks, nblocks, (const float *)x, (float *)y, s, (float *)dot_part);
 }
 hpcx_status spmv_launch_fixup_tables(hpcx_csr A, const int32_t *long_row, const int32_t *long_off,
-                                     int64_t nlong, void *y, cudaStream_t s) {
-  if (A->dtype == HPCX_F64) return launch_fixup<double>(A, long_row, long_off, nlong, (double *)y, s);
-  return launch_fixup<float>(A, long_row, long_off, nlong, (float *)y, s);
+                                     int64_t nlong, void *y, cudaStream_t s, const void *x,
+                                     void *dot_part) {
+  if (A->dtype == HPCX_F64)
+    return launch_fixup<double>(A, long_row, long_off, nlong, (double *)y, s, (const double *)x,
+                                (double *)dot_part);
+  return launch_fixup<float>(A, long_row, long_off, nlong, (float *)y, s, (const float *)x,
+                             (float *)dot_part);
 }
 void spmv_build_rowblocks(const int64_t *rp, int64_t nrows, int tile, const uint8_t *kind, int want,
                           std::vector<RowBlock> &out, std::vector<int32_t> *long_row,

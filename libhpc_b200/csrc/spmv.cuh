@@ -47,6 +47,8 @@ struct hpcx_csr_s {
   void *d_sell_val = nullptr;
   // staging for host operands
   void *d_x = nullptr, *d_y = nullptr;
+  // when set (by the CG solver, cg.cu) the STREAM launches also emit per-block <x, y> partials
+  void *dot_part = nullptr;
   // distributed (set by hpcx_csr_set_halo)
   int64_t nloc = 0, nhalo = 0, nsend = 0;
   std::vector<int64_t> recv_counts, send_counts;

@@ -252,3 +252,17 @@ def ref_index(dim, lo, hi, idx, checked):
     rc = r.hpcref_index(C.c_int(len(d)), C.c_int(lo), C.c_int(hi), _p(d), _p(ix),
                         C.c_int(int(checked)), _p(st), C.byref(total), C.byref(off))
     return rc, st, int(total.value), int(off.value)
+
+
+def cg(rp, col, val, b, x0, max_iters: int, tol: float = 0.0):
+    """orc_cg_*: returns (x, iterations, rr, bb)."""
+    rp = np.ascontiguousarray(rp, dtype=np.int64)
+    x = np.ascontiguousarray(x0, dtype=val.dtype).copy()
+    b = np.ascontiguousarray(b, dtype=val.dtype)
+    fn = lib().orc_cg_f64 if val.dtype == np.float64 else lib().orc_cg_f32
+    fn.restype = C.c_int64
+    rr, bb = C.c_double(), C.c_double()
+    it = fn(C.c_int64(len(rp) - 1), _p(rp), _p(np.ascontiguousarray(col, dtype=np.int32)),
+            _p(np.ascontiguousarray(val)), _p(b), _p(x), C.c_int64(max_iters), C.c_double(tol),
+            C.byref(rr), C.byref(bb))
+    return x, int(it), rr.value, bb.value

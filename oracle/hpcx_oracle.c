@@ -477,3 +477,62 @@ ORC_API int orc_csr_localize(int64_t nrows, const int64_t *row_ptr, const int32_
   sizes[3] = nsend;
   return 0;
 }
+
+/* ------------------------------------------------------------------ CG step
+ * Classical conjugate gradients around the SpMV above, no reference counterpart (the reference
+ * has no solver).  Starts from x; r = b - A x; p = r; per iteration
+ *   q = A p; alpha = <r,r>/<p,q>; x = x + alpha p; r = r - alpha q; beta = <r,r>new/<r,r>;
+ *   p = r + beta p,
+ * every product and sum rounded separately, dot products added in ascending index.  Stops after
+ * max_iters iterations or once <r,r> <= tol^2 <b,b>.  Returns the iterations done; rr_out /
+ * bb_out receive the recurrence <r,r> and <b,b>. */
+#define ORC_CG(NAME, T, SPMV)                                                                  \
+  ORC_API int64_t NAME(int64_t n, const int64_t *row_ptr, const int32_t *col, const T *val,    \
+                       const T *b, T *x, int64_t max_iters, double tol, double *rr_out,         \
+                       double *bb_out) {                                                       \
+    T *r = (T *)malloc((size_t)n * sizeof(T)), *p = (T *)malloc((size_t)n * sizeof(T)),        \
+      *q = (T *)malloc((size_t)n * sizeof(T));                                                 \
+    SPMV(n, row_ptr, col, val, x, q);                                                          \
+    T rr = 0, bb = 0;                                                                          \
+    for (int64_t i = 0; i < n; ++i) {                                                          \
+      r[i] = b[i] - q[i];                                                                      \
+      p[i] = r[i];                                                                             \
+      const T r2 = r[i] * r[i], b2 = b[i] * b[i];                                              \
+      rr = rr + r2;                                                                            \
+      bb = bb + b2;                                                                            \
+    }                                                                                          \
+    const T thresh = (T)(tol * tol) * bb;                                                      \
+    int64_t it = 0;                                                                            \
+    while (it < max_iters && !(rr <= thresh)) {                                                \
+      SPMV(n, row_ptr, col, val, p, q);                                                        \
+      T pq = 0;                                                                                \
+      for (int64_t i = 0; i < n; ++i) {                                                        \
+        const T t = q[i] * p[i];                                                               \
+        pq = pq + t;                                                                           \
+      }                                                                                        \
+      const T alpha = rr / pq;                                                                 \
+      T rn = 0;                                                                                \
+      for (int64_t i = 0; i < n; ++i) {                                                        \
+        const T ap = alpha * p[i], aq = alpha * q[i];                                          \
+        x[i] = x[i] + ap;                                                                      \
+        r[i] = r[i] - aq;                                                                      \
+        const T r2 = r[i] * r[i];                                                              \
+        rn = rn + r2;                                                                          \
+      }                                                                                        \
+      const T beta = rn / rr;                                                                  \
+      rr = rn;                                                                                 \
+      for (int64_t i = 0; i < n; ++i) {                                                        \
+        const T bp = beta * p[i];                                                              \
+        p[i] = r[i] + bp;                                                                      \
+      }                                                                                        \
+      ++it;                                                                                    \
+    }                                                                                          \
+    if (rr_out) *rr_out = (double)rr;                                                          \
+    if (bb_out) *bb_out = (double)bb;                                                          \
+    free(r);                                                                                   \
+    free(p);                                                                                   \
+    free(q);                                                                                   \
+    return it;                                                                                 \
+  }
+ORC_CG(orc_cg_f64, double, orc_spmv_f64)
+ORC_CG(orc_cg_f32, float, orc_spmv_f32)

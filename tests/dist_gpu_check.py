@@ -107,6 +107,29 @@ def main():
                               oracle.spmv_abs(rp, col, val, x2)[r0:r1], tol)
             D.destroy()
 
+    # ---- CG around the distributed product (SPD 27-point operator): iterates vs the global oracle
+    rp, col, val = synth.op27(12, index_dtype=np.int64)
+    n = len(rp) - 1
+    b = synth.field(11, n)
+    x0 = synth.field(12, n) * 0.1
+    want, it, rr, bb = oracle.cg(rp, col, val, b, x0, 10)
+    A = hp.CsrMatrix(rp, col, val)
+    bounds = hp.partition_rows(n, rp, world, 0)
+    L = hp.csr_localize(A, bounds, rank)
+    r0, r1 = int(bounds[rank]), int(bounds[rank + 1])
+    for transport in (0, 1):
+        D = hd.distributed_csr(ctx, L, val.dtype, transport=transport)
+        S = hp.CgSolver(D)
+        bd = torch.from_numpy(b[r0:r1].copy()).cuda()
+        xd = torch.from_numpy(x0[r0:r1].copy()).cuda()
+        torch.cuda.synchronize()
+        res = S.solve(bd, xd, 10)
+        assert res["iterations"] == 10, res
+        assert np.abs(xd.cpu().numpy() - want[r0:r1]).max() <= 1e-10 * np.abs(want).max(), (rank, transport)
+        assert abs(res["rr"] - rr) <= 1e-7 * rr and abs(res["bb"] - bb) <= 1e-10 * bb
+        S.destroy()
+        D.destroy()
+
     if world > 1:
         hd.barrier(ctx)
         dist.barrier()

@@ -4,6 +4,7 @@ import numpy as np
 import pytest
 
 import oracle
+from libhpc_b200 import synth
 from util import random_csr
 
 
@@ -139,3 +140,27 @@ def test_localize_reassembles_global_product():
         assert np.array_equal(yl, y[bounds[r]:bounds[r + 1]])
         assert L["recv_counts"].sum() == L["nhalo"] and L["send_counts"].sum() == L["nsend"]
         assert L["recv_counts"][r] == 0 and L["send_counts"][r] == 0
+
+
+# ---- CG step: analytic checks of the CPU restatement
+@pytest.mark.parametrize("dtype,tol", [(np.float64, 1e-11), (np.float32, 2e-4)])
+def test_cg_oracle_recovers_known_solution(dtype, tol):
+    rp, col, val = synth.laplace2d(24, 24, dtype, np.int64)
+    xs = synth.field(5, 24 * 24, dtype)
+    b = oracle.spmv(rp, col, val, xs)
+    x, it, rr, bb = oracle.cg(rp, col, val, b, np.zeros_like(b), 500, tol / 10)
+    assert 0 < it < 500 and rr <= (tol / 10) ** 2 * bb
+    assert np.abs(x - xs).max() <= 50 * tol * np.abs(xs).max()
+
+
+def test_cg_oracle_identity_and_zero_iterations():
+    n = 50
+    rp = np.arange(n + 1, dtype=np.int64)
+    col = np.arange(n, dtype=np.int32)
+    val = np.full(n, 2.0)
+    b = synth.field(3, n)
+    x, it, rr, bb = oracle.cg(rp, col, val, b, np.zeros(n), 10, 1e-14)
+    assert it == 1 and np.allclose(x, b / 2, rtol=1e-15) and rr == 0.0
+    x0 = synth.field(4, n)
+    x, it, _, _ = oracle.cg(rp, col, val, b, x0, 0)
+    assert it == 0 and np.array_equal(x, x0)
