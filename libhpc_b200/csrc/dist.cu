@@ -701,6 +701,8 @@ hpcx_status hpcx_csr_halo_transport(hpcx_csr A, int32_t transport) {
   return hpcx_comm_barrier(ctx);
 }
 
+}  // extern "C"
+
 namespace hpcx {
 // In-place sum over the ranks of `count` scalars on stream s (the CG solver's dot products).
 hpcx_status allreduce_sum(hpcx_ctx ctx, void *buf, size_t count, int dtype, cudaStream_t s) {
@@ -710,6 +712,8 @@ hpcx_status allreduce_sum(hpcx_ctx ctx, void *buf, size_t count, int dtype, cuda
   return HPCX_OK;
 }
 }  // namespace hpcx
+
+extern "C" {
 
 // Where the fused <x, y> partials of the distributed product go when a CG solver has attached a
 // partial array (A->dot_part): [interior blocks | boundary blocks | long rows].
