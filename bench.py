@@ -412,8 +412,42 @@ def stencil_extra(ctx, torch, stream, world, rank, barrier, max_over_ranks, hp, 
                 "ms_per_sweep": dt / 20 * 1e3,
                 "roofline": {"bound": "hbm", "achieved": m * m * 8 * 20 / dt / 1e9, "peak": peak,
                              "unit": "GB/s", "frac": m * m * 8 * 20 / dt / 1e9 / peak}}
+        # transpose (BM_transpose, test_hpc_benchmark.cpp:672-682) on the same 8192^2 shape: 8 B/cell
+        c = hp.DeviceGrid(ctx, (m, m), np.float32, 0)
+        step = lambda: hp.grid_transpose(b, c, stream=stream)  # noqa: E731
+        with torch.cuda.stream(stream):
+            for _ in range(3):
+                step()
+            dt, _, _ = time_steps(torch, stream, step, 20, barrier)
+        out["transpose_8192sq_fp32"] = {
+            "metric": "stencil_Gcell_updates_per_s", "value": m * m * 20 / dt / 1e9, "ms_per_sweep": dt / 20 * 1e3,
+            "roofline": {"bound": "hbm", "achieved": m * m * 8 * 20 / dt / 1e9, "peak": peak, "unit": "GB/s",
+                         "frac": m * m * 8 * 20 / dt / 1e9 / peak}}
         a.destroy()
         b.destroy()
+        c.destroy()
+        # 16 x 16 convolution (BM_conv, test_hpc_benchmark.cpp:786-806) on the reference's 1024^2 grid:
+        # 512 separately rounded fp32 operations per cell (bit-exact order, no FMA) -> FP32-issue bound
+        k = 1024
+        kb = hp.DeviceGrid(ctx, (k, k), np.float32, 16)
+        ka = hp.DeviceGrid(ctx, (k, k), np.float32, 0)
+        kb.upload(synth.field(32, (k + 32) ** 2, np.float32))
+        w = synth.field(33, 256, np.float32).reshape(16, 16)
+        step = lambda: hp.conv2d(kb, ka, w, stream=stream)  # noqa: E731
+        with torch.cuda.stream(stream):
+            for _ in range(3):
+                step()
+            dt, _, _ = time_steps(torch, stream, step, 20, barrier)
+        sm = torch.cuda.get_device_properties(0).multi_processor_count
+        fp32_peak = sm * 128 * 1.965  # Gop/s: 128 FP32 lanes per SM at the 1965 MHz boost clock
+        out["conv16x16_1024sq_fp32"] = {
+            "metric": "stencil_Gcell_updates_per_s", "value": k * k * 20 / dt / 1e9, "ms_per_sweep": dt / 20 * 1e3,
+            "roofline": {"bound": "fp32-issue (separately rounded mul + add, no FMA)",
+                         "achieved": k * k * 512 * 20 / dt / 1e9, "peak": fp32_peak, "unit": "Gop/s",
+                         "frac": k * k * 512 * 20 / dt / 1e9 / fp32_peak,
+                         "hbm_GBps": k * k * 8 * 20 / dt / 1e9}}
+        ka.destroy()
+        kb.destroy()
     return out
 
 

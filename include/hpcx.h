@@ -142,6 +142,19 @@ HPCX_API hpcx_status hpcx_stencil_sweep(hpcx_grid in, hpcx_grid out,
                                         const hpcx_stencil_desc *st, int32_t steps,
                                         void *stream);
 
+/* 2-D convolution sweep: out(y,x) += sum_{l<kh} sum_{k<kw} in(y+l, x+k) *
+ * weights[l*kw + k], l outer, k inner, every multiply and add rounded separately, accumulating
+ * onto out's current value — BM_conv / BM_conv_block (test_hpc_benchmark.cpp:786-818: nkern =
+ * 16, `kb` is <2,float,16>, `ka` has no ghosts).  in needs High_Bound >= kh-1 / kw-1; weights is
+ * a HOST array of kh*kw values of the grids' dtype.  16 x 16 takes the shared-memory tiled
+ * kernel (bit-identical to the reference loop); other extents (<= 1024 taps) or
+ * HPCX_VARIANT_DIRECT the direct one. */
+HPCX_API hpcx_status hpcx_conv2d(hpcx_grid in, hpcx_grid out, const void *weights, int32_t kh,
+                                 int32_t kw, int32_t variant, void *stream);
+/* out(x, y) = in(y, x) over the interiors of two 2-D grids of shapes (ny, nx) and (nx, ny), any
+ * ghost widths — BM_transpose / BM_transpose_tiling (test_hpc_benchmark.cpp:669-700). */
+HPCX_API hpcx_status hpcx_grid_transpose(hpcx_grid in, hpcx_grid out, void *stream);
+
 /* Ghost-cell pack / unpack (a11).  axis: 0 = slowest.  side: 0 = low, 1 = high.
  * pack copies the `width` INTERIOR planes adjacent to that side into a dense buffer
  * (planes in ascending index order; each plane dense over the full padded extent of the

@@ -278,6 +278,21 @@ def stencil_sweep(gin: DeviceGrid, gout: DeviceGrid, kind: int, radius: int = 0,
     gin.ctx.check(gin.ctx.lib.hpcx_stencil_sweep(gin.h, gout.h, C.byref(d), steps, _stream(stream)))
 
 
+def conv2d(gin: DeviceGrid, gout: DeviceGrid, weights: np.ndarray, variant: int = VARIANT_AUTO, stream=None):
+    """hpcx_conv2d: gout(y,x) += sum_{l,k} gin(y+l, x+k) * weights[l,k] (BM_conv,
+    test_hpc_benchmark.cpp:793-806); weights is a host (kh, kw) array of the grids' dtype."""
+    w = np.ascontiguousarray(weights, dtype=gin.dtype)
+    if w.ndim != 2:
+        raise ValueError("weights must be a (kh, kw) array")
+    gin.ctx.check(gin.ctx.lib.hpcx_conv2d(gin.h, gout.h, w.ctypes.data, w.shape[0], w.shape[1], variant,
+                                          _stream(stream)))
+
+
+def grid_transpose(gin: DeviceGrid, gout: DeviceGrid, stream=None):
+    """hpcx_grid_transpose: gout(x, y) = gin(y, x) (BM_transpose, test_hpc_benchmark.cpp:672-682)."""
+    gin.ctx.check(gin.ctx.lib.hpcx_grid_transpose(gin.h, gout.h, _stream(stream)))
+
+
 def stencil_sweep_host(ctx: Context, a: HPCHighDimensionFlatArray, b: HPCHighDimensionFlatArray,
                        kind: int, radius: int = 0, steps: int = 1, variant: int = VARIANT_AUTO):
     """The reference-facing call: host containers in, host containers out.

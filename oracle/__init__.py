@@ -266,3 +266,46 @@ def cg(rp, col, val, b, x0, max_iters: int, tol: float = 0.0):
             _p(np.ascontiguousarray(val)), _p(b), _p(x), C.c_int64(max_iters), C.c_double(tol),
             C.byref(rr), C.byref(bb))
     return x, int(it), rr.value, bb.value
+
+
+# ------------------------------------------------------------------ conv2d / transpose (8f-2, 8f-3)
+def conv2d(a_in: np.ndarray, a_out: np.ndarray, w: np.ndarray, ny, nx, ilo, ihi, olo=0, ohi=0):
+    """out(y,x) += sum in(y+l,x+k) w(l,k) on flat reference-layout buffers; returns the new out."""
+    out = np.ascontiguousarray(a_out).copy()
+    w = np.ascontiguousarray(w, dtype=out.dtype)
+    fn = lib().orc_conv2d_f32 if out.dtype == np.float32 else lib().orc_conv2d_f64
+    fn(_p(np.ascontiguousarray(a_in, dtype=out.dtype)), _p(out), _p(w), C.c_int64(ny), C.c_int64(nx),
+       C.c_int64(ilo), C.c_int64(ihi), C.c_int64(olo), C.c_int64(ohi), C.c_int(w.shape[0]), C.c_int(w.shape[1]))
+    return out
+
+
+def transpose(a_in: np.ndarray, ny, nx, ilo=0, ihi=0, olo=0, ohi=0) -> np.ndarray:
+    a_in = np.ascontiguousarray(a_in)
+    out = np.zeros((nx + olo + ohi) * (ny + olo + ohi), dtype=a_in.dtype)
+    lib().orc_transpose(_p(a_in), _p(out), C.c_int64(ny), C.c_int64(nx), C.c_int64(ilo), C.c_int64(ihi),
+                        C.c_int64(olo), C.c_int64(ohi), C.c_int(a_in.dtype.itemsize))
+    return out
+
+
+def ref_conv(which: str, ka: np.ndarray, kb: np.ndarray, kc: np.ndarray, n: int) -> np.ndarray:
+    """The reference's BM_conv ("scalar") / BM_conv_block ("block") loop on an n x n grid:
+    ka flat n*n, kb flat <2,float,16> of (n, n), kc flat 16*16.  Returns the updated ka."""
+    r = ref()
+    if r is None:
+        raise RuntimeError("oracle/_ref/libhpcref.so was not built (reference tree absent)")
+    ka = np.ascontiguousarray(ka, dtype=np.float32).copy()
+    r.hpcref_conv(C.c_int({"scalar": 0, "block": 1}[which]), _p(ka),
+                  _p(np.ascontiguousarray(kb, dtype=np.float32)),
+                  _p(np.ascontiguousarray(kc, dtype=np.float32)), C.c_int64(n))
+    return ka
+
+
+def ref_transpose(which: str, a: np.ndarray, n: int) -> np.ndarray:
+    """BM_transpose ("scalar") / BM_transpose_tiling ("tiling", n % 64 == 0) on an n x n grid."""
+    r = ref()
+    if r is None:
+        raise RuntimeError("oracle/_ref/libhpcref.so was not built (reference tree absent)")
+    b = np.empty(n * n, dtype=np.float32)
+    r.hpcref_transpose(C.c_int({"scalar": 0, "tiling": 1}[which]),
+                       _p(np.ascontiguousarray(a, dtype=np.float32)), _p(b), C.c_int64(n))
+    return b

@@ -536,3 +536,39 @@ ORC_API int orc_csr_localize(int64_t nrows, const int64_t *row_ptr, const int32_
   }
 ORC_CG(orc_cg_f64, double, orc_spmv_f64)
 ORC_CG(orc_cg_f32, float, orc_spmv_f32)
+
+/* ------------------------------------------------------------------ conv2d
+ * Reference-pinned: BM_conv (tests/test_hpc_benchmark/test_hpc_benchmark.cpp:792-806):
+ *   ka(y,x) += kb(y+l, x+k) * kc(l,k), l outer, k inner, accumulating onto ka's value.
+ * in: flat <2,T,ilo,ihi> (ihi >= kh-1, kw-1); out: flat <2,T,olo,ohi>, updated in place. */
+#define ORC_CONV(NAME, T)                                                                      \
+  ORC_API void NAME(const T *in, T *out, const T *w, int64_t ny, int64_t nx, int64_t ilo,       \
+                    int64_t ihi, int64_t olo, int64_t ohi, int kh, int kw) {                   \
+    const int64_t pi = nx + ilo + ihi, po = nx + olo + ohi;                                    \
+    _Pragma("omp parallel for") for (int64_t y = 0; y < ny; ++y) {                              \
+      for (int64_t x = 0; x < nx; ++x) {                                                       \
+        T s = out[(y + olo) * po + olo + x];                                                   \
+        for (int l = 0; l < kh; ++l)                                                           \
+          for (int k = 0; k < kw; ++k) {                                                       \
+            const T prod = in[(y + l + ilo) * pi + ilo + x + k] * w[l * kw + k];               \
+            s = s + prod;                                                                      \
+          }                                                                                    \
+        out[(y + olo) * po + olo + x] = s;                                                     \
+      }                                                                                        \
+    }                                                                                          \
+  }
+ORC_CONV(orc_conv2d_f32, float)
+ORC_CONV(orc_conv2d_f64, double)
+
+/* ------------------------------------------------------------------ transpose
+ * Reference-pinned: BM_transpose (…:672-683): b_t(x, y) = a_t(y, x).  in: flat <2,ilo,ihi> of
+ * (ny, nx); out: flat <2,olo,ohi> of (nx, ny); es = element size in bytes. */
+ORC_API void orc_transpose(const void *in, void *out, int64_t ny, int64_t nx, int64_t ilo,
+                           int64_t ihi, int64_t olo, int64_t ohi, int es) {
+  const int64_t pi = nx + ilo + ihi, po = ny + olo + ohi;
+#pragma omp parallel for
+  for (int64_t y = 0; y < ny; ++y)
+    for (int64_t x = 0; x < nx; ++x)
+      memcpy((char *)out + ((x + olo) * po + olo + y) * es,
+             (const char *)in + ((y + ilo) * pi + ilo + x) * es, (size_t)es);
+}

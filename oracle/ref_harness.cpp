@@ -48,6 +48,32 @@ std::unique_ptr<ArrB> g_b;
 #undef a
 #undef b
 
+// Second cut (oracle/Makefile: _ref/ref_bodies2.inc): BM_transpose, BM_transpose_tiling
+// (test_hpc_benchmark.cpp:672-682, 684-698) and BM_conv, BM_conv_block (:793-806, 808-818), with
+// the globals they name: a_t / b_t (:669-670), ka / kb / kc, conv_n, nkern, conv_block (:786-791)
+// and `ma` (:747, only handed to DoNotOptimize by BM_conv).
+constexpr int conv_block = 4;  // :786
+constexpr int nkern = 16;      // :788
+using ArrK = hpc::HPCHighDimensionFlatArray<2, float, nkern>;  // kb, :790
+int conv_n = 0;                // runtime here (constexpr 1 << 10 in the reference, :787)
+int ma = 0;
+std::unique_ptr<ArrB> g_at, g_bt, g_ka, g_kc;
+std::unique_ptr<ArrK> g_kb;
+#define a_t (*g_at)
+#define b_t (*g_bt)
+#define ka (*g_ka)
+#define kb (*g_kb)
+#define kc (*g_kc)
+#pragma GCC diagnostic push
+#pragma GCC diagnostic ignored "-Wunused-variable"
+#include "ref_bodies2.inc"
+#pragma GCC diagnostic pop
+#undef a_t
+#undef b_t
+#undef ka
+#undef kb
+#undef kc
+
 // Exposes the protected index helpers of the reference container.
 template <std::size_t D, std::size_t Lo, std::size_t Hi>
 struct Probe : hpc::HPCHighDimensionFlatArray<D, float, Lo, Hi> {
@@ -134,6 +160,38 @@ __attribute__((visibility("default"))) void hpcref_blur_run(int which) {
 __attribute__((visibility("default"))) void hpcref_blur_result(float *b_flat) {
   _mm_sfence();
   std::memcpy(b_flat, g_b->data(), sizeof(float) * ny * nx);
+}
+
+// which: 0 BM_conv, 1 BM_conv_block (n % 4 == 0).  ka_flat: n*n (updated in place), kb_flat:
+// (n+32)^2 in the reference layout of <2,float,16>, kc_flat: 16*16.
+__attribute__((visibility("default"))) void hpcref_conv(int which, float *ka_flat, const float *kb_flat,
+                                                        const float *kc_flat, int64_t n) {
+  conv_n = (int)n;
+  g_ka.reset(new ArrB(n, n));
+  g_kb.reset(new ArrK(n, n));
+  g_kc.reset(new ArrB(nkern, nkern));
+  std::memcpy(g_ka->data(), ka_flat, sizeof(float) * n * n);
+  std::memcpy(g_kb->data(), kb_flat, sizeof(float) * (n + 2 * nkern) * (n + 2 * nkern));
+  std::memcpy(g_kc->data(), kc_flat, sizeof(float) * nkern * nkern);
+  benchmark::State st;
+  if (which == 0) BM_conv(st); else BM_conv_block(st);
+  std::memcpy(ka_flat, g_ka->data(), sizeof(float) * n * n);
+  g_ka.reset();
+  g_kb.reset();
+  g_kc.reset();
+}
+// which: 0 BM_transpose, 1 BM_transpose_tiling (n % 64 == 0).  n x n floats each.
+__attribute__((visibility("default"))) void hpcref_transpose(int which, const float *a_flat, float *b_flat,
+                                                             int64_t n) {
+  nx = ny = (std::size_t)n;
+  g_at.reset(new ArrB(n, n));
+  g_bt.reset(new ArrB(n, n));
+  std::memcpy(g_at->data(), a_flat, sizeof(float) * n * n);
+  benchmark::State st;
+  if (which == 0) BM_transpose(st); else BM_transpose_tiling(st);
+  std::memcpy(b_flat, g_bt->data(), sizeof(float) * n * n);
+  g_at.reset();
+  g_bt.reset();
 }
 
 // Index math of the reference container for the (D, Lo, Hi) instantiations the tests use.
