@@ -172,19 +172,24 @@ transpose_tile_kernel(const T *__restrict__ in, T *__restrict__ out, Geom2 gi, G
   }
 }
 
+std::vector<unsigned char> g_last_weights;  // what c_weights holds, and the stream that put it there
+cudaStream_t g_last_stream = nullptr;
+int g_last_es = 0;
+
 template <typename T>
 hpcx_status conv2d_t(hpcx_grid in, hpcx_grid out, const T *w, int kh, int kw, int variant, cudaStream_t s) {
   hpcx_ctx ctx = in->ctx;
   // Weights go through the stream so that back-to-back calls with different kernels stay
   // ordered; an unchanged kernel (the iterative use) is not uploaded again.  One device per
   // process (one process per GPU), so one cache suffices.
-  static std::vector<unsigned char> last;
-  static cudaStream_t last_stream = nullptr;
+  std::vector<unsigned char> &last = g_last_weights;  // shared by the fp32 and fp64 paths: one symbol
   const size_t wb = (size_t)kh * kw * sizeof(T);
-  if (last.size() != wb || last_stream != s || memcmp(last.data(), w, wb) != 0) {
+  if (last.size() != wb || g_last_stream != s || g_last_es != (int)sizeof(T) ||
+      memcmp(last.data(), w, wb) != 0) {
     HPCX_CUDA(ctx, cudaMemcpyToSymbolAsync(c_weights, w, wb, 0, cudaMemcpyHostToDevice, s));
     last.assign((const unsigned char *)w, (const unsigned char *)w + wb);
-    last_stream = s;
+    g_last_stream = s;
+    g_last_es = (int)sizeof(T);
   }
   const Geom2 gi = geom2(in), go = geom2(out);
   if (kh == 16 && kw == 16 && variant != HPCX_VARIANT_DIRECT) {

@@ -74,6 +74,11 @@ def test_conv_accumulates_across_calls_and_kernel_changes(ctx):
     # a different kernel right after: the cached constant-memory weights must be replaced
     kc2 = oracle.fill(256, 4, np.float32).reshape(16, 16)
     assert bits_equal(_conv(ctx, kb, ka, kc2, n, n, 16, 16), oracle.conv2d(kb, ka, kc2, n, n, 16, 16))
+    # fp64 with other weights in between, then the fp32 kernel again (one constant symbol serves both)
+    kb64, ka64, kc64 = kb.astype(np.float64), ka.astype(np.float64), oracle.fill(256, 5, np.float64).reshape(16, 16)
+    assert bits_equal(_conv(ctx, kb64, ka64, kc64, n, n, 16, 16, dtype=np.float64),
+                      oracle.conv2d(kb64, ka64, kc64, n, n, 16, 16))
+    assert bits_equal(_conv(ctx, kb, ka, kc2, n, n, 16, 16), oracle.conv2d(kb, ka, kc2, n, n, 16, 16))
 
 
 def test_conv_full_reference_size_1024(ctx):
