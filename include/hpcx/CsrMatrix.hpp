@@ -200,14 +200,79 @@ class DeviceCsr {
     HPCX_CHECK(ctx_, hpcx_spmv(A_, x, HPCX_MEM_DEVICE, y, HPCX_MEM_DEVICE, stream));
   }
 
+  // Device assembly from an edge (COO) list, duplicates merged by adding in list order
+  // (hpcx_csr_from_coo): the arrays never visit the host.
+  static DeviceCsr from_coo(hpcx::Context &ctx, std::size_t nrows, const std::vector<std::int32_t> &rows,
+                            const std::vector<std::int32_t> &cols, const std::vector<T> &vals,
+                            const hpcx_csr_opts *opts = nullptr) {
+    if (rows.size() != cols.size() || rows.size() != vals.size())
+      throw std::out_of_range("invalid index, out of boundary");
+    hpcx_csr_arrays arr{};
+    HPCX_CHECK(ctx.handle(), hpcx_csr_from_coo(ctx.handle(), static_cast<int64_t>(nrows),
+                                               static_cast<int64_t>(rows.size()), rows.data(), cols.data(),
+                                               vals.data(), hpcx::dtypeOf<T>(), HPCX_MEM_HOST, 4, &arr));
+    hpcx_csr_desc d{};
+    d.nrows = d.ncols = static_cast<int64_t>(nrows);
+    d.nnz = arr.nnz;
+    d.row_ptr = arr.row_ptr;
+    d.idx_bytes = 4;
+    d.dtype = hpcx::dtypeOf<T>();
+    d.col_idx = arr.col_idx;
+    d.values = arr.values;
+    d.mem = HPCX_MEM_DEVICE;
+    DeviceCsr out(ctx.handle(), nrows);
+    const hpcx_status st = hpcx_csr_create(ctx.handle(), &d, opts, &out.A_);
+    hpcx_device_free(ctx.handle(), arr.row_ptr);
+    hpcx_device_free(ctx.handle(), arr.col_idx);
+    hpcx_device_free(ctx.handle(), arr.values);
+    HPCX_CHECK(ctx.handle(), st);
+    return out;
+  }
+  DeviceCsr(DeviceCsr &&o) noexcept : ctx_(o.ctx_), A_(o.A_), nrows_(o.nrows_), ncols_(o.ncols_) { o.A_ = nullptr; }
+
   hpcx_csr handle() const noexcept { return A_; }
+  hpcx_ctx context() const noexcept { return ctx_; }
   std::size_t nrows() const noexcept { return nrows_; }
   std::size_t ncols() const noexcept { return ncols_; }
 
  private:
+  DeviceCsr(hpcx_ctx ctx, std::size_t n) : ctx_(ctx), nrows_(n), ncols_(n) {}
   hpcx_ctx ctx_ = nullptr;
   hpcx_csr A_ = nullptr;
   std::size_t nrows_ = 0, ncols_ = 0;
+};
+
+// Conjugate gradients around the product (hpcx_cg_*): q = A*p with <p, q> fused
+// into the SpMV kernel, scalars resident on the device.  A must be symmetric positive definite.
+struct CgResult {
+  int iterations = 0;
+  bool converged = false;
+  double rr = 0, bb = 0;  // ||r||^2 (recurrence) and ||b||^2
+};
+template <typename T>
+class CgSolver {
+ public:
+  explicit CgSolver(const DeviceCsr<T> &A) : ctx_(A.context()) { HPCX_CHECK(ctx_, hpcx_cg_create(A.handle(), &S_)); }
+  ~CgSolver() {
+    if (S_) hpcx_cg_destroy(S_);
+  }
+  CgSolver(const CgSolver &) = delete;
+  CgSolver &operator=(const CgSolver &) = delete;
+
+  // x is the start vector and receives the iterate (host containers).
+  template <class AllocB, class AllocX>
+  CgResult solve(const std::vector<T, AllocB> &b, std::vector<T, AllocX> &x, int max_iters, double rel_tol = 0.0,
+                 int check_every = 0) {
+    if (b.size() != x.size()) throw std::out_of_range("invalid index, out of boundary");
+    hpcx_cg_result r{};
+    HPCX_CHECK(ctx_, hpcx_cg_solve(S_, b.data(), HPCX_MEM_HOST, x.data(), HPCX_MEM_HOST, max_iters, rel_tol,
+                                   check_every, &r, nullptr));
+    return CgResult{r.iterations, r.converged != 0, r.rr, r.bb};
+  }
+
+ private:
+  hpcx_ctx ctx_ = nullptr;
+  hpcx_cg S_ = nullptr;
 };
 
 // y = A*x with host containers: the reference-facing free function.

@@ -14,6 +14,10 @@
 //       3-D 7-point Jacobi (new); a and b hold the same Dirichlet ghosts;
 //       afterwards b is the newest iterate and a the one before it.
 //
+//   hpc::conv2d(ka, kb, kc)      ka(y,x) += sum_{l,k} kb(y+l, x+k) * kc(l,k): BM_conv / BM_conv_block
+//       (:786-818; kb is <2,T,nkern>, kc an nkern x nkern host array); bit-identical for 16 x 16.
+//   hpc::transpose(a_t, b_t)     b_t(x,y) = a_t(y,x): BM_transpose / BM_transpose_tiling (:669-698).
+//
 // hpc::DeviceGrid is the device-resident mirror for callers that iterate without going back
 // to the host (the reference's analogue is a std::vector over CudaAllocator,
 // lib/gpu/util/include/cudaAllocator.hpp:39-83).
@@ -107,7 +111,45 @@ void stencil_sweep(DeviceGrid<3, T, Lo, Hi> &in, DeviceGrid<3, T, Lo, Hi> &out, 
   HPCX_CHECK(in.context(), hpcx_stencil_sweep(in.handle(), out.handle(), &st, j.steps, stream));
 }
 
+// ka(y,x) += sum_{l<KH} sum_{k<KW} kb(y+l, x+k) * kc(l,k)   (BM_conv, test_hpc_benchmark.cpp:793-806)
+template <typename T, std::size_t Lo, std::size_t Hi, std::size_t Lo2, std::size_t Hi2, std::size_t A,
+          class Al>
+void conv2d(DeviceGrid<2, T, Lo, Hi> &ka, DeviceGrid<2, T, Lo2, Hi2> &kb,
+            const HPCHighDimensionFlatArray<2, T, 0, 0, A, Al> &kc, void *stream = nullptr,
+            int variant = HPCX_VARIANT_AUTO) {
+  const auto d = kc.dim();
+  HPCX_CHECK(ka.context(), hpcx_conv2d(kb.handle(), ka.handle(), kc.data(), static_cast<int32_t>(d[0]),
+                                       static_cast<int32_t>(d[1]), variant, stream));
+}
+
+// b_t(x,y) = a_t(y,x)   (BM_transpose, test_hpc_benchmark.cpp:672-682)
+template <typename T, std::size_t Lo, std::size_t Hi, std::size_t Lo2, std::size_t Hi2>
+void transpose(DeviceGrid<2, T, Lo, Hi> &a_t, DeviceGrid<2, T, Lo2, Hi2> &b_t, void *stream = nullptr) {
+  HPCX_CHECK(a_t.context(), hpcx_grid_transpose(a_t.handle(), b_t.handle(), stream));
+}
+
 // ---- host containers in, host containers out (the reference-facing call)
+template <typename T, std::size_t Hi, std::size_t Lo2, std::size_t Hi2, std::size_t A, class Al, std::size_t A2,
+          class Al2, std::size_t A3, class Al3>
+void conv2d(hpcx::Context &ctx, HPCHighDimensionFlatArray<2, T, 0, Hi, A, Al> &ka,
+            const HPCHighDimensionFlatArray<2, T, Lo2, Hi2, A2, Al2> &kb,
+            const HPCHighDimensionFlatArray<2, T, 0, 0, A3, Al3> &kc) {
+  DeviceGrid<2, T, 0, Hi> da(ctx, ka);
+  DeviceGrid<2, T, Lo2, Hi2> db(ctx, kb);
+  conv2d(da, db, kc);
+  da.download(ka);
+}
+
+template <typename T, std::size_t Lo, std::size_t Hi, std::size_t A, class Al, std::size_t Lo2, std::size_t Hi2,
+          std::size_t A2, class Al2>
+void transpose(hpcx::Context &ctx, const HPCHighDimensionFlatArray<2, T, Lo, Hi, A, Al> &a_t,
+               HPCHighDimensionFlatArray<2, T, Lo2, Hi2, A2, Al2> &b_t) {
+  DeviceGrid<2, T, Lo, Hi> da(ctx, a_t);
+  DeviceGrid<2, T, Lo2, Hi2> db(ctx, b_t.dim());
+  transpose(da, db);
+  db.download(b_t);
+}
+
 template <typename T, std::size_t Lo, std::size_t Hi, std::size_t A, class Al, std::size_t Lo2,
           std::size_t Hi2, std::size_t A2, class Al2>
 void stencil_sweep(hpcx::Context &ctx, const HPCHighDimensionFlatArray<2, T, Lo, Hi, A, Al> &a,

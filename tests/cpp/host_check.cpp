@@ -205,6 +205,72 @@ static int run_gpu() {
       std::printf("spmv_short_x out_of_range\n");
     }
   }
+  {  // BM_conv's loop nest (test_hpc_benchmark.cpp:793-806) and BM_transpose's (:672-682)
+    constexpr int nkern = 16;
+    const int n = 96;
+    hpc::HPCHighDimensionFlatArray<2, float> ka(n, n), want(n, n), kc(nkern, nkern);
+    hpc::HPCHighDimensionFlatArray<2, float, nkern> kb(n, n);
+    for (std::size_t i = 0; i < ka.size(); ++i) ka.data()[i] = want.data()[i] = frand(seed);
+    for (std::size_t i = 0; i < kb.size(); ++i) kb.data()[i] = frand(seed);
+    for (std::size_t i = 0; i < kc.size(); ++i) kc.data()[i] = frand(seed);
+    for (int y = 0; y < n; y++)
+      for (int x = 0; x < n; ++x)
+        for (int l = 0; l < nkern; ++l)
+          for (int k = 0; k < nkern; ++k) want(y, x) += kb(y + l, x + k) * kc(l, k);
+    hpc::conv2d(ctx, ka, kb, kc);
+    int same = std::memcmp(ka.data(), want.data(), ka.size() * sizeof(float)) == 0;
+    std::printf("conv2d bit_exact %d\n", same);
+    bad += !same;
+    const int ny = 70, nx = 200;
+    hpc::HPCHighDimensionFlatArray<2, float> a_t(ny, nx), b_t(nx, ny), bw(nx, ny);
+    for (std::size_t i = 0; i < a_t.size(); ++i) a_t.data()[i] = frand(seed);
+    for (int y = 0; y < ny; ++y)
+      for (int x = 0; x < nx; ++x) bw(x, y) = a_t(y, x);
+    hpc::transpose(ctx, a_t, b_t);
+    same = std::memcmp(b_t.data(), bw.data(), bw.size() * sizeof(float)) == 0;
+    std::printf("transpose bit_exact %d\n", same);
+    bad += !same;
+  }
+  {  // COO assembly on the device + CG around the product
+    const int n = 40;
+    auto A = sparse::CsrMatrix<double>::laplace2d(n, n);
+    std::vector<std::int32_t> rows, cols;
+    std::vector<double> vals;
+    for (std::size_t i = 0; i < A.nrows(); ++i)
+      for (auto p = A.row_ptr()[i]; p < A.row_ptr()[i + 1]; ++p) {
+        // every entry split in two halves listed far apart: the merge must add them back
+        rows.push_back((std::int32_t)i);
+        cols.push_back(A.col_idx()[p]);
+        vals.push_back(0.5 * A.values()[p]);
+      }
+    const std::size_t half = rows.size();
+    for (std::size_t e = half; e-- > 0;) {
+      rows.push_back(rows[e]);
+      cols.push_back(cols[e]);
+      vals.push_back(vals[e]);
+    }
+    auto dA = sparse::DeviceCsr<double>::from_coo(ctx, A.nrows(), rows, cols, vals);
+    sparse::DeviceCsr<double> dRef(ctx, A);
+    std::vector<double> x(A.ncols()), y1, y2;
+    for (auto &v : x) v = frand(seed);
+    sparse::spmv(dA, x, y1);
+    sparse::spmv(dRef, x, y2);
+    const int same = std::memcmp(y1.data(), y2.data(), y1.size() * 8) == 0;
+    std::printf("from_coo product bit_exact %d\n", same);
+    bad += !same;
+    std::vector<double> xs(A.nrows()), b, sol(A.nrows(), 0.0);
+    for (auto &v : xs) v = frand(seed);
+    sparse::spmv(dRef, xs, b);
+    sparse::CgSolver<double> cg(dA);
+    const sparse::CgResult res = cg.solve(b, sol, 1000, 1e-11, 16);
+    double err = 0, mag = 0;
+    for (std::size_t i = 0; i < sol.size(); ++i) {
+      err = std::fmax(err, std::fabs(sol[i] - xs[i]));
+      mag = std::fmax(mag, std::fabs(xs[i]));
+    }
+    std::printf("cg iterations %d converged %d rel_err %.3e\n", res.iterations, (int)res.converged, err / mag);
+    bad += !(res.converged && err <= 1e-8 * mag);
+  }
   std::printf("launches %lld\n", (long long)ctx.launchCount());
   std::printf(bad ? "CPP GPU FAIL\n" : "CPP GPU OK\n");
   return bad;
