@@ -10,8 +10,11 @@
  *     (orc_box_sweep_*).  tests/test_oracle_vs_ref.py compares them bit-for-bit with the
  *     reference's own header and loop bodies compiled into oracle/_ref/libhpcref.so
  *     (oracle/Makefile), on this container; golden digests are committed in tests/golden/.
+ *     The 16 x 16 convolution (orc_conv2d_*) and the transpose (orc_transpose) are pinned the
+ *     same way against BM_conv / BM_conv_block / BM_transpose / BM_transpose_tiling
+ *     (tests/test_oracle_dense2d.py, tests/golden/dense2d_ref.npz).
  *   - PARITY UNPINNED by reference tests: CSR builders, SpMV, SELL, Jacobi-7, pack/unpack,
- *     partitioner and halo maps.  The reference contains no such code and no golden
+ *     partitioner, halo maps and the CG step.  The reference contains no such code and no golden
  *     vectors; these are restatements of the contract in include/hpcx.h,
  *     pinned by analytic known-answer tests in tests/test_oracle_kat.py.
  *
