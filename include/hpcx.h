@@ -242,6 +242,25 @@ HPCX_API hpcx_status hpcx_csr_from_coo(hpcx_ctx ctx, int64_t nrows, int64_t nedg
                                        const int32_t *rows, const int32_t *cols,
                                        const void *vals, int32_t dtype, int32_t mem,
                                        int32_t idx_bytes, hpcx_csr_arrays *out);
+/* Sparse-grid bridge: the 5-point operator over the ACTIVE cells of a sparse
+ * 2-D grid — the (x, y) coordinates sparse::RootGrid::foreach enumerates (reference
+ * lib/sparse/include/RootGrid.hpp:20-22, 62-75), in any order, repeats allowed.  Rows are the
+ * distinct cells in (x, y) lexicographic order (x-major, like DenseBlock's m_block[x*B + y],
+ * DenseBlock.hpp:24-28); row r holds 4 on the diagonal and -1 for each of (x-1,y), (x,y-1),
+ * (x,y+1), (x+1,y) that is active (an inactive neighbour is a Dirichlet zero), columns
+ * ascending.  `map` (may be NULL) receives device arrays: cell_row[ncells] = row of each input
+ * cell, row_x / row_y[nrows] = coordinates of each row.  All result arrays are DEVICE memory
+ * owned by the caller (hpcx_device_free). */
+typedef struct {
+  int64_t nrows;
+  int32_t *cell_row;
+  int32_t *row_x;
+  int32_t *row_y;
+} hpcx_cell_map;
+HPCX_API hpcx_status hpcx_csr_from_cells(hpcx_ctx ctx, int64_t ncells, const int32_t *xs,
+                                         const int32_t *ys, int32_t mem, int32_t dtype,
+                                         int32_t idx_bytes, hpcx_csr_arrays *out,
+                                         hpcx_cell_map *map);
 /* Counter-based generators of the synthetic configs, on the device (bit-identical to the
  * host generators).  R-MAT edge k: `scale` quadrant choices with
  * (a,b,c,d) = (.57,.19,.19,.05) from u(seed, k*scale + level), value (float)(2u(seed+1,k)-1).

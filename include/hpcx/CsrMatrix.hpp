@@ -24,6 +24,7 @@
 #include <stdexcept>
 #include <tuple>
 #include <utility>
+#include <mutex>
 #include <vector>
 
 #include "AlignedAlloc.hpp"
@@ -175,6 +176,20 @@ class CsrMatrix {
   buffer<T> values_;
 };
 
+// Sparse-grid bridge (hpcx_csr_from_cells): the 5-point operator over the active
+// cells of a sparse 2-D grid.  `Grid` is anything with the reference's
+// sparse::RootGrid<T, Layout>::foreach(func(x, y, value&)) (lib/sparse/include/RootGrid.hpp:20-22,
+// 62-75; the leaves call func concurrently, hence the lock).  Row r of the operator is the r-th
+// distinct cell in (x, y) order; `cells` receives those coordinates, `x0` the cells' values.
+struct ActiveCells {
+  std::vector<std::int32_t> row_x, row_y;
+};
+template <typename T>
+class DeviceCsr;
+template <typename T, typename Grid>
+DeviceCsr<T> csr_from_grid(hpcx::Context &ctx, Grid &grid, ActiveCells *cells = nullptr,
+                           std::vector<T> *x0 = nullptr, const hpcx_csr_opts *opts = nullptr);
+
 // Device-resident matrix (hpcx_csr_create): upload once, multiply many times.
 template <typename T>
 class DeviceCsr {
@@ -236,6 +251,9 @@ class DeviceCsr {
   std::size_t ncols() const noexcept { return ncols_; }
 
  private:
+  template <typename U, typename Grid>
+  friend DeviceCsr<U> csr_from_grid(hpcx::Context &, Grid &, ActiveCells *, std::vector<U> *,
+                                    const hpcx_csr_opts *);
   DeviceCsr(hpcx_ctx ctx, std::size_t n) : ctx_(ctx), nrows_(n), ncols_(n) {}
   hpcx_ctx ctx_ = nullptr;
   hpcx_csr A_ = nullptr;
@@ -290,6 +308,54 @@ void spmv(const DeviceCsr<T> &A, const std::vector<T, AllocX> &x, std::vector<T,
   if (x.size() != A.ncols()) throw std::out_of_range("invalid index, out of boundary");
   y.resize(A.nrows());
   A.multiply(x.data(), y.data());
+}
+
+template <typename T, typename Grid>
+DeviceCsr<T> csr_from_grid(hpcx::Context &ctx, Grid &grid, ActiveCells *cells, std::vector<T> *x0,
+                           const hpcx_csr_opts *opts) {
+  std::vector<std::int32_t> xs, ys;
+  std::vector<T> vs;
+  std::mutex mu;
+  grid.foreach ([&](auto x, auto y, auto &value) {
+    std::lock_guard<std::mutex> lock(mu);
+    xs.push_back(static_cast<std::int32_t>(x));
+    ys.push_back(static_cast<std::int32_t>(y));
+    vs.push_back(static_cast<T>(value));
+  });
+  hpcx_csr_arrays arr{};
+  hpcx_cell_map map{};
+  HPCX_CHECK(ctx.handle(), hpcx_csr_from_cells(ctx.handle(), static_cast<int64_t>(xs.size()), xs.data(), ys.data(),
+                                               HPCX_MEM_HOST, hpcx::dtypeOf<T>(), 4, &arr, &map));
+  const std::size_t m = static_cast<std::size_t>(map.nrows);
+  std::vector<std::int32_t> cell_row(xs.size());
+  hpcx_status st = HPCX_OK;
+  if (!xs.empty()) st = hpcx_memcpy(ctx.handle(), cell_row.data(), map.cell_row, xs.size() * 4);
+  if (cells && st == HPCX_OK) {
+    cells->row_x.resize(m);
+    cells->row_y.resize(m);
+    if (m) st = hpcx_memcpy(ctx.handle(), cells->row_x.data(), map.row_x, m * 4);
+    if (m && st == HPCX_OK) st = hpcx_memcpy(ctx.handle(), cells->row_y.data(), map.row_y, m * 4);
+  }
+  if (x0 && st == HPCX_OK) {
+    x0->assign(m, T{});
+    for (std::size_t i = 0; i < xs.size(); ++i) (*x0)[cell_row[i]] = vs[i];
+  }
+  hpcx_csr_desc d{};
+  d.nrows = d.ncols = map.nrows;
+  d.nnz = arr.nnz;
+  d.row_ptr = arr.row_ptr;
+  d.idx_bytes = 4;
+  d.dtype = hpcx::dtypeOf<T>();
+  d.col_idx = arr.col_idx;
+  d.values = arr.values;
+  d.mem = HPCX_MEM_DEVICE;
+  DeviceCsr<T> out(ctx.handle(), m);
+  if (st == HPCX_OK) st = hpcx_csr_create(ctx.handle(), &d, opts, &out.A_);
+  for (void *p : {arr.row_ptr, (void *)arr.col_idx, arr.values, (void *)map.cell_row, (void *)map.row_x,
+                  (void *)map.row_y})
+    if (p) hpcx_device_free(ctx.handle(), p);
+  HPCX_CHECK(ctx.handle(), st);
+  return out;
 }
 
 }  // namespace sparse

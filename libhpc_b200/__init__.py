@@ -6,7 +6,7 @@ the host-side mirror of the reference's container interface over that ABI.
 """
 from . import _abi  # noqa: F401
 from .api import (CgSolver, Context, CsrMatrix, DeviceCsr, DeviceCsrArrays, DeviceGrid, HPCHighDimensionFlatArray,  # noqa: F401
-                  HpcxError, conv2d, csr_from_coo, csr_localize, grid_transpose, partition_rows, partition_slabs, spmv, stencil_sweep,
+                  HpcxError, conv2d, csr_from_cells, csr_from_coo, csr_localize, grid_transpose, partition_rows, partition_slabs, spmv, stencil_sweep,
                   synth_field, synth_rmat_csr,
                   stencil_sweep_host)
 from ._abi import (F32, F64, MEM_DEVICE, MEM_HOST, SPMV_SELL, SPMV_STREAM, SPMV_VECTOR,  # noqa: F401

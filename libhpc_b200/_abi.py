@@ -56,6 +56,10 @@ class CgResult(C.Structure):
                 ("bb", C.c_double)]
 
 
+class CellMap(C.Structure):
+    _fields_ = [("nrows", C.c_int64), ("cell_row", C.c_void_p), ("row_x", C.c_void_p), ("row_y", C.c_void_p)]
+
+
 class HaloSizes(C.Structure):
     _fields_ = [("nloc", C.c_int64), ("nnz_loc", C.c_int64), ("nhalo", C.c_int64),
                 ("nsend", C.c_int64)]
@@ -99,6 +103,7 @@ PROTOTYPES = {
     "hpcx_csr_sell_info": (_i32, [_vp, _P(_i64), _P(_i64), _P(_i32), _P(_i32)]),
     "hpcx_csr_sell_download": (_i32, [_vp, _vp, _vp, _vp, _vp, _vp]),
     "hpcx_csr_from_coo": (_i32, [_vp, _i64, _i64, _vp, _vp, _vp, _i32, _i32, _i32, _P(CsrArrays)]),
+    "hpcx_csr_from_cells": (_i32, [_vp, _i64, _vp, _vp, _i32, _i32, _i32, _P(CsrArrays), _P(CellMap)]),
     "hpcx_synth_rmat_coo": (_i32, [_vp, _i32, _i64, C.c_uint64, _vp, _vp, _vp]),
     "hpcx_synth_field": (_i32, [_vp, C.c_uint64, _i64, _i64, _i32, _vp]),
     "hpcx_partition_rows": (_i32, [_i64, _vp, _i32, _i32, _i32, _vp]),

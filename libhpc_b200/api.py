@@ -497,6 +497,33 @@ def csr_from_coo(ctx: Context, nrows: int, rows, cols, vals, idx_bytes: int = 4,
     return DeviceCsrArrays(ctx, nrows, idx_bytes, dtype, raw)
 
 
+def csr_from_cells(ctx: Context, xs, ys, dtype=np.float64, idx_bytes: int = 4, ncells: int | None = None):
+    """Sparse-grid bridge (hpcx_csr_from_cells): the 5-point operator over the active cells
+    (x, y) of a sparse 2-D grid — what sparse::RootGrid::foreach enumerates.  Returns
+    (DeviceCsrArrays, map) with map = dict(nrows, cell_row, row_x, row_y) as host int32 arrays."""
+    px, mx = _ptr(xs)
+    py, my = _ptr(ys)
+    if mx != my:
+        raise ValueError("xs and ys must live in the same memory space")
+    if isinstance(xs, np.ndarray) and (xs.dtype != np.int32 or ys.dtype != np.int32):
+        raise TypeError("xs and ys must be int32")
+    n = len(xs) if ncells is None else int(ncells)
+    raw, cm = _abi.CsrArrays(), _abi.CellMap()
+    ctx.check(ctx.lib.hpcx_csr_from_cells(ctx.h, n, px, py, mx, _dtype_code(dtype), idx_bytes,
+                                          C.byref(raw), C.byref(cm)))
+    arrays = DeviceCsrArrays(ctx, cm.nrows, idx_bytes, dtype, raw)
+    out = dict(nrows=int(cm.nrows))
+    for name, count in (("cell_row", n), ("row_x", cm.nrows), ("row_y", cm.nrows)):
+        a = np.empty(count, dtype=np.int32)
+        p = getattr(cm, name)
+        if count:
+            ctx.memcpy(a, (p, MEM_DEVICE), a.nbytes)
+        if p:
+            ctx.device_free(p)
+        out[name] = a
+    return arrays, out
+
+
 def synth_rmat_csr(ctx: Context, scale: int, edge_factor: int = 16, seed: int = 24,
                    idx_bytes: int = 4) -> DeviceCsrArrays:
     """C5 on the device: R-MAT edges (hpcx_synth_rmat_coo) assembled by hpcx_csr_from_coo.

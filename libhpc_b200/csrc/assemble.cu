@@ -191,6 +191,179 @@ hpcx_status assemble(hpcx_ctx ctx, int64_t nrows, int64_t n, const int32_t *rows
   return HPCX_OK;
 }
 
+
+// ------------------------------------------------------------------ sparse-grid bridge (§8f-4)
+// Cells of a sparse 2-D grid (what sparse::RootGrid::foreach enumerates, reference
+// lib/sparse/include/RootGrid.hpp:20-22, 62-75) -> 5-point operator over the active cells.
+// Rows are the distinct cells in (x, y) lexicographic order (x-major like DenseBlock's
+// m_block[x*B + y], DenseBlock.hpp:24-28); a neighbour that is not active is a Dirichlet zero.
+__device__ __forceinline__ uint64_t cell_key(int32_t x, int32_t y) {
+  return ((uint64_t)((uint32_t)x ^ 0x80000000u) << 32) | (uint64_t)((uint32_t)y ^ 0x80000000u);
+}
+__global__ void cell_keys_kernel(int64_t n, const int32_t *__restrict__ xs, const int32_t *__restrict__ ys,
+                                 uint64_t *__restrict__ keys, int32_t *__restrict__ idx) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    keys[i] = cell_key(xs[i], ys[i]);
+    idx[i] = (int32_t)i;
+  }
+}
+// pos = inclusive head count over the sorted keys: compact the distinct keys, map cells to rows.
+__global__ void cell_rows_kernel(int64_t n, const uint64_t *__restrict__ keys, const int32_t *__restrict__ idx,
+                                 const int32_t *__restrict__ pos, uint64_t *__restrict__ ukeys,
+                                 int32_t *__restrict__ cell_row, int32_t *__restrict__ row_x,
+                                 int32_t *__restrict__ row_y) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const int32_t r = pos[i] - 1;
+    cell_row[idx[i]] = r;
+    if (i == 0 || keys[i] != keys[i - 1]) {
+      const uint64_t k = keys[i];
+      ukeys[r] = k;
+      row_x[r] = (int32_t)((uint32_t)(k >> 32) ^ 0x80000000u);
+      row_y[r] = (int32_t)((uint32_t)k ^ 0x80000000u);
+    }
+  }
+}
+__device__ __forceinline__ int32_t find_key(const uint64_t *__restrict__ ukeys, int64_t m, uint64_t want) {
+  int64_t lo = 0, hi = m;
+  while (lo < hi) {
+    const int64_t mid = (lo + hi) >> 1;
+    if (ukeys[mid] < want) lo = mid + 1; else hi = mid;
+  }
+  return (lo < m && ukeys[lo] == want) ? (int32_t)lo : -1;
+}
+// nbr[4r..4r+3] = rows of (x-1,y), (x,y-1), (x,y+1), (x+1,y) or -1; deg[r] = 1 + active neighbours
+__global__ void cell_neighbours_kernel(int64_t m, const uint64_t *__restrict__ ukeys,
+                                       const int32_t *__restrict__ row_x, const int32_t *__restrict__ row_y,
+                                       int32_t *__restrict__ nbr, int32_t *__restrict__ deg) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < m; r += stride) {
+    const int32_t x = row_x[r], y = row_y[r];
+    int32_t d = 1;
+    const int32_t n0 = x > INT32_MIN ? find_key(ukeys, m, cell_key(x - 1, y)) : -1;
+    const int32_t n1 = y > INT32_MIN ? find_key(ukeys, m, cell_key(x, y - 1)) : -1;
+    const int32_t n2 = y < INT32_MAX ? find_key(ukeys, m, cell_key(x, y + 1)) : -1;
+    const int32_t n3 = x < INT32_MAX ? find_key(ukeys, m, cell_key(x + 1, y)) : -1;
+    nbr[4 * r + 0] = n0;
+    nbr[4 * r + 1] = n1;
+    nbr[4 * r + 2] = n2;
+    nbr[4 * r + 3] = n3;
+    d += (n0 >= 0) + (n1 >= 0) + (n2 >= 0) + (n3 >= 0);
+    deg[r] = d;
+  }
+}
+template <typename T, typename I>
+__global__ void cell_fill_kernel(int64_t m, const int32_t *__restrict__ nbr, const int32_t *__restrict__ start,
+                                 int64_t nnz, I *__restrict__ row_ptr, int32_t *__restrict__ col,
+                                 T *__restrict__ val) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r <= m; r += stride) {
+    if (r == m) {
+      row_ptr[m] = (I)nnz;
+      continue;
+    }
+    int64_t p = start[r];
+    row_ptr[r] = (I)p;
+    // ascending column = ascending (x, y): (x-1,y) < (x,y-1) < (x,y) < (x,y+1) < (x+1,y)
+    if (nbr[4 * r + 0] >= 0) { col[p] = nbr[4 * r + 0]; val[p++] = T(-1); }
+    if (nbr[4 * r + 1] >= 0) { col[p] = nbr[4 * r + 1]; val[p++] = T(-1); }
+    col[p] = (int32_t)r;
+    val[p++] = T(4);
+    if (nbr[4 * r + 2] >= 0) { col[p] = nbr[4 * r + 2]; val[p++] = T(-1); }
+    if (nbr[4 * r + 3] >= 0) { col[p] = nbr[4 * r + 3]; val[p++] = T(-1); }
+  }
+}
+
+template <typename T>
+hpcx_status cells_to_csr(hpcx_ctx ctx, int64_t n, const int32_t *xs, const int32_t *ys, int32_t idx_bytes,
+                         hpcx_csr_arrays *out, hpcx_cell_map *map) {
+  cudaStream_t st = ctx->compute;
+  const size_t nn = (size_t)(n > 0 ? n : 1);
+  DevBuf k0, k1, i0, i1, pos, tmp, ukeys, nbr, deg, start;
+  DevBuf cell_row, row_x, row_y, rp, col, val;  // handed to the caller on success
+  HPCX_CUDA(ctx, cudaMalloc(&cell_row.p, nn * 4));
+  int64_t m = 0, nnz = 0;
+  if (n > 0) {
+    HPCX_CUDA(ctx, cudaMalloc(&k0.p, nn * 8));
+    HPCX_CUDA(ctx, cudaMalloc(&k1.p, nn * 8));
+    HPCX_CUDA(ctx, cudaMalloc(&i0.p, nn * 4));
+    HPCX_CUDA(ctx, cudaMalloc(&i1.p, nn * 4));
+    HPCX_CUDA(ctx, cudaMalloc(&pos.p, nn * 4));
+    cell_keys_kernel<<<grid_for(ctx, n, 256), 256, 0, st>>>(n, xs, ys, (uint64_t *)k0.p, (int32_t *)i0.p);
+    if (hpcx_status s = after_launch(ctx, "cell_keys_kernel")) return s;
+    cub::DoubleBuffer<uint64_t> dk((uint64_t *)k0.p, (uint64_t *)k1.p);
+    cub::DoubleBuffer<int32_t> di((int32_t *)i0.p, (int32_t *)i1.p);
+    size_t tb = 0;
+    HPCX_CUDA(ctx, cub::DeviceRadixSort::SortPairs(nullptr, tb, dk, di, n, 0, 64, st));
+    HPCX_CUDA(ctx, cudaMalloc(&tmp.p, tb ? tb : 1));
+    HPCX_CUDA(ctx, cub::DeviceRadixSort::SortPairs(tmp.p, tb, dk, di, n, 0, 64, st));
+    ctx->launches += 8 * 3;
+    const uint64_t *keys = dk.Current();
+    cub::CountingInputIterator<int64_t> cnt(0);
+    cub::TransformInputIterator<int32_t, HeadFlag, cub::CountingInputIterator<int64_t>> heads(cnt, HeadFlag{keys});
+    size_t sb = 0;
+    HPCX_CUDA(ctx, cub::DeviceScan::InclusiveSum(nullptr, sb, heads, (int32_t *)pos.p, n, st));
+    DevBuf stmp;
+    HPCX_CUDA(ctx, cudaMalloc(&stmp.p, sb ? sb : 1));
+    HPCX_CUDA(ctx, cub::DeviceScan::InclusiveSum(stmp.p, sb, heads, (int32_t *)pos.p, n, st));
+    ctx->launches += 2;
+    int32_t last = 0;
+    HPCX_CUDA(ctx, cudaMemcpyAsync(&last, (int32_t *)pos.p + (n - 1), 4, cudaMemcpyDeviceToHost, st));
+    HPCX_CUDA(ctx, cudaStreamSynchronize(st));
+    m = last;
+    HPCX_CUDA(ctx, cudaMalloc(&ukeys.p, (size_t)m * 8));
+    HPCX_CUDA(ctx, cudaMalloc(&row_x.p, (size_t)m * 4));
+    HPCX_CUDA(ctx, cudaMalloc(&row_y.p, (size_t)m * 4));
+    HPCX_CUDA(ctx, cudaMalloc(&nbr.p, (size_t)m * 16));
+    HPCX_CUDA(ctx, cudaMalloc(&deg.p, (size_t)m * 4));
+    HPCX_CUDA(ctx, cudaMalloc(&start.p, (size_t)m * 4));
+    cell_rows_kernel<<<grid_for(ctx, n, 256), 256, 0, st>>>(n, keys, di.Current(), (const int32_t *)pos.p,
+                                                          (uint64_t *)ukeys.p, (int32_t *)cell_row.p,
+                                                          (int32_t *)row_x.p, (int32_t *)row_y.p);
+    if (hpcx_status s = after_launch(ctx, "cell_rows_kernel")) return s;
+    cell_neighbours_kernel<<<grid_for(ctx, m, 256), 256, 0, st>>>(m, (const uint64_t *)ukeys.p,
+                                                                (const int32_t *)row_x.p, (const int32_t *)row_y.p,
+                                                                (int32_t *)nbr.p, (int32_t *)deg.p);
+    if (hpcx_status s = after_launch(ctx, "cell_neighbours_kernel")) return s;
+    size_t eb = 0;
+    HPCX_CUDA(ctx, cub::DeviceScan::ExclusiveSum(nullptr, eb, (int32_t *)deg.p, (int32_t *)start.p, m, st));
+    DevBuf etmp;
+    HPCX_CUDA(ctx, cudaMalloc(&etmp.p, eb ? eb : 1));
+    HPCX_CUDA(ctx, cub::DeviceScan::ExclusiveSum(etmp.p, eb, (int32_t *)deg.p, (int32_t *)start.p, m, st));
+    ctx->launches += 2;
+    int32_t s_last = 0, d_last = 0;
+    HPCX_CUDA(ctx, cudaMemcpyAsync(&s_last, (int32_t *)start.p + (m - 1), 4, cudaMemcpyDeviceToHost, st));
+    HPCX_CUDA(ctx, cudaMemcpyAsync(&d_last, (int32_t *)deg.p + (m - 1), 4, cudaMemcpyDeviceToHost, st));
+    HPCX_CUDA(ctx, cudaStreamSynchronize(st));
+    nnz = (int64_t)s_last + d_last;
+  }
+  HPCX_CUDA(ctx, cudaMalloc(&rp.p, (size_t)(m + 1) * idx_bytes));
+  HPCX_CUDA(ctx, cudaMalloc(&col.p, (size_t)(nnz > 0 ? nnz : 1) * 4));
+  HPCX_CUDA(ctx, cudaMalloc(&val.p, (size_t)(nnz > 0 ? nnz : 1) * sizeof(T)));
+  if (idx_bytes == 4)
+    cell_fill_kernel<T, int32_t><<<grid_for(ctx, m + 1, 256), 256, 0, st>>>(
+        m, (const int32_t *)nbr.p, (const int32_t *)start.p, nnz, (int32_t *)rp.p, (int32_t *)col.p, (T *)val.p);
+  else
+    cell_fill_kernel<T, int64_t><<<grid_for(ctx, m + 1, 256), 256, 0, st>>>(
+        m, (const int32_t *)nbr.p, (const int32_t *)start.p, nnz, (int64_t *)rp.p, (int32_t *)col.p, (T *)val.p);
+  if (hpcx_status s = after_launch(ctx, "cell_fill_kernel")) return s;
+  HPCX_CUDA(ctx, cudaStreamSynchronize(st));
+  out->nnz = nnz;
+  out->row_ptr = rp.p;
+  out->col_idx = (int32_t *)col.p;
+  out->values = val.p;
+  rp.p = col.p = val.p = nullptr;
+  if (map) {
+    map->nrows = m;
+    map->cell_row = (int32_t *)cell_row.p;
+    map->row_x = (int32_t *)row_x.p;
+    map->row_y = (int32_t *)row_y.p;
+    cell_row.p = row_x.p = row_y.p = nullptr;
+  }
+  return HPCX_OK;
+}
+
 }  // namespace
 }  // namespace hpcx
 
@@ -224,6 +397,28 @@ hpcx_status hpcx_csr_from_coo(hpcx_ctx ctx, int64_t nrows, int64_t nedges, const
   return dtype == HPCX_F64
              ? assemble<double>(ctx, nrows, nedges, rows, cols, (const double *)vals, idx_bytes, out)
              : assemble<float>(ctx, nrows, nedges, rows, cols, (const float *)vals, idx_bytes, out);
+}
+
+hpcx_status hpcx_csr_from_cells(hpcx_ctx ctx, int64_t ncells, const int32_t *xs, const int32_t *ys,
+                                int32_t mem, int32_t dtype, int32_t idx_bytes, hpcx_csr_arrays *out,
+                                hpcx_cell_map *map) {
+  if (!ctx || !out) return HPCX_INVALID_ARG;
+  HPCX_REQUIRE(ctx, ncells >= 0 && ncells < 0x19999999LL, "ncells must be below 2^31 / 5");
+  HPCX_REQUIRE(ctx, idx_bytes == 4 || idx_bytes == 8, "idx_bytes must be 4 or 8");
+  HPCX_REQUIRE(ctx, dtype == HPCX_F32 || dtype == HPCX_F64, "dtype must be HPCX_F32 or HPCX_F64");
+  HPCX_REQUIRE(ctx, ncells == 0 || (xs && ys), "null coordinate arrays");
+  HPCX_CUDA(ctx, cudaSetDevice(ctx->device));
+  DevBuf dx, dy;
+  if (mem == HPCX_MEM_HOST && ncells > 0) {
+    HPCX_CUDA(ctx, cudaMalloc(&dx.p, (size_t)ncells * 4));
+    HPCX_CUDA(ctx, cudaMalloc(&dy.p, (size_t)ncells * 4));
+    HPCX_CUDA(ctx, cudaMemcpy(dx.p, xs, (size_t)ncells * 4, cudaMemcpyHostToDevice));
+    HPCX_CUDA(ctx, cudaMemcpy(dy.p, ys, (size_t)ncells * 4, cudaMemcpyHostToDevice));
+    xs = (const int32_t *)dx.p;
+    ys = (const int32_t *)dy.p;
+  }
+  return dtype == HPCX_F64 ? cells_to_csr<double>(ctx, ncells, xs, ys, idx_bytes, out, map)
+                           : cells_to_csr<float>(ctx, ncells, xs, ys, idx_bytes, out, map);
 }
 
 hpcx_status hpcx_synth_rmat_coo(hpcx_ctx ctx, int32_t scale, int64_t nedges, uint64_t seed,

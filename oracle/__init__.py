@@ -309,3 +309,21 @@ def ref_transpose(which: str, a: np.ndarray, n: int) -> np.ndarray:
     r.hpcref_transpose(C.c_int({"scalar": 0, "tiling": 1}[which]),
                        _p(np.ascontiguousarray(a, dtype=np.float32)), _p(b), C.c_int64(n))
     return b
+
+
+def cells_csr(xs, ys):
+    """orc_cells_csr: (row_ptr, col, val, cell_row, row_x, row_y) of the active-cell operator."""
+    xs = np.ascontiguousarray(xs, dtype=np.int32)
+    ys = np.ascontiguousarray(ys, dtype=np.int32)
+    n = len(xs)
+    rp = np.empty(n + 1, dtype=np.int64)
+    col = np.empty(5 * max(n, 1), dtype=np.int32)
+    val = np.empty(5 * max(n, 1), dtype=np.float64)
+    cell_row = np.empty(max(n, 1), dtype=np.int32)
+    rx = np.empty(max(n, 1), dtype=np.int32)
+    ry = np.empty(max(n, 1), dtype=np.int32)
+    nnz = C.c_int64()
+    fn = lib().orc_cells_csr
+    fn.restype = C.c_int64
+    m = fn(C.c_int64(n), _p(xs), _p(ys), _p(rp), _p(col), _p(val), _p(cell_row), _p(rx), _p(ry), C.byref(nnz))
+    return rp[:m + 1].copy(), col[:nnz.value].copy(), val[:nnz.value].copy(), cell_row[:n].copy(), rx[:m].copy(), ry[:m].copy()

@@ -575,3 +575,60 @@ ORC_API void orc_transpose(const void *in, void *out, int64_t ny, int64_t nx, in
       memcpy((char *)out + ((x + olo) * po + olo + y) * es,
              (const char *)in + ((y + ilo) * pi + ilo + x) * es, (size_t)es);
 }
+
+/* ------------------------------------------------------------------ sparse-grid bridge (§8f-4)
+ * 5-point operator over the active cells of a sparse 2-D grid (the coordinates
+ * sparse::RootGrid::foreach enumerates, lib/sparse/include/RootGrid.hpp:20-22, 62-75).  No
+ * reference counterpart for the operator itself (parity unpinned).  Rows = distinct cells in
+ * (x, y) lexicographic order; 4 on the diagonal, -1 per active 4-neighbour, columns ascending.
+ * Returns the number of rows; *nnz_out the entries.  row_ptr needs ncells + 1 slots, col
+ * 5 * ncells, row_x / row_y ncells, cell_row ncells. */
+typedef struct { int64_t x, y, i; } orc_cell;
+static int orc_cell_cmp(const void *pa, const void *pb) {
+  const orc_cell *a = (const orc_cell *)pa, *b = (const orc_cell *)pb;
+  if (a->x != b->x) return a->x < b->x ? -1 : 1;
+  if (a->y != b->y) return a->y < b->y ? -1 : 1;
+  return a->i < b->i ? -1 : (a->i > b->i);
+}
+static int64_t orc_cell_find(const int32_t *rx, const int32_t *ry, int64_t m, int64_t x, int64_t y) {
+  int64_t lo = 0, hi = m;
+  while (lo < hi) {
+    const int64_t mid = (lo + hi) / 2;
+    if (rx[mid] < x || (rx[mid] == x && ry[mid] < y)) lo = mid + 1; else hi = mid;
+  }
+  return (lo < m && rx[lo] == x && ry[lo] == y) ? lo : -1;
+}
+ORC_API int64_t orc_cells_csr(int64_t ncells, const int32_t *xs, const int32_t *ys, int64_t *row_ptr,
+                              int32_t *col, double *val, int32_t *cell_row, int32_t *row_x,
+                              int32_t *row_y, int64_t *nnz_out) {
+  orc_cell *c = (orc_cell *)malloc((size_t)(ncells > 0 ? ncells : 1) * sizeof(orc_cell));
+  for (int64_t i = 0; i < ncells; ++i) { c[i].x = xs[i]; c[i].y = ys[i]; c[i].i = i; }
+  qsort(c, (size_t)ncells, sizeof(orc_cell), orc_cell_cmp);
+  int64_t m = 0;
+  for (int64_t i = 0; i < ncells; ++i) {
+    if (i == 0 || c[i].x != c[i - 1].x || c[i].y != c[i - 1].y) {
+      row_x[m] = (int32_t)c[i].x;
+      row_y[m] = (int32_t)c[i].y;
+      ++m;
+    }
+    cell_row[c[i].i] = (int32_t)(m - 1);
+  }
+  int64_t p = 0;
+  for (int64_t r = 0; r < m; ++r) {
+    const int64_t x = row_x[r], y = row_y[r];
+    const int64_t nb[5][2] = {{x - 1, y}, {x, y - 1}, {x, y}, {x, y + 1}, {x + 1, y}};
+    row_ptr[r] = p;
+    for (int k = 0; k < 5; ++k) {
+      if (nb[k][0] < INT32_MIN || nb[k][0] > INT32_MAX || nb[k][1] < INT32_MIN || nb[k][1] > INT32_MAX) continue;
+      const int64_t q = k == 2 ? r : orc_cell_find(row_x, row_y, m, nb[k][0], nb[k][1]);
+      if (q < 0) continue;
+      col[p] = (int32_t)q;
+      val[p] = k == 2 ? 4.0 : -1.0;
+      ++p;
+    }
+  }
+  row_ptr[m] = p;
+  *nnz_out = p;
+  free(c);
+  return m;
+}

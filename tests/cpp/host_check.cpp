@@ -13,6 +13,7 @@
 #include <cstdio>
 #include <cstring>
 #include <string>
+#include <tuple>
 #include <vector>
 
 #include <hpcx/CsrMatrix.hpp>
@@ -117,6 +118,15 @@ static float frand(uint64_t &s) {
   s = s * 6364136223846793005ull + 1442695040888963407ull;
   return (float)((s >> 40) & 0xFFFF) / 65536.0f - 0.5f;
 }
+
+// Stand-in with sparse::RootGrid's foreach(func(x, y, value&)) signature (RootGrid.hpp:20-22).
+struct LineGrid {
+  std::vector<std::tuple<std::intptr_t, std::intptr_t, float>> cells;
+  template <typename F>
+  void foreach (const F &f) {
+    for (auto &c : cells) f(std::get<0>(c), std::get<1>(c), std::get<2>(c));
+  }
+};
 
 static int run_gpu() {
   int bad = 0;
@@ -270,6 +280,27 @@ static int run_gpu() {
     }
     std::printf("cg iterations %d converged %d rel_err %.3e\n", res.iterations, (int)res.converged, err / mag);
     bad += !(res.converged && err <= 1e-8 * mag);
+  }
+  {  // sparse-grid bridge: a stand-in with RootGrid's foreach(func(x, y, value&)) signature
+     // (lib/sparse/include/RootGrid.hpp:20-22; the reference tree itself needs oneTBB)
+    LineGrid g;
+    const int nx = 9, ny = 6;
+    for (int y = ny - 1; y >= 0; --y)
+      for (int x = 0; x < nx; ++x) g.cells.emplace_back(x - 4, y + 10, frand(seed));
+    sparse::ActiveCells ac;
+    std::vector<float> x0, y1, y2;
+    auto dG = sparse::csr_from_grid<float>(ctx, g, &ac, &x0);
+    // the same cells as a full rectangle: rows are x-major, i.e. laplace2d(nx, ny)
+    auto L = sparse::CsrMatrix<float>::laplace2d(nx, ny);
+    sparse::DeviceCsr<float> dL(ctx, L);
+    sparse::spmv(dG, x0, y1);
+    sparse::spmv(dL, x0, y2);
+    int ok = dG.nrows() == (std::size_t)(nx * ny) && ac.row_x.front() == -4 && ac.row_y.front() == 10 &&
+             ac.row_x.back() == 4 && ac.row_y.back() == 15 && std::memcmp(y1.data(), y2.data(), y1.size() * 4) == 0;
+    for (auto &c : g.cells)  // x0 carries each cell's value at its row
+      ok = ok && x0[(std::get<0>(c) + 4) * ny + (std::get<1>(c) - 10)] == std::get<2>(c);
+    std::printf("grid_bridge ok %d\n", ok);
+    bad += !ok;
   }
   std::printf("launches %lld\n", (long long)ctx.launchCount());
   std::printf(bad ? "CPP GPU FAIL\n" : "CPP GPU OK\n");

@@ -87,3 +87,48 @@ def test_device_field_matches_oracle(ctx, dtype):
     hp.synth_field(ctx, 7, n, out, dtype, first)
     want = oracle.fill(first + n, 7, dtype)[first:]
     assert bits_equal(out.cpu().numpy(), want)
+
+
+# ---- sparse-grid bridge (hpcx_csr_from_cells)
+def _cells(seed, n, span, dup):
+    rng = np.random.default_rng(seed)
+    xs = rng.integers(-span, span, n).astype(np.int32)
+    ys = rng.integers(-span, span, n).astype(np.int32)
+    if dup and n:
+        xs[: n // 3] = xs[n // 3: 2 * (n // 3)][: n // 3]
+        ys[: n // 3] = ys[n // 3: 2 * (n // 3)][: n // 3]
+    return xs, ys
+
+
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+@pytest.mark.parametrize("n,span,dup,idx_bytes", [(0, 1, False, 4), (1, 1, False, 8), (500, 12, True, 4),
+                                                  (20000, 90, True, 8), (3000, 2 ** 30, False, 4)])
+def test_cells_bridge_matches_oracle(ctx, dtype, n, span, dup, idx_bytes):
+    xs, ys = _cells(n + span, n, span, dup)
+    if n > 5:  # the int32 corners too
+        xs[:2], ys[:2] = (-2 ** 31, 2 ** 31 - 1), (-2 ** 31, 2 ** 31 - 1)
+    rp, col, val, cell_row, rx, ry = oracle.cells_csr(xs, ys)
+    D, m = hp.csr_from_cells(ctx, xs, ys, dtype, idx_bytes)
+    rp_d, col_d, val_d = D.download()
+    assert m["nrows"] == len(rx) and D.nnz == len(col)
+    assert np.array_equal(rp_d.astype(np.int64), rp) and np.array_equal(col_d, col)
+    assert bits_equal(val_d, val.astype(dtype))
+    assert np.array_equal(m["cell_row"], cell_row) and np.array_equal(m["row_x"], rx) and np.array_equal(m["row_y"], ry)
+    if len(rx):
+        A = hp.DeviceCsr.from_device_arrays(ctx, D)
+        x = synth.field(42, len(rx), dtype)
+        y = np.empty(len(rx), dtype)
+        A.spmv(x, y)
+        assert np.array_equal(y, oracle.spmv(rp, col, val.astype(dtype), x))  # rows of <= 5 entries: bit-exact
+        A.destroy()
+    D.destroy()
+
+
+def test_cells_bridge_full_rectangle_is_the_laplacian(ctx):
+    nx, ny = 300, 200
+    xs, ys = np.meshgrid(np.arange(nx, dtype=np.int32), np.arange(ny, dtype=np.int32), indexing="ij")
+    D, m = hp.csr_from_cells(ctx, np.ascontiguousarray(xs.ravel()), np.ascontiguousarray(ys.ravel()))
+    rp, col, val = D.download()
+    rp2, col2, val2 = synth.laplace2d(nx, ny)
+    assert np.array_equal(rp, rp2) and np.array_equal(col, col2) and np.array_equal(val, val2)
+    D.destroy()

@@ -164,3 +164,27 @@ def test_cg_oracle_identity_and_zero_iterations():
     x0 = synth.field(4, n)
     x, it, _, _ = oracle.cg(rp, col, val, b, x0, 0)
     assert it == 0 and np.array_equal(x, x0)
+
+
+# ---- sparse-grid bridge
+def test_cells_operator_on_a_full_rectangle_is_the_laplacian():
+    nx, ny = 7, 5  # rows are x-major: row = x*ny + y, i.e. laplace2d with x as the slow index
+    xs, ys = np.meshgrid(np.arange(nx, dtype=np.int32), np.arange(ny, dtype=np.int32), indexing="ij")
+    perm = np.random.default_rng(1).permutation(nx * ny)
+    rp, col, val, cell_row, rx, ry = oracle.cells_csr(xs.ravel()[perm], ys.ravel()[perm])
+    rp2, col2, val2 = synth.laplace2d(nx, ny, index_dtype=np.int64)
+    assert np.array_equal(rp, rp2) and np.array_equal(col, col2) and np.array_equal(val, val2)
+    assert np.array_equal(cell_row, (xs.ravel() * ny + ys.ravel())[perm])
+    assert np.array_equal(rx * ny + ry, np.arange(nx * ny))
+
+
+def test_cells_operator_handles_repeats_islands_and_negative_coordinates():
+    xs = np.array([3, -2, 3, 100, -2, -2147483648, 2147483647], dtype=np.int32)
+    ys = np.array([4, 7, 4, -100, 8, 0, 2147483647], dtype=np.int32)
+    rp, col, val, cell_row, rx, ry = oracle.cells_csr(xs, ys)
+    assert list(zip(rx, ry)) == [(-2147483648, 0), (-2, 7), (-2, 8), (3, 4), (100, -100), (2147483647, 2147483647)]
+    assert list(cell_row) == [3, 1, 3, 4, 2, 0, 5]
+    assert list(rp) == [0, 1, 3, 5, 6, 7, 8]
+    assert list(col) == [0, 1, 2, 1, 2, 3, 4, 5] and list(val) == [4, 4, -1, -1, 4, 4, 4, 4]
+    rp, col, val, cell_row, rx, ry = oracle.cells_csr(np.empty(0, np.int32), np.empty(0, np.int32))
+    assert list(rp) == [0] and len(col) == 0
