@@ -123,7 +123,16 @@ enum {
    * (ascending address) order; 3-D, ghost >= 1; ping-pong for steps > 1. */
   HPCX_STENCIL_JACOBI7 = 3
 };
-enum { HPCX_VARIANT_AUTO = 0, HPCX_VARIANT_TMA = 1, HPCX_VARIANT_DIRECT = 2 };
+enum {
+  HPCX_VARIANT_AUTO = 0,
+  HPCX_VARIANT_TMA = 1,
+  HPCX_VARIANT_DIRECT = 2,
+  /* JACOBI7, fp32, steps >= 2: temporal blocking — each pass over HBM advances the field by two
+   * sweeps (4 instead of 8 bytes of traffic per cell and sweep), results bit-identical to
+   * single sweeps.  After the call `out` holds iterate `steps`; `in` holds an OLDER iterate
+   * (steps-2, or steps-1 when steps is odd), not necessarily the previous one. */
+  HPCX_VARIANT_TEMPORAL = 3
+};
 typedef struct {
   int32_t kind;
   int32_t radius;   /* BOX_*: r (the reference uses nblur = 8); JACOBI7: ignored */
@@ -137,7 +146,8 @@ typedef struct {
  *        steps must be 1.
  * JACOBI7: in/out same shape, lo,hi >= 1, both hold the same (Dirichlet) ghost values;
  *        after `steps` sweeps the newest iterate is in `out` and the previous one in
- *        `in` (the two handles swap device buffers when steps is even). */
+ *        `in` (the two handles swap device buffers when steps is even); see
+ *        HPCX_VARIANT_TEMPORAL for the two-sweeps-per-pass variant. */
 HPCX_API hpcx_status hpcx_stencil_sweep(hpcx_grid in, hpcx_grid out,
                                         const hpcx_stencil_desc *st, int32_t steps,
                                         void *stream);

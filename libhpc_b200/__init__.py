@@ -10,5 +10,5 @@ from .api import (CgSolver, Context, CsrMatrix, DeviceCsr, DeviceCsrArrays, Devi
                   synth_field, synth_rmat_csr,
                   stencil_sweep_host)
 from ._abi import (F32, F64, MEM_DEVICE, MEM_HOST, SPMV_SELL, SPMV_STREAM, SPMV_VECTOR,  # noqa: F401
-                   STENCIL_BOX_X, STENCIL_BOX_Y, STENCIL_JACOBI7, VARIANT_AUTO, VARIANT_DIRECT,
+                   STENCIL_BOX_X, STENCIL_BOX_Y, STENCIL_JACOBI7, VARIANT_AUTO, VARIANT_DIRECT, VARIANT_TEMPORAL,
                    VARIANT_TMA)

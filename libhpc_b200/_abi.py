@@ -16,7 +16,7 @@ OK, INVALID_ARG, OOM, CUDA_ERROR, NCCL_ERROR, UNSUPPORTED, OUT_OF_RANGE = range(
 F32, F64 = 0, 1
 MEM_HOST, MEM_DEVICE, MEM_MANAGED = 0, 1, 2
 STENCIL_BOX_X, STENCIL_BOX_Y, STENCIL_JACOBI7 = 1, 2, 3
-VARIANT_AUTO, VARIANT_TMA, VARIANT_DIRECT = 0, 1, 2
+VARIANT_AUTO, VARIANT_TMA, VARIANT_DIRECT, VARIANT_TEMPORAL = 0, 1, 2, 3
 SPMV_AUTO, SPMV_STREAM, SPMV_VECTOR, SPMV_SELL = 0, 1, 2, 3
 
 STATUS_NAMES = {0: "HPCX_OK", 1: "HPCX_INVALID_ARG", 2: "HPCX_OOM", 3: "HPCX_CUDA_ERROR",

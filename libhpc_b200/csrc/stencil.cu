@@ -614,6 +614,280 @@ hpcx_status launch_jacobi_tma(hpcx_grid_s *g, void *src, void *dst, int zsplit, 
   return after_launch(ctx, "jacobi7_tma_kernel");
 }
 
+
+// ------------------------------------------------------------------ Jacobi, two sweeps per pass
+// Temporal blocking (HPCX_VARIANT_TEMPORAL): one pass over HBM advances the field by TWO sweeps,
+// so the traffic per sweep drops from 8 to 4 bytes per cell.  Same ring, same add order — the
+// result is bit-identical to two single sweeps.
+//
+// A CTA owns TX = 128 columns, h <= 14 rows and a z segment.  The producer streams boxes of
+// (128 + 8) x (h + 4) cells of iterate t (two halo cells per side in y, plane by plane, from two
+// planes below the segment to two above).  The 8 consumer warps march along z; at step j they
+//   A  compute iterate t+1 of plane j on the tile grown by one cell in x and y (their own two
+//      rows x four columns from registers / shuffles / staged halo rows, plus the two edge
+//      columns x0-1 and x0+128 by lanes 0 and 31); cells outside the domain keep their (fixed,
+//      Dirichlet) ghost value; the plane goes into a double-buffered shared-memory array;
+//   B  compute iterate t+2 of plane j-1 from the t+1 planes j-2, j-1, j (own cells in registers,
+//      x neighbours by shuffle, y neighbours and edge columns from the shared t+1 plane of step
+//      j-1) and stream it to HBM.
+// One named barrier per step orders the t+1 planes between the warps.
+struct JacobiTB {
+  static constexpr int TX = 128, HX = 4, BX = TX + 2 * HX;  // 136 staged columns
+  static constexpr int HO = 14;                               // output rows per tile (max)
+  static constexpr int ER = HO + 2;                           // rows of the grown (t+1) tile
+  static constexpr int BY = HO + 4;                           // staged rows of iterate t
+  static constexpr int S = 6;
+  static constexpr int kSlotBytes = (BX * BY * 4 + 127) / 128 * 128;
+  static constexpr int kSlotFloats = kSlotBytes / 4;
+  static constexpr int kAPlaneFloats = (ER + 2) * BX;  // one guard row above and below
+  static constexpr int kAOff = S * kSlotBytes;
+  static constexpr int kBarOff = kAOff + 2 * kAPlaneFloats * 4;
+  static constexpr int kSmemBytes = kBarOff + 2 * S * 8;
+  static constexpr int kConsumerWarps = 8;
+  static constexpr int kThreads = (kConsumerWarps + 1) * 32;
+};
+
+struct JacobiTBSplit {
+  int ntx, nty, zs, hmax;
+};
+
+#define HPCX_J7(zm, ym, xm, xp, yp, zp) \
+  mul_rn(add_rn(add_rn(add_rn(add_rn(add_rn(zm, ym), xm), xp), yp), zp), sixth)
+
+__global__ void __launch_bounds__(JacobiTB::kThreads, 2)
+jacobi7_tb2_kernel(const __grid_constant__ CUtensorMap map_hi, const __grid_constant__ CUtensorMap map_lo,
+                   float *__restrict__ out, GridGeom g, JacobiTBSplit sp, float sixth) {
+  using C = JacobiTB;
+  extern __shared__ __align__(128) unsigned char smem[];
+  float *ring = reinterpret_cast<float *>(smem);
+  float *abuf = reinterpret_cast<float *>(smem + C::kAOff);
+  uint64_t *full = reinterpret_cast<uint64_t *>(smem + C::kBarOff);
+  uint64_t *empty = full + C::S;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int bx = blockIdx.x % sp.ntx;
+  const int by = (blockIdx.x / sp.ntx) % sp.nty;
+  const int bz = blockIdx.x / (sp.ntx * sp.nty);
+  const int x0 = bx * C::TX;
+  const int y0 = (int)((int64_t)by * g.n1 / sp.nty);
+  const int h = (int)((int64_t)(by + 1) * g.n1 / sp.nty) - y0;
+  const int z0 = (int)((int64_t)bz * g.n0 / sp.zs);
+  const int z1 = (int)((int64_t)(bz + 1) * g.n0 / sp.zs);
+  if (h <= 0 || z1 <= z0) return;
+  const int np = z1 - z0 + 4;  // planes z0-2 .. z1+1 of iterate t
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < C::S; ++s) {
+      mbar_init(full + s, 1);
+      mbar_init(empty + s, C::kConsumerWarps);
+    }
+    mbar_fence_init();
+  }
+  __syncthreads();
+
+  if (warp == C::kConsumerWarps) {
+    if (lane == 0) {
+      const CUtensorMap *map = h == sp.hmax ? &map_hi : &map_lo;
+      tma_prefetch_desc(map);
+      const uint32_t bytes = (uint32_t)(C::BX * (h + 4) * 4);
+      const int c0 = (int)g.xoff + x0 - C::HX;
+      const int c1 = y0 + (int)g.glo1 - 2;  // may be -1: rows outside the array are zero-filled
+      for (int j = 0; j < np; ++j) {
+        const int slot = j % C::S, use = j / C::S;
+        if (use > 0) mbar_wait(empty + slot, (use - 1) & 1);
+        mbar_expect_tx(full + slot, bytes);
+        tma_load_3d(ring + slot * C::kSlotFloats, map, c0, c1, z0 - 2 + j + (int)g.glo0, full + slot);
+      }
+    }
+    return;
+  }
+
+  // ---------------------------------------------------------------- consumers
+  // Warp w owns rows e = 2w, 2w+1 of the grown tile (y = y0 - 1 + e), i.e. box rows 2w+1, 2w+2;
+  // lane owns box columns 4 + 4*lane .. (x = x0 + 4*lane ..); lanes 0 / 31 also own the edge
+  // column 3 / 132 (x = x0 - 1 / x0 + 128).
+  const int br = 2 * warp + 1;
+  const int col = C::HX + 4 * lane;
+  const int ec = lane == 31 ? C::HX + C::TX : C::HX - 1;
+  const bool edge = lane == 0 || lane == 31;
+  auto plane_ptr = [&](int j) { return ring + (j % C::S) * C::kSlotFloats; };
+  auto wait_full = [&](int j) { mbar_wait(full + (j % C::S), (j / C::S) & 1); };
+  auto release = [&](int j) {
+    __syncwarp();
+    if (lane == 0) mbar_arrive(empty + (j % C::S));
+  };
+  auto ld4 = [&](const float *pl, int row) {
+    return *reinterpret_cast<const float4 *>(pl + row * C::BX + col);
+  };
+  // t+1 planes: row e of the grown tile lives at row e + 1 (guard rows 0 and ER + 1)
+  auto aplane = [&](int j) { return abuf + (j & 1) * C::kAPlaneFloats + C::BX; };
+
+  const int gx = x0 + 4 * lane;
+  const int ye0 = y0 - 1 + 2 * warp, ye1 = ye0 + 1;  // y of the two rows
+  const int xe = x0 - C::HX + ec;                     // x of the edge column
+  const bool yin0 = ye0 >= 0 && ye0 < g.n1, yin1 = ye1 >= 0 && ye1 < g.n1;
+  const bool xin[4] = {gx < g.n2, gx + 1 < g.n2, gx + 2 < g.n2, gx + 3 < g.n2};
+  const bool xein = xe >= 0 && xe < g.n2;
+  // output rows: e in [1, h]
+  const bool orow0 = 2 * warp >= 1 && 2 * warp <= h, orow1 = 2 * warp + 1 <= h;
+  const bool full4 = gx + 3 < g.n2;
+  const int64_t plane_stride = g.ext1 * g.pitch;
+
+  float4 pv0, pv1, zc0, zc1;     // iterate t, planes j-1 and j, own cells
+  float pe0, pe1, ze0, ze1;      // same for the edge column
+  float4 aP0, aP1, aC0, aC1;     // iterate t+1, planes j-2 and j-1, own cells
+  aP0 = aP1 = aC0 = aC1 = make_float4(0.f, 0.f, 0.f, 0.f);
+  wait_full(0);
+  {
+    const float *pl = plane_ptr(0);
+    pv0 = ld4(pl, br);
+    pv1 = ld4(pl, br + 1);
+    pe0 = pl[br * C::BX + ec];
+    pe1 = pl[(br + 1) * C::BX + ec];
+  }
+  release(0);
+  wait_full(1);
+  {
+    const float *pl = plane_ptr(1);
+    zc0 = ld4(pl, br);
+    zc1 = ld4(pl, br + 1);
+    ze0 = pl[br * C::BX + ec];
+    ze1 = pl[(br + 1) * C::BX + ec];
+  }
+
+  float *orow = out + gidx(g, z0, ye0, gx);  // plane z0, this thread's first row
+  for (int j = 1; j <= np - 2; ++j) {
+    const int z = z0 - 2 + j;  // plane of the t+1 values made in this step
+    wait_full(j + 1);
+    const float *pn = plane_ptr(j + 1);
+    const float *pc = plane_ptr(j);
+    const float4 nx0 = ld4(pn, br), nx1 = ld4(pn, br + 1);
+    const float ne0 = pn[br * C::BX + ec], ne1 = pn[(br + 1) * C::BX + ec];
+    const float4 up = ld4(pc, br - 1);
+    const float4 dn = ld4(pc, br + 2);
+    float l0 = __shfl_up_sync(0xffffffffu, zc0.w, 1);
+    float l1 = __shfl_up_sync(0xffffffffu, zc1.w, 1);
+    float r0 = __shfl_down_sync(0xffffffffu, zc0.x, 1);
+    float r1 = __shfl_down_sync(0xffffffffu, zc1.x, 1);
+    if (lane == 0) {
+      l0 = ze0;  // box column 3 is this lane's edge column
+      l1 = ze1;
+    }
+    if (lane == 31) {
+      r0 = ze0;  // box column 132
+      r1 = ze1;
+    }
+    // edge column: its own x neighbours and y neighbours come from the staged plane
+    const float eup = pc[(br - 1) * C::BX + ec], edn = pc[(br + 2) * C::BX + ec];
+    const float el0 = pc[br * C::BX + ec - 1], er0 = pc[br * C::BX + ec + 1];
+    const float el1 = pc[(br + 1) * C::BX + ec - 1], er1 = pc[(br + 1) * C::BX + ec + 1];
+    release(j);
+
+    // ---- A: iterate t+1 of plane z on the grown tile
+    const bool zin = z >= 0 && z < g.n0;
+    float4 aN0, aN1;
+    aN0.x = zin && yin0 && xin[0] ? HPCX_J7(pv0.x, up.x, l0, zc0.y, zc1.x, nx0.x) : zc0.x;
+    aN0.y = zin && yin0 && xin[1] ? HPCX_J7(pv0.y, up.y, zc0.x, zc0.z, zc1.y, nx0.y) : zc0.y;
+    aN0.z = zin && yin0 && xin[2] ? HPCX_J7(pv0.z, up.z, zc0.y, zc0.w, zc1.z, nx0.z) : zc0.z;
+    aN0.w = zin && yin0 && xin[3] ? HPCX_J7(pv0.w, up.w, zc0.z, r0, zc1.w, nx0.w) : zc0.w;
+    aN1.x = zin && yin1 && xin[0] ? HPCX_J7(pv1.x, zc0.x, l1, zc1.y, dn.x, nx1.x) : zc1.x;
+    aN1.y = zin && yin1 && xin[1] ? HPCX_J7(pv1.y, zc0.y, zc1.x, zc1.z, dn.y, nx1.y) : zc1.y;
+    aN1.z = zin && yin1 && xin[2] ? HPCX_J7(pv1.z, zc0.z, zc1.y, zc1.w, dn.z, nx1.z) : zc1.z;
+    aN1.w = zin && yin1 && xin[3] ? HPCX_J7(pv1.w, zc0.w, zc1.z, r1, dn.w, nx1.w) : zc1.w;
+    const float aE0 = zin && yin0 && xein ? HPCX_J7(pe0, eup, el0, er0, ze1, ne0) : ze0;
+    const float aE1 = zin && yin1 && xein ? HPCX_J7(pe1, ze0, el1, er1, edn, ne1) : ze1;
+
+    // ---- B: iterate t+2 of plane z-1 from the t+1 planes z-2 (aP), z-1 (aC), z (aN)
+    if (j >= 3) {
+      const float *ac = aplane(j - 1);
+      const float4 bup = *reinterpret_cast<const float4 *>(ac + (2 * warp - 1) * C::BX + col);
+      const float4 bdn = *reinterpret_cast<const float4 *>(ac + (2 * warp + 2) * C::BX + col);
+      float bl0 = __shfl_up_sync(0xffffffffu, aC0.w, 1);
+      float bl1 = __shfl_up_sync(0xffffffffu, aC1.w, 1);
+      float br0 = __shfl_down_sync(0xffffffffu, aC0.x, 1);
+      float br1 = __shfl_down_sync(0xffffffffu, aC1.x, 1);
+      if (lane == 0) {
+        bl0 = ac[(2 * warp) * C::BX + C::HX - 1];
+        bl1 = ac[(2 * warp + 1) * C::BX + C::HX - 1];
+      }
+      if (lane == 31) {
+        br0 = ac[(2 * warp) * C::BX + C::HX + C::TX];
+        br1 = ac[(2 * warp + 1) * C::BX + C::HX + C::TX];
+      }
+      float4 o0, o1;
+      o0.x = HPCX_J7(aP0.x, bup.x, bl0, aC0.y, aC1.x, aN0.x);
+      o0.y = HPCX_J7(aP0.y, bup.y, aC0.x, aC0.z, aC1.y, aN0.y);
+      o0.z = HPCX_J7(aP0.z, bup.z, aC0.y, aC0.w, aC1.z, aN0.z);
+      o0.w = HPCX_J7(aP0.w, bup.w, aC0.z, br0, aC1.w, aN0.w);
+      o1.x = HPCX_J7(aP1.x, aC0.x, bl1, aC1.y, bdn.x, aN1.x);
+      o1.y = HPCX_J7(aP1.y, aC0.y, aC1.x, aC1.z, bdn.y, aN1.y);
+      o1.z = HPCX_J7(aP1.z, aC0.z, aC1.y, aC1.w, bdn.z, aN1.z);
+      o1.w = HPCX_J7(aP1.w, aC0.w, aC1.z, br1, bdn.w, aN1.w);
+      if (full4) {
+        if (orow0) st_cs(reinterpret_cast<float4 *>(orow), o0);
+        if (orow1) st_cs(reinterpret_cast<float4 *>(orow + g.pitch), o1);
+      } else {
+        const float a0[4] = {o0.x, o0.y, o0.z, o0.w}, a1[4] = {o1.x, o1.y, o1.z, o1.w};
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          if (gx + k < g.n2) {
+            if (orow0) orow[k] = a0[k];
+            if (orow1) orow[g.pitch + k] = a1[k];
+          }
+      }
+      orow += plane_stride;
+    }
+
+    // ---- publish the t+1 plane of this step
+    {
+      float *an = aplane(j);
+      *reinterpret_cast<float4 *>(an + (2 * warp) * C::BX + col) = aN0;
+      *reinterpret_cast<float4 *>(an + (2 * warp + 1) * C::BX + col) = aN1;
+      if (edge) {
+        an[(2 * warp) * C::BX + ec] = aE0;
+        an[(2 * warp + 1) * C::BX + ec] = aE1;
+      }
+    }
+    asm volatile("bar.sync 1, %0;" ::"n"(C::kConsumerWarps * 32) : "memory");
+    pv0 = zc0; pv1 = zc1; zc0 = nx0; zc1 = nx1;
+    pe0 = ze0; pe1 = ze1; ze0 = ne0; ze1 = ne1;
+    aP0 = aC0; aP1 = aC1; aC0 = aN0; aC1 = aN1;
+  }
+}
+#undef HPCX_J7
+
+
+// Two sweeps src -> dst in one pass (HPCX_VARIANT_TEMPORAL).  Tiles of 128 x <= 14 cells, z
+// segments chosen so that the CTA count is about two per SM (the kernel's residency).
+hpcx_status launch_jacobi_tb2(hpcx_grid_s *g, void *src, void *dst, int zsplit, cudaStream_t s) {
+  using C = JacobiTB;
+  hpcx_ctx ctx = g->ctx;
+  JacobiTBSplit sp;
+  sp.ntx = (int)((g->n[2] + C::TX - 1) / C::TX);
+  sp.nty = (int)((g->n[1] + C::HO - 1) / C::HO);
+  sp.hmax = (int)((g->n[1] + sp.nty - 1) / sp.nty);
+  const int64_t tiles = (int64_t)sp.ntx * sp.nty;
+  int64_t zs = zsplit > 0 ? zsplit : std::max<int64_t>(1, (2 * (int64_t)ctx->sm_count + tiles / 2) / tiles);
+  zs = std::min<int64_t>(zs, zsplit > 0 ? g->n[0] : std::max<int64_t>(1, g->n[0] / 16));
+  sp.zs = (int)std::max<int64_t>(zs, 1);
+  hpcx_status st = HPCX_OK;
+  const CUtensorMap *hi = jacobi_map(g, src, sp.hmax + 4, &st);
+  if (!hi) return st;
+  const CUtensorMap *lo = jacobi_map(g, src, sp.hmax + 3, &st);
+  if (!lo) return st;
+  hi = jacobi_map(g, src, sp.hmax + 4, &st);  // may have moved if the cache reallocated
+  static bool configured = false;
+  if (!configured) {
+    HPCX_CUDA(ctx, cudaFuncSetAttribute(jacobi7_tb2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        C::kSmemBytes));
+    configured = true;
+  }
+  const unsigned ncta = (unsigned)(sp.ntx * sp.nty * sp.zs);
+  jacobi7_tb2_kernel<<<ncta, C::kThreads, C::kSmemBytes, s>>>(*hi, *lo, (float *)dst, geom_of(g), sp,
+                                                            1.0f / 6.0f);
+  return after_launch(ctx, "jacobi7_tb2_kernel");
+}
+
 }  // namespace
 
 namespace hpcx {
@@ -658,12 +932,21 @@ extern "C" hpcx_status hpcx_stencil_sweep(hpcx_grid in, hpcx_grid out, const hpc
     HPCX_REQUIRE(ctx, in->desc.lo >= 1 && in->desc.hi >= 1 && in->desc.lo == out->desc.lo &&
                           in->desc.hi == out->desc.hi,
                  "JACOBI7 needs identical ghost widths >= 1 on both grids");
-    for (int t = 0; t < steps && rc == HPCX_OK; ++t) {
+    const bool temporal = st->variant == HPCX_VARIANT_TEMPORAL;
+    if (temporal && !(in->desc.dtype == HPCX_F32 && ctx->encode_tiled && in->n[2] < (1 << 30)))
+      return fail(ctx, HPCX_UNSUPPORTED, "the temporally blocked Jacobi needs fp32 and a tensor-map driver");
+    // TEMPORAL: steps/2 fused two-sweep passes, then one single sweep when steps is odd
+    const int passes = temporal ? steps / 2 + (steps & 1) : steps;
+    for (int t = 0; t < passes && rc == HPCX_OK; ++t) {
       void *src = (t & 1) ? out->dev : in->dev;
       void *dst = (t & 1) ? in->dev : out->dev;
-      rc = jacobi7_launch(in, src, dst, st->variant, st->zsplit, 0, in->n[0], s, nullptr);
+      if (temporal && t < steps / 2)
+        rc = launch_jacobi_tb2(in, src, dst, st->zsplit, s);
+      else
+        rc = jacobi7_launch(in, src, dst, temporal ? HPCX_VARIANT_TMA : st->variant, temporal ? 0 : st->zsplit, 0,
+                            in->n[0], s, nullptr);
     }
-    if (rc == HPCX_OK && (steps & 1) == 0) std::swap(in->dev, out->dev);
+    if (rc == HPCX_OK && (passes & 1) == 0) std::swap(in->dev, out->dev);
   } else {
     return fail(ctx, HPCX_INVALID_ARG, "unknown stencil kind");
   }

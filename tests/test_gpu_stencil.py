@@ -91,6 +91,40 @@ def test_jacobi7_fp32_bit_exact(ctx, variant, dims, lo, hi, steps):
     assert bits_equal(prev, oracle.jacobi7(f, nz, ny, nx, lo, hi, steps - 1))
 
 
+@pytest.mark.parametrize("dims,lo,hi", [((1, 1, 1), 1, 1), ((2, 3, 5), 1, 1), ((3, 5, 7), 1, 1), ((16, 14, 128), 1, 1),
+                                        ((17, 33, 129), 1, 1), ((40, 50, 300), 2, 3), ((64, 64, 64), 1, 1),
+                                        ((24, 100, 256), 1, 1), ((5, 37, 64), 1, 2), ((33, 15, 260), 1, 1)])
+@pytest.mark.parametrize("steps", [2, 3, 4, 7])
+def test_jacobi7_temporal_blocking_bit_exact(ctx, dims, lo, hi, steps):
+    """HPCX_VARIANT_TEMPORAL: two sweeps per pass over HBM, bit-identical to single sweeps; `in`
+    ends up holding an older iterate (steps-2, or steps-1 when steps is odd)."""
+    nz, ny, nx = dims
+    f = oracle.fill((nz + lo + hi) * (ny + lo + hi) * (nx + lo + hi), 7, np.float32)
+    newest, older = _jacobi(ctx, f, dims, lo, hi, steps, hp.VARIANT_TEMPORAL)
+    assert bits_equal(newest, oracle.jacobi7(f, nz, ny, nx, lo, hi, steps))
+    assert bits_equal(older, oracle.jacobi7(f, nz, ny, nx, lo, hi, steps - 1 if steps & 1 else steps - 2))
+
+
+@pytest.mark.parametrize("zsplit", [1, 2, 5, 37])
+def test_jacobi7_temporal_blocking_zsplit(ctx, zsplit):
+    dims = (37, 20, 140)
+    f = oracle.fill(39 * 22 * 142, 8, np.float32)
+    newest, _ = _jacobi(ctx, f, dims, 1, 1, 4, hp.VARIANT_TEMPORAL, zsplit)
+    assert bits_equal(newest, oracle.jacobi7(f, *dims, 1, 1, 4))
+
+
+def test_jacobi7_temporal_blocking_512_cubed_and_fp64_rejected(ctx):
+    n = 512
+    f = oracle.fill((n + 2) ** 3, 7, np.float32)
+    tb, _ = _jacobi(ctx, f, (n, n, n), 1, 1, 8, hp.VARIANT_TEMPORAL)
+    tma, _ = _jacobi(ctx, f, (n, n, n), 1, 1, 8, hp.VARIANT_TMA)
+    assert bits_equal(tb, tma)
+    f64 = oracle.fill(11 * 12 * 72, 9, np.float64)
+    with pytest.raises(hp.HpcxError) as e:
+        _jacobi(ctx, f64, (9, 10, 70), 1, 1, 2, hp.VARIANT_TEMPORAL)
+    assert e.value.status == hp._abi.UNSUPPORTED
+
+
 @pytest.mark.parametrize("zsplit", [1, 2, 5])
 def test_jacobi7_zsplit(ctx, zsplit):
     dims = (37, 20, 140)
