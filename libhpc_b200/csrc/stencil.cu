@@ -636,7 +636,7 @@ struct JacobiTB {
   static constexpr int HO = 14;                               // output rows per tile (max)
   static constexpr int ER = HO + 2;                           // rows of the grown (t+1) tile
   static constexpr int BY = HO + 4;                           // staged rows of iterate t
-  static constexpr int S = 6;
+  static constexpr int S = 8;  // power of two: slot = j & 7, phase = (j >> 3) & 1
   static constexpr int kSlotBytes = (BX * BY * 4 + 127) / 128 * 128;
   static constexpr int kSlotFloats = kSlotBytes / 4;
   static constexpr int kAPlaneFloats = (ER + 2) * BX;  // one guard row above and below
@@ -654,7 +654,10 @@ struct JacobiTBSplit {
 #define HPCX_J7(zm, ym, xm, xp, yp, zp) \
   mul_rn(add_rn(add_rn(add_rn(add_rn(add_rn(zm, ym), xm), xp), yp), zp), sixth)
 
-__global__ void __launch_bounds__(JacobiTB::kThreads, 2)
+// EXP: timing experiments only (HPCX_TB_EXP, results are wrong when non-zero): 1 = no stage B,
+// 2 = no consumer barrier, 4 = no global stores, 8 = no edge columns.
+template <int EXP>
+__global__ void __maxnreg__(112)
 jacobi7_tb2_kernel(const __grid_constant__ CUtensorMap map_hi, const __grid_constant__ CUtensorMap map_lo,
                    float *__restrict__ out, GridGeom g, JacobiTBSplit sp, float sixth) {
   using C = JacobiTB;
@@ -693,7 +696,7 @@ jacobi7_tb2_kernel(const __grid_constant__ CUtensorMap map_hi, const __grid_cons
       const int c0 = (int)g.xoff + x0 - C::HX;
       const int c1 = y0 + (int)g.glo1 - 2;  // may be -1: rows outside the array are zero-filled
       for (int j = 0; j < np; ++j) {
-        const int slot = j % C::S, use = j / C::S;
+        const int slot = j & (C::S - 1), use = j / C::S;
         if (use > 0) mbar_wait(empty + slot, (use - 1) & 1);
         mbar_expect_tx(full + slot, bytes);
         tma_load_3d(ring + slot * C::kSlotFloats, map, c0, c1, z0 - 2 + j + (int)g.glo0, full + slot);
@@ -704,154 +707,172 @@ jacobi7_tb2_kernel(const __grid_constant__ CUtensorMap map_hi, const __grid_cons
 
   // ---------------------------------------------------------------- consumers
   // Warp w owns rows e = 2w, 2w+1 of the grown tile (y = y0 - 1 + e), i.e. box rows 2w+1, 2w+2;
-  // lane owns box columns 4 + 4*lane .. (x = x0 + 4*lane ..); lanes 0 / 31 also own the edge
-  // column 3 / 132 (x = x0 - 1 / x0 + 128).
+  // lane owns box columns 4 + 4*lane .. (x = x0 + 4*lane ..).  The two edge columns of the grown
+  // tile (box columns 3 and 132, x = x0 - 1 and x0 + 128) are spread over four lanes: lanes 0 / 1
+  // take the left edge of rows 2w / 2w+1, lanes 30 / 31 the right edge.
   const int br = 2 * warp + 1;
   const int col = C::HX + 4 * lane;
-  const int ec = lane == 31 ? C::HX + C::TX : C::HX - 1;
-  const bool edge = lane == 0 || lane == 31;
-  auto plane_ptr = [&](int j) { return ring + (j % C::S) * C::kSlotFloats; };
-  auto wait_full = [&](int j) { mbar_wait(full + (j % C::S), (j / C::S) & 1); };
-  auto release = [&](int j) {
-    __syncwarp();
-    if (lane == 0) mbar_arrive(empty + (j % C::S));
-  };
-  auto ld4 = [&](const float *pl, int row) {
-    return *reinterpret_cast<const float4 *>(pl + row * C::BX + col);
-  };
-  // t+1 planes: row e of the grown tile lives at row e + 1 (guard rows 0 and ER + 1)
-  auto aplane = [&](int j) { return abuf + (j & 1) * C::kAPlaneFloats + C::BX; };
+  const int r0off = br * C::BX + col, r1off = r0off + C::BX;  // own cells inside a staged plane
+  const int ec = lane < 16 ? C::HX - 1 : C::HX + C::TX;
+  const int eoff = (br + (lane & 1)) * C::BX + ec;            // this lane's edge cell
+  const bool edge = lane < 2 || lane >= 30;
+  const int a0off = (2 * warp) * C::BX + col;                 // own cells inside a t+1 plane
+  const int aeoff = (2 * warp + (lane & 1)) * C::BX + ec;
 
   const int gx = x0 + 4 * lane;
   const int ye0 = y0 - 1 + 2 * warp, ye1 = ye0 + 1;  // y of the two rows
   const int xe = x0 - C::HX + ec;                     // x of the edge column
   const bool yin0 = ye0 >= 0 && ye0 < g.n1, yin1 = ye1 >= 0 && ye1 < g.n1;
-  const bool xin[4] = {gx < g.n2, gx + 1 < g.n2, gx + 2 < g.n2, gx + 3 < g.n2};
-  const bool xein = xe >= 0 && xe < g.n2;
-  // output rows: e in [1, h]
-  const bool orow0 = 2 * warp >= 1 && 2 * warp <= h, orow1 = 2 * warp + 1 <= h;
-  const bool full4 = gx + 3 < g.n2;
+  const bool ein = ((lane & 1) ? yin1 : yin0) && xe >= 0 && xe < g.n2;
+  const bool xragged = x0 + C::TX > g.n2;  // only the last x tile of a domain with n2 % 128 != 0
+  const bool orow0 = 2 * warp >= 1 && 2 * warp <= h, orow1 = 2 * warp + 1 <= h;  // rows e in [1, h]
   const int64_t plane_stride = g.ext1 * g.pitch;
 
-  float4 pv0, pv1, zc0, zc1;     // iterate t, planes j-1 and j, own cells
-  float pe0, pe1, ze0, ze1;      // same for the edge column
-  float4 aP0, aP1, aC0, aC1;     // iterate t+1, planes j-2 and j-1, own cells
-  aP0 = aP1 = aC0 = aC1 = make_float4(0.f, 0.f, 0.f, 0.f);
-  wait_full(0);
-  {
-    const float *pl = plane_ptr(0);
-    pv0 = ld4(pl, br);
-    pv1 = ld4(pl, br + 1);
-    pe0 = pl[br * C::BX + ec];
-    pe1 = pl[(br + 1) * C::BX + ec];
-  }
-  release(0);
-  wait_full(1);
-  {
-    const float *pl = plane_ptr(1);
-    zc0 = ld4(pl, br);
-    zc1 = ld4(pl, br + 1);
-    ze0 = pl[br * C::BX + ec];
-    ze1 = pl[(br + 1) * C::BX + ec];
-  }
-
+  struct TP {  // iterate t of one plane: own cells of the two rows, and the edge cell
+    float4 a, b;
+    float e;
+  };
+  struct AP {  // iterate t+1 of one plane, own cells
+    float4 a, b;
+  };
+  TP t0, t1, t2;
+  AP a0, a1, a2;
+  a0.a = a0.b = a1.a = a1.b = a2.a = a2.b = make_float4(0.f, 0.f, 0.f, 0.f);
+  t2.a = t2.b = a0.a;
+  t2.e = 0.f;
   float *orow = out + gidx(g, z0, ye0, gx);  // plane z0, this thread's first row
-  for (int j = 1; j <= np - 2; ++j) {
-    const int z = z0 - 2 + j;  // plane of the t+1 values made in this step
-    wait_full(j + 1);
-    const float *pn = plane_ptr(j + 1);
-    const float *pc = plane_ptr(j);
-    const float4 nx0 = ld4(pn, br), nx1 = ld4(pn, br + 1);
-    const float ne0 = pn[br * C::BX + ec], ne1 = pn[(br + 1) * C::BX + ec];
-    const float4 up = ld4(pc, br - 1);
-    const float4 dn = ld4(pc, br + 2);
-    float l0 = __shfl_up_sync(0xffffffffu, zc0.w, 1);
-    float l1 = __shfl_up_sync(0xffffffffu, zc1.w, 1);
-    float r0 = __shfl_down_sync(0xffffffffu, zc0.x, 1);
-    float r1 = __shfl_down_sync(0xffffffffu, zc1.x, 1);
+
+  auto load_plane = [&](int j, TP &t) {
+    mbar_wait(full + (j & (C::S - 1)), (j / C::S) & 1);
+    const float *pl = ring + (j & (C::S - 1)) * C::kSlotFloats;
+    t.a = *reinterpret_cast<const float4 *>(pl + r0off);
+    t.b = *reinterpret_cast<const float4 *>(pl + r1off);
+    t.e = pl[eoff];
+  };
+  // One step: P, Cn, N are iterate t of planes j-1, j, j+1 (N is loaded here); aP, aC are
+  // iterate t+1 of planes j-2, j-1; aN (plane j) is made here.
+  auto step = [&](int j, const TP &P, const TP &Cn, TP &N, const AP &aP, const AP &aC, AP &aN) {
+    const int z = z0 - 2 + j;
+    load_plane(j + 1, N);
+    const float *pc = ring + (j & (C::S - 1)) * C::kSlotFloats;
+    const float4 up = *reinterpret_cast<const float4 *>(pc + r0off - C::BX);
+    const float4 dn = *reinterpret_cast<const float4 *>(pc + r1off + C::BX);
+    float l0 = __shfl_up_sync(0xffffffffu, Cn.a.w, 1);
+    float l1 = __shfl_up_sync(0xffffffffu, Cn.b.w, 1);
+    float r0 = __shfl_down_sync(0xffffffffu, Cn.a.x, 1);
+    float r1 = __shfl_down_sync(0xffffffffu, Cn.b.x, 1);
     if (lane == 0) {
-      l0 = ze0;  // box column 3 is this lane's edge column
-      l1 = ze1;
+      l0 = pc[r0off - 1];
+      l1 = pc[r1off - 1];
     }
     if (lane == 31) {
-      r0 = ze0;  // box column 132
-      r1 = ze1;
+      r0 = pc[r0off + 4];
+      r1 = pc[r1off + 4];
     }
-    // edge column: its own x neighbours and y neighbours come from the staged plane
-    const float eup = pc[(br - 1) * C::BX + ec], edn = pc[(br + 2) * C::BX + ec];
-    const float el0 = pc[br * C::BX + ec - 1], er0 = pc[br * C::BX + ec + 1];
-    const float el1 = pc[(br + 1) * C::BX + ec - 1], er1 = pc[(br + 1) * C::BX + ec + 1];
-    release(j);
+    const float eup = pc[eoff - C::BX], edn = pc[eoff + C::BX], elf = pc[eoff - 1], ert = pc[eoff + 1];
+    __syncwarp();
+    if (lane == 0) mbar_arrive(empty + (j & (C::S - 1)));  // plane j is not read from the ring again
 
-    // ---- A: iterate t+1 of plane z on the grown tile
-    const bool zin = z >= 0 && z < g.n0;
-    float4 aN0, aN1;
-    aN0.x = zin && yin0 && xin[0] ? HPCX_J7(pv0.x, up.x, l0, zc0.y, zc1.x, nx0.x) : zc0.x;
-    aN0.y = zin && yin0 && xin[1] ? HPCX_J7(pv0.y, up.y, zc0.x, zc0.z, zc1.y, nx0.y) : zc0.y;
-    aN0.z = zin && yin0 && xin[2] ? HPCX_J7(pv0.z, up.z, zc0.y, zc0.w, zc1.z, nx0.z) : zc0.z;
-    aN0.w = zin && yin0 && xin[3] ? HPCX_J7(pv0.w, up.w, zc0.z, r0, zc1.w, nx0.w) : zc0.w;
-    aN1.x = zin && yin1 && xin[0] ? HPCX_J7(pv1.x, zc0.x, l1, zc1.y, dn.x, nx1.x) : zc1.x;
-    aN1.y = zin && yin1 && xin[1] ? HPCX_J7(pv1.y, zc0.y, zc1.x, zc1.z, dn.y, nx1.y) : zc1.y;
-    aN1.z = zin && yin1 && xin[2] ? HPCX_J7(pv1.z, zc0.z, zc1.y, zc1.w, dn.z, nx1.z) : zc1.z;
-    aN1.w = zin && yin1 && xin[3] ? HPCX_J7(pv1.w, zc0.w, zc1.z, r1, dn.w, nx1.w) : zc1.w;
-    const float aE0 = zin && yin0 && xein ? HPCX_J7(pe0, eup, el0, er0, ze1, ne0) : ze0;
-    const float aE1 = zin && yin1 && xein ? HPCX_J7(pe1, ze0, el1, er1, edn, ne1) : ze1;
+    // ---- A: iterate t+1 of plane z on the grown tile; cells outside the domain keep their value
+    aN.a.x = HPCX_J7(P.a.x, up.x, l0, Cn.a.y, Cn.b.x, N.a.x);
+    aN.a.y = HPCX_J7(P.a.y, up.y, Cn.a.x, Cn.a.z, Cn.b.y, N.a.y);
+    aN.a.z = HPCX_J7(P.a.z, up.z, Cn.a.y, Cn.a.w, Cn.b.z, N.a.z);
+    aN.a.w = HPCX_J7(P.a.w, up.w, Cn.a.z, r0, Cn.b.w, N.a.w);
+    aN.b.x = HPCX_J7(P.b.x, Cn.a.x, l1, Cn.b.y, dn.x, N.b.x);
+    aN.b.y = HPCX_J7(P.b.y, Cn.a.y, Cn.b.x, Cn.b.z, dn.y, N.b.y);
+    aN.b.z = HPCX_J7(P.b.z, Cn.a.z, Cn.b.y, Cn.b.w, dn.z, N.b.z);
+    aN.b.w = HPCX_J7(P.b.w, Cn.a.w, Cn.b.z, r1, dn.w, N.b.w);
+    float aE = (EXP & 8) ? Cn.e : HPCX_J7(P.e, eup, elf, ert, edn, N.e);
+    if (z < 0 || z >= g.n0) {  // ghost plane of the domain (uniform over the CTA)
+      aN.a = Cn.a;
+      aN.b = Cn.b;
+      aE = Cn.e;
+    } else {
+      if (!yin0) aN.a = Cn.a;  // ghost rows (uniform over the warp)
+      if (!yin1) aN.b = Cn.b;
+      if (!ein) aE = Cn.e;
+      if (xragged) {           // ghost / unused columns right of the domain (uniform over the CTA)
+        if (gx >= g.n2) { aN.a.x = Cn.a.x; aN.b.x = Cn.b.x; }
+        if (gx + 1 >= g.n2) { aN.a.y = Cn.a.y; aN.b.y = Cn.b.y; }
+        if (gx + 2 >= g.n2) { aN.a.z = Cn.a.z; aN.b.z = Cn.b.z; }
+        if (gx + 3 >= g.n2) { aN.a.w = Cn.a.w; aN.b.w = Cn.b.w; }
+      }
+    }
 
     // ---- B: iterate t+2 of plane z-1 from the t+1 planes z-2 (aP), z-1 (aC), z (aN)
-    if (j >= 3) {
-      const float *ac = aplane(j - 1);
-      const float4 bup = *reinterpret_cast<const float4 *>(ac + (2 * warp - 1) * C::BX + col);
-      const float4 bdn = *reinterpret_cast<const float4 *>(ac + (2 * warp + 2) * C::BX + col);
-      float bl0 = __shfl_up_sync(0xffffffffu, aC0.w, 1);
-      float bl1 = __shfl_up_sync(0xffffffffu, aC1.w, 1);
-      float br0 = __shfl_down_sync(0xffffffffu, aC0.x, 1);
-      float br1 = __shfl_down_sync(0xffffffffu, aC1.x, 1);
+    if (j >= 3 && !(EXP & 1)) {
+      const float *ac = abuf + ((j - 1) & 1) * C::kAPlaneFloats + C::BX;
+      const float4 bup = *reinterpret_cast<const float4 *>(ac + a0off - C::BX);
+      const float4 bdn = *reinterpret_cast<const float4 *>(ac + a0off + 2 * C::BX);
+      float bl0 = __shfl_up_sync(0xffffffffu, aC.a.w, 1);
+      float bl1 = __shfl_up_sync(0xffffffffu, aC.b.w, 1);
+      float br0 = __shfl_down_sync(0xffffffffu, aC.a.x, 1);
+      float br1 = __shfl_down_sync(0xffffffffu, aC.b.x, 1);
       if (lane == 0) {
-        bl0 = ac[(2 * warp) * C::BX + C::HX - 1];
-        bl1 = ac[(2 * warp + 1) * C::BX + C::HX - 1];
+        bl0 = ac[a0off - 1];
+        bl1 = ac[a0off + C::BX - 1];
       }
       if (lane == 31) {
-        br0 = ac[(2 * warp) * C::BX + C::HX + C::TX];
-        br1 = ac[(2 * warp + 1) * C::BX + C::HX + C::TX];
+        br0 = ac[a0off + 4];
+        br1 = ac[a0off + C::BX + 4];
       }
       float4 o0, o1;
-      o0.x = HPCX_J7(aP0.x, bup.x, bl0, aC0.y, aC1.x, aN0.x);
-      o0.y = HPCX_J7(aP0.y, bup.y, aC0.x, aC0.z, aC1.y, aN0.y);
-      o0.z = HPCX_J7(aP0.z, bup.z, aC0.y, aC0.w, aC1.z, aN0.z);
-      o0.w = HPCX_J7(aP0.w, bup.w, aC0.z, br0, aC1.w, aN0.w);
-      o1.x = HPCX_J7(aP1.x, aC0.x, bl1, aC1.y, bdn.x, aN1.x);
-      o1.y = HPCX_J7(aP1.y, aC0.y, aC1.x, aC1.z, bdn.y, aN1.y);
-      o1.z = HPCX_J7(aP1.z, aC0.z, aC1.y, aC1.w, bdn.z, aN1.z);
-      o1.w = HPCX_J7(aP1.w, aC0.w, aC1.z, br1, bdn.w, aN1.w);
-      if (full4) {
+      o0.x = HPCX_J7(aP.a.x, bup.x, bl0, aC.a.y, aC.b.x, aN.a.x);
+      o0.y = HPCX_J7(aP.a.y, bup.y, aC.a.x, aC.a.z, aC.b.y, aN.a.y);
+      o0.z = HPCX_J7(aP.a.z, bup.z, aC.a.y, aC.a.w, aC.b.z, aN.a.z);
+      o0.w = HPCX_J7(aP.a.w, bup.w, aC.a.z, br0, aC.b.w, aN.a.w);
+      o1.x = HPCX_J7(aP.b.x, aC.a.x, bl1, aC.b.y, bdn.x, aN.b.x);
+      o1.y = HPCX_J7(aP.b.y, aC.a.y, aC.b.x, aC.b.z, bdn.y, aN.b.y);
+      o1.z = HPCX_J7(aP.b.z, aC.a.z, aC.b.y, aC.b.w, bdn.z, aN.b.z);
+      o1.w = HPCX_J7(aP.b.w, aC.a.w, aC.b.z, br1, bdn.w, aN.b.w);
+      if (EXP & 4) {
+        if (o0.x == 123.456f && o1.y == 3.f) orow[0] = o0.y;
+      } else if (!xragged) {
         if (orow0) st_cs(reinterpret_cast<float4 *>(orow), o0);
         if (orow1) st_cs(reinterpret_cast<float4 *>(orow + g.pitch), o1);
       } else {
-        const float a0[4] = {o0.x, o0.y, o0.z, o0.w}, a1[4] = {o1.x, o1.y, o1.z, o1.w};
-#pragma unroll
-        for (int k = 0; k < 4; ++k)
-          if (gx + k < g.n2) {
-            if (orow0) orow[k] = a0[k];
-            if (orow1) orow[g.pitch + k] = a1[k];
+        // ragged right edge of the domain (n2 % 128 != 0; rows stay 16-byte aligned)
+        if (gx + 3 < g.n2) {
+          if (orow0) st_cs(reinterpret_cast<float4 *>(orow), o0);
+          if (orow1) st_cs(reinterpret_cast<float4 *>(orow + g.pitch), o1);
+        } else {
+          if (orow0) {
+            if (gx < g.n2) orow[0] = o0.x;
+            if (gx + 1 < g.n2) orow[1] = o0.y;
+            if (gx + 2 < g.n2) orow[2] = o0.z;
           }
+          if (orow1) {
+            if (gx < g.n2) orow[g.pitch] = o1.x;
+            if (gx + 1 < g.n2) orow[g.pitch + 1] = o1.y;
+            if (gx + 2 < g.n2) orow[g.pitch + 2] = o1.z;
+          }
+        }
       }
       orow += plane_stride;
     }
 
     // ---- publish the t+1 plane of this step
     {
-      float *an = aplane(j);
-      *reinterpret_cast<float4 *>(an + (2 * warp) * C::BX + col) = aN0;
-      *reinterpret_cast<float4 *>(an + (2 * warp + 1) * C::BX + col) = aN1;
-      if (edge) {
-        an[(2 * warp) * C::BX + ec] = aE0;
-        an[(2 * warp + 1) * C::BX + ec] = aE1;
-      }
+      float *an = abuf + (j & 1) * C::kAPlaneFloats + C::BX;
+      *reinterpret_cast<float4 *>(an + a0off) = aN.a;
+      *reinterpret_cast<float4 *>(an + a0off + C::BX) = aN.b;
+      if (edge) an[aeoff] = aE;
     }
-    asm volatile("bar.sync 1, %0;" ::"n"(C::kConsumerWarps * 32) : "memory");
-    pv0 = zc0; pv1 = zc1; zc0 = nx0; zc1 = nx1;
-    pe0 = ze0; pe1 = ze1; ze0 = ne0; ze1 = ne1;
-    aP0 = aC0; aP1 = aC1; aC0 = aN0; aC1 = aN1;
+    if (!(EXP & 2)) asm volatile("bar.sync 1, %0;" ::"n"(C::kConsumerWarps * 32) : "memory");
+  };
+
+  load_plane(0, t0);
+  __syncwarp();
+  if (lane == 0) mbar_arrive(empty + 0);
+  load_plane(1, t1);
+  // three steps per trip so that the plane registers rotate by renaming, not by moves
+  const int last = np - 2;
+  for (int j = 1; j <= last; j += 3) {
+    step(j, t0, t1, t2, a2, a0, a1);
+    if (j + 1 > last) break;
+    step(j + 1, t1, t2, t0, a0, a1, a2);
+    if (j + 2 > last) break;
+    step(j + 2, t2, t0, t1, a1, a2, a0);
   }
 }
 #undef HPCX_J7
@@ -876,15 +897,28 @@ hpcx_status launch_jacobi_tb2(hpcx_grid_s *g, void *src, void *dst, int zsplit, 
   const CUtensorMap *lo = jacobi_map(g, src, sp.hmax + 3, &st);
   if (!lo) return st;
   hi = jacobi_map(g, src, sp.hmax + 4, &st);  // may have moved if the cache reallocated
-  static bool configured = false;
-  if (!configured) {
-    HPCX_CUDA(ctx, cudaFuncSetAttribute(jacobi7_tb2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                        C::kSmemBytes));
-    configured = true;
+  static int exp = -1;
+  if (exp < 0) {
+    const char *e = getenv("HPCX_TB_EXP");
+    exp = e ? atoi(e) : 0;
+#define HPCX_TB_ATTR(E) \
+  HPCX_CUDA(ctx, cudaFuncSetAttribute(jacobi7_tb2_kernel<E>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes))
+    HPCX_TB_ATTR(0); HPCX_TB_ATTR(1); HPCX_TB_ATTR(2); HPCX_TB_ATTR(4); HPCX_TB_ATTR(8); HPCX_TB_ATTR(6); HPCX_TB_ATTR(7);
+#undef HPCX_TB_ATTR
   }
   const unsigned ncta = (unsigned)(sp.ntx * sp.nty * sp.zs);
-  jacobi7_tb2_kernel<<<ncta, C::kThreads, C::kSmemBytes, s>>>(*hi, *lo, (float *)dst, geom_of(g), sp,
-                                                            1.0f / 6.0f);
+#define HPCX_TB_GO(E) \
+  jacobi7_tb2_kernel<E><<<ncta, C::kThreads, C::kSmemBytes, s>>>(*hi, *lo, (float *)dst, geom_of(g), sp, 1.0f / 6.0f)
+  switch (exp) {
+    case 1: HPCX_TB_GO(1); break;
+    case 2: HPCX_TB_GO(2); break;
+    case 4: HPCX_TB_GO(4); break;
+    case 8: HPCX_TB_GO(8); break;
+    case 6: HPCX_TB_GO(6); break;
+    case 7: HPCX_TB_GO(7); break;
+    default: HPCX_TB_GO(0); break;
+  }
+#undef HPCX_TB_GO
   return after_launch(ctx, "jacobi7_tb2_kernel");
 }
 
