@@ -642,9 +642,9 @@ struct JacobiTB {
   static constexpr int kAPlaneFloats = (ER + 2) * BX;  // one guard row above and below
   static constexpr int kAOff = S * kSlotBytes;
   static constexpr int kBarOff = kAOff + 2 * kAPlaneFloats * 4;
-  static constexpr int kSmemBytes = kBarOff + 2 * S * 8;
+  static constexpr int kSmemBytes = kBarOff + S * 8;
   static constexpr int kConsumerWarps = 8;
-  static constexpr int kThreads = (kConsumerWarps + 1) * 32;
+  static constexpr int kThreads = kConsumerWarps * 32;  // no producer warp: thread 0 feeds the ring
 };
 
 struct JacobiTBSplit {
@@ -655,9 +655,9 @@ struct JacobiTBSplit {
   mul_rn(add_rn(add_rn(add_rn(add_rn(add_rn(zm, ym), xm), xp), yp), zp), sixth)
 
 // EXP: timing experiments only (HPCX_TB_EXP, results are wrong when non-zero): 1 = no stage B,
-// 2 = no consumer barrier, 4 = no global stores, 8 = no edge columns.
+// 4 = no global stores, 8 = no edge columns.
 template <int EXP>
-__global__ void __maxnreg__(112)
+__global__ void __launch_bounds__(JacobiTB::kThreads, 2)
 jacobi7_tb2_kernel(const __grid_constant__ CUtensorMap map_hi, const __grid_constant__ CUtensorMap map_lo,
                    float *__restrict__ out, GridGeom g, JacobiTBSplit sp, float sixth) {
   using C = JacobiTB;
@@ -665,7 +665,6 @@ jacobi7_tb2_kernel(const __grid_constant__ CUtensorMap map_hi, const __grid_cons
   float *ring = reinterpret_cast<float *>(smem);
   float *abuf = reinterpret_cast<float *>(smem + C::kAOff);
   uint64_t *full = reinterpret_cast<uint64_t *>(smem + C::kBarOff);
-  uint64_t *empty = full + C::S;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int bx = blockIdx.x % sp.ntx;
@@ -679,31 +678,26 @@ jacobi7_tb2_kernel(const __grid_constant__ CUtensorMap map_hi, const __grid_cons
   if (h <= 0 || z1 <= z0) return;
   const int np = z1 - z0 + 4;  // planes z0-2 .. z1+1 of iterate t
 
+  // The per-step barrier of the consumers (below) already proves that plane j has been read by
+  // every warp, so the ring needs no "empty" barriers and no producer warp: thread 0 issues the
+  // TMA load of plane j + S - 1 right after the barrier of step j.
+  const CUtensorMap *map = h == sp.hmax ? &map_hi : &map_lo;
+  const uint32_t box_bytes = (uint32_t)(C::BX * (h + 4) * 4);
+  const int c0 = (int)g.xoff + x0 - C::HX;
+  const int c1 = y0 + (int)g.glo1 - 2;  // may be -1: rows outside the array are zero-filled
+  auto issue = [&](int p) {            // plane p -> slot p & (S-1); thread 0 only
+    mbar_expect_tx(full + (p & (C::S - 1)), box_bytes);
+    tma_load_3d(ring + (p & (C::S - 1)) * C::kSlotFloats, map, c0, c1, z0 - 2 + p + (int)g.glo0,
+                full + (p & (C::S - 1)));
+  };
   if (threadIdx.x == 0) {
-    for (int s = 0; s < C::S; ++s) {
-      mbar_init(full + s, 1);
-      mbar_init(empty + s, C::kConsumerWarps);
-    }
+    for (int s = 0; s < C::S; ++s) mbar_init(full + s, 1);
     mbar_fence_init();
+    tma_prefetch_desc(map);
   }
   __syncthreads();
-
-  if (warp == C::kConsumerWarps) {
-    if (lane == 0) {
-      const CUtensorMap *map = h == sp.hmax ? &map_hi : &map_lo;
-      tma_prefetch_desc(map);
-      const uint32_t bytes = (uint32_t)(C::BX * (h + 4) * 4);
-      const int c0 = (int)g.xoff + x0 - C::HX;
-      const int c1 = y0 + (int)g.glo1 - 2;  // may be -1: rows outside the array are zero-filled
-      for (int j = 0; j < np; ++j) {
-        const int slot = j & (C::S - 1), use = j / C::S;
-        if (use > 0) mbar_wait(empty + slot, (use - 1) & 1);
-        mbar_expect_tx(full + slot, bytes);
-        tma_load_3d(ring + slot * C::kSlotFloats, map, c0, c1, z0 - 2 + j + (int)g.glo0, full + slot);
-      }
-    }
-    return;
-  }
+  if (threadIdx.x == 0)
+    for (int p = 0; p < C::S && p < np; ++p) issue(p);
 
   // ---------------------------------------------------------------- consumers
   // Warp w owns rows e = 2w, 2w+1 of the grown tile (y = y0 - 1 + e), i.e. box rows 2w+1, 2w+2;
@@ -770,8 +764,6 @@ jacobi7_tb2_kernel(const __grid_constant__ CUtensorMap map_hi, const __grid_cons
       r1 = pc[r1off + 4];
     }
     const float eup = pc[eoff - C::BX], edn = pc[eoff + C::BX], elf = pc[eoff - 1], ert = pc[eoff + 1];
-    __syncwarp();
-    if (lane == 0) mbar_arrive(empty + (j & (C::S - 1)));  // plane j is not read from the ring again
 
     // ---- A: iterate t+1 of plane z on the grown tile; cells outside the domain keep their value
     aN.a.x = HPCX_J7(P.a.x, up.x, l0, Cn.a.y, Cn.b.x, N.a.x);
@@ -858,12 +850,12 @@ jacobi7_tb2_kernel(const __grid_constant__ CUtensorMap map_hi, const __grid_cons
       *reinterpret_cast<float4 *>(an + a0off + C::BX) = aN.b;
       if (edge) an[aeoff] = aE;
     }
-    if (!(EXP & 2)) asm volatile("bar.sync 1, %0;" ::"n"(C::kConsumerWarps * 32) : "memory");
+    __syncthreads();
+    // every warp is done with planes <= j: refill the slot of plane j - 1 with plane j + S - 1
+    if (threadIdx.x == 0 && j + C::S - 1 < np) issue(j + C::S - 1);
   };
 
   load_plane(0, t0);
-  __syncwarp();
-  if (lane == 0) mbar_arrive(empty + 0);
   load_plane(1, t1);
   // three steps per trip so that the plane registers rotate by renaming, not by moves
   const int last = np - 2;
@@ -903,7 +895,7 @@ hpcx_status launch_jacobi_tb2(hpcx_grid_s *g, void *src, void *dst, int zsplit, 
     exp = e ? atoi(e) : 0;
 #define HPCX_TB_ATTR(E) \
   HPCX_CUDA(ctx, cudaFuncSetAttribute(jacobi7_tb2_kernel<E>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes))
-    HPCX_TB_ATTR(0); HPCX_TB_ATTR(1); HPCX_TB_ATTR(2); HPCX_TB_ATTR(4); HPCX_TB_ATTR(8); HPCX_TB_ATTR(6); HPCX_TB_ATTR(7);
+    HPCX_TB_ATTR(0); HPCX_TB_ATTR(1); HPCX_TB_ATTR(4); HPCX_TB_ATTR(8);
 #undef HPCX_TB_ATTR
   }
   const unsigned ncta = (unsigned)(sp.ntx * sp.nty * sp.zs);
@@ -911,11 +903,8 @@ hpcx_status launch_jacobi_tb2(hpcx_grid_s *g, void *src, void *dst, int zsplit, 
   jacobi7_tb2_kernel<E><<<ncta, C::kThreads, C::kSmemBytes, s>>>(*hi, *lo, (float *)dst, geom_of(g), sp, 1.0f / 6.0f)
   switch (exp) {
     case 1: HPCX_TB_GO(1); break;
-    case 2: HPCX_TB_GO(2); break;
     case 4: HPCX_TB_GO(4); break;
     case 8: HPCX_TB_GO(8); break;
-    case 6: HPCX_TB_GO(6); break;
-    case 7: HPCX_TB_GO(7); break;
     default: HPCX_TB_GO(0); break;
   }
 #undef HPCX_TB_GO
