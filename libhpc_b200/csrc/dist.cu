@@ -18,6 +18,10 @@ using namespace hpcx;
 namespace hpcx {
 hpcx_status jacobi7_launch(hpcx_grid_s *g, void *src, void *dst, int variant, int zsplit,
                            int64_t zbeg, int64_t zend, cudaStream_t s, const JacobiPeer *peer);
+hpcx_status allreduce_sum(hpcx_ctx ctx, void *buf, size_t count, int dtype, cudaStream_t s);
+bool jacobi7_tb2_supported(hpcx_grid_s *g);
+hpcx_status jacobi7_tb2_launch(hpcx_grid_s *g, void *src, void *dst, int zsplit, int64_t zbeg, int64_t zend,
+                               bool nb_lo, bool nb_hi, cudaStream_t s);
 hpcx_status spmv_launch_blocks(hpcx_csr A, const RowBlock *d_blocks, int64_t nblocks, const void *x,
                                void *y, cudaStream_t s, void *dot_part);
 hpcx_status spmv_launch_fixup_tables(hpcx_csr A, const int32_t *long_row, const int32_t *long_off,
@@ -100,9 +104,9 @@ struct hpcx_halo_plan_s {
 
 namespace {
 
-// Exchange one ghost plane per side of buffer `buf` (device layout of grid g) with the z
+// Exchange w ghost planes per side of buffer `buf` (device layout of grid g) with the z
 // neighbours.  Planes are contiguous in the device layout, so nothing is packed.
-hpcx_status exchange_planes(hpcx_grid g, void *buf, cudaStream_t s) {
+hpcx_status exchange_planes(hpcx_grid g, void *buf, cudaStream_t s, int64_t w = 1) {
   hpcx_ctx ctx = g->ctx;
   if (ctx->nranks <= 1) return HPCX_OK;
   const int64_t plane = g->ext[1] * g->pitch;
@@ -112,12 +116,12 @@ hpcx_status exchange_planes(hpcx_grid g, void *buf, cudaStream_t s) {
   const int lo = ctx->rank - 1, hi = ctx->rank + 1;
   HPCX_NCCL(ctx, g_nccl.GroupStart());
   if (lo >= 0) {
-    HPCX_NCCL(ctx, g_nccl.Send(at(0), (size_t)plane, ty, lo, comm_of(ctx), s));
-    HPCX_NCCL(ctx, g_nccl.Recv(at(-1), (size_t)plane, ty, lo, comm_of(ctx), s));
+    HPCX_NCCL(ctx, g_nccl.Send(at(0), (size_t)(w * plane), ty, lo, comm_of(ctx), s));
+    HPCX_NCCL(ctx, g_nccl.Recv(at(-w), (size_t)(w * plane), ty, lo, comm_of(ctx), s));
   }
   if (hi < ctx->nranks) {
-    HPCX_NCCL(ctx, g_nccl.Send(at(g->n[0] - 1), (size_t)plane, ty, hi, comm_of(ctx), s));
-    HPCX_NCCL(ctx, g_nccl.Recv(at(g->n[0]), (size_t)plane, ty, hi, comm_of(ctx), s));
+    HPCX_NCCL(ctx, g_nccl.Send(at(g->n[0] - w), (size_t)(w * plane), ty, hi, comm_of(ctx), s));
+    HPCX_NCCL(ctx, g_nccl.Recv(at(g->n[0]), (size_t)(w * plane), ty, hi, comm_of(ctx), s));
   }
   HPCX_NCCL(ctx, g_nccl.GroupEnd());
   return HPCX_OK;
@@ -328,6 +332,25 @@ hpcx_status hpcx_stencil_dist_plan(hpcx_ctx ctx, hpcx_grid in, hpcx_grid out,
     return fail(ctx, HPCX_UNSUPPORTED, "the peer-store transport needs the fp32 TMA sweep");
   if (ctx->nranks > 1 && !ctx->nccl_comm)
     return fail(ctx, HPCX_NCCL_ERROR, "hpcx_comm_init has not been called");
+  if (st->variant == HPCX_VARIANT_TEMPORAL) {
+    // Two sweeps per pass: a slab trades TWO planes per side and pass, so every slab needs ghost
+    // width >= 2 and at least two planes.  The ranks agree on the verdict (sum of per-rank
+    // violations) so that nobody is left waiting in a receive.
+    if (transport != 0 || !jacobi7_tb2_supported(in))
+      return fail(ctx, HPCX_UNSUPPORTED, "the temporally blocked Jacobi needs fp32, a tensor-map driver and transport 0");
+    if (ctx->nranks > 1) {
+      float bad = (in->desc.lo < 2 || in->desc.hi < 2 || in->n[0] < 2) ? 1.f : 0.f, *d_bad = nullptr;
+      HPCX_CUDA(ctx, cudaMalloc(&d_bad, sizeof(float)));
+      cudaMemcpyAsync(d_bad, &bad, sizeof(float), cudaMemcpyHostToDevice, ctx->comm);
+      hpcx_status rc = hpcx::allreduce_sum(ctx, d_bad, 1, HPCX_F32, ctx->comm);
+      if (rc == HPCX_OK && cudaMemcpyAsync(&bad, d_bad, sizeof(float), cudaMemcpyDeviceToHost, ctx->comm) == cudaSuccess)
+        cudaStreamSynchronize(ctx->comm);
+      cudaFree(d_bad);
+      if (rc != HPCX_OK) return rc;
+      if (bad != 0.f)
+        return fail(ctx, HPCX_INVALID_ARG, "TEMPORAL over slabs needs ghost widths >= 2 and >= 2 planes on every rank");
+    }
+  }
   hpcx_halo_plan p = new (std::nothrow) hpcx_halo_plan_s();
   if (!p) return fail(ctx, HPCX_OOM, "host allocation failed");
   p->ctx = ctx;
@@ -407,6 +430,9 @@ static hpcx_status dist_sweep_peer(hpcx_halo_plan p, int32_t steps, cudaStream_t
 //   comm stream   : [wait ev_bnd] send dst boundary planes / receive dst ghost planes
 //   compute stream: interior planes 1 .. n-2 (overlaps the exchange)
 // The ghost planes a step needs were produced by the previous step's exchange.
+// HPCX_VARIANT_TEMPORAL runs steps/2 two-sweep passes the same way with TWO planes per side (the
+// neighbour's boundary plane is advanced redundantly on this rank), then one single sweep when
+// steps is odd: the bytes exchanged per sweep are unchanged, the messages per sweep halve.
 hpcx_status hpcx_stencil_dist_sweep(hpcx_halo_plan p, int32_t steps, void *stream) {
   if (!p) return HPCX_INVALID_ARG;
   hpcx_ctx ctx = p->ctx;
@@ -420,7 +446,7 @@ hpcx_status hpcx_stencil_dist_sweep(hpcx_halo_plan p, int32_t steps, void *strea
   // Make the ghosts of the first source iterate consistent with the neighbours.
   HPCX_CUDA(ctx, cudaEventRecord(p->ev_start, cs));
   HPCX_CUDA(ctx, cudaStreamWaitEvent(ms, p->ev_start, 0));
-  rc = exchange_planes(g, p->in->dev, ms);
+  rc = exchange_planes(g, p->in->dev, ms, (p->st.variant == HPCX_VARIANT_TEMPORAL && steps >= 2) ? 2 : 1);
   if (rc != HPCX_OK) return rc;
   HPCX_CUDA(ctx, cudaEventRecord(p->ev_recv, ms));
 
@@ -429,25 +455,39 @@ hpcx_status hpcx_stencil_dist_sweep(hpcx_halo_plan p, int32_t steps, void *strea
     return dist_sweep_peer(p, steps, cs, stream == nullptr);
   }
 
+  // A pass advances the slab by w sweeps (w = 2: the temporally blocked kernel) and needs w valid
+  // ghost planes per side of its source; the exchange after a pass carries the width the NEXT pass
+  // reads.  Boundary = the w planes next to each z neighbour.
+  const bool temporal = p->st.variant == HPCX_VARIANT_TEMPORAL;
+  const bool nb_lo = ctx->rank > 0, nb_hi = ctx->rank + 1 < ctx->nranks;
+  const int passes = temporal ? steps / 2 + (steps & 1) : steps;
   void *src = p->in->dev, *dst = p->out->dev;
-  for (int t = 0; t < steps; ++t) {
+  for (int t = 0; t < passes; ++t) {
+    const bool two = temporal && t < steps / 2;
+    const int64_t w = two ? 2 : 1;
+    const int64_t lo_end = std::min<int64_t>(w, nz), hi_beg = std::max<int64_t>(lo_end, nz - w);
+    auto launch = [&](int64_t zb, int64_t ze, int zsplit) -> hpcx_status {
+      if (ze <= zb) return HPCX_OK;
+      if (two) return jacobi7_tb2_launch(g, src, dst, zsplit, zb, ze, nb_lo, nb_hi, cs);
+      return jacobi7_launch(g, src, dst, temporal ? HPCX_VARIANT_TMA : p->st.variant, zsplit, zb, ze, cs, nullptr);
+    };
     HPCX_CUDA(ctx, cudaStreamWaitEvent(cs, p->ev_recv, 0));
-    rc = jacobi7_launch(g, src, dst, p->st.variant, 1, 0, 1, cs, nullptr);
-    if (rc == HPCX_OK && nz > 1) rc = jacobi7_launch(g, src, dst, p->st.variant, 1, nz - 1, nz, cs, nullptr);
+    rc = launch(0, lo_end, 1);
+    if (rc == HPCX_OK) rc = launch(hi_beg, nz, 1);
     if (rc != HPCX_OK) return rc;
-    if (t + 1 < steps) {
+    if (t + 1 < passes) {
+      const int64_t wnext = (temporal && t + 1 < steps / 2) ? 2 : 1;
       HPCX_CUDA(ctx, cudaEventRecord(p->ev_bnd, cs));
       HPCX_CUDA(ctx, cudaStreamWaitEvent(ms, p->ev_bnd, 0));
-      rc = exchange_planes(g, dst, ms);
+      rc = exchange_planes(g, dst, ms, wnext);
       if (rc != HPCX_OK) return rc;
       HPCX_CUDA(ctx, cudaEventRecord(p->ev_recv, ms));
     }
-    if (nz > 2) {
-      rc = jacobi7_launch(g, src, dst, p->st.variant, p->st.zsplit, 1, nz - 1, cs, nullptr);
-      if (rc != HPCX_OK) return rc;
-    }
+    rc = launch(lo_end, hi_beg, temporal ? (two ? p->st.zsplit : 0) : p->st.zsplit);
+    if (rc != HPCX_OK) return rc;
     std::swap(src, dst);
   }
+  steps = passes;  // parity of the buffer swap below
   if ((steps & 1) == 0) std::swap(p->in->dev, p->out->dev);
   if (!stream) HPCX_CUDA(ctx, cudaStreamSynchronize(cs));
   return HPCX_OK;

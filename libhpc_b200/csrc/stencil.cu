@@ -649,6 +649,10 @@ struct JacobiTB {
 
 struct JacobiTBSplit {
   int ntx, nty, zs, hmax;
+  int zbeg, zend;  // planes written by this launch
+  int zlo, zhi;    // planes whose iterate t+1 is COMPUTED: [0, n0) on one GPU; a slab with a z
+                   // neighbour grows by one plane on that side (the neighbour's boundary plane,
+                   // recomputed here from the two exchanged ghost planes)
 };
 
 #define HPCX_J7(zm, ym, xm, xp, yp, zp) \
@@ -673,8 +677,8 @@ jacobi7_tb2_kernel(const __grid_constant__ CUtensorMap map_hi, const __grid_cons
   const int x0 = bx * C::TX;
   const int y0 = (int)((int64_t)by * g.n1 / sp.nty);
   const int h = (int)((int64_t)(by + 1) * g.n1 / sp.nty) - y0;
-  const int z0 = (int)((int64_t)bz * g.n0 / sp.zs);
-  const int z1 = (int)((int64_t)(bz + 1) * g.n0 / sp.zs);
+  const int z0 = sp.zbeg + (int)((int64_t)bz * (sp.zend - sp.zbeg) / sp.zs);
+  const int z1 = sp.zbeg + (int)((int64_t)(bz + 1) * (sp.zend - sp.zbeg) / sp.zs);
   if (h <= 0 || z1 <= z0) return;
   const int np = z1 - z0 + 4;  // planes z0-2 .. z1+1 of iterate t
 
@@ -775,7 +779,7 @@ jacobi7_tb2_kernel(const __grid_constant__ CUtensorMap map_hi, const __grid_cons
     aN.b.z = HPCX_J7(P.b.z, Cn.a.z, Cn.b.y, Cn.b.w, dn.z, N.b.z);
     aN.b.w = HPCX_J7(P.b.w, Cn.a.w, Cn.b.z, r1, dn.w, N.b.w);
     float aE = (EXP & 8) ? Cn.e : HPCX_J7(P.e, eup, elf, ert, edn, N.e);
-    if (z < 0 || z >= g.n0) {  // ghost plane of the domain (uniform over the CTA)
+    if (z < sp.zlo || z >= sp.zhi) {  // ghost plane of the domain (uniform over the CTA)
       aN.a = Cn.a;
       aN.b = Cn.b;
       aE = Cn.e;
@@ -872,16 +876,22 @@ jacobi7_tb2_kernel(const __grid_constant__ CUtensorMap map_hi, const __grid_cons
 
 // Two sweeps src -> dst in one pass (HPCX_VARIANT_TEMPORAL).  Tiles of 128 x <= 14 cells, z
 // segments chosen so that the CTA count is about two per SM (the kernel's residency).
-hpcx_status launch_jacobi_tb2(hpcx_grid_s *g, void *src, void *dst, int zsplit, cudaStream_t s) {
+hpcx_status launch_jacobi_tb2(hpcx_grid_s *g, void *src, void *dst, int zsplit, int64_t zbeg, int64_t zend,
+                              bool nb_lo, bool nb_hi, cudaStream_t s) {
   using C = JacobiTB;
   hpcx_ctx ctx = g->ctx;
+  if (zend <= zbeg) return HPCX_OK;
   JacobiTBSplit sp;
+  sp.zbeg = (int)zbeg;
+  sp.zend = (int)zend;
+  sp.zlo = nb_lo ? -1 : 0;
+  sp.zhi = (int)g->n[0] + (nb_hi ? 1 : 0);
   sp.ntx = (int)((g->n[2] + C::TX - 1) / C::TX);
   sp.nty = (int)((g->n[1] + C::HO - 1) / C::HO);
   sp.hmax = (int)((g->n[1] + sp.nty - 1) / sp.nty);
   const int64_t tiles = (int64_t)sp.ntx * sp.nty;
   int64_t zs = zsplit > 0 ? zsplit : std::max<int64_t>(1, (2 * (int64_t)ctx->sm_count + tiles / 2) / tiles);
-  zs = std::min<int64_t>(zs, zsplit > 0 ? g->n[0] : std::max<int64_t>(1, g->n[0] / 16));
+  zs = std::min<int64_t>(zs, zsplit > 0 ? zend - zbeg : std::max<int64_t>(1, (zend - zbeg) / 16));
   sp.zs = (int)std::max<int64_t>(zs, 1);
   hpcx_status st = HPCX_OK;
   const CUtensorMap *hi = jacobi_map(g, src, sp.hmax + 4, &st);
@@ -930,6 +940,20 @@ hpcx_status jacobi7_launch(hpcx_grid_s *g, void *src, void *dst, int variant, in
   }
   return launch_jacobi_tma(g, src, dst, zsplit, zbeg, zend, peer, s);
 }
+
+bool jacobi7_tb2_supported(hpcx_grid_s *g) {
+  return g->desc.dtype == HPCX_F32 && g->ctx->encode_tiled && g->n[2] < (1 << 30);
+}
+
+// Two Jacobi sweeps src -> dst in one pass over planes [zbeg, zend) (shared with dist.cu).  nb_lo /
+// nb_hi: the slab has a z neighbour on that side, i.e. ghost planes -2, -1 / n0, n0+1 of `src`
+// hold the neighbour's iterate t and iterate t+1 of planes -1 / n0 is computed, not copied.
+hpcx_status jacobi7_tb2_launch(hpcx_grid_s *g, void *src, void *dst, int zsplit, int64_t zbeg, int64_t zend,
+                               bool nb_lo, bool nb_hi, cudaStream_t s) {
+  if (!jacobi7_tb2_supported(g))
+    return fail(g->ctx, HPCX_UNSUPPORTED, "the temporally blocked Jacobi needs fp32 and a tensor-map driver");
+  return launch_jacobi_tb2(g, src, dst, zsplit, zbeg, zend, nb_lo, nb_hi, s);
+}
 }  // namespace hpcx
 
 extern "C" hpcx_status hpcx_stencil_sweep(hpcx_grid in, hpcx_grid out, const hpcx_stencil_desc *st,
@@ -956,7 +980,7 @@ extern "C" hpcx_status hpcx_stencil_sweep(hpcx_grid in, hpcx_grid out, const hpc
                           in->desc.hi == out->desc.hi,
                  "JACOBI7 needs identical ghost widths >= 1 on both grids");
     const bool temporal = st->variant == HPCX_VARIANT_TEMPORAL;
-    if (temporal && !(in->desc.dtype == HPCX_F32 && ctx->encode_tiled && in->n[2] < (1 << 30)))
+    if (temporal && !hpcx::jacobi7_tb2_supported(in))
       return fail(ctx, HPCX_UNSUPPORTED, "the temporally blocked Jacobi needs fp32 and a tensor-map driver");
     // TEMPORAL: steps/2 fused two-sweep passes, then one single sweep when steps is odd
     const int passes = temporal ? steps / 2 + (steps & 1) : steps;
@@ -964,7 +988,7 @@ extern "C" hpcx_status hpcx_stencil_sweep(hpcx_grid in, hpcx_grid out, const hpc
       void *src = (t & 1) ? out->dev : in->dev;
       void *dst = (t & 1) ? in->dev : out->dev;
       if (temporal && t < steps / 2)
-        rc = launch_jacobi_tb2(in, src, dst, st->zsplit, s);
+        rc = launch_jacobi_tb2(in, src, dst, st->zsplit, 0, in->n[0], false, false, s);
       else
         rc = jacobi7_launch(in, src, dst, temporal ? HPCX_VARIANT_TMA : st->variant, temporal ? 0 : st->zsplit, 0,
                             in->n[0], s, nullptr);

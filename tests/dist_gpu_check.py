@@ -78,6 +78,44 @@ def main():
         ga.destroy()
         gb.destroy()
 
+    # ---- stencil, two sweeps per pass over slabs (transport 0, ghost width 2, two planes per side)
+    for (nz, ny, nx), steps, gw in (((8 * world, 20, 140), 6, 2), ((2 * world + 1, 30, 260), 5, 2),
+                                    ((5 * world, 15, 128), 4, 3), ((3 * world, 14, 40), 1, 2)):
+        ext = (nz + 2 * gw, ny + 2 * gw, nx + 2 * gw)
+        full = oracle.fill(ext[0] * ext[1] * ext[2], 11, np.float32)
+        b = hp.partition_slabs(nz, world)
+        assert int(np.diff(b).min()) >= 2
+        z0, z1 = int(b[rank]), int(b[rank + 1])
+        slab = np.ascontiguousarray(full.reshape(ext)[z0:z1 + 2 * gw]).ravel()
+        ga = hp.DeviceGrid(ctx, (z1 - z0, ny, nx), np.float32, gw)
+        gb = hp.DeviceGrid(ctx, (z1 - z0, ny, nx), np.float32, gw)
+        ga.upload(slab)
+        gb.upload(slab)
+        plan = hd.HaloPlan(ctx, ga, gb, hp.STENCIL_JACOBI7, hp.VARIANT_TEMPORAL, transport=0)
+        done = 0
+        for k in (steps, 2, 3):  # in -> out semantics: each call sweeps `in` k times into `out`
+            plan.sweep(k)
+            total = done + k
+            want = oracle.jacobi7(full, nz, ny, nx, gw, gw, total).reshape(ext)
+            out = gb.download().reshape(z1 - z0 + 2 * gw, ny + 2 * gw, nx + 2 * gw)
+            assert bits_equal(np.ascontiguousarray(out[gw:-gw, gw:-gw, gw:-gw]),
+                              np.ascontiguousarray(want[z0 + gw:z1 + gw, gw:-gw, gw:-gw])), (rank, nz, "temporal", k)
+            done = total - (1 if k & 1 else 2)  # `in` holds the source of the call's last pass
+        plan.destroy()
+        ga.destroy()
+        gb.destroy()
+    if world > 1:
+        # a slab with ghost width 1 cannot trade two planes: every rank must refuse, none may hang
+        ga = hp.DeviceGrid(ctx, (4, 8, 32), np.float32, 1)
+        gb = hp.DeviceGrid(ctx, (4, 8, 32), np.float32, 1)
+        try:
+            hd.HaloPlan(ctx, ga, gb, hp.STENCIL_JACOBI7, hp.VARIANT_TEMPORAL, transport=0)
+            raise AssertionError("ghost width 1 accepted for TEMPORAL over slabs")
+        except hp.HpcxError:
+            pass
+        ga.destroy()
+        gb.destroy()
+
     # ---- SpMV: banded (C4 shape) by rows, power-law by nnz
     for name, (rp, col, val), mode in (("op27", synth.op27(16, index_dtype=np.int64), 0),
                                        ("rmat", synth.rmat(13, 16, 24, index_dtype=np.int64), 1)):
