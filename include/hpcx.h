@@ -336,7 +336,11 @@ HPCX_API hpcx_status hpcx_comm_ipc_close(hpcx_ctx ctx, void *peer_ptr);
  *   1  fused: one kernel per sweep whose boundary CTAs store their plane straight into the
  *      neighbour's ghost plane over NVLink (CUDA IPC peer windows) and publish a sweep-number
  *      flag that the neighbour's next sweep acquires before reading the ghost (fp32 TMA sweep
- *      only; plan creation is collective over the communicator). */
+ *      only; plan creation is collective over the communicator).
+ * HPCX_VARIANT_TEMPORAL (transport 0 only; plan creation is collective): two sweeps per pass,
+ * TWO ghost planes traded per side and pass — every slab needs lo,hi >= 2 and >= 2 planes
+ * (HPCX_INVALID_ARG on every rank otherwise).  The neighbour's boundary plane is advanced
+ * redundantly on this rank; results stay bit-identical to single sweeps. */
 typedef struct hpcx_halo_plan_s *hpcx_halo_plan;
 HPCX_API hpcx_status hpcx_stencil_dist_plan(hpcx_ctx ctx, hpcx_grid in, hpcx_grid out,
                                             const hpcx_stencil_desc *st, int32_t transport,

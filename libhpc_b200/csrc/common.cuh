@@ -18,6 +18,7 @@
 struct hpcx_ctx_s {
   int device = 0;
   int sm_count = 148;
+  int64_t l2_bytes = 126 << 20;
   int cc_major = 0, cc_minor = 0;
   cudaStream_t compute = nullptr;  // default stream of the context
   cudaStream_t comm = nullptr;     // halo exchange / copy pipeline

@@ -60,6 +60,7 @@ hpcx_status hpcx_init(int32_t device, hpcx_ctx *out) {
   cudaDeviceProp prop;
   HPCX_CUDA(ctx, cudaGetDeviceProperties(&prop, device));
   ctx->sm_count = prop.multiProcessorCount;
+  ctx->l2_bytes = prop.l2CacheSize > 0 ? prop.l2CacheSize : ctx->l2_bytes;
   ctx->cc_major = prop.major;
   ctx->cc_minor = prop.minor;
   if (prop.major != 10)

@@ -21,7 +21,7 @@ hpcx_status jacobi7_launch(hpcx_grid_s *g, void *src, void *dst, int variant, in
 hpcx_status allreduce_sum(hpcx_ctx ctx, void *buf, size_t count, int dtype, cudaStream_t s);
 bool jacobi7_tb2_supported(hpcx_grid_s *g);
 hpcx_status jacobi7_tb2_launch(hpcx_grid_s *g, void *src, void *dst, int zsplit, int64_t zbeg, int64_t zend,
-                               bool nb_lo, bool nb_hi, cudaStream_t s);
+                               bool nb_lo, bool nb_hi, cudaStream_t s, int64_t zbeg2 = 0, int64_t zend2 = 0);
 hpcx_status spmv_launch_blocks(hpcx_csr A, const RowBlock *d_blocks, int64_t nblocks, const void *x,
                                void *y, cudaStream_t s, void *dot_part);
 hpcx_status spmv_launch_fixup_tables(hpcx_csr A, const int32_t *long_row, const int32_t *long_off,
@@ -472,8 +472,12 @@ hpcx_status hpcx_stencil_dist_sweep(hpcx_halo_plan p, int32_t steps, void *strea
       return jacobi7_launch(g, src, dst, temporal ? HPCX_VARIANT_TMA : p->st.variant, zsplit, zb, ze, cs, nullptr);
     };
     HPCX_CUDA(ctx, cudaStreamWaitEvent(cs, p->ev_recv, 0));
-    rc = launch(0, lo_end, 1);
-    if (rc == HPCX_OK) rc = launch(hi_beg, nz, 1);
+    if (two) {  // both boundary strips in one launch
+      rc = jacobi7_tb2_launch(g, src, dst, 1, 0, lo_end, nb_lo, nb_hi, cs, hi_beg, nz);
+    } else {
+      rc = launch(0, lo_end, 1);
+      if (rc == HPCX_OK) rc = launch(hi_beg, nz, 1);
+    }
     if (rc != HPCX_OK) return rc;
     if (t + 1 < passes) {
       const int64_t wnext = (temporal && t + 1 < steps / 2) ? 2 : 1;

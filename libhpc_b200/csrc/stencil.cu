@@ -19,6 +19,7 @@
 #include "grid.cuh"
 
 #include <algorithm>
+#include <cmath>
 #include <type_traits>
 
 using namespace hpcx;
@@ -443,6 +444,171 @@ jacobi7_tma_kernel(const __grid_constant__ CUtensorMap map_hi, const __grid_cons
     jacobi7_consume<S, false>(ring, full, empty, out, g, pr, x0, y0, h, zfirst, np, sp.ntx * sp.nty, sixth);
 }
 
+// Single sweep without a producer warp (the default): the same ring, boxes, thread mapping and
+// peer-store halo transport as above, but the CTA's per-plane barrier — every warp has read
+// plane j out of shared memory — is what frees a slot, and thread 0 issues the next TMA load
+// right after it.  Eight warps instead of nine (register allocation is per four warps), no
+// "empty" mbarriers and no spinning producer competing for issue slots.
+template <int S>
+__global__ void __launch_bounds__(256, 3)
+jacobi7_ring_kernel(const __grid_constant__ CUtensorMap map_hi, const __grid_constant__ CUtensorMap map_lo,
+                    float *__restrict__ out, GridGeom g, JacobiSplit sp, JacobiPeer pr, int zbeg, int zend,
+                    float sixth) {
+  using C = JacobiCfg<S>;
+  extern __shared__ __align__(128) unsigned char smem[];
+  float *ring = reinterpret_cast<float *>(smem);
+  uint64_t *full = reinterpret_cast<uint64_t *>(smem + C::kBarOff);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int bx = blockIdx.x % sp.ntx;
+  const int by = (blockIdx.x / sp.ntx) % sp.nty;
+  const int bz = blockIdx.x / (sp.ntx * sp.nty);
+  const int x0 = bx * C::TX;
+  const int y0 = (int)((int64_t)by * g.n1 / sp.nty);
+  const int h = (int)((int64_t)(by + 1) * g.n1 / sp.nty) - y0;
+  const int nzr = zend - zbeg;
+  const int z0 = zbeg + (int)((int64_t)bz * nzr / sp.zs);
+  const int z1 = zbeg + (int)((int64_t)(bz + 1) * nzr / sp.zs);
+  const int np = z1 - z0 + 2;  // planes z0-1 .. z1
+  if (h <= 0 || z1 <= z0) return;
+
+  const CUtensorMap *map = h == sp.hmax ? &map_hi : &map_lo;
+  const uint32_t box_bytes = (uint32_t)(C::BX * (h + 2) * 4);
+  const int c0 = (int)g.xoff + x0 - C::HX;
+  const int c1 = y0 + (int)g.glo1 - 1;
+  auto issue = [&](int p) {  // plane p (z = z0 - 1 + p) -> slot p % S; thread 0 only
+    if (pr.wait_val) {       // ghost planes filled by a neighbour: wait for its sweep number first
+      const int z = z0 - 1 + p;
+      if (z == -1 && pr.sig_lo) wait_flag(pr.flags + 0, pr.wait_val, pr.counters + 2);
+      if (z == (int)g.n0 && pr.sig_hi) wait_flag(pr.flags + 1, pr.wait_val, pr.counters + 2);
+    }
+    mbar_expect_tx(full + p % S, box_bytes);
+    tma_load_3d(ring + (p % S) * C::kSlotFloats, map, c0, c1, z0 - 1 + p + (int)g.glo0, full + p % S);
+  };
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < S; ++s) mbar_init(full + s, 1);
+    mbar_fence_init();
+    tma_prefetch_desc(map);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0)
+    for (int p = 0; p < S && p < np; ++p) issue(p);
+
+  // Warp w owns tile rows 2w and 2w+1 (box rows 2w+1, 2w+2); lane owns x0 + 4*lane .. +3.
+  const int br = 2 * warp + 1;
+  const int col = C::HX + 4 * lane;
+  const int r0off = br * C::BX + col, r1off = r0off + C::BX;
+  const int gx = x0 + 4 * lane;
+  const bool row0 = 2 * warp < h, row1 = 2 * warp + 1 < h;
+  const bool full4 = gx + 3 < g.n2;
+  const int64_t plane_stride = g.ext1 * g.pitch;
+  float *orow = out + gidx(g, z0, y0 + 2 * warp, gx);
+  const int64_t inplane = (y0 + 2 * warp + g.glo1) * g.pitch + g.xoff + gx;  // offset inside a plane
+  const uint32_t tiles_xy = (uint32_t)(sp.ntx * sp.nty);
+
+  struct PL {
+    float4 a, b;
+  };
+  PL t0, t1, t2;
+  auto load_plane = [&](int j, PL &t) {
+    mbar_wait(full + j % S, (j / S) & 1);
+    const float *pl = ring + (j % S) * C::kSlotFloats;
+    t.a = *reinterpret_cast<const float4 *>(pl + r0off);
+    t.b = *reinterpret_cast<const float4 *>(pl + r1off);
+  };
+#define HPCX_J7(zm, ym, xm, xp, yp, zp) \
+  mul_rn(add_rn(add_rn(add_rn(add_rn(add_rn(zm, ym), xm), xp), yp), zp), sixth)
+  // P, Cn, N: planes j-1, j, j+1 (N is loaded here); writes plane z0 - 1 + j
+  auto step = [&](int j, const PL &P, const PL &Cn, PL &N) {
+    load_plane(j + 1, N);
+    const float *pc = ring + (j % S) * C::kSlotFloats;
+    const float4 up = *reinterpret_cast<const float4 *>(pc + r0off - C::BX);
+    const float4 dn = *reinterpret_cast<const float4 *>(pc + r1off + C::BX);
+    float l0 = __shfl_up_sync(0xffffffffu, Cn.a.w, 1);
+    float l1 = __shfl_up_sync(0xffffffffu, Cn.b.w, 1);
+    float r0 = __shfl_down_sync(0xffffffffu, Cn.a.x, 1);
+    float r1 = __shfl_down_sync(0xffffffffu, Cn.b.x, 1);
+    if (lane == 0) {
+      l0 = pc[r0off - 1];
+      l1 = pc[r1off - 1];
+    }
+    if (lane == 31) {
+      r0 = pc[r0off + 4];
+      r1 = pc[r1off + 4];
+    }
+    float4 o0, o1;
+    o0.x = HPCX_J7(P.a.x, up.x, l0, Cn.a.y, Cn.b.x, N.a.x);
+    o0.y = HPCX_J7(P.a.y, up.y, Cn.a.x, Cn.a.z, Cn.b.y, N.a.y);
+    o0.z = HPCX_J7(P.a.z, up.z, Cn.a.y, Cn.a.w, Cn.b.z, N.a.z);
+    o0.w = HPCX_J7(P.a.w, up.w, Cn.a.z, r0, Cn.b.w, N.a.w);
+    o1.x = HPCX_J7(P.b.x, Cn.a.x, l1, Cn.b.y, dn.x, N.b.x);
+    o1.y = HPCX_J7(P.b.y, Cn.a.y, Cn.b.x, Cn.b.z, dn.y, N.b.y);
+    o1.z = HPCX_J7(P.b.z, Cn.a.z, Cn.b.y, Cn.b.w, dn.z, N.b.z);
+    o1.w = HPCX_J7(P.b.w, Cn.a.w, Cn.b.z, r1, dn.w, N.b.w);
+    // Boundary plane of the slab: the same registers also go straight into the neighbour's ghost
+    // plane over NVLink; after the barrier one thread counts the tile in and the last tile of
+    // the plane publishes the sweep number (CTA-uniform branches).
+    const int z = z0 - 1 + j;
+    float *peer0 = pr.ghost_lo && z == 0 ? pr.ghost_lo + inplane : nullptr;
+    float *peer1 = pr.ghost_hi && z == (int)g.n0 - 1 ? pr.ghost_hi + inplane : nullptr;
+    if (peer0 || peer1) {
+      const float v0[4] = {o0.x, o0.y, o0.z, o0.w}, v1[4] = {o1.x, o1.y, o1.z, o1.w};
+#pragma unroll
+      for (int q = 0; q < 2; ++q) {
+        float *pp = q ? peer1 : peer0;
+        if (!pp) continue;
+        if (full4) {
+          if (row0) *reinterpret_cast<float4 *>(pp) = o0;
+          if (row1) *reinterpret_cast<float4 *>(pp + g.pitch) = o1;
+        } else {
+#pragma unroll
+          for (int c = 0; c < 3; ++c)
+            if (gx + c < g.n2) {
+              if (row0) pp[c] = v0[c];
+              if (row1) pp[g.pitch + c] = v1[c];
+            }
+        }
+      }
+      __threadfence_system();
+    }
+    // every warp has read planes <= j out of shared memory once it passes this barrier
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      if (peer0 && (atomicAdd(pr.counters + 0, 1u) + 1) % tiles_xy == 0) st_release_sys(pr.sig_lo, pr.sig_val);
+      if (peer1 && (atomicAdd(pr.counters + 1, 1u) + 1) % tiles_xy == 0) st_release_sys(pr.sig_hi, pr.sig_val);
+      if (j + S - 1 < np) issue(j + S - 1);
+    }
+    if (full4) {
+      if (row0) st_cs(reinterpret_cast<float4 *>(orow), o0);
+      if (row1) st_cs(reinterpret_cast<float4 *>(orow + g.pitch), o1);
+    } else {
+      if (row0) {
+        if (gx < g.n2) orow[0] = o0.x;
+        if (gx + 1 < g.n2) orow[1] = o0.y;
+        if (gx + 2 < g.n2) orow[2] = o0.z;
+      }
+      if (row1) {
+        if (gx < g.n2) orow[g.pitch] = o1.x;
+        if (gx + 1 < g.n2) orow[g.pitch + 1] = o1.y;
+        if (gx + 2 < g.n2) orow[g.pitch + 2] = o1.z;
+      }
+    }
+    orow += plane_stride;
+  };
+#undef HPCX_J7
+
+  load_plane(0, t0);
+  load_plane(1, t1);
+  const int last = np - 2;
+  for (int j = 1; j <= last; j += 3) {  // three steps per trip: the planes rotate by renaming
+    step(j, t0, t1, t2);
+    if (j + 1 > last) break;
+    step(j + 1, t1, t2, t0);
+    if (j + 2 > last) break;
+    step(j + 2, t2, t0, t1);
+  }
+}
+
 // ------------------------------------------------------------------ host side
 hpcx_status check_same_shape(hpcx_grid a, hpcx_grid b) {
   hpcx_ctx ctx = a->ctx;
@@ -590,10 +756,25 @@ hpcx_status launch_jacobi_tma(hpcx_grid_s *g, void *src, void *dst, int zsplit, 
   using C = JacobiCfg<kJacobiStages>;
   hpcx_ctx ctx = g->ctx;
   const JacobiPeer pr = peer ? *peer : JacobiPeer{};
-  // The top segment marches downwards when its first plane feeds a neighbour (and under
-  // HPCX_JACOBI_DOWN=1, which lets single-GPU tests cover that path).
-  const bool down = pr.ghost_hi != nullptr || ctx->force_jacobi_down;
-  const JacobiSplit sp = jacobi_plan(ctx, g->n[2], g->n[1], zend - zbeg, zsplit, down);
+  static int old_kernel = -1;  // HPCX_JACOBI_PRODUCER=1: the producer-warp kernel everywhere (A/B timing)
+  if (old_kernel < 0) {
+    const char *e = getenv("HPCX_JACOBI_PRODUCER");
+    old_kernel = e && atoi(e) ? 1 : 0;
+  }
+  const bool ring = !old_kernel && !ctx->force_jacobi_down;
+  // Producer-warp kernel only: the top segment marches downwards when its first plane feeds a
+  // neighbour (and under HPCX_JACOBI_DOWN=1, which lets single-GPU tests cover that path).  The
+  // ring kernel needs no such order: its top segment is short and runs in the last wave, right
+  // before the neighbour's next sweep asks for the plane.
+  const bool down = !ring && (pr.ghost_hi != nullptr || ctx->force_jacobi_down);
+  // The ring kernel on grids that do not fit L2 runs fastest with MANY short z segments (about
+  // 8 planes: 512^3 648 Gcell/s with one wave of 444 CTAs, 808 with 64 segments = 18 waves,
+  // profiles/r22_jacobi_zsplit.txt): short-lived CTAs drift out of lock-step, so the DRAM sees a
+  // steady read/write mix, and a wave still covers whole planes, so the tile halos stay L2 hits.
+  int zs_pin = zsplit;
+  if (ring && zsplit <= 0 && 2 * g->ext[0] * g->ext[1] * g->pitch * 4 > ctx->l2_bytes + ctx->l2_bytes / 2)
+    zs_pin = (int)std::max<int64_t>(1, (zend - zbeg + 7) / 8);
+  const JacobiSplit sp = jacobi_plan(ctx, g->n[2], g->n[1], zend - zbeg, zs_pin, down);
   hpcx_status st = HPCX_OK;
   const CUtensorMap *hi = jacobi_map(g, src, sp.hmax + 2, &st);
   if (!hi) return st;
@@ -609,6 +790,17 @@ hpcx_status launch_jacobi_tma(hpcx_grid_s *g, void *src, void *dst, int zsplit, 
     configured = true;
   }
   const unsigned ncta = (unsigned)(sp.ntx * sp.nty * sp.zs);
+  static bool ring_configured = false;
+  if (!ring_configured) {
+    ring_configured = true;
+    HPCX_CUDA(ctx, cudaFuncSetAttribute(jacobi7_ring_kernel<kJacobiStages>,
+                                        cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
+  }
+  if (ring) {
+    jacobi7_ring_kernel<kJacobiStages><<<ncta, 256, C::kSmemBytes, s>>>(
+        *hi, *lo, (float *)dst, geom_of(g), sp, pr, (int)zbeg, (int)zend, 1.0f / 6.0f);
+    return after_launch(ctx, "jacobi7_ring_kernel");
+  }
   jacobi7_tma_kernel<kJacobiStages><<<ncta, C::kThreads, C::kSmemBytes, s>>>(
       *hi, *lo, (float *)dst, geom_of(g), sp, pr, (int)zbeg, (int)zend, 1.0f / 6.0f);
   return after_launch(ctx, "jacobi7_tma_kernel");
@@ -631,12 +823,13 @@ hpcx_status launch_jacobi_tma(hpcx_grid_s *g, void *src, void *dst, int zsplit, 
 //      x neighbours by shuffle, y neighbours and edge columns from the shared t+1 plane of step
 //      j-1) and stream it to HBM.
 // One named barrier per step orders the t+1 planes between the warps.
-struct JacobiTB {
+template <int S_>
+struct JacobiTBCfg {
   static constexpr int TX = 128, HX = 4, BX = TX + 2 * HX;  // 136 staged columns
   static constexpr int HO = 14;                               // output rows per tile (max)
   static constexpr int ER = HO + 2;                           // rows of the grown (t+1) tile
   static constexpr int BY = HO + 4;                           // staged rows of iterate t
-  static constexpr int S = 8;  // power of two: slot = j & 7, phase = (j >> 3) & 1
+  static constexpr int S = S_;  // ring slots: 8 -> 98.6 KB, 2 CTAs/SM; 5 -> 69.2 KB, 3 CTAs/SM
   static constexpr int kSlotBytes = (BX * BY * 4 + 127) / 128 * 128;
   static constexpr int kSlotFloats = kSlotBytes / 4;
   static constexpr int kAPlaneFloats = (ER + 2) * BX;  // one guard row above and below
@@ -649,7 +842,9 @@ struct JacobiTB {
 
 struct JacobiTBSplit {
   int ntx, nty, zs, hmax;
-  int zbeg, zend;  // planes written by this launch
+  int zbeg, zend;  // planes written by this launch, cut into zs segments
+  int zbeg2, zend2;  // optional second range, one more segment (bz == zs): the two boundary strips
+                     // of a slab go out in one launch
   int zlo, zhi;    // planes whose iterate t+1 is COMPUTED: [0, n0) on one GPU; a slab with a z
                    // neighbour grows by one plane on that side (the neighbour's boundary plane,
                    // recomputed here from the two exchanged ghost planes)
@@ -660,11 +855,11 @@ struct JacobiTBSplit {
 
 // EXP: timing experiments only (HPCX_TB_EXP, results are wrong when non-zero): 1 = no stage B,
 // 4 = no global stores, 8 = no edge columns.
-template <int EXP>
-__global__ void __launch_bounds__(JacobiTB::kThreads, 2)
+template <int EXP, int S_>
+__global__ void __launch_bounds__(256, S_ <= 5 ? 3 : 2)
 jacobi7_tb2_kernel(const __grid_constant__ CUtensorMap map_hi, const __grid_constant__ CUtensorMap map_lo,
                    float *__restrict__ out, GridGeom g, JacobiTBSplit sp, float sixth) {
-  using C = JacobiTB;
+  using C = JacobiTBCfg<S_>;
   extern __shared__ __align__(128) unsigned char smem[];
   float *ring = reinterpret_cast<float *>(smem);
   float *abuf = reinterpret_cast<float *>(smem + C::kAOff);
@@ -677,8 +872,8 @@ jacobi7_tb2_kernel(const __grid_constant__ CUtensorMap map_hi, const __grid_cons
   const int x0 = bx * C::TX;
   const int y0 = (int)((int64_t)by * g.n1 / sp.nty);
   const int h = (int)((int64_t)(by + 1) * g.n1 / sp.nty) - y0;
-  const int z0 = sp.zbeg + (int)((int64_t)bz * (sp.zend - sp.zbeg) / sp.zs);
-  const int z1 = sp.zbeg + (int)((int64_t)(bz + 1) * (sp.zend - sp.zbeg) / sp.zs);
+  const int z0 = bz < sp.zs ? sp.zbeg + (int)((int64_t)bz * (sp.zend - sp.zbeg) / sp.zs) : sp.zbeg2;
+  const int z1 = bz < sp.zs ? sp.zbeg + (int)((int64_t)(bz + 1) * (sp.zend - sp.zbeg) / sp.zs) : sp.zend2;
   if (h <= 0 || z1 <= z0) return;
   const int np = z1 - z0 + 4;  // planes z0-2 .. z1+1 of iterate t
 
@@ -690,9 +885,9 @@ jacobi7_tb2_kernel(const __grid_constant__ CUtensorMap map_hi, const __grid_cons
   const int c0 = (int)g.xoff + x0 - C::HX;
   const int c1 = y0 + (int)g.glo1 - 2;  // may be -1: rows outside the array are zero-filled
   auto issue = [&](int p) {            // plane p -> slot p & (S-1); thread 0 only
-    mbar_expect_tx(full + (p & (C::S - 1)), box_bytes);
-    tma_load_3d(ring + (p & (C::S - 1)) * C::kSlotFloats, map, c0, c1, z0 - 2 + p + (int)g.glo0,
-                full + (p & (C::S - 1)));
+    mbar_expect_tx(full + (p % C::S), box_bytes);
+    tma_load_3d(ring + (p % C::S) * C::kSlotFloats, map, c0, c1, z0 - 2 + p + (int)g.glo0,
+                full + (p % C::S));
   };
   if (threadIdx.x == 0) {
     for (int s = 0; s < C::S; ++s) mbar_init(full + s, 1);
@@ -741,8 +936,8 @@ jacobi7_tb2_kernel(const __grid_constant__ CUtensorMap map_hi, const __grid_cons
   float *orow = out + gidx(g, z0, ye0, gx);  // plane z0, this thread's first row
 
   auto load_plane = [&](int j, TP &t) {
-    mbar_wait(full + (j & (C::S - 1)), (j / C::S) & 1);
-    const float *pl = ring + (j & (C::S - 1)) * C::kSlotFloats;
+    mbar_wait(full + (j % C::S), (j / C::S) & 1);
+    const float *pl = ring + (j % C::S) * C::kSlotFloats;
     t.a = *reinterpret_cast<const float4 *>(pl + r0off);
     t.b = *reinterpret_cast<const float4 *>(pl + r1off);
     t.e = pl[eoff];
@@ -752,7 +947,7 @@ jacobi7_tb2_kernel(const __grid_constant__ CUtensorMap map_hi, const __grid_cons
   auto step = [&](int j, const TP &P, const TP &Cn, TP &N, const AP &aP, const AP &aC, AP &aN) {
     const int z = z0 - 2 + j;
     load_plane(j + 1, N);
-    const float *pc = ring + (j & (C::S - 1)) * C::kSlotFloats;
+    const float *pc = ring + (j % C::S) * C::kSlotFloats;
     const float4 up = *reinterpret_cast<const float4 *>(pc + r0off - C::BX);
     const float4 dn = *reinterpret_cast<const float4 *>(pc + r1off + C::BX);
     float l0 = __shfl_up_sync(0xffffffffu, Cn.a.w, 1);
@@ -877,21 +1072,39 @@ jacobi7_tb2_kernel(const __grid_constant__ CUtensorMap map_hi, const __grid_cons
 // Two sweeps src -> dst in one pass (HPCX_VARIANT_TEMPORAL).  Tiles of 128 x <= 14 cells, z
 // segments chosen so that the CTA count is about two per SM (the kernel's residency).
 hpcx_status launch_jacobi_tb2(hpcx_grid_s *g, void *src, void *dst, int zsplit, int64_t zbeg, int64_t zend,
-                              bool nb_lo, bool nb_hi, cudaStream_t s) {
-  using C = JacobiTB;
+                              bool nb_lo, bool nb_hi, cudaStream_t s, int64_t zbeg2 = 0, int64_t zend2 = 0) {
+  using C = JacobiTBCfg<8>;
+  const int per_sm = 2;  // 98.6 KB of shared memory per CTA (five slots and 3 CTAs/SM measured 2 % slower)
   hpcx_ctx ctx = g->ctx;
-  if (zend <= zbeg) return HPCX_OK;
+  if (zend <= zbeg) {
+    if (zend2 <= zbeg2) return HPCX_OK;
+    zbeg = zbeg2, zend = zend2, zbeg2 = zend2 = 0;
+  }
   JacobiTBSplit sp;
   sp.zbeg = (int)zbeg;
   sp.zend = (int)zend;
+  sp.zbeg2 = (int)zbeg2;
+  sp.zend2 = (int)zend2;
   sp.zlo = nb_lo ? -1 : 0;
   sp.zhi = (int)g->n[0] + (nb_hi ? 1 : 0);
   sp.ntx = (int)((g->n[2] + C::TX - 1) / C::TX);
   sp.nty = (int)((g->n[1] + C::HO - 1) / C::HO);
   sp.hmax = (int)((g->n[1] + sp.nty - 1) / sp.nty);
-  const int64_t tiles = (int64_t)sp.ntx * sp.nty;
-  int64_t zs = zsplit > 0 ? zsplit : std::max<int64_t>(1, (2 * (int64_t)ctx->sm_count + tiles / 2) / tiles);
-  zs = std::min<int64_t>(zs, zsplit > 0 ? zend - zbeg : std::max<int64_t>(1, (zend - zbeg) / 16));
+  const int64_t tiles = (int64_t)sp.ntx * sp.nty, nzr = zend - zbeg;
+  int64_t zs = std::min<int64_t>(std::max(zsplit, 1), nzr);
+  if (zsplit <= 0) {
+    // CTAs are long-lived (2 per SM) and the halo rows of a tile are L2 hits only while its
+    // neighbours run in the same wave, so whole waves matter: minimise
+    //   ceil(waves) x (planes per segment + ~40 planes of ramp and tail per CTA),
+    // an under-filled single wave paying for its idle slots (profiles/r22_jacobi_zsplit.txt).
+    const double slots = (double)per_sm * ctx->sm_count;
+    double best = 1e300;
+    for (int64_t c = 1; c <= std::max<int64_t>(1, nzr / 8); ++c) {
+      const double waves = (double)(tiles * c) / slots;
+      const double cost = std::ceil(waves) * (waves < 1.0 ? 1.0 / waves : 1.0) * ((double)nzr / (double)c + 40.0);
+      if (cost < best * (1.0 - 1e-9)) best = cost, zs = c;
+    }
+  }
   sp.zs = (int)std::max<int64_t>(zs, 1);
   hpcx_status st = HPCX_OK;
   const CUtensorMap *hi = jacobi_map(g, src, sp.hmax + 4, &st);
@@ -899,25 +1112,14 @@ hpcx_status launch_jacobi_tb2(hpcx_grid_s *g, void *src, void *dst, int zsplit, 
   const CUtensorMap *lo = jacobi_map(g, src, sp.hmax + 3, &st);
   if (!lo) return st;
   hi = jacobi_map(g, src, sp.hmax + 4, &st);  // may have moved if the cache reallocated
-  static int exp = -1;
-  if (exp < 0) {
-    const char *e = getenv("HPCX_TB_EXP");
-    exp = e ? atoi(e) : 0;
-#define HPCX_TB_ATTR(E) \
-  HPCX_CUDA(ctx, cudaFuncSetAttribute(jacobi7_tb2_kernel<E>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes))
-    HPCX_TB_ATTR(0); HPCX_TB_ATTR(1); HPCX_TB_ATTR(4); HPCX_TB_ATTR(8);
-#undef HPCX_TB_ATTR
+  static bool configured = false;
+  if (!configured) {
+    configured = true;
+    HPCX_CUDA(ctx, cudaFuncSetAttribute(jacobi7_tb2_kernel<0, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        JacobiTBCfg<8>::kSmemBytes));
   }
-  const unsigned ncta = (unsigned)(sp.ntx * sp.nty * sp.zs);
-#define HPCX_TB_GO(E) \
-  jacobi7_tb2_kernel<E><<<ncta, C::kThreads, C::kSmemBytes, s>>>(*hi, *lo, (float *)dst, geom_of(g), sp, 1.0f / 6.0f)
-  switch (exp) {
-    case 1: HPCX_TB_GO(1); break;
-    case 4: HPCX_TB_GO(4); break;
-    case 8: HPCX_TB_GO(8); break;
-    default: HPCX_TB_GO(0); break;
-  }
-#undef HPCX_TB_GO
+  const unsigned ncta = (unsigned)(sp.ntx * sp.nty * (sp.zs + (zend2 > zbeg2 ? 1 : 0)));
+  jacobi7_tb2_kernel<0, 8><<<ncta, 256, C::kSmemBytes, s>>>(*hi, *lo, (float *)dst, geom_of(g), sp, 1.0f / 6.0f);
   return after_launch(ctx, "jacobi7_tb2_kernel");
 }
 
@@ -946,13 +1148,14 @@ bool jacobi7_tb2_supported(hpcx_grid_s *g) {
 }
 
 // Two Jacobi sweeps src -> dst in one pass over planes [zbeg, zend) (shared with dist.cu).  nb_lo /
+// [zbeg2, zend2): optional second strip in the same launch.  nb_lo /
 // nb_hi: the slab has a z neighbour on that side, i.e. ghost planes -2, -1 / n0, n0+1 of `src`
 // hold the neighbour's iterate t and iterate t+1 of planes -1 / n0 is computed, not copied.
 hpcx_status jacobi7_tb2_launch(hpcx_grid_s *g, void *src, void *dst, int zsplit, int64_t zbeg, int64_t zend,
-                               bool nb_lo, bool nb_hi, cudaStream_t s) {
+                               bool nb_lo, bool nb_hi, cudaStream_t s, int64_t zbeg2, int64_t zend2) {
   if (!jacobi7_tb2_supported(g))
     return fail(g->ctx, HPCX_UNSUPPORTED, "the temporally blocked Jacobi needs fp32 and a tensor-map driver");
-  return launch_jacobi_tb2(g, src, dst, zsplit, zbeg, zend, nb_lo, nb_hi, s);
+  return launch_jacobi_tb2(g, src, dst, zsplit, zbeg, zend, nb_lo, nb_hi, s, zbeg2, zend2);
 }
 }  // namespace hpcx
 
