@@ -408,24 +408,26 @@ def stencil_extra(ctx, torch, stream, world, rank, barrier, max_over_ranks, hp, 
         ga.upload(f)
         gb.upload(f)
         del f
-        plan = hd.HaloPlan(ctx, ga, gb, hp.STENCIL_JACOBI7, hp.VARIANT_TEMPORAL, transport=0)
-        step = lambda: plan.sweep(T, stream)  # noqa: E731
-        with torch.cuda.stream(stream):
-            step()
-            n0 = ctx.launch_count()
-            dt, _, _ = time_steps(torch, stream, step, 2, barrier)
-            launches = ctx.launch_count() - n0
-        dt = max_over_ranks(dt)
-        cells = n ** 3 * world * T * 2
-        out["jacobi7_512cubed_fp32_temporal_nccl"] = {
-            "metric": "stencil_Gcell_updates_per_s", "value": cells / dt / 1e9, "sweeps": 2 * T,
-            "ms_per_sweep": dt / (2 * T) * 1e3, "gpu_launches": launches,
-            "transport": "NCCL send/recv, two planes per side and two-sweep pass",
-            "roofline": {"bound": "hbm", "achieved": cells * 8 / world / dt / 1e9, "peak": peak,
-                         "unit": "GB/s", "frac": cells * 8 / world / dt / 1e9 / peak,
-                         "algorithmic_bytes_per_cell": 8,
-                         "note": "two sweeps per pass over HBM: the kernel moves 4 B/cell/sweep, frac may exceed 1"}}
-        plan.destroy()
+        for transport, name in ((1, "temporal"), (0, "temporal_nccl")):
+            plan = hd.HaloPlan(ctx, ga, gb, hp.STENCIL_JACOBI7, hp.VARIANT_TEMPORAL, transport=transport)
+            step = lambda: plan.sweep(T, stream)  # noqa: E731
+            with torch.cuda.stream(stream):
+                step()
+                n0 = ctx.launch_count()
+                dt, _, _ = time_steps(torch, stream, step, 2, barrier)
+                launches = ctx.launch_count() - n0
+            dt = max_over_ranks(dt)
+            cells = n ** 3 * world * T * 2
+            out[f"jacobi7_512cubed_fp32_{name}"] = {
+                "metric": "stencil_Gcell_updates_per_s", "value": cells / dt / 1e9, "sweeps": 2 * T,
+                "ms_per_sweep": dt / (2 * T) * 1e3, "gpu_launches": launches,
+                "transport": ("peer stores + flags (fused), two planes per side and two-sweep pass" if transport
+                              else "NCCL send/recv, two planes per side and two-sweep pass"),
+                "roofline": {"bound": "hbm", "achieved": cells * 8 / world / dt / 1e9, "peak": peak,
+                             "unit": "GB/s", "frac": cells * 8 / world / dt / 1e9 / peak,
+                             "algorithmic_bytes_per_cell": 8,
+                             "note": "two sweeps per pass over HBM: the kernel moves 4 B/cell/sweep, frac may exceed 1"}}
+            plan.destroy()
         ga.destroy()
         gb.destroy()
     if world == 1:

@@ -230,6 +230,32 @@ __global__ void halo_wait_kernel(const uint32_t *flags, uint32_t *err, uint32_t 
   if (has_hi) wait_flag(flags + 1, want, err);
 }
 
+// Two-sweep passes: after the pass kernel, copy this slab's two boundary planes per side straight
+// into the neighbours' ghost planes (peer stores over NVLink; the planes are contiguous), then
+// the last CTA publishes the pass number in the neighbours' flag words and waits for theirs, so
+// that the next pass kernel may read its ghost planes as soon as this kernel has ended.
+__global__ void __launch_bounds__(256)
+halo_push_planes_kernel(const float4 *__restrict__ lo_src, float4 *__restrict__ lo_dst,
+                        const float4 *__restrict__ hi_src, float4 *__restrict__ hi_dst, int64_t n4,
+                        uint32_t *counter, uint32_t *sig_lo, uint32_t *sig_hi, uint32_t sig_val,
+                        const uint32_t *flags, uint32_t *err) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n4; i += stride) {
+    if (lo_dst) lo_dst[i] = __ldg(lo_src + i);
+    if (hi_dst) hi_dst[i] = __ldg(hi_src + i);
+  }
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0 && atomicAdd(counter, 1u) + 1 == gridDim.x) {
+    atomicExch(counter, 0u);
+    __threadfence_system();
+    if (sig_lo) st_release_sys(sig_lo, sig_val);
+    if (sig_hi) st_release_sys(sig_hi, sig_val);
+    if (sig_lo) wait_flag(flags + 0, sig_val, err);
+    if (sig_hi) wait_flag(flags + 1, sig_val, err);
+  }
+}
+
 }  // namespace
 
 extern "C" {
@@ -336,8 +362,8 @@ hpcx_status hpcx_stencil_dist_plan(hpcx_ctx ctx, hpcx_grid in, hpcx_grid out,
     // Two sweeps per pass: a slab trades TWO planes per side and pass, so every slab needs ghost
     // width >= 2 and at least two planes.  The ranks agree on the verdict (sum of per-rank
     // violations) so that nobody is left waiting in a receive.
-    if (transport != 0 || !jacobi7_tb2_supported(in))
-      return fail(ctx, HPCX_UNSUPPORTED, "the temporally blocked Jacobi needs fp32, a tensor-map driver and transport 0");
+    if (!jacobi7_tb2_supported(in))
+      return fail(ctx, HPCX_UNSUPPORTED, "the temporally blocked Jacobi needs fp32 and a tensor-map driver");
     if (ctx->nranks > 1) {
       float bad = (in->desc.lo < 2 || in->desc.hi < 2 || in->n[0] < 2) ? 1.f : 0.f, *d_bad = nullptr;
       HPCX_CUDA(ctx, cudaMalloc(&d_bad, sizeof(float)));
@@ -392,7 +418,12 @@ static hpcx_status dist_sweep_peer(hpcx_halo_plan p, int32_t steps, cudaStream_t
   if (p->in->dev != p->buf[cur] || p->out->dev != p->buf[cur ^ 1])
     return fail(ctx, HPCX_INVALID_ARG, "grid buffers changed since the plan was made");
   hpcx_status rc = HPCX_OK;
-  for (int t = 0; t < steps; ++t) {
+  // HPCX_VARIANT_TEMPORAL: steps/2 two-sweep passes (two planes per side copied into the
+  // neighbours by a push kernel behind each pass), then one single sweep when steps is odd.  `epoch` counts
+  // passes: flags carry the number of the pass whose planes have landed.
+  const bool temporal = p->st.variant == HPCX_VARIANT_TEMPORAL;
+  const int passes = temporal ? steps / 2 + (steps & 1) : steps;
+  for (int t = 0; t < passes; ++t) {
     const int dst = cur ^ 1;
     JacobiPeer pr;
     if (has_lo) {
@@ -405,13 +436,30 @@ static hpcx_status dist_sweep_peer(hpcx_halo_plan p, int32_t steps, cudaStream_t
     }
     pr.flags = p->flags;
     pr.counters = p->flags + 4;
-    pr.wait_val = t == 0 ? 0 : p->epoch + (uint32_t)t;  // sweep 0 reads NCCL-exchanged ghosts
+    pr.wait_val = t == 0 ? 0 : p->epoch + (uint32_t)t;  // pass 0 reads NCCL-exchanged ghosts
     pr.sig_val = p->epoch + (uint32_t)t + 1;
-    rc = jacobi7_launch(g, p->buf[cur], p->buf[dst], HPCX_VARIANT_TMA, p->st.zsplit, 0, g->n[0], cs, &pr);
+    if (temporal && t < steps / 2) {
+      // pass kernel ; push kernel (planes 0, 1 -> low neighbour's ghosts n, n+1; planes n0-2, n0-1
+      // -> high neighbour's ghosts -2, -1; then waits until the neighbours' planes have landed here)
+      rc = jacobi7_tb2_launch(g, p->buf[cur], p->buf[dst], p->st.zsplit, 0, g->n[0], has_lo, has_hi, cs);
+      if (rc != HPCX_OK) return rc;
+      const float *mine = static_cast<const float *>(p->buf[dst]);
+      halo_push_planes_kernel<<<2 * ctx->sm_count, 256, 0, cs>>>(
+          reinterpret_cast<const float4 *>(mine + g->glo[0] * plane),
+          reinterpret_cast<float4 *>(has_lo ? pr.ghost_lo : nullptr),
+          reinterpret_cast<const float4 *>(mine + (g->glo[0] + g->n[0] - 2) * plane),
+          reinterpret_cast<float4 *>(has_hi ? pr.ghost_hi - plane : nullptr), 2 * plane / 4, p->flags + 8,
+          pr.sig_lo, pr.sig_hi, pr.sig_val, p->flags, p->flags + 6);
+      rc = after_launch(ctx, "halo_push_planes_kernel");
+    } else {
+      rc = jacobi7_launch(g, p->buf[cur], p->buf[dst], HPCX_VARIANT_TMA, temporal ? 0 : p->st.zsplit, 0, g->n[0],
+                          cs, &pr);
+    }
     if (rc != HPCX_OK) return rc;
     cur = dst;
   }
-  p->epoch += (uint32_t)steps;
+  p->epoch += (uint32_t)passes;
+  steps = passes;  // parity of the buffer swap below
   halo_wait_kernel<<<1, 1, 0, cs>>>(p->flags, p->flags + 6, p->epoch, has_lo, has_hi);
   rc = after_launch(ctx, "halo_wait_kernel");
   if (rc != HPCX_OK) return rc;

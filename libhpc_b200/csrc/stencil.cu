@@ -462,7 +462,10 @@ jacobi7_ring_kernel(const __grid_constant__ CUtensorMap map_hi, const __grid_con
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int bx = blockIdx.x % sp.ntx;
   const int by = (blockIdx.x / sp.ntx) % sp.nty;
-  const int bz = blockIdx.x / (sp.ntx * sp.nty);
+  // With a neighbour above, the top segment runs second instead of last: both boundary planes
+  // reach the neighbours within the first wave, a whole sweep before they are needed.
+  const int seg = blockIdx.x / (sp.ntx * sp.nty);
+  const int bz = pr.ghost_hi && sp.zs > 2 ? (seg == 0 ? 0 : seg == 1 ? sp.zs - 1 : seg - 1) : seg;
   const int x0 = bx * C::TX;
   const int y0 = (int)((int64_t)by * g.n1 / sp.nty);
   const int h = (int)((int64_t)(by + 1) * g.n1 / sp.nty) - y0;
@@ -884,7 +887,7 @@ jacobi7_tb2_kernel(const __grid_constant__ CUtensorMap map_hi, const __grid_cons
   const uint32_t box_bytes = (uint32_t)(C::BX * (h + 4) * 4);
   const int c0 = (int)g.xoff + x0 - C::HX;
   const int c1 = y0 + (int)g.glo1 - 2;  // may be -1: rows outside the array are zero-filled
-  auto issue = [&](int p) {            // plane p -> slot p & (S-1); thread 0 only
+  auto issue = [&](int p) {            // plane p -> slot p % S; thread 0 only
     mbar_expect_tx(full + (p % C::S), box_bytes);
     tma_load_3d(ring + (p % C::S) * C::kSlotFloats, map, c0, c1, z0 - 2 + p + (int)g.glo0,
                 full + (p % C::S));
@@ -895,8 +898,9 @@ jacobi7_tb2_kernel(const __grid_constant__ CUtensorMap map_hi, const __grid_cons
     tma_prefetch_desc(map);
   }
   __syncthreads();
-  if (threadIdx.x == 0)
+  if (threadIdx.x == 0) {
     for (int p = 0; p < C::S && p < np; ++p) issue(p);
+  }
 
   // ---------------------------------------------------------------- consumers
   // Warp w owns rows e = 2w, 2w+1 of the grown tile (y = y0 - 1 + e), i.e. box rows 2w+1, 2w+2;
@@ -1050,8 +1054,10 @@ jacobi7_tb2_kernel(const __grid_constant__ CUtensorMap map_hi, const __grid_cons
       if (edge) an[aeoff] = aE;
     }
     __syncthreads();
-    // every warp is done with planes <= j: refill the slot of plane j - 1 with plane j + S - 1
-    if (threadIdx.x == 0 && j + C::S - 1 < np) issue(j + C::S - 1);
+    if (threadIdx.x == 0) {
+      // every warp is done with planes <= j: refill the slot of plane j - 1 with plane j + S - 1
+      if (j + C::S - 1 < np) issue(j + C::S - 1);
+    }
   };
 
   load_plane(0, t0);
@@ -1116,7 +1122,7 @@ hpcx_status launch_jacobi_tb2(hpcx_grid_s *g, void *src, void *dst, int zsplit, 
   if (!configured) {
     configured = true;
     HPCX_CUDA(ctx, cudaFuncSetAttribute(jacobi7_tb2_kernel<0, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                        JacobiTBCfg<8>::kSmemBytes));
+                                        C::kSmemBytes));
   }
   const unsigned ncta = (unsigned)(sp.ntx * sp.nty * (sp.zs + (zend2 > zbeg2 ? 1 : 0)));
   jacobi7_tb2_kernel<0, 8><<<ncta, 256, C::kSmemBytes, s>>>(*hi, *lo, (float *)dst, geom_of(g), sp, 1.0f / 6.0f);
@@ -1149,7 +1155,7 @@ bool jacobi7_tb2_supported(hpcx_grid_s *g) {
 
 // Two Jacobi sweeps src -> dst in one pass over planes [zbeg, zend) (shared with dist.cu).  nb_lo /
 // [zbeg2, zend2): optional second strip in the same launch.  nb_lo /
-// nb_hi: the slab has a z neighbour on that side, i.e. ghost planes -2, -1 / n0, n0+1 of `src`
+// nb_lo / nb_hi: the slab has a z neighbour on that side, i.e. ghost planes -2, -1 / n0, n0+1 of `src`
 // hold the neighbour's iterate t and iterate t+1 of planes -1 / n0 is computed, not copied.
 hpcx_status jacobi7_tb2_launch(hpcx_grid_s *g, void *src, void *dst, int zsplit, int64_t zbeg, int64_t zend,
                                bool nb_lo, bool nb_hi, cudaStream_t s, int64_t zbeg2, int64_t zend2) {

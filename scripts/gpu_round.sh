@@ -15,8 +15,8 @@ timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --c
   python bench.py --steps 3 --warmup 3 --no-cpu > $OUT/ncu_launch.log 2>&1; echo "ncu-launches rc=$?" | tee -a $OUT/rc.txt
 timeout 900 ncu --set full --clock-control none --import-source on --kernel-name-base demangled -k "regex:spmv_stream_kernel<double" --launch-skip 4 -c 1 \
   -o $OUT/spmv_stream_full -f python bench.py --steps 3 --warmup 3 --no-cpu --configs headline > $OUT/ncu_spmv.log 2>&1; echo "ncu-spmv rc=$?" | tee -a $OUT/rc.txt
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:jacobi7_tma_kernel --launch-skip 10 -c 1 \
-  -o $OUT/jacobi7_tma_full -f python bench.py --steps 3 --warmup 3 --no-cpu --configs headline > $OUT/ncu_jacobi.log 2>&1; echo "ncu-jacobi rc=$?" | tee -a $OUT/rc.txt
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:jacobi7_ring_kernel --launch-skip 10 -c 1 \
+  -o $OUT/jacobi7_ring_full -f python bench.py --steps 3 --warmup 3 --no-cpu --configs headline > $OUT/ncu_jacobi.log 2>&1; echo "ncu-jacobi rc=$?" | tee -a $OUT/rc.txt
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:jacobi7_tb2_kernel --launch-skip 10 -c 1 \
   -o $OUT/jacobi7_tb2_full -f python bench.py --steps 3 --warmup 3 --no-cpu --configs headline > $OUT/ncu_tb2.log 2>&1; echo "ncu-tb2 rc=$?" | tee -a $OUT/rc.txt
 fi

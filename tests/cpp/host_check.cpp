@@ -182,6 +182,17 @@ static int run_gpu() {
                      std::memcmp(u.data(), w1.data(), u.size() * sizeof(float)) == 0;
     std::printf("jacobi7 bit_exact %d\n", same);
     bad += !same;
+    // two sweeps per pass over HBM (HPCX_VARIANT_TEMPORAL): the newest iterate is the same, bit for bit
+    hpc::HPCHighDimensionFlatArray<3, float, 1> u2(nz, ny, nx), v2(nz, ny, nx);
+    std::memcpy(u2.data(), w1.data(), u2.size() * sizeof(float));  // iterate 1
+    std::memcpy(v2.data(), w1.data(), v2.size() * sizeof(float));
+    sweep(w0, w1);
+    sweep(w1, w0);
+    sweep(w0, w1);  // iterate 5 in w1; u2 holds iterate 1: four more sweeps
+    hpc::stencil_sweep(ctx, u2, v2, hpc::Jacobi7{4, HPCX_VARIANT_TEMPORAL});
+    const int same_tb = std::memcmp(v2.data(), w1.data(), v2.size() * sizeof(float)) == 0;
+    std::printf("jacobi7_temporal bit_exact %d\n", same_tb);
+    bad += !same_tb;
   }
   {  // SpMV, 5-point Laplacian (rows of <= 5 entries: the device order is the CPU order)
     auto A = sparse::CsrMatrix<double>::laplace2d(200, 300);

@@ -79,8 +79,12 @@ def main():
         gb.destroy()
 
     # ---- stencil, two sweeps per pass over slabs (transport 0, ghost width 2, two planes per side)
-    for (nz, ny, nx), steps, gw in (((8 * world, 20, 140), 6, 2), ((2 * world + 1, 30, 260), 5, 2),
-                                    ((5 * world, 15, 128), 4, 3), ((3 * world, 14, 40), 1, 2)):
+    # transport 0: two planes per side over NCCL; 1: the kernel stores them into the neighbours
+    for (nz, ny, nx), steps, gw, transport in (
+            ((8 * world, 20, 140), 6, 2, 0), ((2 * world + 1, 30, 260), 5, 2, 0),
+            ((5 * world, 15, 128), 4, 3, 0), ((3 * world, 14, 40), 1, 2, 0),
+            ((8 * world, 20, 140), 6, 2, 1), ((2 * world + 1, 30, 260), 5, 2, 1),
+            ((5 * world, 15, 128), 4, 3, 1), ((2 * world, 33, 129), 7, 2, 1), ((40 * world, 64, 256), 8, 2, 1)):
         ext = (nz + 2 * gw, ny + 2 * gw, nx + 2 * gw)
         full = oracle.fill(ext[0] * ext[1] * ext[2], 11, np.float32)
         b = hp.partition_slabs(nz, world)
@@ -91,7 +95,7 @@ def main():
         gb = hp.DeviceGrid(ctx, (z1 - z0, ny, nx), np.float32, gw)
         ga.upload(slab)
         gb.upload(slab)
-        plan = hd.HaloPlan(ctx, ga, gb, hp.STENCIL_JACOBI7, hp.VARIANT_TEMPORAL, transport=0)
+        plan = hd.HaloPlan(ctx, ga, gb, hp.STENCIL_JACOBI7, hp.VARIANT_TEMPORAL, transport=transport)
         done = 0
         for k in (steps, 2, 3):  # in -> out semantics: each call sweeps `in` k times into `out`
             plan.sweep(k)
@@ -99,7 +103,7 @@ def main():
             want = oracle.jacobi7(full, nz, ny, nx, gw, gw, total).reshape(ext)
             out = gb.download().reshape(z1 - z0 + 2 * gw, ny + 2 * gw, nx + 2 * gw)
             assert bits_equal(np.ascontiguousarray(out[gw:-gw, gw:-gw, gw:-gw]),
-                              np.ascontiguousarray(want[z0 + gw:z1 + gw, gw:-gw, gw:-gw])), (rank, nz, "temporal", k)
+                              np.ascontiguousarray(want[z0 + gw:z1 + gw, gw:-gw, gw:-gw])), (rank, nz, "temporal", k, transport)
             done = total - (1 if k & 1 else 2)  # `in` holds the source of the call's last pass
         plan.destroy()
         ga.destroy()

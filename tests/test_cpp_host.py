@@ -111,6 +111,7 @@ def test_cpp_entry_points_on_gpu(binary):
     assert rc == 0 and "CPP GPU OK" in out, out + err
     assert "box axis 0 bit_exact 1" in out and "box axis 1 bit_exact 1" in out
     assert "jacobi7 bit_exact 1" in out
+    assert "jacobi7_temporal bit_exact 1" in out
     assert "box_radius system_error" in out and "spmv_short_x out_of_range" in out
     assert "conv2d bit_exact 1" in out and "transpose bit_exact 1" in out
     assert "from_coo product bit_exact 1" in out and "converged 1" in out
