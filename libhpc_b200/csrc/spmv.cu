@@ -469,6 +469,8 @@ void free_csr(hpcx_csr A) {
   cudaFree(A->d_sell_val);
   cudaFree(A->d_x);
   cudaFree(A->d_y);
+  cudaFree(A->d_pipe_cmax);
+  for (cudaEvent_t e : A->pipe_ev) cudaEventDestroy(e);
   cudaFree(A->d_send_idx);
   cudaFree(A->d_sendbuf);
   cudaFree(A->d_xfull);
@@ -514,6 +516,103 @@ void spmv_build_rowblocks(const int64_t *rp, int64_t nrows, int tile, const uint
   build_rowblocks(rp, nrows, tile, kind, want, out, long_row, long_off);
 }
 }  // namespace hpcx
+
+namespace {
+
+// Largest column index referenced by each chunk of nonzeros [pbeg[c], pbeg[c+1]).
+__global__ void __launch_bounds__(256)
+chunk_colmax_kernel(const int32_t *__restrict__ col, const int64_t *__restrict__ pbeg, int nchunks,
+                    int32_t *__restrict__ cmax) {
+  const int c = blockIdx.y;
+  if (c >= nchunks) return;
+  int32_t m = -1;
+  for (int64_t i = pbeg[c] + blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < pbeg[c + 1];
+       i += (int64_t)gridDim.x * blockDim.x)
+    m = max(m, col[i]);
+  for (int o = 16; o; o >>= 1) m = max(m, __shfl_xor_sync(0xffffffffu, m, o));
+  if ((threadIdx.x & 31) == 0 && m >= 0) atomicMax(cmax + c, m);
+}
+
+constexpr int kPipeChunks = 32;
+
+// One-time analysis for host-x / host-y products: cut the row blocks into kPipeChunks chunks and
+// find the largest column each chunk reads.  A chunk can run as soon as x[0 .. cmax] has landed, so
+// banded operators (the C2 / C4 stencil matrices) stream: H2D of x, the product and D2H of y overlap
+// and the call takes about one PCIe transfer instead of two.  Matrices whose every chunk reads up
+// to the last column degrade gracefully to copy-then-compute with the D2H still chunked.
+hpcx_status pipe_analyse(hpcx_csr A) {
+  hpcx_ctx ctx = A->ctx;
+  A->pipe_state = -1;
+  const int64_t nb = (int64_t)A->h_blocks.size();
+  if (A->kernel != HPCX_SPMV_STREAM || A->nlong > 0 || nb < 2 * kPipeChunks || A->ncols < kPipeChunks)
+    return HPCX_OK;
+  const int K = kPipeChunks;
+  A->pipe_first.resize(K + 1);
+  std::vector<int64_t> pbeg(K + 1);
+  for (int c = 0; c <= K; ++c) {
+    A->pipe_first[c] = nb * c / K;
+    pbeg[c] = c < K ? A->h_blocks[A->pipe_first[c]].p0 : A->nnz;
+  }
+  int64_t *d_pbeg = nullptr;
+  HPCX_CUDA(ctx, cudaMalloc((void **)&d_pbeg, (K + 1) * sizeof(int64_t)));
+  cudaError_t e = cudaMalloc((void **)&A->d_pipe_cmax, K * sizeof(int32_t));
+  if (e == cudaSuccess) e = cudaMemset(A->d_pipe_cmax, 0xff, K * sizeof(int32_t));
+  if (e == cudaSuccess) e = cudaMemcpy(d_pbeg, pbeg.data(), (K + 1) * sizeof(int64_t), cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) {
+    chunk_colmax_kernel<<<dim3(64, K), 256>>>(A->d_col, d_pbeg, K, A->d_pipe_cmax);
+    A->pipe_cmax.resize(K);
+    e = cudaMemcpy(A->pipe_cmax.data(), A->d_pipe_cmax, K * sizeof(int32_t), cudaMemcpyDeviceToHost);
+  }
+  cudaFree(d_pbeg);
+  if (e != cudaSuccess) return fail(ctx, HPCX_CUDA_ERROR, std::string("pipe_analyse: ") + cudaGetErrorString(e));
+  A->pipe_ev.resize(2 * K + 2);
+  for (auto &ev : A->pipe_ev) HPCX_CUDA(ctx, cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+  A->pipe_state = 1;
+  return HPCX_OK;
+}
+
+// y(host) = A x(host): x pieces on the copy-in stream, row chunks on s as their columns land, y
+// chunks on the copy-out stream.  The caller synchronises s afterwards.
+hpcx_status spmv_host_pipelined(hpcx_csr A, const void *x, void *y, cudaStream_t s) {
+  hpcx_ctx ctx = A->ctx;
+  const int K = kPipeChunks;
+  const size_t es = (size_t)A->es;
+  cudaEvent_t *ex = A->pipe_ev.data(), *ey = ex + K, entry = ex[2 * K], done = ex[2 * K + 1];
+  auto piece = [&](int j) { return (int64_t)A->ncols * j / K; };  // first column of x piece j
+  HPCX_CUDA(ctx, cudaEventRecord(entry, s));
+  HPCX_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_in, entry, 0));
+  HPCX_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_out, entry, 0));
+  for (int j = 0; j < K; ++j) {
+    const int64_t a = piece(j), b = piece(j + 1);
+    HPCX_CUDA(ctx, cudaMemcpyAsync((char *)A->d_x + a * es, (const char *)x + a * es, (size_t)(b - a) * es,
+                                   cudaMemcpyHostToDevice, ctx->copy_in));
+    HPCX_CUDA(ctx, cudaEventRecord(ex[j], ctx->copy_in));
+  }
+  int waited = -1;
+  for (int c = 0; c < K; ++c) {
+    int need = waited < 0 ? 0 : waited;
+    while (need + 1 < K && piece(need + 1) <= A->pipe_cmax[c]) ++need;
+    if (need > waited) {
+      HPCX_CUDA(ctx, cudaStreamWaitEvent(s, ex[need], 0));
+      waited = need;
+    }
+    const int64_t b0 = A->pipe_first[c], b1 = A->pipe_first[c + 1];
+    hpcx_status st = hpcx::spmv_launch_blocks(A, A->d_blocks + b0, b1 - b0, A->d_x, A->d_y, s, nullptr);
+    if (st != HPCX_OK) return st;
+    HPCX_CUDA(ctx, cudaEventRecord(ey[c], s));
+    HPCX_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_out, ey[c], 0));
+    const int64_t r0 = A->h_blocks[b0].row0;
+    const int64_t r1 = b1 < (int64_t)A->h_blocks.size() ? A->h_blocks[b1].row0 : A->nrows;
+    HPCX_CUDA(ctx, cudaMemcpyAsync((char *)y + r0 * es, (const char *)A->d_y + r0 * es, (size_t)(r1 - r0) * es,
+                                   cudaMemcpyDeviceToHost, ctx->copy_out));
+  }
+  HPCX_CUDA(ctx, cudaEventRecord(done, ctx->copy_out));
+  HPCX_CUDA(ctx, cudaStreamWaitEvent(s, done, 0));
+  if (waited < K - 1) HPCX_CUDA(ctx, cudaStreamWaitEvent(s, ex[K - 1], 0));  // x fully landed before s goes on
+  return HPCX_OK;
+}
+
+}  // namespace
 
 extern "C" {
 
@@ -678,6 +777,20 @@ hpcx_status hpcx_spmv(hpcx_csr A, const void *x, int32_t x_mem, void *y, int32_t
   cudaStream_t s = stream ? (cudaStream_t)stream : ctx->compute;
   const void *dx = x;
   void *dy = y;
+  if (x_mem == HPCX_MEM_HOST && y_mem == HPCX_MEM_HOST && !A->dot_part) {
+    if (A->pipe_state == 0) {
+      hpcx_status st = pipe_analyse(A);
+      if (st != HPCX_OK) return st;
+    }
+    if (A->pipe_state == 1) {
+      if (!A->d_x) HPCX_CUDA(ctx, cudaMalloc(&A->d_x, std::max<size_t>((size_t)A->ncols * A->es, 1)));
+      if (!A->d_y) HPCX_CUDA(ctx, cudaMalloc(&A->d_y, std::max<size_t>((size_t)A->nrows * A->es, 1)));
+      hpcx_status st = spmv_host_pipelined(A, x, y, s);
+      if (st != HPCX_OK) return st;
+      HPCX_CUDA(ctx, cudaStreamSynchronize(s));
+      return HPCX_OK;
+    }
+  }
   if (x_mem == HPCX_MEM_HOST) {
     if (!A->d_x) HPCX_CUDA(ctx, cudaMalloc(&A->d_x, std::max<size_t>((size_t)A->ncols * A->es, 1)));
     HPCX_CUDA(ctx, cudaMemcpyAsync(A->d_x, x, (size_t)A->ncols * A->es, cudaMemcpyHostToDevice, s));

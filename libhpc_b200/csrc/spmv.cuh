@@ -47,6 +47,12 @@ struct hpcx_csr_s {
   void *d_sell_val = nullptr;
   // staging for host operands
   void *d_x = nullptr, *d_y = nullptr;
+  // host-x / host-y products: row chunks pipelined against the PCIe copies (spmv.cu: spmv_host_pipelined)
+  int pipe_state = 0;                 // 0 = not analysed yet, 1 = usable, -1 = not usable
+  std::vector<int64_t> pipe_first;    // first row block of each chunk (+ end)
+  std::vector<int32_t> pipe_cmax;     // largest column index referenced by each chunk
+  std::vector<cudaEvent_t> pipe_ev;   // [0, K) x pieces landed, [K, 2K) chunk computed, 2K entry, 2K+1 done
+  int32_t *d_pipe_cmax = nullptr;
   // when set (by the CG solver, cg.cu) the STREAM launches also emit per-block <x, y> partials
   void *dot_part = nullptr;
   // distributed (set by hpcx_csr_set_halo)

@@ -153,6 +153,42 @@ def test_device_operands_and_repeatability(ctx):
         D.destroy()
 
 
+@pytest.mark.parametrize("name", ["laplace", "op27_f32", "scattered"])
+def test_host_operands_pipelined_against_pcie(ctx, name):
+    """hpcx_spmv with HOST x and y cuts the rows into chunks that run as their columns land
+    (csrc/spmv.cu: spmv_host_pipelined); the result is the device-operand result bit for bit, for a
+    banded operator (streams), and for scattered columns (every chunk waits for all of x)."""
+    torch = pytest.importorskip("torch")
+    if name == "laplace":
+        rp, col, val = synth.laplace2d(640, 512)
+    elif name == "op27_f32":
+        rp, col, val = synth.op27(40, dtype=np.float32)
+    else:
+        n = 60000
+        rng = np.random.default_rng(5)
+        rp, col, val = random_csr(n, n, rng.integers(0, 9, size=n), 9, np.float64)
+    n = len(rp) - 1
+    D = hp.DeviceCsr(ctx, hp.CsrMatrix(rp, col, val))
+    try:
+        assert D.rowblocks().shape[0] >= 64  # enough row blocks for the chunked path
+        for seed in (1, 2, 3):  # the staging buffers are reused: a new x must give the new y
+            x = synth.field(seed, n, val.dtype)
+            xd = torch.from_numpy(x).cuda()
+            yd = torch.full((n,), float("nan"), dtype=xd.dtype, device="cuda")
+            torch.cuda.synchronize()
+            D.spmv(xd, yd)
+            xp = torch.from_numpy(x).pin_memory()
+            yp = torch.full((n,), float("nan"), dtype=xp.dtype).pin_memory()
+            D.spmv(xp.numpy(), yp.numpy())
+            assert bits_equal(yp.numpy(), yd.cpu().numpy())
+            y = np.full(n, np.nan, dtype=val.dtype)  # pageable memory: same answer, no overlap
+            D.spmv(x, y)
+            assert bits_equal(y, yd.cpu().numpy())
+            assert_spmv_close(y, oracle.spmv(rp, col, val, x), oracle.spmv_abs(rp, col, val, x), TOL[val.dtype])
+    finally:
+        D.destroy()
+
+
 def test_reference_facing_free_function(ctx):
     rp, col, val = synth.laplace2d(64, 64)
     A = hp.CsrMatrix(rp, col, val)
