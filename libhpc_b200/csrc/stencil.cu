@@ -1091,6 +1091,7 @@ hpcx_status launch_jacobi_tb2(hpcx_grid_s *g, void *src, void *dst, int zsplit, 
   sp.zend = (int)zend;
   sp.zbeg2 = (int)zbeg2;
   sp.zend2 = (int)zend2;
+
   sp.zlo = nb_lo ? -1 : 0;
   sp.zhi = (int)g->n[0] + (nb_hi ? 1 : 0);
   sp.ntx = (int)((g->n[2] + C::TX - 1) / C::TX);

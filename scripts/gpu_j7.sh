@@ -2,5 +2,6 @@
 TAG=${1:-j7}
 OUT=gpurun_out/$TAG
 mkdir -p $OUT
-TB=1 ZS=0 timeout 300 python scripts/prof_j7.py 2>&1 | tee -a $OUT/tb.txt
-HPCX_TB_FORCE_PEER=1 TB=1 ZS=0 timeout 300 python scripts/prof_j7.py 2>&1 | sed "s/^/forcepeer /" | tee -a $OUT/tb.txt
+for st in 0 200 500 1000 2000 4000; do
+HPCX_TB_STAGGER=$st TB=1 ZS=0 timeout 300 python scripts/prof_j7.py 2>&1 | sed "s/^/stagger$st /" | tee -a $OUT/tb.txt
+done
