@@ -215,7 +215,10 @@ HPCX_API hpcx_status hpcx_csr_create(hpcx_ctx ctx, const hpcx_csr_desc *d,
                                      const hpcx_csr_opts *opts, hpcx_csr *out);
 HPCX_API hpcx_status hpcx_csr_destroy(hpcx_csr A);
 /* y = A*x.  x: ncols entries, y: nrows entries of A's dtype; each may be host, device or
- * managed memory (HPCX_MEM_*).  Host operands are staged through the copy pipeline. */
+ * managed memory (HPCX_MEM_*).  Host operands are staged through the copy pipeline; with BOTH
+ * on the host the rows are cut into chunks that run as soon as the x entries they read have
+ * landed, so that for banded operators H2D of x, the product and D2H of y overlap (pinned
+ * buffers, hpcx_host_alloc, are what makes the copies asynchronous). */
 HPCX_API hpcx_status hpcx_spmv(hpcx_csr A, const void *x, int32_t x_mem, void *y,
                                int32_t y_mem, void *stream);
 /* Round trip of the device-resident CSR arrays (bit-exact structure check). Any pointer
@@ -337,10 +340,11 @@ HPCX_API hpcx_status hpcx_comm_ipc_close(hpcx_ctx ctx, void *peer_ptr);
  *      neighbour's ghost plane over NVLink (CUDA IPC peer windows) and publish a sweep-number
  *      flag that the neighbour's next sweep acquires before reading the ghost (fp32 TMA sweep
  *      only; plan creation is collective over the communicator).
- * HPCX_VARIANT_TEMPORAL (transport 0 only; plan creation is collective): two sweeps per pass,
+ * HPCX_VARIANT_TEMPORAL (either transport; plan creation is collective): two sweeps per pass,
  * TWO ghost planes traded per side and pass — every slab needs lo,hi >= 2 and >= 2 planes
  * (HPCX_INVALID_ARG on every rank otherwise).  The neighbour's boundary plane is advanced
- * redundantly on this rank; results stay bit-identical to single sweeps. */
+ * redundantly on this rank; results stay bit-identical to single sweeps.  Transport 1 pushes the
+ * planes with a small kernel behind each pass (peer stores + flags, no NCCL on the data path). */
 typedef struct hpcx_halo_plan_s *hpcx_halo_plan;
 HPCX_API hpcx_status hpcx_stencil_dist_plan(hpcx_ctx ctx, hpcx_grid in, hpcx_grid out,
                                             const hpcx_stencil_desc *st, int32_t transport,
