@@ -17,6 +17,7 @@
 #include <vector>
 
 #include <hpcx/CsrMatrix.hpp>
+#include <hpcx/Distributed.hpp>
 #include <hpcx/HPCHighDimensionFlatArray.hpp>
 #include <hpcx/Stencil.hpp>
 
@@ -311,6 +312,42 @@ static int run_gpu() {
     for (auto &c : g.cells)  // x0 carries each cell's value at its row
       ok = ok && x0[(std::get<0>(c) + 4) * ny + (std::get<1>(c) - 10)] == std::get<2>(c);
     std::printf("grid_bridge ok %d\n", ok);
+    bad += !ok;
+  }
+  {  // the multi-GPU face with a job of one process: same answers as the single-GPU calls
+    hpcx::Communicator comm(ctx);
+    auto A = sparse::CsrMatrix<double>::laplace2d(64, 96);
+    const auto bounds = sparse::partition_rows(A, comm.size());
+    sparse::DistributedCsr<double> D(ctx, comm, A, bounds);
+    std::vector<double> x(A.ncols()), y(A.nrows(), -1.0), want;
+    for (auto &v : x) v = frand(seed);
+    sparse::spmv(ctx, A, x, want);
+    void *dx = nullptr, *dy = nullptr;
+    hpcx_device_alloc(ctx.handle(), x.size() * 8, &dx);
+    hpcx_device_alloc(ctx.handle(), y.size() * 8, &dy);
+    hpcx_memcpy(ctx.handle(), dx, x.data(), x.size() * 8);
+    D.multiply(static_cast<const double *>(dx), static_cast<double *>(dy));
+    hpcx_memcpy(ctx.handle(), y.data(), dy, y.size() * 8);
+    hpcx_device_free(ctx.handle(), dx);
+    hpcx_device_free(ctx.handle(), dy);
+    int ok = bounds.front() == 0 && bounds.back() == (std::int64_t)A.nrows() && D.owned() == (std::int64_t)A.nrows() &&
+             D.halo_columns().empty() && std::memcmp(y.data(), want.data(), y.size() * 8) == 0;
+
+    const int nz = 12, ny = 10, nx = 70;
+    const auto slabs = hpc::partition_slabs(nz, comm.size());
+    hpc::HPCHighDimensionFlatArray<3, float, 2> u(nz, ny, nx), v(nz, ny, nx), w(nz, ny, nx);
+    for (std::size_t i = 0; i < u.size(); ++i) u.data()[i] = v.data()[i] = w.data()[i] = frand(seed);
+    hpc::stencil_sweep(ctx, w, v, hpc::Jacobi7{5});  // reference answer: five single sweeps (w -> v)
+    hpc::HPCHighDimensionFlatArray<3, float, 2> r(nz, ny, nx);
+    std::memcpy(r.data(), u.data(), u.size() * sizeof(float));
+    {
+      hpc::DeviceGrid<3, float, 2> du(ctx, u), dr(ctx, r);
+      hpc::HaloPlan<float, 2, 2> plan(du, dr, hpc::Jacobi7{1, HPCX_VARIANT_TEMPORAL});
+      plan.sweep(5);
+      dr.download(r);
+    }
+    ok = ok && slabs.back() == nz && std::memcmp(r.data(), v.data(), r.size() * sizeof(float)) == 0;
+    std::printf("distributed_face ok %d\n", ok);
     bad += !ok;
   }
   std::printf("launches %lld\n", (long long)ctx.launchCount());

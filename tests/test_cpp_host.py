@@ -116,3 +116,4 @@ def test_cpp_entry_points_on_gpu(binary):
     assert "conv2d bit_exact 1" in out and "transpose bit_exact 1" in out
     assert "from_coo product bit_exact 1" in out and "converged 1" in out
     assert "grid_bridge ok 1" in out
+    assert "distributed_face ok 1" in out
