@@ -46,7 +46,9 @@ def test_box_sweeps_match_reference_digest(ctx, which):
                                                   ((64, 250), 3, 5, 1), ((257, 31), 8, 9, 0),
                                                   ((40, 256), 8, 8, 0), ((100, 64), 4, 4, 2),
                                                   ((31, 36), 8, 9, 1), ((67, 1028), 8, 8, 0),
-                                                  ((32, 12), 4, 6, 0)])
+                                                  ((32, 12), 4, 6, 0),
+                                                  # whole warps along the row: the shuffle-window BOX_X kernel
+                                                  ((19, 2048), 8, 8, 0), ((7, 1024), 4, 4, 1), ((5, 3072), 8, 10, 0)])
 def test_box_sweeps_ragged_shapes(ctx, dtype, shape, radius, alo, blo):
     ny, nx = shape
     a = oracle.fill((ny + 2 * alo) * (nx + 2 * alo), 13, dtype)
