@@ -430,6 +430,29 @@ def stencil_extra(ctx, torch, stream, world, rank, barrier, max_over_ranks, hp, 
             plan.destroy()
         ga.destroy()
         gb.destroy()
+        # strong scaling: ONE 512^3 domain cut into world z-slabs of 512/world planes
+        nzl = n // world
+        f = synth.field(7, (nzl + 4) * (n + 4) ** 2, np.float32, first=rank * nzl * (n + 4) ** 2)
+        ga = hp.DeviceGrid(ctx, (nzl, n, n), np.float32, 2)
+        gb = hp.DeviceGrid(ctx, (nzl, n, n), np.float32, 2)
+        ga.upload(f)
+        gb.upload(f)
+        del f
+        for variant, name in ((hp.VARIANT_TMA, "tma"), (hp.VARIANT_TEMPORAL, "temporal")):
+            plan = hd.HaloPlan(ctx, ga, gb, hp.STENCIL_JACOBI7, variant, transport=1)
+            step = lambda: plan.sweep(T, stream)  # noqa: E731
+            with torch.cuda.stream(stream):
+                step()
+                dt, _, _ = time_steps(torch, stream, step, 2, barrier)
+            dt = max_over_ranks(dt)
+            cells = nzl * n * n * world * T * 2
+            out[f"jacobi7_512cubed_total_fp32_{name}_strong"] = {
+                "metric": "stencil_Gcell_updates_per_s", "value": cells / dt / 1e9, "scaling": "strong",
+                "planes_per_gpu": nzl, "ms_per_sweep": dt / (2 * T) * 1e3,
+                "transport": "peer stores + flags"}
+            plan.destroy()
+        ga.destroy()
+        gb.destroy()
     if world == 1:
         m = 8192
         a = hp.DeviceGrid(ctx, (m, m), np.float32, 8)
