@@ -403,12 +403,13 @@ hpcx_status hpcx_stencil_dist_plan(hpcx_ctx ctx, hpcx_grid in, hpcx_grid out,
   return HPCX_OK;
 }
 
-// Transport 1: ONE kernel per sweep.  Its boundary CTAs run first (the top z segment marches
-// downwards), write their plane into this rank's dst AND into the neighbour's ghost plane with
-// peer stores over NVLink, and release a sweep-number flag in the neighbour; the next sweep's
-// producer warps acquire that flag before their first TMA load of a ghost plane.  No NCCL call,
+// Transport 1: ONE kernel per sweep.  Its boundary CTAs run in the first wave (the short top z
+// segment is scheduled second), write their plane into this rank's dst AND into the neighbour's
+// ghost plane with peer stores over NVLink, and release a sweep-number flag in the neighbour; the
+// next sweep's CTAs acquire that flag before their first TMA load of a ghost plane.  No NCCL call,
 // no second stream and no pack kernel on the data path; the exchange overlaps the interior
-// planes of the same kernel.
+// planes of the same kernel.  Two-sweep passes (HPCX_VARIANT_TEMPORAL) run the plain pass kernel
+// and push their two boundary planes per side with halo_push_planes_kernel right behind it.
 static hpcx_status dist_sweep_peer(hpcx_halo_plan p, int32_t steps, cudaStream_t cs, bool sync) {
   hpcx_ctx ctx = p->ctx;
   hpcx_grid g = p->in;

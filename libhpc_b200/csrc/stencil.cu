@@ -9,13 +9,17 @@
 //                  operation rounded separately (the library is built with --fmad=false).
 //
 // Kernels:
-//   *_direct   one thread per cell (quad), neighbours through L1 — any dtype / radius / shape.
-//   jacobi7_tma  warp-specialised: a producer warp streams (TX+8)x(TY+2) plane boxes through
-//                a shared-memory ring with 3-D TMA (cp.async.bulk.tensor, SASS UTMALDG) and
-//                mbarriers; 8 consumer warps march along z with the z-1 / z centre values in
-//                registers, x neighbours by warp shuffle, y halo rows from shared memory.
-//                Every input cell is read from HBM once per sweep (tile halos are L2 hits).
-//   boxx_tma / boxy_tma  same ring for the 17-point reference sweeps (radius 8, fp32).
+//   *_direct      one thread per cell (quad), neighbours through L1 — any dtype / radius / shape.
+//   box_x_vec / box_y_reg  register-tiled 17-point reference sweeps (radius 4 or 8).
+//   jacobi7_ring  the default fp32 sweep: (TX+8)x(TY+2) plane boxes arrive in a shared-memory
+//                 ring by 3-D TMA (cp.async.bulk.tensor, SASS UTMALDG) on mbarriers; 8 warps
+//                 march along z with the z-1 / z centre values in registers, x neighbours by
+//                 warp shuffle, y halo rows from shared memory; the per-plane CTA barrier frees
+//                 the slot and thread 0 issues the next load (no producer warp).  Many short z
+//                 segments; the peer-store halo transport of dist.cu lives in the same kernel.
+//   jacobi7_tma   the same ring fed by a ninth, producer warp with full/empty mbarriers — the
+//                 earlier design, kept for A/B timing (HPCX_JACOBI_PRODUCER=1).
+//   jacobi7_tb2   two sweeps per pass over HBM (HPCX_VARIANT_TEMPORAL), bit-identical results.
 #include "grid.cuh"
 
 #include <algorithm>
@@ -224,7 +228,8 @@ __device__ __forceinline__ void st_cs(float4 *p, float4 v) {
 }
 
 // ------------------------------------------------------------------ Jacobi, TMA ring
-// CTA = 8 consumer warps + 1 producer warp.  Tile TX = 128 (one float4 per lane) by
+// Geometry shared by both ring kernels (the producer-warp kernel below adds a ninth warp and the
+// `empty` barriers).  Tile TX = 128 (one float4 per lane) by
 // TY = 16 rows (two adjacent rows per consumer warp), S ring slots of one plane box each.
 template <int S>
 struct JacobiCfg {
