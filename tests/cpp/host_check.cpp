@@ -112,6 +112,20 @@ static int run_csr() {
   } catch (const std::out_of_range &) {
     std::printf("triplets_oob out_of_range\n");
   }
+  // host-side partitioners of the multi-GPU face (static chunking, test_hpc_benchmark.cpp:1356)
+  {
+    const auto A = sparse::CsrMatrix<double, int32_t>::laplace2d(10, 10);
+    const auto rows = sparse::partition_rows(A, 3);
+    const auto by_nnz = sparse::partition_rows(A, 3, sparse::RowSplit::EqualNnz);
+    const auto slabs = hpc::partition_slabs(13, 8);
+    std::printf("partition_rows");
+    for (auto b : rows) std::printf(" %lld", (long long)b);
+    std::printf(" | by_nnz");
+    for (auto b : by_nnz) std::printf(" %lld", (long long)b);
+    std::printf(" | slabs");
+    for (auto b : slabs) std::printf(" %lld", (long long)b);
+    std::printf("\n");
+  }
   return 0;
 }
 

@@ -103,6 +103,13 @@ def test_csr_builders_match_oracle(binary):
     assert g[3] == _fnv1a(rp.astype(np.int64)) and g[4] == _fnv1a(col) and g[5] == _fnv1a(val)
     assert "triplets nnz 4 rp 0 2 3 4 col 0 3 0 1 val 4 2 -1 1.75" in out
     assert "triplets_oob out_of_range" in out
+    # partition helpers of include/hpcx/Distributed.hpp against the oracle's partitioner
+    rp, col, val = oracle.laplace2d(10, 10)
+    m = re.search(r"partition_rows ([\d ]+) \| by_nnz ([\d ]+) \| slabs ([\d ]+)", out)
+    assert m, out
+    assert [int(v) for v in m.group(1).split()] == list(oracle.partition_rows(rp, 100, 3, 0))
+    assert [int(v) for v in m.group(2).split()] == list(oracle.partition_rows(rp, 100, 3, 1))
+    assert [int(v) for v in m.group(3).split()] == list(oracle.partition_rows(None, 13, 8, 0))  # static chunking
 
 
 @pytest.mark.gpu
