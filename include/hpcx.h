@@ -74,6 +74,8 @@ HPCX_API hpcx_status hpcx_host_alloc(hpcx_ctx ctx, size_t bytes, void **out);
 HPCX_API hpcx_status hpcx_host_free(hpcx_ctx ctx, void *p);
 HPCX_API hpcx_status hpcx_device_alloc(hpcx_ctx ctx, size_t bytes, void **out);
 HPCX_API hpcx_status hpcx_device_free(hpcx_ctx ctx, void *p);
+/* Any direction (cudaMemcpyDefault).  Ordered after all work already issued to the device and
+ * complete on return. */
 HPCX_API hpcx_status hpcx_memcpy(hpcx_ctx ctx, void *dst, const void *src, size_t bytes);
 
 /* ------------------------------------------------- ghost-padded grid (a1, a2)
@@ -330,6 +332,16 @@ HPCX_API hpcx_status hpcx_comm_barrier(hpcx_ctx ctx);
 HPCX_API hpcx_status hpcx_comm_ipc_export(hpcx_ctx ctx, const void *dev_ptr, void *handle64);
 HPCX_API hpcx_status hpcx_comm_ipc_open(hpcx_ctx ctx, const void *handle64, void **peer_ptr);
 HPCX_API hpcx_status hpcx_comm_ipc_close(hpcx_ctx ctx, void *peer_ptr);
+/* The fused (peer-store) transports wait on flag words a neighbour writes.  By default such a
+ * wait has no bound, like an NCCL receive.  hpcx_comm_set_timeout (or HPCX_HALO_TIMEOUT_MS in the
+ * environment at hpcx_init) gives it one: a kernel that waits longer records the timeout in a
+ * host-visible word and TRAPS — it never goes on to read a stale ghost plane or x-halo — so the
+ * CUDA context is lost and every later call fails.  hpcx_comm_check reports (and clears) that word
+ * without touching the device: HPCX_NCCL_ERROR after a timeout, HPCX_OK otherwise.  Callers that
+ * pass their own stream use it after synchronising; the library's own synchronising exits
+ * (stream == NULL calls, hpcx_synchronize, hpcx_cg_solve, hpcx_stencil_dist_destroy) call it. */
+HPCX_API hpcx_status hpcx_comm_set_timeout(hpcx_ctx ctx, int64_t milliseconds);
+HPCX_API hpcx_status hpcx_comm_check(hpcx_ctx ctx);
 
 /* Distributed stencil: every rank owns a z-slab (axis 0) grid pair created with
  * hpcx_grid_create; neighbours are rank-1 / rank+1 (no periodic wrap: the outermost
@@ -387,7 +399,7 @@ HPCX_API hpcx_status hpcx_spmv_dist(hpcx_csr A, const void *x_local, void *y_loc
 typedef struct hpcx_cg_s *hpcx_cg;
 typedef struct {
   int32_t iterations;
-  int32_t converged;
+  int32_t converged;  /* 1 converged, 0 not yet, -1 breakdown (<p, A p> not positive: A not SPD, or NaN) */
   double rr;  /* ||r||^2 from the recurrence */
   double bb;  /* ||b||^2 */
 } hpcx_cg_result;

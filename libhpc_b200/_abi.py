@@ -117,6 +117,8 @@ PROTOTYPES = {
     "hpcx_comm_ipc_export": (_i32, [_vp, _vp, _vp]),
     "hpcx_comm_ipc_open": (_i32, [_vp, _vp, _P(_vp)]),
     "hpcx_comm_ipc_close": (_i32, [_vp, _vp]),
+    "hpcx_comm_set_timeout": (_i32, [_vp, _i64]),
+    "hpcx_comm_check": (_i32, [_vp]),
     "hpcx_stencil_dist_plan": (_i32, [_vp, _vp, _vp, _P(StencilDesc), _i32, _P(_vp)]),
     "hpcx_stencil_dist_sweep": (_i32, [_vp, _i32, _vp]),
     "hpcx_stencil_dist_destroy": (_i32, [_vp]),

@@ -564,7 +564,8 @@ class CgSolver:
                                                   C.byref(res) if want_result else None, _stream(stream)))
         if not want_result:
             return None
-        return dict(iterations=res.iterations, converged=bool(res.converged), rr=res.rr, bb=res.bb)
+        return dict(iterations=res.iterations, converged=res.converged == 1, breakdown=res.converged < 0,
+                    rr=res.rr, bb=res.bb)
 
     def destroy(self):
         if self.h:

@@ -72,6 +72,12 @@ __global__ void cg_scalar_kernel(T *__restrict__ sc, int32_t *__restrict__ flags
   }
   if (flags[1]) return;
   if (phase == 1) {
+    // breakdown guard: <p, A p> must be positive for an SPD operator; zero, negative or NaN
+    // stops the iteration (flag -1) instead of spreading NaNs through x
+    if (!(sc[kPQ] > T(0))) {
+      flags[1] = -1;
+      return;
+    }
     sc[kAlpha] = sc[kRR] / sc[kPQ];
   } else {
     sc[kBeta] = sc[kRRnew] / sc[kRR];
@@ -251,8 +257,11 @@ hpcx_status hpcx_cg_create(hpcx_csr A, hpcx_cg *out) {
   if (e == cudaSuccess) e = cudaMalloc(&S->part, parts * es);
   if (e == cudaSuccess) e = cudaMalloc(&S->sc, kScalars * es);
   if (e == cudaSuccess) e = cudaMalloc((void **)&S->flags, 8);
-  if (e == cudaSuccess) e = cudaMemset(S->sc, 0, kScalars * es);
-  if (e == cudaSuccess) e = cudaMemset(S->flags, 0, 8);
+  // on the context's (non-blocking) compute stream and waited for: a legacy-stream cudaMemset would
+  // not be ordered before the first solve's copies on that stream
+  if (e == cudaSuccess) e = cudaMemsetAsync(S->sc, 0, kScalars * es, ctx->compute);
+  if (e == cudaSuccess) e = cudaMemsetAsync(S->flags, 0, 8, ctx->compute);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->compute);
   if (e != cudaSuccess) {
     free_cg(S);
     return fail(ctx, e == cudaErrorMemoryAllocation ? HPCX_OOM : HPCX_CUDA_ERROR,
@@ -272,6 +281,7 @@ hpcx_status hpcx_cg_solve(hpcx_cg S, const void *b, int32_t b_mem, void *x, int3
                           int32_t max_iters, double rel_tol, int32_t check_every,
                           hpcx_cg_result *result, void *stream) {
   if (!S || !b || !x) return HPCX_INVALID_ARG;
+  HPCX_RANGE("hpcx_cg_solve");
   hpcx_ctx ctx = S->A->ctx;
   HPCX_REQUIRE(ctx, max_iters >= 0 && rel_tol >= 0.0 && check_every >= 0, "bad iteration limits");
   cudaStream_t s = stream ? (cudaStream_t)stream : ctx->compute;
@@ -294,7 +304,7 @@ hpcx_status hpcx_cg_solve(hpcx_cg S, const void *b, int32_t b_mem, void *x, int3
   if (rc != HPCX_OK) return rc;
   if (x_mem == HPCX_MEM_HOST) HPCX_CUDA(ctx, cudaMemcpyAsync(x, dx, nb, cudaMemcpyDeviceToHost, s));
   if (result || !stream || x_mem == HPCX_MEM_HOST) {
-    HPCX_CUDA(ctx, cudaStreamSynchronize(s));
+    if (hpcx_status st = sync_and_check(ctx, s)) return st;
     if (result) {
       int32_t fl[2];
       HPCX_CUDA(ctx, cudaMemcpy(fl, S->flags, 8, cudaMemcpyDeviceToHost));

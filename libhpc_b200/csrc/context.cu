@@ -74,8 +74,11 @@ hpcx_status hpcx_init(int32_t device, hpcx_ctx *out) {
   for (auto &ev : ctx->ev) HPCX_CUDA(ctx, cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
   const char *dbg = getenv("HPCX_DEBUG_SYNC");
   ctx->debug_sync = dbg && dbg[0] == '1';
-  const char *jd = getenv("HPCX_JACOBI_DOWN");
-  ctx->force_jacobi_down = jd && jd[0] == '1';
+  // error word of the peer-flag waits: mapped pinned host memory (readable after a device trap)
+  HPCX_CUDA(ctx, cudaHostAlloc((void **)&ctx->err_host, 64, cudaHostAllocMapped | cudaHostAllocPortable));
+  memset(ctx->err_host, 0, 64);
+  HPCX_CUDA(ctx, cudaHostGetDevicePointer((void **)&ctx->err_dev, ctx->err_host, 0));
+  if (const char *to = getenv("HPCX_HALO_TIMEOUT_MS")) ctx->halo_timeout_ns = (uint64_t)atoll(to) * 1000000ull;
   cudaDriverEntryPointQueryResult qres;
   void *fn = nullptr;
   e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
@@ -95,6 +98,8 @@ hpcx_status hpcx_finalize(hpcx_ctx ctx) {
     cudaStreamDestroy(ctx->comm);
     cudaStreamDestroy(ctx->copy_in);
     cudaStreamDestroy(ctx->copy_out);
+    cudaFree(ctx->barrier_token);
+    if (ctx->err_host) cudaFreeHost(ctx->err_host);
   }
   delete ctx;
   return HPCX_OK;
@@ -106,7 +111,9 @@ const char *hpcx_last_error_string(hpcx_ctx ctx) {
 
 hpcx_status hpcx_synchronize(hpcx_ctx ctx) {
   if (!ctx) return HPCX_INVALID_ARG;
-  HPCX_CUDA(ctx, cudaDeviceSynchronize());
+  cudaError_t e = cudaDeviceSynchronize();
+  if (hpcx_status st = comm_check(ctx)) return st;
+  HPCX_CUDA(ctx, e);
   return HPCX_OK;
 }
 
@@ -134,11 +141,12 @@ hpcx_status hpcx_device_free(hpcx_ctx ctx, void *p) {
 }
 hpcx_status hpcx_memcpy(hpcx_ctx ctx, void *dst, const void *src, size_t bytes) {
   if (!ctx) return HPCX_INVALID_ARG;
-  // Synchronous on both sides: device-to-device cudaMemcpy returns before the copy has run and
-  // is not ordered with non-blocking streams, so drain the device before and after.
+  // Contract: ordered after ALL work already issued to the device (the caller's own streams
+  // included — they are unknown here, hence one device-wide drain) and complete on return.  The
+  // copy itself runs on the compute stream, so one stream synchronise ends the call.
   HPCX_CUDA(ctx, cudaDeviceSynchronize());
-  HPCX_CUDA(ctx, cudaMemcpy(dst, src, bytes, cudaMemcpyDefault));
-  HPCX_CUDA(ctx, cudaDeviceSynchronize());
+  HPCX_CUDA(ctx, cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDefault, ctx->compute));
+  HPCX_CUDA(ctx, cudaStreamSynchronize(ctx->compute));
   return HPCX_OK;
 }
 

@@ -13,8 +13,9 @@
 // outputs j with 0 <= r-j < 16.  Each output therefore sees its 256 products in exactly the
 // reference's (l, k) order, so the result is bit-identical, while one shared-memory load
 // (conflict-free: a warp reads 32 consecutive floats) feeds up to 8 multiply-add pairs.  The
-// weights sit in constant memory; the r/k/j loops are fully unrolled so every weight is an
-// immediate constant-bank operand.  The sweep is FP32-issue bound (512 separately rounded
+// weights travel as a __grid_constant__ kernel parameter (parameters live in the constant bank,
+// and nothing is shared between calls, streams or contexts); the r/k/j loops are fully unrolled
+// so every weight is an immediate constant-bank operand.  The sweep is FP32-issue bound (512 separately rounded
 // operations per cell), not HBM bound: 8 B/cell of traffic against 512 flops.
 //
 // transpose_tile_kernel<T>: 64 x 64 tiles through padded shared memory, 16-byte global accesses
@@ -44,12 +45,12 @@ __device__ __forceinline__ float mul_rn(float a, float b) { return __fmul_rn(a, 
 __device__ __forceinline__ double mul_rn(double a, double b) { return __dmul_rn(a, b); }
 
 constexpr int kMaxTaps = 32 * 32;
-__constant__ double c_weights[kMaxTaps];  // float kernels read the same bytes as float
 
-template <typename T>
-__device__ __forceinline__ T weight(int i) {
-  return reinterpret_cast<const T *>(c_weights)[i];
-}
+// Weights of the tiled kernel: a by-value kernel parameter (1 KB fp32 / 2 KB fp64 for 16 x 16).
+template <typename T, int N>
+struct ConvWeights {
+  T v[N];
+};
 
 constexpr int kConvTX = 32, kConvRY = 8, kConvGY = 8;  // 32 columns x (8 groups of 8 rows) per CTA
 
@@ -57,28 +58,30 @@ constexpr int kConvTX = 32, kConvRY = 8, kConvGY = 8;  // 32 columns x (8 groups
 // only honours partially at this size): every weight index is a constant expression, so the
 // multiplies take their weight straight from the constant bank.
 template <typename T, int KH, int KW, int SP, int R, int K>
-__device__ __forceinline__ void conv_tap(const T *__restrict__ col, T (&acc)[kConvRY]) {
+__device__ __forceinline__ void conv_tap(const T *__restrict__ col, T (&acc)[kConvRY],
+                                         const ConvWeights<T, KH * KW> &w) {
   const T v = col[R * SP + K];
 #pragma unroll
   for (int j = 0; j < kConvRY; ++j) {
     const int l = R - j;
-    if (l >= 0 && l < KH) acc[j] = add_rn(acc[j], mul_rn(v, weight<T>(l * KW + K)));
+    if (l >= 0 && l < KH) acc[j] = add_rn(acc[j], mul_rn(v, w.v[l * KW + K]));
   }
 }
 template <typename T, int KH, int KW, int SP, int R, int... K>
 __device__ __forceinline__ void conv_row(const T *__restrict__ col, T (&acc)[kConvRY],
-                                         std::integer_sequence<int, K...>) {
-  (conv_tap<T, KH, KW, SP, R, K>(col, acc), ...);
+                                         const ConvWeights<T, KH * KW> &w, std::integer_sequence<int, K...>) {
+  (conv_tap<T, KH, KW, SP, R, K>(col, acc, w), ...);
 }
 template <typename T, int KH, int KW, int SP, int... R>
 __device__ __forceinline__ void conv_rows(const T *__restrict__ col, T (&acc)[kConvRY],
-                                          std::integer_sequence<int, R...>) {
-  (conv_row<T, KH, KW, SP, R>(col, acc, std::make_integer_sequence<int, KW>{}), ...);
+                                          const ConvWeights<T, KH * KW> &w, std::integer_sequence<int, R...>) {
+  (conv_row<T, KH, KW, SP, R>(col, acc, w, std::make_integer_sequence<int, KW>{}), ...);
 }
 
 template <typename T, int KH, int KW>
 __global__ void __launch_bounds__(kConvTX *kConvGY)
-conv2d_tile_kernel(const T *__restrict__ in, T *__restrict__ out, Geom2 gi, Geom2 go) {
+conv2d_tile_kernel(const T *__restrict__ in, T *__restrict__ out, Geom2 gi, Geom2 go,
+                   const __grid_constant__ ConvWeights<T, KH * KW> w) {
   constexpr int TY = kConvRY * kConvGY;           // 64 output rows per CTA
   constexpr int SW = kConvTX + KW - 1;            // staged tile width
   constexpr int SH = TY + KH - 1;                 // staged tile height
@@ -100,23 +103,24 @@ conv2d_tile_kernel(const T *__restrict__ in, T *__restrict__ out, Geom2 gi, Geom
   for (int j = 0; j < kConvRY; ++j)
     acc[j] = (x < go.nx && yb + j < go.ny) ? out[at2(go, yb + j, x)] : T(0);
   const T *col = tile + (gy * kConvRY) * SP + tx;
-  conv_rows<T, KH, KW, SP>(col, acc, std::make_integer_sequence<int, kConvRY + KH - 1>{});
+  conv_rows<T, KH, KW, SP>(col, acc, w, std::make_integer_sequence<int, kConvRY + KH - 1>{});
 #pragma unroll
   for (int j = 0; j < kConvRY; ++j)
     if (x < go.nx && yb + j < go.ny) out[at2(go, yb + j, x)] = acc[j];
 }
 
-// Any kernel extent: one thread per output, taps through L1.
+// Any kernel extent: one thread per output, taps through L1, weights from a per-call device buffer.
 template <typename T>
 __global__ void __launch_bounds__(256)
-conv2d_direct_kernel(const T *__restrict__ in, T *__restrict__ out, Geom2 gi, Geom2 go, int kh, int kw) {
+conv2d_direct_kernel(const T *__restrict__ in, T *__restrict__ out, Geom2 gi, Geom2 go, int kh, int kw,
+                     const T *__restrict__ w) {
   const int64_t x = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   const int64_t y = blockIdx.y * (int64_t)blockDim.y + threadIdx.y;
   if (x >= go.nx || y >= go.ny) return;
   T s = out[at2(go, y, x)];
   for (int l = 0; l < kh; ++l) {
     const T *p = in + at2(gi, y + l, x);
-    for (int k = 0; k < kw; ++k) s = add_rn(s, mul_rn(__ldg(p + k), weight<T>(l * kw + k)));
+    for (int k = 0; k < kw; ++k) s = add_rn(s, mul_rn(__ldg(p + k), __ldg(w + l * kw + k)));
   }
   out[at2(go, y, x)] = s;
 }
@@ -172,35 +176,29 @@ transpose_tile_kernel(const T *__restrict__ in, T *__restrict__ out, Geom2 gi, G
   }
 }
 
-std::vector<unsigned char> g_last_weights;  // what c_weights holds, and the stream that put it there
-cudaStream_t g_last_stream = nullptr;
-int g_last_es = 0;
-
 template <typename T>
 hpcx_status conv2d_t(hpcx_grid in, hpcx_grid out, const T *w, int kh, int kw, int variant, cudaStream_t s) {
   hpcx_ctx ctx = in->ctx;
-  // Weights go through the stream so that back-to-back calls with different kernels stay
-  // ordered; an unchanged kernel (the iterative use) is not uploaded again.  One device per
-  // process (one process per GPU), so one cache suffices.
-  std::vector<unsigned char> &last = g_last_weights;  // shared by the fp32 and fp64 paths: one symbol
-  const size_t wb = (size_t)kh * kw * sizeof(T);
-  if (last.size() != wb || g_last_stream != s || g_last_es != (int)sizeof(T) ||
-      memcmp(last.data(), w, wb) != 0) {
-    HPCX_CUDA(ctx, cudaMemcpyToSymbolAsync(c_weights, w, wb, 0, cudaMemcpyHostToDevice, s));
-    last.assign((const unsigned char *)w, (const unsigned char *)w + wb);
-    g_last_stream = s;
-    g_last_es = (int)sizeof(T);
-  }
   const Geom2 gi = geom2(in), go = geom2(out);
   if (kh == 16 && kw == 16 && variant != HPCX_VARIANT_DIRECT) {
+    ConvWeights<T, 256> wk;
+    memcpy(wk.v, w, sizeof wk.v);  // captured by the launch: no state outlives the call
     dim3 grid((unsigned)((go.nx + kConvTX - 1) / kConvTX),
               (unsigned)((go.ny + kConvRY * kConvGY - 1) / (kConvRY * kConvGY)));
-    conv2d_tile_kernel<T, 16, 16><<<grid, kConvTX * kConvGY, 0, s>>>((const T *)in->dev, (T *)out->dev, gi, go);
+    conv2d_tile_kernel<T, 16, 16><<<grid, kConvTX * kConvGY, 0, s>>>((const T *)in->dev, (T *)out->dev, gi, go, wk);
     return after_launch(ctx, "conv2d_tile_kernel");
   }
+  // stream-ordered scratch for the weights (the host array may be reused as soon as this returns:
+  // a pageable cudaMemcpyAsync has staged it by then)
+  const size_t wb = (size_t)kh * kw * sizeof(T);
+  T *dw = nullptr;
+  HPCX_CUDA(ctx, cudaMallocAsync((void **)&dw, wb, s));
+  HPCX_CUDA(ctx, cudaMemcpyAsync(dw, w, wb, cudaMemcpyHostToDevice, s));
   dim3 block(64, 4), grid((unsigned)((go.nx + 63) / 64), (unsigned)((go.ny + 3) / 4));
-  conv2d_direct_kernel<T><<<grid, block, 0, s>>>((const T *)in->dev, (T *)out->dev, gi, go, kh, kw);
-  return after_launch(ctx, "conv2d_direct_kernel");
+  conv2d_direct_kernel<T><<<grid, block, 0, s>>>((const T *)in->dev, (T *)out->dev, gi, go, kh, kw, dw);
+  hpcx_status st = after_launch(ctx, "conv2d_direct_kernel");
+  HPCX_CUDA(ctx, cudaFreeAsync(dw, s));
+  return st;
 }
 
 template <typename T>

@@ -27,8 +27,8 @@ hpcx_status spmv_launch_blocks(hpcx_csr A, const RowBlock *d_blocks, int64_t nbl
 hpcx_status spmv_launch_fixup_tables(hpcx_csr A, const int32_t *long_row, const int32_t *long_off,
                                      int64_t nlong, void *y, cudaStream_t s, const void *x,
                                      void *dot_part);
-void spmv_build_rowblocks(const int64_t *rp, int64_t nrows, int tile, const uint8_t *kind, int want,
-                          std::vector<RowBlock> &out, std::vector<int32_t> *long_row,
+void spmv_build_rowblocks(const int64_t *rp, int64_t nrows, int tile, int short_row_max, const uint8_t *kind,
+                          int want, std::vector<RowBlock> &out, std::vector<int32_t> *long_row,
                           std::vector<int32_t> *long_off);
 }  // namespace hpcx
 
@@ -93,7 +93,7 @@ struct hpcx_halo_plan_s {
   int transport = 0;
   cudaEvent_t ev_bnd = nullptr, ev_recv = nullptr, ev_start = nullptr;
   // transport 1 (peer stores): neighbour side 0 = rank-1, 1 = rank+1
-  uint32_t *flags = nullptr;          // local block: [0],[1] flags, [4],[5] counters, [6] error word
+  uint32_t *flags = nullptr;          // local block: [0],[1] flags, [4],[5] counters, [8] push counter
   void *buf[2] = {nullptr, nullptr};  // this rank's two grid buffers at plan time (A = in, B = out)
   void *peer_open[2][3] = {};         // bases returned by cudaIpcOpenMemHandle (A, B, flags)
   float *peer_buf[2][2] = {};         // the neighbour's A and B
@@ -224,10 +224,10 @@ hpcx_status open_peers(hpcx_halo_plan p) {
 
 // Last launch of a peer-store sweep sequence: the stream does not complete before both
 // neighbours have delivered the ghost planes of the newest iterate.
-__global__ void halo_wait_kernel(const uint32_t *flags, uint32_t *err, uint32_t want, int has_lo,
+__global__ void halo_wait_kernel(const uint32_t *flags, PeerWait pw, uint32_t want, int has_lo,
                                  int has_hi) {
-  if (has_lo) wait_flag(flags + 0, want, err);
-  if (has_hi) wait_flag(flags + 1, want, err);
+  if (has_lo) wait_flag(flags + 0, want, pw);
+  if (has_hi) wait_flag(flags + 1, want, pw);
 }
 
 // Two-sweep passes: after the pass kernel, copy this slab's two boundary planes per side straight
@@ -238,7 +238,7 @@ __global__ void __launch_bounds__(256)
 halo_push_planes_kernel(const float4 *__restrict__ lo_src, float4 *__restrict__ lo_dst,
                         const float4 *__restrict__ hi_src, float4 *__restrict__ hi_dst, int64_t n4,
                         uint32_t *counter, uint32_t *sig_lo, uint32_t *sig_hi, uint32_t sig_val,
-                        const uint32_t *flags, uint32_t *err) {
+                        const uint32_t *flags, PeerWait pw) {
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n4; i += stride) {
     if (lo_dst) lo_dst[i] = __ldg(lo_src + i);
@@ -251,8 +251,8 @@ halo_push_planes_kernel(const float4 *__restrict__ lo_src, float4 *__restrict__ 
     __threadfence_system();
     if (sig_lo) st_release_sys(sig_lo, sig_val);
     if (sig_hi) st_release_sys(sig_hi, sig_val);
-    if (sig_lo) wait_flag(flags + 0, sig_val, err);
-    if (sig_hi) wait_flag(flags + 1, sig_val, err);
+    if (sig_lo) wait_flag(flags + 0, sig_val, pw);
+    if (sig_hi) wait_flag(flags + 1, sig_val, pw);
   }
 }
 
@@ -306,12 +306,26 @@ hpcx_status hpcx_comm_barrier(hpcx_ctx ctx) {
     HPCX_CUDA(ctx, cudaDeviceSynchronize());
     return HPCX_OK;
   }
-  static thread_local float *token = nullptr;
-  if (!token) HPCX_CUDA(ctx, cudaMalloc((void **)&token, 16));
+  if (!ctx->barrier_token) {
+    HPCX_CUDA(ctx, cudaMalloc((void **)&ctx->barrier_token, 16));
+    HPCX_CUDA(ctx, cudaMemsetAsync(ctx->barrier_token, 0, 16, ctx->comm));
+  }
+  float *token = ctx->barrier_token;
   HPCX_CUDA(ctx, cudaDeviceSynchronize());
   HPCX_NCCL(ctx, g_nccl.AllReduce(token, token, 1, ncclFloat32, ncclSum, comm_of(ctx), ctx->comm));
   HPCX_CUDA(ctx, cudaStreamSynchronize(ctx->comm));
   return HPCX_OK;
+}
+
+hpcx_status hpcx_comm_set_timeout(hpcx_ctx ctx, int64_t milliseconds) {
+  if (!ctx || milliseconds < 0) return HPCX_INVALID_ARG;
+  ctx->halo_timeout_ns = (uint64_t)milliseconds * 1000000ull;
+  return HPCX_OK;
+}
+
+hpcx_status hpcx_comm_check(hpcx_ctx ctx) {
+  if (!ctx) return HPCX_INVALID_ARG;
+  return comm_check(ctx);
 }
 
 hpcx_status hpcx_comm_ipc_export(hpcx_ctx ctx, const void *dev_ptr, void *handle64) {
@@ -437,6 +451,7 @@ static hpcx_status dist_sweep_peer(hpcx_halo_plan p, int32_t steps, cudaStream_t
     }
     pr.flags = p->flags;
     pr.counters = p->flags + 4;
+    pr.pw = peer_wait_of(ctx);
     pr.wait_val = t == 0 ? 0 : p->epoch + (uint32_t)t;  // pass 0 reads NCCL-exchanged ghosts
     pr.sig_val = p->epoch + (uint32_t)t + 1;
     if (temporal && t < steps / 2) {
@@ -450,7 +465,7 @@ static hpcx_status dist_sweep_peer(hpcx_halo_plan p, int32_t steps, cudaStream_t
           reinterpret_cast<float4 *>(has_lo ? pr.ghost_lo : nullptr),
           reinterpret_cast<const float4 *>(mine + (g->glo[0] + g->n[0] - 2) * plane),
           reinterpret_cast<float4 *>(has_hi ? pr.ghost_hi - plane : nullptr), 2 * plane / 4, p->flags + 8,
-          pr.sig_lo, pr.sig_hi, pr.sig_val, p->flags, p->flags + 6);
+          pr.sig_lo, pr.sig_hi, pr.sig_val, p->flags, pr.pw);
       rc = after_launch(ctx, "halo_push_planes_kernel");
     } else {
       rc = jacobi7_launch(g, p->buf[cur], p->buf[dst], HPCX_VARIANT_TMA, temporal ? 0 : p->st.zsplit, 0, g->n[0],
@@ -461,16 +476,11 @@ static hpcx_status dist_sweep_peer(hpcx_halo_plan p, int32_t steps, cudaStream_t
   }
   p->epoch += (uint32_t)passes;
   steps = passes;  // parity of the buffer swap below
-  halo_wait_kernel<<<1, 1, 0, cs>>>(p->flags, p->flags + 6, p->epoch, has_lo, has_hi);
+  halo_wait_kernel<<<1, 1, 0, cs>>>(p->flags, peer_wait_of(ctx), p->epoch, has_lo, has_hi);
   rc = after_launch(ctx, "halo_wait_kernel");
   if (rc != HPCX_OK) return rc;
   if ((steps & 1) == 0) std::swap(p->in->dev, p->out->dev);  // newest iterate is `out`
-  if (sync) {
-    HPCX_CUDA(ctx, cudaStreamSynchronize(cs));
-    uint32_t err = 0;
-    HPCX_CUDA(ctx, cudaMemcpy(&err, p->flags + 6, 4, cudaMemcpyDeviceToHost));
-    if (err) return fail(ctx, HPCX_NCCL_ERROR, "timed out waiting for a neighbour's halo flag");
-  }
+  if (sync) return sync_and_check(ctx, cs);
   return HPCX_OK;
 }
 
@@ -484,6 +494,7 @@ static hpcx_status dist_sweep_peer(hpcx_halo_plan p, int32_t steps, cudaStream_t
 // steps is odd: the bytes exchanged per sweep are unchanged, the messages per sweep halve.
 hpcx_status hpcx_stencil_dist_sweep(hpcx_halo_plan p, int32_t steps, void *stream) {
   if (!p) return HPCX_INVALID_ARG;
+  HPCX_RANGE("hpcx_stencil_dist_sweep");
   hpcx_ctx ctx = p->ctx;
   HPCX_REQUIRE(ctx, steps >= 1, "steps must be >= 1");
   hpcx_grid g = p->in;
@@ -521,14 +532,17 @@ hpcx_status hpcx_stencil_dist_sweep(hpcx_halo_plan p, int32_t steps, void *strea
       return jacobi7_launch(g, src, dst, temporal ? HPCX_VARIANT_TMA : p->st.variant, zsplit, zb, ze, cs, nullptr);
     };
     HPCX_CUDA(ctx, cudaStreamWaitEvent(cs, p->ev_recv, 0));
+    nvtxRangePushA("sweep: boundary planes");
     if (two) {  // both boundary strips in one launch
       rc = jacobi7_tb2_launch(g, src, dst, 1, 0, lo_end, nb_lo, nb_hi, cs, hi_beg, nz);
     } else {
       rc = launch(0, lo_end, 1);
       if (rc == HPCX_OK) rc = launch(hi_beg, nz, 1);
     }
+    nvtxRangePop();
     if (rc != HPCX_OK) return rc;
     if (t + 1 < passes) {
+      HPCX_RANGE("sweep: ghost-plane exchange (NCCL send/recv)");
       const int64_t wnext = (temporal && t + 1 < steps / 2) ? 2 : 1;
       HPCX_CUDA(ctx, cudaEventRecord(p->ev_bnd, cs));
       HPCX_CUDA(ctx, cudaStreamWaitEvent(ms, p->ev_bnd, 0));
@@ -536,7 +550,10 @@ hpcx_status hpcx_stencil_dist_sweep(hpcx_halo_plan p, int32_t steps, void *strea
       if (rc != HPCX_OK) return rc;
       HPCX_CUDA(ctx, cudaEventRecord(p->ev_recv, ms));
     }
-    rc = launch(lo_end, hi_beg, temporal ? (two ? p->st.zsplit : 0) : p->st.zsplit);
+    {
+      HPCX_RANGE("sweep: interior planes");
+      rc = launch(lo_end, hi_beg, temporal ? (two ? p->st.zsplit : 0) : p->st.zsplit);
+    }
     if (rc != HPCX_OK) return rc;
     std::swap(src, dst);
   }
@@ -549,12 +566,13 @@ hpcx_status hpcx_stencil_dist_sweep(hpcx_halo_plan p, int32_t steps, void *strea
 hpcx_status hpcx_stencil_dist_destroy(hpcx_halo_plan p) {
   if (!p) return HPCX_INVALID_ARG;
   cudaDeviceSynchronize();
+  const hpcx_status pending = comm_check(p->ctx);  // a timed-out wait of an asynchronous sweep surfaces here
   close_peers(p);
   cudaEventDestroy(p->ev_bnd);
   cudaEventDestroy(p->ev_recv);
   cudaEventDestroy(p->ev_start);
   delete p;
-  return HPCX_OK;
+  return pending;
 }
 
 }  // extern "C"
@@ -575,7 +593,7 @@ gather_boundary_x_kernel(const T *__restrict__ x, const int32_t *__restrict__ se
 }
 
 // ---- transport 1: gather + peer store + flag in one kernel ------------------------------
-constexpr int kSyncData = 0, kSyncAck = 64, kSyncCount = 128, kSyncErr = 129, kMaxPeers = 64;
+constexpr int kSyncData = 0, kSyncAck = 64, kSyncCount = 128, kMaxPeers = 64;
 
 // grid = (blocks per segment, segments).  Segment s holds the entries destined for rank
 // seg_rank[s]; they are stored straight into that rank's halo slots.  The last CTA to finish
@@ -585,10 +603,10 @@ __global__ void __launch_bounds__(256)
 push_boundary_x_kernel(const T *__restrict__ x, const int32_t *__restrict__ send_idx,
                        const int32_t *__restrict__ seg_start, const int32_t *__restrict__ seg_rank,
                        void *const *__restrict__ seg_dst, uint32_t *const *__restrict__ seg_flag,
-                       uint32_t *sync, uint32_t epoch) {
+                       uint32_t *sync, uint32_t epoch, PeerWait pw) {
   const int s = blockIdx.y;
   // The destination must have finished reading the previous product's halo (its ack).
-  if (threadIdx.x == 0) wait_flag(sync + kSyncAck + seg_rank[s], epoch - 1, sync + kSyncErr);
+  if (threadIdx.x == 0) wait_flag(sync + kSyncAck + seg_rank[s], epoch - 1, pw);
   __syncthreads();
   const int a = seg_start[s], e = seg_start[s + 1];
   T *dst = static_cast<T *>(seg_dst[s]);
@@ -605,9 +623,8 @@ push_boundary_x_kernel(const T *__restrict__ x, const int32_t *__restrict__ send
 
 // Holds the stream until every source rank's boundary entries of product `epoch` have landed.
 __global__ void halo_x_ready_kernel(uint32_t *sync, const int32_t *__restrict__ src_rank, int nsrc,
-                                    uint32_t epoch) {
-  if ((int)threadIdx.x < nsrc)
-    wait_flag(sync + kSyncData + src_rank[threadIdx.x], epoch, sync + kSyncErr);
+                                    uint32_t epoch, PeerWait pw) {
+  if ((int)threadIdx.x < nsrc) wait_flag(sync + kSyncData + src_rank[threadIdx.x], epoch, pw);
 }
 
 // Tells every source rank that this rank's boundary rows of product `epoch` have read the halo.
@@ -671,6 +688,9 @@ hpcx_status hpcx_csr_set_halo(hpcx_csr A, int64_t nloc, int64_t nhalo, const int
   }
   HPCX_REQUIRE(ctx, nrecv == nhalo, "recv_counts do not add up to nhalo");
   HPCX_REQUIRE(ctx, nsend == 0 || send_idx, "null send_idx");
+  for (int64_t i = 0; i < nsend; ++i)
+    if (send_idx[i] < 0 || send_idx[i] >= nloc)
+      return fail(ctx, HPCX_OUT_OF_RANGE, "send_idx entry outside [0, nloc)");
   A->nsend = nsend;
   cudaFree(A->d_send_idx);
   cudaFree(A->d_sendbuf);
@@ -696,9 +716,9 @@ hpcx_status hpcx_csr_set_halo(hpcx_csr A, int64_t nloc, int64_t nhalo, const int
   std::vector<int32_t> long_row, long_off;
   A->h_blocks_int.clear();
   A->h_blocks_bnd.clear();
-  spmv_build_rowblocks(rp.data(), A->nrows, A->tile, row_kind, 0, A->h_blocks_int, &long_row,
+  spmv_build_rowblocks(rp.data(), A->nrows, A->tile, A->short_row_max, row_kind, 0, A->h_blocks_int, &long_row,
                        &long_off);
-  spmv_build_rowblocks(rp.data(), A->nrows, A->tile, row_kind, 1, A->h_blocks_bnd, &long_row,
+  spmv_build_rowblocks(rp.data(), A->nrows, A->tile, A->short_row_max, row_kind, 1, A->h_blocks_bnd, &long_row,
                        &long_off);
   A->nlong_dist = (int64_t)long_row.size();
   auto up = [&](const void *h, size_t bytes, void **d) -> cudaError_t {
@@ -822,6 +842,7 @@ static hpcx_status spmv_dist_peer(hpcx_csr A, char *xfull, void *y_local, cudaSt
   const uint32_t epoch = ++A->epoch;
   hpcx_status rc;
   if (A->nseg) {
+    HPCX_RANGE("spmv_dist: push boundary x (peer stores)");
     int64_t longest = 0;
     for (int q = 0; q < ctx->nranks; ++q) longest = std::max(longest, A->send_counts[q]);
     dim3 grid((unsigned)std::min<int64_t>(std::max<int64_t>((longest + 255) / 256, 1), ctx->sm_count * 2),
@@ -829,19 +850,23 @@ static hpcx_status spmv_dist_peer(hpcx_csr A, char *xfull, void *y_local, cudaSt
     if (A->dtype == HPCX_F64)
       push_boundary_x_kernel<double><<<grid, 256, 0, cs>>>((const double *)xfull, A->d_send_idx,
                                                            A->d_seg_start, A->d_seg_rank, A->d_seg_dst,
-                                                           A->d_seg_flag, A->d_sync, epoch);
+                                                           A->d_seg_flag, A->d_sync, epoch, peer_wait_of(ctx));
     else
       push_boundary_x_kernel<float><<<grid, 256, 0, cs>>>((const float *)xfull, A->d_send_idx,
                                                           A->d_seg_start, A->d_seg_rank, A->d_seg_dst,
-                                                          A->d_seg_flag, A->d_sync, epoch);
+                                                          A->d_seg_flag, A->d_sync, epoch, peer_wait_of(ctx));
     rc = after_launch(ctx, "push_boundary_x_kernel");
     if (rc != HPCX_OK) return rc;
   }
-  rc = spmv_launch_blocks(A, A->d_blocks_int, (int64_t)A->h_blocks_int.size(), xfull, y_local, cs,
-                          dot_slot(A, 0));
+  {
+    HPCX_RANGE("spmv_dist: interior rows");
+    rc = spmv_launch_blocks(A, A->d_blocks_int, (int64_t)A->h_blocks_int.size(), xfull, y_local, cs,
+                            dot_slot(A, 0));
+  }
   if (rc != HPCX_OK) return rc;
   if (A->nsrc) {
-    halo_x_ready_kernel<<<1, 64, 0, cs>>>(A->d_sync, A->d_src_rank, A->nsrc, epoch);
+    HPCX_RANGE("spmv_dist: wait for the neighbours' flags");
+    halo_x_ready_kernel<<<1, 64, 0, cs>>>(A->d_sync, A->d_src_rank, A->nsrc, epoch, peer_wait_of(ctx));
     rc = after_launch(ctx, "halo_x_ready_kernel");
     if (rc != HPCX_OK) return rc;
   }
@@ -869,6 +894,7 @@ hpcx_status hpcx_csr_x_buffer(hpcx_csr A, void **x_full) {
 // comm stream   : [wait ev] grouped send/recv of the x halo segments -> ev_recv
 hpcx_status hpcx_spmv_dist(hpcx_csr A, const void *x_local, void *y_local, void *stream) {
   if (!A || !x_local || !y_local) return HPCX_INVALID_ARG;
+  HPCX_RANGE("hpcx_spmv_dist");
   hpcx_ctx ctx = A->ctx;
   HPCX_REQUIRE(ctx, A->d_xfull != nullptr, "hpcx_csr_set_halo has not been called");
   if (ctx->nranks > 1 && !ctx->nccl_comm)
@@ -884,12 +910,7 @@ hpcx_status hpcx_spmv_dist(hpcx_csr A, const void *x_local, void *y_local, void 
   if (A->transport == 1 && P > 1) {
     rc = spmv_dist_peer(A, xfull, y_local, cs);
     if (rc != HPCX_OK) return rc;
-    if (!stream) {
-      HPCX_CUDA(ctx, cudaStreamSynchronize(cs));
-      uint32_t err = 0;
-      HPCX_CUDA(ctx, cudaMemcpy(&err, A->d_sync + kSyncErr, 4, cudaMemcpyDeviceToHost));
-      if (err) return fail(ctx, HPCX_NCCL_ERROR, "timed out waiting for a neighbour's x-halo flag");
-    }
+    if (!stream) return sync_and_check(ctx, cs);
     return HPCX_OK;
   }
   if (A->nsend) {

@@ -35,9 +35,10 @@ struct JacobiPeer {
   uint32_t *sig_lo = nullptr;    // flag word in the low / high neighbour that receives sig_val
   uint32_t *sig_hi = nullptr;    //   once this rank's boundary plane has landed there
   const uint32_t *flags = nullptr;  // local: [0] stored by the low neighbour, [1] by the high one
-  uint32_t *counters = nullptr;  // local: [0], [1] CTA arrival counters per side, [2] error word
+  uint32_t *counters = nullptr;  // local: [0], [1] CTA arrival counters per side
   uint32_t wait_val = 0;         // ghost planes of src are valid once flags[side] >= wait_val
   uint32_t sig_val = 0;
+  PeerWait pw;                   // timeout policy of the flag waits (common.cuh)
 };
 // Device element index of logical (z, y, x) — ghost indices are negative / >= n.
 __host__ __device__ inline int64_t grid_dev_index(int64_t z, int64_t y, int64_t x, int64_t glo0,

@@ -252,15 +252,14 @@ spmv_sell_kernel(const int64_t *__restrict__ slice_ptr, const int32_t *__restric
   y[perm[srow]] = s;
 }
 
-// Threads per row of a block.  Rows no longer than g_short_row_max all take the fused
-// one-thread-per-row path (lanes = 1, oracle order); otherwise lanes grow with the mean row
-// length and are raised until the block's longest row costs a lane at most 64 entries.
-int g_short_row_max = 48;
-int lanes_for(int64_t nnz_blk, int64_t nrows, int64_t max_len) {
+// Threads per row of a block.  Rows no longer than short_row_max (a per-matrix option) all take
+// the fused one-thread-per-row path (lanes = 1, oracle order); otherwise lanes grow with the mean
+// row length and are raised until the block's longest row costs a lane at most 64 entries.
+int lanes_for(int64_t nnz_blk, int64_t nrows, int64_t max_len, int short_row_max) {
   if (nrows <= 0) return 1;
   const int64_t avg = (nnz_blk + nrows - 1) / nrows;
   if (nrows == 1 && nnz_blk > 256) return 0;
-  if (max_len <= g_short_row_max) return 1;
+  if (max_len <= short_row_max) return 1;
   int lanes = avg <= 16 ? 2 : avg <= 32 ? 4 : avg <= 64 ? 8 : avg <= 128 ? 16 : 32;
   while (lanes < 32 && max_len > 64 * (int64_t)lanes) lanes <<= 1;
   return lanes;
@@ -268,8 +267,8 @@ int lanes_for(int64_t nnz_blk, int64_t nrows, int64_t max_len) {
 
 // Greedy row blocking. `kind` (may be null) forces a cut wherever the row kind changes
 // and `want` selects which kind to emit (distributed interior / boundary tables).
-void build_rowblocks(const int64_t *rp, int64_t nrows, int tile, const uint8_t *kind, int want,
-                     std::vector<RowBlock> &out, std::vector<int32_t> *long_row,
+void build_rowblocks(const int64_t *rp, int64_t nrows, int tile, int short_row_max, const uint8_t *kind,
+                     int want, std::vector<RowBlock> &out, std::vector<int32_t> *long_row,
                      std::vector<int32_t> *long_off) {
   int64_t r = 0;
   int32_t nparts = long_off && !long_off->empty() ? long_off->back() : 0;
@@ -296,7 +295,7 @@ void build_rowblocks(const int64_t *rp, int64_t nrows, int tile, const uint8_t *
       max_len = std::max(max_len, rp[r + 1] - rp[r]);
       ++r;
     }
-    RowBlock b{(int32_t)r0, (int32_t)(r - r0), -1, lanes_for(rp[r] - p0, r - r0, max_len), p0, rp[r]};
+    RowBlock b{(int32_t)r0, (int32_t)(r - r0), -1, lanes_for(rp[r] - p0, r - r0, max_len, short_row_max), p0, rp[r]};
     out.push_back(b);
   }
 }
@@ -306,12 +305,7 @@ hpcx_status launch_stream_t(hpcx_csr A, const RowBlock *d_blocks, int64_t nblock
                             T *dot_part, cudaStream_t s) {
   if (nblocks == 0) return HPCX_OK;
   using L = StreamSmem<T, TILE>;
-  static bool configured = false;
-  if (!configured) {
-    HPCX_CUDA(A->ctx, cudaFuncSetAttribute(spmv_stream_kernel<T, TILE, DOT>,
-                                           cudaFuncAttributeMaxDynamicSharedMemorySize, L::kBytes));
-    configured = true;
-  }
+  if (hpcx_status st = ensure_dyn_smem(A->ctx, (const void *)spmv_stream_kernel<T, TILE, DOT>, L::kBytes)) return st;
   spmv_stream_kernel<T, TILE, DOT><<<(unsigned)nblocks, kThreads, L::kBytes, s>>>(
       A->d_row_ptr, A->d_col, (const T *)A->d_val, x, y, d_blocks, (T *)A->d_partials, dot_part);
   return after_launch(A->ctx, "spmv_stream_kernel");
@@ -510,10 +504,10 @@ hpcx_status spmv_launch_fixup_tables(hpcx_csr A, const int32_t *long_row, const 
   return launch_fixup<float>(A, long_row, long_off, nlong, (float *)y, s, (const float *)x,
                              (float *)dot_part);
 }
-void spmv_build_rowblocks(const int64_t *rp, int64_t nrows, int tile, const uint8_t *kind, int want,
-                          std::vector<RowBlock> &out, std::vector<int32_t> *long_row,
+void spmv_build_rowblocks(const int64_t *rp, int64_t nrows, int tile, int short_row_max, const uint8_t *kind,
+                          int want, std::vector<RowBlock> &out, std::vector<int32_t> *long_row,
                           std::vector<int32_t> *long_off) {
-  build_rowblocks(rp, nrows, tile, kind, want, out, long_row, long_off);
+  build_rowblocks(rp, nrows, tile, short_row_max, kind, want, out, long_row, long_off);
 }
 }  // namespace hpcx
 
@@ -531,6 +525,26 @@ chunk_colmax_kernel(const int32_t *__restrict__ col, const int64_t *__restrict__
     m = max(m, col[i]);
   for (int o = 16; o; o >>= 1) m = max(m, __shfl_xor_sync(0xffffffffu, m, o));
   if ((threadIdx.x & 31) == 0 && m >= 0) atomicMax(cmax + c, m);
+}
+
+// Smallest and largest column index of the matrix (create-time validation: a column outside
+// [0, ncols) would become an out-of-bounds gather of x in every kernel).
+__global__ void __launch_bounds__(256)
+col_range_kernel(const int32_t *__restrict__ col, int64_t nnz, int32_t *__restrict__ minmax) {
+  int32_t lo = INT32_MAX, hi = INT32_MIN;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < nnz; i += (int64_t)gridDim.x * blockDim.x) {
+    const int32_t c = col[i];
+    lo = min(lo, c);
+    hi = max(hi, c);
+  }
+  for (int o = 16; o; o >>= 1) {
+    lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, o));
+    hi = max(hi, __shfl_xor_sync(0xffffffffu, hi, o));
+  }
+  if ((threadIdx.x & 31) == 0) {
+    atomicMin(minmax + 0, lo);
+    atomicMax(minmax + 1, hi);
+  }
 }
 
 constexpr int kPipeChunks = 32;
@@ -574,6 +588,7 @@ hpcx_status pipe_analyse(hpcx_csr A) {
 // y(host) = A x(host): x pieces on the copy-in stream, row chunks on s as their columns land, y
 // chunks on the copy-out stream.  The caller synchronises s afterwards.
 hpcx_status spmv_host_pipelined(hpcx_csr A, const void *x, void *y, cudaStream_t s) {
+  HPCX_RANGE("spmv: host operands, chunks pipelined against PCIe");
   hpcx_ctx ctx = A->ctx;
   const int K = kPipeChunks;
   const size_t es = (size_t)A->es;
@@ -619,6 +634,7 @@ extern "C" {
 hpcx_status hpcx_csr_create(hpcx_ctx ctx, const hpcx_csr_desc *d, const hpcx_csr_opts *opts,
                             hpcx_csr *out) {
   if (!ctx || !out) return HPCX_INVALID_ARG;
+  HPCX_RANGE("hpcx_csr_create");
   *out = nullptr;
   HPCX_REQUIRE(ctx, d != nullptr, "null CSR descriptor");
   HPCX_REQUIRE(ctx, d->nrows >= 0 && d->ncols >= 0 && d->nnz >= 0, "negative CSR size");
@@ -640,7 +656,7 @@ hpcx_status hpcx_csr_create(hpcx_ctx ctx, const hpcx_csr_desc *d, const hpcx_csr
   A->kernel = opts && opts->kernel ? opts->kernel : HPCX_SPMV_STREAM;
   A->tile = opts && opts->tile_nnz ? opts->tile_nnz : 2048;
   A->lanes_per_row = opts ? opts->lanes_per_row : 0;
-  g_short_row_max = opts && opts->short_row_max > 0 ? opts->short_row_max : 48;
+  A->short_row_max = opts && opts->short_row_max > 0 ? opts->short_row_max : 48;
   A->sell_c = opts && opts->sell_c ? opts->sell_c : 32;
   A->sell_sigma = opts && opts->sell_sigma ? opts->sell_sigma : 1024;
   if (A->tile != 1024 && A->tile != 2048 && A->tile != 4096) {
@@ -725,10 +741,31 @@ hpcx_status hpcx_csr_create(hpcx_ctx ctx, const hpcx_csr_desc *d, const hpcx_csr
     HPCX_TRY_CUDA(cudaMemcpy(A->d_val, d->values, (size_t)d->nnz * A->es, cudaMemcpyDefault));
   }
 
+  if (d->nnz) {
+    // every column index must address x: one pass over the device copy
+    int32_t *d_mm = nullptr, mm[2] = {INT32_MAX, INT32_MIN};
+    HPCX_TRY_CUDA(cudaMalloc((void **)&d_mm, 8));
+    cudaError_t e = cudaMemcpy(d_mm, mm, 8, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) {
+      const int grid = (int)std::min<int64_t>((d->nnz + 255) / 256, (int64_t)ctx->sm_count * 16);
+      col_range_kernel<<<grid, 256>>>(A->d_col, d->nnz, d_mm);
+      ctx->launches++;
+      e = cudaMemcpy(mm, d_mm, 8, cudaMemcpyDeviceToHost);
+    }
+    cudaFree(d_mm);
+    HPCX_TRY_CUDA(e);
+    if (mm[0] < 0 || (int64_t)mm[1] >= d->ncols) {
+      free_csr(A);
+      return fail(ctx, HPCX_OUT_OF_RANGE,
+                  "col_idx outside [0, ncols): min " + std::to_string(mm[0]) + ", max " + std::to_string(mm[1]) +
+                      ", ncols " + std::to_string(d->ncols));
+    }
+  }
+
   // STREAM tables are always built (the distributed path and the bins use them).
   {
     std::vector<int32_t> long_row, long_off;
-    build_rowblocks(rp.data(), d->nrows, A->tile, nullptr, 0, A->h_blocks, &long_row, &long_off);
+    build_rowblocks(rp.data(), d->nrows, A->tile, A->short_row_max, nullptr, 0, A->h_blocks, &long_row, &long_off);
     A->nlong = (int64_t)long_row.size();
     HPCX_TRY(upload_vec(ctx, A->h_blocks, &A->d_blocks));
     HPCX_TRY(upload_vec(ctx, long_row, &A->d_long_row));
@@ -760,6 +797,9 @@ hpcx_status hpcx_csr_create(hpcx_ctx ctx, const hpcx_csr_desc *d, const hpcx_csr
     HPCX_TRY(upload_vec(ctx, A->h_slice_len, &A->d_slice_len));
     HPCX_TRY(upload_vec(ctx, A->h_slice_ptr, &A->d_slice_ptr));
   }
+  // the memsets and copies above ran on the legacy stream; the context's streams are
+  // non-blocking, so make everything visible before the first product is queued on them
+  HPCX_TRY_CUDA(cudaDeviceSynchronize());
   *out = A;
   return HPCX_OK;
 }
@@ -773,6 +813,7 @@ hpcx_status hpcx_csr_destroy(hpcx_csr A) {
 hpcx_status hpcx_spmv(hpcx_csr A, const void *x, int32_t x_mem, void *y, int32_t y_mem,
                       void *stream) {
   if (!A || !x || !y) return HPCX_INVALID_ARG;
+  HPCX_RANGE("hpcx_spmv");
   hpcx_ctx ctx = A->ctx;
   cudaStream_t s = stream ? (cudaStream_t)stream : ctx->compute;
   const void *dx = x;

@@ -23,7 +23,7 @@ struct hpcx_csr_s {
   hpcx_ctx ctx = nullptr;
   int64_t nrows = 0, ncols = 0, nnz = 0;
   int32_t dtype = HPCX_F64, es = 8, idx_bytes = 4;
-  int32_t kernel = HPCX_SPMV_STREAM, tile = 2048, lanes_per_row = 0;
+  int32_t kernel = HPCX_SPMV_STREAM, tile = 2048, lanes_per_row = 0, short_row_max = 48;
   // device CSR (row_ptr always int32 on the device; nnz < 2^31 is enforced at create)
   int32_t *d_row_ptr = nullptr;
   int32_t *d_col = nullptr;

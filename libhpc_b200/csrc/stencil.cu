@@ -17,8 +17,6 @@
 //                 warp shuffle, y halo rows from shared memory; the per-plane CTA barrier frees
 //                 the slot and thread 0 issues the next load (no producer warp).  Many short z
 //                 segments; the peer-store halo transport of dist.cu lives in the same kernel.
-//   jacobi7_tma   the same ring fed by a ninth, producer warp with full/empty mbarriers — the
-//                 earlier design, kept for A/B timing (HPCX_JACOBI_PRODUCER=1).
 //   jacobi7_tb2   two sweeps per pass over HBM (HPCX_VARIANT_TEMPORAL), bit-identical results.
 #include "grid.cuh"
 
@@ -216,11 +214,6 @@ jacobi7_direct_kernel(const T *__restrict__ in, T *__restrict__ out, GridGeom g,
   }
 }
 
-// ------------------------------------------------------------------ mbarrier extras
-__device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
-
 __device__ __forceinline__ void st_cs(float4 *p, float4 v) {
   asm volatile("st.global.cs.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(v.x), "f"(v.y),
                "f"(v.z), "f"(v.w)
@@ -228,9 +221,8 @@ __device__ __forceinline__ void st_cs(float4 *p, float4 v) {
 }
 
 // ------------------------------------------------------------------ Jacobi, TMA ring
-// Geometry shared by both ring kernels (the producer-warp kernel below adds a ninth warp and the
-// `empty` barriers).  Tile TX = 128 (one float4 per lane) by
-// TY = 16 rows (two adjacent rows per consumer warp), S ring slots of one plane box each.
+// Geometry of the ring kernel.  Tile TX = 128 (one float4 per lane) by TY = 16 rows (two adjacent
+// rows per warp), S ring slots of one plane box each.
 template <int S>
 struct JacobiCfg {
   static constexpr int TX = 128, TY = 16, HX = 4;      // HX: x halo staged on each side
@@ -240,9 +232,7 @@ struct JacobiCfg {
   static constexpr int kSlotBytes = (kPlaneBytes + 127) / 128 * 128;  // 9856
   static constexpr int kSlotFloats = kSlotBytes / 4;                 // slot stride in floats
   static constexpr int kBarOff = S * kSlotBytes;
-  static constexpr int kSmemBytes = kBarOff + 2 * S * 8;
-  static constexpr int kConsumerWarps = 8;
-  static constexpr int kThreads = (kConsumerWarps + 1) * 32;
+  static constexpr int kSmemBytes = kBarOff + S * 8;
 };
 
 // Work split (host planner jacobi_plan): the (x, y, z) space is cut into ntx * nty * zs CTAs of
@@ -253,210 +243,13 @@ struct JacobiCfg {
 struct JacobiSplit {
   int ntx, nty, zs;   // tiles along x, y; z segments
   int hmax;           // height of the taller y tiles (<= TY)
-  int down_last;      // the last z segment marches downwards (top plane first)
 };
 
-// Consumer side of the ring.  DOWN: planes arrive in descending z (plane j is z_first - j), so
-// the plane read before the centre is z+1 and the one after it z-1; the add order of the sum is
-// the same either way.
-template <int S, bool DOWN>
-__device__ __forceinline__ void jacobi7_consume(float *ring, uint64_t *full, uint64_t *empty,
-                                                float *__restrict__ out, const GridGeom &g,
-                                                const JacobiPeer &pr, int x0, int y0, int h,
-                                                int zfirst, int np, int tiles_xy, float sixth) {
-  using C = JacobiCfg<S>;
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  // Warp w owns tile rows 2w and 2w+1 (box rows 2w+1, 2w+2); lane owns x0 + 4*lane .. +3.
-  const int br = 2 * warp + 1;
-  const int col = C::HX + 4 * lane;
-  auto plane_ptr = [&](int j) { return ring + (j % S) * C::kSlotFloats; };
-  auto wait_full = [&](int j) { mbar_wait(full + (j % S), (j / S) & 1); };
-  auto release = [&](int j) {
-    __syncwarp();
-    if (lane == 0) mbar_arrive(empty + (j % S));
-  };
-  auto ld4 = [&](const float *pl, int row) {
-    return *reinterpret_cast<const float4 *>(pl + row * C::BX + col);
-  };
-
-  float4 pv0, pv1, zc0, zc1;  // plane j-1 and plane j of this thread's two rows
-  wait_full(0);
-  {
-    const float *pl = plane_ptr(0);
-    pv0 = ld4(pl, br);
-    pv1 = ld4(pl, br + 1);
-  }
-  release(0);
-  wait_full(1);
-  {
-    const float *pl = plane_ptr(1);
-    zc0 = ld4(pl, br);
-    zc1 = ld4(pl, br + 1);
-  }
-
-  const int gx = x0 + 4 * lane;
-  const int gy = y0 + 2 * warp;
-  const bool row0 = 2 * warp < h, row1 = 2 * warp + 1 < h;
-  const bool full4 = gx + 3 < g.n2;
-  const int64_t plane_stride = g.ext1 * g.pitch;
-  const int64_t inplane = (gy + g.glo1) * g.pitch + g.xoff + gx;  // offset inside a plane
-  const int dz = DOWN ? -1 : 1;
-  int z = zfirst + dz;  // first output plane
-  float *orow = out + gidx(g, z, gy, gx);
-
-  for (int j = 1; j <= np - 2; ++j, orow += dz * plane_stride, z += dz) {
-    wait_full(j + 1);
-    const float *pn = plane_ptr(j + 1);
-    const float *pc = plane_ptr(j);
-    const float4 nx0 = ld4(pn, br), nx1 = ld4(pn, br + 1);
-    const float4 up = ld4(pc, br - 1);    // y-1 of row 0
-    const float4 dn = ld4(pc, br + 2);    // y+1 of row 1
-    // x neighbours: shuffles inside the warp, staged halo columns at the two ends.
-    float l0 = __shfl_up_sync(0xffffffffu, zc0.w, 1);
-    float l1 = __shfl_up_sync(0xffffffffu, zc1.w, 1);
-    float r0 = __shfl_down_sync(0xffffffffu, zc0.x, 1);
-    float r1 = __shfl_down_sync(0xffffffffu, zc1.x, 1);
-    if (lane == 0) {
-      l0 = pc[br * C::BX + C::HX - 1];
-      l1 = pc[(br + 1) * C::BX + C::HX - 1];
-    }
-    if (lane == 31) {
-      r0 = pc[br * C::BX + C::HX + C::TX];
-      r1 = pc[(br + 1) * C::BX + C::HX + C::TX];
-    }
-    release(j);  // plane j is not read from shared memory again
-
-    const float4 &zm0 = DOWN ? nx0 : pv0, &zm1 = DOWN ? nx1 : pv1;
-    const float4 &zp0 = DOWN ? pv0 : nx0, &zp1 = DOWN ? pv1 : nx1;
-    float4 o0, o1;
-#define HPCX_J7(o, zm, ym, xm, xp, yp, zp) \
-  o = mul_rn(add_rn(add_rn(add_rn(add_rn(add_rn(zm, ym), xm), xp), yp), zp), sixth)
-    HPCX_J7(o0.x, zm0.x, up.x, l0, zc0.y, zc1.x, zp0.x);
-    HPCX_J7(o0.y, zm0.y, up.y, zc0.x, zc0.z, zc1.y, zp0.y);
-    HPCX_J7(o0.z, zm0.z, up.z, zc0.y, zc0.w, zc1.z, zp0.z);
-    HPCX_J7(o0.w, zm0.w, up.w, zc0.z, r0, zc1.w, zp0.w);
-    HPCX_J7(o1.x, zm1.x, zc0.x, l1, zc1.y, dn.x, zp1.x);
-    HPCX_J7(o1.y, zm1.y, zc0.y, zc1.x, zc1.z, dn.y, zp1.y);
-    HPCX_J7(o1.z, zm1.z, zc0.z, zc1.y, zc1.w, dn.z, zp1.z);
-    HPCX_J7(o1.w, zm1.w, zc0.w, zc1.z, r1, dn.w, zp1.w);
-#undef HPCX_J7
-
-    // Boundary plane of the slab: the same registers also go straight into the neighbour's
-    // ghost plane over NVLink (peer store), then one CTA per side publishes the sweep number.
-    float *peer0 = pr.ghost_lo && z == 0 ? pr.ghost_lo + inplane : nullptr;
-    float *peer1 = pr.ghost_hi && z == (int)g.n0 - 1 ? pr.ghost_hi + inplane : nullptr;
-    if (full4) {
-      if (row0) st_cs(reinterpret_cast<float4 *>(orow), o0);
-      if (row1) st_cs(reinterpret_cast<float4 *>(orow + g.pitch), o1);
-      if (peer0) {
-        if (row0) *reinterpret_cast<float4 *>(peer0) = o0;
-        if (row1) *reinterpret_cast<float4 *>(peer0 + g.pitch) = o1;
-      }
-      if (peer1) {
-        if (row0) *reinterpret_cast<float4 *>(peer1) = o0;
-        if (row1) *reinterpret_cast<float4 *>(peer1 + g.pitch) = o1;
-      }
-    } else {
-      const float a0[4] = {o0.x, o0.y, o0.z, o0.w}, a1[4] = {o1.x, o1.y, o1.z, o1.w};
-#pragma unroll
-      for (int k = 0; k < 4; ++k)
-        if (gx + k < g.n2) {
-          if (row0) orow[k] = a0[k];
-          if (row1) orow[g.pitch + k] = a1[k];
-          if (peer0 && row0) peer0[k] = a0[k];
-          if (peer0 && row1) peer0[g.pitch + k] = a1[k];
-          if (peer1 && row0) peer1[k] = a0[k];
-          if (peer1 && row1) peer1[g.pitch + k] = a1[k];
-        }
-    }
-    if (peer0 || peer1) {  // uniform over the CTA's consumer warps
-      __threadfence_system();
-      asm volatile("bar.sync 1, %0;" ::"n"(C::kConsumerWarps * 32) : "memory");
-      if (threadIdx.x == 0) {
-        if (peer0 && (atomicAdd(pr.counters + 0, 1u) + 1) % (uint32_t)tiles_xy == 0)
-          st_release_sys(pr.sig_lo, pr.sig_val);
-        if (peer1 && (atomicAdd(pr.counters + 1, 1u) + 1) % (uint32_t)tiles_xy == 0)
-          st_release_sys(pr.sig_hi, pr.sig_val);
-      }
-    }
-    pv0 = zc0;
-    pv1 = zc1;
-    zc0 = nx0;
-    zc1 = nx1;
-  }
-}
-
-template <int S>
-__global__ void __launch_bounds__(JacobiCfg<S>::kThreads, 3)
-jacobi7_tma_kernel(const __grid_constant__ CUtensorMap map_hi, const __grid_constant__ CUtensorMap map_lo,
-                   float *__restrict__ out, GridGeom g, JacobiSplit sp, JacobiPeer pr, int zbeg,
-                   int zend, float sixth) {
-  using C = JacobiCfg<S>;
-  extern __shared__ __align__(128) unsigned char smem[];
-  float *ring = reinterpret_cast<float *>(smem);
-  uint64_t *full = reinterpret_cast<uint64_t *>(smem + C::kBarOff);
-  uint64_t *empty = full + S;
-
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int bx = blockIdx.x % sp.ntx;
-  const int by = (blockIdx.x / sp.ntx) % sp.nty;
-  const int bz = blockIdx.x / (sp.ntx * sp.nty);
-  const int x0 = bx * C::TX;
-  const int y0 = (int)((int64_t)by * g.n1 / sp.nty);
-  const int h = (int)((int64_t)(by + 1) * g.n1 / sp.nty) - y0;  // rows of this tile
-  const int nzr = zend - zbeg;
-  const int z0 = zbeg + (int)((int64_t)bz * nzr / sp.zs);
-  const int z1 = zbeg + (int)((int64_t)(bz + 1) * nzr / sp.zs);
-  const int np = z1 - z0 + 2;  // planes z0-1 .. z1
-  if (h <= 0 || z1 <= z0) return;
-  const bool down = sp.down_last && sp.zs > 1 && bz == sp.zs - 1;
-  const int zfirst = down ? z1 : z0 - 1;  // first plane streamed
-
-  if (threadIdx.x == 0) {
-    for (int s = 0; s < S; ++s) {
-      mbar_init(full + s, 1);
-      mbar_init(empty + s, C::kConsumerWarps);
-    }
-    mbar_fence_init();
-  }
-  __syncthreads();
-
-  if (warp == C::kConsumerWarps) {
-    // ---------------------------------------------------------------- producer
-    if (lane == 0) {
-      const CUtensorMap *map = h == sp.hmax ? &map_hi : &map_lo;
-      tma_prefetch_desc(map);
-      const uint32_t bytes = (uint32_t)(C::BX * (h + 2) * 4);
-      const int c0 = (int)g.xoff + x0 - C::HX;
-      const int c1 = y0 + (int)g.glo1 - 1;
-      const int dz = down ? -1 : 1;
-      for (int j = 0; j < np; ++j) {
-        const int z = zfirst + dz * j;
-        // ghost planes filled by a neighbour: wait for its sweep number first
-        if (pr.wait_val) {
-          if (z == -1 && pr.sig_lo) wait_flag(pr.flags + 0, pr.wait_val, pr.counters + 2);
-          if (z == (int)g.n0 && pr.sig_hi) wait_flag(pr.flags + 1, pr.wait_val, pr.counters + 2);
-        }
-        const int slot = j % S, use = j / S;
-        if (use > 0) mbar_wait(empty + slot, (use - 1) & 1);
-        mbar_expect_tx(full + slot, bytes);
-        tma_load_3d(ring + slot * C::kSlotFloats, map, c0, c1, z + (int)g.glo0, full + slot);
-      }
-    }
-    return;
-  }
-
-  if (down)
-    jacobi7_consume<S, true>(ring, full, empty, out, g, pr, x0, y0, h, zfirst, np, sp.ntx * sp.nty, sixth);
-  else
-    jacobi7_consume<S, false>(ring, full, empty, out, g, pr, x0, y0, h, zfirst, np, sp.ntx * sp.nty, sixth);
-}
-
-// Single sweep without a producer warp (the default): the same ring, boxes, thread mapping and
-// peer-store halo transport as above, but the CTA's per-plane barrier — every warp has read
-// plane j out of shared memory — is what frees a slot, and thread 0 issues the next TMA load
-// right after it.  Eight warps instead of nine (register allocation is per four warps), no
-// "empty" mbarriers and no spinning producer competing for issue slots.
+// Single sweep.  There is no producer warp: the CTA's per-plane barrier — every warp has read
+// plane j out of shared memory — is what frees a ring slot, and thread 0 issues the next TMA
+// load right after it.  Eight warps (register allocation is per four warps), no "empty"
+// mbarriers and no spinning producer competing for issue slots (a nine-warp producer/consumer
+// version of this kernel measured 620 against 650 Gcell/s with the same split and was removed).
 template <int S>
 __global__ void __launch_bounds__(256, 3)
 jacobi7_ring_kernel(const __grid_constant__ CUtensorMap map_hi, const __grid_constant__ CUtensorMap map_lo,
@@ -490,8 +283,8 @@ jacobi7_ring_kernel(const __grid_constant__ CUtensorMap map_hi, const __grid_con
   auto issue = [&](int p) {  // plane p (z = z0 - 1 + p) -> slot p % S; thread 0 only
     if (pr.wait_val) {       // ghost planes filled by a neighbour: wait for its sweep number first
       const int z = z0 - 1 + p;
-      if (z == -1 && pr.sig_lo) wait_flag(pr.flags + 0, pr.wait_val, pr.counters + 2);
-      if (z == (int)g.n0 && pr.sig_hi) wait_flag(pr.flags + 1, pr.wait_val, pr.counters + 2);
+      if (z == -1 && pr.sig_lo) wait_flag(pr.flags + 0, pr.wait_val, pr.pw);
+      if (z == (int)g.n0 && pr.sig_hi) wait_flag(pr.flags + 1, pr.wait_val, pr.pw);
     }
     mbar_expect_tx(full + p % S, box_bytes);
     tma_load_3d(ring + (p % S) * C::kSlotFloats, map, c0, c1, z0 - 1 + p + (int)g.glo0, full + p % S);
@@ -713,15 +506,14 @@ constexpr int kJacobiStages = 6;
 
 // Equal-work split: minimise (CTAs per SM, rounded up, at least 3) x (cells one CTA loads).  `zsplit` > 0
 // pins the number of z segments (tests exercise short segments that way).
-JacobiSplit jacobi_plan(hpcx_ctx ctx, int64_t nx, int64_t ny, int64_t nz, int zsplit, bool down_last) {
+JacobiSplit jacobi_plan(hpcx_ctx ctx, int64_t nx, int64_t ny, int64_t nz, int zsplit) {
   using C = JacobiCfg<kJacobiStages>;
   const int64_t ntx = (nx + C::TX - 1) / C::TX;
   const int64_t nty_min = (ny + C::TY - 1) / C::TY;
-  JacobiSplit best{(int)ntx, (int)nty_min, 1, (int)((ny + nty_min - 1) / nty_min), 0};
+  JacobiSplit best{(int)ntx, (int)nty_min, 1, (int)((ny + nty_min - 1) / nty_min)};
   double best_cost = 1e300;
   const int64_t nty_max = std::min<int64_t>(ny, std::max<int64_t>(nty_min * 2, nty_min + 8));
-  // a downward-marching top segment needs a segment of its own
-  const int64_t zs_lo = zsplit > 0 ? std::min<int64_t>(zsplit, nz) : (down_last && nz >= 2 ? 2 : 1);
+  const int64_t zs_lo = zsplit > 0 ? std::min<int64_t>(zsplit, nz) : 1;
   const int64_t zs_hi = zsplit > 0 ? zs_lo : std::max<int64_t>(zs_lo, nz / 8);
   for (int64_t nty = nty_min; nty <= nty_max; ++nty) {
     const int64_t h = (ny + nty - 1) / nty;
@@ -735,11 +527,10 @@ JacobiSplit jacobi_plan(hpcx_ctx ctx, int64_t nx, int64_t ny, int64_t nz, int zs
       const double cost = (double)std::max<int64_t>(per_sm, 3) * (double)(h + 2) * (double)(zl + 2 + 3);
       if (cost < best_cost * (1.0 - 1e-9)) {
         best_cost = cost;
-        best = JacobiSplit{(int)ntx, (int)nty, (int)zs, (int)h, 0};
+        best = JacobiSplit{(int)ntx, (int)nty, (int)zs, (int)h};
       }
     }
   }
-  best.down_last = down_last && best.zs > 1 ? 1 : 0;
   return best;
 }
 
@@ -767,25 +558,14 @@ hpcx_status launch_jacobi_tma(hpcx_grid_s *g, void *src, void *dst, int zsplit, 
   using C = JacobiCfg<kJacobiStages>;
   hpcx_ctx ctx = g->ctx;
   const JacobiPeer pr = peer ? *peer : JacobiPeer{};
-  static int old_kernel = -1;  // HPCX_JACOBI_PRODUCER=1: the producer-warp kernel everywhere (A/B timing)
-  if (old_kernel < 0) {
-    const char *e = getenv("HPCX_JACOBI_PRODUCER");
-    old_kernel = e && atoi(e) ? 1 : 0;
-  }
-  const bool ring = !old_kernel && !ctx->force_jacobi_down;
-  // Producer-warp kernel only: the top segment marches downwards when its first plane feeds a
-  // neighbour (and under HPCX_JACOBI_DOWN=1, which lets single-GPU tests cover that path).  The
-  // ring kernel needs no such order: its top segment is short and runs in the last wave, right
-  // before the neighbour's next sweep asks for the plane.
-  const bool down = !ring && (pr.ghost_hi != nullptr || ctx->force_jacobi_down);
-  // The ring kernel on grids that do not fit L2 runs fastest with MANY short z segments (about
+  // On grids that do not fit L2 the kernel runs fastest with MANY short z segments (about
   // 8 planes: 512^3 648 Gcell/s with one wave of 444 CTAs, 808 with 64 segments = 18 waves,
   // profiles/r22_jacobi_zsplit.txt): short-lived CTAs drift out of lock-step, so the DRAM sees a
   // steady read/write mix, and a wave still covers whole planes, so the tile halos stay L2 hits.
   int zs_pin = zsplit;
-  if (ring && zsplit <= 0 && 2 * g->ext[0] * g->ext[1] * g->pitch * 4 > ctx->l2_bytes + ctx->l2_bytes / 2)
+  if (zsplit <= 0 && 2 * g->ext[0] * g->ext[1] * g->pitch * 4 > ctx->l2_bytes + ctx->l2_bytes / 2)
     zs_pin = (int)std::max<int64_t>(1, (zend - zbeg + 7) / 8);
-  const JacobiSplit sp = jacobi_plan(ctx, g->n[2], g->n[1], zend - zbeg, zs_pin, down);
+  const JacobiSplit sp = jacobi_plan(ctx, g->n[2], g->n[1], zend - zbeg, zs_pin);
   hpcx_status st = HPCX_OK;
   const CUtensorMap *hi = jacobi_map(g, src, sp.hmax + 2, &st);
   if (!hi) return st;
@@ -793,28 +573,12 @@ hpcx_status launch_jacobi_tma(hpcx_grid_s *g, void *src, void *dst, int zsplit, 
   if (!lo) return st;
   // `hi` may have moved if the cache reallocated: fetch it again (cheap, by key).
   hi = jacobi_map(g, src, sp.hmax + 2, &st);
-  static bool configured = false;
-  if (!configured) {
-    HPCX_CUDA(ctx, cudaFuncSetAttribute(jacobi7_tma_kernel<kJacobiStages>,
-                                        cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                        C::kSmemBytes));
-    configured = true;
-  }
+  st = ensure_dyn_smem(ctx, (const void *)jacobi7_ring_kernel<kJacobiStages>, C::kSmemBytes);
+  if (st != HPCX_OK) return st;
   const unsigned ncta = (unsigned)(sp.ntx * sp.nty * sp.zs);
-  static bool ring_configured = false;
-  if (!ring_configured) {
-    ring_configured = true;
-    HPCX_CUDA(ctx, cudaFuncSetAttribute(jacobi7_ring_kernel<kJacobiStages>,
-                                        cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
-  }
-  if (ring) {
-    jacobi7_ring_kernel<kJacobiStages><<<ncta, 256, C::kSmemBytes, s>>>(
-        *hi, *lo, (float *)dst, geom_of(g), sp, pr, (int)zbeg, (int)zend, 1.0f / 6.0f);
-    return after_launch(ctx, "jacobi7_ring_kernel");
-  }
-  jacobi7_tma_kernel<kJacobiStages><<<ncta, C::kThreads, C::kSmemBytes, s>>>(
+  jacobi7_ring_kernel<kJacobiStages><<<ncta, 256, C::kSmemBytes, s>>>(
       *hi, *lo, (float *)dst, geom_of(g), sp, pr, (int)zbeg, (int)zend, 1.0f / 6.0f);
-  return after_launch(ctx, "jacobi7_tma_kernel");
+  return after_launch(ctx, "jacobi7_ring_kernel");
 }
 
 
@@ -864,9 +628,7 @@ struct JacobiTBSplit {
 #define HPCX_J7(zm, ym, xm, xp, yp, zp) \
   mul_rn(add_rn(add_rn(add_rn(add_rn(add_rn(zm, ym), xm), xp), yp), zp), sixth)
 
-// EXP: timing experiments only (HPCX_TB_EXP, results are wrong when non-zero): 1 = no stage B,
-// 4 = no global stores, 8 = no edge columns.
-template <int EXP, int S_>
+template <int S_>
 __global__ void __launch_bounds__(256, S_ <= 5 ? 3 : 2)
 jacobi7_tb2_kernel(const __grid_constant__ CUtensorMap map_hi, const __grid_constant__ CUtensorMap map_lo,
                    float *__restrict__ out, GridGeom g, JacobiTBSplit sp, float sixth) {
@@ -985,7 +747,7 @@ jacobi7_tb2_kernel(const __grid_constant__ CUtensorMap map_hi, const __grid_cons
     aN.b.y = HPCX_J7(P.b.y, Cn.a.y, Cn.b.x, Cn.b.z, dn.y, N.b.y);
     aN.b.z = HPCX_J7(P.b.z, Cn.a.z, Cn.b.y, Cn.b.w, dn.z, N.b.z);
     aN.b.w = HPCX_J7(P.b.w, Cn.a.w, Cn.b.z, r1, dn.w, N.b.w);
-    float aE = (EXP & 8) ? Cn.e : HPCX_J7(P.e, eup, elf, ert, edn, N.e);
+    float aE = HPCX_J7(P.e, eup, elf, ert, edn, N.e);
     if (z < sp.zlo || z >= sp.zhi) {  // ghost plane of the domain (uniform over the CTA)
       aN.a = Cn.a;
       aN.b = Cn.b;
@@ -1003,7 +765,7 @@ jacobi7_tb2_kernel(const __grid_constant__ CUtensorMap map_hi, const __grid_cons
     }
 
     // ---- B: iterate t+2 of plane z-1 from the t+1 planes z-2 (aP), z-1 (aC), z (aN)
-    if (j >= 3 && !(EXP & 1)) {
+    if (j >= 3) {
       const float *ac = abuf + ((j - 1) & 1) * C::kAPlaneFloats + C::BX;
       const float4 bup = *reinterpret_cast<const float4 *>(ac + a0off - C::BX);
       const float4 bdn = *reinterpret_cast<const float4 *>(ac + a0off + 2 * C::BX);
@@ -1028,9 +790,7 @@ jacobi7_tb2_kernel(const __grid_constant__ CUtensorMap map_hi, const __grid_cons
       o1.y = HPCX_J7(aP.b.y, aC.a.y, aC.b.x, aC.b.z, bdn.y, aN.b.y);
       o1.z = HPCX_J7(aP.b.z, aC.a.z, aC.b.y, aC.b.w, bdn.z, aN.b.z);
       o1.w = HPCX_J7(aP.b.w, aC.a.w, aC.b.z, br1, bdn.w, aN.b.w);
-      if (EXP & 4) {
-        if (o0.x == 123.456f && o1.y == 3.f) orow[0] = o0.y;
-      } else if (!xragged) {
+      if (!xragged) {
         if (orow0) st_cs(reinterpret_cast<float4 *>(orow), o0);
         if (orow1) st_cs(reinterpret_cast<float4 *>(orow + g.pitch), o1);
       } else {
@@ -1127,14 +887,10 @@ hpcx_status launch_jacobi_tb2(hpcx_grid_s *g, void *src, void *dst, int zsplit, 
   const CUtensorMap *lo = jacobi_map(g, src, sp.hmax + 3, &st);
   if (!lo) return st;
   hi = jacobi_map(g, src, sp.hmax + 4, &st);  // may have moved if the cache reallocated
-  static bool configured = false;
-  if (!configured) {
-    configured = true;
-    HPCX_CUDA(ctx, cudaFuncSetAttribute(jacobi7_tb2_kernel<0, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                        C::kSmemBytes));
-  }
+  st = ensure_dyn_smem(ctx, (const void *)jacobi7_tb2_kernel<8>, C::kSmemBytes);
+  if (st != HPCX_OK) return st;
   const unsigned ncta = (unsigned)(sp.ntx * sp.nty * (sp.zs + (zend2 > zbeg2 ? 1 : 0)));
-  jacobi7_tb2_kernel<0, 8><<<ncta, 256, C::kSmemBytes, s>>>(*hi, *lo, (float *)dst, geom_of(g), sp, 1.0f / 6.0f);
+  jacobi7_tb2_kernel<8><<<ncta, 256, C::kSmemBytes, s>>>(*hi, *lo, (float *)dst, geom_of(g), sp, 1.0f / 6.0f);
   return after_launch(ctx, "jacobi7_tb2_kernel");
 }
 
@@ -1177,6 +933,7 @@ hpcx_status jacobi7_tb2_launch(hpcx_grid_s *g, void *src, void *dst, int zsplit,
 extern "C" hpcx_status hpcx_stencil_sweep(hpcx_grid in, hpcx_grid out, const hpcx_stencil_desc *st,
                                           int32_t steps, void *stream) {
   if (!in || !out || !st) return HPCX_INVALID_ARG;
+  HPCX_RANGE("hpcx_stencil_sweep");
   hpcx_ctx ctx = in->ctx;
   hpcx_status rc = check_same_shape(in, out);
   if (rc != HPCX_OK) return rc;

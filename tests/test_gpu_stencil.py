@@ -136,16 +136,6 @@ def test_jacobi7_zsplit(ctx, zsplit):
         assert bits_equal(newest, oracle.jacobi7(f, *dims, 1, 1, 3))
 
 
-def test_jacobi7_downward_top_segment():
-    """The marching direction the peer-store transport uses for the top z segment."""
-    import subprocess
-    import sys
-    script = os.path.join(os.path.dirname(__file__), "jacobi_down_check.py")
-    p = subprocess.run([sys.executable, script], capture_output=True, text=True, timeout=600,
-                       env=dict(os.environ, HPCX_JACOBI_DOWN="1"))
-    assert p.returncode == 0 and "DOWN OK" in p.stdout, p.stdout[-2000:] + p.stderr[-4000:]
-
-
 def test_jacobi7_fp64(ctx):
     dims = (9, 10, 70)
     f = oracle.fill(11 * 12 * 72, 9, np.float64)
