@@ -7,7 +7,8 @@ Workload (config.workload): configs[1] of BASELINE.json — CSR SpMV y = A*x, fp
 2-D 5-point Laplacian of an 8192 x 8192 grid (67.1 M rows, 335.5 M nnz) per GPU.  At N > 1
 the grid grows to (8192*N) x 8192 and is row-partitioned into N slabs (weak scaling); each
 product exchanges one grid row of x (8192 doubles) with each neighbour through
-hpcx_spmv_dist (NCCL send/recv on the library's comm stream, overlapped with interior rows).
+hpcx_spmv_dist (fused transport: boundary x entries pushed by peer stores over NVLink; the
+NCCL send/recv transport is timed beside it as an extra).
 
 A step is one product.  `value` = effective GB/s = algorithmic bytes (12 B/nnz + 20 B/row,
 SURVEY.md §8d) of all ranks / max-over-ranks device time, operands resident in HBM.
@@ -15,8 +16,17 @@ SURVEY.md §8d) of all ranks / max-over-ranks device time, operands resident in 
 y: H2D of x and D2H of y inside the timed region, matrix resident as in any iterative use).
 The matrix (4.3 GB) is far larger than L2 (126 MB), so no explicit flush is needed.
 
---impl reference times the CPU restatement of the path (oracle/, OpenMP, all host threads)
-on the same matrix: the reference itself has no SpMV, so kind = "port".
+--impl reference times the CPU restatement of the path (oracle/, OpenMP, every core of the
+affinity mask whatever OMP_NUM_THREADS says) on the same GLOBAL matrix (N slabs at --gpus N): the
+reference itself has no SpMV, so kind = "port".
+
+The stencil half of the metric (Jacobi 512^3, R0 box sweeps) is in `extra` and, compactly, in the
+LAST key of the line (`stencil`), each with its own cpu_baseline (the reference's own loops for R0,
+kind "reference"; the Jacobi restatement, kind "port") and e2e (host array in, host array out).
+At N > 1 the line carries `dist_parity`: before anything is timed, small distributed Jacobi
+problems run through both transports and the temporal variant and every rank compares its slab
+bit-for-bit with the single-GPU sweep of the same global field; the timed distributed SpMV is
+checked against closed forms (A*1 and A*linear field) that a stale halo cannot satisfy.
 """
 from __future__ import annotations
 
@@ -105,6 +115,7 @@ def cpu_spmv_baseline(L: dict, x: np.ndarray, budget_s: float = 12.0, min_reps: 
     and sum rounded separately) timed on this box's host cores on the SAME matrix.
     This is the one place bench.py executes oracle/: as the measured CPU baseline."""
     import oracle
+    host_threads()
     rp, col, val = L["local_row_ptr"], L["local_col"], np.ascontiguousarray(L["values"])
     xfull = np.zeros(L["nloc"] + L["nhalo"])
     xfull[:L["nloc"]] = x
@@ -120,36 +131,57 @@ def cpu_spmv_baseline(L: dict, x: np.ndarray, budget_s: float = 12.0, min_reps: 
 
 
 def host_threads() -> int:
-    n = len(os.sched_getaffinity(0))
-    env = os.environ.get("OMP_NUM_THREADS")
-    return min(n, int(env)) if env and env.isdigit() else n
+    """OpenMP team of the CPU legs: every core of the affinity mask.  Launchers export
+    OMP_NUM_THREADS=1 (torch.distributed.run does), so the count is set explicitly."""
+    import oracle
+    return oracle.set_threads()
+
+
+def mem_available_bytes() -> int:
+    try:
+        for line in open("/proc/meminfo"):
+            if line.startswith("MemAvailable:"):
+                return int(line.split()[1]) * 1024
+    except OSError:
+        pass
+    return 1 << 62
 
 
 def run_reference(args, rank: int, world: int):
-    """--impl reference: the CPU path on the host cores, rank 0 only."""
+    """--impl reference: the CPU path on the host cores, rank 0 only, on the SAME global problem as
+    our arm at this N (an (8192*N) x 8192 grid = N slabs), all host cores."""
     if rank != 0:
         return
-    L = build_local_problem(1, 0)
-    from libhpc_b200 import synth
-    x = synth.field(42, L["nloc"])
     import oracle
-    rp, col, val = L["local_row_ptr"], L["local_col"], np.ascontiguousarray(L["values"])
-    y = np.empty(L["nloc"])
+    cores = host_threads()
+    rows_slab, nnz_slab = GRID * GRID, 5 * GRID * GRID - 2 * GRID  # upper bound per slab
+    need = world * (nnz_slab * 12 + rows_slab * 24)
+    slabs = world
+    avail = mem_available_bytes()
+    if need * 1.2 > avail:  # bounded sample: as many slabs as the host memory holds
+        slabs = max(1, int(world * avail / (need * 1.2)))
+    t = time.time()
+    rp, col, val = oracle.laplace2d(GRID * slabs, GRID)  # int64 row_ptr: nnz exceeds 2^31 from 7 slabs on
+    n, nnz = len(rp) - 1, len(col)
+    x = oracle.fill(n, 42)
+    y = np.empty(n)
+    log(f"[reference] built {slabs}-slab matrix ({n} rows, {nnz} nnz) in {time.time() - t:.1f}s, {cores} threads")
     for _ in range(max(args.warmup, 1)):
         oracle.spmv(rp, col, val, x, out=y)
     t0 = time.perf_counter()
     for _ in range(args.steps):
         oracle.spmv(rp, col, val, x, out=y)
     dt = time.perf_counter() - t0
-    nbytes = algorithmic_bytes(L["nloc"], L["nnz_loc"])
+    nbytes = algorithmic_bytes(n, nnz)
     gbs = nbytes * args.steps / dt / 1e9
-    cores = host_threads()
-    sample = f"full configs[1] matrix ({L['nloc']} rows, {L['nnz_loc']} nnz), {args.steps} products"
+    sample = (f"the full {world}-slab global matrix of our arm's config ({n} rows, {nnz} nnz), {args.steps} products"
+              if slabs == world else
+              f"{slabs} of {world} slabs ({n} rows, {nnz} nnz: what host memory holds), {args.steps} products")
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": gbs, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
-        "data": "synthetic", "config": workload_config(1),
+        "data": "synthetic", "config": workload_config(world), "same_config": slabs == world,
         "cpu_baseline": {"value": gbs, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample,
                          "note": "the reference has no SpMV (SURVEY.md §0); this is the OpenMP CPU "
                                  "restatement in oracle/hpcx_oracle.c"},
@@ -184,6 +216,66 @@ def time_steps(torch, stream, step, steps: int, barrier):
     return e0.elapsed_time(e1) * 1e-3, w0, w1
 
 
+def dist_parity_check(ctx, torch, dist, world, rank, hp, hd, synth):
+    """N > 1, before anything is timed: a (16*N) x 64 x 256 Jacobi problem through the NCCL
+    transport, the fused peer-store transport and the two-sweeps-per-pass variant over both; every
+    rank compares its slab BIT FOR BIT with the single-GPU hpcx_stencil_sweep of the same global
+    field on its own GPU (product vs product: the single-GPU kernel is what the oracle-checked
+    GPU tests cover).  Any mismatch on any rank ends the run non-zero."""
+    nz, ny, nx = 16 * world, 64, 256
+    cases = ((1, hp.VARIANT_TMA, 0, 5, "one_sweep_nccl"), (1, hp.VARIANT_TMA, 1, 6, "one_sweep_peer"),
+             (2, hp.VARIANT_TEMPORAL, 0, 6, "temporal_nccl"), (2, hp.VARIANT_TEMPORAL, 1, 5, "temporal_peer"))
+    verdict = {}
+    for gw, variant, transport, steps, name in cases:
+        ext = (nz + 2 * gw, ny + 2 * gw, nx + 2 * gw)
+        full = synth.field(7, ext[0] * ext[1] * ext[2], np.float32)
+        ga, gb = hp.DeviceGrid(ctx, (nz, ny, nx), np.float32, gw), hp.DeviceGrid(ctx, (nz, ny, nx), np.float32, gw)
+        ga.upload(full)
+        gb.upload(full)
+        hp.stencil_sweep(ga, gb, hp.STENCIL_JACOBI7, steps=steps, variant=hp.VARIANT_TMA)
+        want = gb.download().reshape(ext)
+        ga.destroy()
+        gb.destroy()
+        b = hp.partition_slabs(nz, world)
+        z0, z1 = int(b[rank]), int(b[rank + 1])
+        slab = np.ascontiguousarray(full.reshape(ext)[z0:z1 + 2 * gw]).ravel()
+        sa, sb = (hp.DeviceGrid(ctx, (z1 - z0, ny, nx), np.float32, gw) for _ in range(2))
+        sa.upload(slab)
+        sb.upload(slab)
+        plan = hd.HaloPlan(ctx, sa, sb, hp.STENCIL_JACOBI7, variant, transport=transport)
+        plan.sweep(steps)
+        out = sb.download().reshape(z1 - z0 + 2 * gw, ext[1], ext[2])
+        same = np.array_equal(np.ascontiguousarray(out[gw:-gw, gw:-gw, gw:-gw]).view(np.uint32),
+                              np.ascontiguousarray(want[z0 + gw:z1 + gw, gw:-gw, gw:-gw]).view(np.uint32))
+        plan.destroy()
+        sa.destroy()
+        sb.destroy()
+        t = torch.tensor([1.0 if same else 0.0], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MIN)
+        verdict[name] = "ok" if float(t.item()) == 1.0 else "MISMATCH"
+    if any(v != "ok" for v in verdict.values()):
+        raise SystemExit(f"[rank {rank}] bench.py: distributed Jacobi differs from the single-GPU sweep: {verdict}")
+    return verdict
+
+
+def laplacian_of_linear(torch, rank: int, world: int):
+    """x = f and the exact A*f of the (8192*world) x 8192 5-point Laplacian on this rank's slab for
+    f(Y, X) = 3Y + 5X + 1 (small integers: every product and partial sum is exact in fp64, so the
+    result is order-independent).  Zero in the interior, the missing neighbours' values on the
+    domain boundary — a stale or misplaced halo entry cannot reproduce it."""
+    Y = torch.arange(rank * GRID, (rank + 1) * GRID, dtype=torch.float64, device="cuda")[:, None]
+    X = torch.arange(GRID, dtype=torch.float64, device="cuda")[None, :]
+    f = 3.0 * Y + 5.0 * X + 1.0
+    want = torch.zeros_like(f)
+    want[:, 0] += f[:, 0] - 5.0   # missing left neighbour f(Y, -1) would have cancelled: add it back
+    want[:, -1] += f[:, -1] + 5.0
+    if rank == 0:
+        want[0] += f[0] - 3.0
+    if rank == world - 1:
+        want[-1] += f[-1] + 3.0
+    return f.reshape(-1), want.reshape(-1)
+
+
 def run_ours(args, rank: int, world: int, local: int):
     import torch
     import torch.distributed as dist
@@ -212,15 +304,26 @@ def run_ours(args, rank: int, world: int, local: int):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
+    dist_parity = None
+    if world > 1:
+        dist_parity = dist_parity_check(ctx, torch, dist, world, rank, hp, hd, synth)
+        log(f"[rank {rank}] dist_parity {dist_parity}")
+
+    t = time.time()
     L = build_local_problem(world, rank)
+    build_s = time.time() - t
     nloc, nnz = L["nloc"], L["nnz_loc"]
     A = hp.CsrMatrix(L["local_row_ptr"], L["local_col"], L["values"], ncols=nloc + L["nhalo"])
     t = time.time()
     D = hp.DeviceCsr(ctx, A)
+    create_s = time.time() - t
     if world > 1:
         D.set_halo(L)
         D.halo_transport(1)  # fused gather + peer stores + flags (NCCL variant timed below as extra)
-    log(f"[rank {rank}] hpcx_csr_create {time.time() - t:.1f}s")
+    halo_s = time.time() - t - create_s
+    log(f"[rank {rank}] hpcx_csr_create {create_s:.2f}s, halo tables {halo_s:.2f}s")
+    setup_ms = {"hpcx_csr_create": max_over_ranks(create_s) * 1e3, "halo_tables": max_over_ranks(halo_s) * 1e3,
+                "host_matrix_build_python": max_over_ranks(build_s) * 1e3}
 
     stream = torch.cuda.Stream()
     x_pin = torch.empty(nloc, dtype=torch.float64).pin_memory()
@@ -272,7 +375,23 @@ def run_ours(args, rank: int, world: int, local: int):
         expect[-1] += 1
     if not torch.equal(yv, expect):
         raise SystemExit(f"[rank {rank}] bench.py: A*1 does not match the closed form")
+    del ones, expect
+    # ... and A*f for a linear field f: the halo entries must be the neighbours' CURRENT values
+    f, want = laplacian_of_linear(torch, rank, world)
+    torch.cuda.synchronize()
+    if world == 1:
+        D.spmv(f, yd, stream)
+    else:
+        ctx.memcpy((xfull, hp.MEM_DEVICE), f, nloc * 8)
+        barrier()
+        D.spmv_dist(x_arg, yd, stream)
+    stream.synchronize()
+    if not torch.equal(yd, want):
+        raise SystemExit(f"[rank {rank}] bench.py: A*(linear field) does not match the closed form")
+    del f, want
+    spmv_check = "A*1 and A*(3Y+5X+1) equal their closed forms on every rank (exact in fp64)"
     if world > 1:
+        barrier()
         ctx.memcpy((xfull, hp.MEM_DEVICE), xd, nloc * 8)
 
     # ---- end to end: host x in, host y out, every step
@@ -294,10 +413,12 @@ def run_ours(args, rank: int, world: int, local: int):
     e2e_value = nbytes_rank * world * k_e2e / dt_e2e / 1e9
     checksum = float(np.abs(y_pin.numpy()).sum())
 
-    extra = stencil_extra(ctx, torch, stream, world, rank, barrier, max_over_ranks, hp, hd, synth)
+    extra, stencil = stencil_extra(args, ctx, torch, stream, world, rank, barrier, max_over_ranks, hp, hd, synth)
     extra["cg_iteration_c2_fp64"] = cg_extra(args, ctx, torch, stream, world, barrier, max_over_ranks, hp, D,
                                              nloc, nnz, xd)
     if args.configs == "all":
+        if world == 1:
+            extra["c1_laplace_1024sq_fp64"] = c1_extra(args, ctx, torch, stream, barrier, hp, synth)
         extra.update(sparse_extra(args, ctx, torch, stream, world, rank, barrier, max_over_ranks, hp, hd, synth))
     if world > 1:
         # the same product with the NCCL send/recv exchange, for comparison
@@ -345,7 +466,11 @@ def run_ours(args, rank: int, world: int, local: int):
                     "ms_per_step": dt_e2e / k_e2e * 1e3,
                     "call": "hpcx_spmv(A, x HOST, y HOST)" if world == 1 else
                             "pinned H2D + hpcx_spmv_dist + D2H per rank"},
-            "gpu_launches": launches, "clocks": clocks, "checksum": checksum, "extra": extra,
+            "gpu_launches": launches, "clocks": clocks, "checksum": checksum, "setup_ms": setup_ms,
+            "spmv_check": spmv_check, "dist_parity": dist_parity if world > 1 else "n/a (one GPU)",
+            "extra": extra,
+            # last key on purpose: the stencil half of BASELINE.json's metric survives a truncated tail
+            "stencil": stencil,
         }), flush=True)
     D.destroy()
     ctx.close()
@@ -353,22 +478,45 @@ def run_ours(args, rank: int, world: int, local: int):
         dist.destroy_process_group()
 
 
-def stencil_extra(ctx, torch, stream, world, rank, barrier, max_over_ranks, hp, hd, synth):
+def stencil_extra(args, ctx, torch, stream, world, rank, barrier, max_over_ranks, hp, hd, synth):
     """Second half of BASELINE.json's metric: stencil Gcell-updates/s.
     configs[2]: 3-D 7-point Jacobi, 512^3 fp32 per GPU (z-slabs of a 512*N x 512 x 512 domain at
     N > 1, ghost planes exchanged every sweep), 8 B/cell algorithmic; and at N = 1 the
-    reference-native 17-point box sweeps on 8192^2 fp32 (R0)."""
-    out = {}
+    reference-native 17-point box sweeps on 8192^2 fp32 (R0), each with a cpu_baseline (the
+    reference's own loops for R0, the restatement for Jacobi) and an e2e leg (host array in, host
+    array out through hpcx_grid_upload / hpcx_stencil_sweep / hpcx_grid_download).
+    Returns (detailed entries for `extra`, compact summary for the line's last key)."""
+    out, summary = {}, {"unit": "Gcell-updates/s", "n_gpus": world}
     n, T = 512, 50
     peak, _ = measured_peak()
+
+    def entry(cells_all_ranks, dt, launches=None, **kw):
+        per_rank_gbs = cells_all_ranks * 8 / world / dt / 1e9
+        e = {"metric": "stencil_Gcell_updates_per_s", "value": cells_all_ranks / dt / 1e9,
+             "roofline": {"bound": "hbm", "achieved": per_rank_gbs, "peak": peak, "unit": "GB/s",
+                          "frac": per_rank_gbs / peak, "algorithmic_bytes_per_cell": 8}}
+        if launches is not None:
+            e["gpu_launches"] = launches
+        e.update(kw)
+        return e
+
+    def timed(step, reps=2):
+        with torch.cuda.stream(stream):
+            step()
+            n0 = ctx.launch_count()
+            dt, _, _ = time_steps(torch, stream, step, reps, barrier)
+            launches = ctx.launch_count() - n0
+        return max_over_ranks(dt), launches
+
     f = synth.field(7, (n + 2) ** 3, np.float32, first=rank * (n + 2) ** 3)
     ga, gb = hp.DeviceGrid(ctx, (n, n, n), np.float32, 1), hp.DeviceGrid(ctx, (n, n, n), np.float32, 1)
     ga.upload(f)
     gb.upload(f)
-    del f
     # N > 1: transport 1 = fused peer stores (one kernel per sweep), transport 0 = NCCL send/recv
     plans = {"tma": hd.HaloPlan(ctx, ga, gb, hp.STENCIL_JACOBI7, hp.VARIANT_TMA, transport=1),
              "tma_nccl": hd.HaloPlan(ctx, ga, gb, hp.STENCIL_JACOBI7, hp.VARIANT_TMA, transport=0)} if world > 1 else {}
+    note2 = ("two sweeps per pass over HBM (HPCX_VARIANT_TEMPORAL): the 8 B/cell/sweep figure is kept as the "
+             "algorithmic unit, the kernel moves 4 B/cell/sweep, so frac may exceed 1")
     for variant, name in ((hp.VARIANT_TMA, "tma"), (hp.VARIANT_TMA, "tma_nccl"), (hp.VARIANT_DIRECT, "direct"),
                           (hp.VARIANT_TEMPORAL, "temporal")):
         if (world > 1) != (name in plans) or (world == 1 and name == "tma_nccl"):
@@ -379,30 +527,64 @@ def stencil_extra(ctx, torch, stream, world, rank, barrier, max_over_ranks, hp, 
         else:
             step = lambda: hp.stencil_sweep(ga, gb, hp.STENCIL_JACOBI7, steps=T, variant=variant,  # noqa: E731
                                             stream=stream)
-        with torch.cuda.stream(stream):
-            step()
-            n0 = ctx.launch_count()
-            dt, _, _ = time_steps(torch, stream, step, 2, barrier)
-            launches = ctx.launch_count() - n0
-        dt = max_over_ranks(dt)
+        dt, launches = timed(step)
         cells = n ** 3 * world * T * 2
-        out[f"jacobi7_512cubed_fp32_{name}"] = {
-            "metric": "stencil_Gcell_updates_per_s", "value": cells / dt / 1e9, "sweeps": 2 * T,
-            "ms_per_sweep": dt / (2 * T) * 1e3, "gpu_launches": launches,
-            "transport": {"tma": "peer stores + flags (fused)", "tma_nccl": "NCCL send/recv"}.get(name) if world > 1 else None,
-            "roofline": {"bound": "hbm", "achieved": cells * 8 / world / dt / 1e9, "peak": peak,
-                         "unit": "GB/s", "frac": cells * 8 / world / dt / 1e9 / peak,
-                         "algorithmic_bytes_per_cell": 8}}
+        e = entry(cells, dt, launches, sweeps=2 * T, ms_per_sweep=dt / (2 * T) * 1e3,
+                  transport={"tma": "peer stores + flags (fused)", "tma_nccl": "NCCL send/recv"}.get(name) if world > 1 else None)
         if name == "temporal":
-            out[f"jacobi7_512cubed_fp32_{name}"]["roofline"]["note"] = (
-                "two sweeps per pass over HBM (HPCX_VARIANT_TEMPORAL): the 8 B/cell/sweep figure is kept as the "
-                "algorithmic unit, the kernel moves 4 B/cell/sweep, so frac may exceed 1")
+            e["roofline"]["note"] = note2
+        out[f"jacobi7_512cubed_fp32_{name}"] = e
+        summary["jacobi7_512c_" + {"tma": "1sweep" if world == 1 else "1sweep_peer", "tma_nccl": "1sweep_nccl",
+                                   "direct": "direct", "temporal": "2sweep"}[name]] = round(e["value"], 1)
+        if name == "tma":
+            summary["jacobi7_frac_of_hbm"] = round(e["roofline"]["frac"], 4)
     for plan in plans.values():
         plan.destroy()
+
+    if world == 1 and rank == 0:
+        # ---- e2e: host array in, host array out, every step (one sweep per step: the worst case for
+        # the copies; an iterative caller amortises them over its T sweeps)
+        host_in = ctx.pinned(((n + 2) ** 3,), np.float32)
+        host_out = ctx.pinned(((n + 2) ** 3,), np.float32)
+        host_in[:] = f
+
+        def j_e2e():
+            ga.upload(host_in, stream)
+            hp.stencil_sweep(ga, gb, hp.STENCIL_JACOBI7, steps=1, variant=hp.VARIANT_TMA, stream=stream)
+            gb.download(host_out, stream)
+            stream.synchronize()
+        dt, _ = timed(j_e2e, 5)
+        out["jacobi7_512cubed_fp32_tma"]["e2e"] = {
+            "value": n ** 3 * 5 / dt / 1e9, "unit": "Gcell-updates/s", "ms_per_step": dt / 5 * 1e3,
+            "h2d_bytes_per_step": host_in.nbytes, "d2h_bytes_per_step": host_out.nbytes,
+            "call": "hpcx_grid_upload(pinned) + hpcx_stencil_sweep(1 sweep) + hpcx_grid_download(pinned)"}
+        summary["jacobi7_e2e_1sweep_per_copy"] = round(n ** 3 * 5 / dt / 1e9, 2)
+        if not args.no_cpu:
+            # ---- cpu_baseline (kind "port": the reference has no 3-D stencil): orc_jacobi7_f32, all cores
+            import oracle
+            cores = host_threads()
+            src = np.array(host_in)
+            dst = src.copy()
+            lib = oracle.lib()
+            import ctypes as C
+            call = lambda: lib.orc_jacobi7_f32(src.ctypes.data_as(C.c_void_p), dst.ctypes.data_as(C.c_void_p),  # noqa: E731
+                                               C.c_int64(n), C.c_int64(n), C.c_int64(n), C.c_int64(1), C.c_int64(1))
+            call()
+            ts = []
+            while len(ts) < 3 or (sum(ts) < 6.0 and len(ts) < 12):
+                t0 = time.perf_counter()
+                call()
+                ts.append(time.perf_counter() - t0)
+            out["jacobi7_512cubed_fp32_tma"]["cpu_baseline"] = {
+                "value": n ** 3 / min(ts) / 1e9, "unit": "Gcell-updates/s", "cores": cores, "kind": "port",
+                "sample": f"full 512^3 sweep, best of {len(ts)} after 1 warm-up (oracle/hpcx_oracle.c:orc_jacobi7_f32)"}
+            summary["jacobi7_cpu"] = {"value": round(n ** 3 / min(ts) / 1e9, 3), "cores": cores, "kind": "port"}
+            del src, dst
+    del f
     ga.destroy()
     gb.destroy()
     if world > 1:
-        # two sweeps per pass over slabs: ghost width 2, two planes per side and pass over NCCL
+        # two sweeps per pass over slabs: ghost width 2, two planes per side and pass
         f = synth.field(7, (n + 4) ** 3, np.float32, first=rank * (n + 4) ** 3)
         ga, gb = hp.DeviceGrid(ctx, (n, n, n), np.float32, 2), hp.DeviceGrid(ctx, (n, n, n), np.float32, 2)
         ga.upload(f)
@@ -410,23 +592,14 @@ def stencil_extra(ctx, torch, stream, world, rank, barrier, max_over_ranks, hp, 
         del f
         for transport, name in ((1, "temporal"), (0, "temporal_nccl")):
             plan = hd.HaloPlan(ctx, ga, gb, hp.STENCIL_JACOBI7, hp.VARIANT_TEMPORAL, transport=transport)
-            step = lambda: plan.sweep(T, stream)  # noqa: E731
-            with torch.cuda.stream(stream):
-                step()
-                n0 = ctx.launch_count()
-                dt, _, _ = time_steps(torch, stream, step, 2, barrier)
-                launches = ctx.launch_count() - n0
-            dt = max_over_ranks(dt)
+            dt, launches = timed(lambda: plan.sweep(T, stream))
             cells = n ** 3 * world * T * 2
-            out[f"jacobi7_512cubed_fp32_{name}"] = {
-                "metric": "stencil_Gcell_updates_per_s", "value": cells / dt / 1e9, "sweeps": 2 * T,
-                "ms_per_sweep": dt / (2 * T) * 1e3, "gpu_launches": launches,
-                "transport": ("peer stores + flags (fused), two planes per side and two-sweep pass" if transport
-                              else "NCCL send/recv, two planes per side and two-sweep pass"),
-                "roofline": {"bound": "hbm", "achieved": cells * 8 / world / dt / 1e9, "peak": peak,
-                             "unit": "GB/s", "frac": cells * 8 / world / dt / 1e9 / peak,
-                             "algorithmic_bytes_per_cell": 8,
-                             "note": "two sweeps per pass over HBM: the kernel moves 4 B/cell/sweep, frac may exceed 1"}}
+            e = entry(cells, dt, launches, sweeps=2 * T, ms_per_sweep=dt / (2 * T) * 1e3,
+                      transport=("peer stores + flags (fused), two planes per side and two-sweep pass" if transport
+                                 else "NCCL send/recv, two planes per side and two-sweep pass"))
+            e["roofline"]["note"] = note2
+            out[f"jacobi7_512cubed_fp32_{name}"] = e
+            summary["jacobi7_512c_2sweep_" + ("peer" if transport else "nccl")] = round(e["value"], 1)
             plan.destroy()
         ga.destroy()
         gb.destroy()
@@ -440,16 +613,13 @@ def stencil_extra(ctx, torch, stream, world, rank, barrier, max_over_ranks, hp, 
         del f
         for variant, name in ((hp.VARIANT_TMA, "tma"), (hp.VARIANT_TEMPORAL, "temporal")):
             plan = hd.HaloPlan(ctx, ga, gb, hp.STENCIL_JACOBI7, variant, transport=1)
-            step = lambda: plan.sweep(T, stream)  # noqa: E731
-            with torch.cuda.stream(stream):
-                step()
-                dt, _, _ = time_steps(torch, stream, step, 2, barrier)
-            dt = max_over_ranks(dt)
+            dt, _ = timed(lambda: plan.sweep(T, stream))
             cells = nzl * n * n * world * T * 2
             out[f"jacobi7_512cubed_total_fp32_{name}_strong"] = {
                 "metric": "stencil_Gcell_updates_per_s", "value": cells / dt / 1e9, "scaling": "strong",
                 "planes_per_gpu": nzl, "ms_per_sweep": dt / (2 * T) * 1e3,
                 "transport": "peer stores + flags"}
+            summary["jacobi7_512c_total_strong_" + ("1sweep" if name == "tma" else "2sweep")] = round(cells / dt / 1e9, 1)
             plan.destroy()
         ga.destroy()
         gb.destroy()
@@ -457,29 +627,51 @@ def stencil_extra(ctx, torch, stream, world, rank, barrier, max_over_ranks, hp, 
         m = 8192
         a = hp.DeviceGrid(ctx, (m, m), np.float32, 8)
         b = hp.DeviceGrid(ctx, (m, m), np.float32, 0)
-        a.upload(synth.field(3, (m + 16) ** 2, np.float32))
-        for kind, name in ((hp.STENCIL_BOX_X, "box_x"), (hp.STENCIL_BOX_Y, "box_y")):
-            step = lambda: hp.stencil_sweep(a, b, kind, radius=8, stream=stream)  # noqa: E731
-            with torch.cuda.stream(stream):
-                for _ in range(3):
-                    step()
-                dt, _, _ = time_steps(torch, stream, step, 20, barrier)
-            out[f"r0_{name}_8192sq_fp32"] = {
-                "metric": "stencil_Gcell_updates_per_s", "value": m * m * 20 / dt / 1e9,
-                "ms_per_sweep": dt / 20 * 1e3,
-                "roofline": {"bound": "hbm", "achieved": m * m * 8 * 20 / dt / 1e9, "peak": peak,
-                             "unit": "GB/s", "frac": m * m * 8 * 20 / dt / 1e9 / peak}}
+        fa = synth.field(3, (m + 16) ** 2, np.float32)
+        a.upload(fa)
+        host_a = ctx.pinned(((m + 16) ** 2,), np.float32)
+        host_b = ctx.pinned((m * m,), np.float32)
+        host_a[:] = fa
+        for kind, name, ref_which in ((hp.STENCIL_BOX_X, "box_x", "x_sse"), (hp.STENCIL_BOX_Y, "box_y", "y_sse_ipl")):
+            dt, _ = timed(lambda: hp.stencil_sweep(a, b, kind, radius=8, stream=stream), 20)
+            e = entry(m * m * 20, dt, None, ms_per_sweep=dt / 20 * 1e3)
+
+            def box_e2e():
+                a.upload(host_a, stream)
+                hp.stencil_sweep(a, b, kind, radius=8, stream=stream)
+                b.download(host_b, stream)
+                stream.synchronize()
+            dte, _ = timed(box_e2e, 5)
+            e["e2e"] = {"value": m * m * 5 / dte / 1e9, "unit": "Gcell-updates/s", "ms_per_step": dte / 5 * 1e3,
+                        "h2d_bytes_per_step": host_a.nbytes, "d2h_bytes_per_step": host_b.nbytes,
+                        "call": "hpcx_grid_upload(pinned) + hpcx_stencil_sweep + hpcx_grid_download(pinned): "
+                                "what hpc::stencil_sweep(a, b, Box1D) does on host containers"}
+            summary[f"r0_{name}"] = round(e["value"], 1)
+            summary[f"r0_{name}_e2e"] = round(e["e2e"]["value"], 2)
+            if not args.no_cpu:
+                # cpu_baseline, kind "reference": the reference's OWN loop (BM_x_blur_tiling_simd_prefetch /
+                # BM_YXx_blur_tiling_prefetch_streamed_IPL, test_hpc_benchmark.cpp:425-441, 575-601) compiled
+                # into oracle/_ref, on its own containers, all host cores
+                import oracle
+                cores = host_threads()
+                if oracle.ref() is not None:
+                    ts, bref = oracle.ref_blur_timed(ref_which, fa, m, m, 6)
+                    ts = ts[1:]
+                    same = bool(np.array_equal(bref.view(np.uint32), np.asarray(host_b).view(np.uint32)))
+                    e["cpu_baseline"] = {"value": m * m / min(ts) / 1e9, "unit": "Gcell-updates/s", "cores": cores,
+                                         "kind": "reference", "bit_identical_to_gpu": same,
+                                         "sample": f"full 8192^2 sweep, best of {len(ts)} after 1 warm-up, the "
+                                                   f"reference's own {ref_which} loop (oracle/_ref/libhpcref.so)"}
+                    summary[f"r0_{name}_cpu"] = {"value": round(m * m / min(ts) / 1e9, 3), "cores": cores,
+                                                 "kind": "reference", "bit_identical_to_gpu": same}
+                    if not same:
+                        raise SystemExit(f"bench.py: GPU {name} sweep differs from the reference's own loop")
+            out[f"r0_{name}_8192sq_fp32"] = e
+        del fa
         # transpose (BM_transpose, test_hpc_benchmark.cpp:672-682) on the same 8192^2 shape: 8 B/cell
         c = hp.DeviceGrid(ctx, (m, m), np.float32, 0)
-        step = lambda: hp.grid_transpose(b, c, stream=stream)  # noqa: E731
-        with torch.cuda.stream(stream):
-            for _ in range(3):
-                step()
-            dt, _, _ = time_steps(torch, stream, step, 20, barrier)
-        out["transpose_8192sq_fp32"] = {
-            "metric": "stencil_Gcell_updates_per_s", "value": m * m * 20 / dt / 1e9, "ms_per_sweep": dt / 20 * 1e3,
-            "roofline": {"bound": "hbm", "achieved": m * m * 8 * 20 / dt / 1e9, "peak": peak, "unit": "GB/s",
-                         "frac": m * m * 8 * 20 / dt / 1e9 / peak}}
+        dt, _ = timed(lambda: hp.grid_transpose(b, c, stream=stream), 20)
+        out["transpose_8192sq_fp32"] = entry(m * m * 20, dt, None, ms_per_sweep=dt / 20 * 1e3)
         a.destroy()
         b.destroy()
         c.destroy()
@@ -490,11 +682,7 @@ def stencil_extra(ctx, torch, stream, world, rank, barrier, max_over_ranks, hp, 
         ka = hp.DeviceGrid(ctx, (k, k), np.float32, 0)
         kb.upload(synth.field(32, (k + 32) ** 2, np.float32))
         w = synth.field(33, 256, np.float32).reshape(16, 16)
-        step = lambda: hp.conv2d(kb, ka, w, stream=stream)  # noqa: E731
-        with torch.cuda.stream(stream):
-            for _ in range(3):
-                step()
-            dt, _, _ = time_steps(torch, stream, step, 20, barrier)
+        dt, _ = timed(lambda: hp.conv2d(kb, ka, w, stream=stream), 20)
         sm = torch.cuda.get_device_properties(0).multi_processor_count
         fp32_peak = sm * 128 * 1.965  # Gop/s: 128 FP32 lanes per SM at the 1965 MHz boost clock
         out["conv16x16_1024sq_fp32"] = {
@@ -505,7 +693,7 @@ def stencil_extra(ctx, torch, stream, world, rank, barrier, max_over_ranks, hp, 
                          "hbm_GBps": k * k * 8 * 20 / dt / 1e9}}
         ka.destroy()
         kb.destroy()
-    return out
+    return out, summary
 
 
 def cg_extra(args, ctx, torch, stream, world, barrier, max_over_ranks, hp, D, nloc, nnz, b):
@@ -535,6 +723,56 @@ def cg_extra(args, ctx, torch, stream, world, barrier, max_over_ranks, hp, D, nl
             "roofline": {"bound": "hbm", "achieved": nbytes / per_iter / 1e9, "peak": peak, "unit": "GB/s",
                          "frac": nbytes / per_iter / 1e9 / peak, "algorithmic_bytes_per_iteration": nbytes,
                          "note": "three passes per iteration: fused SpMV+dot, x/r update + <r,r>, p update"}}
+
+
+def c1_extra(args, ctx, torch, stream, barrier, hp, synth):
+    """configs[0] (C1, "reference CPU SIMD path (plumbing)"): 2-D 5-point Laplacian 1024 x 1024, fp64 —
+    the one config the CPU runs comfortably.  84 MB of algorithmic bytes: L2-resident on the GPU, so it
+    is reported as plumbing and excluded from roofline claims."""
+    n = 1024
+    rp, col, val = synth.laplace2d(n, n)
+    A = hp.CsrMatrix(rp, col, val)
+    t0 = time.perf_counter()
+    D = hp.DeviceCsr(ctx, A)
+    create_ms = (time.perf_counter() - t0) * 1e3
+    x = synth.field(42, n * n)
+    xd = torch.from_numpy(x).cuda()
+    yd = torch.empty(n * n, dtype=torch.float64, device="cuda")
+    xh, yh = ctx.pinned((n * n,), np.float64), ctx.pinned((n * n,), np.float64)
+    xh[:] = x
+    torch.cuda.synchronize()
+    nbytes = algorithmic_bytes(n * n, len(col))
+    with torch.cuda.stream(stream):
+        for _ in range(5):
+            D.spmv(xd, yd, stream)
+        dt, _, _ = time_steps(torch, stream, lambda: D.spmv(xd, yd, stream), 50, barrier)
+        for _ in range(3):
+            D.spmv(xh, yh, stream)
+        dte, _, _ = time_steps(torch, stream, lambda: D.spmv(xh, yh, stream), 20, barrier)
+    e = {"metric": METRIC, "value": nbytes * 50 / dt / 1e9, "unit": UNIT, "us_per_step": dt / 50 * 1e6,
+         "rows": n * n, "nnz": int(len(col)), "setup_ms": {"hpcx_csr_create": create_ms},
+         "note": "L2-resident plumbing config: no roofline claim",
+         "e2e": {"value": nbytes * 20 / dte / 1e9, "unit": UNIT, "us_per_step": dte / 20 * 1e6,
+                 "h2d_bytes_per_step": n * n * 8, "d2h_bytes_per_step": n * n * 8,
+                 "call": "hpcx_spmv(A, x HOST, y HOST)"}}
+    if not args.no_cpu:
+        import oracle
+        cores = host_threads()
+        y = np.empty(n * n)
+        oracle.spmv(rp, col, val, x, out=y)
+        ts = []
+        for _ in range(20):
+            t0 = time.perf_counter()
+            oracle.spmv(rp, col, val, x, out=y)
+            ts.append(time.perf_counter() - t0)
+        same = bool(np.array_equal(y.view(np.uint64), np.asarray(yh).view(np.uint64)))
+        e["cpu_baseline"] = {"value": nbytes / min(ts) / 1e9, "unit": UNIT, "cores": cores, "kind": "port",
+                             "us_per_step": min(ts) * 1e6, "bit_identical_to_gpu": same,
+                             "sample": "full C1 matrix, best of 20 products (oracle/hpcx_oracle.c:orc_spmv_i32_f64)"}
+        if not same:
+            raise SystemExit("bench.py: C1 GPU product differs from the CPU restatement (expected bit-identical)")
+    D.destroy()
+    return e
 
 
 def sparse_extra(args, ctx, torch, stream, world, rank, barrier, max_over_ranks, hp, hd, synth):

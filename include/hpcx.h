@@ -74,6 +74,13 @@ HPCX_API hpcx_status hpcx_host_alloc(hpcx_ctx ctx, size_t bytes, void **out);
 HPCX_API hpcx_status hpcx_host_free(hpcx_ctx ctx, void *p);
 HPCX_API hpcx_status hpcx_device_alloc(hpcx_ctx ctx, size_t bytes, void **out);
 HPCX_API hpcx_status hpcx_device_free(hpcx_ctx ctx, void *p);
+/* Context-free allocation by memory kind — what the reference's allocator strategies do
+ * (CudaMemGPUOnly / CudaMemManaged, cudaAllocator.hpp:9-26): HPCX_MEM_DEVICE -> cudaMalloc,
+ * HPCX_MEM_MANAGED -> cudaMallocManaged (valid on host and device; pass it to any entry point with
+ * mem = HPCX_MEM_MANAGED), HPCX_MEM_HOST -> pinned host memory.  Backs include/hpcx/CudaAllocator.hpp.
+ * Returns HPCX_OOM / HPCX_CUDA_ERROR; unlike the reference's deallocate (a no-op, :71-73) free frees. */
+HPCX_API hpcx_status hpcx_mem_alloc(int32_t mem, size_t bytes, void **out);
+HPCX_API hpcx_status hpcx_mem_free(int32_t mem, void *p);
 /* Any direction (cudaMemcpyDefault).  Ordered after all work already issued to the device and
  * complete on return. */
 HPCX_API hpcx_status hpcx_memcpy(hpcx_ctx ctx, void *dst, const void *src, size_t bytes);

@@ -28,6 +28,7 @@
 #include <vector>
 
 #include "AlignedAlloc.hpp"
+#include "CudaAllocator.hpp"
 #include "Runtime.hpp"
 
 namespace sparse {
@@ -214,6 +215,10 @@ class DeviceCsr {
   void multiply_device(const T *x, T *y, void *stream = nullptr) const {
     HPCX_CHECK(ctx_, hpcx_spmv(A_, x, HPCX_MEM_DEVICE, y, HPCX_MEM_DEVICE, stream));
   }
+  // ... or each where its allocator put it (HPCX_MEM_*; see hpcx::memKindOf).
+  void multiply(const T *x, int32_t x_mem, T *y, int32_t y_mem, void *stream = nullptr) const {
+    HPCX_CHECK(ctx_, hpcx_spmv(A_, x, x_mem, y, y_mem, stream));
+  }
 
   // Device assembly from an edge (COO) list, duplicates merged by adding in list order
   // (hpcx_csr_from_coo): the arrays never visit the host.
@@ -285,7 +290,7 @@ class CgSolver {
     hpcx_cg_result r{};
     HPCX_CHECK(ctx_, hpcx_cg_solve(S_, b.data(), HPCX_MEM_HOST, x.data(), HPCX_MEM_HOST, max_iters, rel_tol,
                                    check_every, &r, nullptr));
-    return CgResult{r.iterations, r.converged != 0, r.rr, r.bb};
+    return CgResult{r.iterations, r.converged == 1, r.rr, r.bb};
   }
 
  private:
@@ -300,14 +305,14 @@ void spmv(hpcx::Context &ctx, const CsrMatrix<T, Index> &A, const std::vector<T,
   if (x.size() != A.ncols()) throw std::out_of_range("invalid index, out of boundary");
   y.resize(A.nrows());
   DeviceCsr<T> D(ctx, A);
-  D.multiply(x.data(), y.data());
+  D.multiply(x.data(), hpcx::memKindOf<AllocX>::value, y.data(), hpcx::memKindOf<AllocY>::value);
 }
 
 template <typename T, class AllocX, class AllocY>
 void spmv(const DeviceCsr<T> &A, const std::vector<T, AllocX> &x, std::vector<T, AllocY> &y) {
   if (x.size() != A.ncols()) throw std::out_of_range("invalid index, out of boundary");
   y.resize(A.nrows());
-  A.multiply(x.data(), y.data());
+  A.multiply(x.data(), hpcx::memKindOf<AllocX>::value, y.data(), hpcx::memKindOf<AllocY>::value);
 }
 
 template <typename T, typename Grid>

@@ -5,10 +5,10 @@ The product is libhpcx.so (csrc/, built by `python -m libhpc_b200.build`); this 
 the host-side mirror of the reference's container interface over that ABI.
 """
 from . import _abi  # noqa: F401
-from .api import (CgSolver, Context, CsrMatrix, DeviceCsr, DeviceCsrArrays, DeviceGrid, HPCHighDimensionFlatArray,  # noqa: F401
+from .api import (CgSolver, Context, ManagedArray, CsrMatrix, DeviceCsr, DeviceCsrArrays, DeviceGrid, HPCHighDimensionFlatArray,  # noqa: F401
                   HpcxError, conv2d, csr_from_cells, csr_from_coo, csr_localize, grid_transpose, partition_rows, partition_slabs, spmv, stencil_sweep,
                   synth_field, synth_rmat_csr,
                   stencil_sweep_host)
-from ._abi import (F32, F64, MEM_DEVICE, MEM_HOST, SPMV_SELL, SPMV_STREAM, SPMV_VECTOR,  # noqa: F401
+from ._abi import (F32, F64, MEM_DEVICE, MEM_HOST, MEM_MANAGED, SPMV_AUTO, SPMV_SELL, SPMV_STREAM, SPMV_VECTOR,  # noqa: F401
                    STENCIL_BOX_X, STENCIL_BOX_Y, STENCIL_JACOBI7, VARIANT_AUTO, VARIANT_DIRECT, VARIANT_TEMPORAL,
                    VARIANT_TMA)

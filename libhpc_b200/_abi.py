@@ -80,6 +80,8 @@ PROTOTYPES = {
     "hpcx_host_free": (_i32, [_vp, _vp]),
     "hpcx_device_alloc": (_i32, [_vp, _sz, _P(_vp)]),
     "hpcx_device_free": (_i32, [_vp, _vp]),
+    "hpcx_mem_alloc": (_i32, [_i32, _sz, _P(_vp)]),
+    "hpcx_mem_free": (_i32, [_i32, _vp]),
     "hpcx_memcpy": (_i32, [_vp, _vp, _vp, _sz]),
     "hpcx_grid_stride_total": (_i32, [_P(GridDesc), _P(_i64), _P(_i64)]),
     "hpcx_grid_linearize": (_i32, [_P(GridDesc), _P(_i64), _i32, _P(_i64)]),

@@ -139,6 +139,34 @@ class Context:
         self.close()
 
 
+class ManagedArray:
+    """numpy view of cudaMallocManaged memory (hpcx_mem_alloc): the Python spelling of the
+    reference's `std::vector<T, CudaAllocator<T, CudaMemManaged>>` (lib/gpu/util/include/
+    cudaAllocator.hpp:39-83, radix_sort_gpu.h:22-23).  `.a` is host-addressable; `.arg` is the
+    (pointer, HPCX_MEM_MANAGED) pair the library's entry points take."""
+
+    def __init__(self, shape, dtype, mem: int = _abi.MEM_MANAGED):
+        dt = np.dtype(dtype)
+        n = int(np.prod(shape))
+        self.mem, self.nbytes = mem, max(n * dt.itemsize, 1)
+        p = C.c_void_p()
+        st = _abi.load().hpcx_mem_alloc(mem, self.nbytes, C.byref(p))
+        if st != _abi.OK:
+            _raise(st, "hpcx_mem_alloc")
+        self.ptr = p.value
+        self.a = np.frombuffer((C.c_char * self.nbytes).from_address(self.ptr), dtype=dt, count=n).reshape(shape)
+
+    @property
+    def arg(self):
+        return (self.ptr, self.mem)
+
+    def free(self):
+        if self.ptr:
+            self.a = None
+            _abi.load().hpcx_mem_free(self.mem, self.ptr)
+            self.ptr = None
+
+
 # ------------------------------------------------------------------ dense ghost-padded array
 class HPCHighDimensionFlatArray:
     """hpc::HPCHighDimensionFlatArray<Dimension, T, Low_Bound, High_Bound> on the host.
@@ -348,7 +376,7 @@ class DeviceCsr:
         d = _abi.CsrDesc(A.nrows, A.ncols, A.nnz, A.row_ptr.ctypes.data,
                          A.row_ptr.dtype.itemsize, _dtype_code(A.dtype),
                          A.col_idx.ctypes.data if A.nnz else None,
-                         A.values.ctypes.data if A.nnz else None, MEM_HOST, 0)
+                         A.values.ctypes.data if A.nnz else None, getattr(A, "mem", MEM_HOST), 0)
         o = _abi.CsrOpts(kernel, tile_nnz, sell_c, sell_sigma, lanes_per_row, short_row_max)
         h = C.c_void_p()
         ctx.check(ctx.lib.hpcx_csr_create(ctx.h, C.byref(d), C.byref(o), C.byref(h)))

@@ -139,6 +139,24 @@ hpcx_status hpcx_device_free(hpcx_ctx ctx, void *p) {
   HPCX_CUDA(ctx, cudaFree(p));
   return HPCX_OK;
 }
+hpcx_status hpcx_mem_alloc(int32_t mem, size_t bytes, void **out) {
+  if (!out) return HPCX_INVALID_ARG;
+  *out = nullptr;
+  cudaError_t e;
+  switch (mem) {
+    case HPCX_MEM_DEVICE: e = cudaMalloc(out, bytes ? bytes : 1); break;
+    case HPCX_MEM_MANAGED: e = cudaMallocManaged(out, bytes ? bytes : 1); break;
+    case HPCX_MEM_HOST: e = cudaHostAlloc(out, bytes ? bytes : 1, cudaHostAllocDefault); break;
+    default: return HPCX_INVALID_ARG;
+  }
+  if (e != cudaSuccess) (void)cudaGetLastError();
+  return e == cudaSuccess ? HPCX_OK : e == cudaErrorMemoryAllocation ? HPCX_OOM : HPCX_CUDA_ERROR;
+}
+hpcx_status hpcx_mem_free(int32_t mem, void *p) {
+  if (mem != HPCX_MEM_DEVICE && mem != HPCX_MEM_MANAGED && mem != HPCX_MEM_HOST) return HPCX_INVALID_ARG;
+  const cudaError_t e = mem == HPCX_MEM_HOST ? cudaFreeHost(p) : cudaFree(p);
+  return e == cudaSuccess ? HPCX_OK : HPCX_CUDA_ERROR;
+}
 hpcx_status hpcx_memcpy(hpcx_ctx ctx, void *dst, const void *src, size_t bytes) {
   if (!ctx) return HPCX_INVALID_ARG;
   // Contract: ordered after ALL work already issued to the device (the caller's own streams

@@ -70,6 +70,14 @@ def _p(a):
     return None if a is None else a.ctypes.data_as(C.c_void_p)
 
 
+def set_threads(n: int | None = None) -> int:
+    """OpenMP team size of the oracle and of oracle/_ref (one libgomp per process).  Default: every
+    core of the affinity mask, whatever OMP_NUM_THREADS says (torchrun exports 1)."""
+    n = len(os.sched_getaffinity(0)) if n is None else int(n)
+    lib().orc_set_threads(C.c_int(n))
+    return int(lib().orc_max_threads())
+
+
 # ------------------------------------------------------------------ RNG
 def fill(n: int, seed: int, dtype=np.float64, first: int = 0) -> np.ndarray:
     out = np.empty(n, dtype=dtype)
@@ -239,6 +247,26 @@ def ref_blur(which: str, a_flat: np.ndarray, ny: int, nx: int) -> np.ndarray:
     b = np.empty(ny * nx, dtype=np.float32)
     r.hpcref_blur(C.c_int(REF_BLUR[which]), _p(a_flat), _p(b), C.c_int64(ny), C.c_int64(nx))
     return b
+
+
+def ref_blur_timed(which: str, a_flat: np.ndarray, ny: int, nx: int, reps: int):
+    """The reference's own sweep loop (BM_x_blur ...) timed `reps` times on persistent containers
+    (hpcref_blur_setup / _run / _result, oracle/ref_harness.cpp).  Returns (seconds list, b_flat)."""
+    import time
+    r = ref()
+    if r is None:
+        raise RuntimeError("oracle/_ref/libhpcref.so was not built (reference tree absent)")
+    a_flat = np.ascontiguousarray(a_flat, dtype=np.float32)
+    assert a_flat.size == (ny + 16) * (nx + 16)
+    r.hpcref_blur_setup(_p(a_flat), C.c_int64(ny), C.c_int64(nx))
+    times = []
+    for _ in range(reps):
+        t = time.perf_counter()
+        r.hpcref_blur_run(C.c_int(REF_BLUR[which]))
+        times.append(time.perf_counter() - t)
+    b = np.empty(ny * nx, dtype=np.float32)
+    r.hpcref_blur_result(_p(b))
+    return times, b
 
 
 def ref_index(dim, lo, hi, idx, checked):

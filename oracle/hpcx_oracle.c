@@ -26,7 +26,14 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <omp.h>
+
 #define ORC_API __attribute__((visibility("default")))
+
+/* OpenMP team size of every loop below (and of oracle/_ref, which shares the runtime): bench.py
+ * sets it from the affinity mask, because launchers such as torchrun export OMP_NUM_THREADS=1. */
+ORC_API void orc_set_threads(int n) { if (n > 0) omp_set_num_threads(n); }
+ORC_API int orc_max_threads(void) { return omp_get_max_threads(); }
 
 /* ------------------------------------------------------------------ deterministic RNG
  * Counter-based: u(seed, i) = top 53 bits of

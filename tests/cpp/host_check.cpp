@@ -233,6 +233,16 @@ static int run_gpu() {
     std::vector<double> y2;
     sparse::spmv(dA, x, y2);
     bad += std::memcmp(y.data(), y2.data(), y.size() * 8) != 0;
+    {  // row a6: managed-memory vectors, the way the reference hands buffers to kernels
+       // (std::vector<T, CudaAllocator<T, CudaMemManaged>>, radix_sort_gpu.h:22-23)
+      std::vector<double, CudaAllocator<double, CudaMemManaged>> mx(A.ncols()), my(A.nrows());
+      std::memcpy(mx.data(), x.data(), x.size() * 8);
+      sparse::spmv(dA, mx, my);  // goes through the ABI as HPCX_MEM_MANAGED: no staging copy
+      const int same = std::memcmp(my.data(), y.data(), y.size() * 8) == 0;
+      static_assert(hpcx::memKindOf<decltype(mx)::allocator_type>::value == HPCX_MEM_MANAGED, "managed vectors");
+      std::printf("managed_vectors bit_exact %d\n", same);
+      bad += !same;
+    }
     try {
       std::vector<double> shortx(3);
       sparse::spmv(dA, shortx, y2);

@@ -120,6 +120,7 @@ def test_cpp_entry_points_on_gpu(binary):
     assert "jacobi7 bit_exact 1" in out
     assert "jacobi7_temporal bit_exact 1" in out
     assert "box_radius system_error" in out and "spmv_short_x out_of_range" in out
+    assert "managed_vectors bit_exact 1" in out
     assert "conv2d bit_exact 1" in out and "transpose bit_exact 1" in out
     assert "from_coo product bit_exact 1" in out and "converged 1" in out
     assert "grid_bridge ok 1" in out

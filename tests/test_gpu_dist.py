@@ -26,3 +26,16 @@ def test_dist_paths_multi_gpu(world):
                         f"--nproc-per-node={world}", "--master-addr", "127.0.0.1", "--master-port",
                         str(29500 + world), SCRIPT], capture_output=True, text=True, timeout=1200)
     assert p.returncode == 0 and f"DIST OK world={world}" in p.stdout, p.stdout[-2000:] + p.stderr[-4000:]
+
+
+def test_peer_flag_timeout_traps_and_is_reported():
+    """hpcx_comm_set_timeout: a wait that expires traps (no stale halo is read) and the caller sees
+    HPCX_NCCL_ERROR; without a bound the wait lasts (dist_gpu_check.py delays a rank by 5 s)."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    script = os.path.join(ROOT, "tests", "dist_timeout_check.py")
+    p = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+                        "--master-addr", "127.0.0.1", "--master-port", "29511", script],
+                       capture_output=True, text=True, timeout=600)
+    assert "TIMEOUT OK" in p.stdout, p.stdout[-2000:] + p.stderr[-4000:]

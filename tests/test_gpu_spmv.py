@@ -228,3 +228,115 @@ def test_c2_full_size_properties(ctx):
         assert not y.reshape(n, n)[1:-1, 1:-1].any()
     finally:
         D.destroy()
+
+
+def test_c4_full_size_256_cubed_vs_oracle(ctx):
+    """configs[3] at FULL size (27-point operator on 256^3, 16.8 M rows, 449.5 M nnz, fp64): a
+    random x against the oracle's product, norm-wise and row-wise 1e-12 (every row has <= 27
+    entries, so the one-thread-per-row path sums in the oracle's order: bit-identical)."""
+    n = 256
+    rp, col, val = oracle.op27(n)
+    assert rp[-1] == (3 * n - 2) ** 3 == 449455096
+    x = oracle.fill(n ** 3, 42, np.float64)
+    D = hp.DeviceCsr(ctx, hp.CsrMatrix(rp, col, val))
+    try:
+        y = np.full(n ** 3, np.nan)
+        D.spmv(x, y)
+    finally:
+        D.destroy()
+    y_ref = oracle.spmv(rp, col, val, x)
+    assert_spmv_close(y, y_ref, oracle.spmv_abs(rp, col, val, x), 1e-12)
+    assert bits_equal(y, y_ref)
+
+
+@pytest.mark.parametrize("kernel", [hp.SPMV_AUTO, hp.SPMV_STREAM])
+def test_c5_full_size_rmat_scale24_vs_oracle(ctx, kernel):
+    """configs[4] at FULL size (R-MAT scale 24, 2^28 edges -> 263.4 M merged nonzeros, fp32, longest
+    row 238,875): the device-assembled matrix is downloaded once and a random x is checked against
+    the oracle's product, norm-wise and row-wise 1e-5 — the size at which the long-row chunks, the
+    fix-up kernel and (AUTO) the hub kernel carry most of the nonzeros."""
+    scale = 24
+    arrs = hp.synth_rmat_csr(ctx, scale, 16, 24, 4)
+    try:
+        rp, col, val = arrs.download()
+        D = hp.DeviceCsr.from_device_arrays(ctx, arrs, kernel=kernel)
+    finally:
+        arrs.destroy()
+    assert len(col) == 263432173 and int(np.diff(rp).max()) == 238875
+    n = 1 << scale
+    x = oracle.fill(n, 42, np.float32)
+    try:
+        y = np.full(n, np.nan, dtype=np.float32)
+        D.spmv(x, y)
+        y2 = np.full(n, np.nan, dtype=np.float32)
+        D.spmv(x, y2)
+    finally:
+        D.destroy()
+    assert bits_equal(y, y2)  # deterministic: no atomics on the value path
+    assert_spmv_close(y, oracle.spmv(rp, col, val, x), oracle.spmv_abs(rp, col, val, x), 1e-5)
+
+
+def test_managed_memory_operands(ctx):
+    """Row a6: the reference hands kernels `std::vector<T, CudaAllocator<T, CudaMemManaged>>::data()`
+    (cudaAllocator.hpp:39-83, radix_sort_gpu.h:22-23).  Here the CSR arrays, x and y all live in
+    cudaMallocManaged memory and go through the ABI as HPCX_MEM_MANAGED."""
+    rp, col, val = synth.op27(20)
+    n, nnz = len(rp) - 1, len(col)
+    bufs = [hp.ManagedArray((n + 1,), np.int32), hp.ManagedArray((nnz,), np.int32),
+            hp.ManagedArray((nnz,), np.float64), hp.ManagedArray((n,), np.float64),
+            hp.ManagedArray((n,), np.float64)]
+    mrp, mcol, mval, mx, my = bufs
+    try:
+        mrp.a[:], mcol.a[:], mval.a[:] = rp, col, val
+        mx.a[:] = synth.field(42, n)
+        my.a[:] = np.nan
+        A = hp.CsrMatrix.__new__(hp.CsrMatrix)
+        A.row_ptr, A.col_idx, A.values = mrp.a, mcol.a, mval.a
+        A.nrows, A.ncols, A.nnz, A.mem = n, n, nnz, hp.MEM_MANAGED
+        D = hp.DeviceCsr(ctx, A)
+        try:
+            D.spmv(mx.arg, my.arg)  # stream NULL: synchronous, so the host may read my.a now
+            assert bits_equal(np.array(my.a), oracle.spmv(rp, col, val, np.array(mx.a)))
+            # mixed: managed x, host y
+            y = np.empty(n)
+            D.spmv(mx.arg, y)
+            assert bits_equal(y, np.array(my.a))
+            rp2, col2, val2 = D.download()
+            assert bits_equal(rp2, rp) and bits_equal(col2, col) and bits_equal(val2, val)
+        finally:
+            D.destroy()
+        # a managed flat array as the host side of a grid upload / download
+        g = hp.DeviceGrid(ctx, (6, 10, 70), np.float32, 1)
+        mg = hp.ManagedArray((8 * 12 * 72,), np.float32)
+        mo = hp.ManagedArray((8 * 12 * 72,), np.float32)
+        try:
+            mg.a[:] = synth.field(5, 8 * 12 * 72, np.float32)
+            ctx.check(ctx.lib.hpcx_grid_upload(g.h, mg.ptr, None))
+            ctx.check(ctx.lib.hpcx_grid_download(g.h, mo.ptr, None))
+            assert bits_equal(np.array(mo.a), np.array(mg.a))
+        finally:
+            g.destroy()
+            mg.free()
+            mo.free()
+    finally:
+        for b in bufs:
+            b.free()
+
+
+def test_column_index_outside_x_is_rejected(ctx):
+    """A column index outside [0, ncols) would be an out-of-bounds gather in every kernel:
+    hpcx_csr_create refuses the matrix (HPCX_OUT_OF_RANGE -> IndexError)."""
+    rp = np.array([0, 2, 3], dtype=np.int32)
+    val = np.ones(3)
+    for bad in (np.array([0, 5, 1], np.int32), np.array([0, 1, -1], np.int32)):
+        with pytest.raises(IndexError):
+            hp.DeviceCsr(ctx, hp.CsrMatrix(rp, bad, val, ncols=5))
+    D = hp.DeviceCsr(ctx, hp.CsrMatrix(rp, np.array([0, 4, 1], np.int32), val, ncols=5))  # 4 is fine
+    # ... and so does hpcx_csr_set_halo for a gather index outside the owned block
+    try:
+        L = dict(nloc=2, nhalo=3, nsend=1, recv_counts=np.array([3], np.int64), send_counts=np.array([1], np.int64),
+                 send_idx=np.array([2], np.int32), row_kind=np.zeros(2, np.uint8))
+        with pytest.raises(IndexError):
+            D.set_halo(L)
+    finally:
+        D.destroy()
