@@ -205,7 +205,12 @@ enum {
   HPCX_SPMV_AUTO = 0,
   HPCX_SPMV_STREAM = 1,  /* row-blocked, TMA-bulk staged tiles, adaptive row reduction */
   HPCX_SPMV_VECTOR = 2,  /* classic sub-warp vector-per-row */
-  HPCX_SPMV_SELL = 3     /* SELL-C-sigma repack */
+  HPCX_SPMV_SELL = 3,    /* SELL-C-sigma repack */
+  /* power-law matrices: nonzero-balanced persistent kernel, the x entries of the most referenced
+   * ("hub") columns in shared memory, 128-bit loads of col/val, segmented warp-shuffle row sums.
+   * HPCX_SPMV_AUTO picks it when more than a quarter of the nonzeros sit in rows longer than 256
+   * and the hub columns receive at least 10 % of the gathers; STREAM otherwise. */
+  HPCX_SPMV_HUB = 4
 };
 typedef struct {
   int32_t kernel;      /* HPCX_SPMV_* */

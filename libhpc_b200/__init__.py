@@ -9,6 +9,6 @@ from .api import (CgSolver, Context, ManagedArray, CsrMatrix, DeviceCsr, DeviceC
                   HpcxError, conv2d, csr_from_cells, csr_from_coo, csr_localize, grid_transpose, partition_rows, partition_slabs, spmv, stencil_sweep,
                   synth_field, synth_rmat_csr,
                   stencil_sweep_host)
-from ._abi import (F32, F64, MEM_DEVICE, MEM_HOST, MEM_MANAGED, SPMV_AUTO, SPMV_SELL, SPMV_STREAM, SPMV_VECTOR,  # noqa: F401
+from ._abi import (F32, F64, MEM_DEVICE, MEM_HOST, MEM_MANAGED, SPMV_AUTO, SPMV_HUB, SPMV_SELL, SPMV_STREAM, SPMV_VECTOR,  # noqa: F401
                    STENCIL_BOX_X, STENCIL_BOX_Y, STENCIL_JACOBI7, VARIANT_AUTO, VARIANT_DIRECT, VARIANT_TEMPORAL,
                    VARIANT_TMA)

@@ -17,7 +17,7 @@ F32, F64 = 0, 1
 MEM_HOST, MEM_DEVICE, MEM_MANAGED = 0, 1, 2
 STENCIL_BOX_X, STENCIL_BOX_Y, STENCIL_JACOBI7 = 1, 2, 3
 VARIANT_AUTO, VARIANT_TMA, VARIANT_DIRECT, VARIANT_TEMPORAL = 0, 1, 2, 3
-SPMV_AUTO, SPMV_STREAM, SPMV_VECTOR, SPMV_SELL = 0, 1, 2, 3
+SPMV_AUTO, SPMV_STREAM, SPMV_VECTOR, SPMV_SELL, SPMV_HUB = 0, 1, 2, 3, 4
 
 STATUS_NAMES = {0: "HPCX_OK", 1: "HPCX_INVALID_ARG", 2: "HPCX_OOM", 3: "HPCX_CUDA_ERROR",
                 4: "HPCX_NCCL_ERROR", 5: "HPCX_UNSUPPORTED", 6: "HPCX_OUT_OF_RANGE"}

@@ -21,7 +21,7 @@ import ctypes as C
 import numpy as np
 
 from . import _abi
-from ._abi import (F32, F64, MEM_DEVICE, MEM_HOST, SPMV_SELL, SPMV_STREAM, SPMV_VECTOR,
+from ._abi import (F32, F64, MEM_DEVICE, MEM_HOST, SPMV_AUTO, SPMV_HUB, SPMV_SELL, SPMV_STREAM, SPMV_VECTOR,
                    STENCIL_BOX_X, STENCIL_BOX_Y, STENCIL_JACOBI7, VARIANT_AUTO, VARIANT_DIRECT,
                    VARIANT_TMA)
 
@@ -370,7 +370,7 @@ class CsrMatrix:
 class DeviceCsr:
     """Device-resident matrix behind hpcx_csr_create."""
 
-    def __init__(self, ctx: Context, A: CsrMatrix, kernel: int = SPMV_STREAM, tile_nnz: int = 0,
+    def __init__(self, ctx: Context, A: CsrMatrix, kernel: int = SPMV_AUTO, tile_nnz: int = 0,
                  sell_c: int = 0, sell_sigma: int = 0, lanes_per_row: int = 0, short_row_max: int = 0):
         self.ctx, self.host = ctx, A
         d = _abi.CsrDesc(A.nrows, A.ncols, A.nnz, A.row_ptr.ctypes.data,
@@ -387,7 +387,7 @@ class DeviceCsr:
 
     @classmethod
     def from_device_arrays(cls, ctx: Context, arrays: "DeviceCsrArrays", ncols: int | None = None,
-                           kernel: int = SPMV_STREAM, tile_nnz: int = 0, sell_c: int = 0,
+                           kernel: int = SPMV_AUTO, tile_nnz: int = 0, sell_c: int = 0,
                            sell_sigma: int = 0, lanes_per_row: int = 0, short_row_max: int = 0) -> "DeviceCsr":
         """Matrix whose CSR arrays already live on the device (csr_from_coo)."""
         self = cls.__new__(cls)

@@ -157,8 +157,11 @@ __global__ void __launch_bounds__(256) cg_update_p_kernel(const T *__restrict__ 
 hpcx_status product(hpcx_cg S, cudaStream_t s) {
   hpcx_csr A = S->A;
   A->dot_part = S->part;
+  const int32_t kernel = A->kernel;
+  A->kernel = HPCX_SPMV_STREAM;  // the fused dot lives in the STREAM kernel; its tables always exist
   hpcx_status rc = A->d_xfull ? hpcx_spmv_dist(A, S->p, S->q, s)
                               : hpcx_spmv(A, S->p, HPCX_MEM_DEVICE, S->q, HPCX_MEM_DEVICE, s);
+  A->kernel = kernel;
   A->dot_part = nullptr;
   return rc;
 }
@@ -234,7 +237,8 @@ hpcx_status hpcx_cg_create(hpcx_csr A, hpcx_cg *out) {
   if (!A || !out) return HPCX_INVALID_ARG;
   *out = nullptr;
   hpcx_ctx ctx = A->ctx;
-  HPCX_REQUIRE(ctx, A->kernel == HPCX_SPMV_STREAM, "the CG step needs the STREAM kernel (fused <p, q>)");
+  HPCX_REQUIRE(ctx, A->kernel == HPCX_SPMV_STREAM || A->kernel == HPCX_SPMV_HUB,
+               "the CG step needs the STREAM kernel (fused <p, q>)");
   const bool dist = A->d_xfull != nullptr;
   const int64_t n = dist ? A->nloc : A->nrows;
   HPCX_REQUIRE(ctx, dist ? A->nrows == A->nloc : A->nrows == A->ncols, "CG needs a square matrix");

@@ -23,13 +23,13 @@ bool jacobi7_tb2_supported(hpcx_grid_s *g);
 hpcx_status jacobi7_tb2_launch(hpcx_grid_s *g, void *src, void *dst, int zsplit, int64_t zbeg, int64_t zend,
                                bool nb_lo, bool nb_hi, cudaStream_t s, int64_t zbeg2 = 0, int64_t zend2 = 0);
 hpcx_status spmv_launch_blocks(hpcx_csr A, const RowBlock *d_blocks, int64_t nblocks, const void *x,
-                               void *y, cudaStream_t s, void *dot_part);
+                               void *y, cudaStream_t s, void *dot_part, const SpmvDistArgs *da);
 hpcx_status spmv_launch_fixup_tables(hpcx_csr A, const int32_t *long_row, const int32_t *long_off,
                                      int64_t nlong, void *y, cudaStream_t s, const void *x,
                                      void *dot_part);
-void spmv_build_rowblocks(const int64_t *rp, int64_t nrows, int tile, int short_row_max, const uint8_t *kind,
-                          int want, std::vector<RowBlock> &out, std::vector<int32_t> *long_row,
-                          std::vector<int32_t> *long_off);
+hpcx_status csr_plan_rowblocks(hpcx_csr A, const uint8_t *d_kind, int64_t maxlen, RowBlock **d_blocks,
+                               std::vector<RowBlock> *host, int64_t *n0, int32_t **d_long_row,
+                               int32_t **d_long_off, int64_t *nlong, int64_t *nchunks);
 }  // namespace hpcx
 
 namespace {
@@ -592,45 +592,9 @@ gather_boundary_x_kernel(const T *__restrict__ x, const int32_t *__restrict__ se
     sendbuf[i] = __ldg(x + send_idx[i]);
 }
 
-// ---- transport 1: gather + peer store + flag in one kernel ------------------------------
-constexpr int kSyncData = 0, kSyncAck = 64, kSyncCount = 128, kMaxPeers = 64;
-
-// grid = (blocks per segment, segments).  Segment s holds the entries destined for rank
-// seg_rank[s]; they are stored straight into that rank's halo slots.  The last CTA to finish
-// publishes the product number in every destination.
-template <typename T>
-__global__ void __launch_bounds__(256)
-push_boundary_x_kernel(const T *__restrict__ x, const int32_t *__restrict__ send_idx,
-                       const int32_t *__restrict__ seg_start, const int32_t *__restrict__ seg_rank,
-                       void *const *__restrict__ seg_dst, uint32_t *const *__restrict__ seg_flag,
-                       uint32_t *sync, uint32_t epoch, PeerWait pw) {
-  const int s = blockIdx.y;
-  // The destination must have finished reading the previous product's halo (its ack).
-  if (threadIdx.x == 0) wait_flag(sync + kSyncAck + seg_rank[s], epoch - 1, pw);
-  __syncthreads();
-  const int a = seg_start[s], e = seg_start[s + 1];
-  T *dst = static_cast<T *>(seg_dst[s]);
-  for (int i = a + blockIdx.x * blockDim.x + threadIdx.x; i < e; i += gridDim.x * blockDim.x)
-    dst[i - a] = __ldg(x + send_idx[i]);
-  __threadfence_system();
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    const uint32_t total = gridDim.x * gridDim.y;
-    if ((atomicAdd(sync + kSyncCount, 1u) + 1) % total == 0)
-      for (int k = 0; k < (int)gridDim.y; ++k) st_release_sys(seg_flag[k], epoch);
-  }
-}
-
-// Holds the stream until every source rank's boundary entries of product `epoch` have landed.
-__global__ void halo_x_ready_kernel(uint32_t *sync, const int32_t *__restrict__ src_rank, int nsrc,
-                                    uint32_t epoch, PeerWait pw) {
-  if ((int)threadIdx.x < nsrc) wait_flag(sync + kSyncData + src_rank[threadIdx.x], epoch, pw);
-}
-
-// Tells every source rank that this rank's boundary rows of product `epoch` have read the halo.
-__global__ void halo_x_ack_kernel(uint32_t *const *__restrict__ src_ack, int nsrc, uint32_t epoch) {
-  if ((int)threadIdx.x < nsrc) st_release_sys(src_ack[threadIdx.x], epoch);
-}
+// ---- transport 1: the push (gather + peer stores + flags), the flag waits and the ack all live
+// in the SpMV kernel itself (spmv.cu, DIST instantiation; SpmvDistArgs in spmv.cuh).
+constexpr int kSyncData = 0, kSyncAck = 64, kMaxPeers = 64;  // words of the sync block; counters follow at 128, 129
 
 struct CsrPeerInfo {
   cudaIpcMemHandle_t handle[2];  // allocations holding [owned | halo] x and the sync block
@@ -695,13 +659,12 @@ hpcx_status hpcx_csr_set_halo(hpcx_csr A, int64_t nloc, int64_t nhalo, const int
   cudaFree(A->d_send_idx);
   cudaFree(A->d_sendbuf);
   cudaFree(A->d_xfull);
-  cudaFree(A->d_blocks_int);
-  cudaFree(A->d_blocks_bnd);
+  cudaFree(A->d_blocks_dist);
   cudaFree(A->d_long_row_dist);
   cudaFree(A->d_long_off_dist);
   A->d_send_idx = nullptr;
   A->d_sendbuf = A->d_xfull = nullptr;
-  A->d_blocks_int = A->d_blocks_bnd = nullptr;
+  A->d_blocks_dist = A->d_blocks_int = A->d_blocks_bnd = nullptr;
   A->d_long_row_dist = A->d_long_off_dist = nullptr;
   HPCX_CUDA(ctx, cudaMalloc((void **)&A->d_send_idx, std::max<size_t>((size_t)nsend, 1) * 4));
   HPCX_CUDA(ctx, cudaMalloc(&A->d_sendbuf, std::max<size_t>((size_t)nsend, 1) * A->es));
@@ -709,29 +672,23 @@ hpcx_status hpcx_csr_set_halo(hpcx_csr A, int64_t nloc, int64_t nhalo, const int
   if (nsend)
     HPCX_CUDA(ctx, cudaMemcpy(A->d_send_idx, send_idx, (size_t)nsend * 4, cudaMemcpyHostToDevice));
 
-  // Interior / boundary row-block tables over the device-resident row_ptr.
-  std::vector<int32_t> rp32(A->nrows + 1);
-  HPCX_CUDA(ctx, cudaMemcpy(rp32.data(), A->d_row_ptr, rp32.size() * 4, cudaMemcpyDeviceToHost));
-  std::vector<int64_t> rp(rp32.begin(), rp32.end());
-  std::vector<int32_t> long_row, long_off;
-  A->h_blocks_int.clear();
-  A->h_blocks_bnd.clear();
-  spmv_build_rowblocks(rp.data(), A->nrows, A->tile, A->short_row_max, row_kind, 0, A->h_blocks_int, &long_row,
-                       &long_off);
-  spmv_build_rowblocks(rp.data(), A->nrows, A->tile, A->short_row_max, row_kind, 1, A->h_blocks_bnd, &long_row,
-                       &long_off);
-  A->nlong_dist = (int64_t)long_row.size();
-  auto up = [&](const void *h, size_t bytes, void **d) -> cudaError_t {
-    cudaError_t e = cudaMalloc(d, std::max<size_t>(bytes, 16));
-    if (e == cudaSuccess && bytes) e = cudaMemcpy(*d, h, bytes, cudaMemcpyHostToDevice);
-    return e;
-  };
-  HPCX_CUDA(ctx, up(A->h_blocks_int.data(), A->h_blocks_int.size() * sizeof(RowBlock),
-                    (void **)&A->d_blocks_int));
-  HPCX_CUDA(ctx, up(A->h_blocks_bnd.data(), A->h_blocks_bnd.size() * sizeof(RowBlock),
-                    (void **)&A->d_blocks_bnd));
-  HPCX_CUDA(ctx, up(long_row.data(), long_row.size() * 4, (void **)&A->d_long_row_dist));
-  HPCX_CUDA(ctx, up(long_off.data(), long_off.size() * 4, (void **)&A->d_long_off_dist));
+  // One row-block table [interior blocks | boundary blocks] over the device-resident row_ptr
+  // (csr_plan.cu), cut wherever the row kind changes.
+  uint8_t *d_kind = nullptr;
+  HPCX_CUDA(ctx, cudaMalloc((void **)&d_kind, std::max<size_t>((size_t)nloc, 1)));
+  cudaError_t ke = cudaMemcpy(d_kind, row_kind, (size_t)nloc, cudaMemcpyHostToDevice);
+  std::vector<RowBlock> all;
+  int64_t n0 = 0, nchunks = 0;
+  hpcx_status st = ke == cudaSuccess
+                       ? csr_plan_rowblocks(A, d_kind, A->max_row_len, &A->d_blocks_dist, &all, &n0, &A->d_long_row_dist,
+                                            &A->d_long_off_dist, &A->nlong_dist, &nchunks)
+                       : fail(ctx, HPCX_CUDA_ERROR, std::string("row_kind upload: ") + cudaGetErrorString(ke));
+  cudaFree(d_kind);
+  if (st != HPCX_OK) return st;
+  A->h_blocks_int.assign(all.begin(), all.begin() + n0);
+  A->h_blocks_bnd.assign(all.begin() + n0, all.end());
+  A->d_blocks_int = A->d_blocks_dist;
+  A->d_blocks_bnd = A->d_blocks_dist + n0;
   return HPCX_OK;
 }
 
@@ -834,53 +791,39 @@ static inline void *dot_slot(hpcx_csr A, int64_t first) {
   return A->dot_part ? static_cast<char *>(A->dot_part) + first * A->es : nullptr;
 }
 
-// Transport 1, all on the caller's stream:
-//   push kernel (gather + peer stores + flags) ; interior rows ; wait for the source ranks'
-//   flags ; boundary rows ; ack to the source ranks.
+// Transport 1: ONE launch per product on the caller's stream.  Grid = [push CTAs | interior row
+// blocks | boundary row blocks]: the push CTAs run first (gather + peer stores + flags), the
+// interior blocks overlap the neighbours' pushes, the boundary blocks acquire the flags themselves
+// and the last of them acks the source ranks (round 1 needed five launches for the same).
 static hpcx_status spmv_dist_peer(hpcx_csr A, char *xfull, void *y_local, cudaStream_t cs) {
   hpcx_ctx ctx = A->ctx;
-  const uint32_t epoch = ++A->epoch;
-  hpcx_status rc;
-  if (A->nseg) {
-    HPCX_RANGE("spmv_dist: push boundary x (peer stores)");
-    int64_t longest = 0;
-    for (int q = 0; q < ctx->nranks; ++q) longest = std::max(longest, A->send_counts[q]);
-    dim3 grid((unsigned)std::min<int64_t>(std::max<int64_t>((longest + 255) / 256, 1), ctx->sm_count * 2),
-              (unsigned)A->nseg);
-    if (A->dtype == HPCX_F64)
-      push_boundary_x_kernel<double><<<grid, 256, 0, cs>>>((const double *)xfull, A->d_send_idx,
-                                                           A->d_seg_start, A->d_seg_rank, A->d_seg_dst,
-                                                           A->d_seg_flag, A->d_sync, epoch, peer_wait_of(ctx));
-    else
-      push_boundary_x_kernel<float><<<grid, 256, 0, cs>>>((const float *)xfull, A->d_send_idx,
-                                                          A->d_seg_start, A->d_seg_rank, A->d_seg_dst,
-                                                          A->d_seg_flag, A->d_sync, epoch, peer_wait_of(ctx));
-    rc = after_launch(ctx, "push_boundary_x_kernel");
-    if (rc != HPCX_OK) return rc;
-  }
-  {
-    HPCX_RANGE("spmv_dist: interior rows");
-    rc = spmv_launch_blocks(A, A->d_blocks_int, (int64_t)A->h_blocks_int.size(), xfull, y_local, cs,
-                            dot_slot(A, 0));
-  }
+  HPCX_RANGE("spmv_dist: one launch (push | interior | boundary + ack)");
+  SpmvDistArgs da;
+  da.epoch = ++A->epoch;
+  da.nseg = A->nseg;
+  da.nsrc = A->nsrc;
+  da.n_int = (int)A->h_blocks_int.size();
+  da.n_bnd = (int)A->h_blocks_bnd.size();
+  int64_t longest = 0;
+  for (int q = 0; q < ctx->nranks; ++q) longest = std::max(longest, A->send_counts[q]);
+  da.push_per_seg = (int)std::min<int64_t>(std::max<int64_t>((longest + 2047) / 2048, 1), 16);
+  da.npush = A->nseg * da.push_per_seg;
+  da.send_idx = A->d_send_idx;
+  da.seg_start = A->d_seg_start;
+  da.seg_rank = A->d_seg_rank;
+  da.seg_dst = A->d_seg_dst;
+  da.seg_flag = A->d_seg_flag;
+  da.src_rank = A->d_src_rank;
+  da.src_ack = A->d_src_ack;
+  da.sync = A->d_sync;
+  da.pw = peer_wait_of(ctx);
+  if (A->nsrc > 0 && da.n_bnd == 0)
+    return fail(ctx, HPCX_INVALID_ARG, "halo entries are received but no row is marked as a boundary row");
+  hpcx_status rc = spmv_launch_blocks(A, A->d_blocks_dist, (int64_t)da.n_int + da.n_bnd, xfull, y_local, cs,
+                                      dot_slot(A, 0), &da);
   if (rc != HPCX_OK) return rc;
-  if (A->nsrc) {
-    HPCX_RANGE("spmv_dist: wait for the neighbours' flags");
-    halo_x_ready_kernel<<<1, 64, 0, cs>>>(A->d_sync, A->d_src_rank, A->nsrc, epoch, peer_wait_of(ctx));
-    rc = after_launch(ctx, "halo_x_ready_kernel");
-    if (rc != HPCX_OK) return rc;
-  }
-  rc = spmv_launch_blocks(A, A->d_blocks_bnd, (int64_t)A->h_blocks_bnd.size(), xfull, y_local, cs,
-                          dot_slot(A, (int64_t)A->h_blocks_int.size()));
-  if (rc != HPCX_OK) return rc;
-  rc = spmv_launch_fixup_tables(A, A->d_long_row_dist, A->d_long_off_dist, A->nlong_dist, y_local, cs, xfull,
-                                dot_slot(A, (int64_t)(A->h_blocks_int.size() + A->h_blocks_bnd.size())));
-  if (rc != HPCX_OK) return rc;
-  if (A->nsrc) {
-    halo_x_ack_kernel<<<1, 64, 0, cs>>>(A->d_src_ack, A->nsrc, epoch);
-    rc = after_launch(ctx, "halo_x_ack_kernel");
-  }
-  return rc;
+  return spmv_launch_fixup_tables(A, A->d_long_row_dist, A->d_long_off_dist, A->nlong_dist, y_local, cs, xfull,
+                                  dot_slot(A, (int64_t)da.n_int + da.n_bnd));
 }
 
 hpcx_status hpcx_csr_x_buffer(hpcx_csr A, void **x_full) {
@@ -945,11 +888,11 @@ hpcx_status hpcx_spmv_dist(hpcx_csr A, const void *x_local, void *y_local, void 
     HPCX_CUDA(ctx, cudaEventRecord(ctx->ev[1], ms));
   }
   rc = spmv_launch_blocks(A, A->d_blocks_int, (int64_t)A->h_blocks_int.size(), xfull, y_local, cs,
-                          dot_slot(A, 0));
+                          dot_slot(A, 0), nullptr);
   if (rc != HPCX_OK) return rc;
   if (exchange) HPCX_CUDA(ctx, cudaStreamWaitEvent(cs, ctx->ev[1], 0));
   rc = spmv_launch_blocks(A, A->d_blocks_bnd, (int64_t)A->h_blocks_bnd.size(), xfull, y_local, cs,
-                          dot_slot(A, (int64_t)A->h_blocks_int.size()));
+                          dot_slot(A, (int64_t)A->h_blocks_int.size()), nullptr);
   if (rc != HPCX_OK) return rc;
   rc = spmv_launch_fixup_tables(A, A->d_long_row_dist, A->d_long_off_dist, A->nlong_dist, y_local, cs, xfull,
                                 dot_slot(A, (int64_t)(A->h_blocks_int.size() + A->h_blocks_bnd.size())));

@@ -25,6 +25,12 @@ using namespace hpcx;
 
 namespace hpcx {
 void csr_close_peers(hpcx_csr A);  // dist.cu
+// csr_plan.cu
+hpcx_status csr_scan_rowptr(hpcx_csr A, const void *src, int idx_bytes, int mem, int64_t *maxlen,
+                            int64_t *nnz_long_rows);
+hpcx_status csr_plan_rowblocks(hpcx_csr A, const uint8_t *d_kind, int64_t maxlen, RowBlock **d_blocks,
+                               std::vector<RowBlock> *host, int64_t *n0, int32_t **d_long_row,
+                               int32_t **d_long_off, int64_t *nlong, int64_t *nchunks);
 }
 
 namespace {
@@ -56,14 +62,25 @@ struct StreamSmem {
   static constexpr int kBytes = kWsum + (kThreads / 32) * (int)sizeof(T);
 };
 
-// DOT: additionally emits dot_part[blockIdx.x] = sum over the block's rows of y_i * x_i (square
+constexpr int kSyncData = 0, kSyncAck = 64, kSyncCount = 128, kSyncBnd = 129;  // words of the sync block (dist.cu)
+
+// x gather: the read-only path for owned entries; boundary row blocks of the one-launch distributed
+// product read halo slots a peer GPU wrote DURING this kernel, so they go to L2 (ld.global.cg) —
+// an L1 line fetched earlier by an interior CTA of the same SM could be stale.
+template <typename T>
+__device__ __forceinline__ T gather_x(const T *__restrict__ x, int c, bool from_l2) {
+  return from_l2 ? __ldcg(x + c) : __ldg(x + c);
+}
+
+// DOT: additionally emits dot_part[block] = sum over the block's rows of y_i * x_i (square
 // matrices: the fused q = A*p, <p, q> of the CG step, cg.cu), reduced in a fixed order.
-template <typename T, int TILE, bool DOT>
+// DIST: the one-launch distributed product (SpmvDistArgs, spmv.cuh).
+template <typename T, int TILE, bool DOT, bool DIST>
 __global__ void __launch_bounds__(kThreads)
 spmv_stream_kernel(const int32_t *__restrict__ row_ptr, const int32_t *__restrict__ col,
                    const T *__restrict__ val, const T *__restrict__ x, T *__restrict__ y,
                    const RowBlock *__restrict__ blocks, T *__restrict__ partials,
-                   T *__restrict__ dot_part) {
+                   T *__restrict__ dot_part, const __grid_constant__ SpmvDistArgs da) {
   extern __shared__ __align__(128) unsigned char smem[];
   using L = StreamSmem<T, TILE>;
   T *sval = reinterpret_cast<T *>(smem);
@@ -72,9 +89,34 @@ spmv_stream_kernel(const int32_t *__restrict__ row_ptr, const int32_t *__restric
   T *wsum = reinterpret_cast<T *>(smem + L::kWsum);
 
   const int tid = threadIdx.x;
+  int bidx = blockIdx.x;
+  bool halo = false;  // this block's rows read halo slots of x
+  if constexpr (DIST) {
+    if ((int)blockIdx.x < da.npush) {
+      // ---- push role: segment s of the send list goes into rank seg_rank[s]'s halo slots
+      const int sgm = blockIdx.x / da.push_per_seg, j = blockIdx.x % da.push_per_seg;
+      // the destination must have finished reading the previous product's halo (its ack)
+      if (tid == 0) wait_flag(da.sync + kSyncAck + da.seg_rank[sgm], da.epoch - 1, da.pw);
+      __syncthreads();
+      const int a = da.seg_start[sgm], e = da.seg_start[sgm + 1];
+      T *dst = static_cast<T *>(da.seg_dst[sgm]);
+      for (int i = a + j * kThreads + tid; i < e; i += da.push_per_seg * kThreads) dst[i - a] = __ldg(x + da.send_idx[i]);
+      __threadfence_system();
+      __syncthreads();
+      if (tid == 0 && (atomicAdd(da.sync + kSyncCount, 1u) + 1) % (uint32_t)da.npush == 0)
+        for (int k = 0; k < da.nseg; ++k) st_release_sys(da.seg_flag[k], da.epoch);
+      return;
+    }
+    bidx = blockIdx.x - da.npush;
+    halo = bidx >= da.n_int;
+    if (halo) {  // every source rank's entries of this product must have landed
+      if (tid < da.nsrc) wait_flag(da.sync + kSyncData + da.src_rank[tid], da.epoch, da.pw);
+      __syncthreads();
+    }
+  }
   // Block descriptor: 32 bytes, same for every thread (two broadcast 16-byte loads).
-  const int4 d0 = __ldg(reinterpret_cast<const int4 *>(blocks + blockIdx.x));
-  const longlong2 d1 = __ldg(reinterpret_cast<const longlong2 *>(blocks + blockIdx.x) + 1);
+  const int4 d0 = __ldg(reinterpret_cast<const int4 *>(blocks + bidx));
+  const longlong2 d1 = __ldg(reinterpret_cast<const longlong2 *>(blocks + bidx) + 1);
   const int row0 = d0.x, nrows = d0.y, part = d0.z, lanes = d0.w;
   const int64_t p0 = d1.x, p1 = d1.y;
   const int64_t p0a = p0 & ~int64_t(3);          // 16-byte aligned start in col_idx[]
@@ -112,7 +154,7 @@ spmv_stream_kernel(const int32_t *__restrict__ row_ptr, const int32_t *__restric
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
           const bool on = i + k < e;
-          xv[k] = on ? ldg_nc(x + scol[i + k]) : T(0);
+          xv[k] = on ? gather_x(x, scol[i + k], halo) : T(0);
           vv[k] = on ? sval[i + k] : T(0);
         }
 #pragma unroll
@@ -122,7 +164,7 @@ spmv_stream_kernel(const int32_t *__restrict__ row_ptr, const int32_t *__restric
       y[row0 + r] = s;
       if constexpr (DOT) dot = add_rn(dot, mul_rn(s, ldg_nc(x + row0 + r)));
     }
-    if constexpr (!DOT) return;
+    if constexpr (!DOT && !DIST) return;
   } else {
 
   // Products in place. Four gathers in flight per thread per round.
@@ -131,7 +173,7 @@ spmv_stream_kernel(const int32_t *__restrict__ row_ptr, const int32_t *__restric
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
       const int i = base + k * kThreads;
-      xv[k] = i < cnt ? ldg_nc(x + scol[i]) : T(0);
+      xv[k] = i < cnt ? gather_x(x, scol[i], halo) : T(0);
     }
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
@@ -188,7 +230,15 @@ spmv_stream_kernel(const int32_t *__restrict__ row_ptr, const int32_t *__restric
       T t = wsum[0];
 #pragma unroll
       for (int w = 1; w < kThreads / 32; ++w) t = add_rn(t, wsum[w]);
-      dot_part[blockIdx.x] = t;
+      dot_part[bidx] = t;
+    }
+  }
+  if constexpr (DIST) {
+    if (halo) {
+      // the last boundary block to finish tells the source ranks that their entries have been read
+      __syncthreads();
+      if (tid == 0 && (atomicAdd(da.sync + kSyncBnd, 1u) + 1) % (uint32_t)da.n_bnd == 0)
+        for (int k = 0; k < da.nsrc; ++k) st_release_sys(da.src_ack[k], da.epoch);
     }
   }
 }
@@ -252,82 +302,39 @@ spmv_sell_kernel(const int64_t *__restrict__ slice_ptr, const int32_t *__restric
   y[perm[srow]] = s;
 }
 
-// Threads per row of a block.  Rows no longer than short_row_max (a per-matrix option) all take
-// the fused one-thread-per-row path (lanes = 1, oracle order); otherwise lanes grow with the mean
-// row length and are raised until the block's longest row costs a lane at most 64 entries.
-int lanes_for(int64_t nnz_blk, int64_t nrows, int64_t max_len, int short_row_max) {
-  if (nrows <= 0) return 1;
-  const int64_t avg = (nnz_blk + nrows - 1) / nrows;
-  if (nrows == 1 && nnz_blk > 256) return 0;
-  if (max_len <= short_row_max) return 1;
-  int lanes = avg <= 16 ? 2 : avg <= 32 ? 4 : avg <= 64 ? 8 : avg <= 128 ? 16 : 32;
-  while (lanes < 32 && max_len > 64 * (int64_t)lanes) lanes <<= 1;
-  return lanes;
-}
-
-// Greedy row blocking. `kind` (may be null) forces a cut wherever the row kind changes
-// and `want` selects which kind to emit (distributed interior / boundary tables).
-void build_rowblocks(const int64_t *rp, int64_t nrows, int tile, int short_row_max, const uint8_t *kind,
-                     int want, std::vector<RowBlock> &out, std::vector<int32_t> *long_row,
-                     std::vector<int32_t> *long_off) {
-  int64_t r = 0;
-  int32_t nparts = long_off && !long_off->empty() ? long_off->back() : 0;
-  if (long_off && long_off->empty()) long_off->push_back(0);
-  while (r < nrows) {
-    if (kind && kind[r] != want) {
-      ++r;
-      continue;
-    }
-    const int64_t len = rp[r + 1] - rp[r];
-    if (len > tile) {
-      for (int64_t p = rp[r]; p < rp[r + 1]; p += tile) {
-        RowBlock b{(int32_t)r, 1, nparts++, 0, p, std::min<int64_t>(p + tile, rp[r + 1])};
-        out.push_back(b);
-      }
-      if (long_row) long_row->push_back((int32_t)r);
-      if (long_off) long_off->push_back(nparts);
-      ++r;
-      continue;
-    }
-    const int64_t r0 = r, p0 = rp[r];
-    int64_t max_len = 0;
-    while (r < nrows && r - r0 < tile && rp[r + 1] - p0 <= tile && (!kind || kind[r] == want)) {
-      max_len = std::max(max_len, rp[r + 1] - rp[r]);
-      ++r;
-    }
-    RowBlock b{(int32_t)r0, (int32_t)(r - r0), -1, lanes_for(rp[r] - p0, r - r0, max_len, short_row_max), p0, rp[r]};
-    out.push_back(b);
-  }
-}
-
-template <typename T, int TILE, bool DOT>
+template <typename T, int TILE, bool DOT, bool DIST>
 hpcx_status launch_stream_t(hpcx_csr A, const RowBlock *d_blocks, int64_t nblocks, const T *x, T *y,
-                            T *dot_part, cudaStream_t s) {
-  if (nblocks == 0) return HPCX_OK;
+                            T *dot_part, cudaStream_t s, const SpmvDistArgs &da) {
+  const int64_t grid = nblocks + (DIST ? da.npush : 0);
+  if (grid == 0) return HPCX_OK;
   using L = StreamSmem<T, TILE>;
-  if (hpcx_status st = ensure_dyn_smem(A->ctx, (const void *)spmv_stream_kernel<T, TILE, DOT>, L::kBytes)) return st;
-  spmv_stream_kernel<T, TILE, DOT><<<(unsigned)nblocks, kThreads, L::kBytes, s>>>(
-      A->d_row_ptr, A->d_col, (const T *)A->d_val, x, y, d_blocks, (T *)A->d_partials, dot_part);
+  if (hpcx_status st = ensure_dyn_smem(A->ctx, (const void *)spmv_stream_kernel<T, TILE, DOT, DIST>, L::kBytes)) return st;
+  spmv_stream_kernel<T, TILE, DOT, DIST><<<(unsigned)grid, kThreads, L::kBytes, s>>>(
+      A->d_row_ptr, A->d_col, (const T *)A->d_val, x, y, d_blocks, (T *)A->d_partials, dot_part, da);
   return after_launch(A->ctx, "spmv_stream_kernel");
 }
 
-template <typename T>
-hpcx_status launch_stream(hpcx_csr A, const RowBlock *d_blocks, int64_t nblocks, const T *x, T *y,
-                          cudaStream_t s, T *dot_part = nullptr) {
-  if (dot_part) {
-    switch (A->tile) {
-      case 1024: return launch_stream_t<T, 1024, true>(A, d_blocks, nblocks, x, y, dot_part, s);
-      case 2048: return launch_stream_t<T, 2048, true>(A, d_blocks, nblocks, x, y, dot_part, s);
-      case 4096: return launch_stream_t<T, 4096, true>(A, d_blocks, nblocks, x, y, dot_part, s);
-      default: return fail(A->ctx, HPCX_INVALID_ARG, "tile_nnz must be 1024, 2048 or 4096");
-    }
-  }
+template <typename T, bool DOT, bool DIST>
+hpcx_status launch_stream_tile(hpcx_csr A, const RowBlock *d_blocks, int64_t nblocks, const T *x, T *y, T *dot_part,
+                               cudaStream_t s, const SpmvDistArgs &da) {
   switch (A->tile) {
-    case 1024: return launch_stream_t<T, 1024, false>(A, d_blocks, nblocks, x, y, nullptr, s);
-    case 2048: return launch_stream_t<T, 2048, false>(A, d_blocks, nblocks, x, y, nullptr, s);
-    case 4096: return launch_stream_t<T, 4096, false>(A, d_blocks, nblocks, x, y, nullptr, s);
+    case 1024: return launch_stream_t<T, 1024, DOT, DIST>(A, d_blocks, nblocks, x, y, dot_part, s, da);
+    case 2048: return launch_stream_t<T, 2048, DOT, DIST>(A, d_blocks, nblocks, x, y, dot_part, s, da);
+    case 4096: return launch_stream_t<T, 4096, DOT, DIST>(A, d_blocks, nblocks, x, y, dot_part, s, da);
     default: return fail(A->ctx, HPCX_INVALID_ARG, "tile_nnz must be 1024, 2048 or 4096");
   }
+}
+
+// da != nullptr: the one-launch distributed product (push CTAs + flag waits + ack in the kernel)
+template <typename T>
+hpcx_status launch_stream(hpcx_csr A, const RowBlock *d_blocks, int64_t nblocks, const T *x, T *y,
+                          cudaStream_t s, T *dot_part = nullptr, const SpmvDistArgs *da = nullptr) {
+  static const SpmvDistArgs none{};
+  if (da)
+    return dot_part ? launch_stream_tile<T, true, true>(A, d_blocks, nblocks, x, y, dot_part, s, *da)
+                    : launch_stream_tile<T, false, true>(A, d_blocks, nblocks, x, y, nullptr, s, *da);
+  return dot_part ? launch_stream_tile<T, true, false>(A, d_blocks, nblocks, x, y, dot_part, s, none)
+                  : launch_stream_tile<T, false, false>(A, d_blocks, nblocks, x, y, nullptr, s, none);
 }
 
 template <typename T>
@@ -385,6 +392,10 @@ hpcx_status spmv_device(hpcx_csr A, const T *x, T *y, cudaStream_t s) {
         st = launch_fixup<T>(A, A->d_long_row, A->d_long_off, A->nlong, y, s, x,
                              A->dot_part ? (T *)A->dot_part + A->h_blocks.size() : nullptr);
       return st;
+    case HPCX_SPMV_HUB:
+      if (A->dot_part)  // the fused <x, y> of the CG step lives in the STREAM kernel (its tables always exist)
+        return fail(A->ctx, HPCX_UNSUPPORTED, "fused dot product needs the STREAM kernel");
+      return hub_launch(A, x, y, s);
     case HPCX_SPMV_VECTOR: return launch_vector<T>(A, x, y, s);
     case HPCX_SPMV_SELL: return launch_sell<T>(A, x, y, s);
     default: return fail(A->ctx, HPCX_INVALID_ARG, "unknown SpMV kernel");
@@ -449,6 +460,7 @@ void build_sell(hpcx_csr A, const int64_t *rp, const int32_t *col, const T *val,
 
 void free_csr(hpcx_csr A) {
   hpcx::csr_close_peers(A);
+  hpcx::hub_free(A);
   cudaFree(A->d_row_ptr);
   cudaFree(A->d_col);
   cudaFree(A->d_val);
@@ -468,8 +480,7 @@ void free_csr(hpcx_csr A) {
   cudaFree(A->d_send_idx);
   cudaFree(A->d_sendbuf);
   cudaFree(A->d_xfull);
-  cudaFree(A->d_blocks_int);
-  cudaFree(A->d_blocks_bnd);
+  cudaFree(A->d_blocks_dist);
   cudaFree(A->d_long_row_dist);
   cudaFree(A->d_long_off_dist);
   delete A;
@@ -489,11 +500,11 @@ hpcx_status upload_vec(hpcx_ctx ctx, const std::vector<V> &h, V **d) {
 namespace hpcx {
 // Shared with dist.cu.
 hpcx_status spmv_launch_blocks(hpcx_csr A, const RowBlock *d_blocks, int64_t nblocks, const void *x,
-                               void *y, cudaStream_t s, void *dot_part) {
+                               void *y, cudaStream_t s, void *dot_part, const SpmvDistArgs *da) {
   if (A->dtype == HPCX_F64)
     return launch_stream<double>(A, d_blocks, nblocks, (const double *)x, (double *)y, s,
-                                 (double *)dot_part);
-  return launch_stream<float>(A, d_blocks, nblocks, (const float *)x, (float *)y, s, (float *)dot_part);
+                                 (double *)dot_part, da);
+  return launch_stream<float>(A, d_blocks, nblocks, (const float *)x, (float *)y, s, (float *)dot_part, da);
 }
 hpcx_status spmv_launch_fixup_tables(hpcx_csr A, const int32_t *long_row, const int32_t *long_off,
                                      int64_t nlong, void *y, cudaStream_t s, const void *x,
@@ -503,11 +514,6 @@ hpcx_status spmv_launch_fixup_tables(hpcx_csr A, const int32_t *long_row, const 
                                 (double *)dot_part);
   return launch_fixup<float>(A, long_row, long_off, nlong, (float *)y, s, (const float *)x,
                              (float *)dot_part);
-}
-void spmv_build_rowblocks(const int64_t *rp, int64_t nrows, int tile, int short_row_max, const uint8_t *kind,
-                          int want, std::vector<RowBlock> &out, std::vector<int32_t> *long_row,
-                          std::vector<int32_t> *long_off) {
-  build_rowblocks(rp, nrows, tile, short_row_max, kind, want, out, long_row, long_off);
 }
 }  // namespace hpcx
 
@@ -612,7 +618,7 @@ hpcx_status spmv_host_pipelined(hpcx_csr A, const void *x, void *y, cudaStream_t
       waited = need;
     }
     const int64_t b0 = A->pipe_first[c], b1 = A->pipe_first[c + 1];
-    hpcx_status st = hpcx::spmv_launch_blocks(A, A->d_blocks + b0, b1 - b0, A->d_x, A->d_y, s, nullptr);
+    hpcx_status st = hpcx::spmv_launch_blocks(A, A->d_blocks + b0, b1 - b0, A->d_x, A->d_y, s, nullptr, nullptr);
     if (st != HPCX_OK) return st;
     HPCX_CUDA(ctx, cudaEventRecord(ey[c], s));
     HPCX_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_out, ey[c], 0));
@@ -653,7 +659,7 @@ hpcx_status hpcx_csr_create(hpcx_ctx ctx, const hpcx_csr_desc *d, const hpcx_csr
   A->dtype = d->dtype;
   A->es = (int)dtype_size(d->dtype);
   A->idx_bytes = d->idx_bytes;
-  A->kernel = opts && opts->kernel ? opts->kernel : HPCX_SPMV_STREAM;
+  A->kernel = opts ? opts->kernel : HPCX_SPMV_AUTO;
   A->tile = opts && opts->tile_nnz ? opts->tile_nnz : 2048;
   A->lanes_per_row = opts ? opts->lanes_per_row : 0;
   A->short_row_max = opts && opts->short_row_max > 0 ? opts->short_row_max : 48;
@@ -663,7 +669,7 @@ hpcx_status hpcx_csr_create(hpcx_ctx ctx, const hpcx_csr_desc *d, const hpcx_csr
     delete A;
     return fail(ctx, HPCX_INVALID_ARG, "tile_nnz must be 1024, 2048 or 4096");
   }
-  if (A->kernel < HPCX_SPMV_STREAM || A->kernel > HPCX_SPMV_SELL || A->sell_c < 1 ||
+  if (A->kernel < HPCX_SPMV_AUTO || A->kernel > HPCX_SPMV_HUB || A->sell_c < 1 ||
       A->sell_c > kThreads || kThreads % A->sell_c != 0) {
     delete A;
     return fail(ctx, HPCX_INVALID_ARG, "bad SpMV kernel / SELL slice height");
@@ -687,70 +693,36 @@ hpcx_status hpcx_csr_create(hpcx_ctx ctx, const hpcx_csr_desc *d, const hpcx_csr
     }                                                                                         \
   } while (0)
 
-  // Host copy of row_ptr as int64 (drives every table build).
-  std::vector<int64_t> rp(d->nrows + 1);
-  {
-    const size_t bytes = (size_t)(d->nrows + 1) * d->idx_bytes;
-    std::vector<unsigned char> tmp;
-    const void *src = d->row_ptr;
-    if (d->mem != HPCX_MEM_HOST) {
-      tmp.resize(bytes);
-      HPCX_TRY_CUDA(cudaMemcpy(tmp.data(), d->row_ptr, bytes, cudaMemcpyDeviceToHost));
-      src = tmp.data();
-    }
-    if (d->idx_bytes == 4)
-      for (int64_t i = 0; i <= d->nrows; ++i) rp[i] = ((const int32_t *)src)[i];
-    else
-      for (int64_t i = 0; i <= d->nrows; ++i) rp[i] = ((const int64_t *)src)[i];
-  }
-  if (rp[0] != 0 || rp[d->nrows] != d->nnz) {
-    free_csr(A);
-    return fail(ctx, HPCX_INVALID_ARG, "row_ptr[0] != 0 or row_ptr[nrows] != nnz");
-  }
-  for (int64_t i = 0; i < d->nrows; ++i)
-    if (rp[i + 1] < rp[i]) {
-      free_csr(A);
-      return fail(ctx, HPCX_INVALID_ARG, "row_ptr is not non-decreasing");
-    }
-  // Row-length histogram: bin 0 = empty, bin k = 2^(k-1) <= len < 2^k.
-  for (int64_t i = 0; i < d->nrows; ++i) {
-    int64_t len = rp[i + 1] - rp[i];
-    int b = 0;
-    while (len) {
-      ++b;
-      len >>= 1;
-    }
-    A->bins[b]++;
-  }
-
   // Device CSR. Padded so that 16-byte aligned bulk copies never run past the allocation.
   A->nnz_alloc = round_up(d->nnz, 4) + 8;
   HPCX_TRY_CUDA(cudaMalloc((void **)&A->d_row_ptr, (size_t)(d->nrows + 1) * 4));
   HPCX_TRY_CUDA(cudaMalloc((void **)&A->d_col, (size_t)A->nnz_alloc * 4));
   HPCX_TRY_CUDA(cudaMalloc(&A->d_val, (size_t)A->nnz_alloc * A->es));
-  HPCX_TRY_CUDA(cudaMemset(A->d_col + d->nnz, 0, (size_t)(A->nnz_alloc - d->nnz) * 4));
-  HPCX_TRY_CUDA(cudaMemset((char *)A->d_val + (size_t)d->nnz * A->es, 0,
-                           (size_t)(A->nnz_alloc - d->nnz) * A->es));
-  {
-    std::vector<int32_t> rp32(d->nrows + 1);
-    for (int64_t i = 0; i <= d->nrows; ++i) rp32[i] = (int32_t)rp[i];
-    HPCX_TRY_CUDA(cudaMemcpy(A->d_row_ptr, rp32.data(), rp32.size() * 4, cudaMemcpyHostToDevice));
-  }
+  HPCX_TRY_CUDA(cudaMemsetAsync(A->d_col + d->nnz, 0, (size_t)(A->nnz_alloc - d->nnz) * 4, ctx->compute));
+  HPCX_TRY_CUDA(cudaMemsetAsync((char *)A->d_val + (size_t)d->nnz * A->es, 0,
+                                (size_t)(A->nnz_alloc - d->nnz) * A->es, ctx->compute));
+  // row_ptr: validated, narrowed to int32 and binned by one kernel over the device copy
+  // (csr_plan.cu); nothing loops over the rows on the host
+  int64_t maxlen = 0, nnz_long_rows = 0;
+  HPCX_TRY(csr_scan_rowptr(A, d->row_ptr, d->idx_bytes, d->mem, &maxlen, &nnz_long_rows));
+  A->max_row_len = maxlen;
   if (d->nnz) {
-    HPCX_TRY_CUDA(cudaMemcpy(A->d_col, d->col_idx, (size_t)d->nnz * 4, cudaMemcpyDefault));
-    HPCX_TRY_CUDA(cudaMemcpy(A->d_val, d->values, (size_t)d->nnz * A->es, cudaMemcpyDefault));
+    HPCX_TRY_CUDA(cudaMemcpyAsync(A->d_col, d->col_idx, (size_t)d->nnz * 4, cudaMemcpyDefault, ctx->compute));
+    HPCX_TRY_CUDA(cudaMemcpyAsync(A->d_val, d->values, (size_t)d->nnz * A->es, cudaMemcpyDefault, ctx->compute));
+    HPCX_TRY_CUDA(cudaStreamSynchronize(ctx->compute));
   }
 
   if (d->nnz) {
     // every column index must address x: one pass over the device copy
     int32_t *d_mm = nullptr, mm[2] = {INT32_MAX, INT32_MIN};
     HPCX_TRY_CUDA(cudaMalloc((void **)&d_mm, 8));
-    cudaError_t e = cudaMemcpy(d_mm, mm, 8, cudaMemcpyHostToDevice);
+    cudaError_t e = cudaMemcpyAsync(d_mm, mm, 8, cudaMemcpyHostToDevice, ctx->compute);
     if (e == cudaSuccess) {
       const int grid = (int)std::min<int64_t>((d->nnz + 255) / 256, (int64_t)ctx->sm_count * 16);
-      col_range_kernel<<<grid, 256>>>(A->d_col, d->nnz, d_mm);
+      col_range_kernel<<<grid, 256, 0, ctx->compute>>>(A->d_col, d->nnz, d_mm);
       ctx->launches++;
-      e = cudaMemcpy(mm, d_mm, 8, cudaMemcpyDeviceToHost);
+      e = cudaMemcpyAsync(mm, d_mm, 8, cudaMemcpyDeviceToHost, ctx->compute);
+      if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->compute);
     }
     cudaFree(d_mm);
     HPCX_TRY_CUDA(e);
@@ -762,20 +734,19 @@ hpcx_status hpcx_csr_create(hpcx_ctx ctx, const hpcx_csr_desc *d, const hpcx_csr
     }
   }
 
-  // STREAM tables are always built (the distributed path and the bins use them).
+  // STREAM tables are always built (the distributed path and the CG step use them).
   {
-    std::vector<int32_t> long_row, long_off;
-    build_rowblocks(rp.data(), d->nrows, A->tile, A->short_row_max, nullptr, 0, A->h_blocks, &long_row, &long_off);
-    A->nlong = (int64_t)long_row.size();
-    HPCX_TRY(upload_vec(ctx, A->h_blocks, &A->d_blocks));
-    HPCX_TRY(upload_vec(ctx, long_row, &A->d_long_row));
-    HPCX_TRY(upload_vec(ctx, long_off, &A->d_long_off));
-    const size_t nparts = long_off.empty() ? 0 : (size_t)long_off.back();
-    HPCX_TRY_CUDA(cudaMalloc(&A->d_partials, std::max<size_t>(nparts, 1) * A->es));
+    int64_t n0 = 0, nchunks = 0;
+    HPCX_TRY(csr_plan_rowblocks(A, nullptr, maxlen, &A->d_blocks, &A->h_blocks, &n0, &A->d_long_row, &A->d_long_off,
+                                &A->nlong, &nchunks));
+    HPCX_TRY_CUDA(cudaMalloc(&A->d_partials, std::max<size_t>((size_t)nchunks, 1) * A->es));
   }
 
   if (A->kernel == HPCX_SPMV_SELL) {
-    // The SELL repack needs host copies of col/val.
+    // The SELL repack runs on the host: copies of row_ptr (widened), col and val.
+    std::vector<int32_t> rp32(d->nrows + 1);
+    HPCX_TRY_CUDA(cudaMemcpy(rp32.data(), A->d_row_ptr, rp32.size() * 4, cudaMemcpyDeviceToHost));
+    std::vector<int64_t> rp(rp32.begin(), rp32.end());
     std::vector<int32_t> hcol(d->nnz);
     std::vector<unsigned char> hval((size_t)d->nnz * A->es);
     if (d->nnz) {
@@ -798,8 +769,20 @@ hpcx_status hpcx_csr_create(hpcx_ctx ctx, const hpcx_csr_desc *d, const hpcx_csr
     HPCX_TRY(upload_vec(ctx, A->h_slice_ptr, &A->d_slice_ptr));
   }
   // the memsets and copies above ran on the legacy stream; the context's streams are
-  // non-blocking, so make everything visible before the first product is queued on them
+  // non-blocking, so make everything visible before anything is queued on them
   HPCX_TRY_CUDA(cudaDeviceSynchronize());
+  if (A->kernel == HPCX_SPMV_AUTO || A->kernel == HPCX_SPMV_HUB) {
+    // AUTO: power-law structure (a quarter of the nonzeros in rows longer than 256) AND popular
+    // columns (hub coverage >= 10 %) select the HUB kernel; everything else streams.
+    const bool want = A->kernel == HPCX_SPMV_HUB || nnz_long_rows * 4 > d->nnz;
+    if (want && d->nnz > 0) {
+      HPCX_TRY(hub_build(A));
+      if (A->kernel == HPCX_SPMV_AUTO) A->kernel = A->hub.coverage >= 0.10 ? HPCX_SPMV_HUB : HPCX_SPMV_STREAM;
+      if (A->kernel != HPCX_SPMV_HUB) hub_free(A);
+    } else if (A->kernel == HPCX_SPMV_AUTO) {
+      A->kernel = HPCX_SPMV_STREAM;
+    }
+  }
   *out = A;
   return HPCX_OK;
 }

@@ -17,6 +17,54 @@ struct RowBlock {
 };
 static_assert(sizeof(RowBlock) == 32, "RowBlock is loaded as two 16-byte words");
 
+// Distributed product in ONE launch (transport 1, dist.cu): the grid is [push CTAs | interior row
+// blocks | boundary row blocks].  Push CTAs gather this rank's boundary x entries and store them
+// straight into the neighbours' halo slots over NVLink, then release the product number there;
+// boundary CTAs acquire the source ranks' flags before their first halo gather; the last boundary
+// CTA to finish tells the source ranks that their entries have been consumed (the ack the next
+// product's push waits for).
+struct SpmvDistArgs {
+  int npush = 0, push_per_seg = 1, nseg = 0;  // push CTAs: push_per_seg per destination segment
+  int n_int = 0, n_bnd = 0;                   // row blocks [0, n_int) read owned x only
+  int nsrc = 0;
+  uint32_t epoch = 0;
+  const int32_t *send_idx = nullptr;   // owned entries to gather, grouped by destination
+  const int32_t *seg_start = nullptr;  // nseg + 1 offsets into send_idx
+  const int32_t *seg_rank = nullptr;   // destination rank of each segment
+  void *const *seg_dst = nullptr;      // where each segment lands in the destination's [owned | halo] x
+  uint32_t *const *seg_flag = nullptr; // the destination's data flag for this rank
+  const int32_t *src_rank = nullptr;   // ranks this one receives from
+  uint32_t *const *src_ack = nullptr;  // their ack word for this rank
+  uint32_t *sync = nullptr;            // local block: data flags, acks, counters (dist.cu)
+  PeerWait pw;
+};
+
+// Tables of the HUB kernel (spmv_hub.cu), built on the device at create time.
+struct HubTables {
+  bool ready = false;
+  int K = 0;                    // hub columns (their x entries live in shared memory)
+  double coverage = 0.0;        // fraction of the nonzeros whose column is a hub column
+  // long part (rows of more than 32 entries): nonzero-balanced tiles of 256
+  int64_t nlong = 0, nnzL = 0, ntiles = 0;
+  int32_t *colL = nullptr;      // hub columns encoded as 0x80000000 | slot, padded to whole tiles
+  void *valL = nullptr;
+  uint8_t *rowstart = nullptr;  // bit i: nonzero i of the long part is the first of its row
+  int32_t *tile_seg0 = nullptr; // ntiles + 1: long rows that start before each tile
+  int32_t *lrow = nullptr;      // original row of each long row
+  int32_t *lrp = nullptr;       // nlong + 1 offsets into colL / valL
+  // short part (rows of 1..32 entries): one thread per row
+  int64_t nshort = 0, nnzS = 0;
+  int32_t *colS = nullptr;
+  void *valS = nullptr;
+  int32_t *srp = nullptr, *srow = nullptr;
+  int32_t *hub_col = nullptr;   // column of each hub slot
+  int64_t nwarps = 0;           // warp ranges of the persistent grid
+  void *head_out = nullptr, *tail_out = nullptr;  // per warp range partials
+};
+hpcx_status hub_build(hpcx_csr A);
+hpcx_status hub_launch(hpcx_csr A, const void *x, void *y, cudaStream_t s);
+void hub_free(hpcx_csr A);
+
 }  // namespace hpcx
 
 struct hpcx_csr_s {
@@ -32,6 +80,7 @@ struct hpcx_csr_s {
   // STREAM kernel tables
   std::vector<hpcx::RowBlock> h_blocks;
   hpcx::RowBlock *d_blocks = nullptr;
+  int64_t max_row_len = 0;
   int64_t nlong = 0;            // rows longer than a tile
   int32_t *d_long_row = nullptr;
   int32_t *d_long_off = nullptr;  // nlong + 1
@@ -45,6 +94,7 @@ struct hpcx_csr_s {
   int32_t *d_perm = nullptr, *d_slice_len = nullptr, *d_sell_col = nullptr;
   int64_t *d_slice_ptr = nullptr;
   void *d_sell_val = nullptr;
+  hpcx::HubTables hub;
   // staging for host operands
   void *d_x = nullptr, *d_y = nullptr;
   // host-x / host-y products: row chunks pipelined against the PCIe copies (spmv.cu: spmv_host_pipelined)
@@ -61,6 +111,8 @@ struct hpcx_csr_s {
   int32_t *d_send_idx = nullptr;
   void *d_sendbuf = nullptr;
   void *d_xfull = nullptr;  // [owned | halo]
+  // one table [interior blocks | boundary blocks] (csr_plan.cu); the two pointers below view it
+  hpcx::RowBlock *d_blocks_dist = nullptr;
   std::vector<hpcx::RowBlock> h_blocks_int, h_blocks_bnd;
   hpcx::RowBlock *d_blocks_int = nullptr, *d_blocks_bnd = nullptr;
   // transport 1 (peer stores, hpcx_csr_halo_transport): see dist.cu

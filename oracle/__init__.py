@@ -176,6 +176,16 @@ def spmv(rp, col, val, x, out=None):
     return y
 
 
+def spmv_wide(rp, col, val, x):
+    """fp32 matrix and vector, rows accumulated in double (orc_spmv_wide_f32): the yardstick for
+    rows too long for an fp32 running sum."""
+    assert val.dtype == np.float32
+    y = np.empty(len(rp) - 1, dtype=np.float64)
+    lib().orc_spmv_wide_f32(C.c_int64(len(y)), _p(np.ascontiguousarray(rp, dtype=np.int64)), _p(col), _p(val),
+                            _p(np.ascontiguousarray(x, dtype=np.float32)), _p(y))
+    return y
+
+
 def spmv_abs(rp, col, val, x):
     mag = np.empty(len(rp) - 1, dtype=np.float64)
     fn = lib().orc_spmv_abs_f64 if val.dtype == np.float64 else lib().orc_spmv_abs_f32

@@ -302,6 +302,21 @@ ORC_SPMV(orc_spmv_f32, float)
   }
 ORC_SPMV32(orc_spmv_i32_f64, double)
 ORC_SPMV32(orc_spmv_i32_f32, float)
+/* The same product with every row accumulated in double (fp32 x fp32 products are exact in
+ * double): the yardstick for rows so long that an fp32 running sum — the oracle's own included —
+ * carries more rounding error than the 1e-5 bar (C5's longest row has 238,875 entries: a
+ * sequential fp32 sum drifts by ~sqrt(n) ulps).  Tests compare BOTH the device result and
+ * orc_spmv_f32 with it. */
+ORC_API void orc_spmv_wide_f32(int64_t nrows, const int64_t *row_ptr, const int32_t *col, const float *val,
+                               const float *x, double *y) {
+#pragma omp parallel for schedule(dynamic, 4096)
+  for (int64_t i = 0; i < nrows; ++i) {
+    double s = 0;
+    for (int64_t p = row_ptr[i]; p < row_ptr[i + 1]; ++p) s = s + (double)val[p] * (double)x[col[p]];
+    y[i] = s;
+  }
+}
+
 /* Row-wise magnitude sum_p |a_p x_p| in double (the tolerance scale of SURVEY.md §8c). */
 #define ORC_SPMV_ABS(NAME, T)                                                              \
   ORC_API void NAME(int64_t nrows, const int64_t *row_ptr, const int32_t *col, const T *val, \

@@ -11,7 +11,7 @@ from util import assert_spmv_close, bits_equal, random_csr
 
 pytestmark = pytest.mark.gpu
 TOL = {np.dtype(np.float64): 1e-12, np.dtype(np.float32): 1e-5}
-KERNELS = [hp.SPMV_STREAM, hp.SPMV_VECTOR, hp.SPMV_SELL]
+KERNELS = [hp.SPMV_STREAM, hp.SPMV_VECTOR, hp.SPMV_SELL, hp.SPMV_HUB]
 
 
 def _run(ctx, rp, col, val, x, ncols=None, **opts):
@@ -249,12 +249,15 @@ def test_c4_full_size_256_cubed_vs_oracle(ctx):
     assert bits_equal(y, y_ref)
 
 
-@pytest.mark.parametrize("kernel", [hp.SPMV_AUTO, hp.SPMV_STREAM])
+@pytest.mark.parametrize("kernel", [hp.SPMV_AUTO, hp.SPMV_STREAM, hp.SPMV_HUB])
 def test_c5_full_size_rmat_scale24_vs_oracle(ctx, kernel):
     """configs[4] at FULL size (R-MAT scale 24, 2^28 edges -> 263.4 M merged nonzeros, fp32, longest
-    row 238,875): the device-assembled matrix is downloaded once and a random x is checked against
-    the oracle's product, norm-wise and row-wise 1e-5 — the size at which the long-row chunks, the
-    fix-up kernel and (AUTO) the hub kernel carry most of the nonzeros."""
+    row 238,875): the device-assembled matrix is downloaded once and a random x is checked, norm-wise
+    and row-wise at 1e-5, against the oracle's product with rows accumulated in DOUBLE.  At this row
+    length the fp32 running sum of the oracle itself is off by 1.9e-5 of max|y| (238,875 sequential
+    roundings), so oracle-vs-device in fp32 would measure the oracle's rounding, not the kernel's;
+    the test records that gap as well (bounded at 1e-4) and holds the device to the 1e-5 bar against
+    the wide sum.  This is the size at which the long-row paths and the HUB kernel carry the nonzeros."""
     scale = 24
     arrs = hp.synth_rmat_csr(ctx, scale, 16, 24, 4)
     try:
@@ -273,7 +276,9 @@ def test_c5_full_size_rmat_scale24_vs_oracle(ctx, kernel):
     finally:
         D.destroy()
     assert bits_equal(y, y2)  # deterministic: no atomics on the value path
-    assert_spmv_close(y, oracle.spmv(rp, col, val, x), oracle.spmv_abs(rp, col, val, x), 1e-5)
+    wide, mag = oracle.spmv_wide(rp, col, val, x), oracle.spmv_abs(rp, col, val, x)
+    assert_spmv_close(y, wide, mag, 1e-5)
+    assert_spmv_close(oracle.spmv(rp, col, val, x), wide, mag, 1e-4)  # the fp32 oracle's own rounding
 
 
 def test_managed_memory_operands(ctx):
