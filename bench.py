@@ -96,13 +96,24 @@ class ClockSampler:
 
 
 def build_local_problem(world: int, rank: int):
-    """This rank's slab of the (GRID*world) x GRID Laplacian in local numbering."""
+    """This rank's rows of the (GRID*world) x GRID Laplacian (global column indices), then the
+    library's own partitioner: hpcx_partition_rows for the bounds and the distributed localiser
+    (hpcx_csr_localize_rows + one exchange of column lists + hpcx_halo_send_lists) for the local
+    numbering and the halo tables.  No rank ever holds the global matrix."""
+    import libhpc_b200 as hp
+    from libhpc_b200 import dist as hd
     from libhpc_b200 import synth
     t = time.time()
-    L = synth.laplace2d_slab_local(GRID * world, GRID, rank * GRID, (rank + 1) * GRID)
-    L["recv_counts"], L["send_counts"] = synth.slab_counts(L, world, rank, GRID)
+    nrows_global = GRID * GRID * world
+    bounds = hp.partition_rows(nrows_global, None, world, 0)  # static chunking: one slab of grid rows per rank
+    assert int(bounds[rank]) == rank * GRID * GRID
+    rp, col, val = synth.laplace2d_rows(GRID * world, GRID, rank * GRID, (rank + 1) * GRID)
+    t1 = time.time()
+    L = hd.localize_rows_distributed(rp, col, val, bounds, rank, world, nrows_global)
     L["local_row_ptr"] = L["local_row_ptr"].astype(np.int32)
-    log(f"[rank {rank}] built slab: {L['nloc']} rows, {L['nnz_loc']} nnz in {time.time() - t:.1f}s")
+    L["partition_s"] = time.time() - t1
+    log(f"[rank {rank}] built slab: {L['nloc']} rows, {L['nnz_loc']} nnz in {t1 - t:.1f}s; partitioner "
+        f"{L['partition_s']:.2f}s ({L['nhalo']} halo columns, {L['nsend']} sends)")
     return L
 
 
@@ -323,7 +334,8 @@ def run_ours(args, rank: int, world: int, local: int):
     halo_s = time.time() - t - create_s
     log(f"[rank {rank}] hpcx_csr_create {create_s:.2f}s, halo tables {halo_s:.2f}s")
     setup_ms = {"hpcx_csr_create": max_over_ranks(create_s) * 1e3, "halo_tables": max_over_ranks(halo_s) * 1e3,
-                "host_matrix_build_python": max_over_ranks(build_s) * 1e3}
+                "partitioner_localize_rows": max_over_ranks(L["partition_s"]) * 1e3,
+                "host_matrix_build_python": max_over_ranks(build_s - L["partition_s"]) * 1e3}
 
     stream = torch.cuda.Stream()
     x_pin = torch.empty(nloc, dtype=torch.float64).pin_memory()
@@ -785,8 +797,9 @@ def sparse_extra(args, ctx, torch, stream, world, rank, barrier, max_over_ranks,
     n = 256
     zb = hp.partition_slabs(n, world)
     t = time.time()
-    L = synth.op27_slab_local(n, int(zb[rank]), int(zb[rank + 1]))
-    L["recv_counts"], L["send_counts"] = synth.slab_counts(L, world, rank, n * n)
+    rp_s, col_s, val_s = synth.op27_rows(n, int(zb[rank]), int(zb[rank + 1]))
+    L = hd.localize_rows_distributed(rp_s, col_s, val_s, zb * n * n, rank, world, n ** 3)
+    del rp_s, col_s, val_s
     L["local_row_ptr"] = L["local_row_ptr"].astype(np.int32)
     nloc = L["nloc"]
     A = hp.CsrMatrix(L["local_row_ptr"], L["local_col"], L["values"], ncols=nloc + L["nhalo"])

@@ -331,6 +331,23 @@ HPCX_API hpcx_status hpcx_csr_localize(int64_t nrows, const void *row_ptr, int32
                                        int64_t *send_counts, int32_t *send_idx,
                                        uint8_t *row_kind);
 
+/* The same tables from this rank's OWN rows only (no global matrix anywhere, no table of nrows
+ * entries): row_ptr has nloc + 1 entries starting at 0, col_global holds GLOBAL column indices.
+ * Step 1 (local) yields local_col, halo_gcol, recv_counts, row_kind; sizes->nsend is -1 until
+ * step 2.  The ranks then trade integer lists — every rank sends, to each owner q, the recv_counts[q]
+ * entries of its halo_gcol that q owns (contiguous, ascending) — and step 2 turns what the others
+ * asked of this rank (req_counts[q] columns from rank q, concatenated for q ascending) into
+ * send_idx; send_counts = req_counts.  Bit-identical to hpcx_csr_localize on the global matrix.
+ * libhpc_b200/dist.py: localize_rows_distributed does the exchange over torch.distributed. */
+HPCX_API hpcx_status hpcx_csr_localize_rows(int64_t nrows_global, int64_t nloc, const void *row_ptr,
+                                            int32_t idx_bytes, const int32_t *col_global,
+                                            const int64_t *bounds, int32_t nparts, int32_t rank,
+                                            hpcx_halo_sizes *sizes, int32_t *local_col,
+                                            int64_t *halo_gcol, int64_t *recv_counts, uint8_t *row_kind);
+HPCX_API hpcx_status hpcx_halo_send_lists(const int64_t *bounds, int32_t nparts, int32_t rank,
+                                          const int64_t *req_counts, const int64_t *requests,
+                                          int32_t *send_idx);
+
 /* ------------------------------------------------ multi-GPU transport (a13)
  * One process per GPU.  The caller bootstraps (e.g. through torch.distributed or MPI):
  * rank 0 calls hpcx_comm_unique_id, broadcasts the 128 bytes, every rank calls

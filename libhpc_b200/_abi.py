@@ -112,6 +112,8 @@ PROTOTYPES = {
     "hpcx_partition_slabs": (_i32, [_i64, _i32, _vp]),
     "hpcx_csr_localize": (_i32, [_i64, _vp, _i32, _vp, _vp, _i32, _i32, _P(HaloSizes), _vp, _vp,
                                  _vp, _vp, _vp, _vp, _vp]),
+    "hpcx_csr_localize_rows": (_i32, [_i64, _i64, _vp, _i32, _vp, _vp, _i32, _i32, _P(HaloSizes), _vp, _vp, _vp, _vp]),
+    "hpcx_halo_send_lists": (_i32, [_vp, _i32, _i32, _vp, _vp, _vp]),
     "hpcx_comm_unique_id": (_i32, [_vp, _vp]),
     "hpcx_comm_init": (_i32, [_vp, _i32, _i32, _vp]),
     "hpcx_comm_finalize": (_i32, [_vp]),

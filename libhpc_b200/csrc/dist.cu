@@ -180,19 +180,28 @@ void close_peers(hpcx_halo_plan p) {
   p->flags = nullptr;
 }
 
-// Opens the neighbours' grid buffers and flag blocks.  Collective over the communicator.
-hpcx_status open_peers(hpcx_halo_plan p) {
+// The local flag block of a peer-store plan, and the two buffers the plan was made for.
+hpcx_status plan_prepare(hpcx_halo_plan p) {
   hpcx_ctx ctx = p->ctx;
-  hpcx_grid g = p->in;
   p->buf[0] = p->in->dev;
   p->buf[1] = p->out->dev;
   // A flag block of its own allocation (2 MiB keeps cudaMalloc from sub-allocating it).
   HPCX_CUDA(ctx, cudaMalloc((void **)&p->flags, 2u << 20));
   HPCX_CUDA(ctx, cudaMemset(p->flags, 0, 256));
+  HPCX_CUDA(ctx, cudaDeviceSynchronize());
+  return HPCX_OK;
+}
+
+// Opens the neighbours' grid buffers and flag blocks.  Collective over the communicator.
+hpcx_status open_peers(hpcx_halo_plan p) {
+  hpcx_ctx ctx = p->ctx;
+  hpcx_grid g = p->in;
+  hpcx_status st = plan_prepare(p);
+  if (st != HPCX_OK) return st;
   PeerInfo mine{};
   void *ptrs[3] = {p->buf[0], p->buf[1], p->flags};
   for (int k = 0; k < 3; ++k) {
-    hpcx_status st = ipc_export(ctx, ptrs[k], &mine.handle[k], &mine.offset[k]);
+    st = ipc_export(ctx, ptrs[k], &mine.handle[k], &mine.offset[k]);
     if (st != HPCX_OK) return st;
   }
   mine.n0 = g->n[0];
@@ -201,7 +210,7 @@ hpcx_status open_peers(hpcx_halo_plan p) {
   mine.pitch = g->pitch;
   mine.ext1 = g->ext[1];
   std::vector<PeerInfo> all(ctx->nranks);
-  hpcx_status st = allgather_bytes(ctx, &mine, all.data(), sizeof(PeerInfo));
+  st = allgather_bytes(ctx, &mine, all.data(), sizeof(PeerInfo));
   if (st != HPCX_OK) return st;
   for (int side = 0; side < 2; ++side) {
     const int q = ctx->rank + (side ? 1 : -1);
@@ -626,6 +635,66 @@ void close_csr_peers(hpcx_csr A) {
 
 namespace hpcx {
 void csr_close_peers(hpcx_csr A) { close_csr_peers(A); }
+
+// The sync block of the fused transport: flags by source rank, acks by destination rank, counters.
+hpcx_status csr_peer_prepare(hpcx_csr A) {
+  hpcx_ctx ctx = A->ctx;
+  HPCX_CUDA(ctx, cudaMalloc((void **)&A->d_sync, 2u << 20));  // an allocation of its own (IPC exports whole allocations)
+  HPCX_CUDA(ctx, cudaMemset(A->d_sync, 0, 1024));
+  HPCX_CUDA(ctx, cudaDeviceSynchronize());
+  return HPCX_OK;
+}
+
+// Builds the push / wait tables of the fused transport from what this rank can see of its peers:
+// views[q] = rank q's [owned | halo] x buffer and sync block as pointers valid on THIS device
+// (CUDA IPC windows between processes, plain peer pointers inside one process) plus where this
+// rank's segment lands in q's halo.
+hpcx_status csr_peer_wire(hpcx_csr A, const std::vector<CsrPeerView> &views) {
+  hpcx_ctx ctx = A->ctx;
+  const int P = ctx->nranks, me = ctx->rank;
+  std::vector<int32_t> seg_start{0}, seg_rank, src_rank;
+  std::vector<void *> seg_dst;
+  std::vector<uint32_t *> seg_flag, src_ack;
+  int64_t soff = 0;
+  for (int q = 0; q < P; ++q) {
+    const bool sends = A->send_counts[q] > 0, recvs = A->recv_counts[q] > 0;
+    if (q == me || (!sends && !recvs)) {
+      soff += A->send_counts[q];
+      continue;
+    }
+    const CsrPeerView &v = views[q];
+    if (!v.xfull || !v.sync) return fail(ctx, HPCX_INVALID_ARG, "no window into a rank this one trades with");
+    if (v.recv_cnt_me != A->send_counts[q])
+      return fail(ctx, HPCX_INVALID_ARG, "send/recv counts of two ranks do not match");
+    if (sends) {
+      seg_rank.push_back(q);
+      seg_dst.push_back(v.xfull + (v.nloc + v.recv_off_me) * A->es);
+      seg_flag.push_back(v.sync + kSyncData + me);
+      soff += A->send_counts[q];
+      seg_start.push_back((int32_t)soff);
+    }
+    if (recvs) {
+      src_rank.push_back(q);
+      src_ack.push_back(v.sync + kSyncAck + me);
+    }
+  }
+  A->nseg = (int32_t)seg_rank.size();
+  A->nsrc = (int32_t)src_rank.size();
+  auto up = [&](const void *h, size_t bytes, void **d) -> cudaError_t {
+    cudaError_t e = cudaMalloc(d, std::max<size_t>(bytes, 16));
+    if (e == cudaSuccess && bytes) e = cudaMemcpy(*d, h, bytes, cudaMemcpyHostToDevice);
+    return e;
+  };
+  HPCX_CUDA(ctx, up(seg_start.data(), seg_start.size() * 4, (void **)&A->d_seg_start));
+  HPCX_CUDA(ctx, up(seg_rank.data(), seg_rank.size() * 4, (void **)&A->d_seg_rank));
+  HPCX_CUDA(ctx, up(seg_dst.data(), seg_dst.size() * sizeof(void *), (void **)&A->d_seg_dst));
+  HPCX_CUDA(ctx, up(seg_flag.data(), seg_flag.size() * sizeof(void *), (void **)&A->d_seg_flag));
+  HPCX_CUDA(ctx, up(src_rank.data(), src_rank.size() * 4, (void **)&A->d_src_rank));
+  HPCX_CUDA(ctx, up(src_ack.data(), src_ack.size() * sizeof(void *), (void **)&A->d_src_ack));
+  A->epoch = 0;
+  A->transport = 1;
+  return HPCX_OK;
+}
 }  // namespace hpcx
 
 extern "C" {
@@ -704,10 +773,10 @@ hpcx_status hpcx_csr_halo_transport(hpcx_csr A, int32_t transport) {
   const int P = ctx->nranks, me = ctx->rank;
   HPCX_REQUIRE(ctx, P <= kMaxPeers, "the peer-store transport supports up to 64 ranks");
 
-  HPCX_CUDA(ctx, cudaMalloc((void **)&A->d_sync, 2u << 20));  // an allocation of its own
-  HPCX_CUDA(ctx, cudaMemset(A->d_sync, 0, 1024));
+  hpcx_status st = hpcx::csr_peer_prepare(A);
+  if (st != HPCX_OK) return st;
   CsrPeerInfo mine{};
-  hpcx_status st = ipc_export(ctx, A->d_xfull, &mine.handle[0], &mine.offset[0]);
+  st = ipc_export(ctx, A->d_xfull, &mine.handle[0], &mine.offset[0]);
   if (st == HPCX_OK) st = ipc_export(ctx, A->d_sync, &mine.handle[1], &mine.offset[1]);
   if (st != HPCX_OK) return st;
   mine.nloc = A->nloc;
@@ -720,53 +789,24 @@ hpcx_status hpcx_csr_halo_transport(hpcx_csr A, int32_t transport) {
   std::vector<CsrPeerInfo> all(P);
   st = allgather_bytes(ctx, &mine, all.data(), sizeof(CsrPeerInfo));
   if (st != HPCX_OK) return st;
-
-  std::vector<int32_t> seg_start{0}, seg_rank, src_rank;
-  std::vector<void *> seg_dst;
-  std::vector<uint32_t *> seg_flag, src_ack;
-  int64_t soff = 0;
+  // open the windows of the ranks this one trades with (CUDA IPC) and wire the tables
+  std::vector<hpcx::CsrPeerView> views(P);
   for (int q = 0; q < P; ++q) {
-    const bool sends = A->send_counts[q] > 0, recvs = A->recv_counts[q] > 0;
-    if (q == me || (!sends && !recvs)) {
-      soff += A->send_counts[q];
-      continue;
-    }
-    if (all[q].recv_cnt[me] != A->send_counts[q])
-      return fail(ctx, HPCX_INVALID_ARG, "send/recv counts of two ranks do not match");
+    const bool trades = q != me && (A->send_counts[q] > 0 || A->recv_counts[q] > 0);
+    if (!trades) continue;
     void *bx = nullptr, *bs = nullptr;
     HPCX_CUDA(ctx, cudaIpcOpenMemHandle(&bx, all[q].handle[0], cudaIpcMemLazyEnablePeerAccess));
     A->peer_open.push_back(bx);
     HPCX_CUDA(ctx, cudaIpcOpenMemHandle(&bs, all[q].handle[1], cudaIpcMemLazyEnablePeerAccess));
     A->peer_open.push_back(bs);
-    char *px = (char *)bx + all[q].offset[0];
-    uint32_t *ps = reinterpret_cast<uint32_t *>((char *)bs + all[q].offset[1]);
-    if (sends) {
-      seg_rank.push_back(q);
-      seg_dst.push_back(px + (all[q].nloc + all[q].recv_off[me]) * A->es);
-      seg_flag.push_back(ps + kSyncData + me);
-      soff += A->send_counts[q];
-      seg_start.push_back((int32_t)soff);
-    }
-    if (recvs) {
-      src_rank.push_back(q);
-      src_ack.push_back(ps + kSyncAck + me);
-    }
+    views[q].xfull = (char *)bx + all[q].offset[0];
+    views[q].sync = reinterpret_cast<uint32_t *>((char *)bs + all[q].offset[1]);
+    views[q].nloc = all[q].nloc;
+    views[q].recv_off_me = all[q].recv_off[me];
+    views[q].recv_cnt_me = all[q].recv_cnt[me];
   }
-  A->nseg = (int32_t)seg_rank.size();
-  A->nsrc = (int32_t)src_rank.size();
-  auto up = [&](const void *h, size_t bytes, void **d) -> cudaError_t {
-    cudaError_t e = cudaMalloc(d, std::max<size_t>(bytes, 16));
-    if (e == cudaSuccess && bytes) e = cudaMemcpy(*d, h, bytes, cudaMemcpyHostToDevice);
-    return e;
-  };
-  HPCX_CUDA(ctx, up(seg_start.data(), seg_start.size() * 4, (void **)&A->d_seg_start));
-  HPCX_CUDA(ctx, up(seg_rank.data(), seg_rank.size() * 4, (void **)&A->d_seg_rank));
-  HPCX_CUDA(ctx, up(seg_dst.data(), seg_dst.size() * sizeof(void *), (void **)&A->d_seg_dst));
-  HPCX_CUDA(ctx, up(seg_flag.data(), seg_flag.size() * sizeof(void *), (void **)&A->d_seg_flag));
-  HPCX_CUDA(ctx, up(src_rank.data(), src_rank.size() * 4, (void **)&A->d_src_rank));
-  HPCX_CUDA(ctx, up(src_ack.data(), src_ack.size() * sizeof(void *), (void **)&A->d_src_ack));
-  A->epoch = 0;
-  A->transport = 1;
+  st = hpcx::csr_peer_wire(A, views);
+  if (st != HPCX_OK) return st;
   // Nobody may push before every rank's sync block is zeroed and its windows are open.
   return hpcx_comm_barrier(ctx);
 }

@@ -167,4 +167,94 @@ hpcx_status hpcx_csr_localize(int64_t nrows, const void *row_ptr, int32_t idx_by
   return HPCX_OK;
 }
 
+
+// ---- the same tables without the global matrix -------------------------------------------
+// hpcx_csr_localize wants the whole matrix on every rank and a table of nrows entries; a rank of a
+// real distributed job holds only its own rows.  The two steps below need just those: step 1 is
+// local, step 2 turns the column lists the other ranks ask for (one exchange of integer lists,
+// done by the caller: torch.distributed / MPI / hpcx_comm_*) into this rank's send list.  The
+// results are identical, bit for bit, to hpcx_csr_localize on the global matrix (tests/
+// test_dist_cpu.py, world sizes 2 and 3).
+hpcx_status hpcx_csr_localize_rows(int64_t nrows_global, int64_t nloc, const void *row_ptr, int32_t idx_bytes,
+                                   const int32_t *col_global, const int64_t *bounds, int32_t nparts,
+                                   int32_t rank, hpcx_halo_sizes *sizes, int32_t *local_col,
+                                   int64_t *halo_gcol, int64_t *recv_counts, uint8_t *row_kind) {
+  if (nrows_global < 0 || nloc < 0 || !row_ptr || (idx_bytes != 4 && idx_bytes != 8) || !bounds || nparts < 1 ||
+      rank < 0 || rank >= nparts || !sizes)
+    return HPCX_INVALID_ARG;
+  if (bounds[0] != 0 || bounds[nparts] != nrows_global) return HPCX_INVALID_ARG;
+  for (int p = 0; p < nparts; ++p)
+    if (bounds[p + 1] < bounds[p]) return HPCX_INVALID_ARG;
+  const int64_t r0 = bounds[rank], r1 = bounds[rank + 1];
+  if (r1 - r0 != nloc) return HPCX_INVALID_ARG;
+  if (rp_at(row_ptr, idx_bytes, 0) != 0) return HPCX_INVALID_ARG;
+  const int64_t nnz = rp_at(row_ptr, idx_bytes, nloc);
+  if (nnz > 0 && !col_global) return HPCX_INVALID_ARG;
+  try {
+    // halo columns: sorted distinct columns outside [r0, r1) — ascending global index, which is
+    // ascending (owner, column) because owners are contiguous ranges
+    std::vector<int32_t> halo;
+    for (int64_t p = 0; p < nnz; ++p) {
+      const int64_t c = col_global[p];
+      if (c < 0 || c >= nrows_global) return HPCX_OUT_OF_RANGE;
+      if (c < r0 || c >= r1) halo.push_back((int32_t)c);
+    }
+    std::sort(halo.begin(), halo.end());
+    halo.erase(std::unique(halo.begin(), halo.end()), halo.end());
+    const int64_t nhalo = (int64_t)halo.size();
+    if (nloc + nhalo > INT32_MAX) return HPCX_UNSUPPORTED;
+    sizes->nloc = nloc;
+    sizes->nnz_loc = nnz;
+    sizes->nhalo = nhalo;
+    sizes->nsend = -1;  // known after the exchange (hpcx_halo_send_lists)
+    if (local_col)
+      for (int64_t p = 0; p < nnz; ++p) {
+        const int64_t c = col_global[p];
+        local_col[p] = (c >= r0 && c < r1)
+                           ? (int32_t)(c - r0)
+                           : (int32_t)(nloc + (std::lower_bound(halo.begin(), halo.end(), (int32_t)c) - halo.begin()));
+      }
+    if (halo_gcol)
+      for (int64_t h = 0; h < nhalo; ++h) halo_gcol[h] = halo[(size_t)h];
+    if (recv_counts) {
+      std::fill(recv_counts, recv_counts + nparts, (int64_t)0);
+      for (int64_t h = 0; h < nhalo; ++h) recv_counts[owner_of(bounds, nparts, halo[(size_t)h])]++;
+    }
+    if (row_kind)
+      for (int64_t i = 0; i < nloc; ++i) {
+        uint8_t k = 0;
+        for (int64_t p = rp_at(row_ptr, idx_bytes, i); p < rp_at(row_ptr, idx_bytes, i + 1); ++p) {
+          const int64_t c = col_global[p];
+          if (c < r0 || c >= r1) {
+            k = 1;
+            break;
+          }
+        }
+        row_kind[i] = k;
+      }
+  } catch (const std::bad_alloc &) {
+    return HPCX_OOM;
+  }
+  return HPCX_OK;
+}
+
+hpcx_status hpcx_halo_send_lists(const int64_t *bounds, int32_t nparts, int32_t rank, const int64_t *req_counts,
+                                 const int64_t *requests, int32_t *send_idx) {
+  if (!bounds || nparts < 1 || rank < 0 || rank >= nparts || !req_counts) return HPCX_INVALID_ARG;
+  const int64_t r0 = bounds[rank], r1 = bounds[rank + 1];
+  int64_t off = 0;
+  for (int q = 0; q < nparts; ++q) {
+    if (req_counts[q] < 0 || (q == rank && req_counts[q] != 0)) return HPCX_INVALID_ARG;
+    for (int64_t i = 0; i < req_counts[q]; ++i) {
+      if (!requests || !send_idx) return HPCX_INVALID_ARG;
+      const int64_t c = requests[off + i];
+      if (c < r0 || c >= r1) return HPCX_OUT_OF_RANGE;            // asked for a column this rank does not own
+      if (i > 0 && c <= requests[off + i - 1]) return HPCX_INVALID_ARG;  // lists are ascending and distinct
+      send_idx[off + i] = (int32_t)(c - r0);
+    }
+    off += req_counts[q];
+  }
+  return HPCX_OK;
+}
+
 }  // extern "C"

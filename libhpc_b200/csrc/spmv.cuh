@@ -39,12 +39,22 @@ struct SpmvDistArgs {
   PeerWait pw;
 };
 
+// What one rank sees of another for the fused x-halo transport (dist.cu: csr_peer_wire).
+struct CsrPeerView {
+  char *xfull = nullptr;        // the peer's [owned | halo] x buffer, addressable from this device
+  uint32_t *sync = nullptr;     // the peer's sync block
+  int64_t nloc = 0;             // the peer's owned entries
+  int64_t recv_off_me = 0, recv_cnt_me = 0;  // where this rank's segment lands in the peer's halo
+};
+hpcx_status csr_peer_prepare(hpcx_csr A);
+hpcx_status csr_peer_wire(hpcx_csr A, const std::vector<CsrPeerView> &views);
+
 // Tables of the HUB kernel (spmv_hub.cu), built on the device at create time.
 struct HubTables {
   bool ready = false;
   int K = 0;                    // hub columns (their x entries live in shared memory)
   double coverage = 0.0;        // fraction of the nonzeros whose column is a hub column
-  // long part (rows of more than 32 entries): nonzero-balanced tiles of 256
+  // long part (rows of more than 256 entries): nonzero-balanced tiles of 256
   int64_t nlong = 0, nnzL = 0, ntiles = 0;
   int32_t *colL = nullptr;      // hub columns encoded as 0x80000000 | slot, padded to whole tiles
   void *valL = nullptr;
@@ -52,11 +62,13 @@ struct HubTables {
   int32_t *tile_seg0 = nullptr; // ntiles + 1: long rows that start before each tile
   int32_t *lrow = nullptr;      // original row of each long row
   int32_t *lrp = nullptr;       // nlong + 1 offsets into colL / valL
-  // short part (rows of 1..32 entries): one thread per row
-  int64_t nshort = 0, nnzS = 0;
+  // short part (rows of 1..256 entries): SELL-32 slices over the rows sorted by descending length
+  int64_t nshort = 0, nnzS = 0;  // nnzS = slots of the slices (padding included)
   int32_t *colS = nullptr;
   void *valS = nullptr;
-  int32_t *srp = nullptr, *srow = nullptr;
+  int64_t *sbase = nullptr;      // first slot of each slice (+ total)
+  uint16_t *slen = nullptr;      // length of each sorted short row
+  int32_t *srow = nullptr;       // original row of each sorted short row
   int32_t *hub_col = nullptr;   // column of each hub slot
   int64_t nwarps = 0;           // warp ranges of the persistent grid
   void *head_out = nullptr, *tail_out = nullptr;  // per warp range partials

@@ -20,8 +20,8 @@
 //     larger slice was measured slower for that reason) and serves hub gathers from there
 //     (a random 32-lane shared-memory read costs ~3.5 bank cycles instead of up to 32 lines).
 //
-// Row-length binning (create time, device): rows longer than 32 entries ("long": 88 % of C5's
-// nonzeros in 6.5 % of its rows) and rows of 1..32 entries ("short") are compacted into two
+// Row-length binning (create time, device): rows longer than 256 entries ("long": 65 % of C5's
+// nonzeros in 1.1 % of its rows) and rows of 1..256 entries ("short") are compacted into two
 // private CSR parts, columns hub-encoded; empty rows (9.4 M of C5's 16.8 M) appear in neither and
 // y is cleared by a memset first.
 //
@@ -79,31 +79,31 @@ struct HubArgs {
   const int32_t *tile_seg0;   // ntiles + 1: long rows that start before each tile
   const int32_t *lrow;        // original row index of each long row
   int64_t nnzL, ntiles;
-  // short part: CSR over the short rows
-  const int32_t *colS;
+  // short part: SELL-32 over the short rows sorted by descending length
+  const int32_t *colS;        // column-major slices of 32 rows, hub-encoded
   const void *valS;
-  const int32_t *srp;         // nshort + 1
-  const int32_t *srow;        // original row index of each short row
+  const int64_t *sbase;       // first slot of each slice
+  const uint16_t *slen;       // length of each (sorted) short row
+  const int32_t *srow;        // original row index of each (sorted) short row
   int64_t nshort;
   const int32_t *hub_col;
   int K;
 };
 
-// One half tile (128 nonzeros, 4 per lane, at most one row start per lane).  `carry` is the
-// running sum of the row open when the half tile begins; `seg0` the number of row starts before it.
 template <typename T>
-__device__ __forceinline__ void hub_half_tile(const T (&p)[4], unsigned f4, int lane, int seg0, int range_seg0,
-                                              const int32_t *__restrict__ lrow, T *__restrict__ y,
-                                              T *__restrict__ head_slot, T &carry, int &nstart) {
-  const unsigned any = __ballot_sync(0xffffffffu, f4 != 0);
-  if (any == 0) {
-    T s = add_rn(add_rn(p[0], p[1]), add_rn(p[2], p[3]));
+__device__ __forceinline__ T warp_sum(T s) {
 #pragma unroll
-    for (int m = 16; m > 0; m >>= 1) s = add_rn(s, __shfl_xor_sync(0xffffffffu, s, m));
-    carry = add_rn(carry, s);
-    nstart = 0;
-    return;
-  }
+  for (int m = 16; m > 0; m >>= 1) s = add_rn(s, __shfl_xor_sync(0xffffffffu, s, m));
+  return s;
+}
+
+// One half tile (128 nonzeros, 4 per lane, at most one row start per lane) that contains a row
+// start (`any` = ballot of the lanes that have one).  `carry` is the sum of the row open when the
+// half tile begins (the lanes' private partials already folded in); `seg0` the row starts before it.
+template <typename T>
+__device__ __forceinline__ void hub_half_tile(const T (&p)[4], unsigned f4, unsigned any, int lane, int seg0,
+                                              int range_seg0, const int32_t *__restrict__ lrow,
+                                              T *__restrict__ y, T *__restrict__ head_slot, T &carry) {
   // the lane's run: head = entries before its row start, tail = from the row start on
   const int pos = f4 ? __ffs(f4) - 1 : 4;
   T head = T(0), tail = T(0);
@@ -133,7 +133,6 @@ __device__ __forceinline__ void hub_half_tile(const T (&p)[4], unsigned f4, int 
       y[lrow[seg]] = closed;
   }
   carry = __shfl_sync(0xffffffffu, I, 31);  // tail of the last flagged lane + everything after it
-  nstart = __popc(any);
 }
 
 template <typename T>
@@ -153,19 +152,31 @@ spmv_hub_kernel(const __grid_constant__ HubArgs H, const T *__restrict__ x, T *_
   const int64_t t0 = H.ntiles * w / nw, t1 = H.ntiles * (w + 1) / nw;
   const int range_seg0 = H.tile_seg0[t0];
   const T *__restrict__ valL = static_cast<const T *>(H.valL);
-  T carry = T(0);
+  // The row that is open: `carry` (warp-uniform) + the lanes' private partials `mine`.  Tiles
+  // without a row start — most of them, known from tile_seg0 alone — only add into `mine`: no
+  // bitmap load, no shuffle, no dependency between tiles; the partials are folded into `carry`
+  // when a row start finally closes the row.
+  T carry = T(0), mine = T(0);
+  int seg0 = range_seg0;
+  // the columns of a tile are fetched one tile ahead, so that its gathers can start at once
+  // (3 % on C5; the kernel is bound by memory latency at 32 warps per SM)
+  int4 c0 = make_int4(0, 0, 0, 0), c1 = c0;
+  if (t0 < t1) {
+    c0 = ld_stream(reinterpret_cast<const int4 *>(H.colL + t0 * kTile + lane * 4));
+    c1 = ld_stream(reinterpret_cast<const int4 *>(H.colL + t0 * kTile + 128 + lane * 4));
+  }
   for (int64_t t = t0; t < t1; ++t) {
     const int64_t e0 = t * kTile + lane * 4, e1 = e0 + 128;
-    const int4 c0 = ld_stream(reinterpret_cast<const int4 *>(H.colL + e0));
-    const int4 c1 = ld_stream(reinterpret_cast<const int4 *>(H.colL + e1));
-    // bitmap bytes: half tile h, lanes 2j and 2j+1 share byte t*32 + h*16 + j
-    const unsigned b0 = H.rowstart[t * 32 + (lane >> 1)], b1 = H.rowstart[t * 32 + 16 + (lane >> 1)];
-    const unsigned f0 = (b0 >> ((lane & 1) * 4)) & 15u, f1 = (b1 >> ((lane & 1) * 4)) & 15u;
+    const int seg1 = H.tile_seg0[t + 1];  // warp-uniform, 32 tiles per line
     T v0[4], v1[4], p0[4], p1[4];
     load4(valL, e0, v0);
     load4(valL, e1, v1);
     const T x0[4] = {gx(c0.x), gx(c0.y), gx(c0.z), gx(c0.w)};
     const T x1[4] = {gx(c1.x), gx(c1.y), gx(c1.z), gx(c1.w)};
+    if (t + 1 < t1) {  // the next tile's columns travel while this tile's gathers do
+      c0 = ld_stream(reinterpret_cast<const int4 *>(H.colL + e0 + kTile));
+      c1 = ld_stream(reinterpret_cast<const int4 *>(H.colL + e1 + kTile));
+    }
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
       p0[u] = mul_rn(v0[u], x0[u]);
@@ -178,11 +189,33 @@ spmv_hub_kernel(const __grid_constant__ HubArgs H, const T *__restrict__ x, T *_
         if (e1 + u >= H.nnzL) p1[u] = T(0);
       }
     }
-    int n0, n1;
-    const int seg0 = H.tile_seg0[t];
-    hub_half_tile<T>(p0, f0, lane, seg0, range_seg0, H.lrow, y, head_out + w, carry, n0);
-    hub_half_tile<T>(p1, f1, lane, seg0 + n0, range_seg0, H.lrow, y, head_out + w, carry, n1);
+    const T s0 = add_rn(add_rn(p0[0], p0[1]), add_rn(p0[2], p0[3]));
+    const T s1 = add_rn(add_rn(p1[0], p1[1]), add_rn(p1[2], p1[3]));
+    if (seg1 == seg0) {
+      mine = add_rn(mine, add_rn(s0, s1));
+      continue;
+    }
+    // ---- a row starts in this tile.  Bitmap bytes: half tile h, lanes 2j and 2j+1 share byte t*32 + h*16 + j
+    const unsigned b0 = H.rowstart[t * 32 + (lane >> 1)], b1 = H.rowstart[t * 32 + 16 + (lane >> 1)];
+    const unsigned f0 = (b0 >> ((lane & 1) * 4)) & 15u, f1 = (b1 >> ((lane & 1) * 4)) & 15u;
+    const unsigned any0 = __ballot_sync(0xffffffffu, f0 != 0), any1 = __ballot_sync(0xffffffffu, f1 != 0);
+    if (any0 == 0) {
+      mine = add_rn(mine, s0);
+    } else {
+      carry = add_rn(carry, warp_sum(mine));
+      mine = T(0);
+      hub_half_tile<T>(p0, f0, any0, lane, seg0, range_seg0, H.lrow, y, head_out + w, carry);
+    }
+    if (any1 == 0) {
+      mine = add_rn(mine, s1);
+    } else {
+      carry = add_rn(carry, warp_sum(mine));
+      mine = T(0);
+      hub_half_tile<T>(p1, f1, any1, lane, seg0 + __popc(any0), range_seg0, H.lrow, y, head_out + w, carry);
+    }
+    seg0 = seg1;
   }
+  carry = add_rn(carry, warp_sum(mine));
   if (lane == 0) {
     if (H.tile_seg0[t1] == range_seg0)
       head_out[w] = carry;  // no row start in the whole range (or an empty range: carry = 0)
@@ -190,14 +223,32 @@ spmv_hub_kernel(const __grid_constant__ HubArgs H, const T *__restrict__ x, T *_
       tail_out[w] = carry;
   }
 
-  // ---------------------------------------------------------------- short rows: one thread per row
+  // ---------------------------------------------------------------- short rows
+  // SELL-32 over the short rows sorted by descending length: slice s holds 32 rows column-major,
+  // so every load of col / val is one coalesced line per warp; a lane walks its own row in
+  // ascending p (the oracle's order, so these rows are bit-identical to it).
   const T *__restrict__ valS = static_cast<const T *>(H.valS);
   const int64_t nthreads = (int64_t)gridDim.x * kHubThreads;
-  for (int64_t k = (int64_t)blockIdx.x * kHubThreads + threadIdx.x; k < H.nshort; k += nthreads) {
-    const int a = H.srp[k], e = H.srp[k + 1];
+  const int64_t nslots = (H.nshort + 31) / 32 * 32;
+  for (int64_t k = (int64_t)blockIdx.x * kHubThreads + threadIdx.x; k < nslots; k += nthreads) {
+    const int len = k < H.nshort ? H.slen[k] : 0;
+    const int64_t base = H.sbase[k >> 5] + lane;
     T s = T(0);
-    for (int i = a; i < e; ++i) s = add_rn(s, mul_rn(valS[i], gx(H.colS[i])));
-    y[H.srow[k]] = s;
+    int j = 0;
+    for (; j + 4 <= len; j += 4) {  // four gathers in flight per lane
+      int c[4];
+      T v[4], xv[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) c[u] = __ldcs(H.colS + base + (j + u) * 32);
+#pragma unroll
+      for (int u = 0; u < 4; ++u) v[u] = __ldcs(valS + base + (j + u) * 32);
+#pragma unroll
+      for (int u = 0; u < 4; ++u) xv[u] = gx(c[u]);
+#pragma unroll
+      for (int u = 0; u < 4; ++u) s = add_rn(s, mul_rn(v[u], xv[u]));
+    }
+    for (; j < len; ++j) s = add_rn(s, mul_rn(__ldcs(valS + base + j * 32), gx(__ldcs(H.colS + base + j * 32))));
+    if (k < H.nshort) y[H.srow[k]] = s;
   }
 }
 
@@ -223,7 +274,7 @@ __global__ void spmv_hub_fixup_kernel(const int32_t *__restrict__ tile_seg0, con
 }
 
 // ------------------------------------------------------------------ create-time kernels
-constexpr int kShortMax = 32;  // rows of 1..32 entries are "short" (one thread per row)
+constexpr int kShortMax = 256;  // rows of 1..256 entries are "short" (SELL-32, one thread per row)
 
 __global__ void __launch_bounds__(256) hub_hist_kernel(const int32_t *__restrict__ col, int64_t nnz,
                                                        uint32_t *__restrict__ freq) {
@@ -284,6 +335,39 @@ hub_copy_kernel(const int32_t *__restrict__ rp, const int32_t *__restrict__ col,
     if (bitmap && l == 0) atomicOr(bitmap + (dst >> 5), 1u << (dst & 31));  // row start
   }
 }
+// sort keys of the short rows: kShortMax - length, so that an ascending stable sort yields descending
+// length with ascending row index among equals
+__global__ void __launch_bounds__(256) hub_shortkey_kernel(const int32_t *__restrict__ rp, const int32_t *__restrict__ rows,
+                                                           int64_t n, int32_t *__restrict__ keys) {
+  for (int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; k < n; k += (int64_t)gridDim.x * blockDim.x)
+    keys[k] = kShortMax - (rp[rows[k] + 1] - rp[rows[k]]);
+}
+// slen[k] = length of sorted short row k; width32[s] = 32 * (length of the first = longest row of slice s)
+__global__ void __launch_bounds__(256) hub_slices_kernel(const int32_t *__restrict__ keys_sorted, int64_t n, int64_t nslices,
+                                                         uint16_t *__restrict__ slen, int64_t *__restrict__ width32) {
+  for (int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; k < n; k += (int64_t)gridDim.x * blockDim.x) {
+    const int len = kShortMax - keys_sorted[k];
+    slen[k] = (uint16_t)len;
+    if ((k & 31) == 0) width32[k >> 5] = 32 * (int64_t)len;
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) width32[nslices] = 0;
+}
+// column-major fill of the SELL-32 slices: sorted short row k -> lane k % 32 of slice k / 32
+template <typename V>
+__global__ void __launch_bounds__(256)
+hub_sell_fill_kernel(const int32_t *__restrict__ rp, const int32_t *__restrict__ col, const V *__restrict__ val,
+                     const int32_t *__restrict__ rows, const uint16_t *__restrict__ slen,
+                     const int64_t *__restrict__ sbase, int64_t n, const int32_t *__restrict__ slot,
+                     int32_t *__restrict__ pcol, V *__restrict__ pval) {
+  for (int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; k < n; k += (int64_t)gridDim.x * blockDim.x) {
+    const int src = rp[rows[k]], len = slen[k];
+    const int64_t dst = sbase[k >> 5] + (k & 31);
+    for (int j = 0; j < len; ++j) {
+      pcol[dst + j * 32] = hub_encode(col[src + j], slot);
+      pval[dst + j * 32] = val[src + j];
+    }
+  }
+}
 // tile_seg0[t] = number of long rows whose first nonzero lies before tile t
 __global__ void __launch_bounds__(256) hub_tileseg_kernel(const int32_t *__restrict__ lrp, int32_t nl, int64_t ntiles,
                                                           int32_t *__restrict__ tile_seg0) {
@@ -323,6 +407,7 @@ hpcx_status select_rows(hpcx_ctx ctx, const int32_t *rp, const uint8_t *flags, i
   HPCX_CUDA(ctx, cudaMemcpyAsync(&n, nsel.p, 4, cudaMemcpyDeviceToHost, s));
   HPCX_CUDA(ctx, cudaStreamSynchronize(s));
   *count = n;
+  if (!prp) return HPCX_OK;
   HPCX_CUDA(ctx, cudaMalloc((void **)prp, (size_t)(n + 1) * 4));
   hub_lens_kernel<<<grid_for(ctx, n + 1), 256, 0, s>>>(rp, *rows, n, *prp);
   size_t eb = 0;
@@ -346,8 +431,8 @@ hpcx_status copy_parts(hpcx_csr A, const int32_t *slot, cudaStream_t s) {
                                                                        H.lrp, H.nlong, slot, H.colL, (V *)H.valL,
                                                                        (uint32_t *)H.rowstart);
   if (H.nshort)
-    hub_copy_kernel<V, 1><<<grid_for(ctx, H.nshort), 256, 0, s>>>(A->d_row_ptr, A->d_col, (const V *)A->d_val, H.srow, H.srp,
-                                                                  H.nshort, slot, H.colS, (V *)H.valS, nullptr);
+    hub_sell_fill_kernel<V><<<grid_for(ctx, H.nshort), 256, 0, s>>>(A->d_row_ptr, A->d_col, (const V *)A->d_val, H.srow,
+                                                                    H.slen, H.sbase, H.nshort, slot, H.colS, (V *)H.valS);
   ctx->launches += 2;
   return HPCX_OK;
 }
@@ -366,7 +451,8 @@ void hub_free(hpcx_csr A) {
   cudaFree(H.lrp);
   cudaFree(H.colS);
   cudaFree(H.valS);
-  cudaFree(H.srp);
+  cudaFree(H.sbase);
+  cudaFree(H.slen);
   cudaFree(H.srow);
   cudaFree(H.hub_col);
   cudaFree(H.head_out);
@@ -421,8 +507,41 @@ hpcx_status hub_build(hpcx_csr A) {
   ctx->launches += 1;
   if (hpcx_status st = select_rows(ctx, A->d_row_ptr, (const uint8_t *)is_long.p, nrows, &H.lrow, &H.lrp, &H.nlong, &H.nnzL, s))
     return st;
-  if (hpcx_status st = select_rows(ctx, A->d_row_ptr, (const uint8_t *)is_short.p, nrows, &H.srow, &H.srp, &H.nshort, &H.nnzS, s))
-    return st;
+  {
+    // short rows: ascending list, then a stable sort by descending length -> SELL-32 slices
+    int32_t *rows_asc = nullptr;
+    int64_t dummy = 0;
+    if (hpcx_status st = select_rows(ctx, A->d_row_ptr, (const uint8_t *)is_short.p, nrows, &rows_asc, nullptr, &H.nshort, &dummy, s))
+      return st;
+    Scratch asc, keys, keys2, stmp, w32;
+    asc.p = rows_asc;  // freed with the scope
+    const int64_t ns = H.nshort, nslices = (ns + 31) / 32;
+    HPCX_CUDA(ctx, keys.alloc((size_t)ns * 4));
+    HPCX_CUDA(ctx, keys2.alloc((size_t)ns * 4));
+    HPCX_CUDA(ctx, cudaMalloc((void **)&H.srow, (size_t)std::max<int64_t>(ns, 1) * 4));
+    HPCX_CUDA(ctx, cudaMalloc((void **)&H.slen, (size_t)std::max<int64_t>(ns, 1) * 2));
+    HPCX_CUDA(ctx, cudaMalloc((void **)&H.sbase, (size_t)(nslices + 1) * 8));
+    HPCX_CUDA(ctx, w32.alloc((size_t)(nslices + 1) * 8));
+    HPCX_CUDA(ctx, cudaMemsetAsync(H.sbase, 0, (size_t)(nslices + 1) * 8, s));
+    if (ns) {
+      hub_shortkey_kernel<<<grid_for(ctx, ns), 256, 0, s>>>(A->d_row_ptr, rows_asc, ns, (int32_t *)keys.p);
+      size_t sb = 0;
+      HPCX_CUDA(ctx, cub::DeviceRadixSort::SortPairs(nullptr, sb, (const int32_t *)keys.p, (int32_t *)keys2.p,
+                                                     (const int32_t *)rows_asc, H.srow, (int)ns, 0, 9, s));
+      HPCX_CUDA(ctx, stmp.alloc(sb));
+      HPCX_CUDA(ctx, cub::DeviceRadixSort::SortPairs(stmp.p, sb, (const int32_t *)keys.p, (int32_t *)keys2.p,
+                                                     (const int32_t *)rows_asc, H.srow, (int)ns, 0, 9, s));
+      hub_slices_kernel<<<grid_for(ctx, ns), 256, 0, s>>>((const int32_t *)keys2.p, ns, nslices, H.slen, (int64_t *)w32.p);
+      Scratch etmp;
+      size_t eb = 0;
+      HPCX_CUDA(ctx, cub::DeviceScan::ExclusiveSum(nullptr, eb, (const int64_t *)w32.p, H.sbase, (int)(nslices + 1), s));
+      HPCX_CUDA(ctx, etmp.alloc(eb));
+      HPCX_CUDA(ctx, cub::DeviceScan::ExclusiveSum(etmp.p, eb, (const int64_t *)w32.p, H.sbase, (int)(nslices + 1), s));
+      HPCX_CUDA(ctx, cudaMemcpyAsync(&H.nnzS, H.sbase + nslices, 8, cudaMemcpyDeviceToHost, s));
+      HPCX_CUDA(ctx, cudaStreamSynchronize(s));  // scratch of this scope is freed on exit
+      ctx->launches += 2;
+    }
+  }
   H.coverage = (double)covered / (double)nnz;
   H.ntiles = (H.nnzL + kTile - 1) / kTile;
   const int64_t nallocL = std::max<int64_t>(H.ntiles, 1) * kTile;
@@ -472,7 +591,8 @@ static hpcx_status hub_launch_t(hpcx_csr A, const T *x, T *y, cudaStream_t s) {
   a.ntiles = H.ntiles;
   a.colS = H.colS;
   a.valS = H.valS;
-  a.srp = H.srp;
+  a.sbase = H.sbase;
+  a.slen = H.slen;
   a.srow = H.srow;
   a.nshort = H.nshort;
   a.hub_col = H.hub_col;

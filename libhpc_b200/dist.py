@@ -72,3 +72,63 @@ def distributed_csr(ctx: Context, local: dict, dtype, transport: int = 0, **opts
     if transport:
         D.halo_transport(transport)
     return D
+
+
+def localize_rows_distributed(row_ptr, col_global, values, bounds, rank: int, world: int, nrows_global: int) -> dict:
+    """The tables of csr_localize built from this rank's OWN rows only (hpcx_csr_localize_rows,
+    one exchange of the halo column lists over torch.distributed, hpcx_halo_send_lists): no rank
+    ever holds the global matrix.  row_ptr: nloc + 1 entries from 0; col_global: global columns."""
+    import torch
+    import torch.distributed as dist
+
+    lib = _abi.load()
+    row_ptr = np.ascontiguousarray(row_ptr)
+    col_global = np.ascontiguousarray(col_global, dtype=np.int32)
+    bounds = np.ascontiguousarray(bounds, dtype=np.int64)
+    nloc = len(row_ptr) - 1
+    sz = _abi.HaloSizes()
+    head = (nrows_global, nloc, row_ptr.ctypes.data, row_ptr.dtype.itemsize, col_global.ctypes.data if len(col_global) else None,
+            bounds.ctypes.data, world, rank, C.byref(sz))
+    rc = lib.hpcx_csr_localize_rows(*head, None, None, None, None)
+    if rc != _abi.OK:
+        raise RuntimeError(f"hpcx_csr_localize_rows failed with status {rc}")
+    out = dict(local_col=np.empty(sz.nnz_loc, dtype=np.int32), halo_gcol=np.empty(sz.nhalo, dtype=np.int64),
+               recv_counts=np.empty(world, dtype=np.int64), row_kind=np.empty(nloc, dtype=np.uint8))
+    rc = lib.hpcx_csr_localize_rows(*head, *[out[k].ctypes.data for k in ("local_col", "halo_gcol", "recv_counts", "row_kind")])
+    if rc != _abi.OK:
+        raise RuntimeError(f"hpcx_csr_localize_rows failed with status {rc}")
+    # ---- exchange: who needs how many of whose columns, then the lists themselves
+    on_gpu = world > 1 and dist.get_backend() == "nccl"
+    dev = "cuda" if on_gpu else "cpu"
+    req_counts = np.zeros(world, dtype=np.int64)
+    requests = np.empty(0, dtype=np.int64)
+    if world > 1:
+        mine = torch.from_numpy(out["recv_counts"]).to(dev)
+        allc = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(allc, mine)
+        req_counts = np.array([int(allc[q][rank]) for q in range(world)], dtype=np.int64)  # what q needs from me
+        ops, recv_t, roff = [], [], 0
+        for q in range(world):
+            nr = int(out["recv_counts"][q])
+            if nr:
+                ops.append(dist.P2POp(dist.isend, torch.from_numpy(out["halo_gcol"][roff:roff + nr].copy()).to(dev), q))
+            roff += nr
+            if req_counts[q]:
+                t = torch.empty(int(req_counts[q]), dtype=torch.int64, device=dev)
+                recv_t.append(t)
+                ops.append(dist.P2POp(dist.irecv, t, q))
+        if ops:
+            for w in dist.batch_isend_irecv(ops):
+                w.wait()
+        if recv_t:
+            requests = torch.cat(recv_t).cpu().numpy()
+    send_idx = np.empty(int(req_counts.sum()), dtype=np.int32)
+    rc = lib.hpcx_halo_send_lists(bounds.ctypes.data, world, rank, req_counts.ctypes.data,
+                                  requests.ctypes.data if len(requests) else None,
+                                  send_idx.ctypes.data if len(send_idx) else None)
+    if rc != _abi.OK:
+        raise RuntimeError(f"hpcx_halo_send_lists failed with status {rc}")
+    rp64 = row_ptr.astype(np.int64)
+    out.update(nloc=nloc, nnz_loc=int(sz.nnz_loc), nhalo=int(sz.nhalo), nsend=len(send_idx), send_idx=send_idx,
+               send_counts=req_counts, local_row_ptr=rp64, values=values)
+    return out

@@ -89,6 +89,48 @@ def laplace2d_big(ny: int, nx: int, dtype=np.float64, index_dtype=np.int32, rows
     return rp, col, val
 
 
+def laplace2d_rows(ny: int, nx: int, y0: int, y1: int, dtype=np.float64, index_dtype=np.int64, rows_per_chunk=1024):
+    """Grid rows [y0, y1) of the ny x nx 5-point Laplacian as a CSR row slab with GLOBAL column
+    indices (what one rank of a distributed job holds): (row_ptr from 0, col, val)."""
+    m = (y1 - y0) * nx
+    nnz = 5 * m - 2 * (y1 - y0) - (nx if y0 == 0 else 0) - (nx if y1 == ny else 0)
+    rp = np.empty(m + 1, dtype=index_dtype)
+    col = np.empty(nnz, dtype=np.int32)
+    val = np.empty(nnz, dtype=dtype)
+    p = 0
+    for a in range(y0, y1, rows_per_chunk):
+        b = min(y1, a + rows_per_chunk)
+        k = (b - a) * nx
+        y = np.repeat(np.arange(a, b, dtype=np.int64), nx)
+        x = np.tile(np.arange(nx, dtype=np.int64), b - a)
+        has = np.stack([y > 0, x > 0, np.ones(k, dtype=bool), x < nx - 1, y < ny - 1], axis=1)
+        i = (y * nx + x)[:, None]
+        off = np.array([-nx, -1, 0, 1, nx], dtype=np.int64)[None, :]
+        c = (i + off)[has]
+        q = len(c)
+        col[p:p + q] = c
+        val[p:p + q] = np.broadcast_to(np.array([-1, -1, 4, -1, -1], dtype=dtype)[None, :], has.shape)[has]
+        cnt = has.sum(axis=1)
+        rp[(a - y0) * nx:(b - y0) * nx] = p + np.cumsum(cnt) - cnt
+        p += q
+    rp[m] = p
+    assert p == nnz
+    return rp, col, val
+
+
+def op27_rows(n: int, z0: int, z1: int, dtype=np.float64, planes_per_chunk: int = 16):
+    """Planes [z0, z1) of the n^3 27-point operator as a CSR row slab with GLOBAL column indices."""
+    rps, cols, vals, base = [np.zeros(1, np.int64)], [], [], 0
+    for a in range(z0, z1, planes_per_chunk):
+        b = min(z1, a + planes_per_chunk)
+        rp, c, v = op27(n, dtype, np.int64, a, b)
+        cols.append(c)
+        vals.append(v)
+        rps.append(rp[1:] + base)
+        base += int(rp[-1])
+    return np.concatenate(rps), np.concatenate(cols), np.concatenate(vals)
+
+
 def op27(n: int, dtype=np.float64, index_dtype=np.int32, z_lo: int = 0, z_hi: int | None = None):
     """3-D 27-point operator on n^3 (C4): 27 neighbours ascending, Dirichlet truncation,
     centre 26, others -1.  [z_lo, z_hi) selects a slab of rows (global column numbering)."""

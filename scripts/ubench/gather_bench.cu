@@ -68,6 +68,41 @@ __global__ void __launch_bounds__(THREADS, 1) k_hub(const int *__restrict__ colh
   out[blockIdx.x * (int64_t)THREADS + threadIdx.x] = s;
 }
 
+// same hub kernel, but every warp streams its OWN contiguous range of nonzeros (what the product
+// kernel does) instead of the grid-wide sliding window: 4736 concurrent streams per array
+template <int U, int THREADS>
+__global__ void __launch_bounds__(THREADS, 1) k_hub_contig(const int *__restrict__ colh, const float *__restrict__ val,
+                                                           const float *__restrict__ x, const int *__restrict__ hub_col, int K,
+                                                           int64_t n, float *__restrict__ out, int vec) {
+  extern __shared__ float sx[];
+  for (int i = threadIdx.x; i < K; i += THREADS) sx[i] = __ldg(x + hub_col[i]);
+  __syncthreads();
+  float s = 0.f;
+  const int lane = threadIdx.x & 31;
+  const int64_t w = (int64_t)blockIdx.x * (THREADS / 32) + (threadIdx.x >> 5), nw = (int64_t)gridDim.x * (THREADS / 32);
+  const int64_t ntiles = n / (32 * U);
+  for (int64_t t = ntiles * w / nw; t < ntiles * (w + 1) / nw; ++t) {
+    int c[U]; float v[U], a[U];
+    if (vec) {  // lane owns 4 consecutive entries per half tile: 128-bit loads
+#pragma unroll
+      for (int h = 0; h < U / 4; ++h) {
+        const int4 cc = __ldcs(reinterpret_cast<const int4 *>(colh + t * 32 * U + h * 128 + lane * 4));
+        const float4 vv = __ldcs(reinterpret_cast<const float4 *>(val + t * 32 * U + h * 128 + lane * 4));
+        c[4 * h] = cc.x; c[4 * h + 1] = cc.y; c[4 * h + 2] = cc.z; c[4 * h + 3] = cc.w;
+        v[4 * h] = vv.x; v[4 * h + 1] = vv.y; v[4 * h + 2] = vv.z; v[4 * h + 3] = vv.w;
+      }
+    } else {
+#pragma unroll
+      for (int u = 0; u < U; ++u) { const int64_t j = t * 32 * U + u * 32 + lane; c[u] = __ldg(colh + j); v[u] = __ldg(val + j); }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) a[u] = c[u] < 0 ? sx[c[u] & 0x7fffffff] : __ldg(x + c[u]);
+#pragma unroll
+    for (int u = 0; u < U; ++u) s += v[u] * a[u];
+  }
+  out[blockIdx.x * (int64_t)THREADS + threadIdx.x] = s;
+}
+
 static cudaTextureObject_t make_tex(const float *x, int64_t n) {
   cudaResourceDesc rd{}; rd.resType = cudaResourceTypeLinear; rd.res.linear.devPtr = (void *)x;
   rd.res.linear.desc = cudaCreateChannelDesc<float>(); rd.res.linear.sizeInBytes = (size_t)n * 4;
@@ -111,6 +146,10 @@ extern "C" float gb_run(int which, const int *col, const int *colh, const float 
     // hub with small K and several CTAs per SM is covered by passing K and sms * ctas as `sms`
     case 11: { CK(cudaFuncSetAttribute(k_hub<1, 8, 512>, cudaFuncAttributeMaxDynamicSharedMemorySize, K * 4));
       return time_it([&] { k_hub<1, 8, 512><<<sms, 512, K * 4>>>(colh, val, x, tx, hub_col, K, n, out); }); }
+    case 12: { CK(cudaFuncSetAttribute(k_hub_contig<8, 1024>, cudaFuncAttributeMaxDynamicSharedMemorySize, K * 4));
+      return time_it([&] { k_hub_contig<8, 1024><<<sms, 1024, K * 4>>>(colh, val, x, hub_col, K, n, out, 0); }); }
+    case 13: { CK(cudaFuncSetAttribute(k_hub_contig<8, 1024>, cudaFuncAttributeMaxDynamicSharedMemorySize, K * 4));
+      return time_it([&] { k_hub_contig<8, 1024><<<sms, 1024, K * 4>>>(colh, val, x, hub_col, K, n, out, 1); }); }
   }
   return -2.f;
 }

@@ -50,6 +50,13 @@ def hub_encode(c, K):
 
 names = {0: "stream only", 1: "ldg vec4", 2: "tex vec4", 3: "ldg lane U4", 4: "ldg lane U8", 5: "tex lane U4", 6: "tex lane U8"}
 orders = {"csr": col}
+if os.environ.get("QUICK") == "1":
+    ch, hub = hub_encode(col, 16384)
+    for w, nm in ((7, "hub ldg U8 1024t grid-stride"), (12, "hub contiguous warp ranges, scalar loads"),
+                  (13, "hub contiguous warp ranges, 128-bit loads")):
+        print(f"K=16384 {nm:44s} {run(w, col, ch, hub, 16384):7.3f} ms", flush=True)
+    ctx.close()
+    sys.exit(0)
 T = 32768
 m = nnz // T * T
 cs = col.clone()

@@ -78,6 +78,18 @@ def _worker(rank, world, port, case):
             y2 = oracle.spmv(L["local_row_ptr"], L["local_col"], np.ascontiguousarray(L["values"]), xonly)
             interior = L["row_kind"] == 0
             assert np.array_equal(y2[interior], y[interior]) and np.isnan(y2[~interior]).all()
+            # the same tables from this rank's OWN rows only (hpcx_csr_localize_rows + one exchange of
+            # column lists + hpcx_halo_send_lists): bit-identical to the global-matrix localiser and
+            # to the oracle's
+            from libhpc_b200 import dist as hd
+            r0, r1 = int(bounds[rank]), int(bounds[rank + 1])
+            p0, p1 = int(rp[r0]), int(rp[r1])
+            D = hd.localize_rows_distributed(rp[r0:r1 + 1] - p0, col[p0:p1], val[p0:p1], bounds, rank, world, n)
+            O = oracle.localize(rp, col, bounds, rank)
+            for k in ("local_row_ptr", "local_col", "halo_gcol", "recv_counts", "send_counts", "send_idx", "row_kind"):
+                assert np.array_equal(np.asarray(D[k]), np.asarray(L[k])), (rank, k)
+                assert np.array_equal(np.asarray(D[k]), np.asarray(O[k])), (rank, k, "oracle")
+            assert (D["nloc"], D["nnz_loc"], D["nhalo"], D["nsend"]) == (L["nloc"], L["nnz_loc"], L["nhalo"], L["nsend"])
         else:
             nz, ny, nx, steps = 9, 6, 10, 3
             full = oracle.fill((nz + 2) * (ny + 2) * (nx + 2), 7, np.float32)
