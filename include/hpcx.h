@@ -414,6 +414,47 @@ HPCX_API hpcx_status hpcx_csr_x_buffer(hpcx_csr A, void **x_full);
 HPCX_API hpcx_status hpcx_spmv_dist(hpcx_csr A, const void *x_local, void *y_local,
                                     void *stream);
 
+/* ------------------------------------------------ single process, several GPUs
+ * Every caller the reference has is a single-process program driving its containers from its own
+ * (OpenMP) loops (test_hpc_benchmark.cpp:356); the only multi-stream idiom it contains is driven
+ * by one thread too (cuda_tut_transfer_overlap.cu:92-103).  hpcx_init_multi gives such a program N
+ * GPUs without MPI or torchrun: one context per device inside the process, peer access enabled
+ * between all of them, everything driven from ONE host thread.  A host CSR matrix / host grid is
+ * partitioned by the library (hpcx_partition_rows + hpcx_csr_localize; even split of the slowest
+ * grid axis), and products / sweeps run through the same kernels and the same fused peer-store
+ * transport as the one-process-per-GPU path — the neighbours' buffers are plain peer pointers, and
+ * neither NCCL nor CUDA IPC is involved.  dev_ids == NULL selects devices 0 .. ndev-1.
+ * Not covered here: the CG solver across devices (its scalar all-reduce is NCCL's). */
+typedef struct hpcx_multi_s *hpcx_multi;
+HPCX_API hpcx_status hpcx_init_multi(int32_t ndev, const int32_t *dev_ids, hpcx_multi *out);
+HPCX_API hpcx_status hpcx_multi_finalize(hpcx_multi m);
+HPCX_API int32_t hpcx_multi_size(hpcx_multi m);
+HPCX_API hpcx_ctx hpcx_multi_ctx(hpcx_multi m, int32_t rank);
+HPCX_API const char *hpcx_multi_last_error_string(hpcx_multi m);
+/* y = A*x across all devices.  The descriptor names a HOST (or managed) square matrix; rows are cut
+ * into contiguous blocks (partition_mode as hpcx_partition_rows: 0 by rows, 1 by nonzeros), each
+ * device gets its block in [owned | halo] numbering with the halo tables, and the exchange lists
+ * are wired for the fused transport.  hpcx_multi_spmv takes HOST x and y of the global size. */
+typedef struct hpcx_multi_csr_s *hpcx_multi_csr;
+HPCX_API hpcx_status hpcx_multi_csr_create(hpcx_multi m, const hpcx_csr_desc *d, const hpcx_csr_opts *opts,
+                                           int32_t partition_mode, hpcx_multi_csr *out);
+HPCX_API hpcx_status hpcx_multi_csr_destroy(hpcx_multi_csr A);
+HPCX_API hpcx_status hpcx_multi_csr_bounds(hpcx_multi_csr A, int64_t *bounds /* hpcx_multi_size + 1 */);
+HPCX_API hpcx_status hpcx_multi_spmv(hpcx_multi_csr A, const void *x_host, void *y_host);
+/* A ghost-padded grid (2-D or 3-D) split along its slowest axis into one slab per device.  Upload
+ * hands every slab its ghost slices too (they are its neighbours' boundary slices in the host
+ * array); download writes the owned slices back.  hpcx_multi_stencil_sweep: BOX_X / BOX_Y (one
+ * sweep, slabs independent) and JACOBI7 over `steps` sweeps with the ghost planes traded by peer
+ * stores inside the sweep kernel (HPCX_VARIANT_TEMPORAL included); results are bit-identical to
+ * hpcx_stencil_sweep on one device. */
+typedef struct hpcx_multi_grid_s *hpcx_multi_grid;
+HPCX_API hpcx_status hpcx_multi_grid_create(hpcx_multi m, const hpcx_grid_desc *d, hpcx_multi_grid *out);
+HPCX_API hpcx_status hpcx_multi_grid_destroy(hpcx_multi_grid g);
+HPCX_API hpcx_status hpcx_multi_grid_upload(hpcx_multi_grid g, const void *host_flat);
+HPCX_API hpcx_status hpcx_multi_grid_download(hpcx_multi_grid g, void *host_flat);
+HPCX_API hpcx_status hpcx_multi_stencil_sweep(hpcx_multi_grid in, hpcx_multi_grid out,
+                                              const hpcx_stencil_desc *st, int32_t steps);
+
 /* ------------------------------------------------ CG iteration around SpMV
  * Conjugate gradients for a symmetric positive definite A created with the STREAM kernel —
  * either a single-rank matrix (nrows == ncols) or a distributed one (hpcx_csr_set_halo done:

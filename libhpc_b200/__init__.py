@@ -5,7 +5,7 @@ The product is libhpcx.so (csrc/, built by `python -m libhpc_b200.build`); this 
 the host-side mirror of the reference's container interface over that ABI.
 """
 from . import _abi  # noqa: F401
-from .api import (CgSolver, Context, ManagedArray, CsrMatrix, DeviceCsr, DeviceCsrArrays, DeviceGrid, HPCHighDimensionFlatArray,  # noqa: F401
+from .api import (CgSolver, Context, ManagedArray, MultiContext, MultiCsr, MultiGrid, multi_stencil_sweep, CsrMatrix, DeviceCsr, DeviceCsrArrays, DeviceGrid, HPCHighDimensionFlatArray,  # noqa: F401
                   HpcxError, conv2d, csr_from_cells, csr_from_coo, csr_localize, grid_transpose, partition_rows, partition_slabs, spmv, stencil_sweep,
                   synth_field, synth_rmat_csr,
                   stencil_sweep_host)

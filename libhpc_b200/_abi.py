@@ -130,6 +130,20 @@ PROTOTYPES = {
     "hpcx_csr_halo_transport": (_i32, [_vp, _i32]),
     "hpcx_csr_x_buffer": (_i32, [_vp, _P(_vp)]),
     "hpcx_spmv_dist": (_i32, [_vp, _vp, _vp, _vp]),
+    "hpcx_init_multi": (_i32, [_i32, _vp, _P(_vp)]),
+    "hpcx_multi_finalize": (_i32, [_vp]),
+    "hpcx_multi_size": (_i32, [_vp]),
+    "hpcx_multi_ctx": (_vp, [_vp, _i32]),
+    "hpcx_multi_last_error_string": (C.c_char_p, [_vp]),
+    "hpcx_multi_csr_create": (_i32, [_vp, _P(CsrDesc), _P(CsrOpts), _i32, _P(_vp)]),
+    "hpcx_multi_csr_destroy": (_i32, [_vp]),
+    "hpcx_multi_csr_bounds": (_i32, [_vp, _vp]),
+    "hpcx_multi_spmv": (_i32, [_vp, _vp, _vp]),
+    "hpcx_multi_grid_create": (_i32, [_vp, _P(GridDesc), _P(_vp)]),
+    "hpcx_multi_grid_destroy": (_i32, [_vp]),
+    "hpcx_multi_grid_upload": (_i32, [_vp, _vp]),
+    "hpcx_multi_grid_download": (_i32, [_vp, _vp]),
+    "hpcx_multi_stencil_sweep": (_i32, [_vp, _vp, _P(StencilDesc), _i32]),
     "hpcx_cg_create": (_i32, [_vp, _P(_vp)]),
     "hpcx_cg_destroy": (_i32, [_vp]),
     "hpcx_cg_solve": (_i32, [_vp, _vp, _i32, _vp, _i32, _i32, C.c_double, _i32, _P(CgResult), _vp]),

@@ -659,3 +659,113 @@ def csr_localize(A: CsrMatrix, bounds, rank: int) -> dict:
     p0 = int(A.row_ptr[bounds[rank]])
     out["values"] = A.values[p0:p0 + out["nnz_loc"]]
     return out
+
+
+# ------------------------------------------------------------------ one process, several GPUs
+class MultiContext:
+    """hpcx_init_multi: N GPUs driven from this one process / thread (peer access, no NCCL, no IPC).
+    devices=None takes every visible GPU."""
+
+    def __init__(self, devices=None):
+        self.lib = _abi.load()
+        if devices is None:
+            import torch
+            devices = list(range(torch.cuda.device_count()))
+        self.devices = [int(d) for d in devices]
+        ids = (C.c_int32 * len(self.devices))(*self.devices)
+        h = C.c_void_p()
+        st = self.lib.hpcx_init_multi(len(self.devices), ids, C.byref(h))
+        self.h = h
+        if st != _abi.OK:
+            msg = self.lib.hpcx_multi_last_error_string(h).decode() if h else "hpcx_init_multi failed"
+            if h:
+                self.lib.hpcx_multi_finalize(h)
+            self.h = None
+            _raise(st, msg)
+
+    @property
+    def size(self) -> int:
+        return int(self.lib.hpcx_multi_size(self.h))
+
+    def check(self, st: int):
+        if st != _abi.OK:
+            _raise(st, self.lib.hpcx_multi_last_error_string(self.h).decode())
+
+    def close(self):
+        if self.h:
+            self.lib.hpcx_multi_finalize(self.h)
+            self.h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+
+class MultiCsr:
+    """A host CsrMatrix partitioned over the devices of a MultiContext (hpcx_multi_csr_create)."""
+
+    def __init__(self, mctx: MultiContext, A: CsrMatrix, mode: int = 0, kernel: int = SPMV_AUTO, tile_nnz: int = 0):
+        self.m, self.host = mctx, A
+        d = _abi.CsrDesc(A.nrows, A.ncols, A.nnz, A.row_ptr.ctypes.data, A.row_ptr.dtype.itemsize,
+                         _dtype_code(A.dtype), A.col_idx.ctypes.data if A.nnz else None,
+                         A.values.ctypes.data if A.nnz else None, MEM_HOST, 0)
+        o = _abi.CsrOpts(kernel, tile_nnz, 0, 0, 0, 0)
+        h = C.c_void_p()
+        mctx.check(mctx.lib.hpcx_multi_csr_create(mctx.h, C.byref(d), C.byref(o), mode, C.byref(h)))
+        self.h = h
+
+    def bounds(self) -> np.ndarray:
+        b = np.empty(self.m.size + 1, dtype=np.int64)
+        self.m.check(self.m.lib.hpcx_multi_csr_bounds(self.h, b.ctypes.data))
+        return b
+
+    def spmv(self, x: np.ndarray, y: np.ndarray | None = None) -> np.ndarray:
+        x = np.ascontiguousarray(x, dtype=self.host.dtype)
+        if y is None:
+            y = np.empty(self.host.nrows, dtype=self.host.dtype)
+        self.m.check(self.m.lib.hpcx_multi_spmv(self.h, x.ctypes.data, y.ctypes.data))
+        return y
+
+    def destroy(self):
+        if self.h:
+            self.m.lib.hpcx_multi_csr_destroy(self.h)
+            self.h = None
+
+
+class MultiGrid:
+    """A ghost-padded grid split along its slowest axis over the devices (hpcx_multi_grid_*)."""
+
+    def __init__(self, mctx: MultiContext, dims, dtype=np.float32, lo: int = 0, hi: int | None = None):
+        self.m = mctx
+        self.dims = tuple(int(d) for d in dims)
+        self.dtype = np.dtype(dtype)
+        self.lo = int(lo)
+        self.hi = self.lo if hi is None else int(hi)
+        self.desc = _abi.GridDesc(len(dims), _dtype_code(dtype), self.lo, self.hi, (C.c_int64 * 3)(*self.dims))
+        h = C.c_void_p()
+        mctx.check(mctx.lib.hpcx_multi_grid_create(mctx.h, C.byref(self.desc), C.byref(h)))
+        self.h = h
+        self.total_host = int(np.prod([d + self.lo + self.hi for d in self.dims]))
+
+    def upload(self, host_flat: np.ndarray):
+        assert host_flat.size == self.total_host and host_flat.dtype == self.dtype and host_flat.flags["C_CONTIGUOUS"]
+        self.m.check(self.m.lib.hpcx_multi_grid_upload(self.h, host_flat.ctypes.data))
+
+    def download(self, out: np.ndarray) -> np.ndarray:
+        """Writes the owned slices into `out` (the global flat array; its ghosts are left as they are)."""
+        assert out.size == self.total_host and out.dtype == self.dtype and out.flags["C_CONTIGUOUS"]
+        self.m.check(self.m.lib.hpcx_multi_grid_download(self.h, out.ctypes.data))
+        return out
+
+    def destroy(self):
+        if self.h:
+            self.m.lib.hpcx_multi_grid_destroy(self.h)
+            self.h = None
+
+
+def multi_stencil_sweep(gin: MultiGrid, gout: MultiGrid, kind: int, radius: int = 0, steps: int = 1,
+                        variant: int = VARIANT_AUTO, zsplit: int = 0):
+    d = stencil_desc(kind, radius, variant, zsplit)
+    gin.m.check(gin.m.lib.hpcx_multi_stencil_sweep(gin.h, gout.h, C.byref(d), steps))

@@ -10,8 +10,7 @@
 
 #include <algorithm>
 
-#include "grid.cuh"
-#include "spmv.cuh"
+#include "dist.cuh"
 
 using namespace hpcx;
 
@@ -86,22 +85,7 @@ inline ncclDataType_t nccl_type(int dtype) { return dtype == HPCX_F64 ? ncclFloa
 }  // namespace
 
 // ------------------------------------------------------------------ distributed stencil
-struct hpcx_halo_plan_s {
-  hpcx_ctx ctx = nullptr;
-  hpcx_grid in = nullptr, out = nullptr;
-  hpcx_stencil_desc st{};
-  int transport = 0;
-  cudaEvent_t ev_bnd = nullptr, ev_recv = nullptr, ev_start = nullptr;
-  // transport 1 (peer stores): neighbour side 0 = rank-1, 1 = rank+1
-  uint32_t *flags = nullptr;          // local block: [0],[1] flags, [4],[5] counters, [8] push counter
-  void *buf[2] = {nullptr, nullptr};  // this rank's two grid buffers at plan time (A = in, B = out)
-  void *peer_open[2][3] = {};         // bases returned by cudaIpcOpenMemHandle (A, B, flags)
-  float *peer_buf[2][2] = {};         // the neighbour's A and B
-  uint32_t *peer_flags[2] = {nullptr, nullptr};
-  int64_t peer_n0[2] = {0, 0};
-  uint32_t epoch = 0;                 // sweeps completed through this plan
-};
-
+// (struct hpcx_halo_plan_s: dist.cuh)
 namespace {
 
 // Exchange w ghost planes per side of buffer `buf` (device layout of grid g) with the z
@@ -180,6 +164,8 @@ void close_peers(hpcx_halo_plan p) {
   p->flags = nullptr;
 }
 
+}  // namespace
+namespace hpcx {
 // The local flag block of a peer-store plan, and the two buffers the plan was made for.
 hpcx_status plan_prepare(hpcx_halo_plan p) {
   hpcx_ctx ctx = p->ctx;
@@ -192,6 +178,8 @@ hpcx_status plan_prepare(hpcx_halo_plan p) {
   return HPCX_OK;
 }
 
+}  // namespace hpcx
+namespace {
 // Opens the neighbours' grid buffers and flag blocks.  Collective over the communicator.
 hpcx_status open_peers(hpcx_halo_plan p) {
   hpcx_ctx ctx = p->ctx;
@@ -433,7 +421,9 @@ hpcx_status hpcx_stencil_dist_plan(hpcx_ctx ctx, hpcx_grid in, hpcx_grid out,
 // no second stream and no pack kernel on the data path; the exchange overlaps the interior
 // planes of the same kernel.  Two-sweep passes (HPCX_VARIANT_TEMPORAL) run the plain pass kernel
 // and push their two boundary planes per side with halo_push_planes_kernel right behind it.
-static hpcx_status dist_sweep_peer(hpcx_halo_plan p, int32_t steps, cudaStream_t cs, bool sync) {
+}  // extern "C"
+namespace hpcx {
+hpcx_status stencil_peer_sweep(hpcx_halo_plan p, int32_t steps, cudaStream_t cs, bool sync) {
   hpcx_ctx ctx = p->ctx;
   hpcx_grid g = p->in;
   const bool has_lo = ctx->rank > 0, has_hi = ctx->rank + 1 < ctx->nranks;
@@ -492,6 +482,8 @@ static hpcx_status dist_sweep_peer(hpcx_halo_plan p, int32_t steps, cudaStream_t
   if (sync) return sync_and_check(ctx, cs);
   return HPCX_OK;
 }
+}  // namespace hpcx
+extern "C" {
 
 // Per step t (src -> dst):
 //   compute stream: [wait ghosts of src] boundary planes z = 0, n-1  -> record ev_bnd
@@ -521,7 +513,7 @@ hpcx_status hpcx_stencil_dist_sweep(hpcx_halo_plan p, int32_t steps, void *strea
 
   if (p->transport == 1 && ctx->nranks > 1) {
     HPCX_CUDA(ctx, cudaStreamWaitEvent(cs, p->ev_recv, 0));
-    return dist_sweep_peer(p, steps, cs, stream == nullptr);
+    return hpcx::stencil_peer_sweep(p, steps, cs, stream == nullptr);
   }
 
   // A pass advances the slab by w sweeps (w = 2: the temporally blocked kernel) and needs w valid
@@ -880,7 +872,7 @@ hpcx_status hpcx_spmv_dist(hpcx_csr A, const void *x_local, void *y_local, void 
   HPCX_RANGE("hpcx_spmv_dist");
   hpcx_ctx ctx = A->ctx;
   HPCX_REQUIRE(ctx, A->d_xfull != nullptr, "hpcx_csr_set_halo has not been called");
-  if (ctx->nranks > 1 && !ctx->nccl_comm)
+  if (ctx->nranks > 1 && A->transport == 0 && !ctx->nccl_comm)  // peer stores need no communicator
     return fail(ctx, HPCX_NCCL_ERROR, "hpcx_comm_init has not been called");
   cudaStream_t cs = stream ? (cudaStream_t)stream : ctx->compute;
   cudaStream_t ms = ctx->comm;

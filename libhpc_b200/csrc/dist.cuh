@@ -1,0 +1,29 @@
+// dist.cuh — internals shared by the multi-GPU transports: dist.cu (one process per GPU: NCCL
+// and CUDA IPC windows) and multi.cu (one process, several GPUs: plain peer pointers).
+#pragma once
+#include "grid.cuh"
+#include "spmv.cuh"
+
+struct hpcx_halo_plan_s {
+  hpcx_ctx ctx = nullptr;
+  hpcx_grid in = nullptr, out = nullptr;
+  hpcx_stencil_desc st{};
+  int transport = 0;
+  cudaEvent_t ev_bnd = nullptr, ev_recv = nullptr, ev_start = nullptr;
+  // transport 1 (peer stores): neighbour side 0 = rank-1, 1 = rank+1
+  uint32_t *flags = nullptr;          // local block: [0],[1] flags, [4],[5] counters, [8] push counter
+  void *buf[2] = {nullptr, nullptr};  // this rank's two grid buffers at plan time (A = in, B = out)
+  void *peer_open[2][3] = {};         // bases returned by cudaIpcOpenMemHandle (A, B, flags)
+  float *peer_buf[2][2] = {};         // the neighbour's A and B
+  uint32_t *peer_flags[2] = {nullptr, nullptr};
+  int64_t peer_n0[2] = {0, 0};
+  uint32_t epoch = 0;                 // sweeps completed through this plan
+};
+
+
+namespace hpcx {
+hpcx_status plan_prepare(hpcx_halo_plan p);  // local flag block + the plan's two buffers
+// `steps` sweeps through the fused peer-store transport on stream cs (the neighbours' windows in
+// p->peer_* must be wired); sync: wait for the stream and report a flag timeout.
+hpcx_status stencil_peer_sweep(hpcx_halo_plan p, int32_t steps, cudaStream_t cs, bool sync);
+}  // namespace hpcx
