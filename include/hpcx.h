@@ -189,6 +189,18 @@ HPCX_API hpcx_status hpcx_grid_unpack_face(hpcx_grid g, int32_t axis, int32_t si
                                            int32_t width, const void *buf, int32_t buf_mem,
                                            void *stream);
 
+/* Halo index map of one face in the REFERENCE layout (flat offsets into data() of
+ * hpc::HPCHighDimensionFlatArray, strides as compute_stride_and_total, …:161-171): the cells the
+ * neighbour across (axis, side) needs — the `width` interior slices next to that side (send) —
+ * and the ghost cells it fills here (recv).  Both are *nruns runs of *run_len consecutive elements;
+ * send_start / recv_start (either may be NULL; *nruns entries) receive the first offset of every
+ * run, slower coordinates in row-major order (ghost positions of the slower axes included, as in
+ * hpcx_grid_pack_face).  For a slab split (axis 0) there is a single run: the face is contiguous
+ * and is exchanged in place.  Host only, pure integer. */
+HPCX_API hpcx_status hpcx_grid_export_halo_maps(const hpcx_grid_desc *d, int32_t axis, int32_t side,
+                                                int32_t width, int64_t *nruns, int64_t *run_len,
+                                                int64_t *send_start, int64_t *recv_start);
+
 /* ------------------------------------------------------------- CSR matrix (a7-a9) */
 typedef struct {
   int64_t nrows, ncols, nnz;
@@ -372,9 +384,13 @@ HPCX_API hpcx_status hpcx_comm_ipc_close(hpcx_ctx ctx, void *peer_ptr);
 HPCX_API hpcx_status hpcx_comm_set_timeout(hpcx_ctx ctx, int64_t milliseconds);
 HPCX_API hpcx_status hpcx_comm_check(hpcx_ctx ctx);
 
-/* Distributed stencil: every rank owns a z-slab (axis 0) grid pair created with
- * hpcx_grid_create; neighbours are rank-1 / rank+1 (no periodic wrap: the outermost
- * ghost planes stay Dirichlet).  transport:
+/* Distributed stencil: every rank owns a slab along axis 0 (z planes of a 3-D grid, rows of a 2-D
+ * grid) as a grid pair created with hpcx_grid_create; neighbours are rank-1 / rank+1 (no periodic
+ * wrap: the outermost ghost slices stay Dirichlet).
+ * BOX_X / BOX_Y (the reference's 17-point sweeps over y-slabs, steps == 1, transport 0): BOX_X needs
+ * no exchange; BOX_Y receives the `radius` ghost rows of `in` from the neighbours on the comm
+ * stream while the rows that need none of them are swept, then sweeps the two boundary strips.
+ * JACOBI7 transport:
  *   0  NCCL send/recv of the boundary planes on the comm stream, overlapped with the interior
  *      sweep on the compute stream (three launches per sweep);
  *   1  fused: one kernel per sweep whose boundary CTAs store their plane straight into the
@@ -454,6 +470,14 @@ HPCX_API hpcx_status hpcx_multi_grid_upload(hpcx_multi_grid g, const void *host_
 HPCX_API hpcx_status hpcx_multi_grid_download(hpcx_multi_grid g, void *host_flat);
 HPCX_API hpcx_status hpcx_multi_stencil_sweep(hpcx_multi_grid in, hpcx_multi_grid out,
                                               const hpcx_stencil_desc *st, int32_t steps);
+
+/* The same product with HOST operands (nloc entries each; pinned memory makes the copies
+ * asynchronous).  With the fused transport the copies, the exchange and the product overlap: the
+ * last piece of x goes up first, then the others; once both ends of the owned block have landed one
+ * launch pushes the boundary entries to the neighbours and computes the boundary rows, and the
+ * interior rows follow in chunks whose rows of y travel back while later chunks compute.
+ * Synchronous.  Collective in the sense of hpcx_spmv_dist: every rank must make the call. */
+HPCX_API hpcx_status hpcx_spmv_dist_host(hpcx_csr A, const void *x_host, void *y_host, void *stream);
 
 /* ------------------------------------------------ CG iteration around SpMV
  * Conjugate gradients for a symmetric positive definite A created with the STREAM kernel —

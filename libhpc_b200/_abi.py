@@ -90,6 +90,7 @@ PROTOTYPES = {
     "hpcx_grid_upload": (_i32, [_vp, _vp, _vp]),
     "hpcx_grid_download": (_i32, [_vp, _vp, _vp]),
     "hpcx_grid_device_layout": (_i32, [_vp, _P(_i64), _P(_i64), _P(_i64), _P(_vp)]),
+    "hpcx_grid_export_halo_maps": (_i32, [_P(GridDesc), _i32, _i32, _i32, _P(_i64), _P(_i64), _vp, _vp]),
     "hpcx_stencil_sweep": (_i32, [_vp, _vp, _P(StencilDesc), _i32, _vp]),
     "hpcx_conv2d": (_i32, [_vp, _vp, _vp, _i32, _i32, _i32, _vp]),
     "hpcx_grid_transpose": (_i32, [_vp, _vp, _vp]),
@@ -130,6 +131,7 @@ PROTOTYPES = {
     "hpcx_csr_halo_transport": (_i32, [_vp, _i32]),
     "hpcx_csr_x_buffer": (_i32, [_vp, _P(_vp)]),
     "hpcx_spmv_dist": (_i32, [_vp, _vp, _vp, _vp]),
+    "hpcx_spmv_dist_host": (_i32, [_vp, _vp, _vp, _vp]),
     "hpcx_init_multi": (_i32, [_i32, _vp, _P(_vp)]),
     "hpcx_multi_finalize": (_i32, [_vp]),
     "hpcx_multi_size": (_i32, [_vp]),

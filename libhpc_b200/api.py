@@ -295,6 +295,23 @@ class DeviceGrid:
             self.h = None
 
 
+def grid_halo_maps(dims, lo: int, hi: int, axis: int, side: int, width: int, dtype=np.float32):
+    """hpcx_grid_export_halo_maps: (run_len, send_start[], recv_start[]) of one face, flat offsets in
+    the reference layout."""
+    desc = _abi.GridDesc(len(dims), _dtype_code(dtype), lo, hi, (C.c_int64 * 3)(*[int(d) for d in dims]))
+    nruns, run_len = C.c_int64(), C.c_int64()
+    lib = _abi.load()
+    rc = lib.hpcx_grid_export_halo_maps(C.byref(desc), axis, side, width, C.byref(nruns), C.byref(run_len), None, None)
+    if rc != _abi.OK:
+        _raise(rc, "hpcx_grid_export_halo_maps")
+    send, recv = np.empty(nruns.value, dtype=np.int64), np.empty(nruns.value, dtype=np.int64)
+    rc = lib.hpcx_grid_export_halo_maps(C.byref(desc), axis, side, width, C.byref(nruns), C.byref(run_len),
+                                        send.ctypes.data, recv.ctypes.data)
+    if rc != _abi.OK:
+        _raise(rc, "hpcx_grid_export_halo_maps")
+    return int(run_len.value), send, recv
+
+
 def stencil_desc(kind: int, radius: int = 0, variant: int = VARIANT_AUTO, zsplit: int = 0):
     return _abi.StencilDesc(kind, radius, variant, zsplit)
 
@@ -470,6 +487,13 @@ class DeviceCsr:
     def spmv_dist(self, x_local, y_local, stream=None):
         self.ctx.check(self.ctx.lib.hpcx_spmv_dist(self.h, _ptr(x_local)[0], _ptr(y_local)[0],
                                                    _stream(stream)))
+
+    def spmv_dist_host(self, x_host, y_host, stream=None):
+        """hpcx_spmv_dist_host: host x / y (this rank's owned entries), pipelined against PCIe."""
+        px, mx = _ptr(x_host)
+        py, my = _ptr(y_host)
+        assert mx == MEM_HOST and my == MEM_HOST
+        self.ctx.check(self.ctx.lib.hpcx_spmv_dist_host(self.h, px, py, _stream(stream)))
 
     def destroy(self):
         if self.h:

@@ -9,6 +9,7 @@
 #include <nccl.h>
 
 #include <algorithm>
+#include <functional>
 
 #include "dist.cuh"
 
@@ -19,6 +20,8 @@ hpcx_status jacobi7_launch(hpcx_grid_s *g, void *src, void *dst, int variant, in
                            int64_t zbeg, int64_t zend, cudaStream_t s, const JacobiPeer *peer);
 hpcx_status allreduce_sum(hpcx_ctx ctx, void *buf, size_t count, int dtype, cudaStream_t s);
 bool jacobi7_tb2_supported(hpcx_grid_s *g);
+hpcx_status box_launch_rows(hpcx_grid_s *in, hpcx_grid_s *out, const hpcx_stencil_desc *st, int64_t y0, int64_t y1,
+                            cudaStream_t s);
 hpcx_status jacobi7_tb2_launch(hpcx_grid_s *g, void *src, void *dst, int zsplit, int64_t zbeg, int64_t zend,
                                bool nb_lo, bool nb_hi, cudaStream_t s, int64_t zbeg2 = 0, int64_t zend2 = 0);
 hpcx_status spmv_launch_blocks(hpcx_csr A, const RowBlock *d_blocks, int64_t nblocks, const void *x,
@@ -26,6 +29,8 @@ hpcx_status spmv_launch_blocks(hpcx_csr A, const RowBlock *d_blocks, int64_t nbl
 hpcx_status spmv_launch_fixup_tables(hpcx_csr A, const int32_t *long_row, const int32_t *long_off,
                                      int64_t nlong, void *y, cudaStream_t s, const void *x,
                                      void *dot_part);
+hpcx_status spmv_dist_host_pipelined(hpcx_csr A, const void *x, void *y, cudaStream_t s,
+                                     const std::function<hpcx_status()> &push_and_boundary);
 hpcx_status csr_plan_rowblocks(hpcx_csr A, const uint8_t *d_kind, int64_t maxlen, RowBlock **d_blocks,
                                std::vector<RowBlock> *host, int64_t *n0, int32_t **d_long_row,
                                int32_t **d_long_off, int64_t *nlong, int64_t *nchunks);
@@ -93,9 +98,12 @@ namespace {
 hpcx_status exchange_planes(hpcx_grid g, void *buf, cudaStream_t s, int64_t w = 1) {
   hpcx_ctx ctx = g->ctx;
   if (ctx->nranks <= 1) return HPCX_OK;
-  const int64_t plane = g->ext[1] * g->pitch;
+  // slices of the split axis: z planes of a 3-D grid, rows of a 2-D grid (both contiguous)
+  const bool rows2d = g->desc.ndim == 2;
+  const int64_t plane = rows2d ? g->pitch : g->ext[1] * g->pitch;
+  const int64_t nown = rows2d ? g->n[1] : g->n[0], glo = rows2d ? g->glo[1] : g->glo[0];
   char *base = static_cast<char *>(buf);
-  auto at = [&](int64_t z) { return base + (z + g->glo[0]) * plane * g->es; };
+  auto at = [&](int64_t z) { return base + (z + glo) * plane * g->es; };
   const ncclDataType_t ty = nccl_type(g->desc.dtype);
   const int lo = ctx->rank - 1, hi = ctx->rank + 1;
   HPCX_NCCL(ctx, g_nccl.GroupStart());
@@ -104,8 +112,8 @@ hpcx_status exchange_planes(hpcx_grid g, void *buf, cudaStream_t s, int64_t w = 
     HPCX_NCCL(ctx, g_nccl.Recv(at(-w), (size_t)(w * plane), ty, lo, comm_of(ctx), s));
   }
   if (hi < ctx->nranks) {
-    HPCX_NCCL(ctx, g_nccl.Send(at(g->n[0] - w), (size_t)(w * plane), ty, hi, comm_of(ctx), s));
-    HPCX_NCCL(ctx, g_nccl.Recv(at(g->n[0]), (size_t)(w * plane), ty, hi, comm_of(ctx), s));
+    HPCX_NCCL(ctx, g_nccl.Send(at(nown - w), (size_t)(w * plane), ty, hi, comm_of(ctx), s));
+    HPCX_NCCL(ctx, g_nccl.Recv(at(nown), (size_t)(w * plane), ty, hi, comm_of(ctx), s));
   }
   HPCX_NCCL(ctx, g_nccl.GroupEnd());
   return HPCX_OK;
@@ -353,7 +361,32 @@ hpcx_status hpcx_stencil_dist_plan(hpcx_ctx ctx, hpcx_grid in, hpcx_grid out,
                                    hpcx_halo_plan *out_plan) {
   if (!ctx || !in || !out || !st || !out_plan) return HPCX_INVALID_ARG;
   *out_plan = nullptr;
-  HPCX_REQUIRE(ctx, st->kind == HPCX_STENCIL_JACOBI7, "distributed sweeps support JACOBI7");
+  if (st->kind == HPCX_STENCIL_BOX_X || st->kind == HPCX_STENCIL_BOX_Y) {
+    // the reference's 17-point sweeps over y-slabs (rows split like its static chunking,
+    // test_hpc_benchmark.cpp:1356,1371-1372): BOX_X needs no exchange, BOX_Y trades `radius` rows
+    HPCX_REQUIRE(ctx, in->desc.ndim == 2 && out->desc.ndim == 2, "box sweeps take 2-D grids");
+    HPCX_REQUIRE(ctx, in->desc.dtype == out->desc.dtype, "grids differ in dtype");
+    HPCX_REQUIRE(ctx, in->desc.dim[0] == out->desc.dim[0] && in->desc.dim[1] == out->desc.dim[1],
+                 "grids differ in logical extent");
+    HPCX_REQUIRE(ctx, st->radius >= 0 && st->radius <= in->desc.lo && st->radius <= in->desc.hi,
+                 "radius exceeds the ghost width of the input grid");
+    HPCX_REQUIRE(ctx, in->n[1] >= std::max(st->radius, 1), "a slab needs at least `radius` rows");
+    if (transport != 0)
+      return fail(ctx, HPCX_UNSUPPORTED, "distributed box sweeps use the NCCL transport (0)");
+    if (ctx->nranks > 1 && !ctx->nccl_comm) return fail(ctx, HPCX_NCCL_ERROR, "hpcx_comm_init has not been called");
+    hpcx_halo_plan p = new (std::nothrow) hpcx_halo_plan_s();
+    if (!p) return fail(ctx, HPCX_OOM, "host allocation failed");
+    p->ctx = ctx;
+    p->in = in;
+    p->out = out;
+    p->st = *st;
+    cudaEventCreateWithFlags(&p->ev_bnd, cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&p->ev_recv, cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&p->ev_start, cudaEventDisableTiming);
+    *out_plan = p;
+    return HPCX_OK;
+  }
+  HPCX_REQUIRE(ctx, st->kind == HPCX_STENCIL_JACOBI7, "unknown stencil kind");
   HPCX_REQUIRE(ctx, in->desc.ndim == 3 && out->desc.ndim == 3, "JACOBI7 takes 3-D grids");
   HPCX_REQUIRE(ctx, in->desc.dtype == out->desc.dtype, "grids differ in dtype");
   for (int i = 0; i < 3; ++i)
@@ -504,6 +537,39 @@ hpcx_status hpcx_stencil_dist_sweep(hpcx_halo_plan p, int32_t steps, void *strea
   const int64_t nz = g->n[0];
   hpcx_status rc = HPCX_OK;
 
+  if (p->st.kind == HPCX_STENCIL_BOX_X || p->st.kind == HPCX_STENCIL_BOX_Y) {
+    // One sweep in -> out over this rank's y-slab.  BOX_Y: the `radius` ghost rows of `in` come from
+    // the neighbours (rows are contiguous: nothing is packed) on the comm stream while the rows that
+    // need none of them are swept; the two boundary strips follow the receive.
+    HPCX_REQUIRE(ctx, steps == 1, "box sweeps are single-step");
+    const int64_t ny = g->n[1], r = p->st.kind == HPCX_STENCIL_BOX_Y ? p->st.radius : 0;
+    if (r == 0 || ctx->nranks <= 1) {
+      rc = box_launch_rows(p->in, p->out, &p->st, 0, ny, cs);
+    } else {
+      HPCX_CUDA(ctx, cudaEventRecord(p->ev_start, cs));
+      HPCX_CUDA(ctx, cudaStreamWaitEvent(ms, p->ev_start, 0));
+      {
+        HPCX_RANGE("box sweep: ghost-row exchange (NCCL send/recv)");
+        rc = exchange_planes(g, p->in->dev, ms, r);
+      }
+      if (rc != HPCX_OK) return rc;
+      HPCX_CUDA(ctx, cudaEventRecord(p->ev_recv, ms));
+      const int64_t lo_end = std::min<int64_t>(r, ny), hi_beg = std::max<int64_t>(lo_end, ny - r);
+      {
+        HPCX_RANGE("box sweep: interior rows");
+        rc = box_launch_rows(p->in, p->out, &p->st, lo_end, hi_beg, cs);
+      }
+      if (rc != HPCX_OK) return rc;
+      HPCX_CUDA(ctx, cudaStreamWaitEvent(cs, p->ev_recv, 0));
+      HPCX_RANGE("box sweep: boundary strips");
+      rc = box_launch_rows(p->in, p->out, &p->st, 0, lo_end, cs);
+      if (rc == HPCX_OK) rc = box_launch_rows(p->in, p->out, &p->st, hi_beg, ny, cs);
+    }
+    if (rc != HPCX_OK) return rc;
+    if (!stream) HPCX_CUDA(ctx, cudaStreamSynchronize(cs));
+    return HPCX_OK;
+  }
+
   // Make the ghosts of the first source iterate consistent with the neighbours.
   HPCX_CUDA(ctx, cudaEventRecord(p->ev_start, cs));
   HPCX_CUDA(ctx, cudaStreamWaitEvent(ms, p->ev_start, 0));
@@ -628,6 +694,16 @@ void close_csr_peers(hpcx_csr A) {
 namespace hpcx {
 void csr_close_peers(hpcx_csr A) { close_csr_peers(A); }
 
+// see preload_stencil_kernels (stencil.cu)
+hpcx_status preload_dist_kernels(hpcx_ctx ctx) {
+  cudaFuncAttributes a;
+  HPCX_CUDA(ctx, cudaFuncGetAttributes(&a, (const void *)halo_wait_kernel));
+  HPCX_CUDA(ctx, cudaFuncGetAttributes(&a, (const void *)halo_push_planes_kernel));
+  HPCX_CUDA(ctx, cudaFuncGetAttributes(&a, (const void *)gather_boundary_x_kernel<float>));
+  HPCX_CUDA(ctx, cudaFuncGetAttributes(&a, (const void *)gather_boundary_x_kernel<double>));
+  return HPCX_OK;
+}
+
 // The sync block of the fused transport: flags by source rank, acks by destination rank, counters.
 hpcx_status csr_peer_prepare(hpcx_csr A) {
   hpcx_ctx ctx = A->ctx;
@@ -748,6 +824,8 @@ hpcx_status hpcx_csr_set_halo(hpcx_csr A, int64_t nloc, int64_t nhalo, const int
   if (st != HPCX_OK) return st;
   A->h_blocks_int.assign(all.begin(), all.begin() + n0);
   A->h_blocks_bnd.assign(all.begin() + n0, all.end());
+  for (cudaEvent_t e : A->pipe_dist.ev) cudaEventDestroy(e);
+  A->pipe_dist = PipePlan{};  // the chunking of the host-operand pipeline follows the new tables
   A->d_blocks_int = A->d_blocks_dist;
   A->d_blocks_bnd = A->d_blocks_dist + n0;
   return HPCX_OK;
@@ -827,14 +905,15 @@ static inline void *dot_slot(hpcx_csr A, int64_t first) {
 // blocks | boundary row blocks]: the push CTAs run first (gather + peer stores + flags), the
 // interior blocks overlap the neighbours' pushes, the boundary blocks acquire the flags themselves
 // and the last of them acks the source ranks (round 1 needed five launches for the same).
-static hpcx_status spmv_dist_peer(hpcx_csr A, char *xfull, void *y_local, cudaStream_t cs) {
+static hpcx_status spmv_dist_peer(hpcx_csr A, char *xfull, void *y_local, cudaStream_t cs, bool boundary_only = false) {
   hpcx_ctx ctx = A->ctx;
   HPCX_RANGE("spmv_dist: one launch (push | interior | boundary + ack)");
   SpmvDistArgs da;
   da.epoch = ++A->epoch;
   da.nseg = A->nseg;
   da.nsrc = A->nsrc;
-  da.n_int = (int)A->h_blocks_int.size();
+  // boundary_only (host-operand pipeline): the interior rows run as separate chunked launches
+  da.n_int = boundary_only ? 0 : (int)A->h_blocks_int.size();
   da.n_bnd = (int)A->h_blocks_bnd.size();
   int64_t longest = 0;
   for (int q = 0; q < ctx->nranks; ++q) longest = std::max(longest, A->send_counts[q]);
@@ -851,11 +930,39 @@ static hpcx_status spmv_dist_peer(hpcx_csr A, char *xfull, void *y_local, cudaSt
   da.pw = peer_wait_of(ctx);
   if (A->nsrc > 0 && da.n_bnd == 0)
     return fail(ctx, HPCX_INVALID_ARG, "halo entries are received but no row is marked as a boundary row");
-  hpcx_status rc = spmv_launch_blocks(A, A->d_blocks_dist, (int64_t)da.n_int + da.n_bnd, xfull, y_local, cs,
-                                      dot_slot(A, 0), &da);
-  if (rc != HPCX_OK) return rc;
+  hpcx_status rc = spmv_launch_blocks(A, boundary_only ? A->d_blocks_bnd : A->d_blocks_dist,
+                                      (int64_t)da.n_int + da.n_bnd, xfull, y_local, cs, dot_slot(A, 0), &da);
+  if (rc != HPCX_OK || boundary_only) return rc;
   return spmv_launch_fixup_tables(A, A->d_long_row_dist, A->d_long_off_dist, A->nlong_dist, y_local, cs, xfull,
                                   dot_slot(A, (int64_t)da.n_int + da.n_bnd));
+}
+
+// Host operands: x_host / y_host hold this rank's nloc owned entries.  With the fused transport
+// the call is pipelined against PCIe like hpcx_spmv with host operands: the last piece of x goes
+// up first, then the others; as soon as both ends of the owned block have landed one launch pushes
+// the boundary entries to the neighbours and computes the boundary rows, and the interior rows
+// follow in chunks whose rows of y travel back while later chunks still compute.  Otherwise:
+// copy, product, copy.  Synchronous (the result is in y_host on return).
+hpcx_status hpcx_spmv_dist_host(hpcx_csr A, const void *x_host, void *y_host, void *stream) {
+  if (!A || !x_host || !y_host) return HPCX_INVALID_ARG;
+  HPCX_RANGE("hpcx_spmv_dist_host");
+  hpcx_ctx ctx = A->ctx;
+  HPCX_REQUIRE(ctx, A->d_xfull != nullptr, "hpcx_csr_set_halo has not been called");
+  cudaStream_t cs = stream ? (cudaStream_t)stream : ctx->compute;
+  char *xfull = static_cast<char *>(A->d_xfull);
+  const size_t nb = (size_t)A->nloc * A->es;
+  if (A->transport == 1 && ctx->nranks > 1 && !A->dot_part) {
+    hpcx_status st = spmv_dist_host_pipelined(A, x_host, y_host, cs, [&]() {
+      return spmv_dist_peer(A, xfull, A->d_y, cs, true);
+    });
+    if (st == HPCX_OK) return sync_and_check(ctx, cs);
+    if (st != HPCX_UNSUPPORTED) return st;
+  }
+  if (!A->d_y) HPCX_CUDA(ctx, cudaMalloc(&A->d_y, std::max<size_t>(nb, 1)));
+  if (nb) HPCX_CUDA(ctx, cudaMemcpyAsync(xfull, x_host, nb, cudaMemcpyHostToDevice, cs));
+  if (hpcx_status st = hpcx_spmv_dist(A, xfull, A->d_y, cs)) return st;
+  if (nb) HPCX_CUDA(ctx, cudaMemcpyAsync(y_host, A->d_y, nb, cudaMemcpyDeviceToHost, cs));
+  return sync_and_check(ctx, cs);
 }
 
 hpcx_status hpcx_csr_x_buffer(hpcx_csr A, void **x_full) {

@@ -22,6 +22,10 @@ struct hpcx_halo_plan_s {
 
 
 namespace hpcx {
+// kernels of the peer transports loaded ahead of their first launch (see stencil.cu)
+hpcx_status preload_stencil_kernels(hpcx_ctx ctx);
+hpcx_status preload_dist_kernels(hpcx_ctx ctx);
+hpcx_status preload_spmv_kernels(hpcx_ctx ctx);
 hpcx_status plan_prepare(hpcx_halo_plan p);  // local flag block + the plan's two buffers
 // `steps` sweeps through the fused peer-store transport on stream cs (the neighbours' windows in
 // p->peer_* must be wired); sync: wait for the stream and report a flag timeout.

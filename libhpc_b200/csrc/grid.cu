@@ -45,6 +45,33 @@ hpcx_status hpcx_grid_linearize(const hpcx_grid_desc *d, const int64_t *idx, int
   return HPCX_OK;
 }
 
+// Halo index map of one face in the reference layout.  With the padded extents e[i] and strides
+// st[i] of compute_stride_and_total, the `width` slices of axis a starting at padded coordinate c0
+// are, for every combination of the slower coordinates, one run of width * st[a] consecutive
+// elements starting at sum_{i<a} idx[i]*st[i] + c0*st[a]; runs are listed with the slower
+// coordinates in row-major order.  Send = interior slices next to the side, recv = its ghost slices.
+hpcx_status hpcx_grid_export_halo_maps(const hpcx_grid_desc *d, int32_t axis, int32_t side, int32_t width,
+                                       int64_t *nruns, int64_t *run_len, int64_t *send_start,
+                                       int64_t *recv_start) {
+  if (!desc_ok(d) || axis < 0 || axis >= d->ndim || (side != 0 && side != 1) || !nruns || !run_len)
+    return HPCX_INVALID_ARG;
+  if (width < 1 || width > d->dim[axis] || width > (side ? d->hi : d->lo)) return HPCX_INVALID_ARG;
+  int64_t st[3], total;
+  hpcx_grid_stride_total(d, st, &total);
+  int64_t runs = 1;
+  for (int i = 0; i < axis; ++i) runs *= d->dim[i] + d->lo + d->hi;
+  *nruns = runs;
+  *run_len = (int64_t)width * st[axis];
+  const int64_t send_c0 = side ? d->lo + d->dim[axis] - width : d->lo;  // padded coordinate of the first slice
+  const int64_t recv_c0 = side ? d->lo + d->dim[axis] : d->lo - width;
+  const int64_t outer = axis > 0 ? st[axis - 1] : 0;  // stride of one step of the combined slower coordinates
+  for (int64_t k = 0; k < runs; ++k) {
+    if (send_start) send_start[k] = k * outer + send_c0 * st[axis];
+    if (recv_start) recv_start[k] = k * outer + recv_c0 * st[axis];
+  }
+  return HPCX_OK;
+}
+
 hpcx_status hpcx_grid_create(hpcx_ctx ctx, const hpcx_grid_desc *d, hpcx_grid *out) {
   if (!ctx || !out) return HPCX_INVALID_ARG;
   *out = nullptr;

@@ -136,6 +136,17 @@ hpcx_status hpcx_init_multi(int32_t ndev, const int32_t *dev_ids, hpcx_multi *ou
     }
     c->nranks = ndev;
     c->rank = i;
+    // one thread launches every device's kernels, and kernels of different devices wait on each
+    // other's flags: no kernel may be loaded lazily in the middle of such a sequence
+    cudaSetDevice(dev);
+    st = preload_stencil_kernels(c);
+    if (st == HPCX_OK) st = preload_dist_kernels(c);
+    if (st == HPCX_OK) st = preload_spmv_kernels(c);
+    if (st != HPCX_OK) {
+      m->last_error = c->last_error;
+      cudaSetDevice(prev);
+      return st;
+    }
   }
   // every device may load from and store to every other one (the fused transport's peer stores)
   for (int i = 0; i < ndev; ++i)

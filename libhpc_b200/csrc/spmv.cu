@@ -20,6 +20,7 @@
 #include "spmv.cuh"
 
 #include <algorithm>
+#include <functional>
 
 using namespace hpcx;
 
@@ -76,7 +77,7 @@ __device__ __forceinline__ T gather_x(const T *__restrict__ x, int c, bool from_
 // matrices: the fused q = A*p, <p, q> of the CG step, cg.cu), reduced in a fixed order.
 // DIST: the one-launch distributed product (SpmvDistArgs, spmv.cuh).
 template <typename T, int TILE, bool DOT, bool DIST>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, 8)  // 32 registers: 8 CTAs per SM, as many as the tiles allow
 spmv_stream_kernel(const int32_t *__restrict__ row_ptr, const int32_t *__restrict__ col,
                    const T *__restrict__ val, const T *__restrict__ x, T *__restrict__ y,
                    const RowBlock *__restrict__ blocks, T *__restrict__ partials,
@@ -475,8 +476,8 @@ void free_csr(hpcx_csr A) {
   cudaFree(A->d_sell_val);
   cudaFree(A->d_x);
   cudaFree(A->d_y);
-  cudaFree(A->d_pipe_cmax);
-  for (cudaEvent_t e : A->pipe_ev) cudaEventDestroy(e);
+  for (cudaEvent_t e : A->pipe.ev) cudaEventDestroy(e);
+  for (cudaEvent_t e : A->pipe_dist.ev) cudaEventDestroy(e);
   cudaFree(A->d_send_idx);
   cudaFree(A->d_sendbuf);
   cudaFree(A->d_xfull);
@@ -498,6 +499,27 @@ hpcx_status upload_vec(hpcx_ctx ctx, const std::vector<V> &h, V **d) {
 }  // namespace
 
 namespace hpcx {
+// see preload_stencil_kernels (stencil.cu): the kernels of the distributed product, all tiles
+template <typename T, int TILE>
+static hpcx_status preload_stream(hpcx_ctx ctx) {
+  using L = StreamSmem<T, TILE>;
+  if (hpcx_status st = ensure_dyn_smem(ctx, (const void *)spmv_stream_kernel<T, TILE, false, true>, L::kBytes)) return st;
+  if (hpcx_status st = ensure_dyn_smem(ctx, (const void *)spmv_stream_kernel<T, TILE, true, true>, L::kBytes)) return st;
+  if (hpcx_status st = ensure_dyn_smem(ctx, (const void *)spmv_stream_kernel<T, TILE, false, false>, L::kBytes)) return st;
+  return ensure_dyn_smem(ctx, (const void *)spmv_stream_kernel<T, TILE, true, false>, L::kBytes);
+}
+hpcx_status preload_spmv_kernels(hpcx_ctx ctx) {
+  cudaFuncAttributes a;
+  HPCX_CUDA(ctx, cudaFuncGetAttributes(&a, (const void *)spmv_longrow_fixup_kernel<float>));
+  HPCX_CUDA(ctx, cudaFuncGetAttributes(&a, (const void *)spmv_longrow_fixup_kernel<double>));
+  if (hpcx_status st = preload_stream<float, 1024>(ctx)) return st;
+  if (hpcx_status st = preload_stream<float, 2048>(ctx)) return st;
+  if (hpcx_status st = preload_stream<float, 4096>(ctx)) return st;
+  if (hpcx_status st = preload_stream<double, 1024>(ctx)) return st;
+  if (hpcx_status st = preload_stream<double, 2048>(ctx)) return st;
+  return preload_stream<double, 4096>(ctx);
+}
+
 // Shared with dist.cu.
 hpcx_status spmv_launch_blocks(hpcx_csr A, const RowBlock *d_blocks, int64_t nblocks, const void *x,
                                void *y, cudaStream_t s, void *dot_part, const SpmvDistArgs *da) {
@@ -518,17 +540,40 @@ hpcx_status spmv_launch_fixup_tables(hpcx_csr A, const int32_t *long_row, const 
 }  // namespace hpcx
 
 namespace {
+hpcx_status pipe_analyse(hpcx_csr A, hpcx::PipePlan &P, const std::vector<RowBlock> &blocks, int64_t nlong, int64_t nx);
+hpcx_status spmv_host_pipelined(hpcx_csr A, hpcx::PipePlan &P, const RowBlock *d_blocks,
+                                const std::vector<RowBlock> &blocks, int64_t nx, void *d_x, const void *x, void *y,
+                                cudaStream_t s, const std::function<hpcx_status()> &dist);
+}
+namespace hpcx {
+// Host-operand pipeline of the distributed product (dist.cu: hpcx_spmv_dist_host).  Returns
+// HPCX_UNSUPPORTED when the matrix does not qualify (long rows, too few interior blocks).
+hpcx_status spmv_dist_host_pipelined(hpcx_csr A, const void *x, void *y, cudaStream_t s,
+                                     const std::function<hpcx_status()> &push_and_boundary) {
+  if (A->pipe_dist.state == 0)
+    if (hpcx_status st = pipe_analyse(A, A->pipe_dist, A->h_blocks_int, A->nlong_dist, A->nloc)) return st;
+  if (A->pipe_dist.state != 1) return HPCX_UNSUPPORTED;
+  if (!A->d_y) HPCX_CUDA(A->ctx, cudaMalloc(&A->d_y, std::max<size_t>((size_t)A->nrows * A->es, 1)));
+  return spmv_host_pipelined(A, A->pipe_dist, A->d_blocks_int, A->h_blocks_int, A->nloc, A->d_xfull, x, y, s,
+                             push_and_boundary);
+}
+}  // namespace hpcx
+namespace {
 
 // Largest column index referenced by each chunk of nonzeros [pbeg[c], pbeg[c+1]).
 __global__ void __launch_bounds__(256)
 chunk_colmax_kernel(const int32_t *__restrict__ col, const int64_t *__restrict__ pbeg, int nchunks,
-                    int32_t *__restrict__ cmax) {
+                    int32_t *__restrict__ cmax, int32_t limit) {
   const int c = blockIdx.y;
   if (c >= nchunks) return;
   int32_t m = -1;
+  // columns >= limit are halo slots of a distributed matrix: they arrive from the neighbours, not
+  // with this rank's x, so they do not hold a chunk back
   for (int64_t i = pbeg[c] + blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < pbeg[c + 1];
-       i += (int64_t)gridDim.x * blockDim.x)
-    m = max(m, col[i]);
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int32_t v = col[i];
+    if (v < limit) m = max(m, v);
+  }
   for (int o = 16; o; o >>= 1) m = max(m, __shfl_xor_sync(0xffffffffu, m, o));
   if ((threadIdx.x & 31) == 0 && m >= 0) atomicMax(cmax + c, m);
 }
@@ -560,76 +605,103 @@ constexpr int kPipeChunks = 32;
 // banded operators (the C2 / C4 stencil matrices) stream: H2D of x, the product and D2H of y overlap
 // and the call takes about one PCIe transfer instead of two.  Matrices whose every chunk reads up
 // to the last column degrade gracefully to copy-then-compute with the D2H still chunked.
-hpcx_status pipe_analyse(hpcx_csr A) {
+// `blocks`: the table the chunks are cut from (all row blocks, or the interior blocks of a
+// distributed matrix); nx: entries of x that travel with the call (ncols, or nloc).
+hpcx_status pipe_analyse(hpcx_csr A, hpcx::PipePlan &P, const std::vector<RowBlock> &blocks, int64_t nlong, int64_t nx) {
   hpcx_ctx ctx = A->ctx;
-  A->pipe_state = -1;
-  const int64_t nb = (int64_t)A->h_blocks.size();
-  if (A->kernel != HPCX_SPMV_STREAM || A->nlong > 0 || nb < 2 * kPipeChunks || A->ncols < kPipeChunks)
-    return HPCX_OK;
+  P.state = -1;
+  const int64_t nb = (int64_t)blocks.size();
+  if (nlong > 0 || nb < 2 * kPipeChunks || nx < kPipeChunks) return HPCX_OK;
   const int K = kPipeChunks;
-  A->pipe_first.resize(K + 1);
+  P.first.resize(K + 1);
   std::vector<int64_t> pbeg(K + 1);
   for (int c = 0; c <= K; ++c) {
-    A->pipe_first[c] = nb * c / K;
-    pbeg[c] = c < K ? A->h_blocks[A->pipe_first[c]].p0 : A->nnz;
+    P.first[c] = nb * c / K;
+    // a chunk's nonzeros: from its first block's to the next chunk's first block's (rows of the other
+    // kind in between are covered too, which only makes the bound safer)
+    pbeg[c] = c < K ? blocks[P.first[c]].p0 : blocks[nb - 1].p1;
   }
   int64_t *d_pbeg = nullptr;
+  int32_t *d_cmax = nullptr;
   HPCX_CUDA(ctx, cudaMalloc((void **)&d_pbeg, (K + 1) * sizeof(int64_t)));
-  cudaError_t e = cudaMalloc((void **)&A->d_pipe_cmax, K * sizeof(int32_t));
-  if (e == cudaSuccess) e = cudaMemset(A->d_pipe_cmax, 0xff, K * sizeof(int32_t));
-  if (e == cudaSuccess) e = cudaMemcpy(d_pbeg, pbeg.data(), (K + 1) * sizeof(int64_t), cudaMemcpyHostToDevice);
+  cudaError_t e = cudaMalloc((void **)&d_cmax, K * sizeof(int32_t));
+  if (e == cudaSuccess) e = cudaMemsetAsync(d_cmax, 0xff, K * sizeof(int32_t), ctx->compute);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(d_pbeg, pbeg.data(), (K + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, ctx->compute);
   if (e == cudaSuccess) {
-    chunk_colmax_kernel<<<dim3(64, K), 256>>>(A->d_col, d_pbeg, K, A->d_pipe_cmax);
-    A->pipe_cmax.resize(K);
-    e = cudaMemcpy(A->pipe_cmax.data(), A->d_pipe_cmax, K * sizeof(int32_t), cudaMemcpyDeviceToHost);
+    chunk_colmax_kernel<<<dim3(64, K), 256, 0, ctx->compute>>>(A->d_col, d_pbeg, K, d_cmax, (int32_t)nx);
+    ctx->launches++;
+    P.cmax.resize(K);
+    e = cudaMemcpyAsync(P.cmax.data(), d_cmax, K * sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->compute);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->compute);
   }
   cudaFree(d_pbeg);
+  cudaFree(d_cmax);
   if (e != cudaSuccess) return fail(ctx, HPCX_CUDA_ERROR, std::string("pipe_analyse: ") + cudaGetErrorString(e));
-  A->pipe_ev.resize(2 * K + 2);
-  for (auto &ev : A->pipe_ev) HPCX_CUDA(ctx, cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
-  A->pipe_state = 1;
+  P.ev.resize(2 * K + 2);
+  for (auto &ev : P.ev) HPCX_CUDA(ctx, cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+  P.state = 1;
   return HPCX_OK;
 }
 
 // y(host) = A x(host): x pieces on the copy-in stream, row chunks on s as their columns land, y
 // chunks on the copy-out stream.  The caller synchronises s afterwards.
-hpcx_status spmv_host_pipelined(hpcx_csr A, const void *x, void *y, cudaStream_t s) {
+// Distributed matrices (dist != nullptr): the LAST piece of x goes up first, then pieces 0, 1, ...;
+// once the last and the first have landed `dist` is called — it queues the launch that pushes this
+// rank's boundary entries to the neighbours and computes the boundary rows — and the interior
+// chunks follow as in the single-GPU case, so the exchange overlaps the copies too.
+hpcx_status spmv_host_pipelined(hpcx_csr A, hpcx::PipePlan &P, const RowBlock *d_blocks,
+                                const std::vector<RowBlock> &blocks, int64_t nx, void *d_x, const void *x, void *y,
+                                cudaStream_t s, const std::function<hpcx_status()> &dist) {
   HPCX_RANGE("spmv: host operands, chunks pipelined against PCIe");
   hpcx_ctx ctx = A->ctx;
   const int K = kPipeChunks;
   const size_t es = (size_t)A->es;
-  cudaEvent_t *ex = A->pipe_ev.data(), *ey = ex + K, entry = ex[2 * K], done = ex[2 * K + 1];
-  auto piece = [&](int j) { return (int64_t)A->ncols * j / K; };  // first column of x piece j
+  cudaEvent_t *ex = P.ev.data(), *ey = ex + K, entry = ex[2 * K], done = ex[2 * K + 1];
+  auto piece = [&](int j) { return nx * j / K; };  // first entry of x piece j
   HPCX_CUDA(ctx, cudaEventRecord(entry, s));
   HPCX_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_in, entry, 0));
   HPCX_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_out, entry, 0));
-  for (int j = 0; j < K; ++j) {
+  auto copy_piece = [&](int j) -> hpcx_status {
     const int64_t a = piece(j), b = piece(j + 1);
-    HPCX_CUDA(ctx, cudaMemcpyAsync((char *)A->d_x + a * es, (const char *)x + a * es, (size_t)(b - a) * es,
+    HPCX_CUDA(ctx, cudaMemcpyAsync((char *)d_x + a * es, (const char *)x + a * es, (size_t)(b - a) * es,
                                    cudaMemcpyHostToDevice, ctx->copy_in));
     HPCX_CUDA(ctx, cudaEventRecord(ex[j], ctx->copy_in));
-  }
+    return HPCX_OK;
+  };
+  const int last_copied = dist ? K - 2 : K - 1;  // the piece that lands last
+  if (dist)
+    if (hpcx_status st = copy_piece(K - 1)) return st;
+  for (int j = 0; j <= last_copied; ++j)
+    if (hpcx_status st = copy_piece(j)) return st;
   int waited = -1;
+  if (dist) {
+    HPCX_CUDA(ctx, cudaStreamWaitEvent(s, ex[0], 0));  // pieces K-1 and 0: both ends of the owned block
+    waited = 0;
+    if (hpcx_status st = dist()) return st;
+  }
   for (int c = 0; c < K; ++c) {
     int need = waited < 0 ? 0 : waited;
-    while (need + 1 < K && piece(need + 1) <= A->pipe_cmax[c]) ++need;
+    while (need + 1 < K && piece(need + 1) <= P.cmax[c]) ++need;
+    if (need > last_copied) need = last_copied;  // piece K-1 went first: everything has landed with the last one
     if (need > waited) {
       HPCX_CUDA(ctx, cudaStreamWaitEvent(s, ex[need], 0));
       waited = need;
     }
-    const int64_t b0 = A->pipe_first[c], b1 = A->pipe_first[c + 1];
-    hpcx_status st = hpcx::spmv_launch_blocks(A, A->d_blocks + b0, b1 - b0, A->d_x, A->d_y, s, nullptr, nullptr);
+    const int64_t b0 = P.first[c], b1 = P.first[c + 1];
+    hpcx_status st = hpcx::spmv_launch_blocks(A, d_blocks + b0, b1 - b0, d_x, A->d_y, s, nullptr, nullptr);
     if (st != HPCX_OK) return st;
     HPCX_CUDA(ctx, cudaEventRecord(ey[c], s));
     HPCX_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_out, ey[c], 0));
-    const int64_t r0 = A->h_blocks[b0].row0;
-    const int64_t r1 = b1 < (int64_t)A->h_blocks.size() ? A->h_blocks[b1].row0 : A->nrows;
+    // rows of this chunk: up to the next chunk's first row (rows of the other kind in between — the
+    // boundary rows of a distributed matrix, computed by dist() earlier on s — travel with it)
+    const int64_t r0 = c == 0 ? 0 : blocks[b0].row0;
+    const int64_t r1 = c + 1 < K ? blocks[b1].row0 : A->nrows;
     HPCX_CUDA(ctx, cudaMemcpyAsync((char *)y + r0 * es, (const char *)A->d_y + r0 * es, (size_t)(r1 - r0) * es,
                                    cudaMemcpyDeviceToHost, ctx->copy_out));
   }
   HPCX_CUDA(ctx, cudaEventRecord(done, ctx->copy_out));
   HPCX_CUDA(ctx, cudaStreamWaitEvent(s, done, 0));
-  if (waited < K - 1) HPCX_CUDA(ctx, cudaStreamWaitEvent(s, ex[K - 1], 0));  // x fully landed before s goes on
+  if (waited < last_copied) HPCX_CUDA(ctx, cudaStreamWaitEvent(s, ex[last_copied], 0));  // x fully landed before s goes on
   return HPCX_OK;
 }
 
@@ -802,14 +874,14 @@ hpcx_status hpcx_spmv(hpcx_csr A, const void *x, int32_t x_mem, void *y, int32_t
   const void *dx = x;
   void *dy = y;
   if (x_mem == HPCX_MEM_HOST && y_mem == HPCX_MEM_HOST && !A->dot_part) {
-    if (A->pipe_state == 0) {
-      hpcx_status st = pipe_analyse(A);
-      if (st != HPCX_OK) return st;
+    if (A->pipe.state == 0) {
+      if (A->kernel != HPCX_SPMV_STREAM) A->pipe.state = -1;
+      else if (hpcx_status st = pipe_analyse(A, A->pipe, A->h_blocks, A->nlong, A->ncols)) return st;
     }
-    if (A->pipe_state == 1) {
+    if (A->pipe.state == 1) {
       if (!A->d_x) HPCX_CUDA(ctx, cudaMalloc(&A->d_x, std::max<size_t>((size_t)A->ncols * A->es, 1)));
       if (!A->d_y) HPCX_CUDA(ctx, cudaMalloc(&A->d_y, std::max<size_t>((size_t)A->nrows * A->es, 1)));
-      hpcx_status st = spmv_host_pipelined(A, x, y, s);
+      hpcx_status st = spmv_host_pipelined(A, A->pipe, A->d_blocks, A->h_blocks, A->ncols, A->d_x, x, y, s, nullptr);
       if (st != HPCX_OK) return st;
       HPCX_CUDA(ctx, cudaStreamSynchronize(s));
       return HPCX_OK;

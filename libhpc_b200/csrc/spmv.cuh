@@ -39,6 +39,14 @@ struct SpmvDistArgs {
   PeerWait pw;
 };
 
+// Chunking of a host-operand product (spmv.cu: pipe_analyse / spmv_host_pipelined).
+struct PipePlan {
+  int state = 0;                 // 0 = not analysed yet, 1 = usable, -1 = not usable
+  std::vector<int64_t> first;    // first row block of each chunk (+ end)
+  std::vector<int32_t> cmax;     // largest travelling column index each chunk reads
+  std::vector<cudaEvent_t> ev;   // [0, K) x pieces landed, [K, 2K) chunk computed, 2K entry, 2K+1 done
+};
+
 // What one rank sees of another for the fused x-halo transport (dist.cu: csr_peer_wire).
 struct CsrPeerView {
   char *xfull = nullptr;        // the peer's [owned | halo] x buffer, addressable from this device
@@ -109,12 +117,9 @@ struct hpcx_csr_s {
   hpcx::HubTables hub;
   // staging for host operands
   void *d_x = nullptr, *d_y = nullptr;
-  // host-x / host-y products: row chunks pipelined against the PCIe copies (spmv.cu: spmv_host_pipelined)
-  int pipe_state = 0;                 // 0 = not analysed yet, 1 = usable, -1 = not usable
-  std::vector<int64_t> pipe_first;    // first row block of each chunk (+ end)
-  std::vector<int32_t> pipe_cmax;     // largest column index referenced by each chunk
-  std::vector<cudaEvent_t> pipe_ev;   // [0, K) x pieces landed, [K, 2K) chunk computed, 2K entry, 2K+1 done
-  int32_t *d_pipe_cmax = nullptr;
+  // host-x / host-y products: row chunks pipelined against the PCIe copies (spmv.cu:
+  // spmv_host_pipelined); pipe_dist is the same over the interior blocks of a distributed matrix
+  hpcx::PipePlan pipe, pipe_dist;
   // when set (by the CG solver, cg.cu) the STREAM launches also emit per-block <x, y> partials
   void *dot_part = nullptr;
   // distributed (set by hpcx_csr_set_halo)

@@ -424,59 +424,70 @@ hpcx_status check_same_shape(hpcx_grid a, hpcx_grid b) {
   return HPCX_OK;
 }
 
+// The box launchers take geometries, not handles: a range of rows [y0, y1) of a grid is the same
+// grid with its row origin shifted (the distributed sweep runs interior rows and boundary strips
+// as separate launches, dist.cu).
+struct BoxView {
+  GridGeom gi, go;
+  const void *in;
+  void *out;
+  hpcx_ctx ctx;
+};
+BoxView box_view(hpcx_grid in, hpcx_grid out, int64_t y0, int64_t y1) {
+  BoxView v{geom_of(in), geom_of(out), in->dev, out->dev, in->ctx};
+  v.gi.glo1 += y0;
+  v.go.glo1 += y0;
+  v.gi.n1 = v.go.n1 = y1 - y0;
+  return v;
+}
+
 template <typename T>
-hpcx_status launch_box_direct(hpcx_grid in, hpcx_grid out, int axis, int radius, cudaStream_t s) {
+hpcx_status launch_box_direct(const BoxView &v, int axis, int radius, cudaStream_t s) {
   dim3 block(64, 4);
-  dim3 grid((unsigned)((in->n[2] + 63) / 64), (unsigned)((in->n[1] + 3) / 4));
-  box_direct_kernel<T><<<grid, block, 0, s>>>((const T *)in->dev, (T *)out->dev, geom_of(in),
-                                              geom_of(out), axis, radius);
-  return after_launch(in->ctx, "box_direct_kernel");
+  dim3 grid((unsigned)((v.gi.n2 + 63) / 64), (unsigned)((v.gi.n1 + 3) / 4));
+  box_direct_kernel<T><<<grid, block, 0, s>>>((const T *)v.in, (T *)v.out, v.gi, v.go, axis, radius);
+  return after_launch(v.ctx, "box_direct_kernel");
 }
 
 // Register-tiled variants exist for the radii a 16-byte vector divides (the reference's
 // nblur = 8 among them); everything else takes the direct kernel.
 template <typename T, int R, int ROWS>
-hpcx_status launch_box_fast_r(hpcx_grid in, hpcx_grid out, int axis, cudaStream_t s) {
+hpcx_status launch_box_fast_r(const BoxView &v, int axis, cudaStream_t s) {
   constexpr int V = 16 / (int)sizeof(T);
   if (axis == 2) {
-    dim3 grid((unsigned)((in->n[2] / V + 255) / 256), (unsigned)in->n[1]);
-    box_x_vec_kernel<T, R><<<grid, 256, 0, s>>>((const T *)in->dev, (T *)out->dev, geom_of(in),
-                                                 geom_of(out));
-    return after_launch(in->ctx, "box_x_vec_kernel");
+    dim3 grid((unsigned)((v.gi.n2 / V + 255) / 256), (unsigned)v.gi.n1);
+    box_x_vec_kernel<T, R><<<grid, 256, 0, s>>>((const T *)v.in, (T *)v.out, v.gi, v.go);
+    return after_launch(v.ctx, "box_x_vec_kernel");
   }
   if constexpr (sizeof(T) == 4) {
-    if (in->n[2] % 2 == 0) {  // pitches and x offsets are multiples of 8 floats: 8-byte aligned pairs
-      dim3 grid2((unsigned)((in->n[2] / 2 + 127) / 128), (unsigned)((in->n[1] + ROWS - 1) / ROWS));
-      box_y_reg2_kernel<R, ROWS><<<grid2, 128, 0, s>>>((const float *)in->dev, (float *)out->dev,
-                                                       geom_of(in), geom_of(out));
-      return after_launch(in->ctx, "box_y_reg2_kernel");
+    if (v.gi.n2 % 2 == 0) {  // pitches and x offsets are multiples of 8 floats: 8-byte aligned pairs
+      dim3 grid2((unsigned)((v.gi.n2 / 2 + 127) / 128), (unsigned)((v.gi.n1 + ROWS - 1) / ROWS));
+      box_y_reg2_kernel<R, ROWS><<<grid2, 128, 0, s>>>((const float *)v.in, (float *)v.out, v.gi, v.go);
+      return after_launch(v.ctx, "box_y_reg2_kernel");
     }
   }
-  dim3 grid((unsigned)((in->n[2] + 127) / 128), (unsigned)((in->n[1] + ROWS - 1) / ROWS));
-  box_y_reg_kernel<T, R, ROWS><<<grid, 128, 0, s>>>((const T *)in->dev, (T *)out->dev, geom_of(in),
-                                                     geom_of(out));
-  return after_launch(in->ctx, "box_y_reg_kernel");
+  dim3 grid((unsigned)((v.gi.n2 + 127) / 128), (unsigned)((v.gi.n1 + ROWS - 1) / ROWS));
+  box_y_reg_kernel<T, R, ROWS><<<grid, 128, 0, s>>>((const T *)v.in, (T *)v.out, v.gi, v.go);
+  return after_launch(v.ctx, "box_y_reg_kernel");
 }
 
 template <typename T>
-hpcx_status launch_box(hpcx_grid in, hpcx_grid out, int axis, int radius, int variant, int rows,
-                       cudaStream_t s) {
+hpcx_status launch_box(const BoxView &v, int axis, int radius, int variant, int rows, cudaStream_t s) {
+  if (v.gi.n1 <= 0) return HPCX_OK;
   constexpr int V = 16 / (int)sizeof(T);
-  const bool fast_ok = variant != HPCX_VARIANT_DIRECT && in->n[1] <= 65535 * 32 &&
-                       (axis != 2 || (in->n[2] % V == 0 && in->n[1] <= 65535));
+  const bool fast_ok = variant != HPCX_VARIANT_DIRECT && v.gi.n1 <= 65535 * 32 &&
+                       (axis != 2 || (v.gi.n2 % V == 0 && v.gi.n1 <= 65535));
   if (fast_ok) {
     switch (radius) {
       case 8:
-        return rows == 16 ? launch_box_fast_r<T, 8, 16>(in, out, axis, s)
-                          : launch_box_fast_r<T, 8, 32>(in, out, axis, s);
+        return rows == 16 ? launch_box_fast_r<T, 8, 16>(v, axis, s) : launch_box_fast_r<T, 8, 32>(v, axis, s);
       case 4:
-        return rows == 16 ? launch_box_fast_r<T, 4, 16>(in, out, axis, s)
-                          : launch_box_fast_r<T, 4, 32>(in, out, axis, s);
+        return rows == 16 ? launch_box_fast_r<T, 4, 16>(v, axis, s) : launch_box_fast_r<T, 4, 32>(v, axis, s);
       default: break;
     }
   }
-  if (in->n[1] > 65535 * 4) return fail(in->ctx, HPCX_UNSUPPORTED, "grid too tall for the box sweep");
-  return launch_box_direct<T>(in, out, axis, radius, s);
+  if (v.gi.n1 > 65535 * 4) return fail(v.ctx, HPCX_UNSUPPORTED, "grid too tall for the box sweep");
+  return launch_box_direct<T>(v, axis, radius, s);
 }
 
 int auto_zsplit(hpcx_ctx ctx, int64_t tiles_xy, int64_t nz, int ctas_per_sm) {
@@ -914,6 +925,32 @@ hpcx_status jacobi7_launch(hpcx_grid_s *g, void *src, void *dst, int variant, in
   return launch_jacobi_tma(g, src, dst, zsplit, zbeg, zend, peer, s);
 }
 
+// Box sweep of the rows [y0, y1) of a 2-D grid pair (shared with dist.cu).
+hpcx_status box_launch_rows(hpcx_grid_s *in, hpcx_grid_s *out, const hpcx_stencil_desc *st, int64_t y0, int64_t y1,
+                            cudaStream_t s) {
+  if (y1 <= y0) return HPCX_OK;
+  const int axis = st->kind == HPCX_STENCIL_BOX_X ? 2 : 1;
+  const BoxView v = box_view(in, out, y0, y1);
+  return in->desc.dtype == HPCX_F64 ? launch_box<double>(v, axis, st->radius, st->variant, st->zsplit, s)
+                                    : launch_box<float>(v, axis, st->radius, st->variant, st->zsplit, s);
+}
+
+// Forces the sweep kernels onto the current device now.  CUDA loads kernels lazily, at their
+// first launch, and that load synchronises with kernels already running on the device; in a
+// single-process multi-GPU run (multi.cu) a kernel of device 0 may be spinning on a flag that only
+// a not-yet-launched kernel of device 1 will set — if the ONE host thread is then stuck loading a
+// new kernel for device 0, nothing ever launches device 1's work.  Loading everything up front
+// removes the load from the launch path.
+hpcx_status preload_stencil_kernels(hpcx_ctx ctx) {
+  cudaFuncAttributes a;
+  HPCX_CUDA(ctx, cudaFuncGetAttributes(&a, (const void *)jacobi7_ring_kernel<kJacobiStages>));
+  HPCX_CUDA(ctx, cudaFuncGetAttributes(&a, (const void *)jacobi7_tb2_kernel<8>));
+  HPCX_CUDA(ctx, cudaFuncGetAttributes(&a, (const void *)jacobi7_direct_kernel<float>));
+  HPCX_CUDA(ctx, cudaFuncGetAttributes(&a, (const void *)jacobi7_direct_kernel<double>));
+  if (hpcx_status st = ensure_dyn_smem(ctx, (const void *)jacobi7_ring_kernel<kJacobiStages>, JacobiCfg<kJacobiStages>::kSmemBytes)) return st;
+  return ensure_dyn_smem(ctx, (const void *)jacobi7_tb2_kernel<8>, JacobiTBCfg<8>::kSmemBytes);
+}
+
 bool jacobi7_tb2_supported(hpcx_grid_s *g) {
   return g->desc.dtype == HPCX_F32 && g->ctx->encode_tiled && g->n[2] < (1 << 30);
 }
@@ -947,8 +984,7 @@ extern "C" hpcx_status hpcx_stencil_sweep(hpcx_grid in, hpcx_grid out, const hpc
     HPCX_REQUIRE(ctx, st->radius >= 0 && st->radius <= in->desc.lo && st->radius <= in->desc.hi,
                  "radius exceeds the ghost width of the input grid");
     const int axis = st->kind == HPCX_STENCIL_BOX_X ? 2 : 1;
-    rc = in->desc.dtype == HPCX_F64 ? launch_box<double>(in, out, axis, st->radius, st->variant, st->zsplit, s)
-                                    : launch_box<float>(in, out, axis, st->radius, st->variant, st->zsplit, s);
+    rc = hpcx::box_launch_rows(in, out, st, 0, in->n[1], s);
   } else if (st->kind == HPCX_STENCIL_JACOBI7) {
     if (in->desc.ndim != 3) return fail(ctx, HPCX_UNSUPPORTED, "JACOBI7 takes 3-D grids");
     HPCX_REQUIRE(ctx, in->desc.lo >= 1 && in->desc.hi >= 1 && in->desc.lo == out->desc.lo &&

@@ -40,12 +40,13 @@ def barrier(ctx: Context) -> None:
 
 
 class HaloPlan:
-    """Distributed JACOBI7 over z-slabs (hpcx_stencil_dist_*)."""
+    """Distributed sweeps over slabs of axis 0 (hpcx_stencil_dist_*): JACOBI7 over z-slabs, the
+    reference's box sweeps over y-slabs (radius = the reference's nblur)."""
 
     def __init__(self, ctx: Context, gin: DeviceGrid, gout: DeviceGrid, kind: int, variant: int = 0,
-                 zsplit: int = 0, transport: int = 0):
+                 zsplit: int = 0, transport: int = 0, radius: int = 0):
         self.ctx = ctx
-        d = stencil_desc(kind, 0, variant, zsplit)
+        d = stencil_desc(kind, radius, variant, zsplit)
         h = C.c_void_p()
         ctx.check(ctx.lib.hpcx_stencil_dist_plan(ctx.h, gin.h, gout.h, C.byref(d), transport,
                                                  C.byref(h)))

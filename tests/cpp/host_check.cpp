@@ -4,6 +4,9 @@
 //                               hpc::HPCHighDimensionFlatArray for tests/test_cpp_host.py to compare
 //                               with the reference header (oracle/_ref) and the golden file
 //   host_check csr              prints FNV-1a digests of the CsrMatrix builders' arrays
+//   host_check multi            one process, one thread, every visible GPU (hpcx::MultiContext): the
+//                               reference's sweep loop nests and a CPU SpMV loop against the multi-device
+//                               overloads of hpc::stencil_sweep / sparse::spmv
 //   host_check gpu              runs the sweeps and the product on cuda:0 through the C++ entry
 //                               points and compares with reference-style loop nests written here
 //
@@ -19,6 +22,7 @@
 #include <hpcx/CsrMatrix.hpp>
 #include <hpcx/Distributed.hpp>
 #include <hpcx/HPCHighDimensionFlatArray.hpp>
+#include <hpcx/Multi.hpp>
 #include <hpcx/Stencil.hpp>
 
 static uint64_t fnv1a(const void *p, size_t n, uint64_t h = 1469598103934665603ull) {
@@ -379,12 +383,89 @@ static int run_gpu() {
   return bad;
 }
 
+// One process, one host thread, every visible GPU.
+static int run_multi() {
+  int bad = 0;
+  hpcx::MultiContext gpus;
+  std::printf("multi devices %d\n", gpus.size());
+  uint64_t seed = 11;
+  {  // BM_x_blur / BM_y_blur loop nests (test_hpc_benchmark.cpp:354-368, 444-457) over y-slabs
+    constexpr int nblur = 8;
+    const int ny = 64 * gpus.size() + 10, nx = 256;
+    hpc::HPCHighDimensionFlatArray<2, float, nblur> a(ny, nx);
+    hpc::HPCHighDimensionFlatArray<2, float> b(ny, nx), want(ny, nx);
+    for (std::size_t i = 0; i < a.size(); ++i) a.data()[i] = frand(seed);
+    for (int axis = 0; axis < 2; ++axis) {
+#pragma omp parallel for collapse(2)
+      for (int y = 0; y < ny; ++y)
+        for (int x = 0; x < nx; ++x) {
+          float res = 0.0f;
+          for (int t = -nblur; t <= nblur; ++t) res += axis == 1 ? a(y, x + t) : a(y + t, x);
+          want(y, x) = res;
+        }
+      hpc::stencil_sweep(gpus, a, b, hpc::Box1D{axis, nblur});
+      const int same = std::memcmp(b.data(), want.data(), b.size() * sizeof(float)) == 0;
+      std::printf("multi box axis %d bit_exact %d\n", axis, same);
+      bad += !same;
+    }
+  }
+  {  // 7-point Jacobi over z-slabs, ghost planes traded by peer stores inside the sweep kernel
+    const int nz = 12 * gpus.size() + 5, ny = 18, nx = 130, steps = 6;
+    hpc::HPCHighDimensionFlatArray<3, float, 1> u(nz, ny, nx), v(nz, ny, nx), w0(nz, ny, nx), w1(nz, ny, nx);
+    for (std::size_t i = 0; i < u.size(); ++i) u.data()[i] = v.data()[i] = w0.data()[i] = w1.data()[i] = frand(seed);
+    auto sweep = [&](auto &src, auto &dst) {
+#pragma omp parallel for collapse(2)
+      for (int z = 0; z < nz; ++z)
+        for (int y = 0; y < ny; ++y)
+          for (int x = 0; x < nx; ++x) {
+            float s = src(z - 1, y, x) + src(z, y - 1, x);
+            s = s + src(z, y, x - 1);
+            s = s + src(z, y, x + 1);
+            s = s + src(z, y + 1, x);
+            s = s + src(z + 1, y, x);
+            dst(z, y, x) = s * (1.0f / 6.0f);
+          }
+    };
+    for (int t = 0; t < steps; t += 2) {
+      sweep(w0, w1);
+      sweep(w1, w0);
+    }  // newest iterate (steps) in w0, the one before it in w1
+    hpc::stencil_sweep(gpus, u, v, hpc::Jacobi7{steps});
+    const int same = std::memcmp(v.data(), w0.data(), v.size() * sizeof(float)) == 0 &&
+                     std::memcmp(u.data(), w1.data(), u.size() * sizeof(float)) == 0;
+    std::printf("multi jacobi7 bit_exact %d\n", same);
+    bad += !same;
+  }
+  {  // SpMV: 27-point operator, row blocks over the devices, x halo by peer stores
+    auto A = sparse::CsrMatrix<double>::op27(14);
+    std::vector<double> x(A.ncols()), y, want(A.nrows());
+    for (auto &v : x) v = frand(seed);
+    for (std::size_t i = 0; i < A.nrows(); ++i) {
+      double s = 0.0;
+      for (auto p = A.row_ptr()[i]; p < A.row_ptr()[i + 1]; ++p) {
+        const double prod = A.values()[p] * x[A.col_idx()[p]];
+        s = s + prod;
+      }
+      want[i] = s;
+    }
+    sparse::MultiDeviceCsr<double> dA(gpus, A);
+    for (int rep = 0; rep < 3; ++rep) sparse::spmv(dA, x, y);
+    const int same = y.size() == want.size() && std::memcmp(y.data(), want.data(), y.size() * 8) == 0;
+    const auto b = dA.bounds();
+    std::printf("multi spmv bit_exact %d blocks %zu last %lld\n", same, b.size() - 1, (long long)b.back());
+    bad += !same;
+  }
+  std::printf(bad ? "CPP MULTI FAILED %d\n" : "CPP MULTI OK\n", bad);
+  return bad ? 3 : 0;
+}
+
 int main(int argc, char **argv) {
   const std::string mode = argc > 1 ? argv[1] : "index";
   try {
     if (mode == "index") return run_index();
     if (mode == "csr") return run_csr();
     if (mode == "gpu") return run_gpu();
+    if (mode == "multi") return run_multi();
   } catch (const std::exception &e) {
     std::printf("exception %s\n", e.what());
     return 2;

@@ -120,6 +120,35 @@ def main():
         ga.destroy()
         gb.destroy()
 
+    # ---- R0 across ranks: the reference's 17-point sweeps over y-slabs; BOX_Y trades 8 ghost rows
+    for (ny, nx), kind, axis in (((40 * world + 7, 256), hp.STENCIL_BOX_Y, 0), ((40 * world + 7, 256), hp.STENCIL_BOX_X, 1),
+                                 ((8 * world, 130), hp.STENCIL_BOX_Y, 0)):
+        a_flat = oracle.fill((ny + 16) * (nx + 16), 3, np.float32)
+        want = oracle.box_sweep(a_flat, ny, nx, 8, 8, 0, 0, axis, 8).reshape(ny, nx)
+        if oracle.ref() is not None and nx % 64 == 0:
+            assert bits_equal(want.ravel(), oracle.ref_blur("y_sse_ipl" if axis == 0 else "x_sse", a_flat, ny, nx))
+        b = np.array([ny * r // world for r in range(world + 1)])
+        y0, y1 = int(b[rank]), int(b[rank + 1])
+        slab = np.ascontiguousarray(a_flat.reshape(ny + 16, nx + 16)[y0:y1 + 16]).copy()
+        if world > 1:
+            # the ghost rows shared with a neighbour must come through the exchange: poison them here
+            if rank > 0:
+                slab[:8] = np.nan
+            if rank < world - 1:
+                slab[-8:] = np.nan
+        ga = hp.DeviceGrid(ctx, (y1 - y0, nx), np.float32, 8)
+        gb = hp.DeviceGrid(ctx, (y1 - y0, nx), np.float32, 0)
+        ga.upload(slab.ravel())
+        plan = hd.HaloPlan(ctx, ga, gb, kind, transport=0, radius=8)
+        plan.sweep(1)
+        out = gb.download().reshape(y1 - y0, nx)
+        if kind == hp.STENCIL_BOX_X and world > 1:
+            pass  # BOX_X reads no ghost rows: nothing to check about them
+        assert bits_equal(np.ascontiguousarray(out), np.ascontiguousarray(want[y0:y1])), (rank, "box", kind, ny)
+        plan.destroy()
+        ga.destroy()
+        gb.destroy()
+
     # ---- SpMV: banded (C4 shape) by rows, power-law by nnz
     for name, (rp, col, val), mode in (("op27", synth.op27(16, index_dtype=np.int64), 0),
                                        ("rmat", synth.rmat(13, 16, 24, index_dtype=np.int64), 1)):

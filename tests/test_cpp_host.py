@@ -125,3 +125,12 @@ def test_cpp_entry_points_on_gpu(binary):
     assert "from_coo product bit_exact 1" in out and "converged 1" in out
     assert "grid_bridge ok 1" in out
     assert "distributed_face ok 1" in out
+
+
+@pytest.mark.gpu
+def test_cpp_single_process_multi_gpu(binary):
+    """hpcx::MultiContext from C++: one process, one thread, every visible GPU (SURVEY.md §8b)."""
+    rc, out, err = _run(binary, "multi", 600)
+    assert rc == 0 and "CPP MULTI OK" in out, out + err
+    assert "multi box axis 0 bit_exact 1" in out and "multi box axis 1 bit_exact 1" in out
+    assert "multi jacobi7 bit_exact 1" in out and "multi spmv bit_exact 1" in out

@@ -182,3 +182,30 @@ def test_op27_slab_local_builder_equals_localize_of_global(P):
         assert np.array_equal(got["values"], val[rp[bounds[r]]:rp[bounds[r + 1]]])
         recv, send = synth.slab_counts(got, P, r, n * n)
         assert np.array_equal(recv, want["recv_counts"]) and np.array_equal(send, want["send_counts"])
+
+
+def test_halo_index_maps_match_reference_index_math():
+    """hpcx_grid_export_halo_maps against a brute-force enumeration with the reference's index math
+    (oracle.grid_linearize, pinned to the reference header): every cell of the `width` interior
+    slices next to a face (send) and of the ghost slices behind it (recv), in row-major order."""
+    import itertools
+    for dims, lo, hi in (((5, 7), 2, 2), ((4, 3, 6), 1, 1), ((6, 5, 4), 1, 3), ((3, 9), 8, 8), ((9,), 2, 2)):
+        for axis in range(len(dims)):
+            for side in (0, 1):
+                for width in range(1, min((hi if side else lo), dims[axis]) + 1):
+                    run_len, send, recv = hp.grid_halo_maps(dims, lo, hi, axis, side, width)
+                    slower = [range(-lo, dims[i] + hi) for i in range(axis)]
+                    faster = [range(-lo, dims[i] + hi) for i in range(axis + 1, len(dims))]
+                    s0 = dims[axis] - width if side else 0
+                    r0 = dims[axis] if side else -width
+                    want_s, want_r = [], []
+                    for outer in itertools.product(*slower):
+                        for k in range(width):
+                            for inner in itertools.product(*faster):
+                                want_s.append(oracle.grid_linearize(dims, lo, hi, list(outer) + [s0 + k] + list(inner), True))
+                                want_r.append(oracle.grid_linearize(dims, lo, hi, list(outer) + [r0 + k] + list(inner), True))
+                    got_s = np.concatenate([np.arange(a, a + run_len) for a in send])
+                    got_r = np.concatenate([np.arange(a, a + run_len) for a in recv])
+                    assert got_s.tolist() == want_s and got_r.tolist() == want_r, (dims, lo, hi, axis, side, width)
+    with pytest.raises(hp.HpcxError):
+        hp.grid_halo_maps((5, 7), 1, 1, 0, 0, 2)  # wider than the ghost region
