@@ -411,10 +411,8 @@ def run_ours(args, rank: int, world: int, local: int):
         if world == 1:
             D.spmv(x_pin.numpy(), y_pin.numpy(), stream)  # hpcx_spmv(HOST, HOST): H2D + kernel + D2H + sync
         else:
-            xd.copy_(x_pin, non_blocking=True)
-            D.spmv_dist(xd, yd, stream)
-            y_pin.copy_(yd, non_blocking=True)
-            stream.synchronize()
+            # hpcx_spmv_dist_host: pinned x in, pinned y out; copies, exchange and product overlap
+            D.spmv_dist_host(x_pin.numpy(), y_pin.numpy(), stream)
 
     with torch.cuda.stream(stream):
         for _ in range(min(args.warmup, 3)):
@@ -424,6 +422,34 @@ def run_ours(args, rank: int, world: int, local: int):
     dt_e2e = max_over_ranks(dt_e2e)
     e2e_value = nbytes_rank * world * k_e2e / dt_e2e / 1e9
     checksum = float(np.abs(y_pin.numpy()).sum())
+    # the bound of that leg: the same bytes over PCIe in both directions at once with every rank
+    # copying, and nothing else (host memory / root-complex bandwidth shared by the ranks)
+    s_in, s_out = torch.cuda.Stream(), torch.cuda.Stream()
+
+    def copies_only():
+        with torch.cuda.stream(s_in):
+            xd.copy_(x_pin, non_blocking=True)
+        with torch.cuda.stream(s_out):
+            y_pin.copy_(yd, non_blocking=True)
+        s_in.synchronize()
+        s_out.synchronize()
+    copies_only()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(5):
+        copies_only()
+    torch.cuda.synchronize()
+    pcie_ms = max_over_ranks((time.perf_counter() - t0) / 5) * 1e3
+    if world > 1:
+        # the distributed e2e result must be the device-resident one
+        y_dev = torch.empty_like(yd)
+        ctx.memcpy((xfull, hp.MEM_DEVICE), xd, nloc * 8)
+        barrier()
+        D.spmv_dist(x_arg, y_dev, stream)
+        stream.synchronize()
+        if not torch.equal(y_dev.cpu(), y_pin):
+            raise SystemExit(f"[rank {rank}] bench.py: hpcx_spmv_dist_host differs from the device-resident product")
+        barrier()
 
     extra, stencil = stencil_extra(args, ctx, torch, stream, world, rank, barrier, max_over_ranks, hp, hd, synth)
     extra["cg_iteration_c2_fp64"] = cg_extra(args, ctx, torch, stream, world, barrier, max_over_ranks, hp, D,
@@ -476,8 +502,11 @@ def run_ours(args, rank: int, world: int, local: int):
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": nloc * 8 * world,
                     "d2h_bytes_per_step": nloc * 8 * world, "steps": k_e2e,
                     "ms_per_step": dt_e2e / k_e2e * 1e3,
+                    "pcie_copies_only_ms": pcie_ms,
+                    "note": "pcie_copies_only_ms = the same H2D + D2H with every rank copying at once and no product: "
+                            "the bound of this leg",
                     "call": "hpcx_spmv(A, x HOST, y HOST)" if world == 1 else
-                            "pinned H2D + hpcx_spmv_dist + D2H per rank"},
+                            "hpcx_spmv_dist_host(A, x HOST, y HOST) per rank"},
             "gpu_launches": launches, "clocks": clocks, "checksum": checksum, "setup_ms": setup_ms,
             "spmv_check": spmv_check, "dist_parity": dist_parity if world > 1 else "n/a (one GPU)",
             "extra": extra,

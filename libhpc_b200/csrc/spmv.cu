@@ -66,55 +66,28 @@ struct StreamSmem {
 constexpr int kSyncData = 0, kSyncAck = 64, kSyncCount = 128, kSyncBnd = 129;  // words of the sync block (dist.cu)
 
 // x gather: the read-only path for owned entries; boundary row blocks of the one-launch distributed
-// product read halo slots a peer GPU wrote DURING this kernel, so they go to L2 (ld.global.cg) —
-// an L1 line fetched earlier by an interior CTA of the same SM could be stale.
-template <typename T>
-__device__ __forceinline__ T gather_x(const T *__restrict__ x, int c, bool from_l2) {
-  return from_l2 ? __ldcg(x + c) : __ldg(x + c);
+// product (L2X) read halo slots a peer GPU wrote DURING this kernel, so they go to L2
+// (ld.global.cg) — an L1 line fetched earlier by an interior CTA of the same SM could be stale.
+template <typename T, bool L2X>
+__device__ __forceinline__ T gather_x(const T *__restrict__ x, int c) {
+  if constexpr (L2X) return __ldcg(x + c);
+  else return __ldg(x + c);
 }
 
+// One row block: stage the tile, gather, reduce the rows.
 // DOT: additionally emits dot_part[block] = sum over the block's rows of y_i * x_i (square
 // matrices: the fused q = A*p, <p, q> of the CG step, cg.cu), reduced in a fixed order.
-// DIST: the one-launch distributed product (SpmvDistArgs, spmv.cuh).
-template <typename T, int TILE, bool DOT, bool DIST>
-__global__ void __launch_bounds__(kThreads, 8)  // 32 registers: 8 CTAs per SM, as many as the tiles allow
-spmv_stream_kernel(const int32_t *__restrict__ row_ptr, const int32_t *__restrict__ col,
-                   const T *__restrict__ val, const T *__restrict__ x, T *__restrict__ y,
-                   const RowBlock *__restrict__ blocks, T *__restrict__ partials,
-                   T *__restrict__ dot_part, const __grid_constant__ SpmvDistArgs da) {
-  extern __shared__ __align__(128) unsigned char smem[];
+template <typename T, int TILE, bool DOT, bool L2X>
+__device__ __forceinline__ void stream_block(const int32_t *__restrict__ row_ptr, const int32_t *__restrict__ col,
+                                             const T *__restrict__ val, const T *__restrict__ x, T *__restrict__ y,
+                                             const RowBlock *__restrict__ blocks, T *__restrict__ partials,
+                                             T *__restrict__ dot_part, int bidx, unsigned char *smem) {
   using L = StreamSmem<T, TILE>;
   T *sval = reinterpret_cast<T *>(smem);
   int32_t *scol = reinterpret_cast<int32_t *>(smem + L::kVal);
   uint64_t *bar = reinterpret_cast<uint64_t *>(smem + L::kBar);
   T *wsum = reinterpret_cast<T *>(smem + L::kWsum);
-
   const int tid = threadIdx.x;
-  int bidx = blockIdx.x;
-  bool halo = false;  // this block's rows read halo slots of x
-  if constexpr (DIST) {
-    if ((int)blockIdx.x < da.npush) {
-      // ---- push role: segment s of the send list goes into rank seg_rank[s]'s halo slots
-      const int sgm = blockIdx.x / da.push_per_seg, j = blockIdx.x % da.push_per_seg;
-      // the destination must have finished reading the previous product's halo (its ack)
-      if (tid == 0) wait_flag(da.sync + kSyncAck + da.seg_rank[sgm], da.epoch - 1, da.pw);
-      __syncthreads();
-      const int a = da.seg_start[sgm], e = da.seg_start[sgm + 1];
-      T *dst = static_cast<T *>(da.seg_dst[sgm]);
-      for (int i = a + j * kThreads + tid; i < e; i += da.push_per_seg * kThreads) dst[i - a] = __ldg(x + da.send_idx[i]);
-      __threadfence_system();
-      __syncthreads();
-      if (tid == 0 && (atomicAdd(da.sync + kSyncCount, 1u) + 1) % (uint32_t)da.npush == 0)
-        for (int k = 0; k < da.nseg; ++k) st_release_sys(da.seg_flag[k], da.epoch);
-      return;
-    }
-    bidx = blockIdx.x - da.npush;
-    halo = bidx >= da.n_int;
-    if (halo) {  // every source rank's entries of this product must have landed
-      if (tid < da.nsrc) wait_flag(da.sync + kSyncData + da.src_rank[tid], da.epoch, da.pw);
-      __syncthreads();
-    }
-  }
   // Block descriptor: 32 bytes, same for every thread (two broadcast 16-byte loads).
   const int4 d0 = __ldg(reinterpret_cast<const int4 *>(blocks + bidx));
   const longlong2 d1 = __ldg(reinterpret_cast<const longlong2 *>(blocks + bidx) + 1);
@@ -155,7 +128,7 @@ spmv_stream_kernel(const int32_t *__restrict__ row_ptr, const int32_t *__restric
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
           const bool on = i + k < e;
-          xv[k] = on ? gather_x(x, scol[i + k], halo) : T(0);
+          xv[k] = on ? gather_x<T, L2X>(x, scol[i + k]) : T(0);
           vv[k] = on ? sval[i + k] : T(0);
         }
 #pragma unroll
@@ -165,7 +138,7 @@ spmv_stream_kernel(const int32_t *__restrict__ row_ptr, const int32_t *__restric
       y[row0 + r] = s;
       if constexpr (DOT) dot = add_rn(dot, mul_rn(s, ldg_nc(x + row0 + r)));
     }
-    if constexpr (!DOT && !DIST) return;
+    if constexpr (!DOT) return;
   } else {
 
   // Products in place. Four gathers in flight per thread per round.
@@ -174,7 +147,7 @@ spmv_stream_kernel(const int32_t *__restrict__ row_ptr, const int32_t *__restric
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
       const int i = base + k * kThreads;
-      xv[k] = i < cnt ? gather_x(x, scol[i], halo) : T(0);
+      xv[k] = i < cnt ? gather_x<T, L2X>(x, scol[i]) : T(0);
     }
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
@@ -234,13 +207,49 @@ spmv_stream_kernel(const int32_t *__restrict__ row_ptr, const int32_t *__restric
       dot_part[bidx] = t;
     }
   }
-  if constexpr (DIST) {
-    if (halo) {
-      // the last boundary block to finish tells the source ranks that their entries have been read
+}
+
+// DIST: the one-launch distributed product (SpmvDistArgs, spmv.cuh): grid = [push CTAs | interior
+// row blocks | boundary row blocks].
+template <typename T, int TILE, bool DOT, bool DIST>
+__global__ void __launch_bounds__(kThreads, 8)  // 32 registers: 8 CTAs per SM, as many as the tiles allow
+spmv_stream_kernel(const int32_t *__restrict__ row_ptr, const int32_t *__restrict__ col,
+                   const T *__restrict__ val, const T *__restrict__ x, T *__restrict__ y,
+                   const RowBlock *__restrict__ blocks, T *__restrict__ partials,
+                   T *__restrict__ dot_part, const __grid_constant__ SpmvDistArgs da) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  if constexpr (!DIST) {
+    stream_block<T, TILE, DOT, false>(row_ptr, col, val, x, y, blocks, partials, dot_part, blockIdx.x, smem);
+  } else {
+    const int tid = threadIdx.x;
+    if ((int)blockIdx.x < da.npush) {
+      // ---- push role: segment s of the send list goes into rank seg_rank[s]'s halo slots
+      const int sgm = blockIdx.x / da.push_per_seg, j = blockIdx.x % da.push_per_seg;
+      // the destination must have finished reading the previous product's halo (its ack)
+      if (tid == 0) wait_flag(da.sync + kSyncAck + da.seg_rank[sgm], da.epoch - 1, da.pw);
       __syncthreads();
-      if (tid == 0 && (atomicAdd(da.sync + kSyncBnd, 1u) + 1) % (uint32_t)da.n_bnd == 0)
-        for (int k = 0; k < da.nsrc; ++k) st_release_sys(da.src_ack[k], da.epoch);
+      const int a = da.seg_start[sgm], e = da.seg_start[sgm + 1];
+      T *dst = static_cast<T *>(da.seg_dst[sgm]);
+      for (int i = a + j * kThreads + tid; i < e; i += da.push_per_seg * kThreads) dst[i - a] = __ldg(x + da.send_idx[i]);
+      __threadfence_system();
+      __syncthreads();
+      if (tid == 0 && (atomicAdd(da.sync + kSyncCount, 1u) + 1) % (uint32_t)da.npush == 0)
+        for (int k = 0; k < da.nseg; ++k) st_release_sys(da.seg_flag[k], da.epoch);
+      return;
     }
+    const int bidx = blockIdx.x - da.npush;
+    if (bidx < da.n_int) {  // interior rows: owned x only, exactly the single-GPU block
+      stream_block<T, TILE, DOT, false>(row_ptr, col, val, x, y, blocks, partials, dot_part, bidx, smem);
+      return;
+    }
+    // boundary rows: every source rank's entries of this product must have landed
+    if (tid < da.nsrc) wait_flag(da.sync + kSyncData + da.src_rank[tid], da.epoch, da.pw);
+    __syncthreads();
+    stream_block<T, TILE, DOT, true>(row_ptr, col, val, x, y, blocks, partials, dot_part, bidx, smem);
+    // the last boundary block to finish tells the source ranks that their entries have been read
+    __syncthreads();
+    if (tid == 0 && (atomicAdd(da.sync + kSyncBnd, 1u) + 1) % (uint32_t)da.n_bnd == 0)
+      for (int k = 0; k < da.nsrc; ++k) st_release_sys(da.src_ack[k], da.epoch);
   }
 }
 
