@@ -41,6 +41,7 @@ namespace {
 struct NcclApi {
   ncclResult_t (*GetUniqueId)(ncclUniqueId *);
   ncclResult_t (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int);
+  ncclResult_t (*CommInitRankConfig)(ncclComm_t *, int, ncclUniqueId, int, ncclConfig_t *);  // optional (NCCL >= 2.14)
   ncclResult_t (*CommDestroy)(ncclComm_t);
   ncclResult_t (*Send)(const void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t);
   ncclResult_t (*Recv)(void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t);
@@ -63,6 +64,8 @@ hpcx_status load_nccl(hpcx_ctx ctx) {
   if (!g_nccl.field) return fail(ctx, HPCX_NCCL_ERROR, "libnccl lacks " name)
   HPCX_SYM(GetUniqueId, "ncclGetUniqueId");
   HPCX_SYM(CommInitRank, "ncclCommInitRank");
+  g_nccl.CommInitRankConfig =
+      reinterpret_cast<decltype(g_nccl.CommInitRankConfig)>(dlsym(h, "ncclCommInitRankConfig"));
   HPCX_SYM(CommDestroy, "ncclCommDestroy");
   HPCX_SYM(Send, "ncclSend");
   HPCX_SYM(Recv, "ncclRecv");
@@ -286,7 +289,19 @@ hpcx_status hpcx_comm_init(hpcx_ctx ctx, int32_t nranks, int32_t rank, const voi
   memcpy(&id, id128, sizeof id);
   ncclComm_t comm;
   HPCX_CUDA(ctx, cudaSetDevice(ctx->device));
-  HPCX_NCCL(ctx, g_nccl.CommInitRank(&comm, nranks, id, rank));
+  // The halo messages are a few MiB to at most two neighbours: a handful of NCCL CTAs moves them at
+  // NVLink rate, and every SM slot NCCL does not take stays with the sweep kernel that the
+  // exchange overlaps (HPCX_NCCL_MAX_CTAS overrides; 0 = NCCL's default).
+  int max_ctas = 4;
+  if (const char *e = getenv("HPCX_NCCL_MAX_CTAS")) max_ctas = atoi(e);
+  if (g_nccl.CommInitRankConfig && max_ctas > 0) {
+    ncclConfig_t cfg = NCCL_CONFIG_INITIALIZER;
+    cfg.maxCTAs = max_ctas;
+    cfg.minCTAs = 1;
+    HPCX_NCCL(ctx, g_nccl.CommInitRankConfig(&comm, nranks, id, rank, &cfg));
+  } else {
+    HPCX_NCCL(ctx, g_nccl.CommInitRank(&comm, nranks, id, rank));
+  }
   ctx->nccl_comm = comm;
   ctx->nranks = nranks;
   ctx->rank = rank;
@@ -518,6 +533,74 @@ hpcx_status stencil_peer_sweep(hpcx_halo_plan p, int32_t steps, cudaStream_t cs,
 }  // namespace hpcx
 extern "C" {
 
+}  // extern "C"
+// Everything one NCCL-transport call puts on the two streams (no host synchronisation inside, so the
+// sequence can be captured into a graph): the initial ghost exchange of `in`, then per pass
+//   compute stream: [wait ghosts of src] boundary planes z = 0, n-1  -> record ev_bnd
+//   comm stream   : [wait ev_bnd] send dst boundary planes / receive dst ghost planes
+//   compute stream: interior planes 1 .. n-2 (overlaps the exchange)
+// HPCX_VARIANT_TEMPORAL runs steps/2 two-sweep passes the same way with TWO planes per side (the
+// neighbour's boundary plane is advanced redundantly on this rank), then one single sweep when
+// steps is odd: the bytes exchanged per sweep are unchanged, the messages per sweep halve.
+static hpcx_status nccl_sweeps_enqueue(hpcx_halo_plan p, int32_t steps, cudaStream_t cs) {
+  hpcx_ctx ctx = p->ctx;
+  hpcx_grid g = p->in;
+  cudaStream_t ms = ctx->comm;
+  const int64_t nz = g->n[0];
+  hpcx_status rc = HPCX_OK;
+  // Make the ghosts of the first source iterate consistent with the neighbours.
+  HPCX_CUDA(ctx, cudaEventRecord(p->ev_start, cs));
+  HPCX_CUDA(ctx, cudaStreamWaitEvent(ms, p->ev_start, 0));
+  rc = exchange_planes(g, p->in->dev, ms, (p->st.variant == HPCX_VARIANT_TEMPORAL && steps >= 2) ? 2 : 1);
+  if (rc != HPCX_OK) return rc;
+  HPCX_CUDA(ctx, cudaEventRecord(p->ev_recv, ms));
+  // A pass advances the slab by w sweeps (w = 2: the temporally blocked kernel) and needs w valid
+  // ghost planes per side of its source; the exchange after a pass carries the width the NEXT pass
+  // reads.  Boundary = the w planes next to each z neighbour.
+  const bool temporal = p->st.variant == HPCX_VARIANT_TEMPORAL;
+  const bool nb_lo = ctx->rank > 0, nb_hi = ctx->rank + 1 < ctx->nranks;
+  const int passes = temporal ? steps / 2 + (steps & 1) : steps;
+  void *src = p->in->dev, *dst = p->out->dev;
+  for (int t = 0; t < passes; ++t) {
+    const bool two = temporal && t < steps / 2;
+    const int64_t w = two ? 2 : 1;
+    const int64_t lo_end = std::min<int64_t>(w, nz), hi_beg = std::max<int64_t>(lo_end, nz - w);
+    auto launch = [&](int64_t zb, int64_t ze, int zsplit) -> hpcx_status {
+      if (ze <= zb) return HPCX_OK;
+      if (two) return jacobi7_tb2_launch(g, src, dst, zsplit, zb, ze, nb_lo, nb_hi, cs);
+      return jacobi7_launch(g, src, dst, temporal ? HPCX_VARIANT_TMA : p->st.variant, zsplit, zb, ze, cs, nullptr);
+    };
+    HPCX_CUDA(ctx, cudaStreamWaitEvent(cs, p->ev_recv, 0));
+    nvtxRangePushA("sweep: boundary planes");
+    if (two) {  // both boundary strips in one launch
+      rc = jacobi7_tb2_launch(g, src, dst, 1, 0, lo_end, nb_lo, nb_hi, cs, hi_beg, nz);
+    } else {
+      rc = launch(0, lo_end, 1);
+      if (rc == HPCX_OK) rc = launch(hi_beg, nz, 1);
+    }
+    nvtxRangePop();
+    if (rc != HPCX_OK) return rc;
+    if (t + 1 < passes) {
+      HPCX_RANGE("sweep: ghost-plane exchange (NCCL send/recv)");
+      const int64_t wnext = (temporal && t + 1 < steps / 2) ? 2 : 1;
+      HPCX_CUDA(ctx, cudaEventRecord(p->ev_bnd, cs));
+      HPCX_CUDA(ctx, cudaStreamWaitEvent(ms, p->ev_bnd, 0));
+      rc = exchange_planes(g, dst, ms, wnext);
+      if (rc != HPCX_OK) return rc;
+      HPCX_CUDA(ctx, cudaEventRecord(p->ev_recv, ms));
+    }
+    {
+      HPCX_RANGE("sweep: interior planes");
+      rc = launch(lo_end, hi_beg, temporal ? (two ? p->st.zsplit : 0) : p->st.zsplit);
+    }
+    if (rc != HPCX_OK) return rc;
+    std::swap(src, dst);
+  }
+  return HPCX_OK;
+}
+
+extern "C" {
+
 // Per step t (src -> dst):
 //   compute stream: [wait ghosts of src] boundary planes z = 0, n-1  -> record ev_bnd
 //   comm stream   : [wait ev_bnd] send dst boundary planes / receive dst ghost planes
@@ -570,62 +653,65 @@ hpcx_status hpcx_stencil_dist_sweep(hpcx_halo_plan p, int32_t steps, void *strea
     return HPCX_OK;
   }
 
-  // Make the ghosts of the first source iterate consistent with the neighbours.
-  HPCX_CUDA(ctx, cudaEventRecord(p->ev_start, cs));
-  HPCX_CUDA(ctx, cudaStreamWaitEvent(ms, p->ev_start, 0));
-  rc = exchange_planes(g, p->in->dev, ms, (p->st.variant == HPCX_VARIANT_TEMPORAL && steps >= 2) ? 2 : 1);
-  if (rc != HPCX_OK) return rc;
-  HPCX_CUDA(ctx, cudaEventRecord(p->ev_recv, ms));
-
   if (p->transport == 1 && ctx->nranks > 1) {
+    // Make the ghosts of the first source iterate consistent with the neighbours, then the fused sweeps.
+    HPCX_CUDA(ctx, cudaEventRecord(p->ev_start, cs));
+    HPCX_CUDA(ctx, cudaStreamWaitEvent(ms, p->ev_start, 0));
+    rc = exchange_planes(g, p->in->dev, ms, (p->st.variant == HPCX_VARIANT_TEMPORAL && steps >= 2) ? 2 : 1);
+    if (rc != HPCX_OK) return rc;
+    HPCX_CUDA(ctx, cudaEventRecord(p->ev_recv, ms));
     HPCX_CUDA(ctx, cudaStreamWaitEvent(cs, p->ev_recv, 0));
     return hpcx::stencil_peer_sweep(p, steps, cs, stream == nullptr);
   }
 
-  // A pass advances the slab by w sweeps (w = 2: the temporally blocked kernel) and needs w valid
-  // ghost planes per side of its source; the exchange after a pass carries the width the NEXT pass
-  // reads.  Boundary = the w planes next to each z neighbour.
-  const bool temporal = p->st.variant == HPCX_VARIANT_TEMPORAL;
-  const bool nb_lo = ctx->rank > 0, nb_hi = ctx->rank + 1 < ctx->nranks;
-  const int passes = temporal ? steps / 2 + (steps & 1) : steps;
-  void *src = p->in->dev, *dst = p->out->dev;
-  for (int t = 0; t < passes; ++t) {
-    const bool two = temporal && t < steps / 2;
-    const int64_t w = two ? 2 : 1;
-    const int64_t lo_end = std::min<int64_t>(w, nz), hi_beg = std::max<int64_t>(lo_end, nz - w);
-    auto launch = [&](int64_t zb, int64_t ze, int zsplit) -> hpcx_status {
-      if (ze <= zb) return HPCX_OK;
-      if (two) return jacobi7_tb2_launch(g, src, dst, zsplit, zb, ze, nb_lo, nb_hi, cs);
-      return jacobi7_launch(g, src, dst, temporal ? HPCX_VARIANT_TMA : p->st.variant, zsplit, zb, ze, cs, nullptr);
-    };
-    HPCX_CUDA(ctx, cudaStreamWaitEvent(cs, p->ev_recv, 0));
-    nvtxRangePushA("sweep: boundary planes");
-    if (two) {  // both boundary strips in one launch
-      rc = jacobi7_tb2_launch(g, src, dst, 1, 0, lo_end, nb_lo, nb_hi, cs, hi_beg, nz);
-    } else {
-      rc = launch(0, lo_end, 1);
-      if (rc == HPCX_OK) rc = launch(hi_beg, nz, 1);
+  // NCCL transport.  The whole call — for every pass {boundary planes, grouped send/recv on the comm
+  // stream, interior planes} — is captured ONCE into a CUDA graph per (buffers, steps) and replayed:
+  // a sweep is three launches plus an NCCL group, and at 170 us per sweep their launch gaps and the
+  // event hand-offs between the two streams are what kept this transport at 80 % of the one-GPU rate.
+  bool launched = false;
+  cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+  if (ctx->nranks > 1 && p->graphs_ok && cudaStreamIsCapturing(cs, &cap) == cudaSuccess &&
+      cap == cudaStreamCaptureStatusNone) {
+    cudaGraphExec_t exec = nullptr;
+    for (auto &e : p->graphs)
+      if (e.in == p->in->dev && e.out == p->out->dev && e.steps == steps) exec = e.exec;
+    if (!exec) {
+      HPCX_RANGE("sweep: capture into a CUDA graph");
+      if (hpcx_status st = preload_stencil_kernels(ctx)) return st;  // no attribute calls inside the capture
+      cudaGraph_t graph = nullptr;
+      cudaError_t e = cudaStreamBeginCapture(cs, cudaStreamCaptureModeRelaxed);
+      if (e == cudaSuccess) {
+        rc = nccl_sweeps_enqueue(p, steps, cs);
+        e = cudaStreamEndCapture(cs, &graph);
+        if (rc == HPCX_OK && e == cudaSuccess) e = cudaGraphInstantiate(&exec, graph, 0);
+        if (graph) cudaGraphDestroy(graph);
+      }
+      if (rc != HPCX_OK || e != cudaSuccess || !exec) {
+        (void)cudaGetLastError();
+        p->graphs_ok = false;  // every rank takes the same decision: same code, same library
+        exec = nullptr;
+        rc = HPCX_OK;
+      } else {
+        if (p->graphs.size() >= 8) {
+          for (auto &old : p->graphs) cudaGraphExecDestroy(old.exec);
+          p->graphs.clear();
+        }
+        p->graphs.push_back({p->in->dev, p->out->dev, steps, exec});
+      }
     }
-    nvtxRangePop();
-    if (rc != HPCX_OK) return rc;
-    if (t + 1 < passes) {
-      HPCX_RANGE("sweep: ghost-plane exchange (NCCL send/recv)");
-      const int64_t wnext = (temporal && t + 1 < steps / 2) ? 2 : 1;
-      HPCX_CUDA(ctx, cudaEventRecord(p->ev_bnd, cs));
-      HPCX_CUDA(ctx, cudaStreamWaitEvent(ms, p->ev_bnd, 0));
-      rc = exchange_planes(g, dst, ms, wnext);
-      if (rc != HPCX_OK) return rc;
-      HPCX_CUDA(ctx, cudaEventRecord(p->ev_recv, ms));
+    if (exec) {
+      HPCX_CUDA(ctx, cudaGraphLaunch(exec, cs));
+      ctx->launches += p->graph_launches(steps);
+      launched = true;
     }
-    {
-      HPCX_RANGE("sweep: interior planes");
-      rc = launch(lo_end, hi_beg, temporal ? (two ? p->st.zsplit : 0) : p->st.zsplit);
-    }
-    if (rc != HPCX_OK) return rc;
-    std::swap(src, dst);
   }
-  steps = passes;  // parity of the buffer swap below
-  if ((steps & 1) == 0) std::swap(p->in->dev, p->out->dev);
+  if (!launched) {
+    rc = nccl_sweeps_enqueue(p, steps, cs);
+    if (rc != HPCX_OK) return rc;
+  }
+  const bool temporal = p->st.variant == HPCX_VARIANT_TEMPORAL;
+  const int passes = temporal ? steps / 2 + (steps & 1) : steps;
+  if ((passes & 1) == 0) std::swap(p->in->dev, p->out->dev);
   if (!stream) HPCX_CUDA(ctx, cudaStreamSynchronize(cs));
   return HPCX_OK;
 }
@@ -638,6 +724,7 @@ hpcx_status hpcx_stencil_dist_destroy(hpcx_halo_plan p) {
   cudaEventDestroy(p->ev_bnd);
   cudaEventDestroy(p->ev_recv);
   cudaEventDestroy(p->ev_start);
+  for (auto &e : p->graphs) cudaGraphExecDestroy(e.exec);
   delete p;
   return pending;
 }

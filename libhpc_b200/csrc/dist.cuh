@@ -18,6 +18,20 @@ struct hpcx_halo_plan_s {
   uint32_t *peer_flags[2] = {nullptr, nullptr};
   int64_t peer_n0[2] = {0, 0};
   uint32_t epoch = 0;                 // sweeps completed through this plan
+  // NCCL transport: one captured CUDA graph per (source buffer, destination buffer, steps)
+  struct GraphEntry {
+    void *in, *out;
+    int steps;
+    cudaGraphExec_t exec;
+  };
+  std::vector<GraphEntry> graphs;
+  bool graphs_ok = true;  // cleared when a capture fails: the call then runs eagerly
+  // kernels of this library one replay launches (for hpcx_launch_count)
+  int64_t graph_launches(int steps) const {
+    const bool temporal = st.variant == HPCX_VARIANT_TEMPORAL;
+    const int two = temporal ? steps / 2 : 0, one = temporal ? (steps & 1) : steps;
+    return 2 * (int64_t)two + 3 * (int64_t)one;
+  }
 };
 
 

@@ -84,6 +84,7 @@ void free_plans(hpcx_multi_grid G) {
       cudaEventDestroy(p->ev_bnd);
       cudaEventDestroy(p->ev_recv);
       cudaEventDestroy(p->ev_start);
+      for (auto &e : p->graphs) cudaGraphExecDestroy(e.exec);
       delete p;
     }
   G->plans.clear();

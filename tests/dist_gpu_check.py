@@ -176,6 +176,15 @@ def main():
             D.spmv_dist(xd, yd)
             assert_spmv_close(yd.cpu().numpy(), oracle.spmv(rp, col, val, x2)[r0:r1],
                               oracle.spmv_abs(rp, col, val, x2)[r0:r1], tol)
+            # host operands: this rank's x block in (pinned), its y block out — pipelined against PCIe
+            # and the exchange with the fused transport, copy-product-copy otherwise; same bits as
+            # the device-resident product
+            yd_ref = yd.clone()
+            xh = torch.from_numpy(x2[r0:r1].copy()).pin_memory()
+            yh = torch.full((r1 - r0,), float("nan"), dtype=xh.dtype).pin_memory()
+            for _ in range(2):
+                D.spmv_dist_host(xh.numpy(), yh.numpy())
+            assert bits_equal(yh.numpy(), yd_ref.cpu().numpy()), (rank, name, transport, "dist_host")
             if transport == 1 and world > 1 and name == "op27":
                 # rank skew: the last rank arrives 5 s late at the next product.  The flag waits of
                 # the fused transport have no bound by default (like an NCCL receive), so the other
