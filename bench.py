@@ -545,6 +545,8 @@ def stencil_extra(args, ctx, torch, stream, world, rank, barrier, max_over_ranks
     def timed(step, reps=2):
         with torch.cuda.stream(stream):
             step()
+            step()  # twice: an even number of sweeps swaps the two buffers, and the NCCL transport keeps
+            #         one captured graph per orientation
             n0 = ctx.launch_count()
             dt, _, _ = time_steps(torch, stream, step, reps, barrier)
             launches = ctx.launch_count() - n0
@@ -817,6 +819,73 @@ def c1_extra(args, ctx, torch, stream, barrier, hp, synth):
     return e
 
 
+def c5_distributed(args, ctx, torch, stream, world, rank, barrier, max_over_ranks, hp, hd):
+    """configs[4] across GPUs (STRONG scaling, the global matrix fixed): nnz-balanced contiguous row
+    blocks (hpcx_partition_rows mode 1).  The exchange is all-to-all in shape — every rank needs most
+    of x — and runs through the same fused peer-store transport as the banded operators (one launch
+    per product: push | interior | boundary + ack); no ncclAllGather fallback is needed.  Every rank
+    generates and assembles the global R-MAT on its own GPU (0.1 s), keeps its row block, and the
+    distributed localiser derives the halo tables; the product of a random x is checked against the
+    single-GPU HUB kernel's result on the same rank."""
+    scale = 24
+    nr = 1 << scale
+    t = time.time()
+    arrs = hp.synth_rmat_csr(ctx, scale, 16, 24, 4)
+    R = hp.DeviceCsr.from_device_arrays(ctx, arrs)  # single-GPU reference product (AUTO -> HUB)
+    rp, col, val = arrs.download()
+    arrs.destroy()
+    x = torch.empty(nr, dtype=torch.float32, device="cuda")
+    hp.synth_field(ctx, 42, nr, x, np.float32)
+    y_one = torch.empty(nr, dtype=torch.float32, device="cuda")
+    torch.cuda.synchronize()
+    R.spmv(x, y_one, stream)
+    stream.synchronize()
+    R.destroy()
+    bounds = hp.partition_rows(nr, rp, world, 1)
+    r0, r1 = int(bounds[rank]), int(bounds[rank + 1])
+    p0, p1 = int(rp[r0]), int(rp[r1])
+    L = hd.localize_rows_distributed((rp[r0:r1 + 1] - p0).astype(np.int64), col[p0:p1], val[p0:p1], bounds, rank, world, nr)
+    nnz_total = int(rp[-1])
+    del rp, col, val
+    L["local_row_ptr"] = L["local_row_ptr"].astype(np.int32)
+    A = hp.CsrMatrix(L["local_row_ptr"], L["local_col"], np.ascontiguousarray(L["values"]), ncols=L["nloc"] + L["nhalo"])
+    D = hp.DeviceCsr(ctx, A, kernel=hp.SPMV_STREAM)
+    D.set_halo(L)
+    D.halo_transport(1)
+    log(f"[rank {rank}] C5 block: rows [{r0}, {r1}), {L['nnz_loc']} nnz, {L['nhalo']} halo columns, "
+        f"{L['nsend']} sends, set up in {time.time() - t:.1f}s")
+    xfull = D.x_buffer()
+    ctx.memcpy((xfull, hp.MEM_DEVICE), x[r0:r1].contiguous(), (r1 - r0) * 4)
+    y = torch.empty(r1 - r0, dtype=torch.float32, device="cuda")
+    x_arg = (xfull, hp.MEM_DEVICE)
+    step = lambda: D.spmv_dist(x_arg, y, stream)  # noqa: E731
+    barrier()
+    step()
+    stream.synchronize()
+    # same matrix, same x: the distributed rows against the single-GPU product (different summation
+    # orders in fp32: bound 3e-5 of max|y|, value reported)
+    err = float((y - y_one[r0:r1]).abs().max() / y_one.abs().max())
+    if not err <= 3e-5:
+        raise SystemExit(f"[rank {rank}] bench.py: distributed C5 product differs from the single-GPU one ({err:.2e})")
+    with torch.cuda.stream(stream):
+        for _ in range(3):
+            step()
+        dt, _, _ = time_steps(torch, stream, step, args.steps, barrier)
+    dt = max_over_ranks(dt)
+    gbytes = algorithmic_bytes(nr, nnz_total, 4)
+    peak, _ = measured_peak()
+    e = {"metric": METRIC, "value": gbytes * args.steps / dt / 1e9, "unit": UNIT, "scaling": "strong",
+         "ms_per_step": dt / args.steps * 1e3, "rows": nr, "nnz": nnz_total,
+         "partition": f"{world} nnz-balanced row blocks; rank 0 owns rows [0, {int(bounds[1])})",
+         "halo_columns_rank0": int(L["nhalo"]) if rank == 0 else None,
+         "max_rel_diff_vs_single_gpu": err,
+         "roofline": {"bound": "hbm", "achieved": gbytes / world * args.steps / dt / 1e9, "peak": peak, "unit": "GB/s",
+                      "frac": gbytes / world * args.steps / dt / 1e9 / peak,
+                      "note": "global algorithmic bytes / N per rank; STREAM kernel (the HUB kernel is single-GPU)"}}
+    D.destroy()
+    return e
+
+
 def sparse_extra(args, ctx, torch, stream, world, rank, barrier, max_over_ranks, hp, hd, synth):
     """The other SpMV configs of BASELINE.json as `extra` entries.
     C4 (configs[3]): 27-point operator on 256^3, fp64, row-partitioned into z-slab blocks with
@@ -881,6 +950,8 @@ def sparse_extra(args, ctx, torch, stream, world, rank, barrier, max_over_ranks,
     D.destroy()
     del xd, yd, x, A, L
     if world > 1:
+        out["c5_rmat_scale24_fp32"] = c5_distributed(args, ctx, torch, stream, world, rank, barrier, max_over_ranks,
+                                                      hp, hd)
         return out
 
     scale = 24

@@ -289,10 +289,10 @@ hpcx_status hpcx_comm_init(hpcx_ctx ctx, int32_t nranks, int32_t rank, const voi
   memcpy(&id, id128, sizeof id);
   ncclComm_t comm;
   HPCX_CUDA(ctx, cudaSetDevice(ctx->device));
-  // The halo messages are a few MiB to at most two neighbours: a handful of NCCL CTAs moves them at
-  // NVLink rate, and every SM slot NCCL does not take stays with the sweep kernel that the
-  // exchange overlaps (HPCX_NCCL_MAX_CTAS overrides; 0 = NCCL's default).
-  int max_ctas = 4;
+  // NCCL's own choice of CTAs is kept by default: capping it at 4 for the few-MiB halo messages was
+  // measured SLOWER at 2 GPUs (one sweep 219 vs 199 us, two sweeps 130 vs 105 us per sweep: the
+  // exchange then outlasts the interior sweep it hides behind).  HPCX_NCCL_MAX_CTAS > 0 sets a cap.
+  int max_ctas = 0;
   if (const char *e = getenv("HPCX_NCCL_MAX_CTAS")) max_ctas = atoi(e);
   if (g_nccl.CommInitRankConfig && max_ctas > 0) {
     ncclConfig_t cfg = NCCL_CONFIG_INITIALIZER;
@@ -443,6 +443,7 @@ hpcx_status hpcx_stencil_dist_plan(hpcx_ctx ctx, hpcx_grid in, hpcx_grid out,
   p->out = out;
   p->st = *st;
   p->transport = transport;
+  if (const char *g = getenv("HPCX_NCCL_GRAPHS")) p->graphs_ok = atoi(g) != 0;  // 0: replay nothing, launch every call eagerly
   cudaError_t e = cudaEventCreateWithFlags(&p->ev_bnd, cudaEventDisableTiming);
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->ev_recv, cudaEventDisableTiming);
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->ev_start, cudaEventDisableTiming);
