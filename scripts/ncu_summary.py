@@ -23,7 +23,10 @@ KEEP = re.compile(
     r"lts__t_sectors_srcunit_tex_op_write\.sum|lts__t_bytes\.sum|"
     r"l1tex__t_sector_hit_rate\.pct|l1tex__t_(sectors|requests)_pipe_lsu_mem_global_op_(ld|st)\.sum|"
     r"l1tex__average_t_sectors_per_request_pipe_lsu_mem_global_op_(ld|st)\.ratio|"
-    r"l1tex__data_bank_conflicts_pipe_lsu_mem_shared\.sum|l1tex__data_pipe_lsu_wavefronts_mem_shared\.sum|"
+    r"l1tex__data_bank_conflicts_pipe_lsu_mem_shared\.sum|l1tex__data_pipe_lsu_wavefronts(_mem_shared)?\.sum|"
+    r"l1tex__data_pipe_lsu_wavefronts\.avg\.pct_of_peak_sustained_elapsed|"
+    r"l1tex__t_sectors_pipe_lsu_mem_global_op_ld_lookup_(hit|miss)\.sum|"
+    r"(l1tex|lts)__throughput\.avg\.pct_of_peak_sustained_elapsed|smsp__warps_eligible\.avg\.per_cycle_active|"
     r"launch__(registers_per_thread|grid_size|block_size|waves_per_multiprocessor|"
     r"shared_mem_per_block_dynamic|occupancy_limit_(registers|shared_mem|warps|blocks))|"
     r"sm__warps_active\.avg\.pct_of_peak_sustained_active|sm__throughput\.avg\.pct_of_peak_sustained_elapsed|"
