@@ -24,6 +24,8 @@ hpcx_status box_launch_rows(hpcx_grid_s *in, hpcx_grid_s *out, const hpcx_stenci
                             cudaStream_t s);
 hpcx_status jacobi7_tb2_launch(hpcx_grid_s *g, void *src, void *dst, int zsplit, int64_t zbeg, int64_t zend,
                                bool nb_lo, bool nb_hi, cudaStream_t s, int64_t zbeg2 = 0, int64_t zend2 = 0);
+hpcx_status jacobi7_tb2_peer_launch(hpcx_grid_s *g, void *src, void *dst, int zsplit, const JacobiPeer &peer,
+                                    cudaStream_t s);
 hpcx_status spmv_launch_blocks(hpcx_csr A, const RowBlock *d_blocks, int64_t nblocks, const void *x,
                                void *y, cudaStream_t s, void *dot_part, const SpmvDistArgs *da);
 hpcx_status spmv_launch_fixup_tables(hpcx_csr A, const int32_t *long_row, const int32_t *long_off,
@@ -472,6 +474,9 @@ hpcx_status hpcx_stencil_dist_plan(hpcx_ctx ctx, hpcx_grid in, hpcx_grid out,
 // and push their two boundary planes per side with halo_push_planes_kernel right behind it.
 }  // extern "C"
 namespace hpcx {
+// Slabs of at most this many planes push their boundary planes from inside the two-sweep pass
+// kernel (stencil.cu, jacobi7_tb2_peer_kernel); thicker ones through halo_push_planes_kernel.
+constexpr int64_t kThinSlabPlanes = 128;
 hpcx_status stencil_peer_sweep(hpcx_halo_plan p, int32_t steps, cudaStream_t cs, bool sync) {
   hpcx_ctx ctx = p->ctx;
   hpcx_grid g = p->in;
@@ -502,7 +507,14 @@ hpcx_status stencil_peer_sweep(hpcx_halo_plan p, int32_t steps, cudaStream_t cs,
     pr.pw = peer_wait_of(ctx);
     pr.wait_val = t == 0 ? 0 : p->epoch + (uint32_t)t;  // pass 0 reads NCCL-exchanged ghosts
     pr.sig_val = p->epoch + (uint32_t)t + 1;
-    if (temporal && t < steps / 2) {
+    if (temporal && t < steps / 2 && g->n[0] >= 2 && g->n[0] <= kThinSlabPlanes) {
+      // thin slab: ONE launch per pass — the pass kernel awaits its ghost planes itself and the CTAs
+      // that own planes 0, 1 / n0-2, n0-1 push them into the neighbours' ghosts n, n+1 / -2, -1
+      JacobiPeer pp = pr;
+      if (has_hi) pp.ghost_hi = pr.ghost_hi - plane;  // first of the two ghost planes
+      pp.counters = p->flags + 6;                     // tile counts differ from the one-sweep kernel's
+      rc = jacobi7_tb2_peer_launch(g, p->buf[cur], p->buf[dst], p->st.zsplit, pp, cs);
+    } else if (temporal && t < steps / 2) {
       // pass kernel ; push kernel (planes 0, 1 -> low neighbour's ghosts n, n+1; planes n0-2, n0-1
       // -> high neighbour's ghosts -2, -1; then waits until the neighbours' planes have landed here)
       rc = jacobi7_tb2_launch(g, p->buf[cur], p->buf[dst], p->st.zsplit, 0, g->n[0], has_lo, has_hi, cs);

@@ -639,20 +639,20 @@ struct JacobiTBSplit {
 #define HPCX_J7(zm, ym, xm, xp, yp, zp) \
   mul_rn(add_rn(add_rn(add_rn(add_rn(add_rn(zm, ym), xm), xp), yp), zp), sixth)
 
-template <int S_>
-__global__ void __launch_bounds__(256, S_ <= 5 ? 3 : 2)
-jacobi7_tb2_kernel(const __grid_constant__ CUtensorMap map_hi, const __grid_constant__ CUtensorMap map_lo,
-                   float *__restrict__ out, GridGeom g, JacobiTBSplit sp, float sixth) {
+// One CTA's work: tile (bx, by) x z segment bz of one two-sweep pass.  WAITS (slab with z
+// neighbours, fused transport): a ghost plane of the slab is loaded only after the neighbour's flag
+// says it has landed (pr.wait_val, as in the one-sweep kernel).
+template <int S_, bool WAITS>
+__device__ __forceinline__ void
+jacobi7_tb2_item(const CUtensorMap *map_hi, const CUtensorMap *map_lo, float *__restrict__ out, const GridGeom &g,
+                 const JacobiTBSplit &sp, const JacobiPeer &pr, float sixth, int bx, int by, int bz,
+                 unsigned char *smem) {
   using C = JacobiTBCfg<S_>;
-  extern __shared__ __align__(128) unsigned char smem[];
   float *ring = reinterpret_cast<float *>(smem);
   float *abuf = reinterpret_cast<float *>(smem + C::kAOff);
   uint64_t *full = reinterpret_cast<uint64_t *>(smem + C::kBarOff);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int bx = blockIdx.x % sp.ntx;
-  const int by = (blockIdx.x / sp.ntx) % sp.nty;
-  const int bz = blockIdx.x / (sp.ntx * sp.nty);
   const int x0 = bx * C::TX;
   const int y0 = (int)((int64_t)by * g.n1 / sp.nty);
   const int h = (int)((int64_t)(by + 1) * g.n1 / sp.nty) - y0;
@@ -664,11 +664,16 @@ jacobi7_tb2_kernel(const __grid_constant__ CUtensorMap map_hi, const __grid_cons
   // The per-step barrier of the consumers (below) already proves that plane j has been read by
   // every warp, so the ring needs no "empty" barriers and no producer warp: thread 0 issues the
   // TMA load of plane j + S - 1 right after the barrier of step j.
-  const CUtensorMap *map = h == sp.hmax ? &map_hi : &map_lo;
+  const CUtensorMap *map = h == sp.hmax ? map_hi : map_lo;
   const uint32_t box_bytes = (uint32_t)(C::BX * (h + 4) * 4);
   const int c0 = (int)g.xoff + x0 - C::HX;
   const int c1 = y0 + (int)g.glo1 - 2;  // may be -1: rows outside the array are zero-filled
   auto issue = [&](int p) {            // plane p -> slot p % S; thread 0 only
+    if (WAITS && pr.wait_val) {
+      const int z = z0 - 2 + p;
+      if (z < 0 && pr.sig_lo) wait_flag(pr.flags + 0, pr.wait_val, pr.pw);
+      if (z >= (int)g.n0 && pr.sig_hi) wait_flag(pr.flags + 1, pr.wait_val, pr.pw);
+    }
     mbar_expect_tx(full + (p % C::S), box_bytes);
     tma_load_3d(ring + (p % C::S) * C::kSlotFloats, map, c0, c1, z0 - 2 + p + (int)g.glo0,
                 full + (p % C::S));
@@ -853,11 +858,69 @@ jacobi7_tb2_kernel(const __grid_constant__ CUtensorMap map_hi, const __grid_cons
 }
 #undef HPCX_J7
 
+template <int S_>
+__global__ void __launch_bounds__(256, S_ <= 5 ? 3 : 2)
+jacobi7_tb2_kernel(const __grid_constant__ CUtensorMap map_hi, const __grid_constant__ CUtensorMap map_lo,
+                   float *__restrict__ out, GridGeom g, JacobiTBSplit sp, float sixth) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  const int bx = blockIdx.x % sp.ntx;
+  const int by = (blockIdx.x / sp.ntx) % sp.nty;
+  const int bz = blockIdx.x / (sp.ntx * sp.nty);
+  jacobi7_tb2_item<S_, false>(&map_hi, &map_lo, out, g, sp, JacobiPeer{}, sixth, bx, by, bz, smem);
+}
+
+// The pass kernel of a THIN slab with z neighbours (dist.cu, peer-store transport; strong
+// scaling): ghost planes are awaited inside the kernel and the CTAs that own planes 0, 1 / n-2, n-1
+// copy their tile of those planes (rows y0 .. y0+h, 128 columns) from the iterate they have just
+// written into the neighbour's two ghost planes with peer stores when they are done; the last
+// tile of a side (arrival counter) publishes the pass number in the neighbour's flag word.  One
+// launch per pass and nothing between the passes — at 64 planes per GPU the separate push kernel
+// (halo_push_planes_kernel, which ends with a wait for both neighbours) cost 6 % at 8 GPUs.  On
+// thick slabs a CTA's segment is hundreds of planes long, the push would leave at the very end of
+// the pass, and the push kernel is the better choice (2668 against 2292 Gcell/s at 2 x 512^3).
+// Segments next to a neighbour run first.  pr.ghost_lo / ghost_hi: plane base of the FIRST of the
+// two ghost planes in the neighbour's destination buffer, or null.
+template <int S_>
+__global__ void __launch_bounds__(256, S_ <= 5 ? 3 : 2)
+jacobi7_tb2_peer_kernel(const __grid_constant__ CUtensorMap map_hi, const __grid_constant__ CUtensorMap map_lo,
+                        float *__restrict__ out, GridGeom g, JacobiTBSplit sp, JacobiPeer pr, float sixth) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  const int bx = blockIdx.x % sp.ntx;
+  const int by = (blockIdx.x / sp.ntx) % sp.nty;
+  const int seg = blockIdx.x / (sp.ntx * sp.nty);
+  const bool lo = pr.ghost_lo != nullptr, hi = pr.ghost_hi != nullptr;
+  const int bz = !hi ? seg : !lo ? sp.zs - 1 - seg : (seg & 1) ? sp.zs - 1 - (seg >> 1) : (seg >> 1);
+  jacobi7_tb2_item<S_, true>(&map_hi, &map_lo, out, g, sp, pr, sixth, bx, by, bz, smem);
+  __syncthreads();  // the CTA's stores of the new iterate are visible to all of its threads (L2)
+  const int64_t plane = g.ext1 * g.pitch;
+  const uint32_t tiles = (uint32_t)(sp.ntx * sp.nty);
+#pragma unroll
+  for (int side = 0; side < 2; ++side) {
+    float *peer = side ? pr.ghost_hi : pr.ghost_lo;
+    if (!peer || bz != (side ? sp.zs - 1 : 0)) continue;  // uniform over the CTA
+    const int y0 = (int)((int64_t)by * g.n1 / sp.nty);
+    const int h = (int)((int64_t)(by + 1) * g.n1 / sp.nty) - y0;
+    const int zf = side ? (int)g.n0 - 2 : 0;
+    for (int i = (int)threadIdx.x; i < 2 * h * 32; i += (int)blockDim.x) {
+      const int pl = i / (h * 32), r = (i >> 5) % h, x = bx * JacobiTBCfg<S_>::TX + 4 * (i & 31);
+      if (x >= g.n2) continue;
+      const int64_t inplane = (int64_t)(y0 + r + g.glo1) * g.pitch + g.xoff + x;
+      const float4 v = __ldcg(reinterpret_cast<const float4 *>(out + (zf + pl + g.glo0) * plane + inplane));
+      *reinterpret_cast<float4 *>(peer + pl * plane + inplane) = v;
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0 && (atomicAdd(pr.counters + side, 1u) + 1) % tiles == 0)
+      st_release_sys(side ? pr.sig_hi : pr.sig_lo, pr.sig_val);
+  }
+}
+
 
 // Two sweeps src -> dst in one pass (HPCX_VARIANT_TEMPORAL).  Tiles of 128 x <= 14 cells, z
 // segments chosen so that the CTA count is about two per SM (the kernel's residency).
 hpcx_status launch_jacobi_tb2(hpcx_grid_s *g, void *src, void *dst, int zsplit, int64_t zbeg, int64_t zend,
-                              bool nb_lo, bool nb_hi, cudaStream_t s, int64_t zbeg2 = 0, int64_t zend2 = 0) {
+                              bool nb_lo, bool nb_hi, cudaStream_t s, int64_t zbeg2 = 0, int64_t zend2 = 0,
+                              const JacobiPeer *peer = nullptr) {
   using C = JacobiTBCfg<8>;
   const int per_sm = 2;  // 98.6 KB of shared memory per CTA (five slots and 3 CTAs/SM measured 2 % slower)
   hpcx_ctx ctx = g->ctx;
@@ -891,6 +954,7 @@ hpcx_status launch_jacobi_tb2(hpcx_grid_s *g, void *src, void *dst, int zsplit, 
       if (cost < best * (1.0 - 1e-9)) best = cost, zs = c;
     }
   }
+  if (peer) zs = std::min<int64_t>(zs, std::max<int64_t>(1, nzr / 2));  // planes 0, 1 / n-2, n-1 each inside ONE segment
   sp.zs = (int)std::max<int64_t>(zs, 1);
   hpcx_status st = HPCX_OK;
   const CUtensorMap *hi = jacobi_map(g, src, sp.hmax + 4, &st);
@@ -901,6 +965,13 @@ hpcx_status launch_jacobi_tb2(hpcx_grid_s *g, void *src, void *dst, int zsplit, 
   st = ensure_dyn_smem(ctx, (const void *)jacobi7_tb2_kernel<8>, C::kSmemBytes);
   if (st != HPCX_OK) return st;
   const unsigned ncta = (unsigned)(sp.ntx * sp.nty * (sp.zs + (zend2 > zbeg2 ? 1 : 0)));
+  if (peer) {
+    st = ensure_dyn_smem(ctx, (const void *)jacobi7_tb2_peer_kernel<8>, C::kSmemBytes);
+    if (st != HPCX_OK) return st;
+    jacobi7_tb2_peer_kernel<8><<<ncta, 256, C::kSmemBytes, s>>>(*hi, *lo, (float *)dst, geom_of(g), sp, *peer,
+                                                                 1.0f / 6.0f);
+    return after_launch(ctx, "jacobi7_tb2_peer_kernel");
+  }
   jacobi7_tb2_kernel<8><<<ncta, 256, C::kSmemBytes, s>>>(*hi, *lo, (float *)dst, geom_of(g), sp, 1.0f / 6.0f);
   return after_launch(ctx, "jacobi7_tb2_kernel");
 }
@@ -948,6 +1019,7 @@ hpcx_status preload_stencil_kernels(hpcx_ctx ctx) {
   HPCX_CUDA(ctx, cudaFuncGetAttributes(&a, (const void *)jacobi7_direct_kernel<float>));
   HPCX_CUDA(ctx, cudaFuncGetAttributes(&a, (const void *)jacobi7_direct_kernel<double>));
   if (hpcx_status st = ensure_dyn_smem(ctx, (const void *)jacobi7_ring_kernel<kJacobiStages>, JacobiCfg<kJacobiStages>::kSmemBytes)) return st;
+  if (hpcx_status st = ensure_dyn_smem(ctx, (const void *)jacobi7_tb2_peer_kernel<8>, JacobiTBCfg<8>::kSmemBytes)) return st;
   return ensure_dyn_smem(ctx, (const void *)jacobi7_tb2_kernel<8>, JacobiTBCfg<8>::kSmemBytes);
 }
 
@@ -964,6 +1036,16 @@ hpcx_status jacobi7_tb2_launch(hpcx_grid_s *g, void *src, void *dst, int zsplit,
   if (!jacobi7_tb2_supported(g))
     return fail(g->ctx, HPCX_UNSUPPORTED, "the temporally blocked Jacobi needs fp32 and a tensor-map driver");
   return launch_jacobi_tb2(g, src, dst, zsplit, zbeg, zend, nb_lo, nb_hi, s, zbeg2, zend2);
+}
+
+// The same over a whole thin slab with the halo transport inside the kernel
+// (jacobi7_tb2_peer_kernel).  Needs at least two planes.
+hpcx_status jacobi7_tb2_peer_launch(hpcx_grid_s *g, void *src, void *dst, int zsplit, const JacobiPeer &peer,
+                                    cudaStream_t s) {
+  if (!jacobi7_tb2_supported(g) || g->n[0] < 2)
+    return fail(g->ctx, HPCX_UNSUPPORTED, "the fused two-sweep transport needs fp32, a tensor-map driver and two planes");
+  return launch_jacobi_tb2(g, src, dst, zsplit, 0, g->n[0], peer.ghost_lo != nullptr, peer.ghost_hi != nullptr, s, 0, 0,
+                           &peer);
 }
 }  // namespace hpcx
 

@@ -84,7 +84,9 @@ def main():
             ((8 * world, 20, 140), 6, 2, 0), ((3 * world - 1, 30, 260), 5, 2, 0),
             ((5 * world, 15, 128), 4, 3, 0), ((3 * world, 14, 40), 1, 2, 0),
             ((8 * world, 20, 140), 6, 2, 1), ((3 * world - 1, 30, 260), 5, 2, 1),
-            ((5 * world, 15, 128), 4, 3, 1), ((2 * world, 33, 129), 7, 2, 1), ((40 * world, 64, 256), 8, 2, 1)):
+            ((5 * world, 15, 128), 4, 3, 1), ((2 * world, 33, 129), 7, 2, 1), ((40 * world, 64, 256), 8, 2, 1),
+            # more than 128 planes per rank: the push-kernel transport (thinner slabs push from inside the pass kernel)
+            ((150 * world, 16, 130), 6, 2, 1)):
         ext = (nz + 2 * gw, ny + 2 * gw, nx + 2 * gw)
         full = oracle.fill(ext[0] * ext[1] * ext[2], 11, np.float32)
         b = hp.partition_slabs(nz, world)
