@@ -1,6 +1,7 @@
-#!/usr/bin/env python
-"""A/B sweep of the STREAM kernel's create-time knobs (tile_nnz, short_row_max) on the three SpMV
-configs at full size.  Run on the GPU box: python scripts/spmv_sweep.py > gpurun_out/<tag>/sweep.txt"""
+"""Every SpMV kernel of the library on the three matrix shapes of BASELINE.json at full size
+(C2 Laplacian 8192^2 fp64, C4 27-point 256^3 fp64, C5 R-MAT scale 24 fp32): create time, time per
+product, effective GB/s on the algorithmic bytes of SURVEY.md 8(d).  SURVEY.md 8 a9 asks for the
+row-binned and SELL-C-sigma variants; this is where their numbers come from (profiles/*_spmv_kernels.txt)."""
 import os
 import sys
 import time
@@ -8,67 +9,70 @@ import time
 import numpy as np
 import torch
 
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.abspath(os.path.join(os.path.dirname(__file__), ".."))
 sys.path.insert(0, ROOT)
 import libhpc_b200 as hp  # noqa: E402
 from libhpc_b200 import synth  # noqa: E402
 
 ctx = hp.Context(0)
-stream = torch.cuda.Stream()
-which = sys.argv[1:] or ["c2", "c4", "c5"]
+PEAK = 6543.7
+if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")):
+    import json
+    PEAK = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))).get("hbm_gbs", PEAK))
 
 
-def timeit(D, x, y, reps=20):
-    with torch.cuda.stream(stream):
-        for _ in range(3):
-            D.spmv(x, y, stream)
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record(stream)
-        for _ in range(reps):
-            D.spmv(x, y, stream)
-        e1.record(stream)
+def bench(name, make, n, ncols, dtype, nbytes, variants):
+    x = torch.from_numpy(synth.field(42, ncols, dtype)).cuda()
+    y = torch.empty(n, dtype=x.dtype, device="cuda")
+    ref = None
+    for label, kw in variants:
+        t = time.time()
+        try:
+            D = make(**kw)
+        except Exception as e:  # a variant the library refuses for this shape
+            print(f"{name:4s} {label:28s} refused: {str(e)[:80]}", flush=True)
+            continue
+        tc = time.time() - t
+        stream = torch.cuda.Stream()
         torch.cuda.synchronize()
-    return e0.elapsed_time(e1) / reps
-
-
-def sweep(name, make, dtype, combos):
-    nrows = None
-    for tile, srm in combos:
-        D = make(tile, srm)
-        nrows = D.nrows
-        tdt = torch.float64 if dtype == np.float64 else torch.float32
-        x = torch.empty(D.ncols, dtype=tdt, device="cuda")
-        hp.synth_field(ctx, 42, D.ncols, x, dtype)
-        y = torch.empty(nrows, dtype=tdt, device="cuda")
-        ms = timeit(D, x, y)
-        gbs = D.algorithmic_bytes() / ms / 1e6
-        bl = D.rowblocks()
-        lanes, cnt = np.unique(bl[:, 3], return_counts=True)
-        print(f"{name} tile={tile} short_row_max={srm}: {ms:.4f} ms  {gbs:.0f} GB/s  blocks={len(bl)} "
-              f"lanes={dict(zip(lanes.tolist(), cnt.tolist()))} checksum={float(y.double().abs().sum()):.6e}",
-              flush=True)
+        with torch.cuda.stream(stream):
+            for _ in range(3):
+                D.spmv(x, y, stream)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            for _ in range(20):
+                D.spmv(x, y, stream)
+            e1.record(stream)
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / 20
+        out = y.cpu().numpy().astype(np.float64)
+        if ref is None:
+            ref = out
+        err = np.abs(out - ref).max() / max(np.abs(ref).max(), 1e-300)
+        print(f"{name:4s} {label:28s} create {tc:6.2f} s  {ms:7.3f} ms  {nbytes / ms / 1e6:7.0f} GB/s  "
+              f"{nbytes / ms / 1e6 / PEAK:5.3f} of HBM  max diff vs first {err:.1e}", flush=True)
         D.destroy()
 
 
-if "c2" in which:
-    t = time.time()
-    rp, col, val = synth.laplace2d_big(8192, 8192)
-    A = hp.CsrMatrix(rp, col, val)
-    print(f"c2 built in {time.time() - t:.1f}s", flush=True)
-    sweep("c2", lambda tile, srm: hp.DeviceCsr(ctx, A, tile_nnz=tile, short_row_max=srm), np.float64,
-          [(1024, 48), (2048, 48), (4096, 48)])
-    del A, rp, col, val
-if "c4" in which:
-    t = time.time()
-    L = synth.op27_slab_local(256, 0, 256)
-    A = hp.CsrMatrix(L["local_row_ptr"].astype(np.int32), L["local_col"], L["values"])
-    print(f"c4 built in {time.time() - t:.1f}s", flush=True)
-    sweep("c4", lambda tile, srm: hp.DeviceCsr(ctx, A, tile_nnz=tile, short_row_max=srm), np.float64,
-          [(2048, 8), (1024, 48), (2048, 48), (4096, 48)])
-    del A, L
-if "c5" in which:
-    arrs = hp.synth_rmat_csr(ctx, 24, 16, 24, 4)
-    sweep("c5", lambda tile, srm: hp.DeviceCsr.from_device_arrays(ctx, arrs, tile_nnz=tile, short_row_max=srm),
-          np.float32, [(2048, 8), (1024, 48), (2048, 48), (4096, 48), (2048, 16), (2048, 128), (4096, 128)])
-    arrs.destroy()
-ctx.close()
+GENERIC = [("STREAM", dict(kernel=hp.SPMV_STREAM)), ("VECTOR", dict(kernel=hp.SPMV_VECTOR)),
+           ("SELL-32-1024", dict(kernel=hp.SPMV_SELL)), ("SELL-32-1 (unsorted)", dict(kernel=hp.SPMV_SELL, sell_sigma=1))]
+
+# C2
+rp, col, val = synth.laplace2d(8192, 8192)
+A = hp.CsrMatrix(rp, col, val)
+bench("C2", lambda **kw: hp.DeviceCsr(ctx, A, **kw), A.nrows, A.nrows, np.float64, 12 * A.nnz + 20 * A.nrows + 4, GENERIC)
+del A, rp, col, val
+# C4
+rp, col, val = synth.op27(256)
+A = hp.CsrMatrix(rp, col, val)
+bench("C4", lambda **kw: hp.DeviceCsr(ctx, A, **kw), A.nrows, A.nrows, np.float64, 12 * A.nnz + 20 * A.nrows + 4, GENERIC)
+del A, rp, col, val
+# C5 (assembled on the device; SELL is built from the downloaded arrays)
+arrs = hp.synth_rmat_csr(ctx, 24, 16, 24, 4)
+n = 1 << 24
+rp, col, val = arrs.download()
+nnz = len(col)
+A = hp.CsrMatrix(rp, col, val, ncols=n)
+variants = GENERIC[:2] + [("HUB", dict(kernel=hp.SPMV_HUB)), ("AUTO", dict(kernel=hp.SPMV_AUTO))] + \
+    [(f"SELL-32-{s}", dict(kernel=hp.SPMV_SELL, sell_sigma=s)) for s in (1024, 65536, 1 << 24)]
+bench("C5", lambda **kw: hp.DeviceCsr(ctx, A, **kw), n, n, np.float32, 8 * nnz + 12 * n + 4, variants)
