@@ -68,7 +68,11 @@ hpcx_status hpcx_init(int32_t device, hpcx_ctx *out) {
                 "libhpcx is built for sm_100a only; device is sm_" + std::to_string(prop.major) +
                     std::to_string(prop.minor));
   HPCX_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->compute, cudaStreamNonBlocking));
-  HPCX_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->comm, cudaStreamNonBlocking));
+  // halo exchange stream: highest priority, so that the boundary strips and the NCCL kernels of a
+  // distributed sweep get SM slots ahead of the interior kernel they run beside (dist.cu)
+  int prio_lo = 0, prio_hi = 0;
+  HPCX_CUDA(ctx, cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+  HPCX_CUDA(ctx, cudaStreamCreateWithPriority(&ctx->comm, cudaStreamNonBlocking, prio_hi));
   HPCX_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->copy_in, cudaStreamNonBlocking));
   HPCX_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->copy_out, cudaStreamNonBlocking));
   for (auto &ev : ctx->ev) HPCX_CUDA(ctx, cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));

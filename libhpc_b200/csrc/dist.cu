@@ -397,9 +397,7 @@ hpcx_status hpcx_stencil_dist_plan(hpcx_ctx ctx, hpcx_grid in, hpcx_grid out,
     p->in = in;
     p->out = out;
     p->st = *st;
-    cudaEventCreateWithFlags(&p->ev_bnd, cudaEventDisableTiming);
-    cudaEventCreateWithFlags(&p->ev_recv, cudaEventDisableTiming);
-    cudaEventCreateWithFlags(&p->ev_start, cudaEventDisableTiming);
+    p->create_events();
     *out_plan = p;
     return HPCX_OK;
   }
@@ -446,10 +444,9 @@ hpcx_status hpcx_stencil_dist_plan(hpcx_ctx ctx, hpcx_grid in, hpcx_grid out,
   p->st = *st;
   p->transport = transport;
   if (const char *g = getenv("HPCX_NCCL_GRAPHS")) p->graphs_ok = atoi(g) != 0;  // 0: replay nothing, launch every call eagerly
-  cudaError_t e = cudaEventCreateWithFlags(&p->ev_bnd, cudaEventDisableTiming);
-  if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->ev_recv, cudaEventDisableTiming);
-  if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->ev_start, cudaEventDisableTiming);
+  cudaError_t e = p->create_events();
   if (e != cudaSuccess) {
+    p->destroy_events();
     delete p;
     return fail(ctx, HPCX_CUDA_ERROR, std::string("cudaEventCreate: ") + cudaGetErrorString(e));
   }
@@ -544,14 +541,10 @@ hpcx_status stencil_peer_sweep(hpcx_halo_plan p, int32_t steps, cudaStream_t cs,
   return HPCX_OK;
 }
 }  // namespace hpcx
-extern "C" {
-
-}  // extern "C"
 // Everything one NCCL-transport call puts on the two streams (no host synchronisation inside, so the
 // sequence can be captured into a graph): the initial ghost exchange of `in`, then per pass
-//   compute stream: [wait ghosts of src] boundary planes z = 0, n-1  -> record ev_bnd
-//   comm stream   : [wait ev_bnd] send dst boundary planes / receive dst ghost planes
-//   compute stream: interior planes 1 .. n-2 (overlaps the exchange)
+//   comm stream   : boundary planes z = 0, n-1, then send dst boundary planes / receive dst ghost planes
+//   compute stream: interior planes 1 .. n-2 (beside both)
 // HPCX_VARIANT_TEMPORAL runs steps/2 two-sweep passes the same way with TWO planes per side (the
 // neighbour's boundary plane is advanced redundantly on this rank), then one single sweep when
 // steps is odd: the bytes exchanged per sweep are unchanged, the messages per sweep halve.
@@ -566,7 +559,6 @@ static hpcx_status nccl_sweeps_enqueue(hpcx_halo_plan p, int32_t steps, cudaStre
   HPCX_CUDA(ctx, cudaStreamWaitEvent(ms, p->ev_start, 0));
   rc = exchange_planes(g, p->in->dev, ms, (p->st.variant == HPCX_VARIANT_TEMPORAL && steps >= 2) ? 2 : 1);
   if (rc != HPCX_OK) return rc;
-  HPCX_CUDA(ctx, cudaEventRecord(p->ev_recv, ms));
   // A pass advances the slab by w sweeps (w = 2: the temporally blocked kernel) and needs w valid
   // ghost planes per side of its source; the exchange after a pass carries the width the NEXT pass
   // reads.  Boundary = the w planes next to each z neighbour.
@@ -574,51 +566,59 @@ static hpcx_status nccl_sweeps_enqueue(hpcx_halo_plan p, int32_t steps, cudaStre
   const bool nb_lo = ctx->rank > 0, nb_hi = ctx->rank + 1 < ctx->nranks;
   const int passes = temporal ? steps / 2 + (steps & 1) : steps;
   void *src = p->in->dev, *dst = p->out->dev;
+  // The boundary strips run on the COMM stream (high priority), ahead of the exchange they feed,
+  // while the compute stream goes straight from one interior launch to the next: the interior of
+  // pass t needs the boundary strips of pass t-1 (ev_bnd[(t-1) & 1]) but neither the strips nor the
+  // exchange of pass t, and the strips of pass t need the interior of pass t-1 (ev_int) and the
+  // exchange of pass t-1 (stream order).  With the strips in front of the interior on one stream
+  // (round 1) every sweep paid for their launch, their 128-CTA tail and the hand-over twice.
   for (int t = 0; t < passes; ++t) {
     const bool two = temporal && t < steps / 2;
     const int64_t w = two ? 2 : 1;
     const int64_t lo_end = std::min<int64_t>(w, nz), hi_beg = std::max<int64_t>(lo_end, nz - w);
-    auto launch = [&](int64_t zb, int64_t ze, int zsplit) -> hpcx_status {
+    auto launch = [&](int64_t zb, int64_t ze, int zsplit, cudaStream_t st) -> hpcx_status {
       if (ze <= zb) return HPCX_OK;
-      if (two) return jacobi7_tb2_launch(g, src, dst, zsplit, zb, ze, nb_lo, nb_hi, cs);
-      return jacobi7_launch(g, src, dst, temporal ? HPCX_VARIANT_TMA : p->st.variant, zsplit, zb, ze, cs, nullptr);
+      if (two) return jacobi7_tb2_launch(g, src, dst, zsplit, zb, ze, nb_lo, nb_hi, st);
+      return jacobi7_launch(g, src, dst, temporal ? HPCX_VARIANT_TMA : p->st.variant, zsplit, zb, ze, st, nullptr);
     };
-    HPCX_CUDA(ctx, cudaStreamWaitEvent(cs, p->ev_recv, 0));
+    if (t > 0) HPCX_CUDA(ctx, cudaStreamWaitEvent(ms, p->ev_int, 0));
     nvtxRangePushA("sweep: boundary planes");
     if (two) {  // both boundary strips in one launch
-      rc = jacobi7_tb2_launch(g, src, dst, 1, 0, lo_end, nb_lo, nb_hi, cs, hi_beg, nz);
+      rc = jacobi7_tb2_launch(g, src, dst, 1, 0, lo_end, nb_lo, nb_hi, ms, hi_beg, nz);
     } else {
-      rc = launch(0, lo_end, 1);
-      if (rc == HPCX_OK) rc = launch(hi_beg, nz, 1);
+      rc = launch(0, lo_end, 1, ms);
+      if (rc == HPCX_OK) rc = launch(hi_beg, nz, 1, ms);
     }
     nvtxRangePop();
     if (rc != HPCX_OK) return rc;
+    HPCX_CUDA(ctx, cudaEventRecord(p->ev_bnd[t & 1], ms));
     if (t + 1 < passes) {
       HPCX_RANGE("sweep: ghost-plane exchange (NCCL send/recv)");
       const int64_t wnext = (temporal && t + 1 < steps / 2) ? 2 : 1;
-      HPCX_CUDA(ctx, cudaEventRecord(p->ev_bnd, cs));
-      HPCX_CUDA(ctx, cudaStreamWaitEvent(ms, p->ev_bnd, 0));
       rc = exchange_planes(g, dst, ms, wnext);
       if (rc != HPCX_OK) return rc;
-      HPCX_CUDA(ctx, cudaEventRecord(p->ev_recv, ms));
     }
     {
       HPCX_RANGE("sweep: interior planes");
-      rc = launch(lo_end, hi_beg, temporal ? (two ? p->st.zsplit : 0) : p->st.zsplit);
+      if (t > 0) HPCX_CUDA(ctx, cudaStreamWaitEvent(cs, p->ev_bnd[(t - 1) & 1], 0));
+      rc = launch(lo_end, hi_beg, temporal ? (two ? p->st.zsplit : 0) : p->st.zsplit, cs);
+      if (rc != HPCX_OK) return rc;
+      if (t + 1 < passes) HPCX_CUDA(ctx, cudaEventRecord(p->ev_int, cs));
     }
-    if (rc != HPCX_OK) return rc;
     std::swap(src, dst);
   }
+  // the caller's stream ends behind the strips of the last pass
+  HPCX_CUDA(ctx, cudaStreamWaitEvent(cs, p->ev_bnd[(passes - 1) & 1], 0));
   return HPCX_OK;
 }
 
 extern "C" {
 
 // Per step t (src -> dst):
-//   compute stream: [wait ghosts of src] boundary planes z = 0, n-1  -> record ev_bnd
-//   comm stream   : [wait ev_bnd] send dst boundary planes / receive dst ghost planes
-//   compute stream: interior planes 1 .. n-2 (overlaps the exchange)
-// The ghost planes a step needs were produced by the previous step's exchange.
+//   comm stream   : [wait interior of t-1] boundary planes z = 0, n-1 -> ev_bnd[t & 1];
+//                   send dst boundary planes / receive dst ghost planes
+//   compute stream: [wait boundary planes of t-1] interior planes 1 .. n-2 -> ev_int
+// The ghost planes a step needs were produced by the previous step's exchange (stream order).
 // HPCX_VARIANT_TEMPORAL runs steps/2 two-sweep passes the same way with TWO planes per side (the
 // neighbour's boundary plane is advanced redundantly on this rank), then one single sweep when
 // steps is odd: the bytes exchanged per sweep are unchanged, the messages per sweep halve.
@@ -734,9 +734,7 @@ hpcx_status hpcx_stencil_dist_destroy(hpcx_halo_plan p) {
   cudaDeviceSynchronize();
   const hpcx_status pending = comm_check(p->ctx);  // a timed-out wait of an asynchronous sweep surfaces here
   close_peers(p);
-  cudaEventDestroy(p->ev_bnd);
-  cudaEventDestroy(p->ev_recv);
-  cudaEventDestroy(p->ev_start);
+  p->destroy_events();
   for (auto &e : p->graphs) cudaGraphExecDestroy(e.exec);
   delete p;
   return pending;

@@ -9,7 +9,18 @@ struct hpcx_halo_plan_s {
   hpcx_grid in = nullptr, out = nullptr;
   hpcx_stencil_desc st{};
   int transport = 0;
-  cudaEvent_t ev_bnd = nullptr, ev_recv = nullptr, ev_start = nullptr;
+  // ev_bnd[pass & 1]: boundary strips of a pass done; ev_int: interior of a pass done
+  cudaEvent_t ev_bnd[2] = {nullptr, nullptr}, ev_recv = nullptr, ev_start = nullptr, ev_int = nullptr;
+  cudaError_t create_events() {
+    cudaError_t e = cudaSuccess;
+    for (cudaEvent_t *ev : {&ev_bnd[0], &ev_bnd[1], &ev_recv, &ev_start, &ev_int})
+      if (e == cudaSuccess) e = cudaEventCreateWithFlags(ev, cudaEventDisableTiming);
+    return e;
+  }
+  void destroy_events() {
+    for (cudaEvent_t ev : {ev_bnd[0], ev_bnd[1], ev_recv, ev_start, ev_int})
+      if (ev) cudaEventDestroy(ev);
+  }
   // transport 1 (peer stores): neighbour side 0 = rank-1, 1 = rank+1
   uint32_t *flags = nullptr;          // local block: [0],[1] flags, [4],[5] counters, [8] push counter
   void *buf[2] = {nullptr, nullptr};  // this rank's two grid buffers at plan time (A = in, B = out)

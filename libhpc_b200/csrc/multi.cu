@@ -81,9 +81,7 @@ void free_plans(hpcx_multi_grid G) {
       hpcx_halo_plan p = G->plans[i];
       cudaDeviceSynchronize();
       cudaFree(p->flags);  // peer pointers are not IPC windows here: nothing to close
-      cudaEventDestroy(p->ev_bnd);
-      cudaEventDestroy(p->ev_recv);
-      cudaEventDestroy(p->ev_start);
+      p->destroy_events();
       for (auto &e : p->graphs) cudaGraphExecDestroy(e.exec);
       delete p;
     }
@@ -454,9 +452,7 @@ hpcx_status hpcx_multi_stencil_sweep(hpcx_multi_grid in, hpcx_multi_grid out, co
       p->out = out->g[r];
       p->st = *st;
       p->transport = 1;
-      cudaEventCreateWithFlags(&p->ev_bnd, cudaEventDisableTiming);
-      cudaEventCreateWithFlags(&p->ev_recv, cudaEventDisableTiming);
-      cudaEventCreateWithFlags(&p->ev_start, cudaEventDisableTiming);
+      p->create_events();
       HPCX_MTRY(m, r, plan_prepare(p));
     }
     for (int r = 0; r < P; ++r)
