@@ -12,8 +12,10 @@ NCCL send/recv transport is timed beside it as an extra).
 
 A step is one product.  `value` = effective GB/s = algorithmic bytes (12 B/nnz + 20 B/row,
 SURVEY.md §8d) of all ranks / max-over-ranks device time, operands resident in HBM.
-`e2e` is the same metric through the reference-facing host call (hpcx_spmv with HOST x and
-y: H2D of x and D2H of y inside the timed region, matrix resident as in any iterative use).
+`e2e` is the same metric through the reference-facing host call (hpcx_spmv with HOST x and y at
+N = 1, hpcx_spmv_dist_host per rank at N > 1: H2D of x and D2H of y pipelined against the product
+inside the call and inside the timed region, matrix resident as in any iterative use), with the
+time of the same copies alone (`pcie_copies_only_ms`) beside it.
 The matrix (4.3 GB) is far larger than L2 (126 MB), so no explicit flush is needed.
 
 --impl reference times the CPU restatement of the path (oracle/, OpenMP, every core of the
@@ -278,8 +280,43 @@ def dist_parity_check(ctx, torch, dist, world, rank, hp, hd, synth):
         t = torch.tensor([1.0 if same else 0.0], device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MIN)
         verdict[name] = "ok" if float(t.item()) == 1.0 else "MISMATCH"
+    # R0 box sweeps over y-slabs (ghost rows) and x-slabs (ghost columns, packed faces): every rank's
+    # block against the single-GPU sweep of the global grid
+    for kind, blocks, name in ((hp.STENCIL_BOX_Y, (world, 1), "box_y_yslabs"), (hp.STENCIL_BOX_X, (1, world), "box_x_xslabs")):
+        py, px = blocks
+        ny, nx = 40 * py, 64 * px
+        full = synth.field(5, (ny + 16) * (nx + 16), np.float32)
+        ga, gb = hp.DeviceGrid(ctx, (ny, nx), np.float32, 8), hp.DeviceGrid(ctx, (ny, nx), np.float32, 0)
+        ga.upload(full)
+        hp.stencil_sweep(ga, gb, kind, radius=8)
+        want = gb.download().reshape(ny, nx)
+        ga.destroy()
+        gb.destroy()
+        ry, rx = rank // px, rank % px
+        y0, y1, x0, x1 = ny * ry // py, ny * (ry + 1) // py, nx * rx // px, nx * (rx + 1) // px
+        block = np.ascontiguousarray(full.reshape(ny + 16, nx + 16)[y0:y1 + 16, x0:x1 + 16]).copy()
+        if ry > 0:
+            block[:8] = np.nan  # must come through the exchange
+        if ry < py - 1:
+            block[-8:] = np.nan
+        if rx > 0:
+            block[:, :8] = np.nan
+        if rx < px - 1:
+            block[:, -8:] = np.nan
+        sa, sb = hp.DeviceGrid(ctx, (y1 - y0, x1 - x0), np.float32, 8), hp.DeviceGrid(ctx, (y1 - y0, x1 - x0), np.float32, 0)
+        sa.upload(block.ravel())
+        plan = hd.HaloPlan(ctx, sa, sb, kind, radius=8, blocks=blocks)
+        plan.sweep(1)
+        out = sb.download().reshape(y1 - y0, x1 - x0)
+        same = np.array_equal(np.ascontiguousarray(out).view(np.uint32), np.ascontiguousarray(want[y0:y1, x0:x1]).view(np.uint32))
+        plan.destroy()
+        sa.destroy()
+        sb.destroy()
+        t = torch.tensor([1.0 if same else 0.0], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MIN)
+        verdict[name] = "ok" if float(t.item()) == 1.0 else "MISMATCH"
     if any(v != "ok" for v in verdict.values()):
-        raise SystemExit(f"[rank {rank}] bench.py: distributed Jacobi differs from the single-GPU sweep: {verdict}")
+        raise SystemExit(f"[rank {rank}] bench.py: a distributed sweep differs from the single-GPU sweep: {verdict}")
     return verdict
 
 
@@ -685,6 +722,25 @@ def stencil_extra(args, ctx, torch, stream, world, rank, barrier, max_over_ranks
             plan.destroy()
         ga.destroy()
         gb.destroy()
+    if world > 1:
+        # R0 across GPUs, weak: every rank owns an 8192 x 8192 block of the reference's blur grid.
+        # y-slabs (world x 1 blocks): the y sweep trades 8 ghost rows; x-slabs (1 x world blocks): the
+        # x sweep trades 8 ghost columns as packed faces.  The other sweep of each split needs no
+        # exchange and runs at the one-GPU rate.
+        m = 8192
+        a = hp.DeviceGrid(ctx, (m, m), np.float32, 8)
+        b = hp.DeviceGrid(ctx, (m, m), np.float32, 0)
+        a.upload(synth.field(3, (m + 16) ** 2, np.float32, first=rank))
+        for kind, name, blocks, what in ((hp.STENCIL_BOX_Y, "box_y_yslabs", (world, 1), "8 ghost rows per side (NCCL, in place)"),
+                                         (hp.STENCIL_BOX_X, "box_x_xslabs", (1, world), "8 ghost columns per side (packed faces, NCCL)")):
+            plan = hd.HaloPlan(ctx, a, b, kind, radius=8, blocks=blocks)
+            dt, launches = timed(lambda: [plan.sweep(1, stream) for _ in range(20)])
+            out[f"r0_{name}_8192sq_per_gpu_fp32"] = entry(m * m * world * 40, dt, launches, ms_per_sweep=dt / 40 * 1e3,
+                                                          exchange=what, blocks=list(blocks))
+            summary[f"r0_{name}"] = round(m * m * world * 40 / dt / 1e9, 1)
+            plan.destroy()
+        a.destroy()
+        b.destroy()
     if world == 1:
         m = 8192
         a = hp.DeviceGrid(ctx, (m, m), np.float32, 8)

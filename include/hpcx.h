@@ -406,6 +406,19 @@ typedef struct hpcx_halo_plan_s *hpcx_halo_plan;
 HPCX_API hpcx_status hpcx_stencil_dist_plan(hpcx_ctx ctx, hpcx_grid in, hpcx_grid out,
                                             const hpcx_stencil_desc *st, int32_t transport,
                                             hpcx_halo_plan *out_plan);
+/* BOX_X / BOX_Y over a 2-D BLOCK split: the ranks form a py x px grid (py * px == communicator
+ * size, rank = ry * px + rx), every rank owns one block of the global 2-D grid as a grid pair whose
+ * ghost width covers `radius` on all four sides; blocks of one block row share their y extent,
+ * blocks of one block column their x extent.  BOX_Y trades `radius` ghost rows with ranks
+ * rank -/+ px (contiguous rows, in place); BOX_X trades `radius` ghost columns with ranks
+ * rank -/+ 1 of the same block row: the strided faces are packed and unpacked on the device
+ * (hpcx_grid_pack_face's kernel) around one grouped NCCL send/recv.  Either exchange runs on the
+ * comm stream beside the part of the block that needs no ghosts; the two boundary strips follow.
+ * px == 1 is the y-slab split of hpcx_stencil_dist_plan.  Results are bit-identical to the
+ * single-GPU sweep of the global grid.  Collective over the communicator. */
+HPCX_API hpcx_status hpcx_stencil_dist_plan_blocks(hpcx_ctx ctx, hpcx_grid in, hpcx_grid out,
+                                                   const hpcx_stencil_desc *st, int32_t py, int32_t px,
+                                                   hpcx_halo_plan *out_plan);
 HPCX_API hpcx_status hpcx_stencil_dist_sweep(hpcx_halo_plan plan, int32_t steps, void *stream);
 HPCX_API hpcx_status hpcx_stencil_dist_destroy(hpcx_halo_plan plan);
 

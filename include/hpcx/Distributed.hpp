@@ -103,6 +103,33 @@ class HaloPlan {
   hpcx_halo_plan plan_ = nullptr;
 };
 
+// The reference's box sweeps over a py x px grid of 2-D blocks (px == 1: y-slabs), one block per
+// rank, rank = ry * px + rx; ghost rows / columns come from the neighbouring blocks
+// (hpcx_stencil_dist_plan_blocks).  One sweep in -> out per call.
+template <typename T, std::size_t Lo, std::size_t Hi, std::size_t Lo2, std::size_t Hi2>
+class BoxHaloPlan {
+ public:
+  BoxHaloPlan(DeviceGrid<2, T, Lo, Hi> &in, DeviceGrid<2, T, Lo2, Hi2> &out, Box1D box, int py, int px)
+      : ctx_(in.context()) {
+    if (box.axis != 0 && box.axis != 1)
+      hpcx::throwStatus(HPCX_INVALID_ARG, "Box1D axis must be 0 or 1", __FILE__, __LINE__);
+    hpcx_stencil_desc st{};
+    st.kind = box.axis == 1 ? HPCX_STENCIL_BOX_X : HPCX_STENCIL_BOX_Y;
+    st.radius = box.radius;
+    HPCX_CHECK(ctx_, hpcx_stencil_dist_plan_blocks(ctx_, in.handle(), out.handle(), &st, py, px, &plan_));
+  }
+  ~BoxHaloPlan() {
+    if (plan_) hpcx_stencil_dist_destroy(plan_);
+  }
+  BoxHaloPlan(const BoxHaloPlan &) = delete;
+  BoxHaloPlan &operator=(const BoxHaloPlan &) = delete;
+  void sweep(void *stream = nullptr) { HPCX_CHECK(ctx_, hpcx_stencil_dist_sweep(plan_, 1, stream)); }
+
+ private:
+  hpcx_ctx ctx_ = nullptr;
+  hpcx_halo_plan plan_ = nullptr;
+};
+
 }  // namespace hpc
 
 namespace sparse {

@@ -125,6 +125,7 @@ PROTOTYPES = {
     "hpcx_comm_set_timeout": (_i32, [_vp, _i64]),
     "hpcx_comm_check": (_i32, [_vp]),
     "hpcx_stencil_dist_plan": (_i32, [_vp, _vp, _vp, _P(StencilDesc), _i32, _P(_vp)]),
+    "hpcx_stencil_dist_plan_blocks": (_i32, [_vp, _vp, _vp, _P(StencilDesc), _i32, _i32, _P(_vp)]),
     "hpcx_stencil_dist_sweep": (_i32, [_vp, _i32, _vp]),
     "hpcx_stencil_dist_destroy": (_i32, [_vp]),
     "hpcx_csr_set_halo": (_i32, [_vp, _i64, _i64, _vp, _vp, _vp, _vp]),

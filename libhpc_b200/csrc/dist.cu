@@ -22,6 +22,8 @@ hpcx_status allreduce_sum(hpcx_ctx ctx, void *buf, size_t count, int dtype, cuda
 bool jacobi7_tb2_supported(hpcx_grid_s *g);
 hpcx_status box_launch_rows(hpcx_grid_s *in, hpcx_grid_s *out, const hpcx_stencil_desc *st, int64_t y0, int64_t y1,
                             cudaStream_t s);
+hpcx_status box_launch_tile(hpcx_grid_s *in, hpcx_grid_s *out, const hpcx_stencil_desc *st, int64_t y0, int64_t y1,
+                            int64_t x0, int64_t x1, cudaStream_t s);
 hpcx_status jacobi7_tb2_launch(hpcx_grid_s *g, void *src, void *dst, int zsplit, int64_t zbeg, int64_t zend,
                                bool nb_lo, bool nb_hi, cudaStream_t s, int64_t zbeg2 = 0, int64_t zend2 = 0);
 hpcx_status jacobi7_tb2_peer_launch(hpcx_grid_s *g, void *src, void *dst, int zsplit, const JacobiPeer &peer,
@@ -100,7 +102,7 @@ namespace {
 
 // Exchange w ghost planes per side of buffer `buf` (device layout of grid g) with the z
 // neighbours.  Planes are contiguous in the device layout, so nothing is packed.
-hpcx_status exchange_planes(hpcx_grid g, void *buf, cudaStream_t s, int64_t w = 1) {
+hpcx_status exchange_planes(hpcx_grid g, void *buf, cudaStream_t s, int64_t w = 1, int stride = 1) {
   hpcx_ctx ctx = g->ctx;
   if (ctx->nranks <= 1) return HPCX_OK;
   // slices of the split axis: z planes of a 3-D grid, rows of a 2-D grid (both contiguous)
@@ -110,7 +112,8 @@ hpcx_status exchange_planes(hpcx_grid g, void *buf, cudaStream_t s, int64_t w = 
   char *base = static_cast<char *>(buf);
   auto at = [&](int64_t z) { return base + (z + glo) * plane * g->es; };
   const ncclDataType_t ty = nccl_type(g->desc.dtype);
-  const int lo = ctx->rank - 1, hi = ctx->rank + 1;
+  // stride > 1: rows of a py x px block grid, neighbours are `stride` = px ranks away
+  const int lo = ctx->rank - stride, hi = ctx->rank + stride;
   HPCX_NCCL(ctx, g_nccl.GroupStart());
   if (lo >= 0) {
     HPCX_NCCL(ctx, g_nccl.Send(at(0), (size_t)(w * plane), ty, lo, comm_of(ctx), s));
@@ -121,6 +124,34 @@ hpcx_status exchange_planes(hpcx_grid g, void *buf, cudaStream_t s, int64_t w = 
     HPCX_NCCL(ctx, g_nccl.Recv(at(nown), (size_t)(w * plane), ty, hi, comm_of(ctx), s));
   }
   HPCX_NCCL(ctx, g_nccl.GroupEnd());
+  return HPCX_OK;
+}
+
+// x faces of a block (2-D grids, block split): the `r` owned columns next to each x neighbour are
+// packed (face_copy_kernel, a11), exchanged with rank -1 / +1 of the same block row, and unpacked
+// into the ghost columns.  All on stream s.
+hpcx_status exchange_cols(hpcx_halo_plan p, cudaStream_t s) {
+  hpcx_ctx ctx = p->ctx;
+  hpcx_grid g = p->in;
+  const int r = p->st.radius, rx = ctx->rank % p->px;
+  const bool has[2] = {rx > 0, rx + 1 < p->px};
+  const int peer[2] = {ctx->rank - 1, ctx->rank + 1};
+  int64_t elems = 0;
+  if (hpcx_status st = hpcx_grid_face_elems(g, 1, r, &elems)) return st;
+  for (int side = 0; side < 2; ++side)
+    if (has[side])
+      if (hpcx_status st = hpcx_grid_pack_face(g, 1, side, r, p->face_send[side], HPCX_MEM_DEVICE, s)) return st;
+  const ncclDataType_t ty = nccl_type(g->desc.dtype);
+  HPCX_NCCL(ctx, g_nccl.GroupStart());
+  for (int side = 0; side < 2; ++side)
+    if (has[side]) {
+      HPCX_NCCL(ctx, g_nccl.Send(p->face_send[side], (size_t)elems, ty, peer[side], comm_of(ctx), s));
+      HPCX_NCCL(ctx, g_nccl.Recv(p->face_recv[side], (size_t)elems, ty, peer[side], comm_of(ctx), s));
+    }
+  HPCX_NCCL(ctx, g_nccl.GroupEnd());
+  for (int side = 0; side < 2; ++side)
+    if (has[side])
+      if (hpcx_status st = hpcx_grid_unpack_face(g, 1, side, r, p->face_recv[side], HPCX_MEM_DEVICE, s)) return st;
   return HPCX_OK;
 }
 
@@ -373,6 +404,54 @@ hpcx_status hpcx_comm_ipc_close(hpcx_ctx ctx, void *peer_ptr) {
   return HPCX_OK;
 }
 
+// Plan of a distributed box sweep over a py x px grid of blocks (px == 1: y-slabs).
+static hpcx_status box_plan_create(hpcx_ctx ctx, hpcx_grid in, hpcx_grid out, const hpcx_stencil_desc *st, int py,
+                                   int px, hpcx_halo_plan *out_plan) {
+  HPCX_REQUIRE(ctx, in->desc.ndim == 2 && out->desc.ndim == 2, "box sweeps take 2-D grids");
+  HPCX_REQUIRE(ctx, in->desc.dtype == out->desc.dtype, "grids differ in dtype");
+  HPCX_REQUIRE(ctx, in->desc.dim[0] == out->desc.dim[0] && in->desc.dim[1] == out->desc.dim[1],
+               "grids differ in logical extent");
+  HPCX_REQUIRE(ctx, st->radius >= 0 && st->radius <= in->desc.lo && st->radius <= in->desc.hi,
+               "radius exceeds the ghost width of the input grid");
+  HPCX_REQUIRE(ctx, in->n[1] >= std::max(st->radius, 1), "a block needs at least `radius` rows");
+  HPCX_REQUIRE(ctx, px == 1 || in->n[2] >= std::max(st->radius, 1), "a block needs at least `radius` columns");
+  HPCX_REQUIRE(ctx, py >= 1 && px >= 1 && py * px == ctx->nranks, "py * px must equal the number of ranks");
+  if (ctx->nranks > 1 && !ctx->nccl_comm) return fail(ctx, HPCX_NCCL_ERROR, "hpcx_comm_init has not been called");
+  hpcx_halo_plan p = new (std::nothrow) hpcx_halo_plan_s();
+  if (!p) return fail(ctx, HPCX_OOM, "host allocation failed");
+  p->ctx = ctx;
+  p->in = in;
+  p->out = out;
+  p->st = *st;
+  p->py = py;
+  p->px = px;
+  cudaError_t e = p->create_events();
+  if (e == cudaSuccess && px > 1 && st->kind == HPCX_STENCIL_BOX_X && st->radius > 0) {
+    int64_t elems = 0;
+    hpcx_grid_face_elems(in, 1, st->radius, &elems);
+    for (int side = 0; side < 2 && e == cudaSuccess; ++side) {
+      e = cudaMalloc(&p->face_send[side], (size_t)elems * in->es);
+      if (e == cudaSuccess) e = cudaMalloc(&p->face_recv[side], (size_t)elems * in->es);
+    }
+  }
+  if (e != cudaSuccess) {
+    hpcx_stencil_dist_destroy(p);
+    return fail(ctx, e == cudaErrorMemoryAllocation ? HPCX_OOM : HPCX_CUDA_ERROR,
+                std::string("box plan: ") + cudaGetErrorString(e));
+  }
+  *out_plan = p;
+  return HPCX_OK;
+}
+
+hpcx_status hpcx_stencil_dist_plan_blocks(hpcx_ctx ctx, hpcx_grid in, hpcx_grid out, const hpcx_stencil_desc *st,
+                                          int32_t py, int32_t px, hpcx_halo_plan *out_plan) {
+  if (!ctx || !in || !out || !st || !out_plan) return HPCX_INVALID_ARG;
+  *out_plan = nullptr;
+  if (st->kind != HPCX_STENCIL_BOX_X && st->kind != HPCX_STENCIL_BOX_Y)
+    return fail(ctx, HPCX_UNSUPPORTED, "the block split serves the 2-D box sweeps; JACOBI7 is split into z-slabs");
+  return box_plan_create(ctx, in, out, st, py, px, out_plan);
+}
+
 hpcx_status hpcx_stencil_dist_plan(hpcx_ctx ctx, hpcx_grid in, hpcx_grid out,
                                    const hpcx_stencil_desc *st, int32_t transport,
                                    hpcx_halo_plan *out_plan) {
@@ -381,25 +460,9 @@ hpcx_status hpcx_stencil_dist_plan(hpcx_ctx ctx, hpcx_grid in, hpcx_grid out,
   if (st->kind == HPCX_STENCIL_BOX_X || st->kind == HPCX_STENCIL_BOX_Y) {
     // the reference's 17-point sweeps over y-slabs (rows split like its static chunking,
     // test_hpc_benchmark.cpp:1356,1371-1372): BOX_X needs no exchange, BOX_Y trades `radius` rows
-    HPCX_REQUIRE(ctx, in->desc.ndim == 2 && out->desc.ndim == 2, "box sweeps take 2-D grids");
-    HPCX_REQUIRE(ctx, in->desc.dtype == out->desc.dtype, "grids differ in dtype");
-    HPCX_REQUIRE(ctx, in->desc.dim[0] == out->desc.dim[0] && in->desc.dim[1] == out->desc.dim[1],
-                 "grids differ in logical extent");
-    HPCX_REQUIRE(ctx, st->radius >= 0 && st->radius <= in->desc.lo && st->radius <= in->desc.hi,
-                 "radius exceeds the ghost width of the input grid");
-    HPCX_REQUIRE(ctx, in->n[1] >= std::max(st->radius, 1), "a slab needs at least `radius` rows");
     if (transport != 0)
       return fail(ctx, HPCX_UNSUPPORTED, "distributed box sweeps use the NCCL transport (0)");
-    if (ctx->nranks > 1 && !ctx->nccl_comm) return fail(ctx, HPCX_NCCL_ERROR, "hpcx_comm_init has not been called");
-    hpcx_halo_plan p = new (std::nothrow) hpcx_halo_plan_s();
-    if (!p) return fail(ctx, HPCX_OOM, "host allocation failed");
-    p->ctx = ctx;
-    p->in = in;
-    p->out = out;
-    p->st = *st;
-    p->create_events();
-    *out_plan = p;
-    return HPCX_OK;
+    return box_plan_create(ctx, in, out, st, ctx->nranks, 1, out_plan);
   }
   HPCX_REQUIRE(ctx, st->kind == HPCX_STENCIL_JACOBI7, "unknown stencil kind");
   HPCX_REQUIRE(ctx, in->desc.ndim == 3 && out->desc.ndim == 3, "JACOBI7 takes 3-D grids");
@@ -634,32 +697,40 @@ hpcx_status hpcx_stencil_dist_sweep(hpcx_halo_plan p, int32_t steps, void *strea
   hpcx_status rc = HPCX_OK;
 
   if (p->st.kind == HPCX_STENCIL_BOX_X || p->st.kind == HPCX_STENCIL_BOX_Y) {
-    // One sweep in -> out over this rank's y-slab.  BOX_Y: the `radius` ghost rows of `in` come from
-    // the neighbours (rows are contiguous: nothing is packed) on the comm stream while the rows that
-    // need none of them are swept; the two boundary strips follow the receive.
+    // One sweep in -> out over this rank's block (a y-slab when px == 1).  The `radius` ghost rows
+    // (BOX_Y; contiguous, nothing is packed) or ghost columns (BOX_X with px > 1; packed faces) of
+    // `in` come from the neighbours on the comm stream while the part of the block that needs none
+    // of them is swept; the two boundary strips follow the receive.
     HPCX_REQUIRE(ctx, steps == 1, "box sweeps are single-step");
-    const int64_t ny = g->n[1], r = p->st.kind == HPCX_STENCIL_BOX_Y ? p->st.radius : 0;
-    if (r == 0 || ctx->nranks <= 1) {
+    const int64_t ny = g->n[1], nx = g->n[2];
+    const bool along_y = p->st.kind == HPCX_STENCIL_BOX_Y;
+    const int64_t r = p->st.radius, n = along_y ? ny : nx;
+    const bool exchange = r > 0 && ctx->nranks > 1 && (along_y ? p->py > 1 : p->px > 1);
+    if (!exchange) {
       rc = box_launch_rows(p->in, p->out, &p->st, 0, ny, cs);
     } else {
       HPCX_CUDA(ctx, cudaEventRecord(p->ev_start, cs));
       HPCX_CUDA(ctx, cudaStreamWaitEvent(ms, p->ev_start, 0));
       {
-        HPCX_RANGE("box sweep: ghost-row exchange (NCCL send/recv)");
-        rc = exchange_planes(g, p->in->dev, ms, r);
+        HPCX_RANGE("box sweep: ghost exchange (NCCL send/recv)");
+        rc = along_y ? exchange_planes(g, p->in->dev, ms, r, p->px) : exchange_cols(p, ms);
       }
       if (rc != HPCX_OK) return rc;
       HPCX_CUDA(ctx, cudaEventRecord(p->ev_recv, ms));
-      const int64_t lo_end = std::min<int64_t>(r, ny), hi_beg = std::max<int64_t>(lo_end, ny - r);
+      const int64_t lo_end = std::min<int64_t>(r, n), hi_beg = std::max<int64_t>(lo_end, n - r);
+      auto strip = [&](int64_t b0, int64_t b1) {
+        return along_y ? box_launch_rows(p->in, p->out, &p->st, b0, b1, cs)
+                       : box_launch_tile(p->in, p->out, &p->st, 0, ny, b0, b1, cs);
+      };
       {
-        HPCX_RANGE("box sweep: interior rows");
-        rc = box_launch_rows(p->in, p->out, &p->st, lo_end, hi_beg, cs);
+        HPCX_RANGE("box sweep: interior");
+        rc = strip(lo_end, hi_beg);
       }
       if (rc != HPCX_OK) return rc;
       HPCX_CUDA(ctx, cudaStreamWaitEvent(cs, p->ev_recv, 0));
       HPCX_RANGE("box sweep: boundary strips");
-      rc = box_launch_rows(p->in, p->out, &p->st, 0, lo_end, cs);
-      if (rc == HPCX_OK) rc = box_launch_rows(p->in, p->out, &p->st, hi_beg, ny, cs);
+      rc = strip(0, lo_end);
+      if (rc == HPCX_OK) rc = strip(hi_beg, n);
     }
     if (rc != HPCX_OK) return rc;
     if (!stream) HPCX_CUDA(ctx, cudaStreamSynchronize(cs));
@@ -735,6 +806,10 @@ hpcx_status hpcx_stencil_dist_destroy(hpcx_halo_plan p) {
   const hpcx_status pending = comm_check(p->ctx);  // a timed-out wait of an asynchronous sweep surfaces here
   close_peers(p);
   p->destroy_events();
+  for (int side = 0; side < 2; ++side) {
+    cudaFree(p->face_send[side]);
+    cudaFree(p->face_recv[side]);
+  }
   for (auto &e : p->graphs) cudaGraphExecDestroy(e.exec);
   delete p;
   return pending;

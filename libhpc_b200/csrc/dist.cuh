@@ -9,6 +9,11 @@ struct hpcx_halo_plan_s {
   hpcx_grid in = nullptr, out = nullptr;
   hpcx_stencil_desc st{};
   int transport = 0;
+  // 2-D block split of the box sweeps (hpcx_stencil_dist_plan_blocks): the ranks form a py x px
+  // grid, rank = ry * px + rx; px == 1 is the y-slab split.  face_send / face_recv: packed x faces
+  // (side 0 = towards rx - 1), ext_y x radius elements each.
+  int py = 0, px = 1;
+  void *face_send[2] = {nullptr, nullptr}, *face_recv[2] = {nullptr, nullptr};
   // ev_bnd[pass & 1]: boundary strips of a pass done; ev_int: interior of a pass done
   cudaEvent_t ev_bnd[2] = {nullptr, nullptr}, ev_recv = nullptr, ev_start = nullptr, ev_int = nullptr;
   cudaError_t create_events() {

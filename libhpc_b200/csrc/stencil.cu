@@ -440,6 +440,15 @@ BoxView box_view(hpcx_grid in, hpcx_grid out, int64_t y0, int64_t y1) {
   v.gi.n1 = v.go.n1 = y1 - y0;
   return v;
 }
+// ... and a range of columns [x0, x1) the same grid with its x origin shifted (block split:
+// interior columns beside the exchange, boundary strips behind it).
+BoxView box_view(hpcx_grid in, hpcx_grid out, int64_t y0, int64_t y1, int64_t x0, int64_t x1) {
+  BoxView v = box_view(in, out, y0, y1);
+  v.gi.xoff += x0;
+  v.go.xoff += x0;
+  v.gi.n2 = v.go.n2 = x1 - x0;
+  return v;
+}
 
 template <typename T>
 hpcx_status launch_box_direct(const BoxView &v, int axis, int radius, cudaStream_t s) {
@@ -1004,6 +1013,19 @@ hpcx_status box_launch_rows(hpcx_grid_s *in, hpcx_grid_s *out, const hpcx_stenci
   const BoxView v = box_view(in, out, y0, y1);
   return in->desc.dtype == HPCX_F64 ? launch_box<double>(v, axis, st->radius, st->variant, st->zsplit, s)
                                     : launch_box<float>(v, axis, st->radius, st->variant, st->zsplit, s);
+}
+
+// Box sweep of the tile [y0, y1) x [x0, x1).  The vector kernels need 16-byte aligned column
+// ranges; anything else takes the direct kernel (same sums, same order).
+hpcx_status box_launch_tile(hpcx_grid_s *in, hpcx_grid_s *out, const hpcx_stencil_desc *st, int64_t y0, int64_t y1,
+                            int64_t x0, int64_t x1, cudaStream_t s) {
+  if (y1 <= y0 || x1 <= x0) return HPCX_OK;
+  const int axis = st->kind == HPCX_STENCIL_BOX_X ? 2 : 1;
+  const BoxView v = box_view(in, out, y0, y1, x0, x1);
+  const int64_t vec = 16 / in->es;
+  const int variant = (x0 % vec == 0 && (x1 - x0) % vec == 0) ? st->variant : HPCX_VARIANT_DIRECT;
+  return in->desc.dtype == HPCX_F64 ? launch_box<double>(v, axis, st->radius, variant, st->zsplit, s)
+                                    : launch_box<float>(v, axis, st->radius, variant, st->zsplit, s);
 }
 
 // Forces the sweep kernels onto the current device now.  CUDA loads kernels lazily, at their

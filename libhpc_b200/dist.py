@@ -40,16 +40,21 @@ def barrier(ctx: Context) -> None:
 
 
 class HaloPlan:
-    """Distributed sweeps over slabs of axis 0 (hpcx_stencil_dist_*): JACOBI7 over z-slabs, the
-    reference's box sweeps over y-slabs (radius = the reference's nblur)."""
+    """Distributed sweeps (hpcx_stencil_dist_*): JACOBI7 over z-slabs, the reference's box sweeps
+    over y-slabs (radius = the reference's nblur) or, with blocks=(py, px), over a py x px grid of
+    2-D blocks (rank = ry * px + rx; hpcx_stencil_dist_plan_blocks)."""
 
     def __init__(self, ctx: Context, gin: DeviceGrid, gout: DeviceGrid, kind: int, variant: int = 0,
-                 zsplit: int = 0, transport: int = 0, radius: int = 0):
+                 zsplit: int = 0, transport: int = 0, radius: int = 0, blocks: tuple | None = None):
         self.ctx = ctx
         d = stencil_desc(kind, radius, variant, zsplit)
         h = C.c_void_p()
-        ctx.check(ctx.lib.hpcx_stencil_dist_plan(ctx.h, gin.h, gout.h, C.byref(d), transport,
-                                                 C.byref(h)))
+        if blocks is not None:
+            ctx.check(ctx.lib.hpcx_stencil_dist_plan_blocks(ctx.h, gin.h, gout.h, C.byref(d), int(blocks[0]),
+                                                            int(blocks[1]), C.byref(h)))
+        else:
+            ctx.check(ctx.lib.hpcx_stencil_dist_plan(ctx.h, gin.h, gout.h, C.byref(d), transport,
+                                                     C.byref(h)))
         self.h = h
 
     def sweep(self, steps: int, stream=None):

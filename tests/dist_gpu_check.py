@@ -151,6 +151,49 @@ def main():
         ga.destroy()
         gb.destroy()
 
+    # ---- R0 over a 2-D block split (py x px blocks, rank = ry * px + rx): BOX_X trades 8 ghost
+    # columns (packed faces) inside a block row, BOX_Y 8 ghost rows between block rows
+    shapes = [(py, world // py) for py in range(1, world + 1) if world % py == 0]
+    for py, px in shapes:
+        for (ny, nx), kind, axis in (((24 * py + 5, 64 * px), hp.STENCIL_BOX_X, 1), ((24 * py + 5, 64 * px), hp.STENCIL_BOX_Y, 0),
+                                     ((9 * py, 36 * px + 2), hp.STENCIL_BOX_X, 1), ((9 * py, 36 * px + 2), hp.STENCIL_BOX_Y, 0)):
+            a_flat = oracle.fill((ny + 16) * (nx + 16), 5, np.float32)
+            want = oracle.box_sweep(a_flat, ny, nx, 8, 8, 0, 0, axis, 8).reshape(ny, nx)
+            ry, rx = rank // px, rank % px
+            by = [ny * r // py for r in range(py + 1)]
+            bx = [nx * r // px for r in range(px + 1)]
+            y0, y1, x0, x1 = by[ry], by[ry + 1], bx[rx], bx[rx + 1]
+            block = np.ascontiguousarray(a_flat.reshape(ny + 16, nx + 16)[y0:y1 + 16, x0:x1 + 16]).copy()
+            # ghosts shared with a neighbouring block must come through the exchange: poison them
+            if ry > 0:
+                block[:8] = np.nan
+            if ry < py - 1:
+                block[-8:] = np.nan
+            if rx > 0:
+                block[:, :8] = np.nan
+            if rx < px - 1:
+                block[:, -8:] = np.nan
+            ga = hp.DeviceGrid(ctx, (y1 - y0, x1 - x0), np.float32, 8)
+            gb = hp.DeviceGrid(ctx, (y1 - y0, x1 - x0), np.float32, 0)
+            ga.upload(block.ravel())
+            plan = hd.HaloPlan(ctx, ga, gb, kind, radius=8, blocks=(py, px))
+            plan.sweep(1)
+            out = gb.download().reshape(y1 - y0, x1 - x0)
+            assert bits_equal(np.ascontiguousarray(out), np.ascontiguousarray(want[y0:y1, x0:x1])), \
+                (rank, "box blocks", (py, px), kind, (ny, nx))
+            plan.destroy()
+            ga.destroy()
+            gb.destroy()
+    if world > 1:
+        ga, gb = hp.DeviceGrid(ctx, (16, 64), np.float32, 8), hp.DeviceGrid(ctx, (16, 64), np.float32, 0)
+        try:  # a block grid that does not cover the communicator is refused on every rank
+            hd.HaloPlan(ctx, ga, gb, hp.STENCIL_BOX_X, radius=8, blocks=(world, 2))
+            raise AssertionError("py * px != world accepted")
+        except hp.HpcxError:
+            pass
+        ga.destroy()
+        gb.destroy()
+
     # ---- SpMV: banded (C4 shape) by rows, power-law by nnz
     for name, (rp, col, val), mode in (("op27", synth.op27(16, index_dtype=np.int64), 0),
                                        ("rmat", synth.rmat(13, 16, 24, index_dtype=np.int64), 1)):
