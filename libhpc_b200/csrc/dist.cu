@@ -675,6 +675,97 @@ static hpcx_status nccl_sweeps_enqueue(hpcx_halo_plan p, int32_t steps, cudaStre
   return HPCX_OK;
 }
 
+// One distributed box sweep in -> out over this rank's block (a y-slab when px == 1).  The `radius`
+// ghost rows (BOX_Y; contiguous, nothing is packed) or ghost columns (BOX_X with px > 1; packed
+// faces) of `in` come from the neighbours on the comm stream while the part of the block that needs
+// none of them is swept; the two boundary strips follow the receive.
+static hpcx_status box_sweep_enqueue(hpcx_halo_plan p, int32_t, cudaStream_t cs) {
+  hpcx_ctx ctx = p->ctx;
+  hpcx_grid g = p->in;
+  cudaStream_t ms = ctx->comm;
+  const int64_t ny = g->n[1], nx = g->n[2];
+  const bool along_y = p->st.kind == HPCX_STENCIL_BOX_Y;
+  const int64_t r = p->st.radius, n = along_y ? ny : nx;
+  hpcx_status rc = HPCX_OK;
+  HPCX_CUDA(ctx, cudaEventRecord(p->ev_start, cs));
+  HPCX_CUDA(ctx, cudaStreamWaitEvent(ms, p->ev_start, 0));
+  {
+    HPCX_RANGE("box sweep: ghost exchange (NCCL send/recv)");
+    rc = along_y ? exchange_planes(g, p->in->dev, ms, r, p->px) : exchange_cols(p, ms);
+  }
+  if (rc != HPCX_OK) return rc;
+  HPCX_CUDA(ctx, cudaEventRecord(p->ev_recv, ms));
+  const int64_t lo_end = std::min<int64_t>(r, n), hi_beg = std::max<int64_t>(lo_end, n - r);
+  auto strip = [&](int64_t b0, int64_t b1) {
+    return along_y ? box_launch_rows(p->in, p->out, &p->st, b0, b1, cs)
+                   : box_launch_tile(p->in, p->out, &p->st, 0, ny, b0, b1, cs);
+  };
+  {
+    HPCX_RANGE("box sweep: interior");
+    rc = strip(lo_end, hi_beg);
+  }
+  if (rc != HPCX_OK) return rc;
+  HPCX_CUDA(ctx, cudaStreamWaitEvent(cs, p->ev_recv, 0));
+  HPCX_RANGE("box sweep: boundary strips");
+  rc = strip(0, lo_end);
+  if (rc == HPCX_OK) rc = strip(hi_beg, n);
+  return rc;
+}
+
+// Runs `enqueue(p, steps, cs)` — a sequence of launches, NCCL groups and event hand-overs between
+// the caller's stream and the comm stream, with no host synchronisation inside — as ONE CUDA graph
+// replay: captured the first time a (source buffer, destination buffer, steps) triple is seen,
+// replayed afterwards.  A Jacobi sweep is three launches plus an NCCL group: at 90-170 us per sweep
+// and 100 sweeps per call their launch gaps and the hand-overs between the two streams are what
+// the replay removes.  Falls back to eager launches
+// when the stream is already being captured, HPCX_NCCL_GRAPHS=0, or a capture fails.
+typedef hpcx_status (*enqueue_fn)(hpcx_halo_plan, int32_t, cudaStream_t);
+static hpcx_status replay_or_enqueue(hpcx_halo_plan p, int32_t steps, cudaStream_t cs, enqueue_fn enqueue) {
+  hpcx_ctx ctx = p->ctx;
+  hpcx_status rc = HPCX_OK;
+  cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+  if (ctx->nranks > 1 && p->graphs_ok && cudaStreamIsCapturing(cs, &cap) == cudaSuccess &&
+      cap == cudaStreamCaptureStatusNone) {
+    const hpcx_halo_plan_s::GraphEntry *hit = nullptr;
+    for (auto &e : p->graphs)
+      if (e.in == p->in->dev && e.out == p->out->dev && e.steps == steps) hit = &e;
+    if (!hit) {
+      HPCX_RANGE("sweep: capture into a CUDA graph");
+      if (hpcx_status st = preload_stencil_kernels(ctx)) return st;  // no attribute calls inside the capture
+      cudaGraph_t graph = nullptr;
+      cudaGraphExec_t exec = nullptr;
+      const int64_t before = ctx->launches;
+      cudaError_t e = cudaStreamBeginCapture(cs, cudaStreamCaptureModeRelaxed);
+      if (e == cudaSuccess) {
+        rc = enqueue(p, steps, cs);
+        e = cudaStreamEndCapture(cs, &graph);
+        if (rc == HPCX_OK && e == cudaSuccess) e = cudaGraphInstantiate(&exec, graph, 0);
+        if (graph) cudaGraphDestroy(graph);
+      }
+      const int64_t per_replay = ctx->launches - before;
+      ctx->launches = before;  // nothing has run yet
+      if (rc != HPCX_OK || e != cudaSuccess || !exec) {
+        (void)cudaGetLastError();
+        p->graphs_ok = false;  // every rank takes the same decision: same code, same library
+        rc = HPCX_OK;
+      } else {
+        if (p->graphs.size() >= 8) {
+          for (auto &old : p->graphs) cudaGraphExecDestroy(old.exec);
+          p->graphs.clear();
+        }
+        p->graphs.push_back({p->in->dev, p->out->dev, steps, exec, per_replay});
+        hit = &p->graphs.back();
+      }
+    }
+    if (hit) {
+      HPCX_CUDA(ctx, cudaGraphLaunch(hit->exec, cs));
+      ctx->launches += hit->launches;
+      return HPCX_OK;
+    }
+  }
+  return enqueue(p, steps, cs);
+}
+
 extern "C" {
 
 // Per step t (src -> dst):
@@ -697,41 +788,12 @@ hpcx_status hpcx_stencil_dist_sweep(hpcx_halo_plan p, int32_t steps, void *strea
   hpcx_status rc = HPCX_OK;
 
   if (p->st.kind == HPCX_STENCIL_BOX_X || p->st.kind == HPCX_STENCIL_BOX_Y) {
-    // One sweep in -> out over this rank's block (a y-slab when px == 1).  The `radius` ghost rows
-    // (BOX_Y; contiguous, nothing is packed) or ghost columns (BOX_X with px > 1; packed faces) of
-    // `in` come from the neighbours on the comm stream while the part of the block that needs none
-    // of them is swept; the two boundary strips follow the receive.
     HPCX_REQUIRE(ctx, steps == 1, "box sweeps are single-step");
-    const int64_t ny = g->n[1], nx = g->n[2];
     const bool along_y = p->st.kind == HPCX_STENCIL_BOX_Y;
-    const int64_t r = p->st.radius, n = along_y ? ny : nx;
-    const bool exchange = r > 0 && ctx->nranks > 1 && (along_y ? p->py > 1 : p->px > 1);
-    if (!exchange) {
-      rc = box_launch_rows(p->in, p->out, &p->st, 0, ny, cs);
-    } else {
-      HPCX_CUDA(ctx, cudaEventRecord(p->ev_start, cs));
-      HPCX_CUDA(ctx, cudaStreamWaitEvent(ms, p->ev_start, 0));
-      {
-        HPCX_RANGE("box sweep: ghost exchange (NCCL send/recv)");
-        rc = along_y ? exchange_planes(g, p->in->dev, ms, r, p->px) : exchange_cols(p, ms);
-      }
-      if (rc != HPCX_OK) return rc;
-      HPCX_CUDA(ctx, cudaEventRecord(p->ev_recv, ms));
-      const int64_t lo_end = std::min<int64_t>(r, n), hi_beg = std::max<int64_t>(lo_end, n - r);
-      auto strip = [&](int64_t b0, int64_t b1) {
-        return along_y ? box_launch_rows(p->in, p->out, &p->st, b0, b1, cs)
-                       : box_launch_tile(p->in, p->out, &p->st, 0, ny, b0, b1, cs);
-      };
-      {
-        HPCX_RANGE("box sweep: interior");
-        rc = strip(lo_end, hi_beg);
-      }
-      if (rc != HPCX_OK) return rc;
-      HPCX_CUDA(ctx, cudaStreamWaitEvent(cs, p->ev_recv, 0));
-      HPCX_RANGE("box sweep: boundary strips");
-      rc = strip(0, lo_end);
-      if (rc == HPCX_OK) rc = strip(hi_beg, n);
-    }
+    const bool exchange = p->st.radius > 0 && ctx->nranks > 1 && (along_y ? p->py > 1 : p->px > 1);
+    // eager: replaying the sweep as a CUDA graph was measured and lost (x sweep over x-slabs at
+    // N = 2: 1046 against 1175 Gcell/s; a single 100 us sweep per call leaves a replay nothing to hide)
+    rc = exchange ? box_sweep_enqueue(p, 1, cs) : box_launch_rows(p->in, p->out, &p->st, 0, g->n[1], cs);
     if (rc != HPCX_OK) return rc;
     if (!stream) HPCX_CUDA(ctx, cudaStreamSynchronize(cs));
     return HPCX_OK;
@@ -748,51 +810,9 @@ hpcx_status hpcx_stencil_dist_sweep(hpcx_halo_plan p, int32_t steps, void *strea
     return hpcx::stencil_peer_sweep(p, steps, cs, stream == nullptr);
   }
 
-  // NCCL transport.  The whole call — for every pass {boundary planes, grouped send/recv on the comm
-  // stream, interior planes} — is captured ONCE into a CUDA graph per (buffers, steps) and replayed:
-  // a sweep is three launches plus an NCCL group, and at 170 us per sweep their launch gaps and the
-  // event hand-offs between the two streams are what kept this transport at 80 % of the one-GPU rate.
-  bool launched = false;
-  cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
-  if (ctx->nranks > 1 && p->graphs_ok && cudaStreamIsCapturing(cs, &cap) == cudaSuccess &&
-      cap == cudaStreamCaptureStatusNone) {
-    cudaGraphExec_t exec = nullptr;
-    for (auto &e : p->graphs)
-      if (e.in == p->in->dev && e.out == p->out->dev && e.steps == steps) exec = e.exec;
-    if (!exec) {
-      HPCX_RANGE("sweep: capture into a CUDA graph");
-      if (hpcx_status st = preload_stencil_kernels(ctx)) return st;  // no attribute calls inside the capture
-      cudaGraph_t graph = nullptr;
-      cudaError_t e = cudaStreamBeginCapture(cs, cudaStreamCaptureModeRelaxed);
-      if (e == cudaSuccess) {
-        rc = nccl_sweeps_enqueue(p, steps, cs);
-        e = cudaStreamEndCapture(cs, &graph);
-        if (rc == HPCX_OK && e == cudaSuccess) e = cudaGraphInstantiate(&exec, graph, 0);
-        if (graph) cudaGraphDestroy(graph);
-      }
-      if (rc != HPCX_OK || e != cudaSuccess || !exec) {
-        (void)cudaGetLastError();
-        p->graphs_ok = false;  // every rank takes the same decision: same code, same library
-        exec = nullptr;
-        rc = HPCX_OK;
-      } else {
-        if (p->graphs.size() >= 8) {
-          for (auto &old : p->graphs) cudaGraphExecDestroy(old.exec);
-          p->graphs.clear();
-        }
-        p->graphs.push_back({p->in->dev, p->out->dev, steps, exec});
-      }
-    }
-    if (exec) {
-      HPCX_CUDA(ctx, cudaGraphLaunch(exec, cs));
-      ctx->launches += p->graph_launches(steps);
-      launched = true;
-    }
-  }
-  if (!launched) {
-    rc = nccl_sweeps_enqueue(p, steps, cs);
-    if (rc != HPCX_OK) return rc;
-  }
+  // NCCL transport: the whole call as one graph replay (replay_or_enqueue).
+  rc = replay_or_enqueue(p, steps, cs, nccl_sweeps_enqueue);
+  if (rc != HPCX_OK) return rc;
   const bool temporal = p->st.variant == HPCX_VARIANT_TEMPORAL;
   const int passes = temporal ? steps / 2 + (steps & 1) : steps;
   if ((passes & 1) == 0) std::swap(p->in->dev, p->out->dev);

@@ -39,15 +39,10 @@ struct hpcx_halo_plan_s {
     void *in, *out;
     int steps;
     cudaGraphExec_t exec;
+    int64_t launches;  // kernels of this library one replay launches (for hpcx_launch_count)
   };
   std::vector<GraphEntry> graphs;
   bool graphs_ok = true;  // cleared when a capture fails: the call then runs eagerly
-  // kernels of this library one replay launches (for hpcx_launch_count)
-  int64_t graph_launches(int steps) const {
-    const bool temporal = st.variant == HPCX_VARIANT_TEMPORAL;
-    const int two = temporal ? steps / 2 : 0, one = temporal ? (steps & 1) : steps;
-    return 2 * (int64_t)two + 3 * (int64_t)one;
-  }
 };
 
 
