@@ -392,7 +392,8 @@ HPCX_API hpcx_status hpcx_comm_check(hpcx_ctx ctx);
  * stream while the rows that need none of them are swept, then sweeps the two boundary strips.
  * JACOBI7 transport:
  *   0  NCCL send/recv of the boundary planes on the comm stream, overlapped with the interior
- *      sweep on the compute stream (three launches per sweep);
+ *      sweep on the compute stream (three launches per sweep; a whole call is captured into a
+ *      CUDA graph once and replayed, HPCX_NCCL_GRAPHS=0 turns that off);
  *   1  fused: one kernel per sweep whose boundary CTAs store their plane straight into the
  *      neighbour's ghost plane over NVLink (CUDA IPC peer windows) and publish a sweep-number
  *      flag that the neighbour's next sweep acquires before reading the ghost (fp32 TMA sweep
@@ -401,7 +402,8 @@ HPCX_API hpcx_status hpcx_comm_check(hpcx_ctx ctx);
  * TWO ghost planes traded per side and pass — every slab needs lo,hi >= 2 and >= 2 planes
  * (HPCX_INVALID_ARG on every rank otherwise).  The neighbour's boundary plane is advanced
  * redundantly on this rank; results stay bit-identical to single sweeps.  Transport 1 pushes the
- * planes with a small kernel behind each pass (peer stores + flags, no NCCL on the data path). */
+ * planes with peer stores + flags (no NCCL on the data path): from inside the pass kernel on
+ * slabs of at most 128 planes, with a small kernel behind each pass on thicker ones. */
 typedef struct hpcx_halo_plan_s *hpcx_halo_plan;
 HPCX_API hpcx_status hpcx_stencil_dist_plan(hpcx_ctx ctx, hpcx_grid in, hpcx_grid out,
                                             const hpcx_stencil_desc *st, int32_t transport,
