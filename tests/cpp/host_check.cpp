@@ -375,6 +375,21 @@ static int run_gpu() {
       dr.download(r);
     }
     ok = ok && slabs.back() == nz && std::memcmp(r.data(), v.data(), r.size() * sizeof(float)) == 0;
+    {  // the block-split face of the box sweeps on a 1 x 1 block grid: same answer as hpc::stencil_sweep
+      const int by = 40, bx = 128;
+      hpc::HPCHighDimensionFlatArray<2, float, 8> a(by, bx);
+      hpc::HPCHighDimensionFlatArray<2, float> b0(by, bx), b1(by, bx);
+      for (std::size_t i = 0; i < a.size(); ++i) a.data()[i] = frand(seed);
+      for (int axis = 0; axis < 2; ++axis) {
+        hpc::stencil_sweep(ctx, a, b0, hpc::Box1D{axis, 8});
+        hpc::DeviceGrid<2, float, 8> da(ctx, a);
+        hpc::DeviceGrid<2, float> db(ctx, b1);
+        hpc::BoxHaloPlan<float, 8, 8, 0, 0> plan(da, db, hpc::Box1D{axis, 8}, comm.size(), 1);
+        plan.sweep();
+        db.download(b1);
+        ok = ok && std::memcmp(b0.data(), b1.data(), b0.size() * sizeof(float)) == 0;
+      }
+    }
     std::printf("distributed_face ok %d\n", ok);
     bad += !ok;
   }
