@@ -20,7 +20,7 @@ OBJ = os.path.join(CSRC, "build")
 LIB = os.path.join(HERE, "libhpcx.so")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 
-CU_SOURCES = ["context.cu", "grid.cu", "spmv.cu", "spmv_hub.cu", "csr_plan.cu", "stencil.cu", "dist.cu", "multi.cu", "assemble.cu", "cg.cu", "dense2d.cu"]
+CU_SOURCES = ["context.cu", "grid.cu", "spmv.cu", "spmv_hub.cu", "csr_plan.cu", "sell_build.cu", "stencil.cu", "dist.cu", "multi.cu", "assemble.cu", "cg.cu", "dense2d.cu"]
 CXX_SOURCES = ["partition.cpp"]
 
 NVCC_FLAGS = [

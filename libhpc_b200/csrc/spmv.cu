@@ -412,62 +412,6 @@ hpcx_status spmv_device(hpcx_csr A, const T *x, T *y, cudaStream_t s) {
   }
 }
 
-// SELL-C-sigma builder (host). Within every window of sigma consecutive rows, rows are
-// stably sorted by descending length (ties keep ascending row id); slices of C sorted rows
-// are stored column-major, padded to the slice's longest row with col = the row's own index
-// clamped to ncols-1 and value 0.
-template <typename T>
-void build_sell(hpcx_csr A, const int64_t *rp, const int32_t *col, const T *val,
-                std::vector<int32_t> &scol, std::vector<T> &sval) {
-  const int64_t n = A->nrows;
-  const int C = A->sell_c, S = A->sell_sigma;
-  A->h_perm.resize(n);
-  for (int64_t i = 0; i < n; ++i) A->h_perm[i] = (int32_t)i;
-  if (S > 1)
-    for (int64_t w = 0; w < n; w += S) {
-      const int64_t e = std::min<int64_t>(w + S, n);
-      std::stable_sort(A->h_perm.begin() + w, A->h_perm.begin() + e, [&](int32_t a, int32_t b) {
-        return rp[a + 1] - rp[a] > rp[b + 1] - rp[b];
-      });
-    }
-  const int64_t ns = (n + C - 1) / C;
-  A->sell_nslices = ns;
-  A->h_slice_ptr.assign(ns + 1, 0);
-  A->h_slice_len.assign(ns, 0);
-  for (int64_t s = 0; s < ns; ++s) {
-    int64_t m = 0;
-    for (int64_t j = s * C; j < std::min<int64_t>((s + 1) * C, n); ++j) {
-      const int32_t r = A->h_perm[j];
-      m = std::max<int64_t>(m, rp[r + 1] - rp[r]);
-    }
-    A->h_slice_len[s] = (int32_t)m;
-    A->h_slice_ptr[s + 1] = A->h_slice_ptr[s] + m * C;
-  }
-  A->sell_padded = A->h_slice_ptr[ns];
-  scol.assign(A->sell_padded, 0);
-  sval.assign(A->sell_padded, T(0));
-  for (int64_t s = 0; s < ns; ++s)
-    for (int lane = 0; lane < C; ++lane) {
-      const int64_t j = s * C + lane;
-      const int64_t base = A->h_slice_ptr[s];
-      const int len = A->h_slice_len[s];
-      if (j < n) {
-        const int32_t r = A->h_perm[j];
-        const int64_t a = rp[r], rl = rp[r + 1] - rp[r];
-        const int32_t padc = (int32_t)std::min<int64_t>(r, A->ncols - 1);
-        for (int k = 0; k < len; ++k) {
-          const int64_t i = base + (int64_t)k * C + lane;
-          if (k < rl) {
-            scol[i] = col[a + k];
-            sval[i] = val[a + k];
-          } else {
-            scol[i] = padc;
-          }
-        }
-      }
-    }
-}
-
 void free_csr(hpcx_csr A) {
   hpcx::csr_close_peers(A);
   hpcx::hub_free(A);
@@ -494,15 +438,6 @@ void free_csr(hpcx_csr A) {
   cudaFree(A->d_long_row_dist);
   cudaFree(A->d_long_off_dist);
   delete A;
-}
-
-template <typename V>
-hpcx_status upload_vec(hpcx_ctx ctx, const std::vector<V> &h, V **d) {
-  *d = nullptr;
-  HPCX_CUDA(ctx, cudaMalloc((void **)d, std::max<size_t>(h.size(), 1) * sizeof(V)));
-  if (!h.empty())
-    HPCX_CUDA(ctx, cudaMemcpy(*d, h.data(), h.size() * sizeof(V), cudaMemcpyHostToDevice));
-  return HPCX_OK;
 }
 
 }  // namespace
@@ -823,32 +758,7 @@ hpcx_status hpcx_csr_create(hpcx_ctx ctx, const hpcx_csr_desc *d, const hpcx_csr
     HPCX_TRY_CUDA(cudaMalloc(&A->d_partials, std::max<size_t>((size_t)nchunks, 1) * A->es));
   }
 
-  if (A->kernel == HPCX_SPMV_SELL) {
-    // The SELL repack runs on the host: copies of row_ptr (widened), col and val.
-    std::vector<int32_t> rp32(d->nrows + 1);
-    HPCX_TRY_CUDA(cudaMemcpy(rp32.data(), A->d_row_ptr, rp32.size() * 4, cudaMemcpyDeviceToHost));
-    std::vector<int64_t> rp(rp32.begin(), rp32.end());
-    std::vector<int32_t> hcol(d->nnz);
-    std::vector<unsigned char> hval((size_t)d->nnz * A->es);
-    if (d->nnz) {
-      HPCX_TRY_CUDA(cudaMemcpy(hcol.data(), d->col_idx, (size_t)d->nnz * 4, cudaMemcpyDefault));
-      HPCX_TRY_CUDA(cudaMemcpy(hval.data(), d->values, hval.size(), cudaMemcpyDefault));
-    }
-    std::vector<int32_t> scol;
-    if (A->dtype == HPCX_F64) {
-      std::vector<double> sval;
-      build_sell<double>(A, rp.data(), hcol.data(), (const double *)hval.data(), scol, sval);
-      HPCX_TRY(upload_vec(ctx, sval, (double **)&A->d_sell_val));
-    } else {
-      std::vector<float> sval;
-      build_sell<float>(A, rp.data(), hcol.data(), (const float *)hval.data(), scol, sval);
-      HPCX_TRY(upload_vec(ctx, sval, (float **)&A->d_sell_val));
-    }
-    HPCX_TRY(upload_vec(ctx, scol, &A->d_sell_col));
-    HPCX_TRY(upload_vec(ctx, A->h_perm, &A->d_perm));
-    HPCX_TRY(upload_vec(ctx, A->h_slice_len, &A->d_slice_len));
-    HPCX_TRY(upload_vec(ctx, A->h_slice_ptr, &A->d_slice_ptr));
-  }
+  if (A->kernel == HPCX_SPMV_SELL) HPCX_TRY(sell_build(A, maxlen));  // on the device: sell_build.cu
   // the memsets and copies above ran on the legacy stream; the context's streams are
   // non-blocking, so make everything visible before anything is queued on them
   HPCX_TRY_CUDA(cudaDeviceSynchronize());

@@ -82,6 +82,7 @@ struct HubTables {
   void *head_out = nullptr, *tail_out = nullptr;  // per warp range partials
 };
 hpcx_status hub_build(hpcx_csr A);
+hpcx_status sell_build(hpcx_csr A, int64_t maxlen);  // sell_build.cu: SELL-C-sigma arrays on the device
 hpcx_status hub_launch(hpcx_csr A, const void *x, void *y, cudaStream_t s);
 void hub_free(hpcx_csr A);
 
@@ -109,8 +110,6 @@ struct hpcx_csr_s {
   // SELL-C-sigma
   int32_t sell_c = 0, sell_sigma = 0;
   int64_t sell_nslices = 0, sell_padded = 0;
-  std::vector<int32_t> h_perm, h_slice_len;
-  std::vector<int64_t> h_slice_ptr;
   int32_t *d_perm = nullptr, *d_slice_len = nullptr, *d_sell_col = nullptr;
   int64_t *d_slice_ptr = nullptr;
   void *d_sell_val = nullptr;
