@@ -417,7 +417,10 @@ HPCX_API hpcx_status hpcx_stencil_dist_plan(hpcx_ctx ctx, hpcx_grid in, hpcx_gri
  * (hpcx_grid_pack_face's kernel) around one grouped NCCL send/recv.  Either exchange runs on the
  * comm stream beside the part of the block that needs no ghosts; the two boundary strips follow.
  * px == 1 is the y-slab split of hpcx_stencil_dist_plan.  Results are bit-identical to the
- * single-GPU sweep of the global grid.  Collective over the communicator. */
+ * single-GPU sweep of the global grid, i.e. to the reference loops BM_x_blur / BM_y_blur
+ * (tests/test_hpc_benchmark/test_hpc_benchmark.cpp:354-368, 444-457) run on the whole grid; the
+ * split follows the reference's static chunking idiom (same file, 1356, 1371-1372) along both
+ * axes.  Collective over the communicator. */
 HPCX_API hpcx_status hpcx_stencil_dist_plan_blocks(hpcx_ctx ctx, hpcx_grid in, hpcx_grid out,
                                                    const hpcx_stencil_desc *st, int32_t py, int32_t px,
                                                    hpcx_halo_plan *out_plan);
