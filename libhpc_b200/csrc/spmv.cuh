@@ -42,6 +42,7 @@ struct SpmvDistArgs {
 // Chunking of a host-operand product (spmv.cu: pipe_analyse / spmv_host_pipelined).
 struct PipePlan {
   int state = 0;                 // 0 = not analysed yet, 1 = usable, -1 = not usable
+  int K = 0;                     // chunks (= pieces of x)
   std::vector<int64_t> first;    // first row block of each chunk (+ end)
   std::vector<int32_t> cmax;     // largest travelling column index each chunk reads
   std::vector<cudaEvent_t> ev;   // [0, K) x pieces landed, [K, 2K) chunk computed, 2K entry, 2K+1 done
