@@ -39,6 +39,19 @@ def barrier(ctx: Context) -> None:
     ctx.check(ctx.lib.hpcx_comm_barrier(ctx.h))
 
 
+def block_bounds(ny: int, nx: int, py: int, px: int, rank: int):
+    """(y0, y1, x0, x1) of the block rank = ry * px + rx owns in a py x px split of an ny x nx
+    grid: both axes cut by the reference's static chunking idiom (hpcx_partition_slabs,
+    test_hpc_benchmark.cpp:1356,1371-1372), which is what hpcx_stencil_dist_plan_blocks expects —
+    blocks of one block row share their y extent, blocks of one block column their x extent."""
+    from .api import partition_slabs
+    if py < 1 or px < 1 or not 0 <= rank < py * px:
+        raise ValueError("rank outside the py x px block grid")
+    by, bx = partition_slabs(ny, py), partition_slabs(nx, px)
+    ry, rx = divmod(rank, px)
+    return int(by[ry]), int(by[ry + 1]), int(bx[rx]), int(bx[rx + 1])
+
+
 class HaloPlan:
     """Distributed sweeps (hpcx_stencil_dist_*): JACOBI7 over z-slabs, the reference's box sweeps
     over y-slabs (radius = the reference's nblur) or, with blocks=(py, px), over a py x px grid of

@@ -209,3 +209,23 @@ def test_halo_index_maps_match_reference_index_math():
                     assert got_s.tolist() == want_s and got_r.tolist() == want_r, (dims, lo, hi, axis, side, width)
     with pytest.raises(hp.HpcxError):
         hp.grid_halo_maps((5, 7), 1, 1, 0, 0, 2)  # wider than the ghost region
+
+
+@pytest.mark.parametrize("py,px", [(1, 1), (2, 1), (1, 3), (2, 2), (4, 2), (3, 5)])
+def test_block_bounds_tile_the_grid(py, px):
+    """dist.block_bounds: the py x px blocks cover every cell of the grid exactly once, blocks of one
+    block row share their rows and blocks of one block column their columns (what
+    hpcx_stencil_dist_plan_blocks requires of neighbouring blocks)."""
+    from libhpc_b200 import dist as hd
+    ny, nx = 53, 130
+    seen = np.zeros((ny, nx), dtype=np.int32)
+    rows, cols = {}, {}
+    for rank in range(py * px):
+        y0, y1, x0, x1 = hd.block_bounds(ny, nx, py, px, rank)
+        seen[y0:y1, x0:x1] += 1
+        ry, rx = divmod(rank, px)
+        assert rows.setdefault(ry, (y0, y1)) == (y0, y1)
+        assert cols.setdefault(rx, (x0, x1)) == (x0, x1)
+    assert (seen == 1).all()
+    with pytest.raises(ValueError):
+        hd.block_bounds(ny, nx, py, px, py * px)
