@@ -125,6 +125,6 @@ def _worker(rank, world, port, case):
 
 
 @pytest.mark.parametrize("case,world", [("spmv_op27", 2), ("spmv_rmat", 2), ("spmv_rmat", 3),
-                                        ("jacobi", 2), ("jacobi", 3)])
+                                        ("jacobi", 2), ("jacobi", 3), ("spmv_op27", 4), ("spmv_rmat", 4)])
 def test_partitioned_equals_global(case, world):
     mp.spawn(_worker, args=(world, _free_port(), case), nprocs=world, join=True)
