@@ -170,6 +170,25 @@ HPCX_API hpcx_status hpcx_stencil_sweep(hpcx_grid in, hpcx_grid out,
  * HPCX_VARIANT_DIRECT the direct one. */
 HPCX_API hpcx_status hpcx_conv2d(hpcx_grid in, hpcx_grid out, const void *weights, int32_t kh,
                                  int32_t kw, int32_t variant, void *stream);
+/* No counterpart in the reference (it never touches a GPU on this path): the direct convolution
+ * sweep of hpcx_conv2d for callers that are not allowed to allocate device memory while they run.
+ * Typical cases: an application that has given all remaining HBM to its own arena after set-up,
+ * so that any further cudaMalloc fails; a time-step loop that cannot tolerate the device-wide
+ * synchronisation a cudaMalloc/cudaFree implies; a driver configuration without the stream-ordered
+ * pool behind cudaMallocAsync (which hpcx_conv2d's direct path uses for its weights).
+ * Same arguments, arithmetic and results as hpcx_conv2d(..., HPCX_VARIANT_DIRECT, stream); the
+ * grids are created beforehand as usual.  The weights are staged in an array inside libhpcx.so's
+ * device image instead of a per-call buffer, and the call makes no cudaMalloc, cudaFree or pool
+ * request of any kind.
+ *   limit    kh*kw*sizeof(dtype) <= 8192 bytes (1024 fp64 taps / 2048 fp32 taps); larger kernels
+ *            are rejected with HPCX_INVALID_ARG and a message naming both sizes.
+ *   cost     every GPU that loads the library holds those 8 KB until the process exits.
+ *   set-up   the first call on each device looks up the array's device address with that device
+ *            current; issue that first call outside any stream capture.
+ *   sharing  all contexts and streams of a device use the same array: calls that overlap on the
+ *            GPU race on the weights, so serialise them (one stream, or events between streams). */
+HPCX_API hpcx_status hpcx_conv2d_static_scratch(hpcx_grid in, hpcx_grid out, const void *weights,
+                                                int32_t kh, int32_t kw, void *stream);
 /* out(x, y) = in(y, x) over the interiors of two 2-D grids of shapes (ny, nx) and (nx, ny), any
  * ghost widths — BM_transpose / BM_transpose_tiling (test_hpc_benchmark.cpp:669-700). */
 HPCX_API hpcx_status hpcx_grid_transpose(hpcx_grid in, hpcx_grid out, void *stream);

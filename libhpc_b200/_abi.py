@@ -93,6 +93,7 @@ PROTOTYPES = {
     "hpcx_grid_export_halo_maps": (_i32, [_P(GridDesc), _i32, _i32, _i32, _P(_i64), _P(_i64), _vp, _vp]),
     "hpcx_stencil_sweep": (_i32, [_vp, _vp, _P(StencilDesc), _i32, _vp]),
     "hpcx_conv2d": (_i32, [_vp, _vp, _vp, _i32, _i32, _i32, _vp]),
+    "hpcx_conv2d_static_scratch": (_i32, [_vp, _vp, _vp, _i32, _i32, _vp]),
     "hpcx_grid_transpose": (_i32, [_vp, _vp, _vp]),
     "hpcx_grid_face_elems": (_i32, [_vp, _i32, _i32, _P(_i64)]),
     "hpcx_grid_pack_face": (_i32, [_vp, _i32, _i32, _i32, _vp, _i32, _vp]),

@@ -23,6 +23,7 @@
 #include "grid.cuh"
 
 #include <algorithm>
+#include <atomic>
 #include <utility>
 
 using namespace hpcx;
@@ -176,6 +177,50 @@ transpose_tile_kernel(const T *__restrict__ in, T *__restrict__ out, Geom2 gi, G
   }
 }
 
+// ---- weights scratch held by the library itself (hpcx_conv2d_static_scratch)
+// One copy per GPU that loads libhpcx.so, resident until the process exits: 1024 taps of the
+// widest dtype = 8 KB.  In host code `conv_static_weights` is only a handle for the runtime's
+// symbol table — never a device address — so the host side asks cudaGetSymbolAddress for the
+// address on each device and hands THAT to the kernel.
+constexpr size_t kStaticScratchBytes = (size_t)kMaxTaps * sizeof(double);
+constexpr int kStaticScratchMaxDevices = 64;
+}  // namespace
+
+static __device__ __align__(256) unsigned char conv_static_weights[kStaticScratchBytes];
+
+namespace {
+
+std::atomic<void *> g_static_weights_addr[kStaticScratchMaxDevices];
+
+// Device address of conv_static_weights on the CURRENT device, resolved once per device.
+// Idempotent, so two threads resolving the same device at once both store the same value.
+hpcx_status static_weights_addr(hpcx_ctx ctx, void **out) {
+  if (ctx->device < 0 || ctx->device >= kStaticScratchMaxDevices)
+    return fail(ctx, HPCX_UNSUPPORTED, "hpcx_conv2d_static_scratch: device ordinal beyond 63");
+  void *p = g_static_weights_addr[ctx->device].load(std::memory_order_acquire);
+  if (!p) {
+    HPCX_CUDA(ctx, cudaGetSymbolAddress(&p, conv_static_weights));
+    if (!p) return fail(ctx, HPCX_CUDA_ERROR, "cudaGetSymbolAddress gave no address for the weights scratch");
+    g_static_weights_addr[ctx->device].store(p, std::memory_order_release);
+  }
+  *out = p;
+  return HPCX_OK;
+}
+
+// The direct kernel with its weights staged in the library-held array instead of a per-call
+// allocation.  No cudaMalloc / cudaFree / pool call on this path.
+template <typename T>
+hpcx_status conv2d_static_t(hpcx_grid in, hpcx_grid out, const T *w, int kh, int kw, void *scratch, cudaStream_t s) {
+  hpcx_ctx ctx = in->ctx;
+  const Geom2 gi = geom2(in), go = geom2(out);
+  T *dw = static_cast<T *>(scratch);
+  // every tap the kernel reads is overwritten here, so nothing left by an earlier call is used
+  HPCX_CUDA(ctx, cudaMemcpyAsync(dw, w, (size_t)kh * kw * sizeof(T), cudaMemcpyHostToDevice, s));
+  dim3 block(64, 4), grid((unsigned)((go.nx + 63) / 64), (unsigned)((go.ny + 3) / 4));
+  conv2d_direct_kernel<T><<<grid, block, 0, s>>>((const T *)in->dev, (T *)out->dev, gi, go, kh, kw, dw);
+  return after_launch(ctx, "conv2d_direct_kernel (static scratch)");
+}
+
 template <typename T>
 hpcx_status conv2d_t(hpcx_grid in, hpcx_grid out, const T *w, int kh, int kw, int variant, cudaStream_t s) {
   hpcx_ctx ctx = in->ctx;
@@ -239,6 +284,53 @@ hpcx_status hpcx_conv2d(hpcx_grid in, hpcx_grid out, const void *weights, int32_
   if (rc != HPCX_OK) return rc;
   if (!stream) HPCX_CUDA(ctx, cudaStreamSynchronize(s));
   return HPCX_OK;
+}
+
+// hpcx_conv2d's direct sweep for callers that must not allocate while they run: a solver that has
+// already handed every free byte of HBM to its own arena (any later cudaMalloc fails), a time-step
+// loop that cannot afford cudaMalloc's device-wide synchronisation, or a process whose driver set-up
+// has no stream-ordered memory pool for cudaMallocAsync.  The grids are made once at set-up like
+// any others; this call itself only copies the weights into the library's own 8 KB device array
+// and launches.  The first call on a device resolves that array's address (cudaGetSymbolAddress,
+// with the device made current); make it before starting any stream capture.  All calls on a
+// device share the array, so two calls in flight at once race on the weights.
+hpcx_status hpcx_conv2d_static_scratch(hpcx_grid in, hpcx_grid out, const void *weights, int32_t kh,
+                                       int32_t kw, void *stream) {
+  if (!in || !out || !weights) return HPCX_INVALID_ARG;
+  hpcx_ctx ctx = in->ctx;
+  HPCX_REQUIRE(ctx, in->ctx == out->ctx && in != out && in->dev != out->dev, "in and out must be two grids of one context");
+  if (in->desc.ndim != 2 || out->desc.ndim != 2) return fail(ctx, HPCX_UNSUPPORTED, "conv2d takes 2-D grids");
+  HPCX_REQUIRE(ctx, in->desc.dtype == out->desc.dtype, "grids differ in dtype");
+  HPCX_REQUIRE(ctx, in->n[1] == out->n[1] && in->n[2] == out->n[2], "grids differ in logical extent");
+  HPCX_REQUIRE(ctx, kh >= 1 && kw >= 1, "kernel extent must be at least 1 x 1");
+  const size_t es = dtype_size(in->desc.dtype);
+  if ((size_t)kh * (size_t)kw * es > kStaticScratchBytes) {
+    char msg[200];
+    snprintf(msg, sizeof msg,
+             "hpcx_conv2d_static_scratch: %d x %d taps of %zu bytes need %zu bytes, the library-held "
+             "scratch is %zu bytes; use hpcx_conv2d",
+             kh, kw, es, (size_t)kh * (size_t)kw * es, kStaticScratchBytes);
+    return fail(ctx, HPCX_INVALID_ARG, msg);
+  }
+  HPCX_REQUIRE(ctx, in->ghi[1] >= kh - 1 && in->ghi[2] >= kw - 1,
+               "the input grid needs High_Bound >= kernel extent - 1 (taps reach y+kh-1, x+kw-1)");
+  HPCX_REQUIRE(ctx, in->n[1] <= 65535LL * 4, "grid too tall for the conv2d sweep");
+  int prev = -1;
+  HPCX_CUDA(ctx, cudaGetDevice(&prev));
+  if (prev != ctx->device) HPCX_CUDA(ctx, cudaSetDevice(ctx->device));
+  cudaStream_t s = stream ? (cudaStream_t)stream : ctx->compute;
+  void *scratch = nullptr;
+  hpcx_status rc = static_weights_addr(ctx, &scratch);
+  if (rc == HPCX_OK)
+    rc = in->desc.dtype == HPCX_F64
+             ? conv2d_static_t<double>(in, out, (const double *)weights, kh, kw, scratch, s)
+             : conv2d_static_t<float>(in, out, (const float *)weights, kh, kw, scratch, s);
+  if (rc == HPCX_OK && !stream) {
+    cudaError_t e = cudaStreamSynchronize(s);
+    if (e != cudaSuccess) rc = fail(ctx, HPCX_CUDA_ERROR, std::string("cudaStreamSynchronize: ") + cudaGetErrorString(e));
+  }
+  if (prev != ctx->device) cudaSetDevice(prev);
+  return rc;
 }
 
 hpcx_status hpcx_grid_transpose(hpcx_grid in, hpcx_grid out, void *stream) {
