@@ -476,8 +476,20 @@ def run_ours(args, rank: int, world: int, local: int):
     e2e_value = nbytes_rank * world * k_e2e / dt_e2e / 1e9
     checksum = float(np.abs(y_pin.numpy()).sum())
     if world > 1:
-        # the distributed e2e result must be the device-resident one
+        # the distributed e2e result must be the device-resident one — checked on a product issued
+        # after NaNs have gone through the handle (owned entries and, by the exchange, every halo
+        # slot), so that an entry read before its upload or push had landed could not go unnoticed
         y_dev = torch.empty_like(yd)
+        nan = torch.full_like(xd, float("nan"))
+        ctx.memcpy((xfull, hp.MEM_DEVICE), nan, nloc * 8)
+        barrier()
+        D.spmv_dist(x_arg, y_dev, stream)
+        stream.synchronize()
+        barrier()
+        del nan
+        D.spmv_dist_host(x_pin.numpy(), y_pin.numpy(), stream)
+        stream.synchronize()
+        barrier()
         ctx.memcpy((xfull, hp.MEM_DEVICE), xd, nloc * 8)
         barrier()
         D.spmv_dist(x_arg, y_dev, stream)

@@ -485,6 +485,7 @@ hpcx_status spmv_launch_fixup_tables(hpcx_csr A, const int32_t *long_row, const 
 
 namespace {
 hpcx_status pipe_analyse(hpcx_csr A, hpcx::PipePlan &P, const std::vector<RowBlock> &blocks, int64_t nlong, int64_t nx);
+hpcx_status pipe_dist_pieces(hpcx_csr A, hpcx::PipePlan &P);
 hpcx_status spmv_host_pipelined(hpcx_csr A, hpcx::PipePlan &P, const RowBlock *d_blocks,
                                 const std::vector<RowBlock> &blocks, int64_t nx, void *d_x, const void *x, void *y,
                                 cudaStream_t s, const std::function<hpcx_status()> &dist);
@@ -494,8 +495,14 @@ namespace hpcx {
 // HPCX_UNSUPPORTED when the matrix does not qualify (long rows, too few interior blocks).
 hpcx_status spmv_dist_host_pipelined(hpcx_csr A, const void *x, void *y, cudaStream_t s,
                                      const std::function<hpcx_status()> &push_and_boundary) {
-  if (A->pipe_dist.state == 0)
+  if (A->pipe_dist.state == 0) {
     if (hpcx_status st = pipe_analyse(A, A->pipe_dist, A->h_blocks_int, A->nlong_dist, A->nloc)) return st;
+    if (A->pipe_dist.state == 1)
+      if (hpcx_status st = pipe_dist_pieces(A, A->pipe_dist)) {
+        A->pipe_dist.state = 0;
+        return st;
+      }
+  }
   if (A->pipe_dist.state != 1) return HPCX_UNSUPPORTED;
   if (!A->d_y) HPCX_CUDA(A->ctx, cudaMalloc(&A->d_y, std::max<size_t>((size_t)A->nrows * A->es, 1)));
   return spmv_host_pipelined(A, A->pipe_dist, A->d_blocks_int, A->h_blocks_int, A->nloc, A->d_xfull, x, y, s,
@@ -540,6 +547,36 @@ col_range_kernel(const int32_t *__restrict__ col, int64_t nnz, int32_t *__restri
     atomicMin(minmax + 0, lo);
     atomicMax(minmax + 1, hi);
   }
+}
+
+// Piece j of x is entries [nx * j / K, nx * (j + 1) / K).  Which piece holds entry v?
+__device__ __forceinline__ int piece_of(int32_t v, int64_t nx, int K) {
+  int j = (int)(((int64_t)v * K) / nx);
+  while (j + 1 < K && nx * (j + 1) / K <= v) ++j;
+  while (j > 0 && nx * j / K > v) --j;
+  return j;
+}
+// Pieces of the owned x (entries below nx) referenced by the nonzeros of a set of row blocks / by
+// an index list: bit j of *mask = piece j.  K <= 32.
+__global__ void __launch_bounds__(256)
+piece_mask_blocks_kernel(const int32_t *__restrict__ col, const RowBlock *__restrict__ blocks, int64_t nblocks,
+                         int32_t nx, int K, uint32_t *__restrict__ mask) {
+  uint32_t m = 0;
+  for (int64_t b = blockIdx.x; b < nblocks; b += gridDim.x)
+    for (int64_t i = blocks[b].p0 + threadIdx.x; i < blocks[b].p1; i += blockDim.x) {
+      const int32_t v = col[i];
+      if (v < nx) m |= 1u << piece_of(v, nx, K);
+    }
+  m = __reduce_or_sync(0xffffffffu, m);
+  if ((threadIdx.x & 31) == 0 && m) atomicOr(mask, m);
+}
+__global__ void __launch_bounds__(256)
+piece_mask_list_kernel(const int32_t *__restrict__ idx, int64_t n, int32_t nx, int K, uint32_t *__restrict__ mask) {
+  uint32_t m = 0;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    m |= 1u << piece_of(idx[i], nx, K);
+  m = __reduce_or_sync(0xffffffffu, m);
+  if ((threadIdx.x & 31) == 0 && m) atomicOr(mask, m);
 }
 
 // 32 chunks: the last y chunk leaves about two chunk times after the last x piece has landed
@@ -591,12 +628,43 @@ hpcx_status pipe_analyse(hpcx_csr A, hpcx::PipePlan &P, const std::vector<RowBlo
   return HPCX_OK;
 }
 
+// Distributed plan: which pieces of the owned x does the launch that pushes this rank's boundary
+// entries and computes its boundary rows read?  Those pieces go up first and that launch waits
+// for all of them — a boundary row or a send entry anywhere in the block is covered, not only
+// those at its two ends.
+hpcx_status pipe_dist_pieces(hpcx_csr A, hpcx::PipePlan &P) {
+  static_assert(kPipeChunks <= 32, "the piece mask is one 32-bit word");
+  hpcx_ctx ctx = A->ctx;
+  uint32_t *d_mask = nullptr;
+  HPCX_CUDA(ctx, cudaMalloc((void **)&d_mask, sizeof(uint32_t)));
+  cudaError_t e = cudaMemsetAsync(d_mask, 0, sizeof(uint32_t), ctx->compute);
+  const int64_t nbnd = (int64_t)A->h_blocks_bnd.size();
+  if (e == cudaSuccess && nbnd > 0) {
+    const unsigned g = (unsigned)std::min<int64_t>(nbnd, 8LL * ctx->sm_count);
+    piece_mask_blocks_kernel<<<g, 256, 0, ctx->compute>>>(A->d_col, A->d_blocks_bnd, nbnd, (int32_t)A->nloc, P.K, d_mask);
+    ctx->launches++;
+  }
+  if (e == cudaSuccess && A->nsend > 0) {
+    const unsigned g = (unsigned)std::min<int64_t>((A->nsend + 255) / 256, 8LL * ctx->sm_count);
+    piece_mask_list_kernel<<<g, 256, 0, ctx->compute>>>(A->d_send_idx, A->nsend, (int32_t)A->nloc, P.K, d_mask);
+    ctx->launches++;
+  }
+  if (e == cudaSuccess) e = cudaGetLastError();
+  if (e == cudaSuccess) e = cudaMemcpyAsync(&P.dist_mask, d_mask, sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->compute);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->compute);
+  cudaFree(d_mask);
+  if (e != cudaSuccess) return fail(ctx, HPCX_CUDA_ERROR, std::string("pipe_dist_pieces: ") + cudaGetErrorString(e));
+  return HPCX_OK;
+}
+
 // y(host) = A x(host): x pieces on the copy-in stream, row chunks on s as their columns land, y
 // chunks on the copy-out stream.  The caller synchronises s afterwards.
-// Distributed matrices (dist != nullptr): the LAST piece of x goes up first, then pieces 0, 1, ...;
-// once the last and the first have landed `dist` is called — it queues the launch that pushes this
-// rank's boundary entries to the neighbours and computes the boundary rows — and the interior
-// chunks follow as in the single-GPU case, so the exchange overlaps the copies too.
+// Distributed matrices (dist != nullptr): the pieces of x that the push CTAs and the boundary rows
+// read (P.dist_mask — for a banded operator the two ends of the owned block) go up first, then the
+// others in ascending order; once the first group has landed `dist` is called — it queues the
+// launch that pushes this rank's boundary entries to the neighbours and computes the boundary
+// rows — and the interior chunks follow as in the single-GPU case, so the exchange overlaps the
+// copies too.
 hpcx_status spmv_host_pipelined(hpcx_csr A, hpcx::PipePlan &P, const RowBlock *d_blocks,
                                 const std::vector<RowBlock> &blocks, int64_t nx, void *d_x, const void *x, void *y,
                                 cudaStream_t s, const std::function<hpcx_status()> &dist) {
@@ -609,31 +677,41 @@ hpcx_status spmv_host_pipelined(hpcx_csr A, hpcx::PipePlan &P, const RowBlock *d
   HPCX_CUDA(ctx, cudaEventRecord(entry, s));
   HPCX_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_in, entry, 0));
   HPCX_CUDA(ctx, cudaStreamWaitEvent(ctx->copy_out, entry, 0));
-  auto copy_piece = [&](int j) -> hpcx_status {
-    const int64_t a = piece(j), b = piece(j + 1);
+  // copy order; ex[p] is recorded after the p-th copy, and the copies share one stream, so it
+  // also covers every piece copied before it
+  int order[kPipeChunks], upto[kPipeChunks];  // upto[j]: position by which pieces 0..j have all been copied
+  int nfirst = 0;
+  if (dist)
+    for (int j = 0; j < K; ++j)
+      if (P.dist_mask >> j & 1u) order[nfirst++] = j;
+  {
+    int n = nfirst;
+    for (int j = 0; j < K; ++j)
+      if (!dist || !(P.dist_mask >> j & 1u)) order[n++] = j;
+    int pos[kPipeChunks];
+    for (int p = 0; p < K; ++p) pos[order[p]] = p;
+    for (int j = 0, m = 0; j < K; ++j) upto[j] = m = std::max(m, pos[j]);
+  }
+  for (int p = 0; p < K; ++p) {
+    const int64_t a = piece(order[p]), b = piece(order[p] + 1);
     HPCX_CUDA(ctx, cudaMemcpyAsync((char *)d_x + a * es, (const char *)x + a * es, (size_t)(b - a) * es,
                                    cudaMemcpyHostToDevice, ctx->copy_in));
-    HPCX_CUDA(ctx, cudaEventRecord(ex[j], ctx->copy_in));
-    return HPCX_OK;
-  };
-  const int last_copied = dist ? K - 2 : K - 1;  // the piece that lands last
-  if (dist)
-    if (hpcx_status st = copy_piece(K - 1)) return st;
-  for (int j = 0; j <= last_copied; ++j)
-    if (hpcx_status st = copy_piece(j)) return st;
-  int waited = -1;
+    HPCX_CUDA(ctx, cudaEventRecord(ex[p], ctx->copy_in));
+  }
+  int waited = -1;  // position in the copy order that s has waited for
   if (dist) {
-    HPCX_CUDA(ctx, cudaStreamWaitEvent(s, ex[0], 0));  // pieces K-1 and 0: both ends of the owned block
-    waited = 0;
+    if (nfirst > 0) {
+      HPCX_CUDA(ctx, cudaStreamWaitEvent(s, ex[nfirst - 1], 0));
+      waited = nfirst - 1;
+    }
     if (hpcx_status st = dist()) return st;
   }
   for (int c = 0; c < K; ++c) {
-    int need = waited < 0 ? 0 : waited;
+    int need = 0;  // last piece this chunk reads
     while (need + 1 < K && piece(need + 1) <= P.cmax[c]) ++need;
-    if (need > last_copied) need = last_copied;  // piece K-1 went first: everything has landed with the last one
-    if (need > waited) {
-      HPCX_CUDA(ctx, cudaStreamWaitEvent(s, ex[need], 0));
-      waited = need;
+    if (upto[need] > waited) {
+      waited = upto[need];
+      HPCX_CUDA(ctx, cudaStreamWaitEvent(s, ex[waited], 0));
     }
     const int64_t b0 = P.first[c], b1 = P.first[c + 1];
     hpcx_status st = hpcx::spmv_launch_blocks(A, d_blocks + b0, b1 - b0, d_x, A->d_y, s, nullptr, nullptr);
@@ -649,7 +727,7 @@ hpcx_status spmv_host_pipelined(hpcx_csr A, hpcx::PipePlan &P, const RowBlock *d
   }
   HPCX_CUDA(ctx, cudaEventRecord(done, ctx->copy_out));
   HPCX_CUDA(ctx, cudaStreamWaitEvent(s, done, 0));
-  if (waited < last_copied) HPCX_CUDA(ctx, cudaStreamWaitEvent(s, ex[last_copied], 0));  // x fully landed before s goes on
+  if (waited < K - 1) HPCX_CUDA(ctx, cudaStreamWaitEvent(s, ex[K - 1], 0));  // x fully landed before s goes on
   return HPCX_OK;
 }
 

@@ -46,6 +46,8 @@ struct PipePlan {
   std::vector<int64_t> first;    // first row block of each chunk (+ end)
   std::vector<int32_t> cmax;     // largest travelling column index each chunk reads
   std::vector<cudaEvent_t> ev;   // [0, K) x pieces landed, [K, 2K) chunk computed, 2K entry, 2K+1 done
+  uint32_t dist_mask = 0;        // distributed plan: bit j = piece j of the owned x is read by the push CTAs
+                                 // or by a boundary row, i.e. must have landed before that launch
 };
 
 // What one rank sees of another for the fused x-halo transport (dist.cu: csr_peer_wire).

@@ -195,7 +195,10 @@ def main():
         gb.destroy()
 
     # ---- SpMV: banded (C4 shape) by rows, power-law by nnz
+    # op27(48): 6+ planes of 2304 rows per rank at world <= 8 — enough interior row blocks for the
+    # pipelined host-operand path, with boundary planes far wider than one of its 32 x pieces
     for name, (rp, col, val), mode in (("op27", synth.op27(16, index_dtype=np.int64), 0),
+                                       ("op27_48", synth.op27(48, index_dtype=np.int64), 0),
                                        ("rmat", synth.rmat(13, 16, 24, index_dtype=np.int64), 1)):
         n = len(rp) - 1
         x = synth.field(42, n, val.dtype)
@@ -224,12 +227,30 @@ def main():
             # host operands: this rank's x block in (pinned), its y block out — pipelined against PCIe
             # and the exchange with the fused transport, copy-product-copy otherwise; same bits as
             # the device-resident product
-            yd_ref = yd.clone()
-            xh = torch.from_numpy(x2[r0:r1].copy()).pin_memory()
+            # Every product before this one left its x in the handle's [owned | halo] buffer, so the
+            # host-operand call gets an x the handle has never seen, after a product of NaNs has
+            # poisoned both the owned entries and (through the exchange) the halo slots on every
+            # rank: an entry read before its upload or its push has landed shows up as NaN.
+            xd.fill_(float("nan"))
+            torch.cuda.synchronize()
+            D.spmv_dist(xd, yd)
+            x3 = synth.field(44, n, val.dtype)
+            xh = torch.from_numpy(x3[r0:r1].copy()).pin_memory()
             yh = torch.full((r1 - r0,), float("nan"), dtype=xh.dtype).pin_memory()
-            for _ in range(2):
-                D.spmv_dist_host(xh.numpy(), yh.numpy())
-            assert bits_equal(yh.numpy(), yd_ref.cpu().numpy()), (rank, name, transport, "dist_host")
+            before = ctx.launch_count()
+            D.spmv_dist_host(xh.numpy(), yh.numpy())
+            if name == "op27_48" and transport == 1 and world > 1:
+                assert ctx.launch_count() - before >= 32, "the pipelined host-operand path was not taken"
+            assert_spmv_close(yh.numpy(), oracle.spmv(rp, col, val, x3)[r0:r1],
+                              oracle.spmv_abs(rp, col, val, x3)[r0:r1], tol)
+            first = yh.numpy().copy()
+            D.spmv_dist_host(xh.numpy(), yh.numpy())
+            assert bits_equal(yh.numpy(), first), (rank, name, transport, "dist_host twice")
+            # same bits as the device-resident product of the same x
+            xd.copy_(xh.cuda())
+            torch.cuda.synchronize()
+            D.spmv_dist(xd, yd)
+            assert bits_equal(yh.numpy(), yd.cpu().numpy()), (rank, name, transport, "dist_host")
             if transport == 1 and world > 1 and name == "op27":
                 # rank skew: the last rank arrives 5 s late at the next product.  The flag waits of
                 # the fused transport have no bound by default (like an NCCL receive), so the other
