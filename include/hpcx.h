@@ -61,6 +61,10 @@ typedef struct hpcx_grid_s *hpcx_grid;
 /* ------------------------------------------------------------------ context */
 
 HPCX_API const char *hpcx_version(void);
+/* CUDA devices visible to the process (what cudaGetDeviceCount reports; the reference asks the
+ * runtime directly, lib/gpu/util/include/cudaHelper.cuh:96-101 being its only wrapper layer).
+ * Creates no context.  Returns a negative number when the runtime reports an error. */
+HPCX_API int32_t hpcx_device_count(void);
 /* One context per process and device (one process per GPU). */
 HPCX_API hpcx_status hpcx_init(int32_t device, hpcx_ctx *out);
 HPCX_API hpcx_status hpcx_finalize(hpcx_ctx ctx);
@@ -467,6 +471,19 @@ HPCX_API hpcx_status hpcx_csr_x_buffer(hpcx_csr A, void **x_full);
 HPCX_API hpcx_status hpcx_spmv_dist(hpcx_csr A, const void *x_local, void *y_local,
                                     void *stream);
 
+/* Row-block product with a gathered x (the fallback it prescribes for C5; no
+ * reference counterpart — the reference's only partition idiom is the static chunking of
+ * test_hpc_benchmark.cpp:1356,1369-1377).  A is this rank's contiguous row block created with
+ * GLOBAL column ids (nrows = bounds[rank+1] - bounds[rank], ncols = bounds[nranks]; no
+ * hpcx_csr_set_halo), so hpcx_csr_create picks the kernel from the block's own structure — HUB for
+ * power-law blocks.  x_local: this rank's nrows owned entries (device); x_full: device buffer of
+ * ncols entries that receives every rank's slice (x_local may already be x_full + bounds[rank]);
+ * y_local: nrows entries.  One grouped ncclSend/ncclRecv on `stream`, then the product on the same
+ * stream.  For matrices whose rows reference most of x this moves fewer bytes than the halo lists
+ * of hpcx_csr_set_halo and keeps the single-GPU kernel choice. */
+HPCX_API hpcx_status hpcx_spmv_allgather(hpcx_csr A, const int64_t *bounds, const void *x_local,
+                                         void *x_full, void *y_local, void *stream);
+
 /* ------------------------------------------------ single process, several GPUs
  * Every caller the reference has is a single-process program driving its containers from its own
  * (OpenMP) loops (test_hpc_benchmark.cpp:356); the only multi-stream idiom it contains is driven
@@ -477,7 +494,15 @@ HPCX_API hpcx_status hpcx_spmv_dist(hpcx_csr A, const void *x_local, void *y_loc
  * grid axis), and products / sweeps run through the same kernels and the same fused peer-store
  * transport as the one-process-per-GPU path — the neighbours' buffers are plain peer pointers, and
  * neither NCCL nor CUDA IPC is involved.  dev_ids == NULL selects devices 0 .. ndev-1.
- * Not covered here: the CG solver across devices (its scalar all-reduce is NCCL's). */
+ * Not covered here: the CG solver across devices (its scalar all-reduce is NCCL's).
+ * Flag waits of these contexts are bounded by default (120 s, or HPCX_HALO_TIMEOUT_MS /
+ * hpcx_comm_set_timeout on hpcx_multi_ctx): with one thread queueing every device's kernels, a
+ * launch that fails in the middle of a round would otherwise leave the kernels already queued —
+ * and the thread's next synchronise — waiting for ever.
+ * The fused transports assume that the CTAs of a grid are dispatched in block-index order (the
+ * pushing CTAs come first in every such grid); CUDA does not guarantee that order, it is the
+ * observed behaviour of the hardware scheduler, and the bounded wait is what turns a violation
+ * into an error instead of a hang. */
 typedef struct hpcx_multi_s *hpcx_multi;
 HPCX_API hpcx_status hpcx_init_multi(int32_t ndev, const int32_t *dev_ids, hpcx_multi *out);
 HPCX_API hpcx_status hpcx_multi_finalize(hpcx_multi m);

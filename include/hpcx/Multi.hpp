@@ -38,15 +38,8 @@ class MultiContext {
     if (ids.empty()) {
       n = count;
       if (n <= 0) {
-        // probe: grow until hpcx_init_multi refuses the next device
-        n = 1;
-        for (;;) {
-          hpcx_multi probe = nullptr;
-          const hpcx_status st = hpcx_init_multi(n + 1, nullptr, &probe);
-          if (probe) hpcx_multi_finalize(probe);
-          if (st != HPCX_OK) break;
-          ++n;
-        }
+        n = hpcx_device_count();
+        if (n <= 0) throwStatus(HPCX_CUDA_ERROR, "no CUDA device is visible", __FILE__, __LINE__);
       }
     }
     const hpcx_status st = hpcx_init_multi(n, ids.empty() ? nullptr : ids.data(), &m_);

@@ -76,6 +76,7 @@ PROTOTYPES = {
     "hpcx_last_error_string": (C.c_char_p, [_vp]),
     "hpcx_synchronize": (_i32, [_vp]),
     "hpcx_launch_count": (_i64, [_vp]),
+    "hpcx_device_count": (_i32, []),
     "hpcx_host_alloc": (_i32, [_vp, _sz, _P(_vp)]),
     "hpcx_host_free": (_i32, [_vp, _vp]),
     "hpcx_device_alloc": (_i32, [_vp, _sz, _P(_vp)]),
@@ -148,6 +149,7 @@ PROTOTYPES = {
     "hpcx_multi_grid_upload": (_i32, [_vp, _vp]),
     "hpcx_multi_grid_download": (_i32, [_vp, _vp]),
     "hpcx_multi_stencil_sweep": (_i32, [_vp, _vp, _P(StencilDesc), _i32]),
+    "hpcx_spmv_allgather": (_i32, [_vp, _P(_i64), _vp, _vp, _vp, _vp]),
     "hpcx_cg_create": (_i32, [_vp, _P(_vp)]),
     "hpcx_cg_destroy": (_i32, [_vp]),
     "hpcx_cg_solve": (_i32, [_vp, _vp, _i32, _vp, _i32, _i32, C.c_double, _i32, _P(CgResult), _vp]),

@@ -488,6 +488,14 @@ class DeviceCsr:
         self.ctx.check(self.ctx.lib.hpcx_spmv_dist(self.h, _ptr(x_local)[0], _ptr(y_local)[0],
                                                    _stream(stream)))
 
+    def spmv_allgather(self, bounds, x_local, x_full, y_local, stream=None):
+        """hpcx_spmv_allgather: this handle is a row block with GLOBAL column ids; every rank's slice
+        of x (bounds, world + 1 entries) is gathered into x_full, then the block's kernel runs."""
+        b = np.ascontiguousarray(bounds, dtype=np.int64)
+        self.ctx.check(self.ctx.lib.hpcx_spmv_allgather(self.h, b.ctypes.data_as(C.POINTER(C.c_int64)),
+                                                        _ptr(x_local)[0], _ptr(x_full)[0], _ptr(y_local)[0],
+                                                        _stream(stream)))
+
     def spmv_dist_host(self, x_host, y_host, stream=None):
         """hpcx_spmv_dist_host: host x / y (this rank's owned entries), pipelined against PCIe."""
         px, mx = _ptr(x_host)
@@ -693,8 +701,7 @@ class MultiContext:
     def __init__(self, devices=None):
         self.lib = _abi.load()
         if devices is None:
-            import torch
-            devices = list(range(torch.cuda.device_count()))
+            devices = list(range(max(int(self.lib.hpcx_device_count()), 0)))
         self.devices = [int(d) for d in devices]
         ids = (C.c_int32 * len(self.devices))(*self.devices)
         h = C.c_void_p()

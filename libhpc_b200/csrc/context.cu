@@ -123,6 +123,15 @@ hpcx_status hpcx_synchronize(hpcx_ctx ctx) {
 
 int64_t hpcx_launch_count(hpcx_ctx ctx) { return ctx ? ctx->launches : -1; }
 
+int32_t hpcx_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) {
+    (void)cudaGetLastError();
+    return -1;
+  }
+  return n;
+}
+
 hpcx_status hpcx_host_alloc(hpcx_ctx ctx, size_t bytes, void **out) {
   if (!ctx || !out) return HPCX_INVALID_ARG;
   HPCX_CUDA(ctx, cudaHostAlloc(out, bytes ? bytes : 1, cudaHostAllocDefault));

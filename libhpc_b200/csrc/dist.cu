@@ -970,6 +970,10 @@ hpcx_status hpcx_csr_set_halo(hpcx_csr A, int64_t nloc, int64_t nhalo, const int
   HPCX_REQUIRE(ctx, recv_counts && send_counts && row_kind, "null halo table");
   const int P = ctx->nranks;
   close_csr_peers(A);  // peer windows point into the buffers replaced below
+  // the distributed product, its host-operand pipeline and the CG step all run the STREAM kernel
+  // (its tables always exist); HUB tables built at create time would only hold memory from here on
+  if (A->hub.ready) hub_free(A);
+  if (A->kernel == HPCX_SPMV_HUB) A->kernel = HPCX_SPMV_STREAM;
   A->nloc = nloc;
   A->nhalo = nhalo;
   A->recv_counts.assign(recv_counts, recv_counts + P);
@@ -1180,6 +1184,46 @@ hpcx_status hpcx_csr_x_buffer(hpcx_csr A, void **x_full) {
   if (!A || !x_full) return HPCX_INVALID_ARG;
   HPCX_REQUIRE(A->ctx, A->d_xfull != nullptr, "hpcx_csr_set_halo has not been called");
   *x_full = A->d_xfull;
+  return HPCX_OK;
+}
+
+// Row-block product for matrices whose rows reference most of x anyway (power-law graphs: C5):
+// no [owned | halo] renumbering and no per-entry push — every rank's owned slice of x is gathered
+// into a full-length x on each rank (one grouped send/recv over NVLink; the slices differ in length
+// because the blocks are nnz-balanced), then the block's own kernel — HUB for power-law blocks —
+// runs on the local rows with GLOBAL column ids.  SURVEY.md 8(e): "for C5 fall back to
+// ncclAllGather of x".
+hpcx_status hpcx_spmv_allgather(hpcx_csr A, const int64_t *bounds, const void *x_local, void *x_full,
+                                void *y_local, void *stream) {
+  if (!A || !bounds || !x_local || !x_full || !y_local) return HPCX_INVALID_ARG;
+  HPCX_RANGE("hpcx_spmv_allgather");
+  hpcx_ctx ctx = A->ctx;
+  const int P = ctx->nranks, me = ctx->rank;
+  HPCX_REQUIRE(ctx, A->d_xfull == nullptr, "hpcx_spmv_allgather takes a row block with global column ids (no hpcx_csr_set_halo)");
+  for (int q = 0; q < P; ++q) HPCX_REQUIRE(ctx, bounds[q] <= bounds[q + 1], "bounds must not decrease");
+  HPCX_REQUIRE(ctx, bounds[0] == 0 && bounds[P] == A->ncols && bounds[me + 1] - bounds[me] == A->nrows,
+               "bounds must split the ncols entries of x into one slice per rank, this rank's as long as its row block");
+  if (P > 1 && !ctx->nccl_comm) return fail(ctx, HPCX_NCCL_ERROR, "hpcx_comm_init has not been called");
+  cudaStream_t cs = stream ? (cudaStream_t)stream : ctx->compute;
+  const size_t es = (size_t)A->es;
+  char *xf = static_cast<char *>(x_full);
+  char *mine = xf + (size_t)bounds[me] * es;
+  if (x_local != mine && A->nrows > 0)
+    HPCX_CUDA(ctx, cudaMemcpyAsync(mine, x_local, (size_t)A->nrows * es, cudaMemcpyDeviceToDevice, cs));
+  if (P > 1) {
+    const ncclDataType_t ty = nccl_type(A->dtype);
+    HPCX_NCCL(ctx, g_nccl.GroupStart());
+    for (int d = 1; d < P; ++d) {
+      const int to = (me + d) % P, from = (me - d + P) % P;
+      if (A->nrows > 0) HPCX_NCCL(ctx, g_nccl.Send(mine, (size_t)A->nrows, ty, to, comm_of(ctx), cs));
+      if (bounds[from + 1] > bounds[from])
+        HPCX_NCCL(ctx, g_nccl.Recv(xf + (size_t)bounds[from] * es, (size_t)(bounds[from + 1] - bounds[from]), ty, from,
+                                   comm_of(ctx), cs));
+    }
+    HPCX_NCCL(ctx, g_nccl.GroupEnd());
+  }
+  if (hpcx_status st = hpcx_spmv(A, x_full, HPCX_MEM_DEVICE, y_local, HPCX_MEM_DEVICE, cs)) return st;
+  if (!stream) return sync_and_check(ctx, cs);
   return HPCX_OK;
 }
 

@@ -35,7 +35,7 @@ struct hpcx_multi_grid_s {
   // cached plan of the last Jacobi sweep (per rank), valid for (partner, variant)
   std::vector<hpcx_halo_plan> plans;
   hpcx_multi_grid_s *plan_partner = nullptr;
-  int plan_variant = -1;
+  int plan_variant = -1, plan_zsplit = -1;
 };
 
 namespace {
@@ -88,6 +88,7 @@ void free_plans(hpcx_multi_grid G) {
   G->plans.clear();
   G->plan_partner = nullptr;
   G->plan_variant = -1;
+  G->plan_zsplit = -1;
 }
 
 // Copies the padded slices [s0, s1) of axis 0 between a rank's device grid and the global host
@@ -135,6 +136,11 @@ hpcx_status hpcx_init_multi(int32_t ndev, const int32_t *dev_ids, hpcx_multi *ou
     }
     c->nranks = ndev;
     c->rank = i;
+    // One host thread queues every device's kernels.  If a launch fails half way through a round
+    // the kernels already queued wait for neighbours that will never signal, and the thread's next
+    // synchronise would hang with them: here (unlike the one-process-per-GPU case, where a late
+    // rank is legitimate) the flag waits get a bound unless the caller chose one.
+    if (c->halo_timeout_ns == 0) c->halo_timeout_ns = 120ull * 1000000000ull;
     // one thread launches every device's kernels, and kernels of different devices wait on each
     // other's flags: no kernel may be loaded lazily in the middle of such a sequence
     cudaSetDevice(dev);
@@ -196,6 +202,7 @@ hpcx_status hpcx_multi_csr_create(hpcx_multi m, const hpcx_csr_desc *d, const hp
   if (d->nrows != d->ncols) return mfail(m, HPCX_INVALID_ARG, "the row partition needs a square matrix (x split like y)");
   if (d->idx_bytes != 4 && d->idx_bytes != 8) return mfail(m, HPCX_INVALID_ARG, "idx_bytes must be 4 or 8");
   const int P = (int)m->ctx.size();
+  if (P > 64) return mfail(m, HPCX_UNSUPPORTED, "the peer-store transport supports up to 64 devices (sync-block slots)");
   const int es = (int)dtype_size(d->dtype);
   hpcx_multi_csr M = new (std::nothrow) hpcx_multi_csr_s();
   if (!M) return mfail(m, HPCX_OOM, "host allocation failed");
@@ -242,7 +249,9 @@ hpcx_status hpcx_multi_csr_create(hpcx_multi m, const hpcx_csr_desc *d, const hp
     if (st != HPCX_OK) return bail(st);
     st = lift(m, r, hpcx_csr_set_halo(M->A[r], sz.nloc, sz.nhalo, rc.data(), sc.data(), sidx.data(), kind.data()));
     if (st != HPCX_OK) return bail(st);
-    HPCX_CUDA(ctx, cudaMalloc(&M->A[r]->d_y, std::max<size_t>((size_t)sz.nloc * es, 1)));
+    if (cudaError_t e = cudaMalloc(&M->A[r]->d_y, std::max<size_t>((size_t)sz.nloc * es, 1)); e != cudaSuccess)
+      return bail(lift(m, r, fail(ctx, e == cudaErrorMemoryAllocation ? HPCX_OOM : HPCX_CUDA_ERROR,
+                                  std::string("hpcx_multi_csr_create: y block: ") + cudaGetErrorString(e))));
   }
   if (P > 1) {
     // fused transport: every rank's sync block, then the tables from plain peer pointers
@@ -432,7 +441,8 @@ hpcx_status hpcx_multi_stencil_sweep(hpcx_multi_grid in, hpcx_multi_grid out, co
       if (in->desc.lo < 2 || in->desc.hi < 2 || in->g[r]->n[0] < 2)
         return mfail(m, HPCX_INVALID_ARG, "TEMPORAL over slabs needs ghost widths >= 2 and >= 2 planes on every device");
   // ---- plans: one per rank, wired with plain peer pointers; cached while (in, out, variant) repeat
-  bool reuse = in->plan_partner == out && in->plan_variant == st->variant && (int)in->plans.size() == P;
+  bool reuse = in->plan_partner == out && in->plan_variant == st->variant && in->plan_zsplit == st->zsplit &&
+               (int)in->plans.size() == P;
   for (int r = 0; reuse && r < P; ++r) {
     hpcx_halo_plan p = in->plans[r];
     const bool fwd = in->g[r]->dev == p->buf[0] && out->g[r]->dev == p->buf[1];
@@ -469,6 +479,7 @@ hpcx_status hpcx_multi_stencil_sweep(hpcx_multi_grid in, hpcx_multi_grid out, co
       }
     in->plan_partner = out;
     in->plan_variant = st->variant;
+    in->plan_zsplit = st->zsplit;
   }
   // ---- ghosts of the source iterate: w boundary planes of every slab into its neighbours (peer copies)
   if (hpcx_status rc = sync_all(m)) return rc;

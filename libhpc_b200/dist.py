@@ -12,7 +12,7 @@ import ctypes as C
 import numpy as np
 
 from . import _abi
-from .api import Context, CsrMatrix, DeviceCsr, DeviceGrid, csr_localize, stencil_desc
+from .api import SPMV_STREAM, Context, CsrMatrix, DeviceCsr, DeviceGrid, csr_localize, stencil_desc
 
 
 def init_comm(ctx: Context, rank: int | None = None, world: int | None = None) -> None:
@@ -86,6 +86,9 @@ def distributed_csr(ctx: Context, local: dict, dtype, transport: int = 0, **opts
     A = CsrMatrix(local["local_row_ptr"], local["local_col"],
                   np.ascontiguousarray(local["values"], dtype=dtype),
                   ncols=local["nloc"] + local["nhalo"])
+    # every distributed product runs the STREAM kernel: AUTO would build (and keep) the HUB tables of
+    # a power-law block, a second encoded copy of col / val that nothing here reads
+    opts.setdefault("kernel", SPMV_STREAM)
     D = DeviceCsr(ctx, A, **opts)
     D.set_halo(local)
     if transport:

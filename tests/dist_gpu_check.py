@@ -264,6 +264,38 @@ def main():
                 assert_spmv_close(yd.cpu().numpy(), y_ref[r0:r1], mag[r0:r1], tol)
             D.destroy()
 
+    # ---- row blocks with GLOBAL column ids and a gathered x (hpcx_spmv_allgather): the path for
+    # matrices whose rows reference most of x; the block keeps the single-GPU kernel choice
+    for name, (rp, col, val), mode, kernels in (
+            ("op27", synth.op27(16, index_dtype=np.int64), 0, (hp.SPMV_AUTO,)),
+            ("rmat", synth.rmat(13, 16, 24, index_dtype=np.int64), 1, (hp.SPMV_AUTO, hp.SPMV_HUB, hp.SPMV_STREAM))):
+        n = len(rp) - 1
+        bounds = hp.partition_rows(n, rp, world, mode)
+        r0, r1 = int(bounds[rank]), int(bounds[rank + 1])
+        p0, p1 = int(rp[r0]), int(rp[r1])
+        tol = 1e-12 if val.dtype == np.float64 else 1e-5
+        for kernel in kernels:
+            B = hp.CsrMatrix((rp[r0:r1 + 1] - p0).astype(np.int64), col[p0:p1].copy(), val[p0:p1].copy(), ncols=n)
+            D = hp.DeviceCsr(ctx, B, kernel=kernel)
+            xfull = torch.full((n,), float("nan"), dtype=torch.from_numpy(val[:1]).dtype, device="cuda")
+            yd = torch.full((r1 - r0,), float("nan"), dtype=xfull.dtype, device="cuda")
+            for seed in (42, 43):  # the second product must see the NEW x of every rank
+                x = synth.field(seed, n, val.dtype)
+                xd = torch.from_numpy(x[r0:r1].copy()).cuda()
+                torch.cuda.synchronize()
+                D.spmv_allgather(bounds, xd, xfull, yd)
+                assert_spmv_close(yd.cpu().numpy(), oracle.spmv(rp, col, val, x)[r0:r1],
+                                  oracle.spmv_abs(rp, col, val, x)[r0:r1], tol)
+                assert bits_equal(xfull.cpu().numpy(), x), (rank, name, "gathered x")
+            # owned slice already in place: x_local = x_full + bounds[rank]
+            x = synth.field(44, n, val.dtype)
+            xfull[r0:r1] = torch.from_numpy(x[r0:r1].copy()).cuda()
+            torch.cuda.synchronize()
+            D.spmv_allgather(bounds, xfull[r0:r1], xfull, yd)
+            assert_spmv_close(yd.cpu().numpy(), oracle.spmv(rp, col, val, x)[r0:r1],
+                              oracle.spmv_abs(rp, col, val, x)[r0:r1], tol)
+            D.destroy()
+
     # ---- CG around the distributed product (SPD 27-point operator): iterates vs the global oracle
     rp, col, val = synth.op27(12, index_dtype=np.int64)
     n = len(rp) - 1
