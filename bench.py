@@ -932,6 +932,8 @@ def c5_distributed(args, ctx, torch, stream, world, rank, barrier, max_over_rank
     p0, p1 = int(rp[r0]), int(rp[r1])
     L = hd.localize_rows_distributed((rp[r0:r1 + 1] - p0).astype(np.int64), col[p0:p1], val[p0:p1], bounds, rank, world, nr)
     nnz_total = int(rp[-1])
+    # the same rows with GLOBAL column ids, for the gathered-x variant below
+    rp_blk, col_blk, val_blk = (rp[r0:r1 + 1] - p0).astype(np.int32), col[p0:p1].copy(), val[p0:p1].copy()
     del rp, col, val
     L["local_row_ptr"] = L["local_row_ptr"].astype(np.int32)
     A = hp.CsrMatrix(L["local_row_ptr"], L["local_col"], np.ascontiguousarray(L["values"]), ncols=L["nloc"] + L["nhalo"])
@@ -940,6 +942,7 @@ def c5_distributed(args, ctx, torch, stream, world, rank, barrier, max_over_rank
     D.halo_transport(1)
     log(f"[rank {rank}] C5 block: rows [{r0}, {r1}), {L['nnz_loc']} nnz, {L['nhalo']} halo columns, "
         f"{L['nsend']} sends, set up in {time.time() - t:.1f}s")
+    halo_cols = int(L["nhalo"])
     xfull = D.x_buffer()
     ctx.memcpy((xfull, hp.MEM_DEVICE), x[r0:r1].contiguous(), (r1 - r0) * 4)
     y = torch.empty(r1 - r0, dtype=torch.float32, device="cuda")
@@ -957,18 +960,65 @@ def c5_distributed(args, ctx, torch, stream, world, rank, barrier, max_over_rank
         for _ in range(3):
             step()
         dt, _, _ = time_steps(torch, stream, step, args.steps, barrier)
-    dt = max_over_ranks(dt)
+    dt_push = max_over_ranks(dt)
+    D.destroy()
+    del D, A, L
+    # ---- variant 2 (SURVEY.md 8(e)'s prescription for C5): hpcx_spmv_allgather — the row block keeps
+    # GLOBAL column ids, every rank's slice of x is gathered into a full-length x (64 MiB in all, one
+    # grouped ncclSend/ncclRecv), and the block runs the kernel hpcx_csr_create picks for it (HUB)
+    t = time.time()
+    G = hp.DeviceCsr(ctx, hp.CsrMatrix(rp_blk, col_blk, val_blk, ncols=nr))
+    setup_gather = time.time() - t
+    del rp_blk, col_blk, val_blk
+    # x travels in EQUAL slices (ncclAllGather: balanced traffic) while the rows stay nnz-balanced;
+    # with x split like the rows the rank owning the longest slice (56 % of x at N = 8) sends it N - 1
+    # times and the gather alone takes 0.68 ms (profiles/r3f_bench_n8.json)
+    xbounds = np.arange(world + 1, dtype=np.int64) * (nr // world)
+    e0, e1 = int(xbounds[rank]), int(xbounds[rank + 1])
+    xg = torch.full((nr,), float("nan"), dtype=torch.float32, device="cuda")
+    xg[e0:e1] = x[e0:e1]
+    x_own = xg[e0:e1]
+    stepg = lambda: G.spmv_allgather(xbounds, x_own, xg, y, stream)  # noqa: E731
+    torch.cuda.synchronize()
+    barrier()
+    y.fill_(float("nan"))
+    stepg()
+    stream.synchronize()
+    err_g = float((y - y_one[r0:r1]).abs().max() / y_one.abs().max())
+    if not err_g <= 3e-5 or not torch.equal(xg, x):
+        raise SystemExit(f"[rank {rank}] bench.py: gathered-x C5 product differs from the single-GPU one ({err_g:.2e})")
+    with torch.cuda.stream(stream):
+        for _ in range(3):
+            stepg()
+        dt, _, _ = time_steps(torch, stream, stepg, args.steps, barrier)
+    dt_gather = max_over_ranks(dt)
+    # the same block's kernel alone on the gathered x (no exchange): what the gather costs on top
+    stepk = lambda: G.spmv(xg, y, stream)  # noqa: E731
+    with torch.cuda.stream(stream):
+        stepk()
+        dt, _, _ = time_steps(torch, stream, stepk, args.steps, barrier)
+    dt_kernel = max_over_ranks(dt)
+    G.destroy()
+    log(f"[rank {rank}] C5 gathered-x block set up in {setup_gather:.1f}s; {dt_gather / args.steps * 1e3:.3f} ms per product "
+        f"(block kernel alone {dt / args.steps * 1e3:.3f} ms on this rank; halo push: {dt_push / args.steps * 1e3:.3f} ms)")
+    dt = min(dt_push, dt_gather)
     gbytes = algorithmic_bytes(nr, nnz_total, 4)
     peak, _ = measured_peak()
     e = {"metric": METRIC, "value": gbytes * args.steps / dt / 1e9, "unit": UNIT, "scaling": "strong",
          "ms_per_step": dt / args.steps * 1e3, "rows": nr, "nnz": nnz_total,
          "partition": f"{world} nnz-balanced row blocks; rank 0 owns rows [0, {int(bounds[1])})",
-         "halo_columns_rank0": int(L["nhalo"]) if rank == 0 else None,
-         "max_rel_diff_vs_single_gpu": err,
+         "halo_columns_rank0": halo_cols if rank == 0 else None,
+         "max_rel_diff_vs_single_gpu": max(err, err_g),
+         "variants": {
+             "halo_push_stream_kernel": {"value": gbytes * args.steps / dt_push / 1e9, "ms_per_step": dt_push / args.steps * 1e3,
+                                         "max_rel_diff_vs_single_gpu": err},
+             "allgather_x_block_kernel": {"value": gbytes * args.steps / dt_gather / 1e9, "ms_per_step": dt_gather / args.steps * 1e3,
+                                          "max_rel_diff_vs_single_gpu": err_g,
+                                          "kernel_only_ms_max_over_ranks": dt_kernel / args.steps * 1e3,
+                                          "call": "hpcx_spmv_allgather (x in equal slices by ncclAllGather, then the block's AUTO kernel on its nnz-balanced rows)"}},
          "roofline": {"bound": "hbm", "achieved": gbytes / world * args.steps / dt / 1e9, "peak": peak, "unit": "GB/s",
                       "frac": gbytes / world * args.steps / dt / 1e9 / peak,
-                      "note": "global algorithmic bytes / N per rank; STREAM kernel (the HUB kernel is single-GPU)"}}
-    D.destroy()
+                      "note": "global algorithmic bytes / N per rank, the faster of the two variants"}}
     return e
 
 

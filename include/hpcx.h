@@ -476,11 +476,14 @@ HPCX_API hpcx_status hpcx_spmv_dist(hpcx_csr A, const void *x_local, void *y_loc
  * test_hpc_benchmark.cpp:1356,1369-1377).  A is this rank's contiguous row block created with
  * GLOBAL column ids (nrows = bounds[rank+1] - bounds[rank], ncols = bounds[nranks]; no
  * hpcx_csr_set_halo), so hpcx_csr_create picks the kernel from the block's own structure — HUB for
- * power-law blocks.  x_local: this rank's nrows owned entries (device); x_full: device buffer of
- * ncols entries that receives every rank's slice (x_local may already be x_full + bounds[rank]);
- * y_local: nrows entries.  One grouped ncclSend/ncclRecv on `stream`, then the product on the same
- * stream.  For matrices whose rows reference most of x this moves fewer bytes than the halo lists
- * of hpcx_csr_set_halo and keeps the single-GPU kernel choice. */
+ * power-law blocks.  bounds (nranks + 1 entries, bounds[0] = 0, bounds[nranks] = ncols) says which
+ * slice of x each rank holds; it need not follow the row blocks.  x_local: this rank's slice
+ * (device); x_full: device buffer of ncols entries that receives every rank's slice (x_local may
+ * already be x_full + bounds[rank]); y_local: the nrows results of this rank's rows.  Equal slices
+ * travel by ncclAllGather, unequal ones by one grouped ncclSend/ncclRecv (slower: the owner of the
+ * longest slice sends it nranks - 1 times); either way on `stream`, followed by the product on
+ * the same stream.  For matrices whose rows reference most of x this moves fewer bytes than the
+ * halo lists of hpcx_csr_set_halo and keeps the single-GPU kernel choice. */
 HPCX_API hpcx_status hpcx_spmv_allgather(hpcx_csr A, const int64_t *bounds, const void *x_local,
                                          void *x_full, void *y_local, void *stream);
 

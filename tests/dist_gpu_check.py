@@ -287,6 +287,18 @@ def main():
                 assert_spmv_close(yd.cpu().numpy(), oracle.spmv(rp, col, val, x)[r0:r1],
                                   oracle.spmv_abs(rp, col, val, x)[r0:r1], tol)
                 assert bits_equal(xfull.cpu().numpy(), x), (rank, name, "gathered x")
+            # x in equal slices (ncclAllGather) while the rows stay in their own blocks
+            even = np.arange(world + 1, dtype=np.int64) * (n // world)
+            assert even[-1] == n
+            e0, e1 = int(even[rank]), int(even[rank + 1])
+            x = synth.field(45, n, val.dtype)
+            xfull.fill_(float("nan"))
+            xd = torch.from_numpy(x[e0:e1].copy()).cuda()
+            torch.cuda.synchronize()
+            D.spmv_allgather(even, xd, xfull, yd)
+            assert bits_equal(xfull.cpu().numpy(), x), (rank, name, "gathered x, equal slices")
+            assert_spmv_close(yd.cpu().numpy(), oracle.spmv(rp, col, val, x)[r0:r1],
+                              oracle.spmv_abs(rp, col, val, x)[r0:r1], tol)
             # owned slice already in place: x_local = x_full + bounds[rank]
             x = synth.field(44, n, val.dtype)
             xfull[r0:r1] = torch.from_numpy(x[r0:r1].copy()).cuda()
