@@ -527,6 +527,26 @@ def run_ours(args, rank: int, world: int, local: int):
     if world > 1:
         # the same product with the NCCL send/recv exchange, for comparison
         D.halo_transport(0)
+        # checked before it is timed: A*(3Y+5X+1) through gather_boundary_x_kernel -> grouped
+        # ncclSend/ncclRecv -> boundary rows must equal the closed form exactly on every rank
+        f, want = laplacian_of_linear(torch, rank, world)
+        torch.cuda.synchronize()
+        ctx.memcpy((xfull, hp.MEM_DEVICE), f, nloc * 8)
+        barrier()
+        yd.fill_(float("nan"))
+        torch.cuda.synchronize()  # the fill ran on torch's stream, the product runs on `stream`
+        D.spmv_dist(x_arg, yd, stream)
+        stream.synchronize()
+        if not torch.equal(yd, want):
+            raise SystemExit(f"[rank {rank}] bench.py: NCCL-transport A*(linear field) does not match the closed form")
+        del f, want
+        barrier()
+        ctx.memcpy((xfull, hp.MEM_DEVICE), xd, nloc * 8)
+        barrier()
+        if isinstance(dist_parity, dict):
+            dist_parity["spmv_nccl_transport_closed_form"] = "ok"
+            dist_parity["spmv_peer_transport_closed_forms"] = "ok"
+            dist_parity["spmv_dist_host_after_nan_poison"] = "ok"
         with torch.cuda.stream(stream):
             for _ in range(3):
                 step()
@@ -574,10 +594,12 @@ def run_ours(args, rank: int, world: int, local: int):
                     "call": "hpcx_spmv(A, x HOST, y HOST)" if world == 1 else
                             "hpcx_spmv_dist_host(A, x HOST, y HOST) per rank"},
             "gpu_launches": launches, "clocks": clocks, "checksum": checksum, "setup_ms": setup_ms,
-            "spmv_check": spmv_check, "dist_parity": dist_parity if world > 1 else "n/a (one GPU)",
+            "spmv_check": spmv_check,
             "extra": extra,
-            # last key on purpose: the stencil half of BASELINE.json's metric survives a truncated tail
+            # last keys on purpose: the stencil half of BASELINE.json's metric and the list of
+            # distributed checks (each one ends the run non-zero on a mismatch) survive a truncated tail
             "stencil": stencil,
+            "dist_parity": dist_parity if world > 1 else "n/a (one GPU)",
         }), flush=True)
     D.destroy()
     ctx.close()
@@ -982,6 +1004,7 @@ def c5_distributed(args, ctx, torch, stream, world, rank, barrier, max_over_rank
     torch.cuda.synchronize()
     barrier()
     y.fill_(float("nan"))
+    torch.cuda.synchronize()  # the fill ran on torch's stream, the product runs on `stream`
     stepg()
     stream.synchronize()
     err_g = float((y - y_one[r0:r1]).abs().max() / y_one.abs().max())
